@@ -1,0 +1,453 @@
+// TEST INFRASTRUCTURE ONLY (oracle). Flat C ABI over the UNMODIFIED reference hg::Scene so that tests and the
+// cpu_baseline leg of bench.py can build a scene from plain arrays, run the reference's own
+//   Scene::Update                (harfang/engine/scene.cpp:307-315)
+//   Scene::GetModelDisplayLists  (harfang/engine/scene.cpp:318-404)
+//   CullModelDisplayLists        (harfang/engine/render_pipeline.cpp:2098-2104)
+// and read back worlds / display lists / visible lists. This file is OUR code; it only #includes reference
+// headers. The only restated arithmetic is the bone-matrix product (render_pipeline.cpp:2172-2173 + to_bgfx
+// :59-62) because the reference function is static and interleaved with bgfx calls.
+// Never loaded by the product (harfang3d_b200/).
+#include "engine/animation.h"
+#include "engine/render_pipeline.h"
+#include "engine/scene.h"
+#include "foundation/frustum.h"
+#include "foundation/matrix3.h"
+#include "foundation/matrix4.h"
+#include "foundation/matrix44.h"
+#include "foundation/minmax.h"
+#include "foundation/projection.h"
+#include "foundation/quaternion.h"
+#include "foundation/log.h"
+
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <vector>
+
+using namespace hg;
+
+namespace {
+
+struct RefCtx {
+	PipelineResources resources;
+	std::unique_ptr<Scene> scene;
+	std::vector<ModelRef> models;
+	std::vector<NodeRef> nodes; // by creation order == flat node index
+	std::vector<AnimRef> anims;
+	std::vector<SceneAnimRef> scene_anims;
+	std::vector<ScenePlayAnimRef> play_anims;
+
+	std::vector<ModelDisplayList> opaque, transparent, culled;
+	std::vector<SkinnedModelDisplayList> opaque_skinned, transparent_skinned;
+
+	RefCtx() : scene(new Scene) {}
+	~RefCtx() { scene.reset(); }
+};
+
+inline Mat4 mat4_from(const float *m) { // 12 floats, row-major 3x4 == hg::Mat4::m
+	Mat4 o;
+	memcpy(o.m, m, sizeof(float) * 12);
+	return o;
+}
+
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+} // namespace
+
+extern "C" {
+
+void *hgref_create() {
+	set_log_level(LL_Error); // the path warns on invalid refs (scene.cpp:750-766); keep stderr quiet in tests
+	return new RefCtx;
+}
+
+void hgref_destroy(void *h) { delete static_cast<RefCtx *>(h); }
+
+// Model fixture exactly like harfang/tests/engine/scene.cpp:116-122: bounds + lists of BGFX_INVALID_HANDLEs + mats.
+int hgref_add_model(void *h, int n_lists, const float *bounds6, const uint16_t *mats, const int *bone_off, const uint16_t *bone_table, int n_bind,
+	const float *bind_pose12) {
+	auto *c = static_cast<RefCtx *>(h);
+	Model mdl;
+	for (int i = 0; i < n_lists; ++i) {
+		mdl.bounds.push_back(MinMax(Vec3(bounds6[i * 6 + 0], bounds6[i * 6 + 1], bounds6[i * 6 + 2]), Vec3(bounds6[i * 6 + 3], bounds6[i * 6 + 4], bounds6[i * 6 + 5])));
+		DisplayList dl{BGFX_INVALID_HANDLE, BGFX_INVALID_HANDLE, {}};
+		if (bone_off)
+			for (int j = bone_off[i]; j < bone_off[i + 1]; ++j)
+				dl.bones_table.push_back(bone_table[j]);
+		mdl.lists.push_back(dl);
+		mdl.mats.push_back(mats[i]);
+	}
+	for (int i = 0; i < n_bind; ++i)
+		mdl.bind_pose.push_back(mat4_from(bind_pose12 + i * 12));
+	char name[32];
+	snprintf(name, sizeof(name), "mdl%d", int(c->models.size()));
+	c->models.push_back(c->resources.models.Add(name, mdl));
+	return int(c->models.size()) - 1;
+}
+
+// Append n nodes. parent[] = flat node index (may be > own index) or -1; resolved in a second pass.
+// model[] = -1 -> no object component. has_transform may be NULL (all true).
+int hgref_add_nodes(void *h, int n, const float *trs9, const int32_t *parent, const uint8_t *disabled, const int32_t *model, const uint8_t *n_mats,
+	const uint32_t *transparent_mask, const uint8_t *has_transform) {
+	auto *c = static_cast<RefCtx *>(h);
+	auto &scene = *c->scene;
+	const size_t base = c->nodes.size();
+	scene.ReserveNodes(base + n);
+	scene.ReserveTransforms(base + n);
+	for (int i = 0; i < n; ++i) {
+		Node node = scene.CreateNode();
+		if (!has_transform || has_transform[i]) {
+			const float *t = trs9 + size_t(i) * 9;
+			node.SetTransform(scene.CreateTransform(Vec3(t[0], t[1], t[2]), Vec3(t[3], t[4], t[5]), Vec3(t[6], t[7], t[8])));
+		}
+		if (model && model[i] >= 0) {
+			std::vector<Material> mats(n_mats ? n_mats[i] : 1);
+			for (size_t k = 0; k < mats.size(); ++k)
+				if (transparent_mask && (transparent_mask[i] >> k) & 1)
+					SetMaterialBlendMode(mats[k], BM_Alpha);
+			node.SetObject(scene.CreateObject(c->models[model[i]], mats));
+		}
+		if (disabled && disabled[i])
+			node.Disable();
+		c->nodes.push_back(node.ref);
+	}
+	for (int i = 0; i < n; ++i)
+		if (parent && parent[i] >= 0) {
+			const auto trs_ref = scene.GetNodeTransformRef(c->nodes[base + i]);
+			if (scene.IsValidTransformRef(trs_ref))
+				scene.SetTransformParent(trs_ref, c->nodes[parent[i]]);
+		}
+	return int(c->nodes.size());
+}
+
+int hgref_set_object_bones(void *h, int node, int n, const int32_t *bone_nodes) {
+	auto *c = static_cast<RefCtx *>(h);
+	const auto obj = c->scene->GetNodeObjectRef(c->nodes[node]);
+	c->scene->SetObjectBoneCount(obj, n);
+	for (int i = 0; i < n; ++i)
+		c->scene->SetObjectBone(obj, i, bone_nodes[i] >= 0 ? c->nodes[bone_nodes[i]] : InvalidNodeRef);
+	return 0;
+}
+
+void hgref_set_trs(void *h, int node, const float *t) {
+	auto *c = static_cast<RefCtx *>(h);
+	c->scene->SetTransformTRS(c->scene->GetNodeTransformRef(c->nodes[node]), {Vec3(t[0], t[1], t[2]), Vec3(t[3], t[4], t[5]), Vec3(t[6], t[7], t[8])});
+}
+
+void hgref_get_trs(void *h, int node, float *t) {
+	auto *c = static_cast<RefCtx *>(h);
+	const auto trs = c->scene->GetTransformTRS(c->scene->GetNodeTransformRef(c->nodes[node]));
+	memcpy(t, &trs.pos, 12);
+	memcpy(t + 3, &trs.rot, 12);
+	memcpy(t + 6, &trs.scl, 12);
+}
+
+void hgref_set_parent(void *h, int node, int parent) {
+	auto *c = static_cast<RefCtx *>(h);
+	c->scene->SetTransformParent(c->scene->GetNodeTransformRef(c->nodes[node]), parent >= 0 ? c->nodes[parent] : InvalidNodeRef);
+}
+
+void hgref_enable_node(void *h, int node, int enable) {
+	auto *c = static_cast<RefCtx *>(h);
+	enable ? c->scene->EnableNode(c->nodes[node]) : c->scene->DisableNode(c->nodes[node]);
+}
+
+void hgref_destroy_node(void *h, int node) { static_cast<RefCtx *>(h)->scene->DestroyNode(static_cast<RefCtx *>(h)->nodes[node]); }
+int hgref_garbage_collect(void *h) { return int(static_cast<RefCtx *>(h)->scene->GarbageCollect()); }
+
+// scene.cpp:768-786 — pre-set world matrix (wins over ComputeWorldMatrices when called after ReadyWorldMatrices)
+void hgref_set_node_world(void *h, int node, const float *m12) {
+	auto *c = static_cast<RefCtx *>(h);
+	c->scene->SetNodeWorldMatrix(c->nodes[node], mat4_from(m12));
+}
+
+int hgref_node_transform_idx(void *h, int node) {
+	auto *c = static_cast<RefCtx *>(h);
+	const auto r = c->scene->GetNodeTransformRef(c->nodes[node]);
+	return c->scene->IsValidTransformRef(r) ? int(r.idx) : -1;
+}
+
+// ---- animation -----------------------------------------------------------------------------------------------
+// One hg::Anim per animated node. Track layout of the flat description (shared with the product's C ABI):
+//   vec3 Hermite key  = { int64 t; float v[3]; float tension; float bias; }  (animation.h:42-46)  -> 28 B packed as arrays
+//   quat linear key   = { int64 t; float v[4]; }                             (animation.h:28-31)
+// kinds: 0 Position, 1 Rotation (vec3 Euler), 2 Scale, 3 Rotation (quaternion, sets AF_UseQuaternionForRotation)
+int hgref_add_anim(void *h, int use_quat) {
+	auto *c = static_cast<RefCtx *>(h);
+	Anim anim;
+	anim.flags = use_quat ? AF_UseQuaternionForRotation : 0;
+	c->anims.push_back(c->scene->AddAnim(anim));
+	return int(c->anims.size()) - 1;
+}
+
+int hgref_anim_add_vec3_track(void *h, int anim, int kind, int n_keys, const int64_t *t, const float *v3, const float *tension, const float *bias) {
+	auto *c = static_cast<RefCtx *>(h);
+	Anim *a = c->scene->GetAnim(c->anims[anim]);
+	AnimTrackHermiteT<Vec3> trk;
+	trk.target = kind == 0 ? "Position" : (kind == 1 ? "Rotation" : "Scale");
+	for (int i = 0; i < n_keys; ++i) {
+		AnimKeyHermiteT<Vec3> k;
+		k.t = t[i];
+		k.v = Vec3(v3[i * 3], v3[i * 3 + 1], v3[i * 3 + 2]);
+		k.tension = tension ? tension[i] : 0.f;
+		k.bias = bias ? bias[i] : 0.f;
+		trk.keys.push_back(k);
+	}
+	a->vec3_tracks.push_back(trk);
+	return int(a->vec3_tracks.size()) - 1;
+}
+
+int hgref_anim_add_quat_track(void *h, int anim, int n_keys, const int64_t *t, const float *v4) {
+	auto *c = static_cast<RefCtx *>(h);
+	Anim *a = c->scene->GetAnim(c->anims[anim]);
+	AnimTrackT<Quaternion> trk;
+	trk.target = "Rotation";
+	for (int i = 0; i < n_keys; ++i)
+		trk.keys.push_back({t[i], Quaternion(v4[i * 4], v4[i * 4 + 1], v4[i * 4 + 2], v4[i * 4 + 3])});
+	a->quat_tracks.push_back(trk);
+	return int(a->quat_tracks.size()) - 1;
+}
+
+// SceneAnim = list of (node, anim) pairs (scene.h:104-114)
+int hgref_add_scene_anim(void *h, int n, const int32_t *node, const int32_t *anim, int64_t t_start, int64_t t_end) {
+	auto *c = static_cast<RefCtx *>(h);
+	SceneAnim sa;
+	sa.t_start = t_start;
+	sa.t_end = t_end;
+	for (int i = 0; i < n; ++i)
+		sa.node_anims.push_back({c->nodes[node[i]], c->anims[anim[i]]});
+	c->scene_anims.push_back(c->scene->AddSceneAnim(sa));
+	return int(c->scene_anims.size()) - 1;
+}
+
+// Scene::PlayAnim scene.cpp:2353-2375; loop_mode: 0 once, 1 infinite, 2 loop (animation.h:26)
+int hgref_play_anim(void *h, int scene_anim, int loop_mode, float t_scale) {
+	auto *c = static_cast<RefCtx *>(h);
+	c->play_anims.push_back(c->scene->PlayAnim(c->scene_anims[scene_anim], AnimLoopMode(loop_mode), E_Linear, UnspecifiedAnimTime, UnspecifiedAnimTime, false, t_scale));
+	return int(c->play_anims.size()) - 1;
+}
+
+int hgref_is_playing(void *h, int play) {
+	auto *c = static_cast<RefCtx *>(h);
+	return c->scene->IsPlaying(c->play_anims[play]) ? 1 : 0;
+}
+
+// ---- per-frame path ------------------------------------------------------------------------------------------
+void hgref_update(void *h, int64_t dt) { static_cast<RefCtx *>(h)->scene->Update(dt); }
+
+// The split form used by SceneUpdateSystemsImpl (scene_systems.cpp:153-179): phase 0 = Store+Ready+Anims, phase 1 = Compute+Fixup
+void hgref_update_phase(void *h, int phase, int64_t dt) {
+	auto &s = *static_cast<RefCtx *>(h)->scene;
+	if (phase == 0) {
+		s.StorePreviousWorldMatrices();
+		s.ReadyWorldMatrices();
+		s.UpdatePlayingAnims(dt);
+	} else {
+		s.ComputeWorldMatrices();
+		s.FixupPreviousWorldMatrices();
+	}
+}
+
+int hgref_world_count(void *h) { return int(static_cast<RefCtx *>(h)->scene->GetTransformWorldMatrices().size()); }
+
+int hgref_get_worlds(void *h, float *out12, int previous) {
+	auto &s = *static_cast<RefCtx *>(h)->scene;
+	const auto &w = previous ? s.GetPreviousTransformWorldMatrices() : s.GetTransformWorldMatrices();
+	if (out12 && !w.empty())
+		memcpy(out12, w.data(), w.size() * sizeof(Mat4));
+	return int(w.size());
+}
+
+// kind: 0 opaque, 1 transparent, 2 opaque skinned, 3 transparent skinned. Returns the 4 counts.
+void hgref_get_model_display_lists(void *h, int *counts4) {
+	auto *c = static_cast<RefCtx *>(h);
+	c->scene->GetModelDisplayLists(c->opaque, c->transparent, c->opaque_skinned, c->transparent_skinned, c->resources);
+	counts4[0] = int(c->opaque.size());
+	counts4[1] = int(c->transparent.size());
+	counts4[2] = int(c->opaque_skinned.size());
+	counts4[3] = int(c->transparent_skinned.size());
+}
+
+static int dump_lists(const std::vector<ModelDisplayList> &v, uint32_t *mtx_idx, uint16_t *mdl_idx, uint16_t *lst_idx) {
+	for (size_t i = 0; i < v.size(); ++i) {
+		if (mtx_idx) mtx_idx[i] = v[i].mtx_idx;
+		if (mdl_idx) mdl_idx[i] = v[i].mdl_idx;
+		if (lst_idx) lst_idx[i] = v[i].lst_idx;
+	}
+	return int(v.size());
+}
+
+int hgref_read_display_lists(void *h, int kind, uint32_t *mtx_idx, uint16_t *mdl_idx, uint16_t *lst_idx) {
+	auto *c = static_cast<RefCtx *>(h);
+	return dump_lists(kind == 0 ? c->opaque : c->transparent, mtx_idx, mdl_idx, lst_idx);
+}
+
+// skinned: per list 32 mtx_idxs + 32 bones_idxs + bone_count/mdl/lst (render_pipeline.h:596-603)
+int hgref_read_skinned_lists(void *h, int kind, uint32_t *mtx_idxs32, uint32_t *bones_idxs32, uint16_t *bone_count, uint16_t *mdl_idx, uint16_t *lst_idx) {
+	auto *c = static_cast<RefCtx *>(h);
+	const auto &v = kind == 2 ? c->opaque_skinned : c->transparent_skinned;
+	for (size_t i = 0; i < v.size(); ++i) {
+		memcpy(mtx_idxs32 + i * 32, v[i].mtx_idxs, 32 * 4);
+		memcpy(bones_idxs32 + i * 32, v[i].bones_idxs, 32 * 4);
+		bone_count[i] = v[i].bone_count;
+		mdl_idx[i] = v[i].mdl_idx;
+		lst_idx[i] = v[i].lst_idx;
+	}
+	return int(v.size());
+}
+
+// copy + CullModelDisplayLists exactly as scene_forward_pipeline.cpp:555-558 does; returns survivors, and for each survivor
+// its position in the un-culled list (src_pos) — the "visible index list" of the metric.
+int hgref_cull(void *h, int kind, const float *frustum24, uint32_t *src_pos, uint32_t *mtx_idx) {
+	auto *c = static_cast<RefCtx *>(h);
+	const auto &all = kind == 0 ? c->opaque : c->transparent;
+	Frustum f;
+	memcpy(f.data(), frustum24, 96);
+	c->culled = all;
+	CullModelDisplayLists(f, c->culled, c->scene->GetTransformWorldMatrices(), c->resources);
+	// stable compaction => survivors are a subsequence of `all`; recover positions by a merge walk
+	size_t j = 0;
+	for (size_t i = 0; i < c->culled.size(); ++i) {
+		while (memcmp(&all[j], &c->culled[i], sizeof(ModelDisplayList)) != 0)
+			++j;
+		if (src_pos) src_pos[i] = uint32_t(j);
+		if (mtx_idx) mtx_idx[i] = c->culled[i].mtx_idx;
+		++j;
+	}
+	return int(c->culled.size());
+}
+
+// restated: render_pipeline.cpp:2172-2173 (+ :2177-2181 for previous) and to_bgfx :59-62, using the reference's own operator*
+int hgref_bone_matrices(void *h, int kind, int previous, float *out16) {
+	auto *c = static_cast<RefCtx *>(h);
+	const auto &v = kind == 2 ? c->opaque_skinned : c->transparent_skinned;
+	const auto &mtxs = previous ? c->scene->GetPreviousTransformWorldMatrices() : c->scene->GetTransformWorldMatrices();
+	size_t n = 0;
+	for (const auto &dl : v) {
+		const auto &mdl = c->resources.models.Get_unsafe_(dl.mdl_idx);
+		for (int j = 0; j < dl.bone_count; ++j, ++n) {
+			const Mat4 m = mtxs[dl.mtx_idxs[j]] * mdl.bind_pose[dl.bones_idxs[j]];
+			const float o[16] = {m.m[0][0], m.m[1][0], m.m[2][0], 0.f, m.m[0][1], m.m[1][1], m.m[2][1], 0.f, m.m[0][2], m.m[1][2], m.m[2][2], 0.f, m.m[0][3],
+				m.m[1][3], m.m[2][3], 1.f};
+			if (out16) memcpy(out16 + n * 16, o, 64);
+		}
+	}
+	return int(n);
+}
+
+// ---- view / frustum (a12.3) ------------------------------------------------------------------------------------
+// ComputePerspectiveProjectionMatrix (projection.cpp:29-37) + MakeFrustum(proj, world) (frustum.cpp:17-28).
+// ComputePerspectiveViewState itself is avoided because it calls bgfx::getCaps() (render_pipeline.cpp:76).
+void hgref_make_perspective_frustum(float znear, float zfar, float fov, float ar_x, float ar_y, const float *cam_world12, float *out24) {
+	const Mat44 proj = ComputePerspectiveProjectionMatrix(znear, zfar, FovToZoomFactor(fov), Vec2(ar_x, ar_y));
+	const Frustum f = MakeFrustum(proj, mat4_from(cam_world12));
+	memcpy(out24, f.data(), 96);
+}
+
+void hgref_make_ortho_frustum(float znear, float zfar, float size, float ar_x, float ar_y, const float *cam_world12, float *out24) {
+	const Mat44 proj = ComputeOrthographicProjectionMatrix(znear, zfar, size, Vec2(ar_x, ar_y));
+	const Frustum f = MakeFrustum(proj, mat4_from(cam_world12));
+	memcpy(out24, f.data(), 96);
+}
+
+// ---- math probes: let tests pin the port / GPU path against the reference's own functions and golden vectors ----
+void hgref_transformation_mat4(const float *trs9, float *out12) {
+	const Mat4 m = TransformationMat4(Vec3(trs9[0], trs9[1], trs9[2]), Vec3(trs9[3], trs9[4], trs9[5]), Vec3(trs9[6], trs9[7], trs9[8]));
+	memcpy(out12, m.m, 48);
+}
+void hgref_mat4_mul(const float *a12, const float *b12, float *out12) {
+	const Mat4 m = mat4_from(a12) * mat4_from(b12);
+	memcpy(out12, m.m, 48);
+}
+void hgref_inverse_fast(const float *a12, float *out12) {
+	const Mat4 m = InverseFast(mat4_from(a12));
+	memcpy(out12, m.m, 48);
+}
+void hgref_minmax_transform(const float *m12, const float *mm6, float *out6) {
+	const MinMax o = mat4_from(m12) * MinMax(Vec3(mm6[0], mm6[1], mm6[2]), Vec3(mm6[3], mm6[4], mm6[5]));
+	memcpy(out6, &o.mn, 12);
+	memcpy(out6 + 3, &o.mx, 12);
+}
+int hgref_test_visibility(const float *frustum24, const float *mm6) {
+	Frustum f;
+	memcpy(f.data(), frustum24, 96);
+	return int(TestVisibility(f, MinMax(Vec3(mm6[0], mm6[1], mm6[2]), Vec3(mm6[3], mm6[4], mm6[5]))));
+}
+void hgref_quat_to_euler(const float *q4, float *out3) { // scene.cpp:2172 : ToEuler(Normalize(rot))
+	const Vec3 e = ToEuler(Normalize(Quaternion(q4[0], q4[1], q4[2], q4[3])));
+	memcpy(out3, &e, 12);
+}
+// Evaluate(AnimTrackHermiteT<Vec3>) animation.h:155-169; returns kf interval through GetIntervalKeys :109-128
+int hgref_eval_vec3_track(int n_keys, const int64_t *t, const float *v3, const float *tension, const float *bias, int64_t at, float *out3, int *kf) {
+	AnimTrackHermiteT<Vec3> trk;
+	for (int i = 0; i < n_keys; ++i) {
+		AnimKeyHermiteT<Vec3> k;
+		k.t = t[i];
+		k.v = Vec3(v3[i * 3], v3[i * 3 + 1], v3[i * 3 + 2]);
+		k.tension = tension ? tension[i] : 0.f;
+		k.bias = bias ? bias[i] : 0.f;
+		trk.keys.push_back(k);
+	}
+	Vec3 v(out3[0], out3[1], out3[2]);
+	const bool r = Evaluate(trk, at, v);
+	memcpy(out3, &v, 12);
+	if (kf) {
+		kf[0] = kf[1] = -1;
+		kf[2] = GetIntervalKeys<AnimTrackHermiteT<Vec3>, Vec3>(trk, at, kf[0], kf[1]) ? 1 : 0;
+	}
+	return r ? 1 : 0;
+}
+int hgref_eval_quat_track(int n_keys, const int64_t *t, const float *v4, int64_t at, float *out4) {
+	AnimTrackT<Quaternion> trk;
+	for (int i = 0; i < n_keys; ++i)
+		trk.keys.push_back({t[i], Quaternion(v4[i * 4], v4[i * 4 + 1], v4[i * 4 + 2], v4[i * 4 + 3])});
+	Quaternion q(out4[0], out4[1], out4[2], out4[3]);
+	const bool r = Evaluate(trk, at, q);
+	memcpy(out4, &q, 16);
+	return r ? 1 : 0;
+}
+float hgref_sinf(float x) { return sinf(x); } // the libm the reference links (matrix3.cpp:199-204)
+float hgref_cosf(float x) { return cosf(x); }
+
+// ---- CPU baseline timing (bench.py cpu_baseline / --impl reference). One frame = the reference's own
+// Scene::Update + GetModelDisplayLists + copy + CullModelDisplayLists(opaque) [+ transparent], single thread (the path has no threads).
+// out4 = seconds spent in {Update, GetModelDisplayLists, Cull(incl. copy), bones}, summed over frames. Returns visible count of last frame.
+int hgref_time_frames(void *h, int frames, int64_t dt, const float *frustum24, int with_bones, double *out4) {
+	auto *c = static_cast<RefCtx *>(h);
+	Frustum f;
+	memcpy(f.data(), frustum24, 96);
+	out4[0] = out4[1] = out4[2] = out4[3] = 0;
+	int visible = 0;
+	std::vector<float> bones;
+	for (int i = 0; i < frames; ++i) {
+		const double t0 = now_s();
+		c->scene->Update(dt);
+		const double t1 = now_s();
+		c->scene->GetModelDisplayLists(c->opaque, c->transparent, c->opaque_skinned, c->transparent_skinned, c->resources);
+		const double t2 = now_s();
+		c->culled = c->opaque;
+		CullModelDisplayLists(f, c->culled, c->scene->GetTransformWorldMatrices(), c->resources);
+		visible = int(c->culled.size());
+		if (!c->transparent.empty()) {
+			auto tr = c->transparent;
+			CullModelDisplayLists(f, tr, c->scene->GetTransformWorldMatrices(), c->resources);
+			visible += int(tr.size());
+		}
+		const double t3 = now_s();
+		if (with_bones) {
+			const int n = hgref_bone_matrices(h, 2, 0, nullptr);
+			bones.resize(size_t(n) * 16);
+			hgref_bone_matrices(h, 2, 0, bones.data());
+		}
+		const double t4 = now_s();
+		out4[0] += t1 - t0;
+		out4[1] += t2 - t1;
+		out4[2] += t3 - t2;
+		out4[3] += t4 - t3;
+	}
+	return visible;
+}
+
+} // extern "C"
