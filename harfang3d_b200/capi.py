@@ -1,0 +1,248 @@
+"""ctypes binding of include/hgb200.h. One method per C entry point, same names and argument meaning; errors raise HgbError
+with hgb_last_error(). Arrays are numpy, C-contiguous, exact dtype (checked) — nothing is converted silently."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = 0xFFFFFFFF
+NOT_PLAYING = -(2**63)
+ENTRY_DISABLED = 0x01
+KIND_OPAQUE, KIND_TRANSPARENT = 0, 1
+
+
+class HgbError(RuntimeError):
+    pass
+
+
+def library_path():
+    return os.path.join(_HERE, "libhgb200.so")
+
+
+class Track(C.Structure):
+    _fields_ = [("target_slot", C.c_uint32), ("key_off", C.c_uint32), ("key_count", C.c_uint32), ("play", C.c_uint16), ("kind", C.c_uint8),
+                ("pad", C.c_uint8)]
+
+
+TRACK_DTYPE = np.dtype([("target_slot", "<u4"), ("key_off", "<u4"), ("key_count", "<u4"), ("play", "<u2"), ("kind", "u1"), ("pad", "u1")])
+
+_u32, _i, _p, _sz = C.c_uint32, C.c_int, C.c_void_p, C.c_size_t
+
+# name -> (restype, argtypes). Kept in one table so tests can check that every symbol of include/hgb200.h is exported.
+SIGNATURES = {
+    "hgb_last_error": (C.c_char_p, []),
+    "hgb_device_count": (_i, []),
+    "hgb_create": (_p, [_i, _p]),
+    "hgb_destroy": (None, [_p]),
+    "hgb_set_stream": (_i, [_p, _p]),
+    "hgb_sync": (_i, [_p]),
+    "hgb_set_topology": (_i, [_p, _u32, _p, _p]),
+    "hgb_upload_trs": (_i, [_p, _u32, _u32, _p]),
+    "hgb_set_preset_world": (_i, [_p, _u32, _p, _p]),
+    "hgb_set_bounds": (_i, [_p, _u32, _p]),
+    "hgb_set_display_entries": (_i, [_p, _i, _u32, _p, _p, _p, _p]),
+    "hgb_set_entry_flags": (_i, [_p, _i, _u32, _u32, _p]),
+    "hgb_set_skins": (_i, [_p, _u32, _p, _p, _u32, _p]),
+    "hgb_set_anim_keys": (_i, [_p, _u32, _p, _p, _p, _p, _u32, _p, _p]),
+    "hgb_set_tracks": (_i, [_p, _u32, _p, _u32]),
+    "hgb_set_views": (_i, [_p, _u32, _p]),
+    "hgb_set_instance_views": (_i, [_p, _u32, _p, _p]),
+    "hgb_update": (_i, [_p, _u32, _p, _i]),
+    "hgb_cull": (_i, [_p]),
+    "hgb_bone_matrices": (_i, [_p, _i]),
+    "hgb_get_worlds": (_i, [_p, _u32, _u32, _p, _i]),
+    "hgb_get_trs": (_i, [_p, _u32, _u32, _p]),
+    "hgb_get_visible_count": (_i, [_p, _i, _u32, _p]),
+    "hgb_get_visible": (_i, [_p, _i, _u32, _p, _u32, _p]),
+    "hgb_get_instance_offsets": (_i, [_p, _p]),
+    "hgb_get_bone_matrices": (_i, [_p, _p, _i]),
+    "hgb_device_ptr": (_p, [_p, _i]),
+    "hgb_launch_count": (C.c_uint64, [_p]),
+    "hgb_level_count": (_u32, [_p]),
+    "hgb_is_identity_order": (_i, [_p]),
+    "hgb_time_begin": (_i, [_p]),
+    "hgb_time_end": (_i, [_p, _p]),
+    "hgb_flush_l2": (_i, [_p, _sz]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load libhgb200.so (once). Fails loudly if it was not built — there is no fallback implementation."""
+    global _lib
+    if _lib is None:
+        path = library_path()
+        if not os.path.exists(path):
+            raise HgbError("%s is missing: build it with `make -C harfang3d_b200` (or __graft_entry__.build()). "
+                           "There is no CPU or PyTorch fallback for this path." % path)
+        L = C.CDLL(path)
+        for name, (res, args) in SIGNATURES.items():
+            f = getattr(L, name)
+            f.restype, f.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def _ptr(a, dtype, what):
+    if a is None:
+        return None
+    if not isinstance(a, np.ndarray) or a.dtype != np.dtype(dtype) or not a.flags["C_CONTIGUOUS"]:
+        raise TypeError("%s must be a C-contiguous numpy array of dtype %s" % (what, np.dtype(dtype)))
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """One hgb_ctx = one hg::Scene (or one batch of scene instances)."""
+
+    def __init__(self, device=0, use_graph=True):
+        self._L = lib()
+        opt = (C.c_int * 8)(1 if use_graph else 0, 0, 0, 0, 0, 0, 0, 0)
+        self._h = self._L.hgb_create(device, C.cast(opt, C.c_void_p))
+        if not self._h:
+            raise HgbError(self._L.hgb_last_error().decode())
+        self._h = C.c_void_p(self._h)
+        self.n_slots = 0
+        self.n_entries = [0, 0]
+        self.n_bones = 0
+        self.n_inst = 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.hgb_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise HgbError(self._L.hgb_last_error().decode())
+
+    # ---- edit time ----
+    def set_stream(self, cuda_stream_ptr):
+        self._ck(self._L.hgb_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
+
+    def sync(self):
+        self._ck(self._L.hgb_sync(self._h))
+
+    def set_topology(self, parent_slot, used=None):
+        n = len(parent_slot)
+        self._ck(self._L.hgb_set_topology(self._h, n, _ptr(parent_slot, np.uint32, "parent_slot"), _ptr(used, np.uint8, "used")))
+        self.n_slots = n
+
+    def upload_trs(self, trs9, first=0):
+        assert trs9.ndim == 2 and trs9.shape[1] == 9
+        self._ck(self._L.hgb_upload_trs(self._h, first, trs9.shape[0], _ptr(trs9, np.float32, "trs9")))
+
+    def set_preset_world(self, slots, mats12):
+        self._ck(self._L.hgb_set_preset_world(self._h, len(slots), _ptr(slots, np.uint32, "slots"), _ptr(mats12, np.float32, "mats12")))
+
+    def set_bounds(self, minmax6):
+        self._ck(self._L.hgb_set_bounds(self._h, minmax6.shape[0], _ptr(minmax6, np.float32, "minmax6")))
+
+    def set_display_entries(self, kind, mtx_slot, bounds_idx, flags=None, view=None):
+        self._ck(self._L.hgb_set_display_entries(self._h, kind, len(mtx_slot), _ptr(mtx_slot, np.uint32, "mtx_slot"), _ptr(bounds_idx, np.uint32, "bounds_idx"),
+                                                 _ptr(flags, np.uint8, "flags"), _ptr(view, np.uint16, "view")))
+        self.n_entries[kind] = len(mtx_slot)
+
+    def set_entry_flags(self, kind, first, flags):
+        self._ck(self._L.hgb_set_entry_flags(self._h, kind, first, len(flags), _ptr(flags, np.uint8, "flags")))
+
+    def set_skins(self, mtx_slot, bind_idx, bind_pose12):
+        self._ck(self._L.hgb_set_skins(self._h, len(mtx_slot), _ptr(mtx_slot, np.uint32, "mtx_slot"), _ptr(bind_idx, np.uint32, "bind_idx"),
+                                       bind_pose12.shape[0], _ptr(bind_pose12, np.float32, "bind_pose12")))
+        self.n_bones = len(mtx_slot)
+
+    def set_anim_keys(self, v3_t, v3_val, v3_tension, v3_bias, q_t, q_val):
+        self._ck(self._L.hgb_set_anim_keys(self._h, len(v3_t), _ptr(v3_t, np.int64, "v3_t"), _ptr(v3_val, np.float32, "v3_val"),
+                                           _ptr(v3_tension, np.float32, "v3_tension"), _ptr(v3_bias, np.float32, "v3_bias"), len(q_t),
+                                           _ptr(q_t, np.int64, "q_t"), _ptr(q_val, np.float32, "q_val")))
+
+    def set_tracks(self, tracks, n_play):
+        self._ck(self._L.hgb_set_tracks(self._h, len(tracks), _ptr(tracks, TRACK_DTYPE, "tracks"), n_play))
+
+    def set_views(self, frustum24):
+        f = np.ascontiguousarray(frustum24, np.float32).reshape(-1, 24)
+        self._ck(self._L.hgb_set_views(self._h, f.shape[0], _ptr(f, np.float32, "frustum24")))
+
+    def set_instance_views(self, frustum24, inst_entry_start):
+        f = np.ascontiguousarray(frustum24, np.float32).reshape(-1, 24)
+        self._ck(self._L.hgb_set_instance_views(self._h, f.shape[0], _ptr(f, np.float32, "frustum24"), _ptr(inst_entry_start, np.uint32, "inst_entry_start")))
+        self.n_inst = f.shape[0]
+
+    # ---- per frame ----
+    def update(self, play_t=None, fused_cull=False):
+        n = 0 if play_t is None else len(play_t)
+        self._ck(self._L.hgb_update(self._h, n, _ptr(play_t, np.int64, "play_t"), 1 if fused_cull else 0))
+
+    def cull(self):
+        self._ck(self._L.hgb_cull(self._h))
+
+    def bone_matrices(self, with_previous=False):
+        self._ck(self._L.hgb_bone_matrices(self._h, 1 if with_previous else 0))
+
+    # ---- results ----
+    def get_worlds(self, first=0, count=None, previous=False, out=None):
+        count = self.n_slots - first if count is None else count
+        out = np.empty((count, 12), np.float32) if out is None else out
+        self._ck(self._L.hgb_get_worlds(self._h, first, count, _ptr(out, np.float32, "out"), 1 if previous else 0))
+        return out
+
+    def get_trs(self, first=0, count=None):
+        count = self.n_slots - first if count is None else count
+        out = np.empty((count, 9), np.float32)
+        self._ck(self._L.hgb_get_trs(self._h, first, count, _ptr(out, np.float32, "out")))
+        return out
+
+    def get_visible_count(self, kind=0, view=0):
+        n = C.c_uint32(0)
+        self._ck(self._L.hgb_get_visible_count(self._h, kind, view, C.byref(n)))
+        return n.value
+
+    def get_visible(self, kind=0, view=0, out=None):
+        out = np.empty(max(self.n_entries[kind], 1), np.uint32) if out is None else out
+        n = C.c_uint32(0)
+        self._ck(self._L.hgb_get_visible(self._h, kind, view, _ptr(out, np.uint32, "out"), len(out), C.byref(n)))
+        return out[: n.value]
+
+    def get_instance_offsets(self):
+        out = np.empty(self.n_inst + 1, np.uint32)
+        self._ck(self._L.hgb_get_instance_offsets(self._h, _ptr(out, np.uint32, "out")))
+        return out
+
+    def get_bone_matrices(self, previous=False):
+        out = np.empty((self.n_bones, 16), np.float32)
+        self._ck(self._L.hgb_get_bone_matrices(self._h, _ptr(out, np.float32, "out"), 1 if previous else 0))
+        return out
+
+    # ---- introspection ----
+    def device_ptr(self, which):
+        return self._L.hgb_device_ptr(self._h, which)
+
+    @property
+    def launch_count(self):
+        return self._L.hgb_launch_count(self._h)
+
+    @property
+    def level_count(self):
+        return self._L.hgb_level_count(self._h)
+
+    @property
+    def identity_order(self):
+        return bool(self._L.hgb_is_identity_order(self._h))
+
+    def time_begin(self):
+        self._ck(self._L.hgb_time_begin(self._h))
+
+    def time_end(self):
+        ms = C.c_float(0)
+        self._ck(self._L.hgb_time_end(self._h, C.byref(ms)))
+        return ms.value
+
+    def flush_l2(self, nbytes=256 << 20):
+        self._ck(self._L.hgb_flush_l2(self._h, nbytes))

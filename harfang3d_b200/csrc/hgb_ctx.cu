@@ -1,0 +1,284 @@
+// Host side of the C ABI (include/hgb200.h): owns the device-resident, depth-sorted SoA mirror of one hg::Scene (or one batch of
+// scene instances), rebuilds it when the hierarchy is edited, and enqueues the per-frame kernels. No CPU fallback exists:
+// every entry point that computes needs the CUDA device the context was created on.
+#include "../../include/hgb200.h"
+#include "hgb_kernels2.cuh"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace hgb;
+
+static thread_local std::string g_err;
+
+static int fail(const char *fmt, ...) {
+	char buf[512];
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(buf, sizeof(buf), fmt, ap);
+	va_end(ap);
+	g_err = buf;
+	return 1;
+}
+
+#define CK(call)                                                                                                                                               \
+	do {                                                                                                                                                       \
+		cudaError_t e_ = (call);                                                                                                                               \
+		if (e_ != cudaSuccess)                                                                                                                                 \
+			return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__);                                                           \
+	} while (0)
+
+namespace {
+
+// device buffer that only grows; contents are NOT preserved across a grow
+struct DBuf {
+	void *p = nullptr;
+	size_t cap = 0;
+	cudaError_t reserve(size_t bytes) {
+		if (bytes <= cap)
+			return cudaSuccess;
+		if (p)
+			cudaFree(p);
+		p = nullptr;
+		cap = 0;
+		const size_t want = (bytes + 255) & ~size_t(255);
+		cudaError_t e = cudaMalloc(&p, want);
+		if (e == cudaSuccess)
+			cap = want;
+		return e;
+	}
+	void release() {
+		if (p)
+			cudaFree(p);
+		p = nullptr;
+		cap = 0;
+	}
+	template <typename T> T *as() const { return static_cast<T *>(p); }
+};
+
+struct HBuf { // pinned host staging, grows
+	void *p = nullptr;
+	size_t cap = 0;
+	cudaError_t reserve(size_t bytes) {
+		if (bytes <= cap)
+			return cudaSuccess;
+		if (p)
+			cudaFreeHost(p);
+		p = nullptr;
+		cap = 0;
+		cudaError_t e = cudaMallocHost(&p, bytes);
+		if (e == cudaSuccess)
+			cap = bytes;
+		return e;
+	}
+	void release() {
+		if (p)
+			cudaFreeHost(p);
+		p = nullptr;
+		cap = 0;
+	}
+	template <typename T> T *as() const { return static_cast<T *>(p); }
+};
+
+struct EntryTable {
+	uint32_t n = 0;
+	std::vector<uint32_t> mtx_slot, bounds_idx;
+	std::vector<uint8_t> flags;
+	std::vector<uint16_t> view;
+	DBuf mtx_pos, meta, view_d, vis; // per entry (entry order)
+	DBuf out[kMaxViews];             // surviving indices per view
+	DBuf counts;                     // kMaxViews uint32
+	DBuf ticket, status;             // compaction scratch (per view slices)
+	uint32_t n_tiles = 0;
+};
+
+} // namespace
+
+struct hgb_ctx {
+	int device = 0;
+	bool use_graph = true;
+	cudaStream_t own_stream = nullptr, stream = nullptr;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	uint64_t launches = 0;
+
+	// topology (host)
+	uint32_t n_slots = 0, n_pos = 0; // n_pos = used slots (positions [0,n_pos) are live; holes get positions >= n_pos)
+	std::vector<uint32_t> pos_of_slot, slot_of_pos, parent_pos_h;
+	std::vector<uint32_t> level_off; // level d = positions [level_off[d], level_off[d+1])
+	bool identity = true;
+	bool entries_dirty = true; // CSR by position must be rebuilt
+
+	// device scene
+	DBuf trs, parent_pos, world[2], preset, pos_of_slot_d;
+	size_t trs_stride = 0;
+	int cur = 0; // world[cur] = current frame
+	bool preset_pending = false, preset_dirty = false;
+	DBuf preset_pos, preset_mat;
+	uint32_t n_preset = 0;
+
+	DBuf bounds;
+	uint32_t n_bounds = 0;
+	EntryTable ent[2];
+	DBuf ent_off, pent, pent_view;
+
+	Views views{};          // planes -> view_planes (device)
+	DBuf view_planes;
+	bool instance_mode = false;
+	uint32_t n_inst = 0;
+	DBuf inst_planes, inst_start, inst_rank;
+
+	// skins
+	uint32_t n_bones = 0;
+	DBuf bone_mtx_pos, bone_bind_idx, bind_pose, bone_out[2];
+	std::vector<uint32_t> bone_mtx_slot;
+
+	// animation
+	DBuf v3_t, v3_val, v3_bias, q_t, q_val, tracks_d, play_t_d;
+	uint32_t n_tracks = 0, n_play = 0;
+	std::vector<hgb_track> tracks_h;
+	std::vector<uint32_t> round_off; // tracks sorted so that tracks sharing a target lane fall in successive rounds
+	HBuf play_t_h;
+	std::vector<int64_t> play_t_v;
+
+	HBuf staging;  // pinned host staging for uploads/downloads
+	DBuf staging_d; // device staging (slot-order data before scatter / after gather)
+	DBuf flush;
+
+	// CUDA graph of one frame
+	cudaGraphExec_t graph_exec[2][2] = {}; // [fused][world-buffer parity]
+	bool graph_valid[2][2] = {};
+	uint64_t graph_kernels[2][2] = {};
+};
+
+static void invalidate_graph(hgb_ctx *c) {
+	for (auto &a : c->graph_valid)
+		for (bool &v : a)
+			v = false;
+}
+
+extern "C" {
+
+const char *hgb_last_error(void) { return g_err.c_str(); }
+
+int hgb_device_count(void) {
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess)
+		return 0;
+	return n;
+}
+
+hgb_ctx *hgb_create(int device, const hgb_options *opt) {
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n == 0) {
+		fail("hgb_create: no CUDA device (%s). This library has no CPU path.", e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+		return nullptr;
+	}
+	if (device < 0 || device >= n) {
+		fail("hgb_create: device %d out of range (%d devices)", device, n);
+		return nullptr;
+	}
+	if ((e = cudaSetDevice(device)) != cudaSuccess) {
+		fail("cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+		return nullptr;
+	}
+	hgb_ctx *c = new hgb_ctx;
+	c->device = device;
+	c->use_graph = opt ? opt->use_graph != 0 : true;
+	if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
+		cudaEventCreate(&c->ev1) != cudaSuccess) {
+		fail("hgb_create: stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+		delete c;
+		return nullptr;
+	}
+	c->stream = c->own_stream;
+	c->views.n_views = 0;
+	if (c->view_planes.reserve(kMaxViews * 96) != cudaSuccess) {
+		fail("hgb_create: out of device memory");
+		delete c;
+		return nullptr;
+	}
+	c->views.planes = c->view_planes.as<float4>();
+	return c;
+}
+
+void hgb_destroy(hgb_ctx *c) {
+	if (!c)
+		return;
+	cudaSetDevice(c->device);
+	cudaStreamSynchronize(c->stream);
+	for (auto &a : c->graph_exec)
+		for (cudaGraphExec_t g : a)
+			if (g)
+				cudaGraphExecDestroy(g);
+	DBuf *bufs[] = {&c->trs, &c->parent_pos, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
+		&c->pent, &c->pent_view, &c->inst_planes, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
+		&c->bone_out[1], &c->v3_t, &c->v3_val, &c->v3_bias, &c->q_t, &c->q_val, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->view_planes};
+	for (DBuf *b : bufs)
+		b->release();
+	for (auto &t : c->ent) {
+		DBuf *eb[] = {&t.mtx_pos, &t.meta, &t.view_d, &t.vis, &t.counts, &t.ticket, &t.status};
+		for (DBuf *b : eb)
+			b->release();
+		for (auto &o : t.out)
+			o.release();
+	}
+	c->staging.release();
+	c->play_t_h.release();
+	cudaEventDestroy(c->ev0);
+	cudaEventDestroy(c->ev1);
+	cudaStreamDestroy(c->own_stream);
+	delete c;
+}
+
+int hgb_set_stream(hgb_ctx *c, void *s) {
+	if (!c)
+		return fail("null context");
+	CK(cudaStreamSynchronize(c->stream));
+	c->stream = s ? static_cast<cudaStream_t>(s) : c->own_stream;
+	invalidate_graph(c);
+	return 0;
+}
+
+int hgb_sync(hgb_ctx *c) {
+	if (!c)
+		return fail("null context");
+	CK(cudaSetDevice(c->device));
+	CK(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+uint64_t hgb_launch_count(hgb_ctx *c) { return c ? c->launches : 0; }
+uint32_t hgb_level_count(hgb_ctx *c) { return c && !c->level_off.empty() ? uint32_t(c->level_off.size() - 1) : 0; }
+int hgb_is_identity_order(hgb_ctx *c) { return c && c->identity ? 1 : 0; }
+
+int hgb_time_begin(hgb_ctx *c) {
+	if (!c)
+		return fail("null context");
+	CK(cudaEventRecord(c->ev0, c->stream));
+	return 0;
+}
+int hgb_time_end(hgb_ctx *c, float *ms) {
+	if (!c)
+		return fail("null context");
+	CK(cudaEventRecord(c->ev1, c->stream));
+	CK(cudaEventSynchronize(c->ev1));
+	CK(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+	return 0;
+}
+int hgb_flush_l2(hgb_ctx *c, size_t bytes) {
+	if (!c)
+		return fail("null context");
+	CK(c->flush.reserve(bytes));
+	CK(cudaMemsetAsync(c->flush.p, 0x5a, bytes, c->stream));
+	return 0;
+}
+
+} // extern "C"
+
+#include "hgb_ctx_scene.inl"
+#include "hgb_ctx_frame.inl"

@@ -1,0 +1,339 @@
+// Per-frame half of the C ABI: enqueue (or replay as a CUDA graph) the kernels of one Scene::Update (+ fused cull), stand-alone
+// cull, bone matrices, and the device->host getters. Included by hgb_ctx.cu.
+
+static SceneDev scene_dev(hgb_ctx *c, bool with_preset) {
+	SceneDev s{};
+	s.trs = c->trs.as<float>();
+	s.trs_stride = c->trs_stride;
+	s.parent_pos = c->parent_pos.as<uint32_t>();
+	s.world = c->world[c->cur].as<float>();
+	s.preset = with_preset ? c->preset.as<uint8_t>() : nullptr;
+	s.ent_off = c->ent_off.as<uint32_t>();
+	s.pent = c->pent.as<uint2>();
+	s.bounds6 = c->bounds.as<float>();
+	s.vis[0] = c->ent[0].vis.as<uint8_t>();
+	s.vis[1] = c->ent[1].vis.as<uint8_t>();
+	s.inst_planes = c->inst_planes.as<float4>();
+	s.pent_view = c->pent_view.as<uint16_t>();
+	return s;
+}
+
+// compaction of every (kind, view) list from the vis bytes; returns the number of kernels enqueued through *n_k
+static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k) {
+	const int n_views = c->instance_mode ? 1 : c->views.n_views;
+	for (int k = 0; k < 2; ++k) {
+		EntryTable &t = c->ent[k];
+		if (!t.n)
+			continue;
+		CK(cudaMemsetAsync(t.ticket.p, 0, kMaxViews * 4, c->stream));
+		CK(cudaMemsetAsync(t.status.p, 0, size_t(t.n_tiles) * n_views * 4, c->stream));
+		for (int v = 0; v < n_views; ++v) {
+			CompactDev d{};
+			d.vis = t.vis.as<uint8_t>();
+			d.n = t.n;
+			d.bit = uint32_t(v);
+			d.out = t.out[v].as<uint32_t>();
+			d.count = t.counts.as<uint32_t>() + v;
+			d.ticket = t.ticket.as<uint32_t>() + v;
+			d.status = t.status.as<uint32_t>() + size_t(v) * t.n_tiles;
+			k_compact<<<t.n_tiles, kCompactThreads, 0, c->stream>>>(d);
+			++*n_k;
+		}
+		if (c->instance_mode && k == 0 && c->n_inst) {
+			k_segment_ranks<<<grid_for(c->n_inst * 32), 256, 0, c->stream>>>(t.vis.as<uint8_t>(), 0, c->inst_start.as<uint32_t>(), c->n_inst,
+				t.status.as<uint32_t>(), c->inst_rank.as<uint32_t>());
+			++*n_k;
+		}
+	}
+	CK(cudaGetLastError());
+	return 0;
+}
+
+static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint64_t *n_k) {
+	// animation sampling: one launch per write round (normally one)
+	if (c->n_tracks && c->n_play) {
+		AnimDev a{};
+		a.tracks = c->tracks_d.as<Track>();
+		a.play_t = c->play_t_d.as<int64_t>();
+		a.v3_t = c->v3_t.as<int64_t>();
+		a.v3_val = c->v3_val.as<float4>();
+		a.v3_bias = c->v3_bias.as<float>();
+		a.q_t = c->q_t.as<int64_t>();
+		a.q_val = c->q_val.as<float4>();
+		a.trs = c->trs.as<float>();
+		a.trs_stride = c->trs_stride;
+		for (size_t r = 0; r + 1 < c->round_off.size(); ++r) {
+			const uint32_t first = c->round_off[r], cnt = c->round_off[r + 1] - first;
+			if (!cnt)
+				continue;
+			k_sample_tracks<<<grid_for(cnt), 256, 0, c->stream>>>(a, first, cnt);
+			++*n_k;
+		}
+	}
+	// world matrices, level by level (+ fused visibility)
+	const SceneDev s = scene_dev(c, with_preset);
+	const bool do_fused = fused && (c->ent[0].n || c->ent[1].n);
+	for (size_t d = 0; d + 1 < c->level_off.size(); ++d) {
+		const uint32_t b = c->level_off[d], e = c->level_off[d + 1];
+		if (e == b)
+			continue;
+		const dim3 g = grid_for(e - b);
+		if (!do_fused)
+			k_update_level<false, false><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
+		else if (c->instance_mode)
+			k_update_level<true, true><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
+		else
+			k_update_level<true, false><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
+		++*n_k;
+	}
+	CK(cudaGetLastError());
+	if (do_fused)
+		return enqueue_compaction(c, n_k);
+	return 0;
+}
+
+// graph path: one executable graph per (fused flag, world-buffer parity); re-captured after any edit (invalidate_graph)
+static int launch_frame_graph(hgb_ctx *c, bool fused) {
+	const int f = fused ? 1 : 0, par = c->cur;
+	if (!c->graph_valid[f][par]) {
+		if (c->graph_exec[f][par]) {
+			cudaGraphExecDestroy(c->graph_exec[f][par]);
+			c->graph_exec[f][par] = nullptr;
+		}
+		cudaGraph_t g = nullptr;
+		uint64_t k = 0;
+		CK(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+		const int rc = enqueue_frame_kernels(c, fused, false, &k);
+		const cudaError_t e = cudaStreamEndCapture(c->stream, &g);
+		if (rc)
+			return 1;
+		if (e != cudaSuccess)
+			return fail("cudaStreamEndCapture: %s", cudaGetErrorString(e));
+		CK(cudaGraphInstantiate(&c->graph_exec[f][par], g, 0));
+		cudaGraphDestroy(g);
+		c->graph_kernels[f][par] = k;
+		c->graph_valid[f][par] = true;
+	}
+	CK(cudaGraphLaunch(c->graph_exec[f][par], c->stream));
+	c->launches += c->graph_kernels[f][par];
+	return 0;
+}
+
+extern "C" {
+
+int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cull) {
+	if (!c)
+		return fail("null context");
+	if (!c->n_slots)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	if (fused_cull && !c->instance_mode && c->views.n_views == 0 && (c->ent[0].n || c->ent[1].n))
+		return fail("hgb_update(fused_cull): no views set (hgb_set_views / hgb_set_instance_views)");
+	if (prepare_tables(c))
+		return 1;
+	if (n_play > c->n_play)
+		return fail("hgb_update: %u play clocks given but hgb_set_tracks declared %u play slots", n_play, c->n_play);
+
+	// a2 StorePreviousWorldMatrices: pointer swap. a3 ReadyWorldMatrices: the 'updated' flags only exist as the preset mask.
+	c->cur ^= 1;
+	const bool with_preset = c->preset_pending;
+	if (c->preset_dirty) {
+		CK(cudaMemsetAsync(c->preset.p, 0, c->n_slots, c->stream));
+		c->preset_dirty = false;
+	}
+	if (with_preset) {
+		k_apply_presets<<<grid_for(c->n_preset, 128), 128, 0, c->stream>>>(c->preset_pos.as<uint32_t>(), c->preset_mat.as<float4>(), c->n_preset,
+			c->world[c->cur].as<float4>(), c->preset.as<uint8_t>());
+		++c->launches;
+		c->preset_pending = false;
+		c->preset_dirty = true;
+	}
+	if (c->n_play) {
+		// pageable source on purpose: the runtime stages small pageable copies before returning, so the vector can be reused next
+		// frame without waiting for this frame's copy
+		c->play_t_v.resize(c->n_play);
+		for (uint32_t i = 0; i < c->n_play; ++i)
+			c->play_t_v[i] = i < n_play ? play_t[i] : INT64_MIN;
+		CK(cudaMemcpyAsync(c->play_t_d.p, c->play_t_v.data(), size_t(c->n_play) * 8, cudaMemcpyHostToDevice, c->stream));
+	}
+
+	const bool fused = fused_cull != 0;
+	if (!c->use_graph || with_preset) {
+		uint64_t k = 0;
+		if (enqueue_frame_kernels(c, fused, with_preset, &k))
+			return 1;
+		c->launches += k;
+		return 0;
+	}
+	return launch_frame_graph(c, fused);
+}
+
+int hgb_cull(hgb_ctx *c) {
+	if (!c)
+		return fail("null context");
+	CK(cudaSetDevice(c->device));
+	if (!c->instance_mode && c->views.n_views == 0)
+		return fail("hgb_cull: no views set");
+	if (prepare_tables(c))
+		return 1;
+	uint64_t k = 0;
+	for (int kind = 0; kind < 2; ++kind) {
+		EntryTable &t = c->ent[kind];
+		if (!t.n)
+			continue;
+		CullDev d{};
+		d.mtx_pos = t.mtx_pos.as<uint32_t>();
+		d.meta = t.meta.as<uint32_t>();
+		d.view = t.view_d.as<uint16_t>();
+		d.world = c->world[c->cur].as<float>();
+		d.bounds6 = c->bounds.as<float>();
+		d.inst_planes = c->inst_planes.as<float4>();
+		d.vis = t.vis.as<uint8_t>();
+		d.n = t.n;
+		if (c->instance_mode)
+			k_cull_flags<true><<<grid_for(t.n), 256, 0, c->stream>>>(d, c->views);
+		else
+			k_cull_flags<false><<<grid_for(t.n), 256, 0, c->stream>>>(d, c->views);
+		++k;
+	}
+	CK(cudaGetLastError());
+	if (enqueue_compaction(c, &k))
+		return 1;
+	c->launches += k;
+	return 0;
+}
+
+int hgb_bone_matrices(hgb_ctx *c, int with_previous) {
+	if (!c)
+		return fail("null context");
+	if (!c->n_bones)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	if (prepare_tables(c))
+		return 1;
+	BoneDev b{};
+	b.mtx_pos = c->bone_mtx_pos.as<uint32_t>();
+	b.bind_idx = c->bone_bind_idx.as<uint32_t>();
+	b.bind_pose = c->bind_pose.as<float>();
+	b.world = c->world[c->cur].as<float>();
+	b.world_prev = with_previous ? c->world[c->cur ^ 1].as<float>() : nullptr;
+	b.out = c->bone_out[0].as<float>();
+	b.out_prev = c->bone_out[1].as<float>();
+	b.n = c->n_bones;
+	k_bone_matrices<<<grid_for(b.n), 256, 0, c->stream>>>(b);
+	++c->launches;
+	CK(cudaGetLastError());
+	return 0;
+}
+
+// ---- getters -------------------------------------------------------------------------------------------------------------
+int hgb_get_worlds(hgb_ctx *c, uint32_t first, uint32_t count, float *out12, int previous) {
+	if (!c)
+		return fail("null context");
+	if (uint64_t(first) + count > c->n_slots)
+		return fail("hgb_get_worlds: range outside the topology");
+	if (!count)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	const float *w = c->world[previous ? c->cur ^ 1 : c->cur].as<float>();
+	if (c->identity) {
+		CK(cudaMemcpyAsync(out12, w + size_t(first) * 12, size_t(count) * 48, cudaMemcpyDeviceToHost, c->stream));
+	} else {
+		CK(c->staging_d.reserve(size_t(count) * 48));
+		k_gather_worlds<<<grid_for(count * 3), 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(w), c->pos_of_slot_d.as<uint32_t>(), first, count,
+			c->staging_d.as<float4>());
+		++c->launches;
+		CK(cudaMemcpyAsync(out12, c->staging_d.p, size_t(count) * 48, cudaMemcpyDeviceToHost, c->stream));
+	}
+	CK(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+int hgb_get_trs(hgb_ctx *c, uint32_t first, uint32_t count, float *out9) {
+	if (!c)
+		return fail("null context");
+	if (uint64_t(first) + count > c->n_slots)
+		return fail("hgb_get_trs: range outside the topology");
+	if (!count)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	CK(c->staging_d.reserve(size_t(count) * 36));
+	k_gather_trs<<<grid_for(count), 256, 0, c->stream>>>(c->trs.as<float>(), c->trs_stride, c->identity ? nullptr : c->pos_of_slot_d.as<uint32_t>(), first, count,
+		c->staging_d.as<float>());
+	++c->launches;
+	CK(cudaMemcpyAsync(out9, c->staging_d.p, size_t(count) * 36, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+int hgb_get_visible_count(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_count) {
+	if (!c)
+		return fail("null context");
+	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews))
+		return fail("hgb_get_visible_count: bad kind/view");
+	*out_count = 0;
+	if (!c->ent[kind].n)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	CK(cudaMemcpyAsync(out_count, c->ent[kind].counts.as<uint32_t>() + view, 4, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+int hgb_get_visible(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_idx, uint32_t capacity, uint32_t *out_count) {
+	uint32_t n = 0;
+	if (hgb_get_visible_count(c, kind, view, &n))
+		return 1;
+	if (out_count)
+		*out_count = n;
+	if (n > capacity)
+		return fail("hgb_get_visible: %u survivors but capacity %u", n, capacity);
+	if (n) {
+		CK(cudaMemcpyAsync(out_idx, c->ent[kind].out[view].p, size_t(n) * 4, cudaMemcpyDeviceToHost, c->stream));
+		CK(cudaStreamSynchronize(c->stream));
+	}
+	return 0;
+}
+
+int hgb_get_instance_offsets(hgb_ctx *c, uint32_t *out) {
+	if (!c)
+		return fail("null context");
+	if (!c->instance_mode)
+		return fail("hgb_get_instance_offsets: not in instance mode");
+	CK(cudaSetDevice(c->device));
+	if (c->n_inst)
+		CK(cudaMemcpyAsync(out, c->inst_rank.p, size_t(c->n_inst) * 4, cudaMemcpyDeviceToHost, c->stream));
+	uint32_t total = 0;
+	if (hgb_get_visible_count(c, 0, 0, &total))
+		return 1;
+	out[c->n_inst] = total;
+	return 0;
+}
+
+int hgb_get_bone_matrices(hgb_ctx *c, float *out16, int previous) {
+	if (!c)
+		return fail("null context");
+	if (!c->n_bones)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	CK(cudaMemcpyAsync(out16, c->bone_out[previous ? 1 : 0].p, size_t(c->n_bones) * 64, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+void *hgb_device_ptr(hgb_ctx *c, int which) {
+	if (!c)
+		return nullptr;
+	switch (which) {
+	case 0: return c->world[c->cur].p;
+	case 1: return c->world[c->cur ^ 1].p;
+	case 2: return c->ent[0].out[0].p;
+	case 3: return c->ent[0].counts.p;
+	case 4: return c->bone_out[0].p;
+	case 5: return c->inst_rank.p;
+	case 6: return c->trs.p;
+	default: return nullptr;
+	}
+}
+
+} // extern "C"

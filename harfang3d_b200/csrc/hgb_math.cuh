@@ -1,0 +1,210 @@
+// Device arithmetic of the scene-update path, written so that every result is bit-identical to the reference's
+// g++ -O2 x86-64 build (SSE2 scalar float, no contraction) on the same inputs:
+//   * this TU is compiled with -fmad=false, so no float/double mul+add is ever contracted; the only fused operations
+//     are the explicit fma() calls below, which mirror glibc's -mfma build of sinf/cosf;
+//   * division and sqrt are the IEEE round-to-nearest forms (nvcc defaults -prec-div=true -prec-sqrt=true, -ftz=false).
+// Reference anchors are given per function (paths relative to the reference's harfang/ directory).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace hgb {
+
+struct Mat4 { // == hg::Mat4::m, row-major 3x4 (foundation/matrix4.h:25)
+	float m[3][4];
+};
+
+// ---- sinf/cosf --------------------------------------------------------------------------------------------------
+// The reference calls libm sinf/cosf (foundation/matrix3.cpp:199-204). glibc 2.39 (sysdeps/ieee754/flt-32/sincosf.h)
+// reduces in double, evaluates a double polynomial and rounds once to float; on FMA-capable hosts each a*b+c is one
+// fused op. Restating that in FP64 here gives the same float for all 2^32 inputs (host-side proof: oracle/exhaustive_sincos.c),
+// which is what makes visibility bit-exact instead of "1 ulp away near a frustum plane". B200 has a full-rate FP64 pipe;
+// ~16 DP ops per angle stay hidden under the HBM traffic of the kernel.
+__device__ __forceinline__ uint32_t abstop12(float x) { return (__float_as_uint(x) >> 20) & 0x7ffu; }
+
+// 4/pi as a sliding window of 32-bit words, for |x| >= 120 (rare: Euler angles are normally within a few turns)
+__device__ const uint32_t c_inv_pio4[24] = {0xa2, 0xa2f9, 0xa2f983, 0xa2f9836e, 0xf9836e4e, 0x836e4e44, 0x6e4e4415, 0x4e441529, 0x441529fc, 0x1529fc27,
+	0x29fc2757, 0xfc2757d1, 0x2757d1f5, 0x57d1f534, 0xd1f534dd, 0xf534ddc0, 0x34ddc0db, 0xddc0db62, 0xc0db6295, 0xdb629599, 0x6295993c, 0x95993c43, 0x993c4390,
+	0x3c439041};
+
+__device__ __noinline__ double sc_reduce_large(uint32_t xi, int &n_out) {
+	const uint32_t *arr = &c_inv_pio4[(xi >> 26) & 15];
+	const int shift = (xi >> 23) & 7;
+	xi = (xi & 0xffffffu) | 0x800000u;
+	xi <<= shift;
+	uint64_t res0 = uint32_t(xi * arr[0]);
+	const uint64_t res1 = uint64_t(xi) * arr[4];
+	const uint64_t res2 = uint64_t(xi) * arr[8];
+	res0 = (res2 >> 32) | (res0 << 32);
+	res0 += res1;
+	const uint64_t n = (res0 + (1ULL << 61)) >> 62;
+	res0 -= n << 62;
+	n_out = int(n);
+	return __dmul_rn(double(int64_t(res0)), 0x1.921FB54442D18p-62);
+}
+
+// polynomial pair on the reduced argument; q selects the table (q&2 flips the cosine polynomial's sign)
+__device__ __forceinline__ float sc_sin_poly(double x, double x2) {
+	const double x3 = __dmul_rn(x, x2);
+	const double s1 = fma(x2, -0x1.994eb3774cf24p-13, 0x1.1107605230bc4p-7);
+	const double x7 = __dmul_rn(x3, x2);
+	const double s = fma(x3, -0x1.555545995a603p-3, x);
+	return __double2float_rn(fma(x7, s1, s));
+}
+__device__ __forceinline__ float sc_cos_poly(double x2, bool neg) {
+	const double sg = neg ? -1.0 : 1.0; // table[1] holds the negated cosine coefficients; negation is exact
+	const double x4 = __dmul_rn(x2, x2);
+	const double c2 = fma(x2, sg * 0x1.99343027bf8c3p-16, sg * -0x1.6c087e89a359dp-10);
+	const double c1 = fma(x2, sg * -0x1.ffffffd0c621cp-2, sg * 0x1p0);
+	const double x6 = __dmul_rn(x4, x2);
+	const double c = fma(x4, sg * 0x1.55553e1068f19p-5, c1);
+	return __double2float_rn(fma(x6, c2, c));
+}
+
+// sinf(y) and cosf(y) exactly as glibc computes them (each is an independent libm call in the reference; they share the
+// argument reduction, so it is done once here).
+__device__ __forceinline__ void sincos_libm(float y, float &s_out, float &c_out) {
+	const uint32_t top = abstop12(y);
+	double x = double(y);
+	if (top < 0x3f4u) { // |y| < pi/4  (abstop12(0x1.921FB6p-1f))
+		if (top < 0x398u) { // |y| < 2^-12
+			s_out = y;
+			c_out = 1.0f;
+			return;
+		}
+		const double x2 = __dmul_rn(x, x);
+		s_out = sc_sin_poly(x, x2);
+		c_out = sc_cos_poly(x2, false);
+		return;
+	}
+	int n, ns, nc; // quadrant; sign selectors for sin / cos
+	if (top < 0x42fu) { // |y| < 120
+		const double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);
+		n = (__double2int_rz(r) + 0x800000) >> 24;
+		x = fma(-double(n), 0x1.921FB54442D18p0, x);
+		ns = n;
+		nc = n + 1;
+	} else if (top < 0x7f8u) {
+		const uint32_t xi = __float_as_uint(y);
+		x = sc_reduce_large(xi, n);
+		ns = nc = n + int(xi >> 31);
+		// table switch also keys on n+sign here (s_sinf.c / s_cosf.c large path)
+		const double x2 = __dmul_rn(x, x);
+		const bool neg = (ns & 2) != 0;
+		const double sgn = ((ns & 3) == 1 || (ns & 3) == 2) ? -1.0 : 1.0; // sign[] = {1,-1,-1,1}
+		const double xs = __dmul_rn(x, sgn);
+		s_out = (n & 1) ? sc_cos_poly(x2, neg) : sc_sin_poly(xs, x2);
+		c_out = (n & 1) ? sc_sin_poly(xs, x2) : sc_cos_poly(x2, neg);
+		return;
+	} else {
+		s_out = c_out = y - y; // inf/nan -> nan
+		return;
+	}
+	const double x2 = __dmul_rn(x, x);
+	const bool neg = (n & 2) != 0;
+	const double sgn_s = ((ns & 3) == 1 || (ns & 3) == 2) ? -1.0 : 1.0;
+	const double sgn_c = ((nc & 3) == 1 || (nc & 3) == 2) ? -1.0 : 1.0;
+	// sinf: poly(x*sign[n&3], x2, n) ; cosf: poly(x*sign[(n+1)&3], x2, n^1)
+	if (n & 1) {
+		s_out = sc_cos_poly(x2, neg);
+		c_out = sc_sin_poly(__dmul_rn(x, sgn_c), x2);
+	} else {
+		s_out = sc_sin_poly(__dmul_rn(x, sgn_s), x2);
+		c_out = sc_cos_poly(x2, neg);
+	}
+}
+
+// ---- TransformationMat4(pos, euler, scale) ------------------------------------------------------------------------
+// foundation/matrix4.cpp:176-183 -> RotationMat3(e, RO_YXZ) foundation/matrix3.cpp:180-260. For euler_order_yxz the unpacked
+// axes are i=1 j=0 k=2 (odd, no repeat); the left-handed and the odd negations cancel exactly, leaving
+// angle_0 = e.y, angle_1 = e.x, angle_2 = e.z.
+__device__ __forceinline__ Mat4 transformation_mat4(float px, float py, float pz, float ex, float ey, float ez, float sx, float sy, float sz) {
+	float s0, c0, s1, c1, s2, c2;
+	sincos_libm(ey, s0, c0);
+	sincos_libm(ex, s1, c1);
+	sincos_libm(ez, s2, c2);
+	const float s0s2 = s0 * s2, s0c2 = s0 * c2, c0s2 = c0 * s2, c0c2 = c0 * c2;
+	const float r11 = c1 * c2, r10 = c1 * s2, r12 = -s1;
+	const float r01 = s1 * s0c2 - c0s2, r00 = s1 * s0s2 + c0c2, r02 = s0 * c1;
+	const float r21 = s1 * c0c2 + s0s2, r20 = s1 * c0s2 - s0c2, r22 = c0 * c1;
+	Mat4 o;
+	o.m[0][0] = r00 * sx, o.m[0][1] = r01 * sy, o.m[0][2] = r02 * sz, o.m[0][3] = px;
+	o.m[1][0] = r10 * sx, o.m[1][1] = r11 * sy, o.m[1][2] = r12 * sz, o.m[1][3] = py;
+	o.m[2][0] = r20 * sx, o.m[2][1] = r21 * sy, o.m[2][2] = r22 * sz, o.m[2][3] = pz;
+	return o;
+}
+
+// operator*(Mat4, Mat4) foundation/matrix4.cpp:31-44 — left-to-right sums, translation column adds a[r][3] last
+__device__ __forceinline__ Mat4 mat4_mul(const Mat4 &a, const Mat4 &b) {
+	Mat4 o;
+#pragma unroll
+	for (int r = 0; r < 3; ++r) {
+#pragma unroll
+		for (int c = 0; c < 3; ++c)
+			o.m[r][c] = a.m[r][0] * b.m[0][c] + a.m[r][1] * b.m[1][c] + a.m[r][2] * b.m[2][c];
+		o.m[r][3] = a.m[r][0] * b.m[0][3] + a.m[r][1] * b.m[1][3] + a.m[r][2] * b.m[2][3] + a.m[r][3];
+	}
+	return o;
+}
+
+__device__ __forceinline__ Mat4 load_mat4(const float *__restrict__ p) { // 48 B, 16-B aligned
+	const float4 *q = reinterpret_cast<const float4 *>(p);
+	const float4 a = q[0], b = q[1], c = q[2];
+	Mat4 o;
+	o.m[0][0] = a.x, o.m[0][1] = a.y, o.m[0][2] = a.z, o.m[0][3] = a.w;
+	o.m[1][0] = b.x, o.m[1][1] = b.y, o.m[1][2] = b.z, o.m[1][3] = b.w;
+	o.m[2][0] = c.x, o.m[2][1] = c.y, o.m[2][2] = c.z, o.m[2][3] = c.w;
+	return o;
+}
+__device__ __forceinline__ void store_mat4(float *__restrict__ p, const Mat4 &o) {
+	float4 *q = reinterpret_cast<float4 *>(p);
+	q[0] = make_float4(o.m[0][0], o.m[0][1], o.m[0][2], o.m[0][3]);
+	q[1] = make_float4(o.m[1][0], o.m[1][1], o.m[1][2], o.m[1][3]);
+	q[2] = make_float4(o.m[2][0], o.m[2][1], o.m[2][2], o.m[2][3]);
+}
+
+// ---- culling predicate -----------------------------------------------------------------------------------------------
+// operator*(Mat4, MinMax) foundation/minmax.cpp:226-244 (Arvo) followed by TestVisibility(Frustum, MinMax)
+// foundation/frustum.cpp:59-79. Returns true when the entry SURVIVES CullModelDisplayLists (engine/render_pipeline.cpp:2098-2104),
+// i.e. visibility != V_Outside.
+struct Aabb {
+	float mn[3], mx[3];
+};
+
+__device__ __forceinline__ Aabb minmax_transform(const Mat4 &m, const float *__restrict__ b6) {
+	Aabb o;
+#pragma unroll
+	for (int j = 0; j < 3; ++j) {
+		float mn = m.m[j][3], mx = m.m[j][3];
+#pragma unroll
+		for (int i = 0; i < 3; ++i) {
+			const float a = m.m[j][i] * b6[i], b = m.m[j][i] * b6[3 + i];
+			if (a < b) {
+				mn += a;
+				mx += b;
+			} else {
+				mn += b;
+				mx += a;
+			}
+		}
+		o.mn[j] = mn;
+		o.mx[j] = mx;
+	}
+	return o;
+}
+
+__device__ __forceinline__ bool survives_frustum(const float4 *__restrict__ planes, const Aabb &bb) {
+	const float cx = bb.mn[0] + bb.mx[0], cy = bb.mn[1] + bb.mx[1], cz = bb.mn[2] + bb.mx[2];
+	const float ex = bb.mx[0] - bb.mn[0], ey = bb.mx[1] - bb.mn[1], ez = bb.mx[2] - bb.mn[2];
+	bool inside = true;
+#pragma unroll
+	for (int n = 0; n < 6; ++n) {
+		const float4 p = __ldg(planes + n);
+		const float d = p.x * cx + p.y * cy + p.z * cz;
+		const float r = fabsf(p.x) * ex + fabsf(p.y) * ey + fabsf(p.z) * ez;
+		inside = inside && !(d - r > -p.w * 2.f);
+	}
+	return inside;
+}
+
+} // namespace hgb

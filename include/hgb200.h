@@ -1,0 +1,132 @@
+/* hgb200 — C ABI of the B200-native scene-update path for HARFANG scenes.
+ *
+ * The reference (harfang3d/harfang3d v3.2.7) has no FFI around this path: it is the C++ members of hg::Scene plus the free
+ * function CullModelDisplayLists. A maintainer binds this library UNDER that C++ API: hg::Scene keeps its
+ * containers and handles; the per-frame functions below replace the bodies of
+ *
+ *   Scene::StorePreviousWorldMatrices / ReadyWorldMatrices / ComputeWorldMatrices / FixupPreviousWorldMatrices
+ *                                                    harfang/engine/scene.cpp:280-304 (driver: Scene::Update :307-315)
+ *   Scene::UpdatePlayingAnims -> EvaluateBoundAnim    harfang/engine/scene.cpp:2380-2431, :2154-2181 (transform targets)
+ *   Scene::GetModelDisplayLists (enable-flag logic)   harfang/engine/scene.cpp:318-404
+ *   CullModelDisplayLists                             harfang/engine/render_pipeline.cpp:2098-2104
+ *   bone-matrix loop of _DrawSkinnedModelDisplayLists harfang/engine/render_pipeline.cpp:2172-2181
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on error; the message is in hgb_last_error() (thread-local). Nothing throws.
+ *     (The reference's own convention is warn()+neutral value, harfang/engine/scene.cpp:750-766; the C++ facade maps codes to that.)
+ *   - one context = one hg::Scene, or one batch of scene instances laid out in one slot space. A context is not thread-safe;
+ *     contexts are independent. All work is enqueued on the context's CUDA stream; getters synchronise that stream.
+ *   - "slot" = transform component index (the index of Scene::GetTransformWorldMatrices(), scene.cpp:361). Matrices are
+ *     hg::Mat4 bit layout: float[12], row-major 3x4 (harfang/foundation/matrix4.h:25). TRS = hg::TransformTRS: pos, rot (Euler
+ *     radians, order YXZ), scale = float[9] (harfang/engine/node.h:36-38). Frustum = 6 planes x {x,y,z,w}, order
+ *     Top,Bottom,Left,Right,Near,Far = hg::Frustum (harfang/foundation/frustum.h:14-16).
+ *   - there is NO CPU fallback: without a CUDA device hgb_create fails.
+ */
+#ifndef HGB200_H
+#define HGB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hgb_ctx hgb_ctx;
+
+#define HGB_ROOT 0xffffffffu      /* parent_slot value of a root transform */
+#define HGB_MAX_VIEWS 8           /* frusta tested per entry in one pass (view + 4 PSSM splits + spot = 6 in the reference) */
+#define HGB_ENTRY_DISABLED 0x01   /* node has NF_Disabled|NF_InstanceDisabled (harfang/engine/scene.h:166-170) */
+#define HGB_KIND_OPAQUE 0
+#define HGB_KIND_TRANSPARENT 1
+#define HGB_NOT_PLAYING INT64_MIN /* play_t value of a play slot with nothing playing */
+
+typedef struct hgb_options {
+	int use_graph; /* 1: capture the per-frame launch sequence in a CUDA graph (default), 0: plain stream launches */
+	int reserved[7];
+} hgb_options;
+
+/* one bound animation track (BoundToNodeAnim entry, harfang/engine/scene.h:74-88) */
+typedef struct hgb_track {
+	uint32_t target_slot; /* transform slot of the bound node */
+	uint32_t key_off;     /* first key in the pool of its kind */
+	uint32_t key_count;
+	uint16_t play;        /* play slot whose clock drives it (ScenePlayAnim, scene.h:884-895) */
+	uint8_t kind;         /* 0 "Position", 1 "Rotation" Euler vec3, 2 "Scale" (Hermite vec3) ; 3 "Rotation" quaternion (linear) */
+	uint8_t pad;
+} hgb_track;
+
+const char *hgb_last_error(void);
+int hgb_device_count(void);
+
+hgb_ctx *hgb_create(int device, const hgb_options *opt /* nullable */);
+void hgb_destroy(hgb_ctx *);
+int hgb_set_stream(hgb_ctx *, void *cuda_stream); /* cudaStream_t; NULL = the context's own stream */
+int hgb_sync(hgb_ctx *);
+
+/* ---- scene description (edit time) ---- */
+/* Transform hierarchy. parent_slot[i] = slot of the parent's transform (node->transform hop already resolved,
+ * scene.cpp:268) or HGB_ROOT; used[i]==0 marks holes of the slot list (vector_list.h). Rebuilds the depth-sorted layout. */
+int hgb_set_topology(hgb_ctx *, uint32_t n_slots, const uint32_t *parent_slot, const uint8_t *used /* nullable */);
+/* TRS of slots [first, first+count) — dirty-range upload. */
+int hgb_upload_trs(hgb_ctx *, uint32_t first, uint32_t count, const float *trs9);
+/* SetNodeWorldMatrix overrides (scene.cpp:768-786) for the NEXT hgb_update only. */
+int hgb_set_preset_world(hgb_ctx *, uint32_t n, const uint32_t *slot, const float *mat12);
+
+/* MinMax table: Model::bounds of every (model, list) in use (render_pipeline.h:419-424). */
+int hgb_set_bounds(hgb_ctx *, uint32_t n_bounds, const float *minmax6);
+/* Display entries of one kind, in the reference's emission order (node index x list index, scene.cpp:330-364).
+ * flags: HGB_ENTRY_DISABLED. view: per-entry instance id for hgb_set_instance_views (nullable). */
+int hgb_set_display_entries(hgb_ctx *, int kind, uint32_t n, const uint32_t *mtx_slot, const uint32_t *bounds_idx, const uint8_t *flags,
+	const uint16_t *view /* nullable */);
+int hgb_set_entry_flags(hgb_ctx *, int kind, uint32_t first, uint32_t count, const uint8_t *flags);
+
+/* Skins: one record per (skinned display list, bone), in list order (SkinnedModelDisplayList::mtx_idxs/bones_idxs,
+ * render_pipeline.h:596-603, resolved as in scene.cpp:365-394); bind_idx indexes the bind-pose pool. */
+int hgb_set_skins(hgb_ctx *, uint32_t n_bones, const uint32_t *mtx_slot, const uint32_t *bind_idx, uint32_t n_bind, const float *bind_pose12);
+
+/* Animation keys and bound tracks. vec3 pool = AnimKeyHermiteT<Vec3> (animation.h:42-46), quat pool = AnimKeyT<Quaternion>. */
+int hgb_set_anim_keys(hgb_ctx *, uint32_t n_vec3_keys, const int64_t *v3_t, const float *v3_val3, const float *v3_tension, const float *v3_bias,
+	uint32_t n_quat_keys, const int64_t *q_t, const float *q_val4);
+int hgb_set_tracks(hgb_ctx *, uint32_t n_tracks, const hgb_track *tracks, uint32_t n_play_slots);
+
+/* Views. Either up to HGB_MAX_VIEWS frusta tested against every entry, or one frustum per scene instance (entry -> view[]). */
+int hgb_set_views(hgb_ctx *, uint32_t n_views, const float *frustum24);
+int hgb_set_instance_views(hgb_ctx *, uint32_t n_instances, const float *frustum24, const uint32_t *inst_entry_start /* n_instances+1, kind 0 */);
+
+/* ---- per frame ---- */
+/* Scene::Update body: swap current/previous worlds, clear updated flags, apply presets, sample the tracks at play_t[]
+ * (clocks are stepped by the caller exactly as scene.cpp:2386-2413 — int64, host side), propagate world matrices level by level.
+ * fused_cull != 0: the visibility of every display entry is evaluated in the same pass and compacted (hgb_cull is implied). */
+int hgb_update(hgb_ctx *, uint32_t n_play, const int64_t *play_t, int fused_cull);
+/* CullModelDisplayLists against the current views using the stored world matrices. */
+int hgb_cull(hgb_ctx *);
+/* Bone matrices of every skin record (and the previous-frame twin). */
+int hgb_bone_matrices(hgb_ctx *, int with_previous);
+
+/* ---- results (device -> host; each call synchronises the stream) ---- */
+int hgb_get_worlds(hgb_ctx *, uint32_t first, uint32_t count, float *out12, int previous);
+int hgb_get_trs(hgb_ctx *, uint32_t first, uint32_t count, float *out9);
+int hgb_get_visible_count(hgb_ctx *, int kind, uint32_t view, uint32_t *out_count);
+/* surviving entry indices (into the table given to hgb_set_display_entries), ascending = reference order */
+int hgb_get_visible(hgb_ctx *, int kind, uint32_t view, uint32_t *out_idx, uint32_t capacity, uint32_t *out_count);
+/* instance mode: exclusive offsets of every instance's survivors inside the kind-0 list, n_instances+1 values */
+int hgb_get_instance_offsets(hgb_ctx *, uint32_t *out_offsets);
+int hgb_get_bone_matrices(hgb_ctx *, float *out16, int previous);
+
+/* ---- introspection for benchmarks / interop ---- */
+/* device pointers: 0 worlds, 1 previous worlds, 2 visible list (kind 0, view 0), 3 visible count (kind 0, view 0), 4 bone matrices,
+ * 5 instance offsets, 6 TRS SoA */
+void *hgb_device_ptr(hgb_ctx *, int which);
+uint64_t hgb_launch_count(hgb_ctx *);   /* kernels launched by this context so far (graph launches count their kernel nodes) */
+uint32_t hgb_level_count(hgb_ctx *);
+int hgb_is_identity_order(hgb_ctx *);   /* 1 when slot order already is the depth-sorted order (no shuffle kernels needed) */
+/* CUDA-event stopwatch on the context's stream: begin records an event, end records one, synchronises and returns the ms between. */
+int hgb_time_begin(hgb_ctx *);
+int hgb_time_end(hgb_ctx *, float *out_ms);
+/* Write `bytes` bytes of a scratch buffer (allocated on first use) — L2 flush between timed iterations. */
+int hgb_flush_l2(hgb_ctx *, size_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

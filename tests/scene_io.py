@@ -1,0 +1,98 @@
+"""TEST INFRASTRUCTURE: build the reference's hg::Scene (through oracle/_ref) from a FlatScene, and run reference frames."""
+import ctypes as C
+
+import numpy as np
+
+from tests.oracle_lib import P
+
+
+class RefScene:
+    def __init__(self, ref, fs):
+        self.L, self.fs = ref, fs
+        self.h = C.c_void_p(ref.hgref_create())
+        for m in fs.models:
+            L_ = m["bounds"].shape[0]
+            if m["bone_tables"] is not None:
+                off = np.cumsum([0] + [len(t) for t in m["bone_tables"]]).astype(np.int32)
+                tbl = np.concatenate(m["bone_tables"]).astype(np.uint16)
+            else:
+                off, tbl = None, None
+            bp = m["bind_pose"]
+            ref.hgref_add_model(self.h, L_, P(np.ascontiguousarray(m["bounds"], np.float32)), P(np.ascontiguousarray(m["mats"], np.uint16)),
+                                P(off), P(tbl), 0 if bp is None else bp.shape[0], None if bp is None else P(np.ascontiguousarray(bp, np.float32)))
+        ref.hgref_add_nodes(self.h, fs.n, P(np.ascontiguousarray(fs.trs)), P(fs.parent), P(fs.disabled), P(fs.model), P(fs.n_mats),
+                            P(fs.transparent_mask), None)
+        for node, b in fs.bones.items():
+            ref.hgref_set_object_bones(self.h, int(node), len(b), P(np.ascontiguousarray(b, np.int32)))
+        for a in range(len(fs.anim_node)):
+            ref.hgref_add_anim(self.h, int(fs.anim_use_quat[a]))
+        for k in range(len(fs.trk_anim)):
+            a, kind, off, cnt = int(fs.trk_anim[k]), int(fs.trk_kind[k]), int(fs.trk_key_off[k]), int(fs.trk_key_count[k])
+            if kind == 3:
+                ref.hgref_anim_add_quat_track(self.h, a, cnt, P(fs.q_t[off:off + cnt]), P(np.ascontiguousarray(fs.q_val[off:off + cnt])))
+            else:
+                ref.hgref_anim_add_vec3_track(self.h, a, kind, cnt, P(fs.v3_t[off:off + cnt]), P(np.ascontiguousarray(fs.v3_val[off:off + cnt])),
+                                              P(fs.v3_tension[off:off + cnt]), P(fs.v3_bias[off:off + cnt]))
+        for anims, ts, te in fs.scene_anims:
+            nodes = np.ascontiguousarray(fs.anim_node[anims], np.int32)
+            ref.hgref_add_scene_anim(self.h, len(anims), P(nodes), P(np.ascontiguousarray(anims, np.int32)), int(ts), int(te))
+        for sa, loop, scale in fs.plays:
+            ref.hgref_play_anim(self.h, sa, loop, scale)
+
+    def close(self):
+        if self.h:
+            self.L.hgref_destroy(self.h)
+            self.h = None
+
+    def update(self, dt):
+        self.L.hgref_update(self.h, int(dt))
+
+    def worlds(self, previous=False):
+        n = self.L.hgref_world_count(self.h) if not previous else self.L.hgref_get_worlds(self.h, None, 1)
+        w = np.zeros((n, 12), np.float32)
+        self.L.hgref_get_worlds(self.h, P(w), 1 if previous else 0)
+        return w
+
+    def trs(self, nodes):
+        out = np.zeros((len(nodes), 9), np.float32)
+        for i, nd in enumerate(nodes):
+            self.L.hgref_get_trs(self.h, int(nd), P(out[i]))
+        return out
+
+    def display_lists(self):
+        """returns counts and (mtx_idx, mdl_idx, lst_idx) of the opaque and transparent lists"""
+        counts = np.zeros(4, np.int32)
+        self.L.hgref_get_model_display_lists(self.h, P(counts))
+        out = {}
+        for kind in (0, 1):
+            n = int(counts[kind])
+            mtx, mdl, lst = np.zeros(n, np.uint32), np.zeros(n, np.uint16), np.zeros(n, np.uint16)
+            self.L.hgref_read_display_lists(self.h, kind, P(mtx), P(mdl), P(lst))
+            out[kind] = (mtx, mdl, lst)
+        return counts, out
+
+    def cull(self, kind, frustum24):
+        """copy + CullModelDisplayLists; returns the surviving (mtx_idx) sequence and positions in the un-culled list"""
+        counts = np.zeros(4, np.int32)
+        self.L.hgref_get_model_display_lists(self.h, P(counts))
+        n = int(counts[kind])
+        pos, mtx = np.zeros(max(n, 1), np.uint32), np.zeros(max(n, 1), np.uint32)
+        k = self.L.hgref_cull(self.h, kind, P(np.ascontiguousarray(frustum24, np.float32)), P(pos), P(mtx))
+        return pos[:k].copy(), mtx[:k].copy()
+
+    def skinned_lists(self, kind=2):
+        counts = np.zeros(4, np.int32)
+        self.L.hgref_get_model_display_lists(self.h, P(counts))
+        n = int(counts[kind])
+        mi, bi = np.zeros((max(n, 1), 32), np.uint32), np.zeros((max(n, 1), 32), np.uint32)
+        bc, mdl, lst = np.zeros(max(n, 1), np.uint16), np.zeros(max(n, 1), np.uint16), np.zeros(max(n, 1), np.uint16)
+        self.L.hgref_read_skinned_lists(self.h, kind, P(mi), P(bi), P(bc), P(mdl), P(lst))
+        return mi[:n], bi[:n], bc[:n], mdl[:n], lst[:n]
+
+    def bone_matrices(self, previous=False, kind=2):
+        counts = np.zeros(4, np.int32)
+        self.L.hgref_get_model_display_lists(self.h, P(counts))
+        n = self.L.hgref_bone_matrices(self.h, kind, 1 if previous else 0, None)
+        out = np.zeros((n, 16), np.float32)
+        self.L.hgref_bone_matrices(self.h, kind, 1 if previous else 0, P(out))
+        return out
