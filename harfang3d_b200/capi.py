@@ -12,6 +12,9 @@ ENTRY_DISABLED = 0x01
 KIND_OPAQUE, KIND_TRANSPARENT = 0, 1
 
 
+KERNEL_CLASSES = ("k_sample_tracks", "k_update_level", "k_compact", "k_segment_ranks", "k_cull_flags", "k_bone_matrices")
+
+
 class HgbError(RuntimeError):
     pass
 
@@ -64,6 +67,8 @@ SIGNATURES = {
     "hgb_time_begin": (_i, [_p]),
     "hgb_time_end": (_i, [_p, _p]),
     "hgb_flush_l2": (_i, [_p, _sz]),
+    "hgb_set_profiling": (_i, [_p, _i]),
+    "hgb_get_profile": (_i, [_p, _p, _p, _i]),
 }
 
 _lib = None
@@ -243,6 +248,15 @@ class Context:
         ms = C.c_float(0)
         self._ck(self._L.hgb_time_end(self._h, C.byref(ms)))
         return ms.value
+
+    def set_profiling(self, on):
+        self._ck(self._L.hgb_set_profiling(self._h, 1 if on else 0))
+
+    def get_profile(self, reset=True):
+        """{kernel class: (total ms, launches)} accumulated since the last reset"""
+        ms, n = np.zeros(len(KERNEL_CLASSES), np.float64), np.zeros(len(KERNEL_CLASSES), np.uint64)
+        self._ck(self._L.hgb_get_profile(self._h, _ptr(ms, np.float64, "ms"), _ptr(n, np.uint64, "n"), 1 if reset else 0))
+        return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(KERNEL_CLASSES)}
 
     def flush_l2(self, nbytes=256 << 20):
         self._ck(self._L.hgb_flush_l2(self._h, nbytes))

@@ -84,6 +84,17 @@ struct HBuf { // pinned host staging, grows
 	template <typename T> T *as() const { return static_cast<T *>(p); }
 };
 
+// per-kernel CUDA-event timing (hgb_set_profiling): every launch of a profiled frame is bracketed by an event pair on the
+// context's stream; classes follow HGB_K_* of the header
+struct Prof {
+	bool on = false;
+	std::vector<cudaEvent_t> ev; // pairs
+	std::vector<int> cls;        // class of pair i
+	size_t used = 0;             // pairs in flight
+	double ms[HGB_K_COUNT] = {};
+	uint64_t n[HGB_K_COUNT] = {};
+};
+
 struct EntryTable {
 	uint32_t n = 0;
 	std::vector<uint32_t> mtx_slot, bounds_idx;
@@ -104,6 +115,7 @@ struct hgb_ctx {
 	cudaStream_t own_stream = nullptr, stream = nullptr;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	uint64_t launches = 0;
+	Prof prof;
 
 	// topology (host)
 	uint32_t n_slots = 0, n_pos = 0; // n_pos = used slots (positions [0,n_pos) are live; holes get positions >= n_pos)
@@ -153,6 +165,44 @@ struct hgb_ctx {
 	bool graph_valid[2][2] = {};
 	uint64_t graph_kernels[2][2] = {};
 };
+
+// bracket one kernel launch with events when profiling (never during graph capture: profiled frames use plain launches)
+static void prof_begin(hgb_ctx *c, int cls) {
+	Prof &p = c->prof;
+	if (!p.on)
+		return;
+	if (p.used * 2 == p.ev.size()) {
+		cudaEvent_t a = nullptr, b = nullptr;
+		cudaEventCreate(&a);
+		cudaEventCreate(&b);
+		p.ev.push_back(a);
+		p.ev.push_back(b);
+		p.cls.push_back(cls);
+	}
+	p.cls[p.used] = cls;
+	cudaEventRecord(p.ev[p.used * 2], c->stream);
+}
+static void prof_end(hgb_ctx *c) {
+	Prof &p = c->prof;
+	if (!p.on)
+		return;
+	cudaEventRecord(p.ev[p.used * 2 + 1], c->stream);
+	++p.used;
+}
+static int prof_collect(hgb_ctx *c) {
+	Prof &p = c->prof;
+	if (!p.used)
+		return 0;
+	CK(cudaStreamSynchronize(c->stream));
+	for (size_t i = 0; i < p.used; ++i) {
+		float ms = 0.f;
+		CK(cudaEventElapsedTime(&ms, p.ev[i * 2], p.ev[i * 2 + 1]));
+		p.ms[p.cls[i]] += ms;
+		++p.n[p.cls[i]];
+	}
+	p.used = 0;
+	return 0;
+}
 
 static void invalidate_graph(hgb_ctx *c) {
 	for (auto &a : c->graph_valid)
@@ -227,6 +277,8 @@ void hgb_destroy(hgb_ctx *c) {
 		for (auto &o : t.out)
 			o.release();
 	}
+	for (cudaEvent_t e : c->prof.ev)
+		cudaEventDestroy(e);
 	c->staging.release();
 	c->play_t_h.release();
 	cudaEventDestroy(c->ev0);
@@ -268,6 +320,31 @@ int hgb_time_end(hgb_ctx *c, float *ms) {
 	CK(cudaEventRecord(c->ev1, c->stream));
 	CK(cudaEventSynchronize(c->ev1));
 	CK(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+	return 0;
+}
+int hgb_set_profiling(hgb_ctx *c, int on) {
+	if (!c)
+		return fail("null context");
+	if (prof_collect(c))
+		return 1;
+	c->prof.on = on != 0;
+	return 0;
+}
+int hgb_get_profile(hgb_ctx *c, double *ms_by_class, uint64_t *launches_by_class, int reset) {
+	if (!c)
+		return fail("null context");
+	if (prof_collect(c))
+		return 1;
+	for (int k = 0; k < HGB_K_COUNT; ++k) {
+		if (ms_by_class)
+			ms_by_class[k] = c->prof.ms[k];
+		if (launches_by_class)
+			launches_by_class[k] = c->prof.n[k];
+		if (reset) {
+			c->prof.ms[k] = 0;
+			c->prof.n[k] = 0;
+		}
+	}
 	return 0;
 }
 int hgb_flush_l2(hgb_ctx *c, size_t bytes) {

@@ -36,12 +36,16 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k) {
 			d.count = t.counts.as<uint32_t>() + v;
 			d.ticket = t.ticket.as<uint32_t>() + v;
 			d.status = t.status.as<uint32_t>() + size_t(v) * t.n_tiles;
+			prof_begin(c, HGB_K_COMPACT);
 			k_compact<<<t.n_tiles, kCompactThreads, 0, c->stream>>>(d);
+			prof_end(c);
 			++*n_k;
 		}
 		if (c->instance_mode && k == 0 && c->n_inst) {
+			prof_begin(c, HGB_K_SEGMENT_RANKS);
 			k_segment_ranks<<<grid_for(c->n_inst * 32), 256, 0, c->stream>>>(t.vis.as<uint8_t>(), 0, c->inst_start.as<uint32_t>(), c->n_inst,
 				t.status.as<uint32_t>(), c->inst_rank.as<uint32_t>());
+			prof_end(c);
 			++*n_k;
 		}
 	}
@@ -66,7 +70,9 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 			const uint32_t first = c->round_off[r], cnt = c->round_off[r + 1] - first;
 			if (!cnt)
 				continue;
+			prof_begin(c, HGB_K_SAMPLE_TRACKS);
 			k_sample_tracks<<<grid_for(cnt), 256, 0, c->stream>>>(a, first, cnt);
+			prof_end(c);
 			++*n_k;
 		}
 	}
@@ -78,12 +84,14 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		if (e == b)
 			continue;
 		const dim3 g = grid_for(e - b);
+		prof_begin(c, HGB_K_UPDATE_LEVEL);
 		if (!do_fused)
 			k_update_level<false, false><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
 		else if (c->instance_mode)
 			k_update_level<true, true><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
 		else
 			k_update_level<true, false><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
+		prof_end(c);
 		++*n_k;
 	}
 	CK(cudaGetLastError());
@@ -158,7 +166,7 @@ int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cul
 	}
 
 	const bool fused = fused_cull != 0;
-	if (!c->use_graph || with_preset) {
+	if (!c->use_graph || with_preset || c->prof.on) {
 		uint64_t k = 0;
 		if (enqueue_frame_kernels(c, fused, with_preset, &k))
 			return 1;
@@ -190,10 +198,12 @@ int hgb_cull(hgb_ctx *c) {
 		d.inst_planes = c->inst_planes.as<float4>();
 		d.vis = t.vis.as<uint8_t>();
 		d.n = t.n;
+		prof_begin(c, HGB_K_CULL_FLAGS);
 		if (c->instance_mode)
 			k_cull_flags<true><<<grid_for(t.n), 256, 0, c->stream>>>(d, c->views);
 		else
 			k_cull_flags<false><<<grid_for(t.n), 256, 0, c->stream>>>(d, c->views);
+		prof_end(c);
 		++k;
 	}
 	CK(cudaGetLastError());
@@ -220,7 +230,9 @@ int hgb_bone_matrices(hgb_ctx *c, int with_previous) {
 	b.out = c->bone_out[0].as<float>();
 	b.out_prev = c->bone_out[1].as<float>();
 	b.n = c->n_bones;
+	prof_begin(c, HGB_K_BONE_MATRICES);
 	k_bone_matrices<<<grid_for(b.n), 256, 0, c->stream>>>(b);
+	prof_end(c);
 	++c->launches;
 	CK(cudaGetLastError());
 	return 0;

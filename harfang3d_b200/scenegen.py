@@ -146,10 +146,13 @@ def add_position_tracks(fs, nodes, rng, n_keys=32, play_loop=True):
     t = np.tile(np.arange(n_keys, dtype=np.int64) * KEY_DT, a)
     fs.v3_t = np.concatenate([fs.v3_t, t])
     centre = fs.trs[nodes, 0:3]
-    val = (np.repeat(centre, n_keys, axis=0) + rng.uniform(-2, 2, (a * n_keys, 3))).astype(np.float32)
-    fs.v3_val = np.concatenate([fs.v3_val, val])
-    fs.v3_tension = np.concatenate([fs.v3_tension, rng.uniform(-0.5, 0.5, a * n_keys).astype(np.float32)])
-    fs.v3_bias = np.concatenate([fs.v3_bias, rng.uniform(-0.5, 0.5, a * n_keys).astype(np.float32)])
+    val = rng.random((a * n_keys, 3), dtype=np.float32)  # f32 draws: the 16M-node batch has 10^8 keys
+    val *= np.float32(4)
+    val -= np.float32(2)
+    val += np.repeat(centre, n_keys, axis=0)
+    fs.v3_val = np.concatenate([fs.v3_val, val]) if len(fs.v3_val) else val
+    fs.v3_tension = np.concatenate([fs.v3_tension, rng.random(a * n_keys, dtype=np.float32) - np.float32(0.5)])
+    fs.v3_bias = np.concatenate([fs.v3_bias, rng.random(a * n_keys, dtype=np.float32) - np.float32(0.5)])
     fs.scene_anims.append((base_anim + np.arange(a, dtype=np.int32), 0, (n_keys - 1) * KEY_DT))
     fs.plays.append((len(fs.scene_anims) - 1, 2 if play_loop else 0, 1.0))
     return base_trk

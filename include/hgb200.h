@@ -123,6 +123,18 @@ int hgb_is_identity_order(hgb_ctx *);   /* 1 when slot order already is the dept
 /* CUDA-event stopwatch on the context's stream: begin records an event, end records one, synchronises and returns the ms between. */
 int hgb_time_begin(hgb_ctx *);
 int hgb_time_end(hgb_ctx *, float *out_ms);
+/* Per-kernel CUDA-event timing. While on, frames are enqueued as plain stream launches (no graph) and every kernel launch is
+ * bracketed by an event pair on the context's stream. hgb_get_profile synchronises and returns the accumulated milliseconds and
+ * launch counts per kernel class (arrays of HGB_K_COUNT). */
+#define HGB_K_SAMPLE_TRACKS 0
+#define HGB_K_UPDATE_LEVEL 1
+#define HGB_K_COMPACT 2
+#define HGB_K_SEGMENT_RANKS 3
+#define HGB_K_CULL_FLAGS 4
+#define HGB_K_BONE_MATRICES 5
+#define HGB_K_COUNT 6
+int hgb_set_profiling(hgb_ctx *, int on);
+int hgb_get_profile(hgb_ctx *, double *ms_by_class, uint64_t *launches_by_class, int reset);
 /* Write `bytes` bytes of a scratch buffer (allocated on first use) — L2 flush between timed iterations. */
 int hgb_flush_l2(hgb_ctx *, size_t bytes);
 

@@ -210,6 +210,24 @@ int hgref_anim_add_quat_track(void *h, int anim, int n_keys, const int64_t *t, c
 	return int(a->quat_tracks.size()) - 1;
 }
 
+// Bulk form of the three calls above (one ctypes call for a whole flat description; used for the large bench scenes).
+int hgref_add_anims_bulk(void *h, int n_anims, const uint8_t *use_quat, int n_tracks, const int32_t *trk_anim, const uint8_t *trk_kind, const uint32_t *key_off,
+	const uint32_t *key_count, const int64_t *v3_t, const float *v3_val, const float *v3_tension, const float *v3_bias, const int64_t *q_t, const float *q_val) {
+	auto *c = static_cast<RefCtx *>(h);
+	const int base = int(c->anims.size());
+	for (int a = 0; a < n_anims; ++a)
+		hgref_add_anim(h, use_quat ? use_quat[a] : 0);
+	for (int k = 0; k < n_tracks; ++k) {
+		const size_t o = key_off[k];
+		if (trk_kind[k] == 3)
+			hgref_anim_add_quat_track(h, base + trk_anim[k], int(key_count[k]), q_t + o, q_val + o * 4);
+		else
+			hgref_anim_add_vec3_track(h, base + trk_anim[k], trk_kind[k], int(key_count[k]), v3_t + o, v3_val + o * 3, v3_tension ? v3_tension + o : nullptr,
+				v3_bias ? v3_bias + o : nullptr);
+	}
+	return int(c->anims.size());
+}
+
 // SceneAnim = list of (node, anim) pairs (scene.h:104-114)
 int hgref_add_scene_anim(void *h, int n, const int32_t *node, const int32_t *anim, int64_t t_start, int64_t t_end) {
 	auto *c = static_cast<RefCtx *>(h);

@@ -75,6 +75,7 @@ def load_ref():
     _sig(L, "hgref_add_anim", c_i, [c_p, c_i])
     _sig(L, "hgref_anim_add_vec3_track", c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p])
     _sig(L, "hgref_anim_add_quat_track", c_i, [c_p, c_i, c_i, c_p, c_p])
+    _sig(L, "hgref_add_anims_bulk", c_i, [c_p, c_i, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p])
     _sig(L, "hgref_add_scene_anim", c_i, [c_p, c_i, c_p, c_p, c_i64, c_i64])
     _sig(L, "hgref_play_anim", c_i, [c_p, c_i, c_i, c_f])
     _sig(L, "hgref_is_playing", c_i, [c_p, c_i])

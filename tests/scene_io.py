@@ -24,15 +24,12 @@ class RefScene:
                             P(fs.transparent_mask), None)
         for node, b in fs.bones.items():
             ref.hgref_set_object_bones(self.h, int(node), len(b), P(np.ascontiguousarray(b, np.int32)))
-        for a in range(len(fs.anim_node)):
-            ref.hgref_add_anim(self.h, int(fs.anim_use_quat[a]))
-        for k in range(len(fs.trk_anim)):
-            a, kind, off, cnt = int(fs.trk_anim[k]), int(fs.trk_kind[k]), int(fs.trk_key_off[k]), int(fs.trk_key_count[k])
-            if kind == 3:
-                ref.hgref_anim_add_quat_track(self.h, a, cnt, P(fs.q_t[off:off + cnt]), P(np.ascontiguousarray(fs.q_val[off:off + cnt])))
-            else:
-                ref.hgref_anim_add_vec3_track(self.h, a, kind, cnt, P(fs.v3_t[off:off + cnt]), P(np.ascontiguousarray(fs.v3_val[off:off + cnt])),
-                                              P(fs.v3_tension[off:off + cnt]), P(fs.v3_bias[off:off + cnt]))
+        if len(fs.anim_node):
+            c = np.ascontiguousarray
+            ref.hgref_add_anims_bulk(self.h, len(fs.anim_node), P(c(fs.anim_use_quat, np.uint8)), len(fs.trk_anim), P(c(fs.trk_anim, np.int32)),
+                                     P(c(fs.trk_kind, np.uint8)), P(c(fs.trk_key_off, np.uint32)), P(c(fs.trk_key_count, np.uint32)), P(c(fs.v3_t, np.int64)),
+                                     P(c(fs.v3_val, np.float32)), P(c(fs.v3_tension, np.float32)), P(c(fs.v3_bias, np.float32)), P(c(fs.q_t, np.int64)),
+                                     P(c(fs.q_val, np.float32)))
         for anims, ts, te in fs.scene_anims:
             nodes = np.ascontiguousarray(fs.anim_node[anims], np.int32)
             ref.hgref_add_scene_anim(self.h, len(anims), P(nodes), P(np.ascontiguousarray(anims, np.int32)), int(ts), int(te))

