@@ -11,8 +11,8 @@ static SceneDev scene_dev(hgb_ctx *c, bool with_preset) {
 	s.ent_off = c->ent_off.as<uint32_t>();
 	s.pent = c->pent.as<uint2>();
 	s.bounds6 = c->bounds.as<float>();
-	s.vis[0] = c->ent[0].vis.as<uint8_t>();
-	s.vis[1] = c->ent[1].vis.as<uint8_t>();
+	s.vis0 = c->ent[0].vis.as<uint8_t>();
+	s.vis1 = c->ent[1].vis.as<uint8_t>();
 	s.inst_planes = c->inst_planes.as<float4>();
 	s.pent_view = c->pent_view.as<uint16_t>();
 	return s;

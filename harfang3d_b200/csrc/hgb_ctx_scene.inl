@@ -8,6 +8,16 @@ static int upload(hgb_ctx *c, DBuf &dst, const void *src, size_t bytes) {
 	return 0;
 }
 
+// plane {x,y,z,w} -> {x,y,z,-2w}: TestVisibility compares against plane_d_x2 = -plane.w * 2.f (foundation/frustum.cpp:72), exact in float
+static void precondition_planes(const float *in, uint32_t n_planes, float *out) {
+	for (uint32_t i = 0; i < n_planes; ++i) {
+		out[i * 4 + 0] = in[i * 4 + 0];
+		out[i * 4 + 1] = in[i * 4 + 1];
+		out[i * 4 + 2] = in[i * 4 + 2];
+		out[i * 4 + 3] = -in[i * 4 + 3] * 2.f;
+	}
+}
+
 static inline dim3 grid_for(uint32_t n, uint32_t block = 256) { return dim3((n + block - 1) / block); }
 
 extern "C" {
@@ -319,8 +329,11 @@ int hgb_set_views(hgb_ctx *c, uint32_t n_views, const float *frustum24) {
 	}
 	c->instance_mode = false;
 	c->views.n_views = int(n_views);
-	if (n_views) // pageable source: staged by the runtime before returning
-		CK(cudaMemcpyAsync(c->view_planes.p, frustum24, size_t(n_views) * 96, cudaMemcpyHostToDevice, c->stream));
+	if (n_views) { // pageable source: staged by the runtime before returning
+		float cond[kMaxViews * 24];
+		precondition_planes(frustum24, n_views * 6, cond);
+		CK(cudaMemcpyAsync(c->view_planes.p, cond, size_t(n_views) * 96, cudaMemcpyHostToDevice, c->stream));
+	}
 	return 0;
 }
 
@@ -331,7 +344,9 @@ int hgb_set_instance_views(hgb_ctx *c, uint32_t n_inst, const float *frustum24, 
 		return fail("hgb_set_instance_views: at most 65535 instances per context (uint16 view id)");
 	CK(cudaSetDevice(c->device));
 	const bool shape_change = !c->instance_mode || c->n_inst != n_inst;
-	if (upload(c, c->inst_planes, frustum24, size_t(n_inst) * 96))
+	std::vector<float> cond(size_t(n_inst) * 24);
+	precondition_planes(frustum24, n_inst * 6, cond.data());
+	if (upload(c, c->inst_planes, cond.data(), size_t(n_inst) * 96))
 		return 1;
 	if (inst_entry_start && upload(c, c->inst_start, inst_entry_start, size_t(n_inst + 1) * 4))
 		return 1;

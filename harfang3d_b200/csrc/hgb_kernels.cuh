@@ -14,7 +14,7 @@ constexpr int kMaxViews = 8;
 constexpr uint32_t kEntDisabled = 1u << 24;
 constexpr uint32_t kEntKindTransparent = 1u << 31; // in PosEntry::entry (bit 31): which of the two entry tables
 
-// View frusta live in device memory (6 float4 per view: Top,Bottom,Left,Right,Near,Far, foundation/frustum.h:14) so that a camera
+// View frusta live in device memory (6 float4 per view: Top,Bottom,Left,Right,Near,Far, foundation/frustum.h:14; w holds -2*w) so that a camera
 // move is a 96-byte copy and never invalidates the captured frame graph.
 struct Views {
 	const float4 *planes;
@@ -32,7 +32,7 @@ struct SceneDev {
 	const uint32_t *ent_off;    // n_pos + 1
 	const uint2 *pent;          // {entry index | kind bit, meta}
 	const float *bounds6;       // MinMax table, 6 floats per (model, list)
-	uint8_t *vis[2];            // per entry table: bit v set -> survives view v
+	uint8_t *vis0, *vis1;       // per entry table (opaque, transparent): bit v set -> survives view v
 	const float4 *inst_planes;  // per-instance frusta (6 float4 each) or null
 	const uint16_t *pent_view;  // per pent record: which instance frustum (only with inst_planes)
 };
@@ -45,6 +45,12 @@ struct SceneDev {
 // engine/scene.cpp:330-364, engine/render_pipeline.cpp:2098-2104) and only a 1-byte visibility mask per entry is written.
 template <bool FUSED, bool PER_INSTANCE>
 __global__ void __launch_bounds__(256) k_update_level(SceneDev s, Views views, uint32_t begin, uint32_t end) {
+	__shared__ float4 s_planes[kMaxViews * 6];
+	if (FUSED && !PER_INSTANCE) { // the shared view frusta: one broadcast LDS.128 per plane instead of a global load
+		if (threadIdx.x < uint32_t(views.n_views) * 6u)
+			s_planes[threadIdx.x] = views.planes[threadIdx.x];
+		__syncthreads();
+	}
 	const uint32_t p = begin + blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= end)
 		return;
@@ -74,10 +80,10 @@ __global__ void __launch_bounds__(256) k_update_level(SceneDev s, Views views, u
 					bits = survives_frustum(s.inst_planes + size_t(s.pent_view[k]) * 6, bb) ? 1u : 0u;
 				} else {
 					for (int v = 0; v < views.n_views; ++v)
-						bits |= survives_frustum(views.planes + v * 6, bb) ? (1u << v) : 0u;
+						bits |= survives_frustum(s_planes + v * 6, bb) ? (1u << v) : 0u;
 				}
 			}
-			s.vis[rec.x >> 31][rec.x & 0x7fffffffu] = uint8_t(bits);
+			((rec.x >> 31) ? s.vis1 : s.vis0)[rec.x & 0x7fffffffu] = uint8_t(bits);
 		}
 	}
 }
@@ -97,6 +103,12 @@ struct CullDev {
 };
 
 template <bool PER_INSTANCE> __global__ void __launch_bounds__(256) k_cull_flags(CullDev c, Views views) {
+	__shared__ float4 s_planes[kMaxViews * 6];
+	if (!PER_INSTANCE) {
+		if (threadIdx.x < uint32_t(views.n_views) * 6u)
+			s_planes[threadIdx.x] = views.planes[threadIdx.x];
+		__syncthreads();
+	}
 	const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
 	if (e >= c.n)
 		return;

@@ -27,7 +27,7 @@ __device__ const uint32_t c_inv_pio4[24] = {0xa2, 0xa2f9, 0xa2f983, 0xa2f9836e, 
 	0x29fc2757, 0xfc2757d1, 0x2757d1f5, 0x57d1f534, 0xd1f534dd, 0xf534ddc0, 0x34ddc0db, 0xddc0db62, 0xc0db6295, 0xdb629599, 0x6295993c, 0x95993c43, 0x993c4390,
 	0x3c439041};
 
-__device__ __noinline__ double sc_reduce_large(uint32_t xi, int &n_out) {
+__device__ __forceinline__ double sc_reduce_large(uint32_t xi, int &n_out) {
 	const uint32_t *arr = &c_inv_pio4[(xi >> 26) & 15];
 	const int shift = (xi >> 23) & 7;
 	xi = (xi & 0xffffffu) | 0x800000u;
@@ -43,7 +43,9 @@ __device__ __noinline__ double sc_reduce_large(uint32_t xi, int &n_out) {
 	return __dmul_rn(double(int64_t(res0)), 0x1.921FB54442D18p-62);
 }
 
-// polynomial pair on the reduced argument; q selects the table (q&2 flips the cosine polynomial's sign)
+// The two polynomials of sincosf.h on the reduced argument, each rounded once to float. Every operation is sign-symmetric
+// under round-to-nearest, so sin_poly(-x) == -sin_poly(x) and the negated-coefficient cosine table of glibc (__sincosf_table[1])
+// gives exactly -cos_poly(x2): quadrant signs are applied to the rounded floats instead of evaluating four variants.
 __device__ __forceinline__ float sc_sin_poly(double x, double x2) {
 	const double x3 = __dmul_rn(x, x2);
 	const double s1 = fma(x2, -0x1.994eb3774cf24p-13, 0x1.1107605230bc4p-7);
@@ -51,67 +53,52 @@ __device__ __forceinline__ float sc_sin_poly(double x, double x2) {
 	const double s = fma(x3, -0x1.555545995a603p-3, x);
 	return __double2float_rn(fma(x7, s1, s));
 }
-__device__ __forceinline__ float sc_cos_poly(double x2, bool neg) {
-	const double sg = neg ? -1.0 : 1.0; // table[1] holds the negated cosine coefficients; negation is exact
+__device__ __forceinline__ float sc_cos_poly(double x2) {
 	const double x4 = __dmul_rn(x2, x2);
-	const double c2 = fma(x2, sg * 0x1.99343027bf8c3p-16, sg * -0x1.6c087e89a359dp-10);
-	const double c1 = fma(x2, sg * -0x1.ffffffd0c621cp-2, sg * 0x1p0);
+	const double c2 = fma(x2, 0x1.99343027bf8c3p-16, -0x1.6c087e89a359dp-10);
+	const double c1 = fma(x2, -0x1.ffffffd0c621cp-2, 0x1p0);
 	const double x6 = __dmul_rn(x4, x2);
-	const double c = fma(x4, sg * 0x1.55553e1068f19p-5, c1);
+	const double c = fma(x4, 0x1.55553e1068f19p-5, c1);
 	return __double2float_rn(fma(x6, c2, c));
 }
 
-// sinf(y) and cosf(y) exactly as glibc computes them (each is an independent libm call in the reference; they share the
-// argument reduction, so it is done once here).
+// |y| >= 120, inf, nan: rare (Euler angles are within a few turns), kept out of line
+__device__ __noinline__ float2 sincos_libm_slow(float y) {
+	if (abstop12(y) >= 0x7f8u)
+		return make_float2(y - y, y - y); // inf/nan -> nan
+	const uint32_t xi = __float_as_uint(y);
+	int n;
+	const double x = sc_reduce_large(xi, n);
+	const int m = n + int(xi >> 31); // s_sinf.c / s_cosf.c large path: sign and table are keyed on n + sign, the polynomial on n
+	const double x2 = __dmul_rn(x, x);
+	const float sp = sc_sin_poly(x, x2), cp = sc_cos_poly(x2);
+	const float sgn_sp = ((m & 3) == 1 || (m & 3) == 2) ? -sp : sp; // sign[] = {1,-1,-1,1}
+	const float neg_cp = (m & 2) ? -cp : cp;                        // __sincosf_table[1] = negated cosine coefficients
+	return make_float2((n & 1) ? neg_cp : sgn_sp, (n & 1) ? sgn_sp : neg_cp);
+}
+
+// sinf(y) and cosf(y) exactly as glibc computes them (each is an independent libm call in the reference). One branch-free path
+// for every |y| < 120: the |y| < pi/4 case of s_sinf.c is the general reduction with n = 0 (x is left untouched), and the
+// |y| < 2^-12 shortcut is a select. Proven equal to libm for all 2^32 inputs on the host: oracle/exhaustive_sincos_merged.c.
 __device__ __forceinline__ void sincos_libm(float y, float &s_out, float &c_out) {
 	const uint32_t top = abstop12(y);
-	double x = double(y);
-	if (top < 0x3f4u) { // |y| < pi/4  (abstop12(0x1.921FB6p-1f))
-		if (top < 0x398u) { // |y| < 2^-12
-			s_out = y;
-			c_out = 1.0f;
-			return;
-		}
-		const double x2 = __dmul_rn(x, x);
-		s_out = sc_sin_poly(x, x2);
-		c_out = sc_cos_poly(x2, false);
+	if (top >= 0x42fu) {
+		const float2 sc = sincos_libm_slow(y);
+		s_out = sc.x, c_out = sc.y;
 		return;
 	}
-	int n, ns, nc; // quadrant; sign selectors for sin / cos
-	if (top < 0x42fu) { // |y| < 120
-		const double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);
-		n = (__double2int_rz(r) + 0x800000) >> 24;
-		x = fma(-double(n), 0x1.921FB54442D18p0, x);
-		ns = n;
-		nc = n + 1;
-	} else if (top < 0x7f8u) {
-		const uint32_t xi = __float_as_uint(y);
-		x = sc_reduce_large(xi, n);
-		ns = nc = n + int(xi >> 31);
-		// table switch also keys on n+sign here (s_sinf.c / s_cosf.c large path)
-		const double x2 = __dmul_rn(x, x);
-		const bool neg = (ns & 2) != 0;
-		const double sgn = ((ns & 3) == 1 || (ns & 3) == 2) ? -1.0 : 1.0; // sign[] = {1,-1,-1,1}
-		const double xs = __dmul_rn(x, sgn);
-		s_out = (n & 1) ? sc_cos_poly(x2, neg) : sc_sin_poly(xs, x2);
-		c_out = (n & 1) ? sc_sin_poly(xs, x2) : sc_cos_poly(x2, neg);
-		return;
-	} else {
-		s_out = c_out = y - y; // inf/nan -> nan
-		return;
-	}
-	const double x2 = __dmul_rn(x, x);
-	const bool neg = (n & 2) != 0;
-	const double sgn_s = ((ns & 3) == 1 || (ns & 3) == 2) ? -1.0 : 1.0;
-	const double sgn_c = ((nc & 3) == 1 || (nc & 3) == 2) ? -1.0 : 1.0;
-	// sinf: poly(x*sign[n&3], x2, n) ; cosf: poly(x*sign[(n+1)&3], x2, n^1)
-	if (n & 1) {
-		s_out = sc_cos_poly(x2, neg);
-		c_out = sc_sin_poly(__dmul_rn(x, sgn_c), x2);
-	} else {
-		s_out = sc_sin_poly(__dmul_rn(x, sgn_s), x2);
-		c_out = sc_cos_poly(x2, neg);
-	}
+	const double x = double(y);
+	const double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);
+	const int n = (__double2int_rz(r) + 0x800000) >> 24;
+	const double xr = fma(-double(n), 0x1.921FB54442D18p0, x);
+	const double x2 = __dmul_rn(xr, xr);
+	const float sp = sc_sin_poly(xr, x2), cp = sc_cos_poly(x2);
+	float s = (n & 1) ? cp : sp, c = (n & 1) ? sp : cp;
+	s = (n & 2) ? -s : s;
+	c = ((n + 1) & 2) ? -c : c;
+	const bool tiny = top < 0x398u; // |y| < 2^-12
+	s_out = tiny ? y : s;
+	c_out = tiny ? 1.0f : c;
 }
 
 // ---- TransformationMat4(pos, euler, scale) ------------------------------------------------------------------------
@@ -193,16 +180,17 @@ __device__ __forceinline__ Aabb minmax_transform(const Mat4 &m, const float *__r
 	return o;
 }
 
+// planes are stored pre-conditioned: {x, y, z, -2*w} (the reference computes plane_d_x2 = -plane.w * 2.f per test; exact either way)
 __device__ __forceinline__ bool survives_frustum(const float4 *__restrict__ planes, const Aabb &bb) {
 	const float cx = bb.mn[0] + bb.mx[0], cy = bb.mn[1] + bb.mx[1], cz = bb.mn[2] + bb.mx[2];
 	const float ex = bb.mx[0] - bb.mn[0], ey = bb.mx[1] - bb.mn[1], ez = bb.mx[2] - bb.mn[2];
 	bool inside = true;
 #pragma unroll
 	for (int n = 0; n < 6; ++n) {
-		const float4 p = __ldg(planes + n);
+		const float4 p = planes[n];
 		const float d = p.x * cx + p.y * cy + p.z * cz;
 		const float r = fabsf(p.x) * ex + fabsf(p.y) * ey + fabsf(p.z) * ez;
-		inside = inside && !(d - r > -p.w * 2.f);
+		inside = inside && !(d - r > p.w);
 	}
 	return inside;
 }

@@ -120,6 +120,7 @@ def static_scene(n_nodes, depth, fanout, n_models=1, seed=0, disabled_frac=0.01,
     parent = tree_parents(level_sizes(n_nodes, depth, fanout))
     trs = random_trs(rng, n_nodes, parent)
     trs[:, 6:9] = rng.uniform(0.8, 1.25, (n_nodes, 3)) * scale_world  # keep deep chains from exploding
+    trs[parent < 0, 0:3] = rng.uniform(-2, 2, (int((parent < 0).sum()), 3))  # the camera (at the origin) sits inside the scene: a cone of it is visible
     return FlatScene(trs=trs, parent=parent, disabled=(rng.random(n_nodes) < disabled_frac).astype(np.uint8),
                      model=rng.integers(0, n_models, n_nodes).astype(np.int32), n_mats=np.ones(n_nodes, np.uint8),
                      transparent_mask=np.zeros(n_nodes, np.uint32), models=box_models(rng, n_models), camera=dict(DEFAULT_CAMERA))
@@ -207,6 +208,8 @@ def config_c3(seed=3, n_chars=4096, n_bones=64, n_keys=32):
         model[b + 1 + n_bones] = 1
     trs = random_trs(rng, n, parent, child_extent=1.0)
     trs[:, 6:9] = rng.uniform(0.9, 1.1, (n, 3))
+    roots = np.arange(n_chars) * per  # a crowd in front of and around the camera: part of it is inside the frustum
+    trs[roots, 0:3] = np.stack([rng.uniform(-60, 60, n_chars), rng.uniform(-5, 5, n_chars), rng.uniform(-20, 100, n_chars)], axis=1)
     half = n_bones // 2
     bind = np.zeros((n_bones, 12), np.float32)
     bind[:, [0, 5, 10]] = 1
@@ -266,10 +269,10 @@ def config_c5(seed=5, n_instances=8192, nodes_per_instance=2048, depth=6):
     off = (np.arange(n_instances + 1, dtype=np.int64) * nodes_per_instance)
     parent = np.tile(parent1, n_instances).astype(np.int64)
     parent = np.where(parent >= 0, parent + np.repeat(off[:-1], nodes_per_instance), -1).astype(np.int32)
-    trs = random_trs(rng, n, parent)
+    trs = random_trs(rng, n, parent, root_extent=2.0)  # every instance lives around its own origin; its camera is inside it
     trs[:, 6:9] = rng.uniform(0.8, 1.25, (n, 3))
     fs = FlatScene(trs=trs, parent=parent, disabled=(rng.random(n) < 0.01).astype(np.uint8), model=rng.integers(0, 4, n).astype(np.int32),
                    n_mats=np.ones(n, np.uint8), transparent_mask=np.zeros(n, np.uint32), models=box_models(rng, 4), camera=dict(DEFAULT_CAMERA))
     fs.instance_start = off.astype(np.uint32)
-    fs.instance_cameras = random_camera_worlds(rng, n_instances)
+    fs.instance_cameras = random_camera_worlds(rng, n_instances, extent=8.0)
     return fs
