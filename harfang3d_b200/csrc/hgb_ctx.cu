@@ -125,8 +125,9 @@ struct hgb_ctx {
 	bool entries_dirty = true; // CSR by position must be rebuilt
 
 	// device scene
-	DBuf trs, parent_pos, world[2], preset, pos_of_slot_d;
-	size_t trs_stride = 0;
+	DBuf tiles, world[2], preset, pos_of_slot_d; // tiles: node tiles (TRS rows, parent, first entry), see hgb_kernels.cuh
+	uint32_t n_tiles = 0;
+	bool transpose_store = true;
 	int cur = 0; // world[cur] = current frame
 	bool preset_pending = false, preset_dirty = false;
 	DBuf preset_pos, preset_mat;
@@ -135,7 +136,7 @@ struct hgb_ctx {
 	DBuf bounds;
 	uint32_t n_bounds = 0;
 	EntryTable ent[2];
-	DBuf ent_off, pent, pent_view;
+	DBuf ent_off, pent, pos_view; // overflow CSR of nodes with several entries; per-position instance id
 
 	Views views{};          // planes -> view_planes (device)
 	DBuf view_planes;
@@ -149,7 +150,10 @@ struct hgb_ctx {
 	std::vector<uint32_t> bone_mtx_slot;
 
 	// animation
-	DBuf v3_t, v3_val, v3_bias, q_t, q_val, tracks_d, play_t_d;
+	DBuf keys, cursor, tracks_d, play_t_d; // keys: 32-byte records, vec3 keys then quaternion keys
+	uint32_t n_v3_keys = 0, n_q_keys = 0;
+	DBuf anim_val, bind_pos_d, bind_group_d; // track-driven (node, pos|rot|scale) triples: values + where they are bound
+	uint32_t n_bound = 0;                    // triples currently bound on the device (tiles hold slots, not values)
 	uint32_t n_tracks = 0, n_play = 0;
 	std::vector<hgb_track> tracks_h;
 	std::vector<uint32_t> round_off; // tracks sorted so that tracks sharing a target lane fall in successive rounds
@@ -239,6 +243,7 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 	hgb_ctx *c = new hgb_ctx;
 	c->device = device;
 	c->use_graph = opt ? opt->use_graph != 0 : true;
+	c->transpose_store = opt ? opt->reserved[0] == 0 : true; // reserved[0] = 1: per-thread 48-byte row stores (A/B switch for profiling)
 	if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
 		cudaEventCreate(&c->ev1) != cudaSuccess) {
 		fail("hgb_create: stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -265,9 +270,9 @@ void hgb_destroy(hgb_ctx *c) {
 		for (cudaGraphExec_t g : a)
 			if (g)
 				cudaGraphExecDestroy(g);
-	DBuf *bufs[] = {&c->trs, &c->parent_pos, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
-		&c->pent, &c->pent_view, &c->inst_planes, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
-		&c->bone_out[1], &c->v3_t, &c->v3_val, &c->v3_bias, &c->q_t, &c->q_val, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->view_planes};
+	DBuf *bufs[] = {&c->tiles, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
+		&c->pent, &c->pos_view, &c->inst_planes, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
+		&c->bone_out[1], &c->keys, &c->cursor, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->view_planes};
 	for (DBuf *b : bufs)
 		b->release();
 	for (auto &t : c->ent) {

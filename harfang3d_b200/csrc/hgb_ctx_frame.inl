@@ -3,9 +3,9 @@
 
 static SceneDev scene_dev(hgb_ctx *c, bool with_preset) {
 	SceneDev s{};
-	s.trs = c->trs.as<float>();
-	s.trs_stride = c->trs_stride;
-	s.parent_pos = c->parent_pos.as<uint32_t>();
+	s.tiles = c->tiles.as<uint32_t>();
+	s.anim_val = c->anim_val.as<float4>();
+	s.transpose_store = c->transpose_store ? 1 : 0;
 	s.world = c->world[c->cur].as<float>();
 	s.preset = with_preset ? c->preset.as<uint8_t>() : nullptr;
 	s.ent_off = c->ent_off.as<uint32_t>();
@@ -14,7 +14,7 @@ static SceneDev scene_dev(hgb_ctx *c, bool with_preset) {
 	s.vis0 = c->ent[0].vis.as<uint8_t>();
 	s.vis1 = c->ent[1].vis.as<uint8_t>();
 	s.inst_planes = c->inst_planes.as<float4>();
-	s.pent_view = c->pent_view.as<uint16_t>();
+	s.pos_view = c->pos_view.as<uint16_t>();
 	return s;
 }
 
@@ -59,13 +59,10 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		AnimDev a{};
 		a.tracks = c->tracks_d.as<Track>();
 		a.play_t = c->play_t_d.as<int64_t>();
-		a.v3_t = c->v3_t.as<int64_t>();
-		a.v3_val = c->v3_val.as<float4>();
-		a.v3_bias = c->v3_bias.as<float>();
-		a.q_t = c->q_t.as<int64_t>();
-		a.q_val = c->q_val.as<float4>();
-		a.trs = c->trs.as<float>();
-		a.trs_stride = c->trs_stride;
+		a.keys = c->keys.as<uint4>();
+		a.quat_base = c->n_v3_keys;
+		a.cursor = c->cursor.as<uint32_t>();
+		a.anim_val = c->anim_val.as<float4>();
 		for (size_t r = 0; r + 1 < c->round_off.size(); ++r) {
 			const uint32_t first = c->round_off[r], cnt = c->round_off[r + 1] - first;
 			if (!cnt)
@@ -270,8 +267,8 @@ int hgb_get_trs(hgb_ctx *c, uint32_t first, uint32_t count, float *out9) {
 		return 0;
 	CK(cudaSetDevice(c->device));
 	CK(c->staging_d.reserve(size_t(count) * 36));
-	k_gather_trs<<<grid_for(count), 256, 0, c->stream>>>(c->trs.as<float>(), c->trs_stride, c->identity ? nullptr : c->pos_of_slot_d.as<uint32_t>(), first, count,
-		c->staging_d.as<float>());
+	k_gather_trs<<<grid_for(count), 256, 0, c->stream>>>(c->tiles.as<uint32_t>(), c->identity ? nullptr : c->pos_of_slot_d.as<uint32_t>(), first, count,
+		c->staging_d.as<float>(), c->anim_val.as<float4>());
 	++c->launches;
 	CK(cudaMemcpyAsync(out9, c->staging_d.p, size_t(count) * 36, cudaMemcpyDeviceToHost, c->stream));
 	CK(cudaStreamSynchronize(c->stream));
@@ -343,7 +340,7 @@ void *hgb_device_ptr(hgb_ctx *c, int which) {
 	case 3: return c->ent[0].counts.p;
 	case 4: return c->bone_out[0].p;
 	case 5: return c->inst_rank.p;
-	case 6: return c->trs.p;
+	case 6: return c->tiles.p;
 	default: return nullptr;
 	}
 }

@@ -96,30 +96,36 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 
 	// carry the device TRS over to the new order (animation may have modified it on the device)
 	const uint32_t keep = std::min(c->n_slots, n);
-	const bool carry = keep > 0 && c->trs.p;
+	const bool carry = keep > 0 && c->tiles.p;
 	if (carry) {
 		CK(c->staging_d.reserve(size_t(keep) * 9 * 4));
-		k_gather_trs<<<grid_for(keep), 256, 0, c->stream>>>(c->trs.as<float>(), c->trs_stride, c->identity ? nullptr : c->pos_of_slot_d.as<uint32_t>(), 0, keep,
-			c->staging_d.as<float>());
+		k_gather_trs<<<grid_for(keep), 256, 0, c->stream>>>(c->tiles.as<uint32_t>(), c->identity ? nullptr : c->pos_of_slot_d.as<uint32_t>(), 0, keep,
+			c->staging_d.as<float>(), c->anim_val.as<float4>());
 		++c->launches;
 		CK(cudaStreamSynchronize(c->stream));
 	}
 
-	const size_t stride = (size_t(n) + 31) & ~size_t(31);
-	DBuf new_trs;
-	CK(new_trs.reserve(std::max<size_t>(stride, 32) * 9 * 4));
-	CK(cudaMemsetAsync(new_trs.p, 0, new_trs.cap, c->stream));
-	if (upload(c, c->pos_of_slot_d, pos_of_slot.data(), size_t(n) * 4) || upload(c, c->parent_pos, parent_pos.data(), size_t(n) * 4))
+	const uint32_t n_tiles = (n + 31) / 32;
+	DBuf new_tiles, rows;
+	CK(new_tiles.reserve(std::max<size_t>(n_tiles, 1) * kTileWords * 4));
+	CK(cudaMemsetAsync(new_tiles.p, 0, new_tiles.cap, c->stream));
+	if (upload(c, c->pos_of_slot_d, pos_of_slot.data(), size_t(n) * 4) || upload(c, rows, parent_pos.data(), size_t(n) * 4))
 		return 1;
+	if (n) {
+		k_fill_rows<<<grid_for(n), 256, 0, c->stream>>>(new_tiles.as<uint32_t>(), kRowParent, rows.as<uint32_t>(), n);
+		++c->launches;
+	}
 	if (carry) {
 		k_scatter_trs<<<grid_for(keep), 256, 0, c->stream>>>(c->staging_d.as<float>(), identity ? nullptr : c->pos_of_slot_d.as<uint32_t>(), 0, keep,
-			new_trs.as<float>(), stride);
+			new_tiles.as<uint32_t>(), nullptr); // the new tiles hold plain values: triples are re-bound by prepare_tables
 		++c->launches;
 	}
 	CK(cudaStreamSynchronize(c->stream)); // host vectors above go out of scope
-	c->trs.release();
-	c->trs = new_trs;
-	c->trs_stride = stride;
+	rows.release();
+	c->tiles.release();
+	c->tiles = new_tiles;
+	c->n_tiles = n_tiles;
+	c->n_bound = 0;
 	for (int i = 0; i < 2; ++i) {
 		const size_t bytes = std::max<size_t>(n, 1) * 48;
 		if (c->world[i].cap < bytes) {
@@ -156,7 +162,7 @@ int hgb_upload_trs(hgb_ctx *c, uint32_t first, uint32_t count, const float *trs9
 	// the caller's buffer may be pageable: the copy is then staged by the driver; pinned buffers go straight over PCIe/C2C
 	CK(cudaMemcpyAsync(c->staging_d.p, trs9, bytes, cudaMemcpyHostToDevice, c->stream));
 	k_scatter_trs<<<grid_for(count), 256, 0, c->stream>>>(c->staging_d.as<float>(), c->identity ? nullptr : c->pos_of_slot_d.as<uint32_t>(), first, count,
-		c->trs.as<float>(), c->trs_stride);
+		c->tiles.as<uint32_t>(), c->anim_val.as<float4>());
 	++c->launches;
 	CK(cudaGetLastError());
 	return 0;
@@ -256,18 +262,27 @@ int hgb_set_anim_keys(hgb_ctx *c, uint32_t n3, const int64_t *v3_t, const float 
 	if (!c)
 		return fail("null context");
 	CK(cudaSetDevice(c->device));
-	std::vector<float> packed(size_t(n3) * 4), bias(n3, 0.f);
-	for (uint32_t i = 0; i < n3; ++i) {
-		packed[size_t(i) * 4 + 0] = v3_val3[size_t(i) * 3 + 0];
-		packed[size_t(i) * 4 + 1] = v3_val3[size_t(i) * 3 + 1];
-		packed[size_t(i) * 4 + 2] = v3_val3[size_t(i) * 3 + 2];
-		packed[size_t(i) * 4 + 3] = v3_tension ? v3_tension[i] : 0.f;
-		if (v3_bias)
-			bias[i] = v3_bias[i];
+	// one 32-byte record per key: {t (8), v.x, v.y | v.z, tension or v.w, bias, 0}; quaternion keys after the vec3 keys
+	const size_t total = size_t(n3) + nq;
+	CK(c->staging.reserve(std::max<size_t>(total, 1) * 32));
+	uint32_t *rec = c->staging.as<uint32_t>();
+	auto f2u = [](float f) { uint32_t u; memcpy(&u, &f, 4); return u; };
+	for (size_t i = 0; i < n3; ++i) {
+		uint32_t *r = rec + i * 8;
+		memcpy(r, v3_t + i, 8);
+		r[2] = f2u(v3_val3[i * 3 + 0]), r[3] = f2u(v3_val3[i * 3 + 1]), r[4] = f2u(v3_val3[i * 3 + 2]);
+		r[5] = f2u(v3_tension ? v3_tension[i] : 0.f), r[6] = f2u(v3_bias ? v3_bias[i] : 0.f), r[7] = 0;
 	}
-	if (upload(c, c->v3_t, v3_t, size_t(n3) * 8) || upload(c, c->v3_val, packed.data(), size_t(n3) * 16) || upload(c, c->v3_bias, bias.data(), size_t(n3) * 4) ||
-		upload(c, c->q_t, q_t, size_t(nq) * 8) || upload(c, c->q_val, q_val4, size_t(nq) * 16))
+	for (size_t i = 0; i < nq; ++i) {
+		uint32_t *r = rec + (size_t(n3) + i) * 8;
+		memcpy(r, q_t + i, 8);
+		r[2] = f2u(q_val4[i * 4 + 0]), r[3] = f2u(q_val4[i * 4 + 1]), r[4] = f2u(q_val4[i * 4 + 2]), r[5] = f2u(q_val4[i * 4 + 3]);
+		r[6] = r[7] = 0;
+	}
+	if (upload(c, c->keys, rec, total * 32))
 		return 1;
+	c->n_v3_keys = n3;
+	c->n_q_keys = nq;
 	CK(cudaStreamSynchronize(c->stream));
 	invalidate_graph(c);
 	return 0;
@@ -310,8 +325,16 @@ int hgb_set_tracks(hgb_ctx *c, uint32_t n, const hgb_track *tracks, uint32_t n_p
 	c->n_tracks = n;
 	c->n_play = n_play;
 	CK(cudaSetDevice(c->device));
+	for (uint32_t i = 0; i < n; ++i) {
+		const uint64_t pool = tracks[i].kind == 3 ? c->n_q_keys : c->n_v3_keys;
+		if (uint64_t(tracks[i].key_off) + tracks[i].key_count > pool)
+			return fail("hgb_set_tracks: track %u reads keys [%u,%u) outside its pool of %llu (call hgb_set_anim_keys first)", i, tracks[i].key_off,
+				tracks[i].key_off + tracks[i].key_count, (unsigned long long)pool);
+	}
 	CK(c->play_t_d.reserve(std::max<size_t>(n_play, 1) * 8));
 	CK(c->play_t_h.reserve(std::max<size_t>(n_play, 1) * 8));
+	CK(c->cursor.reserve(std::max<size_t>(n, 1) * 4));
+	CK(cudaMemsetAsync(c->cursor.p, 0, c->cursor.cap, c->stream));
 	c->entries_dirty = true; // target positions are resolved with the entries
 	invalidate_graph(c);
 	return 0;
@@ -370,6 +393,13 @@ static int prepare_tables(hgb_ctx *c) {
 	if (!c->entries_dirty)
 		return 0;
 	CK(cudaSetDevice(c->device));
+	if (c->n_bound) { // give the track-driven triples their values back before rows are rewritten and tracks re-bound
+		k_bind_lanes<<<grid_for(c->n_bound), 256, 0, c->stream>>>(c->tiles.as<uint32_t>(), c->anim_val.as<float4>(), c->bind_pos_d.as<uint32_t>(),
+			c->bind_group_d.as<uint8_t>(), c->n_bound, 0);
+		++c->launches;
+		CK(cudaStreamSynchronize(c->stream));
+		c->n_bound = 0;
+	}
 	const uint32_t n_pos_all = c->n_slots;
 	std::vector<uint32_t> ent_off(size_t(n_pos_all) + 2, 0);
 	for (int k = 0; k < 2; ++k) {
@@ -403,28 +433,54 @@ static int prepare_tables(hgb_ctx *c) {
 		CK(t.status.reserve(size_t(std::max(t.n_tiles, 1u)) * kMaxViews * 4));
 		CK(cudaStreamSynchronize(c->stream));
 	}
+	// first entry of every position goes into tile rows 10/11; the others into the overflow CSR (ent_off counts them +1 so far)
+	std::vector<uint32_t> row_meta(n_pos_all, 0), row_eidx(n_pos_all, 0);
+	std::vector<uint16_t> pos_view(c->instance_mode ? n_pos_all : 0, 0);
+	for (uint32_t p = 0; p < n_pos_all; ++p)
+		if (ent_off[p + 1] > 0)
+			--ent_off[p + 1]; // the first entry is not in the CSR
 	for (size_t i = 0; i + 1 < ent_off.size(); ++i)
 		ent_off[i + 1] += ent_off[i];
 	const uint32_t total = ent_off[n_pos_all];
 	std::vector<uint2> pent(total);
-	std::vector<uint16_t> pent_view(c->instance_mode ? total : 0);
 	{
 		std::vector<uint32_t> fill(ent_off.begin(), ent_off.end() - 1);
 		for (int k = 0; k < 2; ++k) {
 			const EntryTable &t = c->ent[k];
 			for (uint32_t e = 0; e < t.n; ++e) {
 				const uint32_t p = c->pos_of_slot[t.mtx_slot[e]];
-				const uint32_t at = fill[p]++;
-				pent[at] = make_uint2(e | (k ? kEntKindTransparent : 0u), t.bounds_idx[e] | (uint32_t(t.flags[e] & HGB_ENTRY_DISABLED ? 1 : 0) << 24));
-				if (c->instance_mode)
-					pent_view[at] = t.view[e];
+				const uint32_t meta = t.bounds_idx[e] | (t.flags[e] & HGB_ENTRY_DISABLED ? kEntDisabled : 0u);
+				if (!(row_meta[p] & kEntHas)) {
+					row_meta[p] = meta | kEntHas | (k ? kEntKindTransparent : 0u);
+					row_eidx[p] = e;
+					if (c->instance_mode)
+						pos_view[p] = t.view[e];
+				} else {
+					row_meta[p] |= kEntMore;
+					pent[fill[p]++] = make_uint2(e | (k ? kEntKindTransparent : 0u), meta);
+					if (c->instance_mode && pos_view[p] != t.view[e])
+						return fail("display entries of transform slot %u belong to different instances (%u and %u)", t.mtx_slot[e], pos_view[p], t.view[e]);
+				}
 			}
 		}
 	}
 	if (upload(c, c->ent_off, ent_off.data(), (size_t(n_pos_all) + 1) * 4) || upload(c, c->pent, pent.data(), size_t(total) * 8))
 		return 1;
-	if (c->instance_mode && upload(c, c->pent_view, pent_view.data(), size_t(total) * 2))
+	if (c->instance_mode && upload(c, c->pos_view, pos_view.data(), size_t(n_pos_all) * 2))
 		return 1;
+	if (n_pos_all) {
+		DBuf rows;
+		if (upload(c, rows, row_meta.data(), size_t(n_pos_all) * 4))
+			return 1;
+		k_fill_rows<<<grid_for(n_pos_all), 256, 0, c->stream>>>(c->tiles.as<uint32_t>(), kRowEntMeta, rows.as<uint32_t>(), n_pos_all);
+		CK(cudaStreamSynchronize(c->stream));
+		if (upload(c, rows, row_eidx.data(), size_t(n_pos_all) * 4))
+			return 1;
+		k_fill_rows<<<grid_for(n_pos_all), 256, 0, c->stream>>>(c->tiles.as<uint32_t>(), kRowEntIdx, rows.as<uint32_t>(), n_pos_all);
+		CK(cudaStreamSynchronize(c->stream));
+		rows.release();
+		c->launches += 2;
+	}
 
 	// bones and tracks: slot -> position
 	std::vector<uint32_t> bone_pos(c->n_bones);
@@ -435,15 +491,44 @@ static int prepare_tables(hgb_ctx *c) {
 	}
 	if (upload(c, c->bone_mtx_pos, bone_pos.data(), size_t(c->n_bones) * 4))
 		return 1;
+	// tracks: every driven (position, pos|rot|scale) triple gets one anim_val slot, ordered by position; tracks are sorted by slot
+	// inside their write round so that consecutive threads write consecutive float4s
 	std::vector<Track> tr(c->tracks_h.size());
+	std::vector<uint64_t> keys_pg(tr.size());
 	for (size_t i = 0; i < tr.size(); ++i) {
 		const hgb_track &h = c->tracks_h[i];
 		if (h.target_slot >= c->n_slots)
 			return fail("track %zu targets slot %u outside the topology", i, h.target_slot);
-		tr[i] = Track{c->pos_of_slot[h.target_slot], h.key_off, h.key_count, h.play, h.kind, 0};
+		keys_pg[i] = (uint64_t(c->pos_of_slot[h.target_slot]) << 2) | (h.kind == 3 ? 1u : h.kind);
 	}
+	std::vector<uint64_t> uniq(keys_pg);
+	std::sort(uniq.begin(), uniq.end());
+	uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+	for (size_t i = 0; i < tr.size(); ++i) {
+		const hgb_track &h = c->tracks_h[i];
+		const uint32_t slot = uint32_t(std::lower_bound(uniq.begin(), uniq.end(), keys_pg[i]) - uniq.begin());
+		tr[i] = Track{slot, h.key_off, h.key_count, h.play, h.kind, 0};
+	}
+	for (size_t r = 0; r + 1 < c->round_off.size(); ++r)
+		std::sort(tr.begin() + c->round_off[r], tr.begin() + c->round_off[r + 1], [](const Track &a, const Track &b) { return a.out_slot < b.out_slot; });
 	if (upload(c, c->tracks_d, tr.data(), tr.size() * sizeof(Track)))
 		return 1;
+	const uint32_t n_bind = uint32_t(uniq.size());
+	if (n_bind) {
+		std::vector<uint32_t> bpos(n_bind);
+		std::vector<uint8_t> bgrp(n_bind);
+		for (uint32_t i = 0; i < n_bind; ++i)
+			bpos[i] = uint32_t(uniq[i] >> 2), bgrp[i] = uint8_t(uniq[i] & 3);
+		if (upload(c, c->bind_pos_d, bpos.data(), size_t(n_bind) * 4) || upload(c, c->bind_group_d, bgrp.data(), n_bind))
+			return 1;
+		CK(c->anim_val.reserve(size_t(n_bind) * 16));
+		CK(cudaMemsetAsync(c->cursor.p, 0, c->cursor.cap, c->stream));
+		k_bind_lanes<<<grid_for(n_bind), 256, 0, c->stream>>>(c->tiles.as<uint32_t>(), c->anim_val.as<float4>(), c->bind_pos_d.as<uint32_t>(),
+			c->bind_group_d.as<uint8_t>(), n_bind, 1);
+		++c->launches;
+		CK(cudaStreamSynchronize(c->stream)); // bpos/bgrp go out of scope
+		c->n_bound = n_bind;
+	}
 	CK(cudaStreamSynchronize(c->stream));
 	c->entries_dirty = false;
 	invalidate_graph(c);

@@ -10,9 +10,27 @@ namespace hgb {
 constexpr uint32_t kRoot = 0xffffffffu;
 constexpr int kMaxViews = 8;
 
-// entry meta word: bounds index in the low 24 bits, flags in the high 8
-constexpr uint32_t kEntDisabled = 1u << 24;
-constexpr uint32_t kEntKindTransparent = 1u << 31; // in PosEntry::entry (bit 31): which of the two entry tables
+// ---- node tiles -------------------------------------------------------------------------------------------------------------
+// Per-node inputs live in TILES of 32 consecutive positions: 12 rows of 32 words = 1536 contiguous bytes, so one warp reads its
+// 32 nodes as 12 fully coalesced 128-byte rows at immediate offsets from a single address:
+//   rows 0..8  px py pz rx ry rz sx sy sz   (hg::TransformTRS, engine/node.h:36-38)
+//   row  9     parent position (kRoot for roots)
+//   row  10    first display entry of the node: bounds index (bits 0..23) | kEnt* flags | animated-triple bits
+//   row  11    index of that entry in its kind's table
+// = exactly the 48 algorithmic bytes a node contributes to the fused pass. Nodes with more than one display entry (multi-list
+// models) continue in an overflow CSR (ent_off / pent), read only when kEntMore is set.
+constexpr uint32_t kTileRows = 12, kTileWords = kTileRows * 32;
+constexpr uint32_t kRowParent = 9, kRowEntMeta = 10, kRowEntIdx = 11;
+__host__ __device__ __forceinline__ size_t tile_word(uint32_t p, uint32_t row) { return size_t(p >> 5) * kTileWords + row * 32u + (p & 31u); }
+
+// entry meta word: bounds index in the low 24 bits, flags above
+constexpr uint32_t kEntDisabled = 1u << 24;        // node has NF_Disabled|NF_InstanceDisabled
+constexpr uint32_t kLaneAnimated = 1u << 25;       // bits 25/26/27: the pos / rot / scale triple of this node is driven by bound tracks:
+                                                   // its x row holds an index into anim_val[] (float4) instead of a value (see k_sample_tracks)
+constexpr uint32_t kLaneAnimatedMask = 7u << 25;
+constexpr uint32_t kEntHas = 1u << 29;             // row 10/11 hold an entry
+constexpr uint32_t kEntMore = 1u << 30;            // further entries of this node in the overflow CSR
+constexpr uint32_t kEntKindTransparent = 1u << 31; // which of the two entry tables (row 10; bit 31 of PosEntry::x in the CSR)
 
 // View frusta live in device memory (6 float4 per view: Top,Bottom,Left,Right,Near,Far, foundation/frustum.h:14; w holds -2*w) so that a camera
 // move is a 96-byte copy and never invalidates the captured frame graph.
@@ -22,20 +40,33 @@ struct Views {
 };
 
 struct SceneDev {
-	// per position (sorted order)
-	const float *trs;           // SoA: 9 arrays of stride trs_stride: px py pz rx ry rz sx sy sz
-	size_t trs_stride;
-	const uint32_t *parent_pos; // kRoot for roots
+	const uint32_t *tiles;      // node tiles (see above)
+	const float4 *anim_val;     // sampled pos / rot / scale triples of track-driven nodes (written coalesced by k_sample_tracks)
 	float *world;               // AoS 12 floats per position, 16-B aligned (== hg::Mat4 bit layout)
 	const uint8_t *preset;      // nullable: 1 -> world[p] was pre-set this frame (Scene::SetNodeWorldMatrix), keep it
-	// fused cull: display entries attached to each position (CSR)
-	const uint32_t *ent_off;    // n_pos + 1
-	const uint2 *pent;          // {entry index | kind bit, meta}
+	// fused cull
+	const uint32_t *ent_off;    // overflow CSR: n_pos + 1
+	const uint2 *pent;          //   {entry index | kind bit 31, meta}
 	const float *bounds6;       // MinMax table, 6 floats per (model, list)
 	uint8_t *vis0, *vis1;       // per entry table (opaque, transparent): bit v set -> survives view v
 	const float4 *inst_planes;  // per-instance frusta (6 float4 each) or null
-	const uint16_t *pent_view;  // per pent record: which instance frustum (only with inst_planes)
+	const uint16_t *pos_view;   // per position: which instance frustum (only with inst_planes)
+	int transpose_store;        // 1: world rows leave the SM as 3 contiguous 512-byte warp stores (shared-memory transpose)
 };
+
+// visibility mask of one display entry against the shared views (shared memory) or the node's instance frustum
+template <bool PER_INSTANCE>
+__device__ __forceinline__ uint32_t entry_visibility(const SceneDev &s, const Mat4 &world, uint32_t meta, const float4 *s_planes, int n_views, uint32_t p) {
+	if (meta & kEntDisabled)
+		return 0;
+	const Aabb bb = minmax_transform(world, s.bounds6 + size_t(meta & 0xffffffu) * 6);
+	if (PER_INSTANCE)
+		return survives_frustum(s.inst_planes + size_t(s.pos_view[p]) * 6, bb) ? 1u : 0u;
+	uint32_t bits = 0;
+	for (int v = 0; v < n_views; ++v)
+		bits |= survives_frustum(s_planes + v * 6, bb) ? (1u << v) : 0u;
+	return bits;
+}
 
 // ---- world-matrix propagation, one level per launch ---------------------------------------------------------------------
 // Replaces Scene::ComputeTransformWorldMatrix (engine/scene.cpp:263-277) for the positions [begin, end) of one hierarchy
@@ -43,47 +74,86 @@ struct SceneDev {
 // by the previous launch. With FUSED the freshly computed world matrix is tested, still in registers, against the
 // view frusta for every display entry attached to the position (GetModelDisplayLists flag logic + CullModelDisplayLists,
 // engine/scene.cpp:330-364, engine/render_pipeline.cpp:2098-2104) and only a 1-byte visibility mask per entry is written.
+// `begin` is a multiple of 32 relative to the grid (blockDim = 256), so a warp covers 32 consecutive positions.
 template <bool FUSED, bool PER_INSTANCE>
-__global__ void __launch_bounds__(256) k_update_level(SceneDev s, Views views, uint32_t begin, uint32_t end) {
+__global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views, uint32_t begin, uint32_t end) {
 	__shared__ float4 s_planes[kMaxViews * 6];
+	__shared__ float4 s_out[8][96]; // per warp: 32 world matrices = 1536 B, for the transposed store
 	if (FUSED && !PER_INSTANCE) { // the shared view frusta: one broadcast LDS.128 per plane instead of a global load
 		if (threadIdx.x < uint32_t(views.n_views) * 6u)
 			s_planes[threadIdx.x] = views.planes[threadIdx.x];
 		__syncthreads();
 	}
 	const uint32_t p = begin + blockIdx.x * blockDim.x + threadIdx.x;
-	if (p >= end)
+	const bool live = p < end;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	if (__ballot_sync(0xffffffffu, live) == 0)
 		return;
 
 	Mat4 world;
-	if (s.preset && s.preset[p]) {
-		world = load_mat4(s.world + size_t(p) * 12);
-	} else {
-		const float *t = s.trs + p;
-		const size_t st = s.trs_stride;
-		const float px = t[0], py = t[st], pz = t[2 * st], ex = t[3 * st], ey = t[4 * st], ez = t[5 * st], sx = t[6 * st], sy = t[7 * st], sz = t[8 * st];
-		const uint32_t par = s.parent_pos[p];
-		world = transformation_mat4(px, py, pz, ex, ey, ez, sx, sy, sz);
-		if (par != kRoot)
-			world = mat4_mul(load_mat4(s.world + size_t(par) * 12), world);
+	uint32_t meta = 0, eidx = 0;
+	if (live) {
+		const uint32_t *t = s.tiles + tile_word(p, 0);
+		meta = t[kRowEntMeta * 32];
+		if (FUSED)
+			eidx = t[kRowEntIdx * 32];
+		if (s.preset && s.preset[p]) {
+			world = load_mat4(s.world + size_t(p) * 12);
+		} else {
+			float px = __uint_as_float(t[0]), py = __uint_as_float(t[32]), pz = __uint_as_float(t[64]);
+			float ex = __uint_as_float(t[96]), ey = __uint_as_float(t[128]), ez = __uint_as_float(t[160]);
+			float sx = __uint_as_float(t[192]), sy = __uint_as_float(t[224]), sz = __uint_as_float(t[256]);
+			const uint32_t par = t[kRowParent * 32];
+			if (meta & kLaneAnimatedMask) { // track-driven triples: fetch the value sampled this frame (or the last one sampled)
+				if (meta & kLaneAnimated) {
+					const float4 v = s.anim_val[__float_as_uint(px)];
+					px = v.x, py = v.y, pz = v.z;
+				}
+				if (meta & (kLaneAnimated << 1)) {
+					const float4 v = s.anim_val[__float_as_uint(ex)];
+					ex = v.x, ey = v.y, ez = v.z;
+				}
+				if (meta & (kLaneAnimated << 2)) {
+					const float4 v = s.anim_val[__float_as_uint(sx)];
+					sx = v.x, sy = v.y, sz = v.z;
+				}
+			}
+			world = transformation_mat4(px, py, pz, ex, ey, ez, sx, sy, sz);
+			if (par != kRoot)
+				world = mat4_mul(load_mat4(s.world + size_t(par) * 12), world);
+		}
+	}
+
+	// store the world rows (a preset row is rewritten with its own value)
+	if (s.transpose_store) {
+		float4 *so = s_out[warp];
+		if (live) {
+			so[lane * 3 + 0] = make_float4(world.m[0][0], world.m[0][1], world.m[0][2], world.m[0][3]);
+			so[lane * 3 + 1] = make_float4(world.m[1][0], world.m[1][1], world.m[1][2], world.m[1][3]);
+			so[lane * 3 + 2] = make_float4(world.m[2][0], world.m[2][1], world.m[2][2], world.m[2][3]);
+		}
+		__syncwarp();
+		const uint32_t p0 = p - lane;                              // first position of the warp
+		const uint32_t n_f4 = (min(end, p0 + 32u) - p0) * 3u;       // float4s this warp owns
+		float4 *dst = reinterpret_cast<float4 *>(s.world) + size_t(p0) * 3;
+#pragma unroll
+		for (int j = 0; j < 3; ++j)
+			if (lane + 32u * j < n_f4)
+				dst[lane + 32u * j] = so[lane + 32u * j];
+	} else if (live) {
 		store_mat4(s.world + size_t(p) * 12, world);
 	}
 
-	if (FUSED) {
-		const uint32_t e0 = s.ent_off[p], e1 = s.ent_off[p + 1];
-		for (uint32_t k = e0; k < e1; ++k) {
-			const uint2 rec = s.pent[k];
-			uint32_t bits = 0;
-			if (!(rec.y & kEntDisabled)) {
-				const Aabb bb = minmax_transform(world, s.bounds6 + size_t(rec.y & 0xffffffu) * 6);
-				if (PER_INSTANCE) {
-					bits = survives_frustum(s.inst_planes + size_t(s.pent_view[k]) * 6, bb) ? 1u : 0u;
-				} else {
-					for (int v = 0; v < views.n_views; ++v)
-						bits |= survives_frustum(s_planes + v * 6, bb) ? (1u << v) : 0u;
-				}
+	if (FUSED && live && (meta & kEntHas)) {
+		const uint32_t bits = entry_visibility<PER_INSTANCE>(s, world, meta, s_planes, views.n_views, p);
+		((meta & kEntKindTransparent) ? s.vis1 : s.vis0)[eidx] = uint8_t(bits);
+		if (meta & kEntMore) {
+			const uint32_t e0 = s.ent_off[p], e1 = s.ent_off[p + 1];
+			for (uint32_t k = e0; k < e1; ++k) {
+				const uint2 rec = s.pent[k];
+				const uint32_t b = entry_visibility<PER_INSTANCE>(s, world, rec.y, s_planes, views.n_views, p);
+				((rec.x >> 31) ? s.vis1 : s.vis0)[rec.x & 0x7fffffffu] = uint8_t(b);
 			}
-			((rec.x >> 31) ? s.vis1 : s.vis0)[rec.x & 0x7fffffffu] = uint8_t(bits);
 		}
 	}
 }

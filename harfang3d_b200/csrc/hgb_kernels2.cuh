@@ -9,8 +9,8 @@ namespace hgb {
 // transform targets: Evaluate(track, t, value) -> TRS lane of the bound node's transform.
 //   GetIntervalKeys (engine/animation.h:109-128) is a linear scan for the first key with key.t > t; the binary search
 //   below returns the same index (upper_bound) because keys are sorted by time.
-struct Track { // 16 B
-	uint32_t target_pos; // position of the target transform
+struct alignas(16) Track { // 16 B, read as one uint4
+	uint32_t out_slot;   // anim_val[] slot of the (node, pos|rot|scale) triple this track drives
 	uint32_t key_off;    // first key in the pool of its kind
 	uint32_t key_count;
 	uint16_t play;       // index into play_t[]
@@ -18,25 +18,33 @@ struct Track { // 16 B
 	uint8_t pad;
 };
 
+// One key = one 32-byte record (one DRAM sector), vec3 Hermite and quaternion keys alike:
+//   q0 = {t lo, t hi, v.x, v.y}   q1 = {v.z, tension | v.w, bias, -}
+// so the four keys of a Hermite evaluation are 128 contiguous bytes and their times come with them (AnimKeyHermiteT<Vec3>,
+// AnimKeyT<Quaternion>: engine/animation.h:28-46). Quaternion keys follow the vec3 keys in the same pool.
 struct AnimDev {
 	const Track *tracks;
 	const int64_t *play_t;    // per playing anim: evaluation time (ns), INT64_MIN = not playing
-	const int64_t *v3_t;      // vec3 Hermite key pool: times
-	const float4 *v3_val;     //   {v.x, v.y, v.z, tension}
-	const float *v3_bias;     //   bias
-	const int64_t *q_t;       // quaternion key pool
-	const float4 *q_val;
-	float *trs;               // SoA TRS (see SceneDev)
-	size_t trs_stride;
+	const uint4 *keys;        // 2 x uint4 per key
+	uint32_t quat_base;       // first quaternion key in the pool
+	uint32_t *cursor;         // per track: lower key of the interval found last frame (search hint only, never changes a result)
+	float4 *anim_val;         // output: one float4 per driven (node, triple); consecutive tracks write consecutive slots
 };
+
+__device__ __forceinline__ int64_t key_time(const uint4 *keys, uint32_t k) {
+	const uint2 t = *reinterpret_cast<const uint2 *>(keys + size_t(k) * 2);
+	return int64_t(uint64_t(t.x) | (uint64_t(t.y) << 32));
+}
 
 __device__ __forceinline__ float time_to_sec_f(int64_t t) { return __double2float_rn(__ddiv_rn(double(t), 1000000000.0)); } // foundation/time.h:13
 
-__device__ __forceinline__ uint32_t upper_bound_i64(const int64_t *__restrict__ t, uint32_t n, int64_t at) {
+// GetIntervalKeys (engine/animation.h:109-128) scans linearly for the first key with key.t > t; keys are sorted by time, so this
+// binary search returns the same index (upper_bound).
+__device__ __forceinline__ uint32_t upper_bound_keys(const uint4 *keys, uint32_t n, int64_t at) {
 	uint32_t lo = 0, hi = n;
 	while (lo < hi) {
 		const uint32_t mid = (lo + hi) >> 1;
-		if (t[mid] > at)
+		if (key_time(keys, mid) > at)
 			hi = mid;
 		else
 			lo = mid + 1;
@@ -95,54 +103,88 @@ __global__ void __launch_bounds__(256) k_sample_tracks(AnimDev a, uint32_t first
 	const uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= first + n_tracks)
 		return;
-	const Track trk = a.tracks[i];
+	Track trk;
+	*reinterpret_cast<uint4 *>(&trk) = *reinterpret_cast<const uint4 *>(a.tracks + i);
 	const int64_t at = a.play_t[trk.play];
 	if (at == INT64_MIN || trk.key_count == 0) // not playing / Evaluate() returns false on an empty track (animation.h:156)
 		return;
 	const uint32_t n = trk.key_count;
-	float *dst = a.trs + trk.target_pos;
+	const uint4 *keys = a.keys + size_t(trk.key_off + (trk.kind == 3 ? a.quat_base : 0u)) * 2;
+
+	// interval search: the interval found last frame, then the one after it (a frame rarely advances more than one key), then the
+	// binary search (time jumps, loop wrap)
+	uint32_t cur = min(a.cursor[i], n - 1);
+	uint4 k1a = keys[size_t(cur) * 2], k1b = keys[size_t(cur) * 2 + 1]; // candidate kf1
+	uint32_t nxt = min(cur + 1, n - 1);
+	uint4 k2a = keys[size_t(nxt) * 2], k2b = keys[size_t(nxt) * 2 + 1]; // candidate kf2
+	int64_t t_cur = int64_t(uint64_t(k1a.x) | (uint64_t(k1a.y) << 32)), t_nxt = int64_t(uint64_t(k2a.x) | (uint64_t(k2a.y) << 32));
+	uint32_t ub;
+	if (t_cur <= at && (cur + 1 == n || at < t_nxt)) {
+		ub = cur + 1;
+	} else {
+		bool found = false;
+		if (cur + 1 < n && t_nxt <= at) { // advance by one key
+			const uint32_t n2 = min(cur + 2, n - 1);
+			const uint4 k3a = keys[size_t(n2) * 2], k3b = keys[size_t(n2) * 2 + 1];
+			const int64_t t_n2 = int64_t(uint64_t(k3a.x) | (uint64_t(k3a.y) << 32));
+			if (cur + 2 == n || at < t_n2) {
+				found = true;
+				ub = cur + 2;
+				k1a = k2a, k1b = k2b, k2a = k3a, k2b = k3b;
+			}
+		}
+		if (!found) {
+			ub = upper_bound_keys(keys, n, at);
+			if (ub > 0 && ub < n) { // reload the pair the evaluation needs
+				k1a = keys[size_t(ub - 1) * 2], k1b = keys[size_t(ub - 1) * 2 + 1];
+				k2a = keys[size_t(ub) * 2], k2b = keys[size_t(ub) * 2 + 1];
+			}
+		}
+		a.cursor[i] = ub > 0 ? ub - 1 : 0;
+	}
+	float4 *dst = a.anim_val + trk.out_slot;
+
 	if (trk.kind == 3) { // AnimTrackT<Quaternion>: EvaluateLinear animation.h:141-153, then ToEuler(Normalize())
-		const int64_t *t = a.q_t + trk.key_off;
-		const float4 *v = a.q_val + trk.key_off;
-		const uint32_t ub = upper_bound_i64(t, n, at);
 		float4 q;
 		if (ub == 0 || ub == n) {
-			q = v[ub == 0 ? 0 : n - 1];
+			const uint32_t k = ub == 0 ? 0 : n - 1;
+			const uint4 ka = keys[size_t(k) * 2], kb = keys[size_t(k) * 2 + 1];
+			q = make_float4(__uint_as_float(ka.z), __uint_as_float(ka.w), __uint_as_float(kb.x), __uint_as_float(kb.y));
 		} else {
-			const float4 q0 = v[ub - 1], q1 = v[ub];
-			const float k = time_to_sec_f(at - t[ub - 1]) / time_to_sec_f(t[ub] - t[ub - 1]);
+			const float4 q0 = make_float4(__uint_as_float(k1a.z), __uint_as_float(k1a.w), __uint_as_float(k1b.x), __uint_as_float(k1b.y));
+			const float4 q1 = make_float4(__uint_as_float(k2a.z), __uint_as_float(k2a.w), __uint_as_float(k2b.x), __uint_as_float(k2b.y));
+			const int64_t t1 = int64_t(uint64_t(k1a.x) | (uint64_t(k1a.y) << 32)), t2 = int64_t(uint64_t(k2a.x) | (uint64_t(k2a.y) << 32));
+			const float k = time_to_sec_f(at - t1) / time_to_sec_f(t2 - t1);
 			q = make_float4(q0.x + (q1.x - q0.x) * k, q0.y + (q1.y - q0.y) * k, q0.z + (q1.z - q0.z) * k, q0.w + (q1.w - q0.w) * k);
 		}
 		float ex, ey, ez;
 		quat_to_euler(q.x, q.y, q.z, q.w, ex, ey, ez);
-		dst[3 * a.trs_stride] = ex, dst[4 * a.trs_stride] = ey, dst[5 * a.trs_stride] = ez;
+		*dst = make_float4(ex, ey, ez, 0.f);
 		return;
 	}
 	// AnimTrackHermiteT<Vec3>: EvaluateHermite animation.h:155-169
-	const int64_t *t = a.v3_t + trk.key_off;
-	const float4 *v = a.v3_val + trk.key_off;
-	const uint32_t ub = upper_bound_i64(t, n, at);
 	float ox, oy, oz;
 	if (ub == 0 || ub == n) {
-		const float4 k = v[ub == 0 ? 0 : n - 1];
-		ox = k.x, oy = k.y, oz = k.z;
+		const uint32_t k = ub == 0 ? 0 : n - 1;
+		const uint4 ka = keys[size_t(k) * 2], kb = keys[size_t(k) * 2 + 1];
+		ox = __uint_as_float(ka.z), oy = __uint_as_float(ka.w), oz = __uint_as_float(kb.x);
 	} else {
 		const uint32_t kf1 = ub - 1, kf2 = ub;
 		const uint32_t kf0 = kf1 > 0 ? kf1 - 1 : 0, kf3 = kf2 + 1 < n - 1 ? kf2 + 1 : n - 1;
-		const float u = time_to_sec_f(at - t[kf1]) / time_to_sec_f(t[kf2] - t[kf1]);
-		const float4 y0 = v[kf0], y1 = v[kf1], y2 = v[kf2], y3 = v[kf3];
-		const float tension = y1.w, bias = a.v3_bias[trk.key_off + kf1];
-		const float t2 = u * u, t3 = t2 * u;
-		const float a0 = 2.F * t3 - 3.F * t2 + 1.F;
-		const float a1 = t3 - 2.F * t2 + u;
-		const float a2 = t3 - t2;
-		const float a3 = -2.F * t3 + 3.F * t2;
-		ox = hermite1(y0.x, y1.x, y2.x, y3.x, a0, a1, a2, a3, tension, bias);
-		oy = hermite1(y0.y, y1.y, y2.y, y3.y, a0, a1, a2, a3, tension, bias);
-		oz = hermite1(y0.z, y1.z, y2.z, y3.z, a0, a1, a2, a3, tension, bias);
+		const uint4 k0a = keys[size_t(kf0) * 2], k0b = keys[size_t(kf0) * 2 + 1], k3a = keys[size_t(kf3) * 2], k3b = keys[size_t(kf3) * 2 + 1];
+		const int64_t t1 = int64_t(uint64_t(k1a.x) | (uint64_t(k1a.y) << 32)), t2 = int64_t(uint64_t(k2a.x) | (uint64_t(k2a.y) << 32));
+		const float u = time_to_sec_f(at - t1) / time_to_sec_f(t2 - t1);
+		const float tension = __uint_as_float(k1b.y), bias = __uint_as_float(k1b.z);
+		const float t2_ = u * u, t3 = t2_ * u;
+		const float a0 = 2.F * t3 - 3.F * t2_ + 1.F;
+		const float a1 = t3 - 2.F * t2_ + u;
+		const float a2 = t3 - t2_;
+		const float a3 = -2.F * t3 + 3.F * t2_;
+		ox = hermite1(__uint_as_float(k0a.z), __uint_as_float(k1a.z), __uint_as_float(k2a.z), __uint_as_float(k3a.z), a0, a1, a2, a3, tension, bias);
+		oy = hermite1(__uint_as_float(k0a.w), __uint_as_float(k1a.w), __uint_as_float(k2a.w), __uint_as_float(k3a.w), a0, a1, a2, a3, tension, bias);
+		oz = hermite1(__uint_as_float(k0b.x), __uint_as_float(k1b.x), __uint_as_float(k2b.x), __uint_as_float(k3b.x), a0, a1, a2, a3, tension, bias);
 	}
-	const size_t lane0 = size_t(trk.kind) * 3;
-	dst[lane0 * a.trs_stride] = ox, dst[(lane0 + 1) * a.trs_stride] = oy, dst[(lane0 + 2) * a.trs_stride] = oz;
+	*dst = make_float4(ox, oy, oz, 0.f);
 }
 
 // ---- skin bone matrices ----------------------------------------------------------------------------------------------
@@ -179,28 +221,71 @@ __global__ void __launch_bounds__(256) k_bone_matrices(BoneDev b) {
 }
 
 // ---- layout shuffles -----------------------------------------------------------------------------------------------------
-// host TRS upload: AoS hg::TransformTRS (9 floats, engine/node.h:36-38) in SLOT order -> SoA lanes in POSITION order
+// host TRS upload: AoS hg::TransformTRS (9 floats, engine/node.h:36-38) in SLOT order -> tile rows in POSITION order
 __global__ void __launch_bounds__(256) k_scatter_trs(const float *__restrict__ staging9, const uint32_t *__restrict__ pos_of_slot, uint32_t first_slot,
-	uint32_t count, float *__restrict__ trs, size_t stride) {
+	uint32_t count, uint32_t *__restrict__ tiles, float4 *__restrict__ anim_val) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= count)
 		return;
 	const uint32_t p = pos_of_slot ? pos_of_slot[first_slot + i] : first_slot + i;
 	const float *s = staging9 + size_t(i) * 9;
+	uint32_t *d = tiles + tile_word(p, 0);
+	const uint32_t meta = d[kRowEntMeta * 32];
 #pragma unroll
-	for (int c = 0; c < 9; ++c)
-		trs[c * stride + p] = s[c];
+	for (int g = 0; g < 3; ++g) {
+		if (meta & (kLaneAnimated << g)) // track-driven triple: the value lives in anim_val (SetTransformPos on an animated node)
+			anim_val[d[g * 96]] = make_float4(s[g * 3], s[g * 3 + 1], s[g * 3 + 2], 0.f);
+		else
+			d[g * 96] = __float_as_uint(s[g * 3]), d[g * 96 + 32] = __float_as_uint(s[g * 3 + 1]), d[g * 96 + 64] = __float_as_uint(s[g * 3 + 2]);
+	}
 }
 
-__global__ void __launch_bounds__(256) k_gather_trs(const float *__restrict__ trs, size_t stride, const uint32_t *__restrict__ pos_of_slot, uint32_t first_slot,
-	uint32_t count, float *__restrict__ out9) {
+__global__ void __launch_bounds__(256) k_gather_trs(const uint32_t *__restrict__ tiles, const uint32_t *__restrict__ pos_of_slot, uint32_t first_slot,
+	uint32_t count, float *__restrict__ out9, const float4 *__restrict__ anim_val) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= count)
 		return;
 	const uint32_t p = pos_of_slot ? pos_of_slot[first_slot + i] : first_slot + i;
+	const uint32_t *s = tiles + tile_word(p, 0);
+	const uint32_t meta = s[kRowEntMeta * 32];
+	float *o = out9 + size_t(i) * 9;
 #pragma unroll
-	for (int c = 0; c < 9; ++c)
-		out9[size_t(i) * 9 + c] = trs[c * stride + p];
+	for (int g = 0; g < 3; ++g) {
+		if (meta & (kLaneAnimated << g)) {
+			const float4 v = anim_val[s[g * 96]];
+			o[g * 3] = v.x, o[g * 3 + 1] = v.y, o[g * 3 + 2] = v.z;
+		} else {
+			o[g * 3] = __uint_as_float(s[g * 96]), o[g * 3 + 1] = __uint_as_float(s[g * 96 + 32]), o[g * 3 + 2] = __uint_as_float(s[g * 96 + 64]);
+		}
+	}
+}
+
+// Bind / unbind the track-driven triples. bind: anim_val[slot] takes the triple's current value, the tile's x row takes the slot
+// and the animated bit is set; unbind is the inverse (the last sampled value stays in the TRS, as in the reference where
+// EvaluateBoundAnim writes into the Transform, engine/scene.cpp:2165-2180).
+__global__ void __launch_bounds__(256) k_bind_lanes(uint32_t *__restrict__ tiles, float4 *__restrict__ anim_val, const uint32_t *__restrict__ bind_pos,
+	const uint8_t *__restrict__ bind_group, uint32_t n, int bind) {
+	const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+	if (slot >= n)
+		return;
+	const uint32_t g = bind_group[slot];
+	uint32_t *d = tiles + tile_word(bind_pos[slot], 0);
+	if (bind) {
+		anim_val[slot] = make_float4(__uint_as_float(d[g * 96]), __uint_as_float(d[g * 96 + 32]), __uint_as_float(d[g * 96 + 64]), 0.f);
+		d[g * 96] = slot;
+		atomicOr(d + kRowEntMeta * 32, kLaneAnimated << g);
+	} else {
+		const float4 v = anim_val[slot];
+		d[g * 96] = __float_as_uint(v.x), d[g * 96 + 32] = __float_as_uint(v.y), d[g * 96 + 64] = __float_as_uint(v.z);
+		atomicAnd(d + kRowEntMeta * 32, ~(kLaneAnimated << g));
+	}
+}
+
+// rows 9..11 of the tiles (parent position, first entry meta, first entry index) from position-ordered staging arrays
+__global__ void __launch_bounds__(256) k_fill_rows(uint32_t *__restrict__ tiles, uint32_t row, const uint32_t *__restrict__ src, uint32_t n_pos) {
+	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p < n_pos)
+		tiles[tile_word(p, row)] = src[p];
 }
 
 // worlds in POSITION order -> SLOT order (only when the permutation is not the identity); one thread per float4

@@ -46,19 +46,24 @@ __device__ __forceinline__ double sc_reduce_large(uint32_t xi, int &n_out) {
 // The two polynomials of sincosf.h on the reduced argument, each rounded once to float. Every operation is sign-symmetric
 // under round-to-nearest, so sin_poly(-x) == -sin_poly(x) and the negated-coefficient cosine table of glibc (__sincosf_table[1])
 // gives exactly -cos_poly(x2): quadrant signs are applied to the rounded floats instead of evaluating four variants.
+// Coefficients in constant memory: DFMA/DMUL take them as c[bank][offset] operands (an immediate double costs two UMOVs per use).
+__constant__ double c_sc[11] = {
+	-0x1.994eb3774cf24p-13, 0x1.1107605230bc4p-7, -0x1.555545995a603p-3,                             // S3 S2 S1
+	0x1.99343027bf8c3p-16, -0x1.6c087e89a359dp-10, -0x1.ffffffd0c621cp-2, 0x1p0, 0x1.55553e1068f19p-5, // C4 C3 C1 C0 C2
+	0x1.45F306DC9C883p+23, 0x1.921FB54442D18p0, 0x1.921FB54442D18p-62};                             // 2^24*2/pi, pi/2, pi/2 * 2^-62
 __device__ __forceinline__ float sc_sin_poly(double x, double x2) {
 	const double x3 = __dmul_rn(x, x2);
-	const double s1 = fma(x2, -0x1.994eb3774cf24p-13, 0x1.1107605230bc4p-7);
+	const double s1 = fma(x2, c_sc[0], c_sc[1]);
 	const double x7 = __dmul_rn(x3, x2);
-	const double s = fma(x3, -0x1.555545995a603p-3, x);
+	const double s = fma(x3, c_sc[2], x);
 	return __double2float_rn(fma(x7, s1, s));
 }
 __device__ __forceinline__ float sc_cos_poly(double x2) {
 	const double x4 = __dmul_rn(x2, x2);
-	const double c2 = fma(x2, 0x1.99343027bf8c3p-16, -0x1.6c087e89a359dp-10);
-	const double c1 = fma(x2, -0x1.ffffffd0c621cp-2, 0x1p0);
+	const double c2 = fma(x2, c_sc[3], c_sc[4]);
+	const double c1 = fma(x2, c_sc[5], c_sc[6]);
 	const double x6 = __dmul_rn(x4, x2);
-	const double c = fma(x4, 0x1.55553e1068f19p-5, c1);
+	const double c = fma(x4, c_sc[7], c1);
 	return __double2float_rn(fma(x6, c2, c));
 }
 
@@ -88,9 +93,9 @@ __device__ __forceinline__ void sincos_libm(float y, float &s_out, float &c_out)
 		return;
 	}
 	const double x = double(y);
-	const double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);
+	const double r = __dmul_rn(x, c_sc[8]);
 	const int n = (__double2int_rz(r) + 0x800000) >> 24;
-	const double xr = fma(-double(n), 0x1.921FB54442D18p0, x);
+	const double xr = fma(-double(n), c_sc[9], x);
 	const double x2 = __dmul_rn(xr, xr);
 	const float sp = sc_sin_poly(xr, x2), cp = sc_cos_poly(x2);
 	float s = (n & 1) ? cp : sp, c = (n & 1) ? sp : cp;

@@ -329,3 +329,51 @@ def test_profile_counters(hgb):
     prof = ctx.get_profile()
     assert prof["k_update_level"][1] == 4 and prof["k_update_level"][0] > 0 and prof["k_compact"][1] == 1
     ctx.close()
+
+
+def test_edits_while_animated(hgb, oracles):
+    """TRS uploads, re-parenting and track re-binding on a scene whose Position triples are track-driven (the sampled values live in
+    a side array on the device): every observable (worlds, TRS, visible list) keeps matching the reference's Scene after each edit."""
+    ref, _ = oracles
+    if ref is None:
+        pytest.skip("needs the compiled reference")
+    from tests.scene_io import RefScene
+    from tests.oracle_lib import P
+    rng = np.random.default_rng(71)
+    fs = scenegen.static_scene(4_000, 5, 6, n_models=3, seed=71)
+    nodes = np.sort(rng.choice(fs.n, 1_200, replace=False)).astype(np.int32)
+    scenegen.add_position_tracks(fs, nodes, rng, n_keys=12)
+    ctx = hgb.Context(0)
+    t = hostmirror.upload(ctx, fs)
+    orc = RefScene(ref, fs)
+    clocks = hostmirror.PlayClocks(fs)
+    fr = hostmirror.scene_frusta(fs)[0]
+
+    def frame():
+        ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True)
+        orc.update(scenegen.FRAME_DT)
+        assert (bits(ctx.get_worlds()) == bits(orc.worlds()[: fs.n])).all()
+        assert (bits(ctx.get_trs()) == bits(orc.trs(np.arange(fs.n)))).all()
+        check_visible(ctx, t, orc, fr)
+
+    frame(); frame()
+    # 1. the host rewrites every TRS (SetTransformTRS on animated nodes too: the track overwrites pos again next frame)
+    new_trs = fs.trs.copy()
+    new_trs[:, 3:6] += rng.uniform(-0.3, 0.3, (fs.n, 3)).astype(np.float32)
+    new_trs[:, 0:3] += 0.25
+    ctx.upload_trs(np.ascontiguousarray(new_trs))
+    for i in range(fs.n):
+        ref.hgref_set_trs(orc.h, i, P(np.ascontiguousarray(new_trs[i])))
+    assert (bits(ctx.get_trs()) == bits(orc.trs(np.arange(fs.n)))).all()
+    frame()
+    # 2. re-parent a few hundred leaves under other nodes of a smaller index (no cycles): the depth-sorted layout is rebuilt
+    parent = fs.parent.copy()
+    leaves = np.setdiff1d(np.arange(fs.n), np.unique(parent[parent >= 0]))
+    moved = rng.choice(leaves, 300, replace=False)
+    for nd in moved:
+        parent[nd] = int(rng.integers(0, 40))
+        ref.hgref_set_parent(orc.h, int(nd), int(parent[nd]))
+    fs.parent = parent
+    ctx.set_topology(np.where(parent >= 0, parent, 0xFFFFFFFF).astype(np.uint32))
+    frame(); frame()
+    orc.close(); ctx.close()
