@@ -179,6 +179,7 @@ def main():
     ap.add_argument("--workload", default="c4", choices=["c4", "c2", "c5"])
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (debug only; the reported config says so)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lookahead", type=int, default=0, help="A/B switch: L2 prefetch distance in positions (0 = default, -1 = off)")
     ap.add_argument("--row-store", action="store_true", help="A/B switch: per-thread world row stores instead of the transposed warp store")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -199,7 +200,7 @@ def main():
 
     fs, desc = workload(args.workload, rank, args.scale)
     n_nodes = fs.n
-    ctx = harfang3d_b200.Context(local_rank, row_store=args.row_store)
+    ctx = harfang3d_b200.Context(local_rank, row_store=args.row_store, lookahead=args.lookahead)
     t = hostmirror.upload(ctx, fs)
     n_entries = len(t["ent0_mtx_slot"]) + len(t["ent1_mtx_slot"])
     clocks = hostmirror.PlayClocks(fs)

@@ -128,6 +128,7 @@ struct hgb_ctx {
 	DBuf tiles, world[2], preset, pos_of_slot_d; // tiles: node tiles (TRS rows, parent, first entry), see hgb_kernels.cuh
 	uint32_t n_tiles = 0;
 	bool transpose_store = true;
+	uint32_t lookahead = 0; // positions (see SceneDev::lookahead)
 	int cur = 0; // world[cur] = current frame
 	bool preset_pending = false, preset_dirty = false;
 	DBuf preset_pos, preset_mat;
@@ -243,7 +244,14 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 	hgb_ctx *c = new hgb_ctx;
 	c->device = device;
 	c->use_graph = opt ? opt->use_graph != 0 : true;
-	c->transpose_store = opt ? opt->reserved[0] == 0 : true; // reserved[0] = 1: per-thread 48-byte row stores (A/B switch for profiling)
+	{
+		cudaDeviceProp prop;
+		if (cudaGetDeviceProperties(&prop, device) == cudaSuccess)
+			c->lookahead = uint32_t(prop.multiProcessorCount) * 6u * 256u; // one wave of resident CTAs (6 x 256 threads per SM)
+		if (opt && opt->lookahead != 0)
+			c->lookahead = opt->lookahead < 0 ? 0u : uint32_t(opt->lookahead); // A/B switch: -1 = off, n = positions
+	}
+	c->transpose_store = opt ? opt->row_store == 0 : true; // reserved[0] = 1: per-thread 48-byte row stores (A/B switch for profiling)
 	if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
 		cudaEventCreate(&c->ev1) != cudaSuccess) {
 		fail("hgb_create: stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));

@@ -6,6 +6,7 @@ static SceneDev scene_dev(hgb_ctx *c, bool with_preset) {
 	s.tiles = c->tiles.as<uint32_t>();
 	s.anim_val = c->anim_val.as<float4>();
 	s.transpose_store = c->transpose_store ? 1 : 0;
+	s.lookahead = c->lookahead;
 	s.world = c->world[c->cur].as<float>();
 	s.preset = with_preset ? c->preset.as<uint8_t>() : nullptr;
 	s.ent_off = c->ent_off.as<uint32_t>();

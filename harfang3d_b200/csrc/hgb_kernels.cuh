@@ -52,7 +52,11 @@ struct SceneDev {
 	const float4 *inst_planes;  // per-instance frusta (6 float4 each) or null
 	const uint16_t *pos_view;   // per position: which instance frustum (only with inst_planes)
 	int transpose_store;        // 1: world rows leave the SM as 3 contiguous 512-byte warp stores (shared-memory transpose)
+	uint32_t lookahead;         // positions: a warp asks L2 for the tile (and its parents' rows) this far ahead of its own; 0 = off
 };
+
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
 // visibility mask of one display entry against the shared views (shared memory) or the node's instance frustum
 template <bool PER_INSTANCE>
@@ -89,6 +93,13 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 	if (__ballot_sync(0xffffffffu, live) == 0)
 		return;
+	// Software prefetch into L2: CTAs are dispatched in position order, so the tile `lookahead` positions ahead belongs to a CTA that
+	// starts about one CTA lifetime from now. Its 12 rows are requested by 12 lanes here, which turns the first (and otherwise fully
+	// exposed) DRAM latency of that CTA into an L2 hit.
+	const uint32_t pf = p - lane + s.lookahead;
+	const bool do_pf = s.lookahead != 0 && pf < end;
+	if (do_pf && lane < kTileRows)
+		prefetch_l2(s.tiles + tile_word(pf & ~31u, lane));
 
 	Mat4 world;
 	uint32_t meta = 0, eidx = 0;
@@ -104,6 +115,10 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 			float ex = __uint_as_float(t[96]), ey = __uint_as_float(t[128]), ez = __uint_as_float(t[160]);
 			float sx = __uint_as_float(t[192]), sy = __uint_as_float(t[224]), sz = __uint_as_float(t[256]);
 			const uint32_t par = t[kRowParent * 32];
+			if (par != kRoot) { // start the parent row on its way while the trigonometry runs (no registers held)
+				prefetch_l1(s.world + size_t(par) * 12);
+				prefetch_l1(s.world + size_t(par) * 12 + 11);
+			}
 			if (meta & kLaneAnimatedMask) { // track-driven triples: fetch the value sampled this frame (or the last one sampled)
 				if (meta & kLaneAnimated) {
 					const float4 v = s.anim_val[__float_as_uint(px)];
@@ -142,6 +157,12 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 				dst[lane + 32u * j] = so[lane + 32u * j];
 	} else if (live) {
 		store_mat4(s.world + size_t(p) * 12, world);
+	}
+
+	if (do_pf && lane < 3) { // ... and the rows of that tile's parents (siblings are adjacent: a few hundred contiguous bytes)
+		const uint32_t par_f = s.tiles[tile_word(pf, kRowParent)];
+		if (par_f != kRoot)
+			prefetch_l2(s.world + size_t(par_f) * 12 + lane * 32);
 	}
 
 	if (FUSED && live && (meta & kEntHas)) {
@@ -199,11 +220,11 @@ template <bool PER_INSTANCE> __global__ void __launch_bounds__(256) k_cull_flags
 
 // ---- order-preserving stream compaction --------------------------------------------------------------------------------------
 // The reference's cull is std::remove_if + resize (stable). Single pass: each CTA takes the next tile (ticket counter, so
-// tiles are started in order), ballots/popcounts its 2048 visibility bits, publishes its aggregate and resolves its
+// tiles are started in order), popcounts its 8192 visibility bits, publishes its aggregate and resolves its
 // exclusive prefix by decoupled look-back over the preceding tiles' status words; survivors are written in entry order.
 // status word: bits 31..30 = 0 invalid / 1 aggregate / 2 inclusive prefix, bits 29..0 = count (entry tables are < 2^24).
 constexpr int kCompactThreads = 256;
-constexpr int kCompactItems = 8;
+constexpr int kCompactItems = 32; // per thread: two 16-byte loads, one 32-bit survivor mask
 constexpr int kCompactTile = kCompactThreads * kCompactItems;
 
 struct CompactDev {
@@ -224,17 +245,18 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact(CompactDev c) {
 	const uint32_t tile = s_tile;
 	const uint32_t base = tile * kCompactTile + threadIdx.x * kCompactItems;
 
-	// 8 flags per thread, one 64-bit load (vis buffers are padded to a tile multiple and zero-filled)
-	const uint2 raw = *reinterpret_cast<const uint2 *>(c.vis + base);
+	// 32 flags per thread, two 128-bit loads (vis buffers are padded to a tile multiple and zero-filled); bit `c.bit` of every byte is
+	// gathered into one 32-bit mask: (w >> bit) & 0x01010101 leaves one bit per byte, * 0x10204080 moves the four of them to bits 28..31
+	const uint4 *src = reinterpret_cast<const uint4 *>(c.vis + base);
+	const uint4 ra = src[0], rb = src[1];
+	const uint32_t w[8] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
 	uint32_t mask = 0;
 #pragma unroll
-	for (int i = 0; i < 4; ++i) {
-		mask |= ((raw.x >> (8 * i + c.bit)) & 1u) << i;
-		mask |= ((raw.y >> (8 * i + c.bit)) & 1u) << (4 + i);
-	}
+	for (int i = 0; i < 8; ++i)
+		mask |= ((((w[i] >> c.bit) & 0x01010101u) * 0x10204080u) >> 28) << (4 * i);
 	if (base + kCompactItems > c.n) { // ragged tail: drop bits past n
 		const uint32_t valid = base < c.n ? c.n - base : 0;
-		mask &= (1u << valid) - 1u;
+		mask &= valid >= 32 ? 0xffffffffu : (1u << valid) - 1u;
 	}
 	const uint32_t cnt = __popc(mask);
 
@@ -300,10 +322,10 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact(CompactDev c) {
 	__syncthreads();
 
 	uint32_t rank = s_prefix + warp_off + (incl - cnt);
-#pragma unroll
-	for (int i = 0; i < kCompactItems; ++i)
-		if (mask & (1u << i))
-			c.out[rank++] = base + i;
+	while (mask) { // survivors of this thread, ascending
+		c.out[rank++] = base + (__ffs(mask) - 1);
+		mask &= mask - 1;
+	}
 }
 
 // Batched scene instances (one camera per instance): the global stable compaction already keeps each instance's survivors

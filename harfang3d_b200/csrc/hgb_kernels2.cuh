@@ -111,49 +111,46 @@ __global__ void __launch_bounds__(256) k_sample_tracks(AnimDev a, uint32_t first
 	const uint32_t n = trk.key_count;
 	const uint4 *keys = a.keys + size_t(trk.key_off + (trk.kind == 3 ? a.quat_base : 0u)) * 2;
 
-	// interval search: the interval found last frame, then the one after it (a frame rarely advances more than one key), then the
-	// binary search (time jumps, loop wrap)
-	uint32_t cur = min(a.cursor[i], n - 1);
-	uint4 k1a = keys[size_t(cur) * 2], k1b = keys[size_t(cur) * 2 + 1]; // candidate kf1
-	uint32_t nxt = min(cur + 1, n - 1);
-	uint4 k2a = keys[size_t(nxt) * 2], k2b = keys[size_t(nxt) * 2 + 1]; // candidate kf2
-	int64_t t_cur = int64_t(uint64_t(k1a.x) | (uint64_t(k1a.y) << 32)), t_nxt = int64_t(uint64_t(k2a.x) | (uint64_t(k2a.y) << 32));
+	// Interval search. The four keys around the interval found last frame are requested at once (eight independent 16-byte loads, 128
+	// contiguous bytes); the interval is then that one, or the next one (a frame rarely advances more than one key), else the binary
+	// search (time jumps, loop wrap). kA..kD = keys kf0, kf1, kf2, kf3 of EvaluateHermite.
+	const uint32_t cur = min(a.cursor[i], n - 1);
+	const uint32_t i0 = cur > 0 ? cur - 1 : 0, i2 = min(cur + 1, n - 1), i3 = min(cur + 2, n - 1);
+	uint4 kAa = keys[size_t(i0) * 2], kAb = keys[size_t(i0) * 2 + 1];
+	uint4 kBa = keys[size_t(cur) * 2], kBb = keys[size_t(cur) * 2 + 1];
+	uint4 kCa = keys[size_t(i2) * 2], kCb = keys[size_t(i2) * 2 + 1];
+	uint4 kDa = keys[size_t(i3) * 2], kDb = keys[size_t(i3) * 2 + 1];
+	auto t_of = [](const uint4 &k) { return int64_t(uint64_t(k.x) | (uint64_t(k.y) << 32)); };
 	uint32_t ub;
-	if (t_cur <= at && (cur + 1 == n || at < t_nxt)) {
+	if (t_of(kBa) <= at && (cur + 1 == n || at < t_of(kCa))) {
 		ub = cur + 1;
+	} else if (cur + 1 < n && t_of(kCa) <= at && (cur + 2 == n || at < t_of(kDa))) {
+		ub = cur + 2;
+		const uint32_t i4 = min(cur + 3, n - 1);
+		kAa = kBa, kAb = kBb, kBa = kCa, kBb = kCb, kCa = kDa, kCb = kDb;
+		kDa = keys[size_t(i4) * 2], kDb = keys[size_t(i4) * 2 + 1];
+		a.cursor[i] = cur + 1;
 	} else {
-		bool found = false;
-		if (cur + 1 < n && t_nxt <= at) { // advance by one key
-			const uint32_t n2 = min(cur + 2, n - 1);
-			const uint4 k3a = keys[size_t(n2) * 2], k3b = keys[size_t(n2) * 2 + 1];
-			const int64_t t_n2 = int64_t(uint64_t(k3a.x) | (uint64_t(k3a.y) << 32));
-			if (cur + 2 == n || at < t_n2) {
-				found = true;
-				ub = cur + 2;
-				k1a = k2a, k1b = k2b, k2a = k3a, k2b = k3b;
-			}
-		}
-		if (!found) {
-			ub = upper_bound_keys(keys, n, at);
-			if (ub > 0 && ub < n) { // reload the pair the evaluation needs
-				k1a = keys[size_t(ub - 1) * 2], k1b = keys[size_t(ub - 1) * 2 + 1];
-				k2a = keys[size_t(ub) * 2], k2b = keys[size_t(ub) * 2 + 1];
-			}
-		}
-		a.cursor[i] = ub > 0 ? ub - 1 : 0;
+		ub = upper_bound_keys(keys, n, at);
+		const uint32_t kf1 = ub > 0 ? ub - 1 : 0, kf2 = min(ub, n - 1);
+		const uint32_t kf0 = kf1 > 0 ? kf1 - 1 : 0, kf3 = min(kf2 + 1, n - 1);
+		kAa = keys[size_t(kf0) * 2], kAb = keys[size_t(kf0) * 2 + 1];
+		kBa = keys[size_t(kf1) * 2], kBb = keys[size_t(kf1) * 2 + 1];
+		kCa = keys[size_t(kf2) * 2], kCb = keys[size_t(kf2) * 2 + 1];
+		kDa = keys[size_t(kf3) * 2], kDb = keys[size_t(kf3) * 2 + 1];
+		a.cursor[i] = kf1;
 	}
+	// ub == 0: before the first key -> kB is key 0 (kf1 clamps to 0). ub == n: at/after the last key -> kB is key n-1.
 	float4 *dst = a.anim_val + trk.out_slot;
 
 	if (trk.kind == 3) { // AnimTrackT<Quaternion>: EvaluateLinear animation.h:141-153, then ToEuler(Normalize())
 		float4 q;
 		if (ub == 0 || ub == n) {
-			const uint32_t k = ub == 0 ? 0 : n - 1;
-			const uint4 ka = keys[size_t(k) * 2], kb = keys[size_t(k) * 2 + 1];
-			q = make_float4(__uint_as_float(ka.z), __uint_as_float(ka.w), __uint_as_float(kb.x), __uint_as_float(kb.y));
+			q = make_float4(__uint_as_float(kBa.z), __uint_as_float(kBa.w), __uint_as_float(kBb.x), __uint_as_float(kBb.y));
 		} else {
-			const float4 q0 = make_float4(__uint_as_float(k1a.z), __uint_as_float(k1a.w), __uint_as_float(k1b.x), __uint_as_float(k1b.y));
-			const float4 q1 = make_float4(__uint_as_float(k2a.z), __uint_as_float(k2a.w), __uint_as_float(k2b.x), __uint_as_float(k2b.y));
-			const int64_t t1 = int64_t(uint64_t(k1a.x) | (uint64_t(k1a.y) << 32)), t2 = int64_t(uint64_t(k2a.x) | (uint64_t(k2a.y) << 32));
+			const float4 q0 = make_float4(__uint_as_float(kBa.z), __uint_as_float(kBa.w), __uint_as_float(kBb.x), __uint_as_float(kBb.y));
+			const float4 q1 = make_float4(__uint_as_float(kCa.z), __uint_as_float(kCa.w), __uint_as_float(kCb.x), __uint_as_float(kCb.y));
+			const int64_t t1 = t_of(kBa), t2 = t_of(kCa);
 			const float k = time_to_sec_f(at - t1) / time_to_sec_f(t2 - t1);
 			q = make_float4(q0.x + (q1.x - q0.x) * k, q0.y + (q1.y - q0.y) * k, q0.z + (q1.z - q0.z) * k, q0.w + (q1.w - q0.w) * k);
 		}
@@ -165,24 +162,19 @@ __global__ void __launch_bounds__(256) k_sample_tracks(AnimDev a, uint32_t first
 	// AnimTrackHermiteT<Vec3>: EvaluateHermite animation.h:155-169
 	float ox, oy, oz;
 	if (ub == 0 || ub == n) {
-		const uint32_t k = ub == 0 ? 0 : n - 1;
-		const uint4 ka = keys[size_t(k) * 2], kb = keys[size_t(k) * 2 + 1];
-		ox = __uint_as_float(ka.z), oy = __uint_as_float(ka.w), oz = __uint_as_float(kb.x);
+		ox = __uint_as_float(kBa.z), oy = __uint_as_float(kBa.w), oz = __uint_as_float(kBb.x);
 	} else {
-		const uint32_t kf1 = ub - 1, kf2 = ub;
-		const uint32_t kf0 = kf1 > 0 ? kf1 - 1 : 0, kf3 = kf2 + 1 < n - 1 ? kf2 + 1 : n - 1;
-		const uint4 k0a = keys[size_t(kf0) * 2], k0b = keys[size_t(kf0) * 2 + 1], k3a = keys[size_t(kf3) * 2], k3b = keys[size_t(kf3) * 2 + 1];
-		const int64_t t1 = int64_t(uint64_t(k1a.x) | (uint64_t(k1a.y) << 32)), t2 = int64_t(uint64_t(k2a.x) | (uint64_t(k2a.y) << 32));
+		const int64_t t1 = t_of(kBa), t2 = t_of(kCa);
 		const float u = time_to_sec_f(at - t1) / time_to_sec_f(t2 - t1);
-		const float tension = __uint_as_float(k1b.y), bias = __uint_as_float(k1b.z);
+		const float tension = __uint_as_float(kBb.y), bias = __uint_as_float(kBb.z);
 		const float t2_ = u * u, t3 = t2_ * u;
 		const float a0 = 2.F * t3 - 3.F * t2_ + 1.F;
 		const float a1 = t3 - 2.F * t2_ + u;
 		const float a2 = t3 - t2_;
 		const float a3 = -2.F * t3 + 3.F * t2_;
-		ox = hermite1(__uint_as_float(k0a.z), __uint_as_float(k1a.z), __uint_as_float(k2a.z), __uint_as_float(k3a.z), a0, a1, a2, a3, tension, bias);
-		oy = hermite1(__uint_as_float(k0a.w), __uint_as_float(k1a.w), __uint_as_float(k2a.w), __uint_as_float(k3a.w), a0, a1, a2, a3, tension, bias);
-		oz = hermite1(__uint_as_float(k0b.x), __uint_as_float(k1b.x), __uint_as_float(k2b.x), __uint_as_float(k3b.x), a0, a1, a2, a3, tension, bias);
+		ox = hermite1(__uint_as_float(kAa.z), __uint_as_float(kBa.z), __uint_as_float(kCa.z), __uint_as_float(kDa.z), a0, a1, a2, a3, tension, bias);
+		oy = hermite1(__uint_as_float(kAa.w), __uint_as_float(kBa.w), __uint_as_float(kCa.w), __uint_as_float(kDa.w), a0, a1, a2, a3, tension, bias);
+		oz = hermite1(__uint_as_float(kAb.x), __uint_as_float(kBb.x), __uint_as_float(kCb.x), __uint_as_float(kDb.x), a0, a1, a2, a3, tension, bias);
 	}
 	*dst = make_float4(ox, oy, oz, 0.f);
 }

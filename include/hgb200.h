@@ -42,7 +42,11 @@ typedef struct hgb_ctx hgb_ctx;
 
 typedef struct hgb_options {
 	int use_graph; /* 1: capture the per-frame launch sequence in a CUDA graph (default), 0: plain stream launches */
-	int reserved[7];
+	int row_store; /* profiling A/B switch. 0 (default): a warp's 32 world matrices leave the SM as 3 contiguous 512-byte stores
+	                  (shared-memory transpose); 1: every thread stores its own 48-byte row */
+	int lookahead; /* profiling A/B switch. L2 software-prefetch distance of the level kernel in positions: 0 = default (one wave of
+	                  resident CTAs), -1 = off, n = n positions */
+	int reserved[5];
 } hgb_options;
 
 /* one bound animation track (BoundToNodeAnim entry, harfang/engine/scene.h:74-88) */
