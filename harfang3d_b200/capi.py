@@ -53,6 +53,7 @@ SIGNATURES = {
     "hgb_set_instance_views": (_i, [_p, _u32, _p, _p]),
     "hgb_update": (_i, [_p, _u32, _p, _i]),
     "hgb_cull": (_i, [_p]),
+    "hgb_cull_list": (_i, [_p, _u32, _p, _p, _u32, _p, _p, _p, _p]),
     "hgb_bone_matrices": (_i, [_p, _i]),
     "hgb_get_worlds": (_i, [_p, _u32, _u32, _p, _i]),
     "hgb_get_trs": (_i, [_p, _u32, _u32, _p]),
@@ -189,6 +190,15 @@ class Context:
 
     def cull(self):
         self._ck(self._L.hgb_cull(self._h))
+
+    def cull_list(self, mtx_slot, bounds_idx, bounds6, frustum24):
+        """CullModelDisplayLists on a caller-owned list -> surviving entry indices, in order"""
+        out, n = np.empty(max(len(mtx_slot), 1), np.uint32), C.c_uint32(0)
+        f = np.ascontiguousarray(frustum24, np.float32).reshape(24)
+        self._ck(self._L.hgb_cull_list(self._h, len(mtx_slot), _ptr(mtx_slot, np.uint32, "mtx_slot"), _ptr(bounds_idx, np.uint32, "bounds_idx"),
+                                       bounds6.shape[0], _ptr(bounds6, np.float32, "bounds6"), _ptr(f, np.float32, "frustum24"),
+                                       _ptr(out, np.uint32, "out"), C.byref(n)))
+        return out[: n.value]
 
     def bone_matrices(self, with_previous=False):
         self._ck(self._L.hgb_bone_matrices(self._h, 1 if with_previous else 0))

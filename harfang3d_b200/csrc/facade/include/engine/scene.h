@@ -1,0 +1,228 @@
+// hg::Scene facade — the reference's scene API for the scene-update path (harfang/engine/scene.h:173-901, node.h:36-380), same member
+// names, argument meaning and warn-and-neutral-value error behaviour. The scene graph (nodes, components, refs, anims) lives on the
+// host like in the reference; the per-frame members forward to the CUDA path through the C ABI of include/hgb200.h:
+//   StorePreviousWorldMatrices / ReadyWorldMatrices / UpdatePlayingAnims / ComputeWorldMatrices / FixupPreviousWorldMatrices / Update
+//   GetTransformWorldMatrices / GetPreviousTransformWorldMatrices (lazy device -> host), SetNodeWorldMatrix (preset)
+// There is no CPU implementation of those members here: without a CUDA device they warn() and leave the matrices untouched.
+#pragma once
+#include "engine/animation.h"
+#include "engine/render_pipeline.h"
+#include "foundation/generational_vector_list.h"
+#include "foundation/hg_math_types.h"
+#include <string>
+#include <vector>
+
+struct hgb_ctx;
+
+namespace hg {
+
+using NodeRef = gen_ref;
+using ComponentRef = gen_ref;
+using AnimRef = gen_ref;
+using SceneAnimRef = gen_ref;
+using ScenePlayAnimRef = gen_ref;
+extern const NodeRef InvalidNodeRef;
+extern const ComponentRef InvalidComponentRef;
+extern const ScenePlayAnimRef InvalidScenePlayAnimRef;
+extern time_ns UnspecifiedAnimTime;
+
+struct TransformTRS { // engine/node.h:36-38
+	Vec3 pos{0, 0, 0}, rot{0, 0, 0}, scl{1, 1, 1};
+};
+
+class Scene;
+
+// value-type handles (engine/node.h:66-67,282-380): a scene pointer + a generational ref; stale handles fail IsValid()
+struct Transform {
+	Scene *scene{nullptr};
+	ComponentRef ref;
+	bool IsValid() const;
+	Vec3 GetPos() const;
+	void SetPos(const Vec3 &v);
+	Vec3 GetRot() const;
+	void SetRot(const Vec3 &v);
+	Vec3 GetScale() const;
+	void SetScale(const Vec3 &v);
+	void SetParent(const NodeRef &parent);
+};
+struct Object {
+	Scene *scene{nullptr};
+	ComponentRef ref;
+	bool IsValid() const;
+};
+struct Node {
+	Scene *scene{nullptr};
+	NodeRef ref;
+	bool IsValid() const;
+	uint32_t GetUid() const { return ref.idx; } // node.h:289
+	void Enable();
+	void Disable();
+	bool IsEnabled() const;
+	Transform GetTransform() const;
+	void SetTransform(const Transform &t);
+	Object GetObject() const;
+	void SetObject(const Object &o);
+	Mat4 GetWorld() const;
+	void SetWorld(const Mat4 &m);
+};
+
+struct NodeAnim { // scene.h:104-107
+	NodeRef node;
+	AnimRef anim;
+};
+struct SceneAnim { // scene.h:109-118
+	std::string name;
+	time_ns t_start{0}, t_end{0};
+	AnimRef scene_anim;
+	std::vector<NodeAnim> node_anims;
+	time_ns frame_duration{50000000}; // 20 fps
+};
+
+static const uint32_t NF_Disabled = 0x1, NF_InstanceDisabled = 0x2; // scene.h:166-170
+
+class Scene {
+public:
+	Scene();
+	~Scene();
+	Scene(const Scene &) = delete;
+	Scene &operator=(const Scene &) = delete;
+
+	size_t GarbageCollect(); // components no node refers to are removed (scene.cpp:92-237, transform / object / anim passes)
+
+	// ---- nodes (scene.h:191-234) ----
+	Node CreateNode(std::string name = {});
+	void DestroyNode(NodeRef ref);
+	void DestroyNode(const Node &node) { DestroyNode(node.ref); }
+	bool IsValidNodeRef(NodeRef ref) const { return nodes.is_valid(ref); }
+	void ReserveNodes(size_t count) { nodes.reserve(count); }
+	void EnableNode(NodeRef ref);
+	void DisableNode(NodeRef ref);
+	bool IsNodeEnabled(NodeRef ref) const { return nodes.is_valid(ref) ? !(nodes[ref.idx].flags & (NF_Disabled | NF_InstanceDisabled)) : false; }
+	size_t GetNodeCount() const { return nodes.size(); }
+	bool IsChildOf(NodeRef node, NodeRef parent) const; // component.cpp:21-33
+
+	// ---- transforms (scene.h:242-284) ----
+	Transform CreateTransform();
+	Transform CreateTransform(const Vec3 &pos, const Vec3 &rot = {0, 0, 0}, const Vec3 &scl = {1, 1, 1}, NodeRef parent = {});
+	void DestroyTransform(ComponentRef ref);
+	void ReserveTransforms(size_t count) { transforms.reserve(count); }
+	bool IsValidTransformRef(ComponentRef ref) const { return transforms.is_valid(ref); }
+	Vec3 GetTransformPos(ComponentRef ref) const;
+	void SetTransformPos(ComponentRef ref, const Vec3 &v);
+	Vec3 GetTransformRot(ComponentRef ref) const;
+	void SetTransformRot(ComponentRef ref, const Vec3 &v);
+	Vec3 GetTransformScale(ComponentRef ref) const;
+	void SetTransformScale(ComponentRef ref, const Vec3 &v);
+	TransformTRS GetTransformTRS(ComponentRef ref) const;
+	void SetTransformTRS(ComponentRef ref, const TransformTRS &v);
+	NodeRef GetTransformParent(ComponentRef ref) const;
+	void SetTransformParent(ComponentRef ref, const NodeRef &v); // rejects cycles like component.cpp:184-193
+	ComponentRef GetNodeTransformRef(NodeRef ref) const;
+	void SetNodeTransform(NodeRef ref, ComponentRef cref);
+	void SetNodeTransform(NodeRef ref, const Transform &v) { SetNodeTransform(ref, v.ref); }
+	Mat4 GetNodeWorldMatrix(NodeRef ref) const;            // scene.cpp:750-766
+	void SetNodeWorldMatrix(NodeRef ref, const Mat4 &world); // scene.cpp:768-786: wins over ComputeWorldMatrices for this frame
+
+	// ---- objects (scene.h:327-358) ----
+	Object CreateObject();
+	Object CreateObject(const ModelRef &model, std::vector<Material> materials = {});
+	void DestroyObject(ComponentRef ref);
+	bool IsValidObjectRef(ComponentRef ref) const { return objects.is_valid(ref); }
+	void SetObjectModel(ComponentRef ref, const ModelRef &model);
+	ModelRef GetObjectModel(ComponentRef ref) const;
+	void SetObjectMaterialCount(ComponentRef ref, size_t count);
+	void SetObjectMaterial(ComponentRef ref, size_t slot, Material mat);
+	size_t GetObjectBoneCount(ComponentRef ref) const;
+	void SetObjectBoneCount(ComponentRef ref, size_t count);
+	bool SetObjectBone(ComponentRef ref, size_t idx, NodeRef bone_node); // component.cpp:679-691
+	NodeRef GetObjectBone(ComponentRef ref, size_t idx) const;
+	ComponentRef GetNodeObjectRef(NodeRef ref) const;
+	void SetNodeObject(NodeRef ref, ComponentRef cref);
+	void SetNodeObject(NodeRef ref, const Object &v) { SetNodeObject(ref, v.ref); }
+
+	// ---- per-frame path (scene.h:287-292,601-614) ----
+	void StorePreviousWorldMatrices();
+	void ReadyWorldMatrices();
+	void ComputeWorldMatrices();
+	void FixupPreviousWorldMatrices();
+	void Update(time_ns dt);
+	const std::vector<Mat4> &GetTransformWorldMatrices() const;
+	const std::vector<Mat4> &GetPreviousTransformWorldMatrices() const;
+	void GetModelDisplayLists(std::vector<ModelDisplayList> &out_opaque, std::vector<ModelDisplayList> &out_transparent,
+		std::vector<SkinnedModelDisplayList> &out_opaque_skinned, std::vector<SkinnedModelDisplayList> &out_transparent_skinned,
+		const PipelineResources &resources) const;
+
+	// ---- animation (scene.h:620-663) ----
+	AnimRef AddAnim(Anim anim);
+	void DestroyAnim(AnimRef ref);
+	bool IsValidAnim(AnimRef ref) const { return anims.is_valid(ref); }
+	Anim *GetAnim(AnimRef ref);
+	const Anim *GetAnim(AnimRef ref) const;
+	SceneAnimRef AddSceneAnim(SceneAnim anim);
+	void DestroySceneAnim(SceneAnimRef ref);
+	SceneAnim *GetSceneAnim(SceneAnimRef ref);
+	ScenePlayAnimRef PlayAnim(SceneAnimRef ref, AnimLoopMode loop_mode = ALM_Once, Easing easing = E_Linear, time_ns t_start = UnspecifiedAnimTime,
+		time_ns t_end = UnspecifiedAnimTime, bool paused = false, float t_scale = 1.f);
+	bool IsPlaying(ScenePlayAnimRef ref) const;
+	void StopAnim(ScenePlayAnimRef ref);
+	void StopAllAnims();
+	void UpdatePlayingAnims(time_ns dt);
+
+	// ---- extensions of the B200 path (not in the reference) ----
+	// Up to 8 frusta evaluated inside Update (fused with the world-matrix pass). GetVisibleModelDisplayLists then returns what
+	// GetModelDisplayLists + CullModelDisplayLists(view) would, without a second pass over the matrices.
+	void SetCullingFrustums(const std::vector<Frustum> &frustums, const PipelineResources &resources); // resources must outlive the scene's use of it
+	bool GetVisibleModelDisplayLists(uint32_t view, bool transparent, std::vector<ModelDisplayList> &out, const PipelineResources &resources);
+	hgb_ctx *GetDeviceContext() const { return ctx; }
+	int GetDeviceIndex() const { return device; }
+	static void SetDefaultDevice(int device);
+
+private:
+	friend void CullModelDisplayLists(const Frustum &, std::vector<ModelDisplayList> &, const std::vector<Mat4> &, const PipelineResources &);
+	friend size_t ComputeSkinMatrices(const std::vector<SkinnedModelDisplayList> &, const std::vector<Mat4> &, const PipelineResources &, std::vector<float> &, bool);
+	struct Impl;
+
+	struct Node_ { // scene.h:698-702
+		std::string name;
+		uint32_t flags{0};
+		ComponentRef transform, object;
+	};
+	struct Transform_ { // scene.h:734-737
+		TransformTRS TRS;
+		NodeRef parent;
+	};
+	struct Object_ { // scene.h:750-757
+		ModelRef model;
+		std::vector<Material> materials;
+		std::vector<NodeRef> bones;
+	};
+	struct ScenePlayAnim_ { // scene.h:884-895
+		SceneAnimRef scene_anim;
+		time_ns t_start, t_end, t;
+		int8_t t_scale;
+		AnimLoopMode loop_mode;
+		bool paused;
+		uint32_t play_slot; // index into the device's play clock array
+	};
+
+	generational_vector_list<Node_> nodes;
+	generational_vector_list<Transform_> transforms;
+	generational_vector_list<Object_> objects;
+	generational_vector_list<Anim> anims;
+	generational_vector_list<SceneAnim> scene_anims;
+	generational_vector_list<ScenePlayAnim_> play_anims;
+
+	mutable std::vector<Mat4> transform_worlds, previous_transform_worlds; // host mirrors, refreshed lazily
+	mutable bool worlds_valid{false}, previous_valid{false};
+	mutable bool trs_host_stale{false}; // the device sampled tracks into the TRS: refresh before the host reads or edits them
+
+	hgb_ctx *ctx{nullptr};
+	int device{0};
+	Impl *impl; // dirty tracking + staging (facade/src/hg_scene.cpp)
+
+	bool EnsureContext() const;
+	void RefreshTRSFromDevice() const;
+	bool SyncEdits(const PipelineResources *resources);
+};
+
+} // namespace hg

@@ -1,0 +1,2 @@
+#pragma once
+#include "foundation/hg_math_types.h"

@@ -1,0 +1,942 @@
+// hg::Scene facade — host side of the drop-in boundary. The scene graph is kept on the host with the
+// reference's semantics (slot reuse order, generational refs, warn-and-neutral-value errors); edits are tracked as dirty state and
+// flushed to the device context (include/hgb200.h) at the start of a frame; the per-frame members only enqueue GPU work.
+// Nothing in this file computes a world matrix, samples a key or tests a frustum: without a CUDA device those members warn and return.
+#include "engine/scene.h"
+#include "foundation/log.h"
+#include "hgb200.h"
+
+#include <algorithm>
+#include <map>
+#include <mutex>
+
+namespace hg {
+
+const NodeRef InvalidNodeRef;
+const ComponentRef InvalidComponentRef;
+const ScenePlayAnimRef InvalidScenePlayAnimRef;
+time_ns UnspecifiedAnimTime = INT64_MIN; // scene.cpp: "unspecified" sentinel of PlayAnim's t_start / t_end
+
+static int g_default_device = 0;
+void Scene::SetDefaultDevice(int device) { g_default_device = device; }
+
+// CullModelDisplayLists / ComputeSkinMatrices receive the world-matrix vector, not the scene (render_pipeline.h:584): the vector's
+// address identifies the scene whose device context holds the matrices.
+static std::mutex g_registry_mutex;
+static std::map<const void *, Scene *> g_registry;
+
+struct Scene::Impl {
+	bool topology_dirty{true};
+	bool trs_all_dirty{true};
+	std::vector<uint32_t> dirty_trs;
+	bool anims_dirty{true};
+	bool entries_dirty{true};
+	bool views_dirty{false};
+	bool in_frame{false}; // between ReadyWorldMatrices and ComputeWorldMatrices: SetNodeWorldMatrix records presets
+	const PipelineResources *resources{nullptr};
+	std::vector<Frustum> frusta;
+	std::vector<uint32_t> preset_slots;
+	std::vector<float> preset_mats;
+	std::vector<int64_t> play_t;        // evaluation time per play slot (HGB_NOT_PLAYING when idle)
+	std::vector<float> staging;
+	// fused culling: the entry tables given to the device (every entry, disabled ones flagged) and what they map back to
+	std::vector<ModelDisplayList> ent[2];
+	std::vector<uint8_t> ent_flags[2];
+	// ComputeSkinMatrices cache
+	std::vector<uint32_t> skin_mtx, skin_bind;
+	size_t skin_bind_count{0};
+	bool warned_no_device{false};
+	bool rebind_after_frame{false}; // a finished ALM_Once anim is evaluated one last time, then its tracks are unbound
+};
+
+static void check(int rc) {
+	if (rc)
+		warn(hgb_last_error());
+}
+
+Scene::Scene() : impl(new Impl) {
+	device = g_default_device;
+	std::lock_guard<std::mutex> lock(g_registry_mutex);
+	g_registry[&transform_worlds] = this;
+	g_registry[&previous_transform_worlds] = this;
+}
+
+Scene::~Scene() {
+	{
+		std::lock_guard<std::mutex> lock(g_registry_mutex);
+		g_registry.erase(&transform_worlds);
+		g_registry.erase(&previous_transform_worlds);
+	}
+	if (ctx)
+		hgb_destroy(ctx);
+	delete impl;
+}
+
+bool Scene::EnsureContext() const {
+	if (ctx)
+		return true;
+	Scene *self = const_cast<Scene *>(this);
+	self->ctx = hgb_create(device, nullptr);
+	if (!ctx) {
+		if (!impl->warned_no_device)
+			warn(hgb_last_error()); // no CPU fallback: the per-frame members do nothing without a device
+		impl->warned_no_device = true;
+		return false;
+	}
+	return true;
+}
+
+// ---- handles ---------------------------------------------------------------------------------------------------------------
+bool Node::IsValid() const { return scene && scene->IsValidNodeRef(ref); }
+void Node::Enable() { if (scene) scene->EnableNode(ref); }
+void Node::Disable() { if (scene) scene->DisableNode(ref); }
+bool Node::IsEnabled() const { return scene && scene->IsNodeEnabled(ref); }
+Transform Node::GetTransform() const { return scene ? Transform{scene, scene->GetNodeTransformRef(ref)} : Transform{}; }
+void Node::SetTransform(const Transform &t) { if (scene) scene->SetNodeTransform(ref, t.ref); }
+Object Node::GetObject() const { return scene ? Object{scene, scene->GetNodeObjectRef(ref)} : Object{}; }
+void Node::SetObject(const Object &o) { if (scene) scene->SetNodeObject(ref, o.ref); }
+Mat4 Node::GetWorld() const { return scene ? scene->GetNodeWorldMatrix(ref) : Mat4::Identity; }
+void Node::SetWorld(const Mat4 &m) { if (scene) scene->SetNodeWorldMatrix(ref, m); }
+bool Transform::IsValid() const { return scene && scene->IsValidTransformRef(ref); }
+Vec3 Transform::GetPos() const { return scene ? scene->GetTransformPos(ref) : Vec3(); }
+void Transform::SetPos(const Vec3 &v) { if (scene) scene->SetTransformPos(ref, v); }
+Vec3 Transform::GetRot() const { return scene ? scene->GetTransformRot(ref) : Vec3(); }
+void Transform::SetRot(const Vec3 &v) { if (scene) scene->SetTransformRot(ref, v); }
+Vec3 Transform::GetScale() const { return scene ? scene->GetTransformScale(ref) : Vec3(1, 1, 1); }
+void Transform::SetScale(const Vec3 &v) { if (scene) scene->SetTransformScale(ref, v); }
+void Transform::SetParent(const NodeRef &parent) { if (scene) scene->SetTransformParent(ref, parent); }
+bool Object::IsValid() const { return scene && scene->IsValidObjectRef(ref); }
+
+// ---- nodes -------------------------------------------------------------------------------------------------------------------
+Node Scene::CreateNode(std::string name) {
+	Node_ n;
+	n.name = std::move(name);
+	impl->entries_dirty = true;
+	return {this, nodes.add_ref(std::move(n))};
+}
+
+void Scene::DestroyNode(NodeRef ref) {
+	if (!nodes.is_valid(ref))
+		return;
+	nodes.remove_ref(ref);
+	impl->topology_dirty = true; // children of its transform become roots (a stale parent ref is a root, scene.cpp:268-272)
+	impl->entries_dirty = true;
+	impl->anims_dirty = true;
+}
+
+void Scene::EnableNode(NodeRef ref) {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node reference");
+		return;
+	}
+	nodes[ref.idx].flags &= ~NF_Disabled;
+	impl->entries_dirty = true;
+}
+
+void Scene::DisableNode(NodeRef ref) {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node reference");
+		return;
+	}
+	nodes[ref.idx].flags |= NF_Disabled;
+	impl->entries_dirty = true;
+}
+
+bool Scene::IsChildOf(NodeRef node, NodeRef parent) const { // walk up from `node`; bounded by the node count against corrupted graphs
+	size_t guard = nodes.capacity() + 1;
+	while (guard--) {
+		if (!nodes.is_valid(node))
+			return false;
+		const ComponentRef t = nodes[node.idx].transform;
+		if (!transforms.is_valid(t))
+			return false;
+		const NodeRef up = transforms[t.idx].parent;
+		if (up == parent)
+			return true;
+		node = up;
+	}
+	return false;
+}
+
+// ---- transforms --------------------------------------------------------------------------------------------------------------
+Transform Scene::CreateTransform() {
+	const ComponentRef ref = transforms.add_ref(Transform_{});
+	impl->topology_dirty = true;
+	return {this, ref};
+}
+
+Transform Scene::CreateTransform(const Vec3 &pos, const Vec3 &rot, const Vec3 &scl, NodeRef parent) {
+	Transform_ t;
+	t.TRS.pos = pos, t.TRS.rot = rot, t.TRS.scl = scl;
+	t.parent = parent;
+	const ComponentRef ref = transforms.add_ref(t);
+	impl->topology_dirty = true;
+	return {this, ref};
+}
+
+void Scene::DestroyTransform(ComponentRef ref) {
+	if (transforms.is_valid(ref)) {
+		transforms.remove_ref(ref);
+		impl->topology_dirty = true;
+		impl->entries_dirty = true;
+		impl->anims_dirty = true;
+	}
+}
+
+// The device samples bound tracks straight into its TRS; the host copy is refreshed on the first host access after such a frame.
+void Scene::RefreshTRSFromDevice() const {
+	if (!trs_host_stale)
+		return;
+	trs_host_stale = false;
+	const uint32_t n = uint32_t(transforms.capacity());
+	if (!ctx || !n || impl->topology_dirty)
+		return;
+	impl->staging.resize(size_t(n) * 9);
+	if (hgb_get_trs(ctx, 0, n, impl->staging.data())) {
+		warn(hgb_last_error());
+		return;
+	}
+	auto &trs = const_cast<generational_vector_list<Transform_> &>(transforms);
+	for (uint32_t i = transforms.first(); i != transforms.invalid_idx; i = transforms.next(i)) {
+		const float *s = impl->staging.data() + size_t(i) * 9;
+		trs[i].TRS.pos = Vec3(s[0], s[1], s[2]), trs[i].TRS.rot = Vec3(s[3], s[4], s[5]), trs[i].TRS.scl = Vec3(s[6], s[7], s[8]);
+	}
+}
+
+#define HG_GET_TRS(FIELD, DFLT)                                                                                                                                \
+	if (!transforms.is_valid(ref)) {                                                                                                                           \
+		warn("Invalid transform component");                                                                                                                   \
+		return DFLT;                                                                                                                                           \
+	}                                                                                                                                                          \
+	RefreshTRSFromDevice();                                                                                                                                    \
+	return transforms[ref.idx].TRS.FIELD;
+#define HG_SET_TRS(FIELD)                                                                                                                                      \
+	if (!transforms.is_valid(ref)) {                                                                                                                           \
+		warn("Invalid transform component");                                                                                                                   \
+		return;                                                                                                                                                \
+	}                                                                                                                                                          \
+	RefreshTRSFromDevice();                                                                                                                                    \
+	transforms[ref.idx].TRS.FIELD = v;                                                                                                                         \
+	impl->dirty_trs.push_back(ref.idx);
+
+Vec3 Scene::GetTransformPos(ComponentRef ref) const { HG_GET_TRS(pos, Vec3()) }
+void Scene::SetTransformPos(ComponentRef ref, const Vec3 &v) { HG_SET_TRS(pos) }
+Vec3 Scene::GetTransformRot(ComponentRef ref) const { HG_GET_TRS(rot, Vec3()) }
+void Scene::SetTransformRot(ComponentRef ref, const Vec3 &v) { HG_SET_TRS(rot) }
+Vec3 Scene::GetTransformScale(ComponentRef ref) const { HG_GET_TRS(scl, Vec3(1, 1, 1)) }
+void Scene::SetTransformScale(ComponentRef ref, const Vec3 &v) { HG_SET_TRS(scl) }
+
+TransformTRS Scene::GetTransformTRS(ComponentRef ref) const {
+	if (!transforms.is_valid(ref)) {
+		warn("Invalid transform component");
+		return {};
+	}
+	RefreshTRSFromDevice();
+	return transforms[ref.idx].TRS;
+}
+
+void Scene::SetTransformTRS(ComponentRef ref, const TransformTRS &v) {
+	if (!transforms.is_valid(ref)) {
+		warn("Invalid transform component");
+		return;
+	}
+	RefreshTRSFromDevice();
+	transforms[ref.idx].TRS = v;
+	impl->dirty_trs.push_back(ref.idx);
+}
+
+NodeRef Scene::GetTransformParent(ComponentRef ref) const {
+	if (!transforms.is_valid(ref)) {
+		warn("Invalid transform component");
+		return InvalidNodeRef;
+	}
+	return transforms[ref.idx].parent;
+}
+
+void Scene::SetTransformParent(ComponentRef ref, const NodeRef &v) {
+	if (!transforms.is_valid(ref)) {
+		warn("Invalid transform component");
+		return;
+	}
+	// refuse a parent whose own ancestry passes through this transform (component.cpp:21-33,184-193)
+	NodeRef walk = v;
+	size_t guard = nodes.capacity() + 1;
+	while (nodes.is_valid(walk) && guard--) {
+		const ComponentRef t = nodes[walk.idx].transform;
+		if (t == ref) {
+			warn("Cyclical reference detected");
+			return;
+		}
+		if (!transforms.is_valid(t))
+			break;
+		walk = transforms[t.idx].parent;
+	}
+	transforms[ref.idx].parent = v;
+	impl->topology_dirty = true;
+}
+
+ComponentRef Scene::GetNodeTransformRef(NodeRef ref) const {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node");
+		return InvalidComponentRef;
+	}
+	return nodes[ref.idx].transform;
+}
+
+void Scene::SetNodeTransform(NodeRef ref, ComponentRef cref) {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node");
+		return;
+	}
+	nodes[ref.idx].transform = cref;
+	impl->topology_dirty = true; // children reach their parent's transform through the parent NODE (scene.cpp:268)
+	impl->entries_dirty = true;
+	impl->anims_dirty = true;
+}
+
+Mat4 Scene::GetNodeWorldMatrix(NodeRef ref) const {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node");
+		return Mat4::Identity;
+	}
+	const ComponentRef t = nodes[ref.idx].transform;
+	if (!transforms.is_valid(t)) {
+		warn("Invalid node transform");
+		return Mat4::Identity;
+	}
+	const std::vector<Mat4> &w = GetTransformWorldMatrices();
+	if (t.idx >= w.size()) {
+		warn("Invalid node transform index");
+		return Mat4::Identity;
+	}
+	return w[t.idx];
+}
+
+void Scene::SetNodeWorldMatrix(NodeRef ref, const Mat4 &world) {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node");
+		return;
+	}
+	const ComponentRef t = nodes[ref.idx].transform;
+	if (!transforms.is_valid(t)) {
+		warn("Invalid node transform");
+		return;
+	}
+	// recorded as a preset of the frame being prepared: it wins over ComputeWorldMatrices and is the parent of the node's children
+	impl->preset_slots.push_back(t.idx);
+	impl->preset_mats.insert(impl->preset_mats.end(), &world.m[0][0], &world.m[0][0] + 12);
+	if (worlds_valid && t.idx < transform_worlds.size())
+		transform_worlds[t.idx] = world;
+}
+
+// ---- objects -----------------------------------------------------------------------------------------------------------------
+Object Scene::CreateObject() { return {this, objects.add_ref(Object_{})}; }
+
+Object Scene::CreateObject(const ModelRef &model, std::vector<Material> materials) {
+	Object_ o;
+	o.model = model;
+	o.materials = std::move(materials);
+	return {this, objects.add_ref(std::move(o))};
+}
+
+void Scene::DestroyObject(ComponentRef ref) {
+	if (objects.is_valid(ref)) {
+		objects.remove_ref(ref);
+		impl->entries_dirty = true;
+	}
+}
+
+#define HG_OBJ(RET)                                                                                                                                            \
+	if (!objects.is_valid(ref)) {                                                                                                                              \
+		warn("Invalid object component");                                                                                                                      \
+		return RET;                                                                                                                                            \
+	}
+void Scene::SetObjectModel(ComponentRef ref, const ModelRef &model) {
+	HG_OBJ()
+	objects[ref.idx].model = model;
+	impl->entries_dirty = true;
+}
+ModelRef Scene::GetObjectModel(ComponentRef ref) const {
+	HG_OBJ(InvalidModelRef)
+	return objects[ref.idx].model;
+}
+void Scene::SetObjectMaterialCount(ComponentRef ref, size_t count) {
+	HG_OBJ()
+	objects[ref.idx].materials.resize(count);
+	impl->entries_dirty = true;
+}
+void Scene::SetObjectMaterial(ComponentRef ref, size_t slot, Material mat) {
+	HG_OBJ()
+	if (slot >= objects[ref.idx].materials.size()) {
+		warn("Invalid material slot");
+		return;
+	}
+	objects[ref.idx].materials[slot] = mat;
+	impl->entries_dirty = true;
+}
+size_t Scene::GetObjectBoneCount(ComponentRef ref) const {
+	HG_OBJ(0)
+	return objects[ref.idx].bones.size();
+}
+void Scene::SetObjectBoneCount(ComponentRef ref, size_t count) {
+	HG_OBJ()
+	objects[ref.idx].bones.resize(count);
+	impl->entries_dirty = true;
+}
+bool Scene::SetObjectBone(ComponentRef ref, size_t idx, NodeRef bone_node) {
+	HG_OBJ(false)
+	if (idx >= objects[ref.idx].bones.size()) {
+		warn("Invalid bone index");
+		return false;
+	}
+	objects[ref.idx].bones[idx] = bone_node;
+	impl->entries_dirty = true;
+	return true;
+}
+NodeRef Scene::GetObjectBone(ComponentRef ref, size_t idx) const {
+	HG_OBJ(InvalidNodeRef)
+	return idx < objects[ref.idx].bones.size() ? objects[ref.idx].bones[idx] : InvalidNodeRef;
+}
+ComponentRef Scene::GetNodeObjectRef(NodeRef ref) const {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node");
+		return InvalidComponentRef;
+	}
+	return nodes[ref.idx].object;
+}
+void Scene::SetNodeObject(NodeRef ref, ComponentRef cref) {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node");
+		return;
+	}
+	nodes[ref.idx].object = cref;
+	impl->entries_dirty = true;
+}
+
+// ---- animation ---------------------------------------------------------------------------------------------------------------
+AnimRef Scene::AddAnim(Anim anim) { return anims.add_ref(std::move(anim)); }
+void Scene::DestroyAnim(AnimRef ref) {
+	anims.remove_ref(ref);
+	impl->anims_dirty = true;
+}
+Anim *Scene::GetAnim(AnimRef ref) {
+	impl->anims_dirty = true; // the caller may edit the tracks through the pointer
+	return anims.is_valid(ref) ? &anims[ref.idx] : nullptr;
+}
+const Anim *Scene::GetAnim(AnimRef ref) const { return anims.is_valid(ref) ? &anims[ref.idx] : nullptr; }
+SceneAnimRef Scene::AddSceneAnim(SceneAnim anim) { return scene_anims.add_ref(std::move(anim)); }
+void Scene::DestroySceneAnim(SceneAnimRef ref) {
+	scene_anims.remove_ref(ref);
+	impl->anims_dirty = true;
+}
+SceneAnim *Scene::GetSceneAnim(SceneAnimRef ref) { return scene_anims.is_valid(ref) ? &scene_anims[ref.idx] : nullptr; }
+
+ScenePlayAnimRef Scene::PlayAnim(SceneAnimRef ref, AnimLoopMode loop_mode, Easing, time_ns t_start, time_ns t_end, bool paused, float t_scale) {
+	if (!scene_anims.is_valid(ref)) {
+		warn("Invalid scene animation reference");
+		return InvalidScenePlayAnimRef;
+	}
+	ScenePlayAnim_ p;
+	p.scene_anim = ref;
+	p.t_start = t_start != UnspecifiedAnimTime ? t_start : scene_anims[ref.idx].t_start;
+	p.t_end = t_end != UnspecifiedAnimTime ? t_end : scene_anims[ref.idx].t_end;
+	p.t = p.t_start;
+	p.t_scale = int8_t(t_scale * 16.f); // 4-bit fixed point, 16 == 1x (scene.cpp:2371)
+	p.loop_mode = loop_mode;
+	p.paused = paused;
+	p.play_slot = 0;
+	impl->anims_dirty = true;
+	return play_anims.add_ref(p);
+}
+
+bool Scene::IsPlaying(ScenePlayAnimRef ref) const { return play_anims.is_valid(ref); }
+void Scene::StopAnim(ScenePlayAnimRef ref) {
+	play_anims.remove_ref(ref);
+	impl->anims_dirty = true;
+}
+void Scene::StopAllAnims() {
+	play_anims.clear();
+	impl->anims_dirty = true;
+}
+
+// Clock half of UpdatePlayingAnims (scene.cpp:2380-2431): exact int64 arithmetic on the host, O(#playing anims). The evaluation half
+// (EvaluateBoundAnim -> Evaluate*) is the device's k_sample_tracks, fed with the times computed here.
+void Scene::UpdatePlayingAnims(time_ns dt) {
+	if (impl->anims_dirty)
+		SyncEdits(impl->resources); // (re)binds tracks and assigns play slots
+	std::fill(impl->play_t.begin(), impl->play_t.end(), HGB_NOT_PLAYING);
+	std::vector<uint32_t> finished;
+	for (uint32_t i = play_anims.first(); i != play_anims.invalid_idx; i = play_anims.next(i)) {
+		ScenePlayAnim_ &p = play_anims[i];
+		if (!p.paused)
+			p.t += (dt * p.t_scale) >> 4;
+		const time_ns span = p.t_end - p.t_start;
+		if (p.loop_mode == ALM_Loop) {
+			if (p.t_scale >= 0) {
+				while (p.t >= p.t_end && span > 0)
+					p.t -= span;
+			} else {
+				while (p.t <= p.t_start && span > 0)
+					p.t += span;
+			}
+		} else if (p.loop_mode == ALM_Once) {
+			if (p.t_scale >= 0 ? p.t >= p.t_end : p.t <= p.t_start) {
+				p.t = p.t_scale >= 0 ? p.t_end : p.t_start;
+				finished.push_back(i); // evaluated one last time this frame, then removed
+			}
+		}
+		if (p.play_slot < impl->play_t.size())
+			impl->play_t[p.play_slot] = p.t;
+	}
+	for (uint32_t i : finished)
+		play_anims.remove(i);
+	if (!finished.empty())
+		impl->rebind_after_frame = true; // re-bound (without the finished plays) once this frame's sampling has been enqueued
+	if (!impl->play_t.empty())
+		trs_host_stale = true;
+}
+
+// ---- edit flush: host scene graph -> device context ------------------------------------------------------------------------------
+// bounds table: one MinMax per (model, list) of the resource cache, indexed through `base` of the model
+static void build_bounds(const PipelineResources &res, std::vector<float> &bounds6, std::vector<uint32_t> &base_of_model) {
+	bounds6.clear();
+	base_of_model.assign(0x10000, 0xffffffffu);
+	for (uint32_t m = res.models.first(); m != 0xffffffffu; m = res.models.next(m)) {
+		const Model &mdl = res.models.Get_unsafe_(uint16_t(m));
+		base_of_model[m] = uint32_t(bounds6.size() / 6);
+		for (const MinMax &b : mdl.bounds) {
+			const float v[6] = {b.mn.x, b.mn.y, b.mn.z, b.mx.x, b.mx.y, b.mx.z};
+			bounds6.insert(bounds6.end(), v, v + 6);
+		}
+	}
+}
+
+bool Scene::SyncEdits(const PipelineResources *resources) {
+	if (!EnsureContext())
+		return false;
+	const uint32_t n = uint32_t(transforms.capacity());
+
+	if (impl->topology_dirty) {
+		RefreshTRSFromDevice(); // sampled values must survive the re-layout: they are re-uploaded below
+		std::vector<uint32_t> parent(n, HGB_ROOT);
+		std::vector<uint8_t> used(n, 0);
+		for (uint32_t i = transforms.first(); i != transforms.invalid_idx; i = transforms.next(i)) {
+			used[i] = 1;
+			const NodeRef pn = transforms[i].parent; // parent is a NODE: hop node -> its transform (scene.cpp:268)
+			if (nodes.is_valid(pn)) {
+				const ComponentRef pt = nodes[pn.idx].transform;
+				if (transforms.is_valid(pt) && pt.idx != i)
+					parent[i] = pt.idx;
+			}
+		}
+		if (hgb_set_topology(ctx, n, parent.data(), used.data())) {
+			warn(hgb_last_error());
+			return false;
+		}
+		impl->topology_dirty = false;
+		impl->trs_all_dirty = true;
+	}
+
+	if (impl->trs_all_dirty && n) {
+		impl->staging.assign(size_t(n) * 9, 0.f);
+		for (uint32_t i = transforms.first(); i != transforms.invalid_idx; i = transforms.next(i))
+			memcpy(impl->staging.data() + size_t(i) * 9, &transforms[i].TRS, 36);
+		check(hgb_upload_trs(ctx, 0, n, impl->staging.data()));
+	} else if (!impl->dirty_trs.empty()) {
+		std::vector<uint32_t> &d = impl->dirty_trs;
+		std::sort(d.begin(), d.end());
+		d.erase(std::unique(d.begin(), d.end()), d.end());
+		for (size_t a = 0; a < d.size();) { // contiguous runs of dirty slots -> one upload each
+			size_t b = a + 1;
+			while (b < d.size() && d[b] == d[b - 1] + 1)
+				++b;
+			impl->staging.resize((b - a) * 9);
+			for (size_t k = a; k < b; ++k)
+				if (transforms.is_used(d[k]))
+					memcpy(impl->staging.data() + (k - a) * 9, &transforms[d[k]].TRS, 36);
+			check(hgb_upload_trs(ctx, d[a], uint32_t(b - a), impl->staging.data()));
+			a = b;
+		}
+	}
+	impl->trs_all_dirty = false;
+	impl->dirty_trs.clear();
+
+	// bound tracks (BindNodeAnim scene.cpp:2070-2152: the LAST track with a matching target name wins; AF_UseQuaternionForRotation
+	// selects the quaternion "Rotation" track and ignores the Euler one, EvaluateBoundAnim :2168-2177), flattened in the reference's
+	// evaluation order: playing anims by index, node anims in order, Position / Rotation / Scale
+	if (impl->anims_dirty) {
+		std::vector<int64_t> v3_t, q_t;
+		std::vector<float> v3_val, v3_tension, v3_bias, q_val;
+		std::vector<hgb_track> tracks;
+		uint32_t n_play = 0;
+		for (uint32_t pi = play_anims.first(); pi != play_anims.invalid_idx; pi = play_anims.next(pi)) {
+			ScenePlayAnim_ &p = play_anims[pi];
+			p.play_slot = n_play++;
+			if (p.play_slot >= 65535) {
+				warn("Too many playing anims for one device context (65535)");
+				break;
+			}
+			if (!scene_anims.is_valid(p.scene_anim))
+				continue;
+			for (const NodeAnim &na : scene_anims[p.scene_anim.idx].node_anims) {
+				if (!anims.is_valid(na.anim) || !nodes.is_valid(na.node))
+					continue;
+				const ComponentRef t = nodes[na.node.idx].transform;
+				if (!transforms.is_valid(t))
+					continue;
+				const Anim &anim = anims[na.anim.idx];
+				int pos = -1, rot = -1, scl = -1, qrot = -1;
+				for (size_t i = 0; i < anim.vec3_tracks.size(); ++i) {
+					const std::string &tg = anim.vec3_tracks[i].target;
+					if (tg == "Position") pos = int(i);
+					else if (tg == "Rotation") rot = int(i);
+					else if (tg == "Scale") scl = int(i);
+				}
+				for (size_t i = 0; i < anim.quat_tracks.size(); ++i)
+					if (anim.quat_tracks[i].target == "Rotation")
+						qrot = int(i);
+				auto add_v3 = [&](int idx, uint8_t kind) {
+					if (idx < 0)
+						return;
+					const auto &keys = anim.vec3_tracks[idx].keys;
+					hgb_track tr{t.idx, uint32_t(v3_t.size()), uint32_t(keys.size()), uint16_t(p.play_slot), kind, 0};
+					for (const auto &k : keys) {
+						v3_t.push_back(k.t);
+						v3_val.push_back(k.v.x), v3_val.push_back(k.v.y), v3_val.push_back(k.v.z);
+						v3_tension.push_back(k.tension), v3_bias.push_back(k.bias);
+					}
+					tracks.push_back(tr);
+				};
+				add_v3(pos, 0);
+				if (anim.flags & AF_UseQuaternionForRotation) {
+					if (qrot >= 0) {
+						const auto &keys = anim.quat_tracks[qrot].keys;
+						hgb_track tr{t.idx, uint32_t(q_t.size()), uint32_t(keys.size()), uint16_t(p.play_slot), 3, 0};
+						for (const auto &k : keys) {
+							q_t.push_back(k.t);
+							q_val.push_back(k.v.x), q_val.push_back(k.v.y), q_val.push_back(k.v.z), q_val.push_back(k.v.w);
+						}
+						tracks.push_back(tr);
+					}
+				} else {
+					add_v3(rot, 1);
+				}
+				add_v3(scl, 2);
+			}
+		}
+		check(hgb_set_anim_keys(ctx, uint32_t(v3_t.size()), v3_t.data(), v3_val.data(), v3_tension.data(), v3_bias.data(), uint32_t(q_t.size()), q_t.data(),
+			q_val.data()));
+		check(hgb_set_tracks(ctx, uint32_t(tracks.size()), tracks.data(), n_play));
+		impl->play_t.assign(n_play, HGB_NOT_PLAYING);
+		impl->anims_dirty = false;
+	}
+
+	// fused culling (extension): the device entry tables = every rigid display entry in GetModelDisplayLists order, disabled nodes
+	// flagged instead of skipped, so that Enable/DisableNode only changes a flag
+	if (resources && !impl->frusta.empty() && impl->entries_dirty) {
+		std::vector<float> bounds6;
+		std::vector<uint32_t> base_of_model;
+		build_bounds(*resources, bounds6, base_of_model);
+		std::vector<uint32_t> mtx[2], bidx[2];
+		for (int k = 0; k < 2; ++k)
+			impl->ent[k].clear(), impl->ent_flags[k].clear();
+		for (uint32_t ni = nodes.first(); ni != nodes.invalid_idx; ni = nodes.next(ni)) {
+			const Node_ &node = nodes[ni];
+			if (!transforms.is_valid(node.transform) || !objects.is_valid(node.object))
+				continue;
+			const Object_ &obj = objects[node.object.idx];
+			const uint16_t mdl_idx = resources->models.GetValidatedRefIndex(obj.model);
+			if (mdl_idx == 0xffff)
+				continue;
+			const Model &mdl = resources->models.Get_unsafe_(mdl_idx);
+			if (!obj.bones.empty() && obj.bones.size() == mdl.bind_pose.size())
+				continue; // skinned lists are never culled (scene_forward_pipeline.cpp:560-562)
+			const uint8_t flag = (node.flags & (NF_Disabled | NF_InstanceDisabled)) ? HGB_ENTRY_DISABLED : 0;
+			for (size_t i = 0; i < mdl.lists.size() && i < mdl.bounds.size(); ++i) {
+				const uint16_t mat_idx = mdl.mats[i];
+				if (mat_idx >= obj.materials.size())
+					continue;
+				const int k = GetMaterialBlendMode(obj.materials[mat_idx]) != BM_Opaque ? 1 : 0;
+				impl->ent[k].push_back({&obj.materials[mat_idx], node.transform.idx, mdl_idx, uint16_t(i)});
+				impl->ent_flags[k].push_back(flag);
+				mtx[k].push_back(node.transform.idx);
+				bidx[k].push_back(base_of_model[mdl_idx] + uint32_t(i));
+			}
+		}
+		check(hgb_set_bounds(ctx, uint32_t(bounds6.size() / 6), bounds6.data()));
+		for (int k = 0; k < 2; ++k)
+			check(hgb_set_display_entries(ctx, k, uint32_t(mtx[k].size()), mtx[k].data(), bidx[k].data(), impl->ent_flags[k].data(), nullptr));
+		impl->entries_dirty = false;
+	}
+	if (impl->views_dirty && !impl->frusta.empty()) {
+		check(hgb_set_views(ctx, uint32_t(impl->frusta.size()), &impl->frusta[0][0].x));
+		impl->views_dirty = false;
+	}
+	return true;
+}
+
+void Scene::SetCullingFrustums(const std::vector<Frustum> &frustums, const PipelineResources &resources) {
+	if (frustums.size() > HGB_MAX_VIEWS) {
+		warn("Too many culling frustums (8 at most)");
+		return;
+	}
+	if (impl->resources != &resources || impl->frusta.empty() != frustums.empty())
+		impl->entries_dirty = true;
+	impl->resources = &resources;
+	impl->frusta = frustums;
+	impl->views_dirty = true;
+}
+
+bool Scene::GetVisibleModelDisplayLists(uint32_t view, bool transparent, std::vector<ModelDisplayList> &out, const PipelineResources &) {
+	out.clear();
+	const int k = transparent ? 1 : 0;
+	if (!ctx || impl->frusta.empty() || view >= impl->frusta.size() || impl->entries_dirty) {
+		warn("GetVisibleModelDisplayLists: no fused culling result for this view (SetCullingFrustums + Update first)");
+		return false;
+	}
+	std::vector<uint32_t> idx(std::max<size_t>(impl->ent[k].size(), 1));
+	uint32_t n = 0;
+	if (hgb_get_visible(ctx, k, view, idx.data(), uint32_t(idx.size()), &n)) {
+		warn(hgb_last_error());
+		return false;
+	}
+	out.reserve(n);
+	for (uint32_t i = 0; i < n; ++i)
+		out.push_back(impl->ent[k][idx[i]]);
+	return true;
+}
+
+// ---- per-frame path ----------------------------------------------------------------------------------------------------------
+// a2 (scene.cpp:291-294): the device swaps its two world buffers inside hgb_update; the host mirrors swap with them.
+void Scene::StorePreviousWorldMatrices() {
+	std::swap(transform_worlds, previous_transform_worlds);
+	std::swap(worlds_valid, previous_valid);
+	// the registry is keyed by vector ADDRESS, which std::swap does not change: both addresses keep naming this scene
+}
+
+// a3 (scene.cpp:280-284): sizes the world vectors to transforms.capacity() and opens the frame: edits are flushed to the device and
+// SetNodeWorldMatrix calls from here to ComputeWorldMatrices are recorded as presets.
+void Scene::ReadyWorldMatrices() {
+	transform_worlds.resize(transforms.capacity());
+	worlds_valid = false;
+	impl->preset_slots.clear();
+	impl->preset_mats.clear();
+	impl->in_frame = true;
+	SyncEdits(impl->resources);
+}
+
+// a4 (scene.cpp:263-289) — on the device: k_sample_tracks + k_update_level per hierarchy level (+ fused visibility / compaction)
+void Scene::ComputeWorldMatrices() {
+	impl->in_frame = false;
+	if (!SyncEdits(impl->resources)) // setters may have run since ReadyWorldMatrices (scripts, physics)
+		return;
+	if (!impl->preset_slots.empty())
+		check(hgb_set_preset_world(ctx, uint32_t(impl->preset_slots.size()), impl->preset_slots.data(), impl->preset_mats.data()));
+	const bool fused = impl->resources && !impl->frusta.empty();
+	check(hgb_update(ctx, uint32_t(impl->play_t.size()), impl->play_t.data(), fused ? 1 : 0));
+	std::fill(impl->play_t.begin(), impl->play_t.end(), HGB_NOT_PLAYING); // a clock drives the sampling of ONE frame
+	if (impl->rebind_after_frame)
+		impl->anims_dirty = true, impl->rebind_after_frame = false;
+	impl->preset_slots.clear();
+	impl->preset_mats.clear();
+	worlds_valid = false;
+}
+
+// a5 (scene.cpp:296-304): the reference resizes the previous vectors; its copy loop is a no-op (`==` at :303)
+void Scene::FixupPreviousWorldMatrices() { previous_transform_worlds.resize(transform_worlds.size()); }
+
+void Scene::Update(time_ns dt) { // scene.cpp:307-315
+	StorePreviousWorldMatrices();
+	ReadyWorldMatrices();
+	UpdatePlayingAnims(dt);
+	ComputeWorldMatrices();
+	FixupPreviousWorldMatrices();
+}
+
+static void download_worlds(hgb_ctx *ctx, std::vector<Mat4> &dst, size_t capacity, bool previous) {
+	dst.resize(capacity);
+	if (ctx && capacity)
+		check(hgb_get_worlds(ctx, 0, uint32_t(capacity), &dst[0].m[0][0], previous ? 1 : 0));
+}
+
+const std::vector<Mat4> &Scene::GetTransformWorldMatrices() const {
+	if (!worlds_valid) {
+		if (ctx && !impl->topology_dirty)
+			download_worlds(ctx, transform_worlds, transforms.capacity(), false);
+		worlds_valid = true;
+	}
+	return transform_worlds;
+}
+
+const std::vector<Mat4> &Scene::GetPreviousTransformWorldMatrices() const {
+	if (!previous_valid) {
+		if (ctx && !impl->topology_dirty)
+			download_worlds(ctx, previous_transform_worlds, transforms.capacity(), true);
+		previous_valid = true;
+	}
+	return previous_transform_worlds;
+}
+
+// ---- display lists (host walk, like the reference: it only reads flags and refs, scene.cpp:318-404) -----------------------------
+void Scene::GetModelDisplayLists(std::vector<ModelDisplayList> &out_opaque, std::vector<ModelDisplayList> &out_transparent,
+	std::vector<SkinnedModelDisplayList> &out_opaque_skinned, std::vector<SkinnedModelDisplayList> &out_transparent_skinned,
+	const PipelineResources &resources) const {
+	out_opaque.clear(), out_transparent.clear(), out_opaque_skinned.clear(), out_transparent_skinned.clear();
+	out_opaque.reserve(nodes.size());
+	for (uint32_t ni = nodes.first(); ni != nodes.invalid_idx; ni = nodes.next(ni)) {
+		const Node_ &node = nodes[ni];
+		if (node.flags & (NF_Disabled | NF_InstanceDisabled))
+			continue;
+		if (!transforms.is_valid(node.transform) || !objects.is_valid(node.object))
+			continue; // a valid transform is required even for skinned objects, like the reference (:335-336)
+		const Object_ &obj = objects[node.object.idx];
+		const uint16_t mdl_idx = resources.models.GetValidatedRefIndex(obj.model);
+		const Model &mdl = resources.models.Get_unsafe_(mdl_idx);
+		const size_t bone_count = obj.bones.size();
+		const bool skinned = bone_count > 0 && bone_count == mdl.bind_pose.size();
+		for (size_t i = 0; i < mdl.lists.size(); ++i) {
+			const uint16_t mat_idx = mdl.mats[i];
+			if (mat_idx >= obj.materials.size())
+				continue; // silently dropped (:352)
+			const Material *mat = &obj.materials[mat_idx];
+			const bool transparent = GetMaterialBlendMode(*mat) != BM_Opaque;
+			if (!skinned) {
+				(transparent ? out_transparent : out_opaque).push_back({mat, node.transform.idx, mdl_idx, uint16_t(i)});
+				continue;
+			}
+			SkinnedModelDisplayList dl{};
+			dl.mat = mat;
+			const std::vector<uint16_t> &table = mdl.lists[i].bones_table;
+			const size_t n = std::min<size_t>(table.size(), max_skinned_model_matrix_count);
+			for (size_t j = 0; j < n; ++j) {
+				uint16_t bone_idx = table[j];
+				uint32_t mtx_idx = node.transform.idx; // a stale bone ref falls back to the object's own transform (:372-383)
+				if (bone_idx < bone_count) {
+					const NodeRef bone = obj.bones[bone_idx];
+					if (nodes.is_valid(bone) && transforms.is_valid(nodes[bone.idx].transform))
+						mtx_idx = nodes[bone.idx].transform.idx;
+				} else {
+					bone_idx = 0;
+				}
+				dl.mtx_idxs[j] = mtx_idx;
+				dl.bones_idxs[j] = bone_idx;
+			}
+			dl.bone_count = uint16_t(n);
+			dl.mdl_idx = mdl_idx;
+			dl.lst_idx = uint16_t(i);
+			(transparent ? out_transparent_skinned : out_opaque_skinned).push_back(dl);
+		}
+	}
+}
+
+static Scene *scene_of(const std::vector<Mat4> &mtxs) {
+	std::lock_guard<std::mutex> lock(g_registry_mutex);
+	auto i = g_registry.find(&mtxs);
+	return i == g_registry.end() ? nullptr : i->second;
+}
+
+// render_pipeline.cpp:2098-2104 through hgb_cull_list: any caller-owned list, any frustum, the scene's current world matrices
+void CullModelDisplayLists(const Frustum &frustum, std::vector<ModelDisplayList> &display_lists, const std::vector<Mat4> &mtxs, const PipelineResources &resources) {
+	if (display_lists.empty())
+		return;
+	Scene *scene = scene_of(mtxs);
+	if (!scene || !scene->ctx) {
+		warn("CullModelDisplayLists: the matrices do not belong to a live hg::Scene with a device context; list left unculled");
+		return;
+	}
+	std::vector<float> bounds6;
+	std::vector<uint32_t> base_of_model;
+	build_bounds(resources, bounds6, base_of_model);
+	const uint32_t n = uint32_t(display_lists.size());
+	std::vector<uint32_t> mtx(n), bidx(n), out(n);
+	for (uint32_t i = 0; i < n; ++i) {
+		mtx[i] = display_lists[i].mtx_idx;
+		bidx[i] = base_of_model[display_lists[i].mdl_idx] + display_lists[i].lst_idx;
+	}
+	uint32_t count = 0;
+	if (hgb_cull_list(scene->ctx, n, mtx.data(), bidx.data(), uint32_t(bounds6.size() / 6), bounds6.data(), &frustum[0].x, out.data(), &count)) {
+		warn(hgb_last_error());
+		return;
+	}
+	for (uint32_t i = 0; i < count; ++i) // ascending survivor indices: the in-place gather never overwrites an unread entry
+		display_lists[i] = display_lists[out[i]];
+	display_lists.resize(count);
+}
+
+// render_pipeline.cpp:2157-2188 (math :2172-2173, previous frame :2177-2181) through hgb_set_skins / hgb_bone_matrices
+size_t ComputeSkinMatrices(const std::vector<SkinnedModelDisplayList> &display_lists, const std::vector<Mat4> &mtxs, const PipelineResources &resources,
+	std::vector<float> &out16, bool previous) {
+	out16.clear();
+	Scene *scene = scene_of(mtxs);
+	if (!scene || !scene->ctx) {
+		warn("ComputeSkinMatrices: the matrices do not belong to a live hg::Scene with a device context");
+		return 0;
+	}
+	// bind-pose pool: every model's bind pose back to back
+	std::vector<float> pool;
+	std::vector<uint32_t> base_of_model(0x10000, 0);
+	for (uint32_t m = resources.models.first(); m != 0xffffffffu; m = resources.models.next(m)) {
+		const Model &mdl = resources.models.Get_unsafe_(uint16_t(m));
+		base_of_model[m] = uint32_t(pool.size() / 12);
+		for (const Mat4 &b : mdl.bind_pose)
+			pool.insert(pool.end(), &b.m[0][0], &b.m[0][0] + 12);
+	}
+	std::vector<uint32_t> mtx, bind;
+	for (const SkinnedModelDisplayList &dl : display_lists)
+		for (uint16_t j = 0; j < dl.bone_count; ++j) {
+			mtx.push_back(dl.mtx_idxs[j]);
+			bind.push_back(base_of_model[dl.mdl_idx] + dl.bones_idxs[j]);
+		}
+	if (mtx.empty())
+		return 0;
+	Scene::Impl *impl = scene->impl;
+	if (mtx != impl->skin_mtx || bind != impl->skin_bind || pool.size() != impl->skin_bind_count) { // records changed: re-upload
+		if (hgb_set_skins(scene->ctx, uint32_t(mtx.size()), mtx.data(), bind.data(), uint32_t(pool.size() / 12), pool.data())) {
+			warn(hgb_last_error());
+			return 0;
+		}
+		impl->skin_mtx = mtx, impl->skin_bind = bind, impl->skin_bind_count = pool.size();
+	}
+	out16.resize(mtx.size() * 16);
+	if (hgb_bone_matrices(scene->ctx, previous ? 1 : 0) || hgb_get_bone_matrices(scene->ctx, out16.data(), previous ? 1 : 0)) {
+		warn(hgb_last_error());
+		out16.clear();
+		return 0;
+	}
+	return mtx.size();
+}
+
+// ---- garbage collection (scene.cpp:92-237): components no node refers to, anims no scene anim refers to -----------------------
+size_t Scene::GarbageCollect() {
+	size_t removed = 0;
+	std::vector<uint8_t> trs_used(transforms.capacity(), 0), obj_used(objects.capacity(), 0);
+	for (uint32_t ni = nodes.first(); ni != nodes.invalid_idx; ni = nodes.next(ni)) {
+		if (transforms.is_valid(nodes[ni].transform))
+			trs_used[nodes[ni].transform.idx] = 1;
+		if (objects.is_valid(nodes[ni].object))
+			obj_used[nodes[ni].object.idx] = 1;
+	}
+	for (uint32_t i = transforms.first(); i != transforms.invalid_idx;) {
+		const uint32_t nx = transforms.next(i);
+		if (!trs_used[i]) {
+			transforms.remove_ref(transforms.get_ref(i));
+			++removed;
+			impl->topology_dirty = true;
+		}
+		i = nx;
+	}
+	for (uint32_t i = objects.first(); i != objects.invalid_idx;) {
+		const uint32_t nx = objects.next(i);
+		if (!obj_used[i]) {
+			objects.remove_ref(objects.get_ref(i));
+			++removed;
+			impl->entries_dirty = true;
+		}
+		i = nx;
+	}
+	if (removed)
+		impl->anims_dirty = true;
+	return removed;
+}
+
+} // namespace hg

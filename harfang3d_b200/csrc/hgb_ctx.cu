@@ -164,6 +164,7 @@ struct hgb_ctx {
 	HBuf staging;  // pinned host staging for uploads/downloads
 	DBuf staging_d; // device staging (slot-order data before scatter / after gather)
 	DBuf flush;
+	DBuf adhoc_pos, adhoc_meta, adhoc_bounds, adhoc_planes, adhoc_vis, adhoc_out, adhoc_scratch; // hgb_cull_list
 
 	// CUDA graph of one frame
 	cudaGraphExec_t graph_exec[2][2] = {}; // [fused][world-buffer parity]
@@ -280,7 +281,7 @@ void hgb_destroy(hgb_ctx *c) {
 				cudaGraphExecDestroy(g);
 	DBuf *bufs[] = {&c->tiles, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
 		&c->pent, &c->pos_view, &c->inst_planes, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
-		&c->bone_out[1], &c->keys, &c->cursor, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->view_planes};
+		&c->bone_out[1], &c->keys, &c->cursor, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes};
 	for (DBuf *b : bufs)
 		b->release();
 	for (auto &t : c->ent) {

@@ -211,6 +211,71 @@ int hgb_cull(hgb_ctx *c) {
 	return 0;
 }
 
+int hgb_cull_list(hgb_ctx *c, uint32_t n, const uint32_t *mtx_slot, const uint32_t *bounds_idx, uint32_t n_bounds, const float *bounds6, const float *frustum24,
+	uint32_t *out_idx, uint32_t *out_count) {
+	if (!c)
+		return fail("null context");
+	if (out_count)
+		*out_count = 0;
+	if (!n)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	std::vector<uint32_t> pos(n);
+	for (uint32_t e = 0; e < n; ++e) {
+		if (mtx_slot[e] >= c->n_slots)
+			return fail("hgb_cull_list: entry %u references slot %u outside the topology", e, mtx_slot[e]);
+		if (bounds_idx[e] >= n_bounds)
+			return fail("hgb_cull_list: entry %u references bounds %u outside the table", e, bounds_idx[e]);
+		pos[e] = c->pos_of_slot[mtx_slot[e]];
+	}
+	const uint32_t n_tiles = (n + kCompactTile - 1) / kCompactTile;
+	float cond[24];
+	precondition_planes(frustum24, 6, cond);
+	if (upload(c, c->adhoc_pos, pos.data(), size_t(n) * 4) || upload(c, c->adhoc_meta, bounds_idx, size_t(n) * 4) ||
+		upload(c, c->adhoc_bounds, bounds6, size_t(n_bounds) * 24) || upload(c, c->adhoc_planes, cond, 96))
+		return 1;
+	CK(c->adhoc_vis.reserve(size_t(n_tiles + 1) * kCompactTile));
+	CK(c->adhoc_out.reserve(size_t(n) * 4));
+	CK(c->adhoc_scratch.reserve(size_t(n_tiles + 2) * 4));
+	CK(cudaMemsetAsync(c->adhoc_vis.p, 0, size_t(n_tiles + 1) * kCompactTile, c->stream));
+	CK(cudaMemsetAsync(c->adhoc_scratch.p, 0, size_t(n_tiles + 2) * 4, c->stream));
+	CullDev d{};
+	d.mtx_pos = c->adhoc_pos.as<uint32_t>();
+	d.meta = c->adhoc_meta.as<uint32_t>();
+	d.world = c->world[c->cur].as<float>();
+	d.bounds6 = c->adhoc_bounds.as<float>();
+	d.vis = c->adhoc_vis.as<uint8_t>();
+	d.n = n;
+	Views v{c->adhoc_planes.as<float4>(), 1};
+	prof_begin(c, HGB_K_CULL_FLAGS);
+	k_cull_flags<false><<<grid_for(n), 256, 0, c->stream>>>(d, v);
+	prof_end(c);
+	CompactDev cd{};
+	cd.vis = d.vis;
+	cd.n = n;
+	cd.bit = 0;
+	cd.out = c->adhoc_out.as<uint32_t>();
+	cd.count = c->adhoc_scratch.as<uint32_t>();
+	cd.ticket = c->adhoc_scratch.as<uint32_t>() + 1;
+	cd.status = c->adhoc_scratch.as<uint32_t>() + 2;
+	prof_begin(c, HGB_K_COMPACT);
+	k_compact<<<n_tiles, kCompactThreads, 0, c->stream>>>(cd);
+	prof_end(c);
+	c->launches += 2;
+	CK(cudaGetLastError());
+	uint32_t count = 0;
+	CK(cudaMemcpyAsync(&count, cd.count, 4, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream)); // also keeps pos[] alive until the upload is done
+	if (count > n)
+		return fail("hgb_cull_list: internal error (count %u > n %u)", count, n);
+	if (count)
+		CK(cudaMemcpyAsync(out_idx, c->adhoc_out.p, size_t(count) * 4, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	if (out_count)
+		*out_count = count;
+	return 0;
+}
+
 int hgb_bone_matrices(hgb_ctx *c, int with_previous) {
 	if (!c)
 		return fail("null context");

@@ -104,6 +104,11 @@ int hgb_set_instance_views(hgb_ctx *, uint32_t n_instances, const float *frustum
 int hgb_update(hgb_ctx *, uint32_t n_play, const int64_t *play_t, int fused_cull);
 /* CullModelDisplayLists against the current views using the stored world matrices. */
 int hgb_cull(hgb_ctx *);
+/* CullModelDisplayLists (render_pipeline.cpp:2098-2104) for an arbitrary caller-owned list, exactly like the reference's free function:
+ * entry e uses the current world matrix of transform slot mtx_slot[e] and the MinMax bounds6[bounds_idx[e]]; the surviving entry
+ * indices are written to out_idx in order (capacity n) and their number to *out_count. Independent of the entry tables above. */
+int hgb_cull_list(hgb_ctx *, uint32_t n, const uint32_t *mtx_slot, const uint32_t *bounds_idx, uint32_t n_bounds, const float *bounds6,
+	const float *frustum24, uint32_t *out_idx, uint32_t *out_count);
 /* Bone matrices of every skin record (and the previous-frame twin). */
 int hgb_bone_matrices(hgb_ctx *, int with_previous);
 

@@ -7,6 +7,10 @@
 // headers. The only restated arithmetic is the bone-matrix product (render_pipeline.cpp:2172-2173 + to_bgfx
 // :59-62) because the reference function is static and interleaved with bgfx calls.
 // Never loaded by the product (harfang3d_b200/).
+//
+// The same file also compiles, unchanged, against the hg::Scene FACADE of the product (harfang3d_b200/csrc/facade/include, -DHG_FACADE):
+// that build (oracle/_facade/libhg_facade_driver.so, `make -C oracle facade_driver`) is how tests/test_facade.py drives the facade
+// through the very calls that drive the reference. Only the probes of reference-internal host math are compiled out there.
 #include "engine/animation.h"
 #include "engine/render_pipeline.h"
 #include "engine/scene.h"
@@ -341,6 +345,16 @@ int hgref_cull(void *h, int kind, const float *frustum24, uint32_t *src_pos, uin
 int hgref_bone_matrices(void *h, int kind, int previous, float *out16) {
 	auto *c = static_cast<RefCtx *>(h);
 	const auto &v = kind == 2 ? c->opaque_skinned : c->transparent_skinned;
+#ifdef HG_FACADE
+	{ // the facade exposes the loop as a callable (computed on the device)
+		std::vector<float> o;
+		const size_t nb = ComputeSkinMatrices(v, previous ? c->scene->GetPreviousTransformWorldMatrices() : c->scene->GetTransformWorldMatrices(), c->resources,
+			o, previous != 0);
+		if (out16 && nb)
+			memcpy(out16, o.data(), nb * 64);
+		return int(nb);
+	}
+#else
 	const auto &mtxs = previous ? c->scene->GetPreviousTransformWorldMatrices() : c->scene->GetTransformWorldMatrices();
 	size_t n = 0;
 	for (const auto &dl : v) {
@@ -353,6 +367,7 @@ int hgref_bone_matrices(void *h, int kind, int previous, float *out16) {
 		}
 	}
 	return int(n);
+#endif
 }
 
 // ---- view / frustum (a12.3) ------------------------------------------------------------------------------------
@@ -383,6 +398,7 @@ void hgref_inverse_fast(const float *a12, float *out12) {
 	const Mat4 m = InverseFast(mat4_from(a12));
 	memcpy(out12, m.m, 48);
 }
+#ifndef HG_FACADE // reference-internal host math (the facade computes these on the device only)
 void hgref_minmax_transform(const float *m12, const float *mm6, float *out6) {
 	const MinMax o = mat4_from(m12) * MinMax(Vec3(mm6[0], mm6[1], mm6[2]), Vec3(mm6[3], mm6[4], mm6[5]));
 	memcpy(out6, &o.mn, 12);
@@ -426,6 +442,7 @@ int hgref_eval_quat_track(int n_keys, const int64_t *t, const float *v4, int64_t
 	memcpy(out4, &q, 16);
 	return r ? 1 : 0;
 }
+#endif
 float hgref_sinf(float x) { return sinf(x); } // the libm the reference links (matrix3.cpp:199-204)
 float hgref_cosf(float x) { return cosf(x); }
 

@@ -54,11 +54,8 @@ def load_port():
     return L
 
 
-def load_ref():
-    so = os.path.join(ORACLE, "_ref", "libhg_ref.so")
-    if not os.path.exists(so):
-        return None
-    L = C.CDLL(so)
+def _bind_scene_driver(L, with_probes):
+    """signatures of oracle/ref_driver.cpp (same file for the reference build and the facade build)"""
     _sig(L, "hgref_create", c_p, [])
     _sig(L, "hgref_destroy", None, [c_p])
     _sig(L, "hgref_add_model", c_i, [c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_p])
@@ -90,17 +87,35 @@ def load_ref():
     _sig(L, "hgref_bone_matrices", c_i, [c_p, c_i, c_i, c_p])
     _sig(L, "hgref_make_perspective_frustum", None, [c_f] * 5 + [c_p, c_p])
     _sig(L, "hgref_make_ortho_frustum", None, [c_f] * 5 + [c_p, c_p])
-    for n in ("hgref_transformation_mat4", "hgref_inverse_fast", "hgref_quat_to_euler"):
+    for n in ("hgref_transformation_mat4", "hgref_inverse_fast"):
         _sig(L, n, None, [c_p, c_p])
-    for n in ("hgref_mat4_mul", "hgref_minmax_transform"):
-        _sig(L, n, None, [c_p, c_p, c_p])
-    _sig(L, "hgref_test_visibility", c_i, [c_p, c_p])
-    _sig(L, "hgref_eval_vec3_track", c_i, [c_i, c_p, c_p, c_p, c_p, c_i64, c_p, c_p])
-    _sig(L, "hgref_eval_quat_track", c_i, [c_i, c_p, c_p, c_i64, c_p])
+    _sig(L, "hgref_mat4_mul", None, [c_p, c_p, c_p])
     _sig(L, "hgref_sinf", c_f, [c_f])
     _sig(L, "hgref_cosf", c_f, [c_f])
     _sig(L, "hgref_time_frames", c_i, [c_p, c_i, c_i64, c_p, c_i, c_p])
+    if with_probes:  # reference-internal host math: compiled out of the facade build
+        _sig(L, "hgref_minmax_transform", None, [c_p, c_p, c_p])
+        _sig(L, "hgref_quat_to_euler", None, [c_p, c_p])
+        _sig(L, "hgref_test_visibility", c_i, [c_p, c_p])
+        _sig(L, "hgref_eval_vec3_track", c_i, [c_i, c_p, c_p, c_p, c_p, c_i64, c_p, c_p])
+        _sig(L, "hgref_eval_quat_track", c_i, [c_i, c_p, c_p, c_i64, c_p])
     return L
+
+
+def load_ref():
+    so = os.path.join(ORACLE, "_ref", "libhg_ref.so")
+    if not os.path.exists(so):
+        return None
+    return _bind_scene_driver(C.CDLL(so), True)
+
+
+def load_facade_driver():
+    """oracle/ref_driver.cpp compiled against the PRODUCT's hg::Scene facade (make -C oracle facade_driver): same flat calls, so
+    tests.scene_io.RefScene drives the facade exactly like it drives the reference. None when not built."""
+    so = os.path.join(ORACLE, "_facade", "libhg_facade_driver.so")
+    if not os.path.exists(so):
+        return None
+    return _bind_scene_driver(C.CDLL(so), False)
 
 
 def bits(a):

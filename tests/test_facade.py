@@ -1,0 +1,171 @@
+"""The hg::Scene facade (harfang3d_b200/csrc/facade) driven through the SAME flat driver that drives the reference
+(oracle/ref_driver.cpp compiled twice: against /root/reference -> oracle/_ref, against the facade headers -> oracle/_facade).
+
+CPU tests: the host-side half of the facade — slot containers, refs, GetModelDisplayLists — needs no GPU and must match the
+reference's behaviour (harfang/tests/engine/scene.cpp:115-154, foundation/vector_list.h).
+GPU tests: whole frames (Update, display lists, CullModelDisplayLists, bone matrices, presets, edits) == the reference / golden fixtures.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from harfang3d_b200 import hostmirror, scenegen
+from tests import oracle_lib
+from tests.golden.gen_golden import golden_scenes
+from tests.oracle_lib import P, bits
+from tests.scene_io import RefScene
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def fac():
+    L = oracle_lib.load_facade_driver()
+    if L is None:
+        pytest.skip("oracle/_facade/libhg_facade_driver.so not built (make -C harfang3d_b200 facade && make -C oracle facade_driver)")
+    return L
+
+
+def six_objects():
+    n = 6
+    return scenegen.FlatScene(trs=np.tile(np.array([0, 0, 0, 0, 0, 0, 1, 1, 1], np.float32), (n, 1)), parent=np.full(n, -1, np.int32),
+                              disabled=np.zeros(n, np.uint8), model=np.zeros(n, np.int32), n_mats=np.ones(n, np.uint8),
+                              transparent_mask=np.zeros(n, np.uint32), models=scenegen.box_models(np.random.default_rng(0), 1),
+                              camera=dict(scenegen.DEFAULT_CAMERA))
+
+
+def test_facade_display_list_counts_like_reference_unit_test(fac):
+    """harfang/tests/engine/scene.cpp:115-154 restated against the facade: 6 / 3 / 6 / 0 opaque lists (host-side, no GPU needed)"""
+    sc = RefScene(fac, six_objects())
+    counts = lambda: sc.display_lists()[0][0]
+    assert counts() == 6
+    for i in (0, 2, 4):
+        fac.hgref_enable_node(sc.h, i, 0)
+    assert counts() == 3
+    for i in range(6):
+        fac.hgref_enable_node(sc.h, i, 1)
+    assert counts() == 6
+    for i in range(6):
+        fac.hgref_enable_node(sc.h, i, 0)
+    assert counts() == 0
+    sc.close()
+
+
+@pytest.mark.ref
+def test_facade_slot_reuse_and_lists_match_reference(fac, ref):
+    """destroy nodes + garbage collect + create again: transform slots are reused in the reference's order (LIFO free list), so the
+    mtx_idx sequence of the display lists is identical (host-side)"""
+    rng = np.random.default_rng(5)
+    fs = scenegen.static_scene(400, 4, 6, n_models=3, seed=5, disabled_frac=0.1)
+    a, b = RefScene(ref, fs), RefScene(fac, fs)
+    kill = rng.choice(fs.n, 120, replace=False)
+    for L_, s in ((ref, a), (fac, b)):
+        for nd in kill:
+            L_.hgref_destroy_node(s.h, int(nd))
+        assert L_.hgref_garbage_collect(s.h) > 0
+    extra = scenegen.static_scene(90, 2, 89, n_models=3, seed=6, disabled_frac=0.0)
+    for L_, s in ((ref, a), (fac, b)):
+        L_.hgref_add_nodes(s.h, extra.n, P(np.ascontiguousarray(extra.trs)), None, P(extra.disabled), P(extra.model), P(extra.n_mats),
+                           P(extra.transparent_mask), None)
+    idx_a = [ref.hgref_node_transform_idx(a.h, i) for i in range(fs.n + extra.n)]
+    idx_b = [fac.hgref_node_transform_idx(b.h, i) for i in range(fs.n + extra.n)]
+    assert idx_a == idx_b
+    (ca, la), (cb, lb) = a.display_lists(), b.display_lists()
+    assert (ca == cb).all() and all((x == y).all() for x, y in zip(la[0], lb[0]))
+    a.close(); b.close()
+
+
+# ---- GPU: whole frames through the facade ---------------------------------------------------------------------------------------
+def frame_checks(sc, gs, name, fs, frames, dt):
+    for _ in range(frames):
+        sc.update(dt)
+    assert (bits(sc.worlds()[: fs.n]) == bits(gs[name + "_worlds"])).all()
+    if frames > 1:
+        assert (bits(sc.worlds(previous=True)[: fs.n]) == bits(gs[name + "_worlds_prev"])).all()
+    counts, lists = sc.display_lists()
+    assert (counts == gs[name + "_dl_counts"]).all() and (lists[0][0] == gs[name + "_dl_mtx"]).all()
+    if name + "_trs" in gs:
+        assert (bits(sc.trs(gs[name + "_trs_nodes"])) == bits(gs[name + "_trs"])).all()
+    frusta = hostmirror.scene_frusta(fs)
+    for v in range(len(frusta)):
+        pos, mtx = sc.cull(0, frusta[v])
+        assert (pos == gs["%s_vis%d_pos" % (name, v)]).all() and (mtx == gs["%s_vis%d_mtx" % (name, v)]).all()
+    if name + "_bones" in gs:
+        assert (bits(sc.bone_matrices()) == bits(gs[name + "_bones"])).all()
+        assert (bits(sc.bone_matrices(previous=True)) == bits(gs[name + "_bones_prev"])).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["c1", "pos", "c5s"])
+def test_facade_frames_match_golden(fac, name):
+    """Scene::Update + GetModelDisplayLists + CullModelDisplayLists through the facade == reference outputs (bit-exact)"""
+    gs = np.load(os.path.join(G, "scenes.npz"))
+    make, frames, dt = golden_scenes()[name]
+    fs = make()
+    sc = RefScene(fac, fs)
+    frame_checks(sc, gs, name, fs, frames, dt)
+    sc.close()
+
+
+@pytest.mark.gpu
+def test_facade_skinned_animated_within_tolerance(fac):
+    """c3s has quaternion rotation tracks (device atan2): matrices within 1e-5 of the reference fixtures, lists identical"""
+    gs = np.load(os.path.join(G, "scenes.npz"))
+    make, frames, dt = golden_scenes()["c3s"]
+    fs = make()
+    sc = RefScene(fac, fs)
+    for _ in range(frames):
+        sc.update(dt)
+    w, w_ref = sc.worlds()[: fs.n], gs["c3s_worlds"]
+    scale = np.abs(w_ref).max()
+    assert (np.abs(w.astype(np.float64) - w_ref) / np.maximum(np.abs(w_ref), 1e-6 * scale)).max() <= 1e-5
+    b, b_ref = sc.bone_matrices(), gs["c3s_bones"]
+    assert b.shape == b_ref.shape and (np.abs(b.astype(np.float64) - b_ref) / np.maximum(np.abs(b_ref), 1e-6 * np.abs(b_ref).max())).max() <= 1e-5
+    counts, _ = sc.display_lists()
+    assert (counts == gs["c3s_dl_counts"]).all()
+    sc.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.ref
+def test_facade_presets_and_edits_match_reference(fac, ref):
+    """SceneUpdateSystems-style split frame with SetNodeWorldMatrix presets, then TRS edits, re-parenting, enable/disable"""
+    rng = np.random.default_rng(81)
+    fs = scenegen.static_scene(3_000, 5, 6, n_models=2, seed=81)
+    nodes = np.sort(rng.choice(fs.n, 700, replace=False)).astype(np.int32)
+    scenegen.add_position_tracks(fs, nodes, rng, n_keys=10)
+    a, b = RefScene(ref, fs), RefScene(fac, fs)
+    fr = hostmirror.scene_frusta(fs)[0]
+    slots = rng.choice(fs.n, 150, replace=False)
+    mats = np.zeros((150, 12), np.float32); mats[:, [0, 5, 10]] = 1; mats[:, [3, 7, 11]] = rng.uniform(-10, 10, (150, 3))
+
+    def same():
+        assert (bits(a.worlds()[: fs.n]) == bits(b.worlds()[: fs.n])).all()
+        assert (bits(a.trs(np.arange(0, fs.n, 7))) == bits(b.trs(np.arange(0, fs.n, 7)))).all()
+        (pa, ma), (pb, mb) = a.cull(0, fr), b.cull(0, fr)
+        assert (pa == pb).all() and (ma == mb).all()
+
+    for frame in range(3):
+        for L_, s in ((ref, a), (fac, b)):
+            L_.hgref_update_phase(s.h, 0, scenegen.FRAME_DT)
+            if frame == 1:
+                for sl, m in zip(slots, mats):
+                    L_.hgref_set_node_world(s.h, int(sl), P(np.ascontiguousarray(m)))
+            L_.hgref_update_phase(s.h, 1, scenegen.FRAME_DT)
+        same()
+    leaves = np.setdiff1d(np.arange(fs.n), np.unique(fs.parent[fs.parent >= 0]))
+    moved = rng.choice(leaves, 200, replace=False)
+    for L_, s in ((ref, a), (fac, b)):
+        for i in range(0, fs.n, 3):
+            t = fs.trs[i].copy(); t[3:6] += 0.1; t[0:3] -= 0.2
+            L_.hgref_set_trs(s.h, i, P(np.ascontiguousarray(t)))
+        for k, nd in enumerate(moved):
+            L_.hgref_set_parent(s.h, int(nd), int(k % 30))
+        for nd in range(0, fs.n, 11):
+            L_.hgref_enable_node(s.h, nd, 0)
+    for frame in range(2):
+        a.update(scenegen.FRAME_DT); b.update(scenegen.FRAME_DT)
+        same()
+    a.close(); b.close()
