@@ -276,3 +276,17 @@ def config_c5(seed=5, n_instances=8192, nodes_per_instance=2048, depth=6):
     fs.instance_start = off.astype(np.uint32)
     fs.instance_cameras = random_camera_worlds(rng, n_instances, extent=8.0)
     return fs
+
+
+def slice_instances(fs, i0, i1):
+    """The sub-batch [i0, i1) of an instance batch without animation (config_c5 style): what one rank owns when the batch is sharded
+    across GPUs (sharding.partition_instances). Node indices are rebased to the slice; models are shared (replicated per rank)."""
+    assert fs.instance_start is not None and len(fs.anim_node) == 0 and not fs.bones
+    lo, hi = int(fs.instance_start[i0]), int(fs.instance_start[i1])
+    parent = fs.parent[lo:hi].astype(np.int64)
+    parent = np.where(parent >= 0, parent - lo, -1).astype(np.int32)
+    sub = FlatScene(trs=fs.trs[lo:hi].copy(), parent=parent, disabled=fs.disabled[lo:hi].copy(), model=fs.model[lo:hi].copy(),
+                    n_mats=fs.n_mats[lo:hi].copy(), transparent_mask=fs.transparent_mask[lo:hi].copy(), models=fs.models, camera=dict(fs.camera))
+    sub.instance_start = (fs.instance_start[i0:i1 + 1].astype(np.int64) - lo).astype(np.uint32)
+    sub.instance_cameras = fs.instance_cameras[i0:i1].copy()
+    return sub

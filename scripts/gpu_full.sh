@@ -1,0 +1,17 @@
+#!/bin/bash
+# One gpurun call: parity tests, bench (own + reference arm), then — only after the same bench command exited 0 without ncu —
+# the ncu launch list and full captures of the hot kernels.
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,memory.total,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
+nproc >> gpurun_out/gpu.txt; free -g >> gpurun_out/gpu.txt; lscpu | egrep "Model name|^CPU\(s\)|Thread|Socket" >> gpurun_out/gpu.txt
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
+tail -5 gpurun_out/pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke exit $?"; tail -2 gpurun_out/smoke.log
+timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
+timeout 600 python bench.py --impl reference --steps 6 --warmup 2 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; cat gpurun_out/bench_ref.json
+B="python bench.py --steps 3 --warmup 3 --no-cpu-baseline"
+timeout 600 $B > gpurun_out/plain.log 2>&1 &&
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv $B > gpurun_out/ncu1.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_update_level -s 16 -c 8 -o gpurun_out/prof_update_level $B > gpurun_out/ncu2.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_compact|k_sample_tracks" -s 4 -c 2 -o gpurun_out/prof_others $B > gpurun_out/ncu3.log 2>&1
+ls -la gpurun_out
