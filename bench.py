@@ -101,36 +101,39 @@ class ClockSampler:
 
 
 # ---- CPU legs (the only place outside tests/ that may touch oracle/) -------------------------------------------------------
-def cpu_reference_rate(threads, nodes_per_scene, frames, seed=4, warm=1):
-    """nodes/s of the reference's own Scene::Update + GetModelDisplayLists + CullModelDisplayLists on `threads` host threads,
-    one hg::Scene (one scene of the c4 batch: depth 8, 25 % animated) per thread. Returns (rate, kind, description)."""
+def cpu_reference_rate(threads, n_scenes, nodes_per_scene, frames, seed=4, warm=1):
+    """nodes/s of the reference's own Scene::Update + GetModelDisplayLists + CullModelDisplayLists on `threads` host threads.
+    The sample is `n_scenes` scenes of the c4 batch (depth 8, 25 % animated, one hg::Scene each — the reference path itself is
+    single-threaded, scene instances are independent), dealt round-robin to the threads; a frame = every scene stepped once.
+    Returns (rate, kind, description)."""
     from tests import oracle_lib
     from tests.oracle_lib import P
     ref = oracle_lib.load_ref()
     kind = "reference" if ref is not None else "port"
-    scenes, secs = [None] * threads, [0.0] * threads
+    threads = max(1, min(threads, n_scenes))
+    scenes = [None] * n_scenes
 
-    def build(i):
-        fs = scenegen.config_c4(seed=seed + i, n_scenes=1, nodes_per_scene=nodes_per_scene, animated_frac=0.25, n_keys=16)
-        fr = np.ascontiguousarray(hostmirror.scene_frusta(fs)[0])
-        if ref is not None:
-            from tests.scene_io import RefScene
-            scenes[i] = (RefScene(ref, fs), fr)
-        else:
-            from tests.port_scene import PortScene
-            scenes[i] = (PortScene(oracle_lib.load_port(), fs), fr)
+    def build(th):
+        for i in range(th, n_scenes, threads):
+            fs = scenegen.config_c4(seed=seed + i, n_scenes=1, nodes_per_scene=nodes_per_scene, animated_frac=0.25, n_keys=16)
+            fr = np.ascontiguousarray(hostmirror.scene_frusta(fs)[0])
+            if ref is not None:
+                from tests.scene_io import RefScene
+                scenes[i] = (RefScene(ref, fs), fr)
+            else:
+                from tests.port_scene import PortScene
+                scenes[i] = (PortScene(oracle_lib.load_port(), fs), fr)
 
-    def run(i, n_frames):
-        sc, fr = scenes[i]
-        t0 = time.perf_counter()
-        if ref is not None:
-            out = np.zeros(4)
-            ref.hgref_time_frames(sc.h, n_frames, FRAME_DT, P(fr), 0, P(out))
-        else:
-            for _ in range(n_frames):
-                sc.update(FRAME_DT)
-                sc.cull(0, fr)
-        secs[i] = time.perf_counter() - t0
+    def run(th, n_frames):
+        for _ in range(n_frames if ref is None else 1):
+            for i in range(th, n_scenes, threads):
+                sc, fr = scenes[i]
+                if ref is not None:  # scenes are independent: n_frames of one scene, then the next, is the same work as frame-major order
+                    out = np.zeros(4)
+                    ref.hgref_time_frames(sc.h, n_frames, FRAME_DT, P(fr), 0, P(out))
+                else:
+                    sc.update(FRAME_DT)
+                    sc.cull(0, fr)
 
     def par(fn, *a):
         th = [threading.Thread(target=fn, args=(i,) + a) for i in range(threads)]
@@ -144,27 +147,33 @@ def cpu_reference_rate(threads, nodes_per_scene, frames, seed=4, warm=1):
     wall = time.perf_counter() - t0
     for sc, _ in scenes:
         sc.close()
-    rate = threads * nodes_per_scene * frames / wall
-    return rate, kind, "%d thread(s) x 1 hg::Scene of %d nodes (one scene of the c4 batch) x %d frames, wall %.2f s" % (threads, nodes_per_scene, frames, wall)
+    rate = n_scenes * nodes_per_scene * frames / wall
+    return rate, kind, "%d hg::Scene(s) of %d nodes (scenes of the c4 batch) on %d thread(s) x %d frames, wall %.2f s" % (
+        n_scenes, nodes_per_scene, threads, frames, wall)
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
 
 def run_reference_arm(args, rank):
+    """The reference's own CPU implementation on all host threads, on the c4 batch itself: 16 hg::Scenes of 1M nodes (scaled by --scale),
+    one step = one frame of every scene."""
     if rank != 0:
         return
-    threads = os.cpu_count() or 1
-    try:
-        threads = len(os.sched_getaffinity(0))
-    except AttributeError:
-        pass
-    nodes = 250_000
-    per_step = threads * nodes
-    # every step = one frame of `threads` independent scenes
-    rate, kind, sample = cpu_reference_rate(threads, nodes, args.steps, warm=args.warmup)
+    threads = host_threads()
+    n_scenes = max(1, int(round(16 * args.scale)))
+    nodes = 1_000_000
+    rate, kind, sample = cpu_reference_rate(threads, n_scenes, nodes, args.steps, warm=args.warmup)
     v = rate / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": per_step / rate * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "c4 (bounded sample): " + sample},
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+            "ms_per_step": n_scenes * nodes / rate * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "c4: %d scenes x 1M nodes, depth 8, 25%% animated (Position track, 16 keys), Scene::Update + GetModelDisplayLists + "
+                                   "CullModelDisplayLists, 1 camera; CPU: " % n_scenes + sample, "scale": args.scale},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": min(threads, n_scenes), "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
@@ -173,7 +182,7 @@ def run_reference_arm(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--workload", default="c4", choices=["c4", "c2", "c5"])
@@ -206,14 +215,30 @@ def main():
     clocks = hostmirror.PlayClocks(fs)
     K, W = args.steps, max(args.warmup, 3)
 
-    class _DevWord:  # the context's visible-count word as a torch tensor (no copy): input of the NCCL gather
-        def __init__(self, ptr):
-            self.__cuda_array_interface__ = {"shape": (1,), "typestr": "<i4", "data": (int(ptr), False), "version": 2}
-
-    cnt_all = torch.zeros(world, dtype=torch.int32, device="cuda") if world > 1 else None
-    cnt_mine = [None]
+    # N>1: the path's only exchange — visible counts all-gathered, visible lists gathered to rank 0 with grouped
+    # send/recv sized from the counts. The tensors are views of the context's own device buffers (no staging copy).
+    gather = None
+    gathered = [0]
     if world > 1:
+        from harfang3d_b200 import sharding
         ctx.set_stream(torch.cuda.current_stream().cuda_stream)  # one stream for our kernels and the NCCL gather
+        n_ent0 = len(t["ent0_mtx_slot"])
+        ent_all = torch.zeros(world, dtype=torch.int64, device="cuda")
+        ent_all[rank] = n_ent0
+        dist.all_reduce(ent_all)
+        ent_all = ent_all.cpu().numpy()
+        entry_base = np.concatenate([[0], np.cumsum(ent_all)[:-1]])
+        if fs.instance_cameras is not None:  # c5: per-instance offsets of the compacted list
+            n_inst = len(fs.instance_cameras)
+            bounds = np.arange(world + 1, dtype=np.int64) * n_inst
+            off_view = sharding.device_view(ctx.device_ptr(5), n_inst + 1)
+        else:                                # c4: one camera per rank batch = one "instance" per rank
+            bounds = np.arange(world + 1, dtype=np.int64)
+            off_view = torch.zeros(2, dtype=torch.int32, device="cuda")
+            cnt_view = sharding.device_view(ctx.device_ptr(3), 1)
+        idx_view = sharding.device_view(ctx.device_ptr(2), max(n_ent0, 1))
+        gather_out = torch.empty(int(ent_all.sum()), dtype=torch.int32, device="cuda") if rank == 0 else None
+        gather = sharding.VisibilityGather(bounds, entry_base, dst=0)
 
     def barrier():
         if world > 1:
@@ -222,10 +247,11 @@ def main():
 
     def step_resident():
         ctx.update(clocks.step(FRAME_DT), fused_cull=True)
-        if world > 1:  # NCCL visibility gather: per-rank visible counts, enqueued behind the compaction without a host sync
-            if cnt_mine[0] is None:
-                cnt_mine[0] = torch.as_tensor(_DevWord(ctx.device_ptr(3)), device="cuda")
-            dist.all_gather_into_tensor(cnt_all, cnt_mine[0])
+        if gather is not None:
+            if fs.instance_cameras is None:
+                off_view[1:].copy_(cnt_view)
+            res = gather.gather(off_view, idx_view, out=gather_out)
+            gathered[0] = int(res.offsets[-1])
 
     # ---- warm-up, then the device-resident timed region -------------------------------------------------------------------
     for _ in range(W):
@@ -248,7 +274,6 @@ def main():
         step_resident()
     prof = ctx.get_profile(reset=True)
     ctx.set_profiling(False)
-    clocks_rec = sampler.stop()
     lvl_ms, lvl_n = prof["k_update_level"]
     per_step_ms = {k: v[0] / K for k, v in prof.items() if v[1]}
 
@@ -276,6 +301,8 @@ def main():
         barrier()
         h2d = (n_nodes * 36 if full else 0) + 8 * len(fs.plays)
         e2e[name] = [dt_s, h2d, 4 + 4 * len(vis)]
+
+    clocks_rec = sampler.stop()  # sampled from the start of the timed region to the end of the e2e legs (all under load)
 
     # ---- reduce over ranks --------------------------------------------------------------------------------------------------
     def rmax(x):
@@ -318,6 +345,8 @@ def main():
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "nodes_per_gpu": n_nodes, "display_entries_per_gpu": n_entries, "visible_fraction": f_vis,
                        "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (lvl_bytes_per_step / 1e9), "frame_graph": True,
+                       "exchange": None if world == 1 else "per step: visible counts all-gathered (NCCL), visible lists gathered to rank 0 "
+                                   "(grouped send/recv sized from the counts; %d entries gathered in the last step)" % gathered[0],
                        "scale": args.scale},
             "e2e": {"value": total_nodes * K / e2e["e2e"][0] / 1e6, "unit": UNIT, "h2d_bytes_per_step": e2e["e2e"][1], "d2h_bytes_per_step": e2e["e2e"][2],
                     "what": "every step: hgb_upload_trs of ALL nodes from pinned host + hgb_update + hgb_get_visible to pinned host"},
@@ -330,7 +359,7 @@ def main():
             "clocks": clocks_rec,
         }
         if not args.no_cpu_baseline and world == 1:
-            rate, kind, sample = cpu_reference_rate(1, 250_000, 12)
+            rate, kind, sample = cpu_reference_rate(1, 1, 1_000_000, 40)  # ~10 s of one host core
             line["cpu_baseline"] = {"value": rate / 1e6, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample}
         print(json.dumps(line), flush=True)
     ctx.close()
