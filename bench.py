@@ -57,8 +57,10 @@ def workload(name, rank, scale=1.0):
         fs = scenegen.config_c2(seed=2 + 1000 * rank, n_nodes=max(1000, int(1_000_000 * scale)))
         return fs, "c2: %d-node static scene, depth 8, fused update+cull" % fs.n
     if name == "c5":
-        fs = scenegen.config_c5(seed=5 + 1000 * rank, n_instances=max(1, int(8192 * scale)))
-        return fs, "c5: %d instances x 2048 nodes, depth 6, one camera per instance" % (fs.n // 2048)
+        # per-rank share of BASELINE configs[4] at 2 GPUs (8192 instances x 2048 nodes = 16.8M slots exceed the reference's 2^24-1
+        # vector_list capacity for ONE scene/context, foundation/vector_list.h:40)
+        fs = scenegen.config_c5(seed=5 + 1000 * rank, n_instances=max(1, int(4096 * scale)))
+        return fs, "c5: %d instances x 2048 nodes per GPU, depth 6, one camera per instance" % (fs.n // 2048)
     raise SystemExit("unknown workload %s" % name)
 
 
@@ -222,6 +224,8 @@ def main():
     if world > 1:
         from harfang3d_b200 import sharding
         ctx.set_stream(torch.cuda.current_stream().cuda_stream)  # one stream for our kernels and the NCCL gather
+        ctx.update(clocks.step(0), fused_cull=True)              # first frame: builds the device tables the views below point into
+        ctx.sync()
         n_ent0 = len(t["ent0_mtx_slot"])
         ent_all = torch.zeros(world, dtype=torch.int64, device="cuda")
         ent_all[rank] = n_ent0
@@ -231,7 +235,9 @@ def main():
         if fs.instance_cameras is not None:  # c5: per-instance offsets of the compacted list
             n_inst = len(fs.instance_cameras)
             bounds = np.arange(world + 1, dtype=np.int64) * n_inst
-            off_view = sharding.device_view(ctx.device_ptr(5), n_inst + 1)
+            rank_view = sharding.device_view(ctx.device_ptr(5), n_inst)  # exclusive ranks of the instances' first entries
+            off_view = torch.zeros(n_inst + 1, dtype=torch.int32, device="cuda")
+            cnt_view = sharding.device_view(ctx.device_ptr(3), 1)
         else:                                # c4: one camera per rank batch = one "instance" per rank
             bounds = np.arange(world + 1, dtype=np.int64)
             off_view = torch.zeros(2, dtype=torch.int32, device="cuda")
@@ -248,10 +254,11 @@ def main():
     def step_resident():
         ctx.update(clocks.step(FRAME_DT), fused_cull=True)
         if gather is not None:
-            if fs.instance_cameras is None:
-                off_view[1:].copy_(cnt_view)
+            if fs.instance_cameras is not None:
+                off_view[:-1].copy_(rank_view)
+            off_view[-1:].copy_(cnt_view)
             res = gather.gather(off_view, idx_view, out=gather_out)
-            gathered[0] = int(res.offsets[-1])
+            gathered[0] = res.total
 
     # ---- warm-up, then the device-resident timed region -------------------------------------------------------------------
     for _ in range(W):

@@ -35,13 +35,27 @@ def device_view(ptr, n, dtype=torch.int32, device=None):
 
 
 class GatherResult:
-    """counts[i] / offsets[i] of global instance i and the concatenated visible entry indices (None on ranks that do not receive)."""
+    """Result of one gather. counts_padded: (world, pad) int32 tensor on the gather's device, row r = the visible counts of rank r's
+    instances (zero padded); rank_totals: visible entries per rank (host); idx: concatenated visible entry indices in instance order
+    (None on ranks that do not receive). counts / offsets (per GLOBAL instance) are derived on demand — the per-frame path never
+    touches per-instance data on the host."""
 
-    def __init__(self, counts, offsets, idx, rank_totals):
-        self.counts, self.offsets, self.idx, self.rank_totals = counts, offsets, idx, rank_totals
+    def __init__(self, counts_padded, sizes, idx, rank_totals):
+        self.counts_padded, self.sizes, self.idx, self.rank_totals = counts_padded, sizes, idx, rank_totals
+        self.total = int(rank_totals.sum())
+
+    @property
+    def counts(self):
+        c = self.counts_padded.cpu().numpy().astype(np.int64)
+        return np.concatenate([c[r, : self.sizes[r]] for r in range(len(self.sizes))]) if len(self.sizes) else np.zeros(0, np.int64)
+
+    @property
+    def offsets(self):
+        return np.concatenate([[0], np.cumsum(self.counts)])
 
     def instance(self, i):
-        return self.idx[int(self.offsets[i]): int(self.offsets[i + 1])]
+        off = self.offsets
+        return self.idx[int(off[i]): int(off[i + 1])]
 
 
 class VisibilityGather:
@@ -62,7 +76,7 @@ class VisibilityGather:
         self.pad = int(self.sizes.max()) if self.world else 0
         self.entry_base = [int(x) for x in entry_base]
         self.dst = dst
-        self._cnt_pad = self._cnt_all = None
+        self._cnt_pad = self._cnt_all = self._tot_all = None
 
     # step 1 -------------------------------------------------------------------------------------------------------------
     def gather_counts(self, local_counts):
@@ -80,13 +94,13 @@ class VisibilityGather:
     def gather(self, local_offsets, local_idx, out=None):
         """local_offsets: int32 tensor of n_local+1 exclusive offsets into local_idx (hgb_get_instance_offsets layout);
         local_idx: int32 tensor with the surviving local entry indices (only the first local_offsets[-1] are read).
-        out: optional preallocated int32 tensor on the receiving rank(s). Reads the counts back to the host once (the sizes of the
-        variable-length transfers)."""
+        out: optional preallocated int32 tensor on the receiving rank(s). One host read per call: the `world` per-rank totals that size
+        the variable-length transfers; the per-instance counts stay on the device."""
         counts_dev = self.gather_counts(local_offsets[1:] - local_offsets[:-1])
-        counts_h = counts_dev.cpu().numpy().astype(np.int64)  # the one host read: world x pad words
-        counts = np.concatenate([counts_h[r, : self.sizes[r]] for r in range(self.world)]) if self.world else np.zeros(0, np.int64)
-        rank_totals = np.array([counts_h[r, : self.sizes[r]].sum() for r in range(self.world)], np.int64)
-        offsets = np.concatenate([[0], np.cumsum(counts)])
+        if self._tot_all is None or self._tot_all.device != local_offsets.device:
+            self._tot_all = torch.zeros(self.world, dtype=torch.int32, device=local_offsets.device)
+        dist.all_gather_into_tensor(self._tot_all, local_offsets[-1:].contiguous(), group=self.group)
+        rank_totals = self._tot_all.cpu().numpy().astype(np.int64)  # the one host read: world words
         rank_off = np.concatenate([[0], np.cumsum(rank_totals)])
         total = int(rank_off[-1])
         mine = int(rank_totals[self.rank])
@@ -112,7 +126,7 @@ class VisibilityGather:
         if ops:
             for w in dist.batch_isend_irecv(ops):
                 w.wait()
-        return GatherResult(counts, offsets, res, rank_totals)
+        return GatherResult(counts_dev, self.sizes, res, rank_totals)
 
     def _global(self, r):
         return dist.get_global_rank(self.group, r) if self.group is not None else r
