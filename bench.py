@@ -191,6 +191,10 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (debug only; the reported config says so)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--lookahead", type=int, default=0, help="A/B switch: L2 prefetch distance in positions (0 = default, -1 = off)")
+    ap.add_argument("--tma-level", action="store_true", help="A/B switch: persistent TMA-staged level kernel instead of one thread per node (LDG rows)")
+    ap.add_argument("--merge-small", action="store_true", help="A/B switch: runs of small top levels in one cooperative launch")
+    ap.add_argument("--slice-nodes", type=int, default=0, help="A/B switch: slice size of big levels under the overlapped sampler (0 = no slicing)")
+    ap.add_argument("--overlap", action="store_true", help="A/B switch: sample tracks by target level on a second stream, overlapped with the level kernels")
     ap.add_argument("--row-store", action="store_true", help="A/B switch: per-thread world row stores instead of the transposed warp store")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -211,7 +215,7 @@ def main():
 
     fs, desc = workload(args.workload, rank, args.scale)
     n_nodes = fs.n
-    ctx = harfang3d_b200.Context(local_rank, row_store=args.row_store, lookahead=args.lookahead)
+    ctx = harfang3d_b200.Context(local_rank, row_store=args.row_store, lookahead=args.lookahead, tma_level=args.tma_level, merge_small=args.merge_small, overlap_sampler=args.overlap, slice_nodes=args.slice_nodes)
     t = hostmirror.upload(ctx, fs)
     n_entries = len(t["ent0_mtx_slot"]) + len(t["ent1_mtx_slot"])
     clocks = hostmirror.PlayClocks(fs)

@@ -12,7 +12,7 @@ ENTRY_DISABLED = 0x01
 KIND_OPAQUE, KIND_TRANSPARENT = 0, 1
 
 
-KERNEL_CLASSES = ("k_sample_tracks", "k_update_level", "k_compact", "k_segment_ranks", "k_cull_flags", "k_bone_matrices")
+KERNEL_CLASSES = ("k_sample_tracks", "k_update_level", "k_compact", "k_segment_ranks", "k_cull_flags", "k_bone_matrices", "k_sort_keys")
 
 
 class HgbError(RuntimeError):
@@ -55,6 +55,8 @@ SIGNATURES = {
     "hgb_cull": (_i, [_p]),
     "hgb_cull_list": (_i, [_p, _u32, _p, _p, _u32, _p, _p, _p, _p]),
     "hgb_bone_matrices": (_i, [_p, _i]),
+    "hgb_sort_keys": (_i, [_p, _i, _u32, _p]),
+    "hgb_get_sort_keys": (_i, [_p, _i, _u32, _p, _u32, _p]),
     "hgb_get_worlds": (_i, [_p, _u32, _u32, _p, _i]),
     "hgb_get_trs": (_i, [_p, _u32, _u32, _p]),
     "hgb_get_visible_count": (_i, [_p, _i, _u32, _p]),
@@ -102,11 +104,11 @@ def _ptr(a, dtype, what):
 class Context:
     """One hgb_ctx = one hg::Scene (or one batch of scene instances)."""
 
-    def __init__(self, device=0, use_graph=True, row_store=False, lookahead=0):
+    def __init__(self, device=0, use_graph=True, row_store=False, lookahead=0, tma_level=False, merge_small=False, overlap_sampler=False, slice_nodes=0):
         """row_store=True: world rows are stored per thread (3 x 16 B at a 48-byte stride) instead of through the shared-memory
         transpose — an A/B switch for profiling (hgb_options.reserved[0])"""
         self._L = lib()
-        opt = (C.c_int * 8)(1 if use_graph else 0, 1 if row_store else 0, lookahead, 0, 0, 0, 0, 0)  # lookahead: 0 default, -1 off, n positions
+        opt = (C.c_int * 8)(1 if use_graph else 0, 1 if row_store else 0, lookahead, 1 if tma_level else 0, 0, 1 if merge_small else 0, 1 if overlap_sampler else 0, slice_nodes)  # lookahead: 0 default, -1 off, n positions
         self._h = self._L.hgb_create(device, C.cast(opt, C.c_void_p))
         if not self._h:
             raise HgbError(self._L.hgb_last_error().decode())
@@ -198,6 +200,14 @@ class Context:
         self._ck(self._L.hgb_cull_list(self._h, len(mtx_slot), _ptr(mtx_slot, np.uint32, "mtx_slot"), _ptr(bounds_idx, np.uint32, "bounds_idx"),
                                        bounds6.shape[0], _ptr(bounds6, np.float32, "bounds6"), _ptr(f, np.float32, "frustum24"),
                                        _ptr(out, np.uint32, "out"), C.byref(n)))
+        return out[: n.value]
+
+    def sort_keys(self, kind, view, view_mat12):
+        """ComputeModelDisplayListSortKeys for the survivors of list (kind, view) -> uint32 keys in visible-list order"""
+        m = np.ascontiguousarray(view_mat12, np.float32).reshape(12)
+        self._ck(self._L.hgb_sort_keys(self._h, kind, view, _ptr(m, np.float32, "view_mat12")))
+        out, n = np.empty(max(self.n_entries[kind], 1), np.uint32), C.c_uint32(0)
+        self._ck(self._L.hgb_get_sort_keys(self._h, kind, view, _ptr(out, np.uint32, "out"), len(out), C.byref(n)))
         return out[: n.value]
 
     def bone_matrices(self, with_previous=False):

@@ -3,6 +3,7 @@
 // every entry point that computes needs the CUDA device the context was created on.
 #include "../../include/hgb200.h"
 #include "hgb_kernels2.cuh"
+#include "hgb_kernels_tma.cuh"
 
 #include <algorithm>
 #include <cstdarg>
@@ -102,6 +103,7 @@ struct EntryTable {
 	std::vector<uint16_t> view;
 	DBuf mtx_pos, meta, view_d, vis; // per entry (entry order)
 	DBuf out[kMaxViews];             // surviving indices per view
+	DBuf keys[kMaxViews];            // sort keys of the survivors (hgb_sort_keys)
 	DBuf counts;                     // kMaxViews uint32
 	DBuf ticket, status;             // compaction scratch (per view slices)
 	uint32_t n_tiles = 0;
@@ -128,6 +130,16 @@ struct hgb_ctx {
 	DBuf tiles, world[2], preset, pos_of_slot_d; // tiles: node tiles (TRS rows, parent, first entry), see hgb_kernels.cuh
 	uint32_t n_tiles = 0;
 	bool transpose_store = true;
+	bool tma_level = false;   // A/B switch: persistent TMA-staged level kernel instead of one thread per node with LDG rows (measured slower: r01c)
+	bool merge_small = false; // runs of small levels in one cooperative launch (k_update_levels_small); opt-in: no gain inside a CUDA graph
+	bool overlap_sampler = false; // opt-in: sample tracks by target level on a second stream, overlapped with the level kernels (measured slower: r01c)
+	cudaStream_t stream2 = nullptr;
+	std::vector<cudaEvent_t> ev_chunk; // [0] fork, [1] join, [2+g] chunk of level group g
+	std::vector<uint32_t> trk_pos_h;   // target position of every round-0 track, ascending (chunk boundaries of the overlapped sampler)
+	uint32_t slice_nodes = 0;          // >0: with the overlapped sampler, big levels are cut into slices of this many positions (multiple of 256)
+	uint32_t small_level_max = 0, small_ctas = 0; // a level is small when it fits one grid-stride pass of the co-resident grid
+	DBuf level_barrier;
+	uint32_t persistent_ctas = 148 * 6; // resident CTAs of the device for the persistent level kernel
 	uint32_t lookahead = 0; // positions (see SceneDev::lookahead)
 	int cur = 0; // world[cur] = current frame
 	bool preset_pending = false, preset_dirty = false;
@@ -135,6 +147,7 @@ struct hgb_ctx {
 	uint32_t n_preset = 0;
 
 	DBuf bounds;
+	std::vector<float> bounds_stage; // interleaved host copy during an upload
 	uint32_t n_bounds = 0;
 	EntryTable ent[2];
 	DBuf ent_off, pent, pos_view; // overflow CSR of nodes with several entries; per-position instance id
@@ -152,6 +165,8 @@ struct hgb_ctx {
 
 	// animation
 	DBuf keys, cursor, tracks_d, play_t_d; // keys: 32-byte records, vec3 keys then quaternion keys
+	DBuf key_rec;                          // 128-byte interval records, one per key (k_build_key_records)
+	bool records_dirty = true;
 	uint32_t n_v3_keys = 0, n_q_keys = 0;
 	DBuf anim_val, bind_pos_d, bind_group_d; // track-driven (node, pos|rot|scale) triples: values + where they are bound
 	uint32_t n_bound = 0;                    // triples currently bound on the device (tiles hold slots, not values)
@@ -248,10 +263,26 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 	{
 		cudaDeviceProp prop;
 		if (cudaGetDeviceProperties(&prop, device) == cudaSuccess)
+		{
 			c->lookahead = uint32_t(prop.multiProcessorCount) * 6u * 256u; // one wave of resident CTAs (6 x 256 threads per SM)
+			c->persistent_ctas = uint32_t(prop.multiProcessorCount) * 6u;
+			int per_sm = 0, coop = 0;
+			cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
+			if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_update_levels_small<true, false>, 256, 0) == cudaSuccess && per_sm > 0) {
+				int per_sm2 = per_sm;
+				cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, k_update_levels_small<true, true>, 256, 0);
+				c->small_ctas = uint32_t(prop.multiProcessorCount) * uint32_t(std::min(per_sm, per_sm2));
+				c->small_level_max = c->small_ctas * 256u;
+			}
+		}
 		if (opt && opt->lookahead != 0)
 			c->lookahead = opt->lookahead < 0 ? 0u : uint32_t(opt->lookahead); // A/B switch: -1 = off, n = positions
 	}
+	c->tma_level = opt ? opt->tma_level != 0 : false;
+	c->merge_small = opt ? opt->merge_small != 0 : false;
+	c->overlap_sampler = opt ? opt->overlap_sampler != 0 : false;
+	if (opt && opt->slice_nodes > 0)
+		c->slice_nodes = (uint32_t(opt->slice_nodes) + 255u) & ~255u;
 	c->transpose_store = opt ? opt->row_store == 0 : true; // reserved[0] = 1: per-thread 48-byte row stores (A/B switch for profiling)
 	if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
 		cudaEventCreate(&c->ev1) != cudaSuccess) {
@@ -260,6 +291,21 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		return nullptr;
 	}
 	c->stream = c->own_stream;
+	if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) {
+		fail("hgb_create: stream creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+		delete c;
+		return nullptr;
+	}
+	for (int i = 0; i < 96; ++i) { // fork/join/chunk events of the overlapped sampler, created up front (never during graph capture)
+		cudaEvent_t e = nullptr;
+		if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess)
+			c->ev_chunk.push_back(e);
+	}
+	if (c->level_barrier.reserve(256) != cudaSuccess) { // grid-barrier word of k_update_levels_small (allocated here: never during graph capture)
+		fail("hgb_create: cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError()));
+		delete c;
+		return nullptr;
+	}
 	c->views.n_views = 0;
 	if (c->view_planes.reserve(kMaxViews * 96) != cudaSuccess) {
 		fail("hgb_create: out of device memory");
@@ -281,7 +327,7 @@ void hgb_destroy(hgb_ctx *c) {
 				cudaGraphExecDestroy(g);
 	DBuf *bufs[] = {&c->tiles, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
 		&c->pent, &c->pos_view, &c->inst_planes, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
-		&c->bone_out[1], &c->keys, &c->cursor, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes};
+		&c->bone_out[1], &c->keys, &c->cursor, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes, &c->level_barrier, &c->key_rec};
 	for (DBuf *b : bufs)
 		b->release();
 	for (auto &t : c->ent) {
@@ -290,6 +336,8 @@ void hgb_destroy(hgb_ctx *c) {
 			b->release();
 		for (auto &o : t.out)
 			o.release();
+		for (auto &o : t.keys)
+			o.release();
 	}
 	for (cudaEvent_t e : c->prof.ev)
 		cudaEventDestroy(e);
@@ -297,6 +345,10 @@ void hgb_destroy(hgb_ctx *c) {
 	c->play_t_h.release();
 	cudaEventDestroy(c->ev0);
 	cudaEventDestroy(c->ev1);
+	for (cudaEvent_t e : c->ev_chunk)
+		cudaEventDestroy(e);
+	if (c->stream2)
+		cudaStreamDestroy(c->stream2);
 	cudaStreamDestroy(c->own_stream);
 	delete c;
 }

@@ -54,44 +54,161 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k) {
 	return 0;
 }
 
-static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint64_t *n_k) {
-	// animation sampling: one launch per write round (normally one)
-	if (c->n_tracks && c->n_play) {
-		AnimDev a{};
-		a.tracks = c->tracks_d.as<Track>();
-		a.play_t = c->play_t_d.as<int64_t>();
-		a.keys = c->keys.as<uint4>();
-		a.quat_base = c->n_v3_keys;
-		a.cursor = c->cursor.as<uint32_t>();
-		a.anim_val = c->anim_val.as<float4>();
-		for (size_t r = 0; r + 1 < c->round_off.size(); ++r) {
-			const uint32_t first = c->round_off[r], cnt = c->round_off[r + 1] - first;
-			if (!cnt)
-				continue;
-			prof_begin(c, HGB_K_SAMPLE_TRACKS);
-			k_sample_tracks<<<grid_for(cnt), 256, 0, c->stream>>>(a, first, cnt);
-			prof_end(c);
-			++*n_k;
-		}
-	}
-	// world matrices, level by level (+ fused visibility)
-	const SceneDev s = scene_dev(c, with_preset);
-	const bool do_fused = fused && (c->ent[0].n || c->ent[1].n);
-	for (size_t d = 0; d + 1 < c->level_off.size(); ++d) {
-		const uint32_t b = c->level_off[d], e = c->level_off[d + 1];
-		if (e == b)
-			continue;
+static void launch_level(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t b, uint32_t e) {
+	if (c->tma_level) { // persistent warps, TMA-staged tiles (hgb_kernels_tma.cuh)
+		const uint32_t n_lt = ((e - 1u) >> 5) - (b >> 5) + 1u;
+		const dim3 g(std::min((n_lt + kTmaWarps - 1u) / kTmaWarps, c->persistent_ctas));
+		if (!do_fused)
+			k_update_level_tma<false, false><<<g, kTmaWarps * 32, 0, c->stream>>>(s, c->views, b, e);
+		else if (c->instance_mode)
+			k_update_level_tma<true, true><<<g, kTmaWarps * 32, 0, c->stream>>>(s, c->views, b, e);
+		else
+			k_update_level_tma<true, false><<<g, kTmaWarps * 32, 0, c->stream>>>(s, c->views, b, e);
+	} else {
 		const dim3 g = grid_for(e - b);
-		prof_begin(c, HGB_K_UPDATE_LEVEL);
 		if (!do_fused)
 			k_update_level<false, false><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
 		else if (c->instance_mode)
 			k_update_level<true, true><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
 		else
 			k_update_level<true, false><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
+	}
+}
+
+static int launch_small_run(hgb_ctx *c, const SceneDev &s, bool do_fused, size_t d, size_t run, uint32_t widest) {
+	SmallLevels lv{};
+	lv.n = uint32_t(run);
+	for (size_t k = 0; k <= run; ++k)
+		lv.off[k] = c->level_off[d + k];
+	CK(cudaMemsetAsync(c->level_barrier.p, 0, 4, c->stream));
+	cudaLaunchConfig_t cfg{};
+	cfg.gridDim = dim3(std::min((widest + 255u) / 256u, c->small_ctas));
+	cfg.blockDim = dim3(256);
+	cfg.stream = c->stream;
+	cudaLaunchAttribute at[1];
+	at[0].id = cudaLaunchAttributeCooperative;
+	at[0].val.cooperative = 1;
+	cfg.attrs = at;
+	cfg.numAttrs = 1;
+	uint32_t *bar = c->level_barrier.as<uint32_t>();
+	if (!do_fused)
+		CK(cudaLaunchKernelEx(&cfg, k_update_levels_small<false, false>, s, c->views, lv, bar));
+	else if (c->instance_mode)
+		CK(cudaLaunchKernelEx(&cfg, k_update_levels_small<true, true>, s, c->views, lv, bar));
+	else
+		CK(cudaLaunchKernelEx(&cfg, k_update_levels_small<true, false>, s, c->views, lv, bar));
+	return 0;
+}
+
+// One frame. Level groups (a level, or a run of small levels) go out in order on the context's stream. The track sampler is HBM-bound
+// and issue-light, the level kernels issue-heavy: with `overlap_sampler` the tracks are sampled in chunks by TARGET LEVEL on a second
+// stream, each level group waiting only for its own chunk — so the chunk of the (huge) last level streams its keys while the upper
+// levels compute. Tracks are sorted by target position (prepare_tables), so a chunk is a contiguous track range.
+static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint64_t *n_k) {
+	const SceneDev s = scene_dev(c, with_preset);
+	const bool do_fused = fused && (c->ent[0].n || c->ent[1].n);
+	const size_t n_levels = c->level_off.size() - 1;
+	const bool has_anim = c->n_tracks && c->n_play;
+	AnimDev a{};
+	if (has_anim) {
+		a.tracks = c->tracks_d.as<Track>();
+		a.play_t = c->play_t_d.as<int64_t>();
+		a.keys = c->keys.as<uint4>();
+		a.rec = c->key_rec.as<uint4>();
+		a.quat_base = c->n_v3_keys;
+		a.cursor = c->cursor.as<uint32_t>();
+		a.anim_val = c->anim_val.as<float4>();
+	}
+	// level groups: a level, a run of small levels, or — with the overlapped sampler — a slice of a big level, so that the sampler chunk
+	// of slice k+1 streams its keys while slice k computes (the level kernel is issue-bound and leaves HBM headroom, the sampler is
+	// HBM-bound and leaves issue slots)
+	struct Group {
+		size_t d0, d1;   // levels [d0, d1)
+		uint32_t b, e;   // positions (a slice when d1 == d0 + 1)
+		uint32_t widest;
+	};
+	const bool want_overlap = has_anim && c->overlap_sampler && !c->prof.on && c->round_off.size() == 2 && !c->trk_pos_h.empty();
+	std::vector<Group> groups;
+	for (size_t d = 0; d < n_levels;) {
+		if (c->level_off[d + 1] == c->level_off[d]) {
+			++d;
+			continue;
+		}
+		size_t run = 0;
+		uint32_t widest = 0;
+		if (c->merge_small) {
+			while (d + run < n_levels && run < size_t(kMaxSmallRun)) {
+				const uint32_t sz = c->level_off[d + run + 1] - c->level_off[d + run];
+				if (sz == 0 || sz > c->small_level_max)
+					break;
+				widest = std::max(widest, sz);
+				++run;
+			}
+		}
+		if (run >= 2) {
+			groups.push_back({d, d + run, c->level_off[d], c->level_off[d + run], widest});
+			d += run;
+			continue;
+		}
+		const uint32_t lb = c->level_off[d], le = c->level_off[d + 1];
+		const uint32_t slice = want_overlap && c->slice_nodes ? c->slice_nodes : 0xffffff00u;
+		for (uint32_t p0 = lb; p0 < le;) {
+			const uint32_t p1 = (le - p0 <= slice + slice / 2) ? le : p0 + slice; // slice is a multiple of 256: warps keep their tile alignment
+			groups.push_back({d, d + 1, p0, p1, 0});
+			p0 = p1;
+		}
+		++d;
+	}
+
+	while (want_overlap && c->ev_chunk.size() < groups.size() + 2) { // 96 exist from hgb_create; more only for very deep or very large scenes
+		cudaEvent_t e = nullptr;
+		CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+		c->ev_chunk.push_back(e);
+	}
+	const bool overlap = want_overlap;
+	std::vector<char> has_chunk(groups.size(), 0);
+	if (has_anim && !overlap) { // sequential: one launch per write round (normally one)
+		for (size_t r = 0; r + 1 < c->round_off.size(); ++r) {
+			const uint32_t first = c->round_off[r], cnt = c->round_off[r + 1] - first;
+			if (!cnt)
+				continue;
+			prof_begin(c, HGB_K_SAMPLE_TRACKS);
+			k_sample_tracks<<<grid_for(cnt, kSampleWarps * 32), kSampleWarps * 32, 0, c->stream>>>(a, first, cnt);
+			prof_end(c);
+			++*n_k;
+		}
+	} else if (overlap) {
+		CK(cudaEventRecord(c->ev_chunk[0], c->stream)); // fork (also orders the chunks behind this frame's play-clock upload)
+		CK(cudaStreamWaitEvent(c->stream2, c->ev_chunk[0], 0));
+		for (size_t g = 0; g < groups.size(); ++g) {
+			// tracks are sorted by target position: the chunk of positions [b, e) is a contiguous track range
+			const uint32_t lo = uint32_t(std::lower_bound(c->trk_pos_h.begin(), c->trk_pos_h.end(), groups[g].b) - c->trk_pos_h.begin());
+			const uint32_t hi = uint32_t(std::lower_bound(c->trk_pos_h.begin(), c->trk_pos_h.end(), groups[g].e) - c->trk_pos_h.begin());
+			if (hi > lo) {
+				k_sample_tracks<<<grid_for(hi - lo, kSampleWarps * 32), kSampleWarps * 32, 0, c->stream2>>>(a, lo, hi - lo);
+				++*n_k;
+				CK(cudaEventRecord(c->ev_chunk[g + 2], c->stream2));
+				has_chunk[g] = 1;
+			}
+		}
+		CK(cudaEventRecord(c->ev_chunk[1], c->stream2)); // join point
+	}
+
+	for (size_t g = 0; g < groups.size(); ++g) {
+		if (has_chunk[g])
+			CK(cudaStreamWaitEvent(c->stream, c->ev_chunk[g + 2], 0));
+		prof_begin(c, HGB_K_UPDATE_LEVEL);
+		if (groups[g].d1 - groups[g].d0 >= 2) {
+			if (launch_small_run(c, s, do_fused, groups[g].d0, groups[g].d1 - groups[g].d0, groups[g].widest))
+				return 1;
+		} else {
+			launch_level(c, s, do_fused, groups[g].b, groups[g].e);
+		}
 		prof_end(c);
 		++*n_k;
 	}
+	if (overlap)
+		CK(cudaStreamWaitEvent(c->stream, c->ev_chunk[1], 0));
 	CK(cudaGetLastError());
 	if (do_fused)
 		return enqueue_compaction(c, n_k);
@@ -231,8 +348,9 @@ int hgb_cull_list(hgb_ctx *c, uint32_t n, const uint32_t *mtx_slot, const uint32
 	const uint32_t n_tiles = (n + kCompactTile - 1) / kCompactTile;
 	float cond[24];
 	precondition_planes(frustum24, 6, cond);
+	interleave_bounds(bounds6, n_bounds, c->bounds_stage); // stays alive until the stream synchronisation below
 	if (upload(c, c->adhoc_pos, pos.data(), size_t(n) * 4) || upload(c, c->adhoc_meta, bounds_idx, size_t(n) * 4) ||
-		upload(c, c->adhoc_bounds, bounds6, size_t(n_bounds) * 24) || upload(c, c->adhoc_planes, cond, 96))
+		upload(c, c->adhoc_bounds, c->bounds_stage.data(), size_t(n_bounds) * 24) || upload(c, c->adhoc_planes, cond, 96))
 		return 1;
 	CK(c->adhoc_vis.reserve(size_t(n_tiles + 1) * kCompactTile));
 	CK(c->adhoc_out.reserve(size_t(n) * 4));
@@ -298,6 +416,55 @@ int hgb_bone_matrices(hgb_ctx *c, int with_previous) {
 	prof_end(c);
 	++c->launches;
 	CK(cudaGetLastError());
+	return 0;
+}
+
+// ComputeModelDisplayListSortKeys for the visible list (kind, view) of the last cull
+int hgb_sort_keys(hgb_ctx *c, int kind, uint32_t view, const float *view_mat12) {
+	if (!c)
+		return fail("null context");
+	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews) || !view_mat12)
+		return fail("hgb_sort_keys: bad kind/view/matrix");
+	EntryTable &t = c->ent[kind];
+	if (!t.n)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	if (prepare_tables(c))
+		return 1;
+	if (!t.out[view].p)
+		return fail("hgb_sort_keys: list (kind %d, view %u) has not been culled", kind, view);
+	CK(t.keys[view].reserve(size_t(t.n) * 4));
+	SortKeyDev d{};
+	d.visible = t.out[view].as<uint32_t>();
+	d.count = t.counts.as<uint32_t>() + view;
+	d.mtx_pos = t.mtx_pos.as<uint32_t>();
+	d.meta = t.meta.as<uint32_t>();
+	d.world = c->world[c->cur].as<float>();
+	d.bounds6 = c->bounds.as<float>();
+	memcpy(d.view, view_mat12, 48);
+	d.keys = t.keys[view].as<uint32_t>();
+	prof_begin(c, HGB_K_SORT_KEYS);
+	k_sort_keys<<<grid_for(t.n), 256, 0, c->stream>>>(d, t.n);
+	prof_end(c);
+	++c->launches;
+	CK(cudaGetLastError());
+	return 0;
+}
+
+int hgb_get_sort_keys(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_keys, uint32_t capacity, uint32_t *out_count) {
+	uint32_t n = 0;
+	if (hgb_get_visible_count(c, kind, view, &n))
+		return 1;
+	if (out_count)
+		*out_count = n;
+	if (n > capacity)
+		return fail("hgb_get_sort_keys: %u keys but capacity %u", n, capacity);
+	if (n) {
+		if (!c->ent[kind].keys[view].p)
+			return fail("hgb_get_sort_keys: hgb_sort_keys has not run for (kind %d, view %u)", kind, view);
+		CK(cudaMemcpyAsync(out_keys, c->ent[kind].keys[view].p, size_t(n) * 4, cudaMemcpyDeviceToHost, c->stream));
+		CK(cudaStreamSynchronize(c->stream));
+	}
 	return 0;
 }
 

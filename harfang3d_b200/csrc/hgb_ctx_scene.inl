@@ -18,6 +18,16 @@ static void precondition_planes(const float *in, uint32_t n_planes, float *out) 
 	}
 }
 
+// hg::MinMax {mn.xyz, mx.xyz} (foundation/minmax.h:13-18) -> device form {mn.x, mx.x, mn.y, mx.y, mn.z, mx.z} (see minmax_transform)
+static void interleave_bounds(const float *in, size_t n, std::vector<float> &out) {
+	out.resize(std::max<size_t>(n, 1) * 6);
+	for (size_t i = 0; i < n; ++i)
+		for (int k = 0; k < 3; ++k) {
+			out[i * 6 + 2 * k] = in[i * 6 + k];
+			out[i * 6 + 2 * k + 1] = in[i * 6 + 3 + k];
+		}
+}
+
 static inline dim3 grid_for(uint32_t n, uint32_t block = 256) { return dim3((n + block - 1) / block); }
 
 extern "C" {
@@ -192,7 +202,8 @@ int hgb_set_bounds(hgb_ctx *c, uint32_t n, const float *minmax6) {
 	if (n >= (1u << 24))
 		return fail("hgb_set_bounds: too many bounds");
 	CK(cudaSetDevice(c->device));
-	if (upload(c, c->bounds, minmax6, size_t(n) * 24))
+	interleave_bounds(minmax6, n, c->bounds_stage);
+	if (upload(c, c->bounds, c->bounds_stage.data(), size_t(n) * 24))
 		return 1;
 	CK(cudaStreamSynchronize(c->stream));
 	c->n_bounds = n;
@@ -264,7 +275,7 @@ int hgb_set_anim_keys(hgb_ctx *c, uint32_t n3, const int64_t *v3_t, const float 
 	CK(cudaSetDevice(c->device));
 	// one 32-byte record per key: {t (8), v.x, v.y | v.z, tension or v.w, bias, 0}; quaternion keys after the vec3 keys
 	const size_t total = size_t(n3) + nq;
-	CK(c->staging.reserve(std::max<size_t>(total, 1) * 32));
+	CK(c->staging.reserve((total + 4) * 32));
 	uint32_t *rec = c->staging.as<uint32_t>();
 	auto f2u = [](float f) { uint32_t u; memcpy(&u, &f, 4); return u; };
 	for (size_t i = 0; i < n3; ++i) {
@@ -279,10 +290,14 @@ int hgb_set_anim_keys(hgb_ctx *c, uint32_t n3, const int64_t *v3_t, const float 
 		r[2] = f2u(q_val4[i * 4 + 0]), r[3] = f2u(q_val4[i * 4 + 1]), r[4] = f2u(q_val4[i * 4 + 2]), r[5] = f2u(q_val4[i * 4 + 3]);
 		r[6] = r[7] = 0;
 	}
-	if (upload(c, c->keys, rec, total * 32))
+	// 4 keys of zero padding after the pool: k_sample_tracks reads fixed 4-key windows (128 contiguous bytes) starting at any key
+	memset(rec + total * 8, 0, 4 * 32);
+	if (upload(c, c->keys, rec, (total + 4) * 32))
 		return 1;
 	c->n_v3_keys = n3;
 	c->n_q_keys = nq;
+	c->records_dirty = true;
+	c->entries_dirty = true; // prepare_tables rebuilds the interval records
 	CK(cudaStreamSynchronize(c->stream));
 	invalidate_graph(c);
 	return 0;
@@ -331,6 +346,18 @@ int hgb_set_tracks(hgb_ctx *c, uint32_t n, const hgb_track *tracks, uint32_t n_p
 			return fail("hgb_set_tracks: track %u reads keys [%u,%u) outside its pool of %llu (call hgb_set_anim_keys first)", i, tracks[i].key_off,
 				tracks[i].key_off + tracks[i].key_count, (unsigned long long)pool);
 	}
+	{ // interval records are built per key range: two tracks may share a range (instanced animation) but ranges must not partially overlap
+		std::vector<std::pair<uint64_t, uint32_t>> rng(n);
+		for (uint32_t i = 0; i < n; ++i)
+			rng[i] = {(uint64_t(tracks[i].kind == 3) << 32) | tracks[i].key_off, tracks[i].key_count};
+		std::sort(rng.begin(), rng.end());
+		for (uint32_t i = 1; i < n; ++i)
+			if (rng[i] != rng[i - 1] && rng[i - 1].first + rng[i - 1].second > rng[i].first && (rng[i].first >> 32) == (rng[i - 1].first >> 32) &&
+				rng[i - 1].second && rng[i].second)
+				return fail("hgb_set_tracks: key ranges [%u,+%u) and [%u,+%u) overlap without being identical", uint32_t(rng[i - 1].first), rng[i - 1].second,
+					uint32_t(rng[i].first), rng[i].second);
+	}
+	c->records_dirty = true;
 	CK(c->play_t_d.reserve(std::max<size_t>(n_play, 1) * 8));
 	CK(c->play_t_h.reserve(std::max<size_t>(n_play, 1) * 8));
 	CK(c->cursor.reserve(std::max<size_t>(n, 1) * 4));
@@ -513,6 +540,22 @@ static int prepare_tables(hgb_ctx *c) {
 		std::sort(tr.begin() + c->round_off[r], tr.begin() + c->round_off[r + 1], [](const Track &a, const Track &b) { return a.out_slot < b.out_slot; });
 	if (upload(c, c->tracks_d, tr.data(), tr.size() * sizeof(Track)))
 		return 1;
+	// chunk boundaries of the overlapped sampler: target position of every round-0 track (ascending: tracks are sorted by slot = position)
+	c->trk_pos_h.clear();
+	if (c->round_off.size() == 2 && !tr.empty()) {
+		c->trk_pos_h.resize(tr.size());
+		for (size_t i = 0; i < tr.size(); ++i)
+			c->trk_pos_h[i] = uint32_t(uniq[tr[i].out_slot] >> 2);
+	}
+	if (c->records_dirty && !tr.empty()) { // 128-byte interval records from the compact key pool (device side, once per key/track edit)
+		const size_t total = size_t(c->n_v3_keys) + c->n_q_keys;
+		CK(c->key_rec.reserve((total + 1) * 128));
+		k_build_key_records<<<grid_for(uint32_t(tr.size())), 256, 0, c->stream>>>(c->tracks_d.as<Track>(), uint32_t(tr.size()), c->keys.as<uint4>(), c->n_v3_keys,
+			c->key_rec.as<uint4>());
+		++c->launches;
+		CK(cudaGetLastError());
+		c->records_dirty = false;
+	}
 	const uint32_t n_bind = uint32_t(uniq.size());
 	if (n_bind) {
 		std::vector<uint32_t> bpos(n_bind);

@@ -68,8 +68,14 @@ __device__ __forceinline__ uint32_t entry_visibility(const SceneDev &s, const Ma
 		return survives_frustum(s.inst_planes + size_t(s.pos_view[p]) * 6, bb) ? 1u : 0u;
 	uint32_t bits = 0;
 	for (int v = 0; v < n_views; ++v)
-		bits |= survives_frustum(s_planes + v * 6, bb) ? (1u << v) : 0u;
+		bits |= survives_frustum_x(s_planes + v * 12, bb) ? (1u << v) : 0u; // s_planes: expanded form, 2 float4 per plane
 	return bits;
+}
+
+// fill the CTA's expanded copy of the shared view frusta (call before a __syncthreads)
+__device__ __forceinline__ void stage_planes(float4 *s_planes, const Views &views) {
+	if (threadIdx.x < uint32_t(views.n_views) * 6u)
+		expand_plane(views.planes[threadIdx.x], s_planes[threadIdx.x * 2], s_planes[threadIdx.x * 2 + 1]);
 }
 
 // ---- world-matrix propagation, one level per launch ---------------------------------------------------------------------
@@ -81,11 +87,10 @@ __device__ __forceinline__ uint32_t entry_visibility(const SceneDev &s, const Ma
 // `begin` is a multiple of 32 relative to the grid (blockDim = 256), so a warp covers 32 consecutive positions.
 template <bool FUSED, bool PER_INSTANCE>
 __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views, uint32_t begin, uint32_t end) {
-	__shared__ float4 s_planes[kMaxViews * 6];
+	__shared__ float4 s_planes[kMaxViews * 12];
 	__shared__ float4 s_out[8][96]; // per warp: 32 world matrices = 1536 B, for the transposed store
-	if (FUSED && !PER_INSTANCE) { // the shared view frusta: one broadcast LDS.128 per plane instead of a global load
-		if (threadIdx.x < uint32_t(views.n_views) * 6u)
-			s_planes[threadIdx.x] = views.planes[threadIdx.x];
+	if (FUSED && !PER_INSTANCE) { // the shared view frusta: broadcast LDS.128s instead of global loads
+		stage_planes(s_planes, views);
 		__syncthreads();
 	}
 	const uint32_t p = begin + blockIdx.x * blockDim.x + threadIdx.x;

@@ -25,32 +25,14 @@ struct alignas(16) Track { // 16 B, read as one uint4
 struct AnimDev {
 	const Track *tracks;
 	const int64_t *play_t;    // per playing anim: evaluation time (ns), INT64_MIN = not playing
-	const uint4 *keys;        // 2 x uint4 per key
+	const uint4 *keys;        // compact pool: 2 x uint4 per key (source of the records)
+	const uint4 *rec;         // interval records: 8 x uint4 (128 B, aligned) per key, see k_build_key_records
 	uint32_t quat_base;       // first quaternion key in the pool
 	uint32_t *cursor;         // per track: lower key of the interval found last frame (search hint only, never changes a result)
 	float4 *anim_val;         // output: one float4 per driven (node, triple); consecutive tracks write consecutive slots
 };
 
-__device__ __forceinline__ int64_t key_time(const uint4 *keys, uint32_t k) {
-	const uint2 t = *reinterpret_cast<const uint2 *>(keys + size_t(k) * 2);
-	return int64_t(uint64_t(t.x) | (uint64_t(t.y) << 32));
-}
-
 __device__ __forceinline__ float time_to_sec_f(int64_t t) { return __double2float_rn(__ddiv_rn(double(t), 1000000000.0)); } // foundation/time.h:13
-
-// GetIntervalKeys (engine/animation.h:109-128) scans linearly for the first key with key.t > t; keys are sorted by time, so this
-// binary search returns the same index (upper_bound).
-__device__ __forceinline__ uint32_t upper_bound_keys(const uint4 *keys, uint32_t n, int64_t at) {
-	uint32_t lo = 0, hi = n;
-	while (lo < hi) {
-		const uint32_t mid = (lo + hi) >> 1;
-		if (key_time(keys, mid) > at)
-			hi = mid;
-		else
-			lo = mid + 1;
-	}
-	return lo;
-}
 
 // HermiteInterpolate foundation/math.h:137-149 on one component
 __device__ __forceinline__ float hermite1(float y0, float y1, float y2, float y3, float a0, float a1, float a2, float a3, float tension, float bias) {
@@ -99,56 +81,139 @@ __device__ __forceinline__ void quat_to_euler(float x, float y, float z, float w
 	ex = a1, ey = a0, ez = a2;
 }
 
-__global__ void __launch_bounds__(256) k_sample_tracks(AnimDev a, uint32_t first, uint32_t n_tracks) {
-	const uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= first + n_tracks)
+// Interval records. The sampler's HBM traffic is one gather per track per frame; measured on the B200 (profiles/README.md r01c), a
+// 128-byte window that crosses a 128-byte line costs 70 % more time than an aligned one, and with 32-byte keys three windows out of
+// four cross. So the device keeps, next to the compact pool, one 128-BYTE-ALIGNED RECORD PER KEY: record k of a track holds the
+// keys {k-1, k, k+1, k+2} (clamped to the track) = everything EvaluateHermite / EvaluateLinear need for the interval that starts at
+// key k, plus the time of key k+2 to recognise "advanced by one interval". One frame = one aligned line per track. Costs 4x the
+// key memory (HBM is 180 GB; the 16M-node batch's 64M keys take 8 GB), built on the device by k_build_key_records at bind time.
+__global__ void __launch_bounds__(256) k_build_key_records(const Track *__restrict__ tracks, uint32_t n_tracks, const uint4 *__restrict__ keys,
+	uint32_t quat_base, uint4 *__restrict__ rec) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_tracks)
 		return;
-	Track trk;
-	*reinterpret_cast<uint4 *>(&trk) = *reinterpret_cast<const uint4 *>(a.tracks + i);
-	const int64_t at = a.play_t[trk.play];
-	if (at == INT64_MIN || trk.key_count == 0) // not playing / Evaluate() returns false on an empty track (animation.h:156)
+	const uint32_t n = tracks[i].key_count;
+	const size_t base = size_t(tracks[i].key_off) + (tracks[i].kind == 3 ? quat_base : 0u);
+	for (uint32_t k = 0; k < n; ++k) {
+		const uint32_t src[4] = {k > 0 ? k - 1 : 0u, k, min(k + 1, n - 1), min(k + 2, n - 1)};
+		uint4 *d = rec + (base + k) * 8;
+#pragma unroll
+		for (int j = 0; j < 4; ++j) {
+			d[j * 2] = keys[(base + src[j]) * 2];
+			d[j * 2 + 1] = keys[(base + src[j]) * 2 + 1];
+		}
+	}
+}
+
+// time of key k of a track, read from its record (slot 1 of record k is key k itself)
+__device__ __forceinline__ int64_t rec_key_time(const uint4 *rec, uint32_t k) {
+	const uint2 t = *reinterpret_cast<const uint2 *>(rec + size_t(k) * 8 + 2);
+	return int64_t(uint64_t(t.x) | (uint64_t(t.y) << 32));
+}
+__device__ __forceinline__ uint32_t upper_bound_rec(const uint4 *rec, uint32_t n, int64_t at) {
+	uint32_t lo = 0, hi = n;
+	while (lo < hi) {
+		const uint32_t mid = (lo + hi) >> 1;
+		if (rec_key_time(rec, mid) > at)
+			hi = mid;
+		else
+			lo = mid + 1;
+	}
+	return lo;
+}
+
+// One thread per bound track; a warp fetches its 32 records cooperatively — 8 lanes per record, 16 bytes per lane, straight into
+// shared memory with cp.async (LDGSTS, L1 bypassed) — so one load instruction covers four complete 128-byte lines (per-thread
+// 16-byte gathers are bound by L1 wavefronts at 89 % of the data-pipe peak, profiles/r01b). Each lane then reads its own record
+// (144-byte stride: conflict-free LDS.128). Pass 0 fetches the record of last frame's interval (cursor); when the interval moved
+// (next key, time jump, loop wrap) pass 1 fetches the record of the new one for the lanes that need it.
+constexpr int kSampleWarps = 8;
+constexpr uint32_t kWinStride = 144;
+
+__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src) {
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+}
+
+__global__ void __launch_bounds__(kSampleWarps * 32) k_sample_tracks(AnimDev a, uint32_t first, uint32_t n_tracks) {
+	__shared__ __align__(16) uint8_t s_win[kSampleWarps][32 * kWinStride];
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+	bool active = i < first + n_tracks;
+	Track trk{};
+	int64_t at = INT64_MIN;
+	if (active) {
+		*reinterpret_cast<uint4 *>(&trk) = *reinterpret_cast<const uint4 *>(a.tracks + i);
+		at = a.play_t[trk.play];
+		active = at != INT64_MIN && trk.key_count != 0; // not playing / Evaluate() returns false on an empty track (animation.h:156)
+	}
+	if (!__any_sync(0xffffffffu, active))
 		return;
 	const uint32_t n = trk.key_count;
-	const uint4 *keys = a.keys + size_t(trk.key_off + (trk.kind == 3 ? a.quat_base : 0u)) * 2;
-
-	// Interval search. The four keys around the interval found last frame are requested at once (eight independent 16-byte loads, 128
-	// contiguous bytes); the interval is then that one, or the next one (a frame rarely advances more than one key), else the binary
-	// search (time jumps, loop wrap). kA..kD = keys kf0, kf1, kf2, kf3 of EvaluateHermite.
-	const uint32_t cur = min(a.cursor[i], n - 1);
-	const uint32_t i0 = cur > 0 ? cur - 1 : 0, i2 = min(cur + 1, n - 1), i3 = min(cur + 2, n - 1);
-	uint4 kAa = keys[size_t(i0) * 2], kAb = keys[size_t(i0) * 2 + 1];
-	uint4 kBa = keys[size_t(cur) * 2], kBb = keys[size_t(cur) * 2 + 1];
-	uint4 kCa = keys[size_t(i2) * 2], kCb = keys[size_t(i2) * 2 + 1];
-	uint4 kDa = keys[size_t(i3) * 2], kDb = keys[size_t(i3) * 2 + 1];
+	const uint32_t kbase = trk.key_off + (trk.kind == 3 ? a.quat_base : 0u);
+	const uint4 *rec = a.rec + size_t(kbase) * 8;
+	uint8_t *sw = s_win[warp];
+	const uint4 *win = reinterpret_cast<const uint4 *>(sw + lane * kWinStride);
+	const uint32_t sub = lane & 7u, grp = lane >> 3;
+	const uint8_t *pool = reinterpret_cast<const uint8_t *>(a.rec);
 	auto t_of = [](const uint4 &k) { return int64_t(uint64_t(k.x) | (uint64_t(k.y) << 32)); };
-	uint32_t ub;
-	if (t_of(kBa) <= at && (cur + 1 == n || at < t_of(kCa))) {
-		ub = cur + 1;
-	} else if (cur + 1 < n && t_of(kCa) <= at && (cur + 2 == n || at < t_of(kDa))) {
-		ub = cur + 2;
-		const uint32_t i4 = min(cur + 3, n - 1);
-		kAa = kBa, kAb = kBb, kBa = kCa, kBb = kCb, kCa = kDa, kCb = kDb;
-		kDa = keys[size_t(i4) * 2], kDb = keys[size_t(i4) * 2 + 1];
-		a.cursor[i] = cur + 1;
-	} else {
-		ub = upper_bound_keys(keys, n, at);
-		const uint32_t kf1 = ub > 0 ? ub - 1 : 0, kf2 = min(ub, n - 1);
-		const uint32_t kf0 = kf1 > 0 ? kf1 - 1 : 0, kf3 = min(kf2 + 1, n - 1);
-		kAa = keys[size_t(kf0) * 2], kAb = keys[size_t(kf0) * 2 + 1];
-		kBa = keys[size_t(kf1) * 2], kBb = keys[size_t(kf1) * 2 + 1];
-		kCa = keys[size_t(kf2) * 2], kCb = keys[size_t(kf2) * 2 + 1];
-		kDa = keys[size_t(kf3) * 2], kDb = keys[size_t(kf3) * 2 + 1];
-		a.cursor[i] = kf1;
+
+	uint32_t kf1 = active ? min(a.cursor[i], n - 1) : 0u; // record wanted
+	uint32_t ub = 0, sh = 0;                              // sh = 1: interval advanced by one key, slots shift by one
+	uint4 nDa = make_uint4(0, 0, 0, 0), nDb = nDa;        // ... and this is the new fourth key
+	bool want = active;
+#pragma unroll 1
+	for (int pass = 0; pass < 2; ++pass) {
+		// cooperative fetch: round r serves tracks 4r..4r+3
+		const uint32_t want_rec = want ? kbase + kf1 : 0xffffffffu;
+#pragma unroll
+		for (int r = 0; r < 8; ++r) {
+			const uint32_t tr = r * 4 + grp;
+			const uint32_t k = __shfl_sync(0xffffffffu, want_rec, tr);
+			if (k != 0xffffffffu)
+				cp_async16(uint32_t(__cvta_generic_to_shared(sw + tr * kWinStride + sub * 16)), pool + size_t(k) * 128 + sub * 16);
+		}
+		asm volatile("cp.async.wait_all;" ::: "memory");
+		__syncwarp();
+		if (pass == 1)
+			break;
+		// interval: the one found last frame, or the next one (a frame rarely advances more than one key), else the binary search
+		want = false;
+		if (active) {
+			const uint32_t cur = kf1;
+			const int64_t tB = t_of(win[2]), tC = t_of(win[4]);
+			if (tB <= at && (cur + 1 == n || at < tC)) {
+				ub = cur + 1;
+			} else if (cur + 1 < n && tC <= at && (cur + 2 == n || at < t_of(win[6]))) {
+				// next interval: its record is this one shifted by a key; only its fourth key (32 bytes) is new
+				ub = cur + 2;
+				sh = 1;
+				nDa = rec[size_t(cur + 1) * 8 + 6], nDb = rec[size_t(cur + 1) * 8 + 7];
+				a.cursor[i] = cur + 1;
+			} else {
+				ub = upper_bound_rec(rec, n, at);
+				kf1 = ub > 0 ? ub - 1 : 0; // ub == 0: before the first key -> key 0; ub == n: at/after the last key -> key n-1
+				if (kf1 != cur) {
+					a.cursor[i] = kf1;
+					want = true;
+				}
+			}
+		}
+		if (!__any_sync(0xffffffffu, want))
+			break;
+		__syncwarp(); // every lane has read its pass-0 record before pass 1 overwrites windows
 	}
-	// ub == 0: before the first key -> kB is key 0 (kf1 clamps to 0). ub == n: at/after the last key -> kB is key n-1.
+	if (!active)
+		return;
+	// slots kf0, kf1, kf2, kf3 of EvaluateHermite (animation.h:155-169), neighbours clamped to the track
+	const uint4 *w = win + sh * 2;
+	const uint4 kBa = w[2], kBb = w[3];
 	float4 *dst = a.anim_val + trk.out_slot;
 
 	if (trk.kind == 3) { // AnimTrackT<Quaternion>: EvaluateLinear animation.h:141-153, then ToEuler(Normalize())
-		float4 q;
-		if (ub == 0 || ub == n) {
-			q = make_float4(__uint_as_float(kBa.z), __uint_as_float(kBa.w), __uint_as_float(kBb.x), __uint_as_float(kBb.y));
-		} else {
-			const float4 q0 = make_float4(__uint_as_float(kBa.z), __uint_as_float(kBa.w), __uint_as_float(kBb.x), __uint_as_float(kBb.y));
+		float4 q = make_float4(__uint_as_float(kBa.z), __uint_as_float(kBa.w), __uint_as_float(kBb.x), __uint_as_float(kBb.y));
+		if (!(ub == 0 || ub == n)) {
+			const uint4 kCa = w[4], kCb = w[5];
+			const float4 q0 = q;
 			const float4 q1 = make_float4(__uint_as_float(kCa.z), __uint_as_float(kCa.w), __uint_as_float(kCb.x), __uint_as_float(kCb.y));
 			const int64_t t1 = t_of(kBa), t2 = t_of(kCa);
 			const float k = time_to_sec_f(at - t1) / time_to_sec_f(t2 - t1);
@@ -164,6 +229,8 @@ __global__ void __launch_bounds__(256) k_sample_tracks(AnimDev a, uint32_t first
 	if (ub == 0 || ub == n) {
 		ox = __uint_as_float(kBa.z), oy = __uint_as_float(kBa.w), oz = __uint_as_float(kBb.x);
 	} else {
+		const uint4 kAa = w[0], kAb = w[1], kCa = w[4], kCb = w[5];
+		const uint4 kDa = sh ? nDa : win[6], kDb = sh ? nDb : win[7];
 		const int64_t t1 = t_of(kBa), t2 = t_of(kCa);
 		const float u = time_to_sec_f(at - t1) / time_to_sec_f(t2 - t1);
 		const float tension = __uint_as_float(kBb.y), bias = __uint_as_float(kBb.z);
@@ -210,6 +277,52 @@ __global__ void __launch_bounds__(256) k_bone_matrices(BoneDev b) {
 	store_bgfx(b.out + size_t(i) * 16, mat4_mul(load_mat4(b.world + size_t(mp) * 12), bind));
 	if (b.world_prev)
 		store_bgfx(b.out_prev + size_t(i) * 16, mat4_mul(load_mat4(b.world_prev + size_t(mp) * 12), bind));
+}
+
+// ---- transparent-list sort keys -------------------------------------------------------------------------------------------
+// ComputeModelDisplayListSortKeys (engine/scene_forward_pipeline.cpp:438-483) for the SURVIVORS of a culled list: model-view matrix =
+// view * world (operator*(Mat4,Mat4)), the 8 corners of the list's MinMax through operator*(Mat4,Vec3) (foundation/matrix4.cpp:78-81;
+// only z is used), the closest z clamped at 0, then ComputeSortKey (engine/render_pipeline.cpp:89-94): +100 m, clamp, 1 mm fixed point.
+struct SortKeyDev {
+	const uint32_t *visible;  // surviving entry indices
+	const uint32_t *count;    // how many (device word)
+	const uint32_t *mtx_pos;  // per entry
+	const uint32_t *meta;     // per entry: bounds idx | flags
+	const float *world;
+	const float *bounds6;     // interleaved {mn.x, mx.x, mn.y, mx.y, mn.z, mx.z}
+	float view[12];           // ViewState::view
+	uint32_t *keys;           // out: one per survivor
+};
+
+__global__ void __launch_bounds__(256) k_sort_keys(SortKeyDev d, uint32_t capacity) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= capacity || i >= *d.count)
+		return;
+	const uint32_t e = d.visible[i];
+	Mat4 view;
+#pragma unroll
+	for (int k = 0; k < 12; ++k)
+		view.m[k / 4][k % 4] = d.view[k];
+	const Mat4 mv = mat4_mul(view, load_mat4(d.world + size_t(d.mtx_pos[e]) * 12));
+	const float *b = d.bounds6 + size_t(d.meta[e] & 0xffffffu) * 6;
+	const float mnx = b[0], mxx = b[1], mny = b[2], mxy = b[3], mnz = b[4], mxz = b[5];
+	// corner order of the reference (the running minimum is order-independent for finite values; kept anyway)
+	const float cx[8] = {mnx, mxx, mxx, mnx, mnx, mxx, mxx, mnx};
+	const float cy[8] = {mny, mny, mxy, mxy, mny, mny, mxy, mxy};
+	const float cz[8] = {mnz, mnz, mnz, mnz, mxz, mxz, mxz, mxz};
+	float closest = 3.402823466e+38f;
+#pragma unroll
+	for (int k = 0; k < 8; ++k) {
+		const float z = cx[k] * mv.m[2][0] + cy[k] * mv.m[2][1] + cz[k] * mv.m[2][2] + mv.m[2][3];
+		if (z < closest)
+			closest = z;
+	}
+	if (closest < 0.f)
+		closest = 0.f;
+	float depth = closest + 100.f;
+	if (depth < 0.f)
+		depth = 0.f;
+	d.keys[i] = uint32_t(__float2ll_rz(depth * 1000.f)); // x86-64 converts through a 64-bit integer and keeps the low word
 }
 
 // ---- layout shuffles -----------------------------------------------------------------------------------------------------

@@ -14,6 +14,30 @@ struct Mat4 { // == hg::Mat4::m, row-major 3x4 (foundation/matrix4.h:25)
 	float m[3][4];
 };
 
+// ---- packed FP32 (Blackwell mul.f32x2: two IEEE round-to-nearest products per issue slot) ----------------------------------------
+// The level kernel is co-limited by instruction issue (profiles/README.md r01b), and a third of its instructions are FMULs that come
+// in pairs sharing one operand. mul.rn.f32x2 computes two independent correctly-rounded products, so every result keeps the bits of
+// the scalar form. ONLY products are packed, and packed sums are used only where no product feeds them directly: ptxas 12.9 contracts
+// mul.rn.f32x2 -> add.rn.f32x2 chains into FFMA2 even under -fmad=false (verified in SASS), which would break bit-exactness.
+// tests/test_capi_symbols.py asserts that the library's SASS holds no FFMA/FFMA2 at all.
+typedef unsigned long long f32x2_t;
+__device__ __forceinline__ f32x2_t pk2(float lo, float hi) {
+	f32x2_t r;
+	asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+	return r;
+}
+__device__ __forceinline__ void upk2(f32x2_t v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2_t mul2(f32x2_t a, f32x2_t b) {
+	f32x2_t r;
+	asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+	return r;
+}
+__device__ __forceinline__ f32x2_t add2(f32x2_t a, f32x2_t b) {
+	f32x2_t r;
+	asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+	return r;
+}
+
 // ---- sinf/cosf --------------------------------------------------------------------------------------------------
 // The reference calls libm sinf/cosf (foundation/matrix3.cpp:199-204). glibc 2.39 (sysdeps/ieee754/flt-32/sincosf.h)
 // reduces in double, evaluates a double polynomial and rounds once to float; on FMA-capable hosts each a*b+c is one
@@ -115,26 +139,46 @@ __device__ __forceinline__ Mat4 transformation_mat4(float px, float py, float pz
 	sincos_libm(ey, s0, c0);
 	sincos_libm(ex, s1, c1);
 	sincos_libm(ez, s2, c2);
-	const float s0s2 = s0 * s2, s0c2 = s0 * c2, c0s2 = c0 * s2, c0c2 = c0 * c2;
-	const float r11 = c1 * c2, r10 = c1 * s2, r12 = -s1;
-	const float r01 = s1 * s0c2 - c0s2, r00 = s1 * s0s2 + c0c2, r02 = s0 * c1;
-	const float r21 = s1 * c0c2 + s0s2, r20 = s1 * c0s2 - s0c2, r22 = c0 * c1;
+	// products in pairs that share a factor (same factors, same roundings as the scalar form)
+	const f32x2_t s2c2 = pk2(s2, c2);
+	float s0s2, s0c2, c0s2, c0c2, r10, r11, r02, r22;
+	upk2(mul2(pk2(s0, s0), s2c2), s0s2, s0c2);
+	upk2(mul2(pk2(c0, c0), s2c2), c0s2, c0c2);
+	upk2(mul2(pk2(c1, c1), s2c2), r10, r11);
+	upk2(mul2(pk2(c1, c1), pk2(s0, c0)), r02, r22);
+	float a01, a00, a21, a20;
+	upk2(mul2(pk2(s1, s1), pk2(s0c2, s0s2)), a01, a00);
+	upk2(mul2(pk2(s1, s1), pk2(c0c2, c0s2)), a21, a20);
+	const float r12 = -s1;
+	const float r01 = a01 - c0s2, r00 = a00 + c0c2;
+	const float r21 = a21 + s0s2, r20 = a20 - s0c2;
 	Mat4 o;
-	o.m[0][0] = r00 * sx, o.m[0][1] = r01 * sy, o.m[0][2] = r02 * sz, o.m[0][3] = px;
-	o.m[1][0] = r10 * sx, o.m[1][1] = r11 * sy, o.m[1][2] = r12 * sz, o.m[1][3] = py;
-	o.m[2][0] = r20 * sx, o.m[2][1] = r21 * sy, o.m[2][2] = r22 * sz, o.m[2][3] = pz;
+	upk2(mul2(pk2(sx, sx), pk2(r00, r10)), o.m[0][0], o.m[1][0]);
+	upk2(mul2(pk2(sy, sy), pk2(r01, r11)), o.m[0][1], o.m[1][1]);
+	upk2(mul2(pk2(sz, sz), pk2(r02, r12)), o.m[0][2], o.m[1][2]);
+	upk2(mul2(pk2(r20, r21), pk2(sx, sy)), o.m[2][0], o.m[2][1]);
+	o.m[2][2] = r22 * sz;
+	o.m[0][3] = px, o.m[1][3] = py, o.m[2][3] = pz;
 	return o;
 }
 
 // operator*(Mat4, Mat4) foundation/matrix4.cpp:31-44 — left-to-right sums, translation column adds a[r][3] last
 __device__ __forceinline__ Mat4 mat4_mul(const Mat4 &a, const Mat4 &b) {
 	Mat4 o;
+	const f32x2_t b00 = pk2(b.m[0][0], b.m[0][1]), b02 = pk2(b.m[0][2], b.m[0][3]);
+	const f32x2_t b10 = pk2(b.m[1][0], b.m[1][1]), b12 = pk2(b.m[1][2], b.m[1][3]);
+	const f32x2_t b20 = pk2(b.m[2][0], b.m[2][1]), b22 = pk2(b.m[2][2], b.m[2][3]);
 #pragma unroll
 	for (int r = 0; r < 3; ++r) {
-#pragma unroll
-		for (int c = 0; c < 3; ++c)
-			o.m[r][c] = a.m[r][0] * b.m[0][c] + a.m[r][1] * b.m[1][c] + a.m[r][2] * b.m[2][c];
-		o.m[r][3] = a.m[r][0] * b.m[0][3] + a.m[r][1] * b.m[1][3] + a.m[r][2] * b.m[2][3] + a.m[r][3];
+		const f32x2_t a0 = pk2(a.m[r][0], a.m[r][0]), a1 = pk2(a.m[r][1], a.m[r][1]), a2 = pk2(a.m[r][2], a.m[r][2]);
+		float p0, p1, p2, p3, q0, q1, q2, q3, t0, t1, t2, t3;
+		upk2(mul2(a0, b00), p0, p1), upk2(mul2(a0, b02), p2, p3);
+		upk2(mul2(a1, b10), q0, q1), upk2(mul2(a1, b12), q2, q3);
+		upk2(mul2(a2, b20), t0, t1), upk2(mul2(a2, b22), t2, t3);
+		o.m[r][0] = p0 + q0 + t0;
+		o.m[r][1] = p1 + q1 + t1;
+		o.m[r][2] = p2 + q2 + t2;
+		o.m[r][3] = p3 + q3 + t3 + a.m[r][3];
 	}
 	return o;
 }
@@ -163,24 +207,25 @@ struct Aabb {
 	float mn[3], mx[3];
 };
 
+// The device MinMax table is stored interleaved: {mn.x, mx.x, mn.y, mx.y, mn.z, mx.z} (hgb_set_bounds converts), so (mn[i], mx[i]) is
+// one 8-byte pair: both products of a matrix element are one mul2, and (mn, mx) += (lo, hi) is one add2 (its operands come from
+// selects, never straight from a product).
 __device__ __forceinline__ Aabb minmax_transform(const Mat4 &m, const float *__restrict__ b6) {
+	const float2 *bp = reinterpret_cast<const float2 *>(b6);
+	const float2 bx = bp[0], by = bp[1], bz = bp[2];
+	const f32x2_t bb[3] = {pk2(bx.x, bx.y), pk2(by.x, by.y), pk2(bz.x, bz.y)};
 	Aabb o;
 #pragma unroll
 	for (int j = 0; j < 3; ++j) {
-		float mn = m.m[j][3], mx = m.m[j][3];
+		f32x2_t acc = pk2(m.m[j][3], m.m[j][3]);
 #pragma unroll
 		for (int i = 0; i < 3; ++i) {
-			const float a = m.m[j][i] * b6[i], b = m.m[j][i] * b6[3 + i];
-			if (a < b) {
-				mn += a;
-				mx += b;
-			} else {
-				mn += b;
-				mx += a;
-			}
+			float a, b;
+			upk2(mul2(pk2(m.m[j][i], m.m[j][i]), bb[i]), a, b);
+			const bool lt = a < b;
+			acc = add2(acc, pk2(lt ? a : b, lt ? b : a));
 		}
-		o.mn[j] = mn;
-		o.mx[j] = mx;
+		upk2(acc, o.mn[j], o.mx[j]);
 	}
 	return o;
 }
@@ -196,6 +241,31 @@ __device__ __forceinline__ bool survives_frustum(const float4 *__restrict__ plan
 		const float d = p.x * cx + p.y * cy + p.z * cz;
 		const float r = fabsf(p.x) * ex + fabsf(p.y) * ey + fabsf(p.z) * ez;
 		inside = inside && !(d - r > p.w);
+	}
+	return inside;
+}
+
+// Same test with the planes expanded in shared memory to two float4 each: {x, |x|, y, |y|} {z, |z|, -2w, 0}, so that the products of
+// d and r pair up: (x*cx, |x|*ex) is one mul2. Sums stay scalar, left to right as in the reference.
+__device__ __forceinline__ void expand_plane(const float4 p, float4 &a, float4 &b) {
+	a = make_float4(p.x, fabsf(p.x), p.y, fabsf(p.y));
+	b = make_float4(p.z, fabsf(p.z), p.w, 0.f);
+}
+__device__ __forceinline__ bool survives_frustum_x(const float4 *__restrict__ planes2, const Aabb &bb) {
+	const f32x2_t cex = pk2(bb.mn[0] + bb.mx[0], bb.mx[0] - bb.mn[0]);
+	const f32x2_t cey = pk2(bb.mn[1] + bb.mx[1], bb.mx[1] - bb.mn[1]);
+	const f32x2_t cez = pk2(bb.mn[2] + bb.mx[2], bb.mx[2] - bb.mn[2]);
+	bool inside = true;
+#pragma unroll
+	for (int n = 0; n < 6; ++n) {
+		const float4 a = planes2[2 * n], b = planes2[2 * n + 1];
+		float dx, rx, dy, ry, dz, rz;
+		upk2(mul2(pk2(a.x, a.y), cex), dx, rx);
+		upk2(mul2(pk2(a.z, a.w), cey), dy, ry);
+		upk2(mul2(pk2(b.x, b.y), cez), dz, rz);
+		const float d = dx + dy + dz;
+		const float r = rx + ry + rz;
+		inside = inside && !(d - r > b.z);
 	}
 	return inside;
 }

@@ -290,3 +290,46 @@ def slice_instances(fs, i0, i1):
     sub.instance_start = (fs.instance_start[i0:i1 + 1].astype(np.int64) - lo).astype(np.uint32)
     sub.instance_cameras = fs.instance_cameras[i0:i1].copy()
     return sub
+
+
+def extract_range(fs, lo, hi):
+    """Nodes [lo, hi) of a batch as a stand-alone FlatScene (the range must be closed under parents — e.g. one scene of config_c4 —
+    and must not contain skins). Animation is carried over: the Anims bound to nodes of the range, with their tracks and keys, and
+    every SceneAnim / play restricted to them (same clocks). Used by the full-size parity tests: the reference runs one scene of the
+    batch while the GPU runs all of them."""
+    assert not fs.bones
+    parent = fs.parent[lo:hi].astype(np.int64)
+    assert ((parent < 0) | ((parent >= lo) & (parent < hi))).all(), "range is not closed under parents"
+    sub = FlatScene(trs=fs.trs[lo:hi].copy(), parent=np.where(parent >= 0, parent - lo, -1).astype(np.int32), disabled=fs.disabled[lo:hi].copy(),
+                    model=fs.model[lo:hi].copy(), n_mats=fs.n_mats[lo:hi].copy(), transparent_mask=fs.transparent_mask[lo:hi].copy(), models=fs.models,
+                    camera=dict(fs.camera))
+    if len(fs.anim_node):
+        keep_anim = (fs.anim_node >= lo) & (fs.anim_node < hi)
+        new_anim = np.cumsum(keep_anim) - 1
+        sub.anim_node = (fs.anim_node[keep_anim] - lo).astype(np.int32)
+        sub.anim_use_quat = fs.anim_use_quat[keep_anim].copy()
+        keep_trk = keep_anim[fs.trk_anim]
+        sub.trk_anim = new_anim[fs.trk_anim[keep_trk]].astype(np.int32)
+        sub.trk_kind = fs.trk_kind[keep_trk].copy()
+        sub.trk_key_count = fs.trk_key_count[keep_trk].copy()
+        is_q = sub.trk_kind == 3
+        cnt = sub.trk_key_count.astype(np.int64)
+        off = np.zeros(len(cnt), np.int64)
+        for m in (~is_q, is_q):
+            off[m] = np.concatenate([[0], np.cumsum(cnt[m])[:-1]]) if m.any() else 0
+        sub.trk_key_off = off.astype(np.uint32)
+        old_off = fs.trk_key_off[keep_trk].astype(np.int64)
+
+        def take(pool_arrays, mask):
+            if not mask.any():
+                return [a[:0].copy() for a in pool_arrays]
+            idx = np.concatenate([np.arange(o, o + c) for o, c in zip(old_off[mask], cnt[mask])]) if len(set(cnt[mask])) > 1 else \
+                (old_off[mask][:, None] + np.arange(int(cnt[mask][0]))[None, :]).reshape(-1)
+            return [a[idx] for a in pool_arrays]
+        sub.v3_t, sub.v3_val, sub.v3_tension, sub.v3_bias = take([fs.v3_t, fs.v3_val, fs.v3_tension, fs.v3_bias], ~is_q)
+        sub.q_t, sub.q_val = take([fs.q_t, fs.q_val], is_q)
+        for anims, ts, te in fs.scene_anims:
+            a = np.asarray(anims)
+            sub.scene_anims.append((new_anim[a[keep_anim[a]]].astype(np.int32), ts, te))
+        sub.plays = list(fs.plays)
+    return sub

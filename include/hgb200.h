@@ -46,7 +46,16 @@ typedef struct hgb_options {
 	                  (shared-memory transpose); 1: every thread stores its own 48-byte row */
 	int lookahead; /* profiling A/B switch. L2 software-prefetch distance of the level kernel in positions: 0 = default (one wave of
 	                  resident CTAs), -1 = off, n = n positions */
-	int reserved[5];
+	int tma_level;     /* profiling A/B switch. 0 (default): level kernel with one thread per node, tile rows read with 128-byte LDGs (+ the
+	                      L2 look-ahead above); 1: persistent level kernel, node tiles staged with TMA bulk copies, world rows leave as
+	                      bulk stores (measured 3 % slower on the 16M-node batch, profiles/README.md r01c) */
+	int reserved0;
+	int merge_small;   /* 1: runs of consecutive small levels go out as one cooperative launch with grid barriers between the levels
+	                      (k_update_levels_small). Default 0: measured faster per kernel but not inside the frame graph (profiles r01c) */
+	int overlap_sampler; /* 1: tracks are sampled in chunks by target level on a second stream, overlapped with the level kernels. Default 0:
+	                        both kernels lean on HBM, running them together measured 1-8 % slower than back to back (profiles r01c) */
+	int slice_nodes;   /* with overlap_sampler, levels larger than this are cut into slices of this many nodes, each waiting only for its
+	                      own track chunk (0 = no slicing; rounded up to a multiple of 256) */
 } hgb_options;
 
 /* one bound animation track (BoundToNodeAnim entry, harfang/engine/scene.h:74-88) */
@@ -109,6 +118,10 @@ int hgb_cull(hgb_ctx *);
  * indices are written to out_idx in order (capacity n) and their number to *out_count. Independent of the entry tables above. */
 int hgb_cull_list(hgb_ctx *, uint32_t n, const uint32_t *mtx_slot, const uint32_t *bounds_idx, uint32_t n_bounds, const float *bounds6,
 	const float *frustum24, uint32_t *out_idx, uint32_t *out_count);
+/* ComputeModelDisplayListSortKeys (harfang/engine/scene_forward_pipeline.cpp:438-483, ComputeSortKey render_pipeline.cpp:89-94) for the
+ * survivors of list (kind, view) of the last cull: one 1-mm fixed-point key per visible entry, from the closest view-space z of the 8
+ * corners of its MinMax. view_mat12 = ViewState::view (hg::Mat4). Keys are returned in visible-list order by hgb_get_sort_keys. */
+int hgb_sort_keys(hgb_ctx *, int kind, uint32_t view, const float *view_mat12);
 /* Bone matrices of every skin record (and the previous-frame twin). */
 int hgb_bone_matrices(hgb_ctx *, int with_previous);
 
@@ -121,6 +134,7 @@ int hgb_get_visible(hgb_ctx *, int kind, uint32_t view, uint32_t *out_idx, uint3
 /* instance mode: exclusive offsets of every instance's survivors inside the kind-0 list, n_instances+1 values */
 int hgb_get_instance_offsets(hgb_ctx *, uint32_t *out_offsets);
 int hgb_get_bone_matrices(hgb_ctx *, float *out16, int previous);
+int hgb_get_sort_keys(hgb_ctx *, int kind, uint32_t view, uint32_t *out_keys, uint32_t capacity, uint32_t *out_count);
 
 /* ---- introspection for benchmarks / interop ---- */
 /* device pointers: 0 worlds, 1 previous worlds, 2 visible list (kind 0, view 0), 3 visible count (kind 0, view 0), 4 bone matrices,
@@ -141,7 +155,8 @@ int hgb_time_end(hgb_ctx *, float *out_ms);
 #define HGB_K_SEGMENT_RANKS 3
 #define HGB_K_CULL_FLAGS 4
 #define HGB_K_BONE_MATRICES 5
-#define HGB_K_COUNT 6
+#define HGB_K_SORT_KEYS 6
+#define HGB_K_COUNT 7
 int hgb_set_profiling(hgb_ctx *, int on);
 int hgb_get_profile(hgb_ctx *, double *ms_by_class, uint64_t *launches_by_class, int reset);
 /* Write `bytes` bytes of a scratch buffer (allocated on first use) — L2 flush between timed iterations. */

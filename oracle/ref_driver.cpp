@@ -28,6 +28,7 @@
 #include <cstdio>
 #include <cstring>
 #include <memory>
+#include <limits>
 #include <vector>
 
 using namespace hg;
@@ -403,6 +404,35 @@ void hgref_minmax_transform(const float *m12, const float *mm6, float *out6) {
 	const MinMax o = mat4_from(m12) * MinMax(Vec3(mm6[0], mm6[1], mm6[2]), Vec3(mm6[3], mm6[4], mm6[5]));
 	memcpy(out6, &o.mn, 12);
 	memcpy(out6 + 3, &o.mx, 12);
+}
+// restated: ComputeModelDisplayListSortKeys, engine/scene_forward_pipeline.cpp:438-483 (that TU drags the whole forward pipeline in, so its
+// loop is repeated here with the reference's own operator*(Mat4,Mat4), operator*(Mat4,Vec3) and ComputeSortKey, render_pipeline.cpp:89-94)
+// over the list left by the last hgref_cull. view12 = ViewState::view.
+int hgref_sort_keys(void *h, const float *view12, uint32_t *out) {
+	auto *c = static_cast<RefCtx *>(h);
+	Mat4 view;
+	memcpy(&view, view12, 48);
+	const auto &mtxs = c->scene->GetTransformWorldMatrices();
+	size_t n = 0;
+	for (const auto &dl : c->culled) {
+		const Mat4 mdl_view_mtx = view * mtxs[dl.mtx_idx];
+		const auto &bound = c->resources.models.Get_unsafe_(dl.mdl_idx).bounds[dl.lst_idx];
+		const Vec3 vtx[8] = {{bound.mn.x, bound.mn.y, bound.mn.z}, {bound.mx.x, bound.mn.y, bound.mn.z}, {bound.mx.x, bound.mx.y, bound.mn.z},
+			{bound.mn.x, bound.mx.y, bound.mn.z}, {bound.mn.x, bound.mn.y, bound.mx.z}, {bound.mx.x, bound.mn.y, bound.mx.z},
+			{bound.mx.x, bound.mx.y, bound.mx.z}, {bound.mn.x, bound.mx.y, bound.mx.z}};
+		float closest = std::numeric_limits<float>::max();
+		for (auto &v : vtx) {
+			const Vec3 in_view = mdl_view_mtx * v;
+			if (in_view.z < closest)
+				closest = in_view.z;
+		}
+		if (closest < 0.f)
+			closest = 0.f;
+		if (out)
+			out[n] = ComputeSortKey(closest);
+		++n;
+	}
+	return int(n);
 }
 int hgref_test_visibility(const float *frustum24, const float *mm6) {
 	Frustum f;

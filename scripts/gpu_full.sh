@@ -13,5 +13,5 @@ B="python bench.py --steps 3 --warmup 3 --no-cpu-baseline"
 timeout 600 $B > gpurun_out/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv $B > gpurun_out/ncu1.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_update_level -s 16 -c 8 -o gpurun_out/prof_update_level $B > gpurun_out/ncu2.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_compact|k_sample_tracks" -s 4 -c 2 -o gpurun_out/prof_others $B > gpurun_out/ncu3.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_compact|k_sample_tracks|k_update_levels_small" -s 6 -c 3 -o gpurun_out/prof_others $B > gpurun_out/ncu3.log 2>&1
 ls -la gpurun_out

@@ -97,6 +97,7 @@ def _bind_scene_driver(L, with_probes):
         _sig(L, "hgref_minmax_transform", None, [c_p, c_p, c_p])
         _sig(L, "hgref_quat_to_euler", None, [c_p, c_p])
         _sig(L, "hgref_test_visibility", c_i, [c_p, c_p])
+        _sig(L, "hgref_sort_keys", c_i, [c_p, c_p, c_p])
         _sig(L, "hgref_eval_vec3_track", c_i, [c_i, c_p, c_p, c_p, c_p, c_i64, c_p, c_p])
         _sig(L, "hgref_eval_quat_track", c_i, [c_i, c_p, c_p, c_i64, c_p])
     return L

@@ -86,6 +86,14 @@ class RefScene:
         self.L.hgref_read_skinned_lists(self.h, kind, P(mi), P(bi), P(bc), P(mdl), P(lst))
         return mi[:n], bi[:n], bc[:n], mdl[:n], lst[:n]
 
+    def sort_keys(self, view12):
+        """ComputeModelDisplayListSortKeys over the list left by the last cull()"""
+        v = np.ascontiguousarray(view12, np.float32).reshape(12)
+        n = self.L.hgref_sort_keys(self.h, P(v), None)
+        out = np.zeros(max(n, 1), np.uint32)
+        self.L.hgref_sort_keys(self.h, P(v), P(out))
+        return out[:n]
+
     def bone_matrices(self, previous=False, kind=2):
         counts = np.zeros(4, np.int32)
         self.L.hgref_get_model_display_lists(self.h, P(counts))

@@ -4,6 +4,8 @@ import os
 import re
 import subprocess
 
+import pytest
+
 import harfang3d_b200
 from harfang3d_b200 import capi
 
@@ -49,3 +51,29 @@ def test_product_does_not_touch_the_oracle():
                     assert bad not in txt, (f, bad)
     out = subprocess.check_output(["ldd", harfang3d_b200.library_path()], text=True)
     assert "hg_port" not in out and "hg_ref" not in out
+
+
+def test_no_contracted_float_math_in_the_kernels():
+    """Bit-exactness with the reference's x86-64 build rests on FP32 multiplies and adds never being fused. -fmad=false covers the
+    scalar code, but ptxas 12.9 contracts mul.rn.f32x2 -> add.rn.f32x2 into FFMA2 regardless, so the packed products of
+    csrc/hgb_math.cuh must never feed a packed add directly. Guard: no FFMA2 anywhere in the library's SASS, and scalar FFMA only in
+    the kernels that divide (IEEE division expands to FFMA sequences): the track samplers."""
+    import shutil
+    import subprocess
+    from harfang3d_b200 import capi
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(capi.library_path()) or not os.path.exists(cuobjdump):
+        pytest.skip("library or cuobjdump not available")
+    sass = subprocess.run([cuobjdump, "-sass", capi.library_path()], capture_output=True, text=True, check=True).stdout
+    fn, ffma, packed = None, {}, 0
+    for line in sass.splitlines():
+        if "Function :" in line:
+            fn = line.split("Function :")[1].strip()
+        elif " FFMA2 " in line:
+            raise AssertionError("FFMA2 (contracted packed multiply-add) in %s" % fn)
+        elif " FFMA " in line or " FFMA." in line:
+            ffma[fn] = ffma.get(fn, 0) + 1
+        elif " FMUL2 " in line:
+            packed += 1
+    assert packed > 0, "the packed products are expected to compile to FMUL2"
+    assert all("k_sample_tracks" in f for f in ffma), "scalar FFMA outside the dividing kernels: %s" % sorted(ffma)

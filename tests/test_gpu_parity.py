@@ -327,7 +327,13 @@ def test_profile_counters(hgb):
     ctx.set_profiling(True)
     ctx.update(None, fused_cull=True)
     prof = ctx.get_profile()
-    assert prof["k_update_level"][1] == 4 and prof["k_update_level"][0] > 0 and prof["k_compact"][1] == 1
+    assert prof["k_update_level"][1] == 4 and prof["k_update_level"][0] > 0 and prof["k_compact"][1] == 1  # one launch per level
+    ctx.close()
+    ctx = hgb.Context(0, merge_small=True)  # the four small levels of the 10k-node scene as ONE cooperative launch
+    hostmirror.upload(ctx, fs)
+    ctx.set_profiling(True)
+    ctx.update(None, fused_cull=True)
+    assert ctx.get_profile()["k_update_level"][1] == 1
     ctx.close()
 
 
