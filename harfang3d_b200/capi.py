@@ -43,6 +43,7 @@ SIGNATURES = {
     "hgb_set_topology": (_i, [_p, _u32, _p, _p]),
     "hgb_upload_trs": (_i, [_p, _u32, _u32, _p]),
     "hgb_set_preset_world": (_i, [_p, _u32, _p, _p]),
+    "hgb_set_matrices": (_i, [_p, _u32, _p, _p, _i]),
     "hgb_set_bounds": (_i, [_p, _u32, _p]),
     "hgb_set_display_entries": (_i, [_p, _i, _u32, _p, _p, _p, _p]),
     "hgb_set_entry_flags": (_i, [_p, _i, _u32, _u32, _p]),
@@ -151,6 +152,10 @@ class Context:
 
     def set_preset_world(self, slots, mats12):
         self._ck(self._L.hgb_set_preset_world(self._h, len(slots), _ptr(slots, np.uint32, "slots"), _ptr(mats12, np.float32, "mats12")))
+
+    def set_matrices(self, slots, mats12, local=False):
+        """batched Scene::SetTransformWorldMatrix (local=False) / SetTransformLocalMatrix (local=True)"""
+        self._ck(self._L.hgb_set_matrices(self._h, len(slots), _ptr(slots, np.uint32, "slots"), _ptr(mats12, np.float32, "mats12"), 1 if local else 0))
 
     def set_bounds(self, minmax6):
         self._ck(self._L.hgb_set_bounds(self._h, minmax6.shape[0], _ptr(minmax6, np.float32, "minmax6")))

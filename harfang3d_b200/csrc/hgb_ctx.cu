@@ -122,6 +122,7 @@ struct hgb_ctx {
 	// topology (host)
 	uint32_t n_slots = 0, n_pos = 0; // n_pos = used slots (positions [0,n_pos) are live; holes get positions >= n_pos)
 	std::vector<uint32_t> pos_of_slot, slot_of_pos, parent_pos_h;
+	std::vector<uint32_t> stamp_w, stamp_r; // hgb_set_matrices: run stamps per position
 	std::vector<uint32_t> level_off; // level d = positions [level_off[d], level_off[d+1])
 	bool identity = true;
 	bool entries_dirty = true; // CSR by position must be rebuilt

@@ -30,6 +30,8 @@ static void interleave_bounds(const float *in, size_t n, std::vector<float> &out
 
 static inline dim3 grid_for(uint32_t n, uint32_t block = 256) { return dim3((n + block - 1) / block); }
 
+static int prepare_tables(hgb_ctx *c);
+
 extern "C" {
 
 int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const uint8_t *used) {
@@ -193,6 +195,57 @@ int hgb_set_preset_world(hgb_ctx *c, uint32_t n, const uint32_t *slot, const flo
 	CK(cudaStreamSynchronize(c->stream));
 	c->n_preset = n;
 	c->preset_pending = n > 0;
+	return 0;
+}
+
+// Scene::SetTransformWorldMatrix (is_local = 0, component.cpp:265-281) / SetTransformLocalMatrix (is_local = 1, :236-248) for a batch of
+// transforms, with the reference's sequential semantics: the batch is cut wherever an entry touches a row an earlier entry of the same
+// launch reads or writes.
+int hgb_set_matrices(hgb_ctx *c, uint32_t n, const uint32_t *slot, const float *mat12, int is_local) {
+	if (!c)
+		return fail("null context");
+	if (!n)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	if (prepare_tables(c)) // triples bound to tracks must be known before TRS rows are written
+		return 1;
+	std::vector<uint32_t> pos(n);
+	for (uint32_t i = 0; i < n; ++i) {
+		if (slot[i] >= c->n_slots || c->pos_of_slot[slot[i]] >= c->n_pos)
+			return fail("hgb_set_matrices: slot %u is not a live transform", slot[i]);
+		pos[i] = c->pos_of_slot[slot[i]];
+	}
+	if (upload(c, c->preset_pos, pos.data(), size_t(n) * 4) || upload(c, c->preset_mat, mat12, size_t(n) * 48))
+		return 1;
+	c->preset_pending = false; // the staging buffers are shared with hgb_set_preset_world
+	c->n_preset = 0;
+	std::vector<uint32_t> &stamp_w = c->stamp_w, &stamp_r = c->stamp_r; // run id in which a position was written / read as a parent
+	stamp_w.assign(c->n_slots, 0);
+	stamp_r.assign(c->n_slots, 0);
+	uint32_t run = 1, first = 0;
+	auto flush = [&](uint32_t end) -> int {
+		if (end > first) {
+			k_set_matrices<<<grid_for(end - first, 128), 128, 0, c->stream>>>(c->preset_pos.as<uint32_t>() + first, c->preset_mat.as<float4>() + size_t(first) * 3,
+				end - first, is_local, c->world[c->cur].as<float>(), c->tiles.as<uint32_t>(), c->anim_val.as<float4>());
+			++c->launches;
+			CK(cudaGetLastError());
+		}
+		first = end;
+		++run;
+		return 0;
+	};
+	for (uint32_t i = 0; i < n; ++i) {
+		const uint32_t p = pos[i], par = c->parent_pos_h[p];
+		const bool clash = stamp_w[p] == run || stamp_r[p] == run || (par != kRoot && stamp_w[par] == run);
+		if (clash && flush(i))
+			return 1;
+		stamp_w[p] = run;
+		if (par != kRoot)
+			stamp_r[par] = run;
+	}
+	if (flush(n))
+		return 1;
+	CK(cudaStreamSynchronize(c->stream)); // pos[] and the caller's matrices are free again
 	return 0;
 }
 

@@ -43,6 +43,26 @@ __device__ __forceinline__ float hermite1(float y0, float y1, float y2, float y3
 	return y1 * a0 + m0 * a1 + m1 * a2 + y2 * a3;
 }
 
+// ToEuler(Mat3, RO_YXZ) foundation/matrix3.cpp:91-137,141-163 (euler_order_yxz: i=1 j=0 k=2; the odd and the left-handed negations
+// cancel). atan2 is the double libm function in the reference (float arguments promoted, result narrowed); CUDA's double atan2
+// (<= 2 ulp) narrows to the same float except when the double result sits within ~1e-16 relative of a float rounding boundary —
+// covered by the 1e-5 matrix tolerance.
+__device__ __forceinline__ void mat3_to_euler_yxz(float m00, float m02, float m10, float m11, float m12, float m20, float m22, float &ex, float &ey, float &ez) {
+	const float s1 = -m12;
+	const float c1 = sqrtf(m11 * m11 + m10 * m10);
+	float a0, a2;
+	const float a1 = __double2float_rn(atan2(double(s1), double(c1)));
+	if (c1 > 1.1920929e-07f) {
+		a0 = __double2float_rn(atan2(double(m02), double(m22)));
+		a2 = __double2float_rn(atan2(double(m10), double(m11)));
+	} else {
+		a0 = 0.F;
+		const float sign_s1 = s1 < 0.F ? -1.F : (s1 > 0.F ? 1.F : 0.F);
+		a2 = __double2float_rn(__dmul_rn(double(-sign_s1), atan2(double(-m20), double(m00))));
+	}
+	ex = a1, ey = a0, ez = a2;
+}
+
 // ToEuler(Normalize(q)) engine/scene.cpp:2172 : foundation/quaternion.cpp:57-60 (Normalize), :141-166 (ToMatrix3),
 // foundation/matrix3.cpp:91-137 (ToEuler, euler_order_yxz: i=1 j=0 k=2). atan2 is the double libm function in the reference
 // (float args promoted, result narrowed); CUDA's double atan2 (<= 2 ulp) narrows to the same float except when the double
@@ -66,19 +86,7 @@ __device__ __forceinline__ void quat_to_euler(float x, float y, float z, float w
 	const float m02 = 2.f * (tmp1 + tmp2) * invs;
 	tmp1 = y * z, tmp2 = x * w;
 	const float m12 = 2.f * (tmp1 - tmp2) * invs;
-	const float s1 = -m12;
-	const float c1 = sqrtf(m11 * m11 + m10 * m10);
-	float a0, a2;
-	const float a1 = __double2float_rn(atan2(double(s1), double(c1)));
-	if (c1 > 1.1920929e-07f) {
-		a0 = __double2float_rn(atan2(double(m02), double(m22)));
-		a2 = __double2float_rn(atan2(double(m10), double(m11)));
-	} else {
-		a0 = 0.F;
-		const float sign_s1 = s1 < 0.F ? -1.F : (s1 > 0.F ? 1.F : 0.F);
-		a2 = __double2float_rn(__dmul_rn(double(-sign_s1), atan2(double(-m20), double(m00))));
-	}
-	ex = a1, ey = a0, ez = a2;
+	mat3_to_euler_yxz(m00, m02, m10, m11, m12, m20, m22, ex, ey, ez);
 }
 
 // Interval records. The sampler's HBM traffic is one gather per track per frame; measured on the B200 (profiles/README.md r01c), a
@@ -323,6 +331,80 @@ __global__ void __launch_bounds__(256) k_sort_keys(SortKeyDev d, uint32_t capaci
 	if (depth < 0.f)
 		depth = 0.f;
 	d.keys[i] = uint32_t(__float2ll_rz(depth * 1000.f)); // x86-64 converts through a 64-bit integer and keeps the low word
+}
+
+// ---- Scene::SetTransformWorldMatrix / SetTransformLocalMatrix, batched --------------------------------------------------------------
+// engine/component.cpp:265-281 / :236-248: the world row is written, local = InverseFast(world[parent]) * world (or the given local,
+// with world = world[parent] * local) and Decompose(local) (foundation/matrix4.cpp:208-252) refreshes the transform's TRS, Euler angles
+// through ToEuler. The host splits a batch into launches such that no entry reads or rewrites a row another entry of the same launch
+// writes, so a batch behaves like the reference's sequential calls.
+__device__ __forceinline__ Mat4 inverse_fast(const Mat4 &m) { // foundation/matrix4.cpp:293-303
+	float sc[3];
+#pragma unroll
+	for (int c = 0; c < 3; ++c)
+		sc[c] = 1.F / (m.m[0][c] * m.m[0][c] + m.m[1][c] * m.m[1][c] + m.m[2][c] * m.m[2][c]);
+	Mat4 o;
+#pragma unroll
+	for (int r = 0; r < 3; ++r)
+#pragma unroll
+		for (int c = 0; c < 3; ++c)
+			o.m[r][c] = m.m[c][r] * sc[r];
+	const float tx = -m.m[0][3], ty = -m.m[1][3], tz = -m.m[2][3];
+#pragma unroll
+	for (int r = 0; r < 3; ++r)
+		o.m[r][3] = o.m[r][0] * tx + o.m[r][1] * ty + o.m[r][2] * tz;
+	return o;
+}
+
+__global__ void __launch_bounds__(128) k_set_matrices(const uint32_t *__restrict__ pos, const float4 *__restrict__ mats, uint32_t n, int is_local,
+	float *__restrict__ world, uint32_t *__restrict__ tiles, float4 *__restrict__ anim_val) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n)
+		return;
+	const uint32_t p = pos[i];
+	const float4 r0 = mats[i * 3], r1 = mats[i * 3 + 1], r2 = mats[i * 3 + 2];
+	Mat4 given;
+	given.m[0][0] = r0.x, given.m[0][1] = r0.y, given.m[0][2] = r0.z, given.m[0][3] = r0.w;
+	given.m[1][0] = r1.x, given.m[1][1] = r1.y, given.m[1][2] = r1.z, given.m[1][3] = r1.w;
+	given.m[2][0] = r2.x, given.m[2][1] = r2.y, given.m[2][2] = r2.z, given.m[2][3] = r2.w;
+	uint32_t *d = tiles + tile_word(p, 0);
+	const uint32_t par = d[kRowParent * 32];
+	Mat4 local = given, wrld = given;
+	if (par != kRoot) {
+		const Mat4 pw = load_mat4(world + size_t(par) * 12);
+		if (is_local)
+			wrld = mat4_mul(pw, given);
+		else
+			local = mat4_mul(inverse_fast(pw), given);
+	}
+	store_mat4(world + size_t(p) * 12, wrld);
+	// Decompose(local): position, scale (negative scale folded into x), renormalised axes -> Euler YXZ
+	const float vx[3] = {local.m[0][0], local.m[1][0], local.m[2][0]}, vy[3] = {local.m[0][1], local.m[1][1], local.m[2][1]},
+				vz[3] = {local.m[0][2], local.m[1][2], local.m[2][2]};
+	float sx = sqrtf(vx[0] * vx[0] + vx[1] * vx[1] + vx[2] * vx[2]);
+	const float sy = sqrtf(vy[0] * vy[0] + vy[1] * vy[1] + vy[2] * vy[2]);
+	const float sz = sqrtf(vz[0] * vz[0] + vz[1] * vz[1] + vz[2] * vz[2]);
+	const float lx = vy[1] * vz[2] - vy[2] * vz[1], ly = vy[2] * vz[0] - vy[0] * vz[2], lz = vy[0] * vz[1] - vy[1] * vz[0]; // Cross(vy, vz)
+	if (lx * vx[0] + ly * vx[1] + lz * vx[2] < 0.f)
+		sx = -sx;
+	float m[3][3]; // column c = axis c / its scale (identity axis when the scale is 0)
+#pragma unroll
+	for (int r = 0; r < 3; ++r) {
+		m[r][0] = sx ? vx[r] / sx : (r == 0 ? 1.f : 0.f);
+		m[r][1] = sy ? vy[r] / sy : (r == 1 ? 1.f : 0.f);
+		m[r][2] = sz ? vz[r] / sz : (r == 2 ? 1.f : 0.f);
+	}
+	float ex, ey, ez;
+	mat3_to_euler_yxz(m[0][0], m[0][2], m[1][0], m[1][1], m[1][2], m[2][0], m[2][2], ex, ey, ez);
+	const float trs[9] = {local.m[0][3], local.m[1][3], local.m[2][3], ex, ey, ez, sx, sy, sz};
+	const uint32_t meta = d[kRowEntMeta * 32];
+#pragma unroll
+	for (int g = 0; g < 3; ++g) {
+		if (meta & (kLaneAnimated << g)) // track-driven triple: the value lives in anim_val
+			anim_val[d[g * 96]] = make_float4(trs[g * 3], trs[g * 3 + 1], trs[g * 3 + 2], 0.f);
+		else
+			d[g * 96] = __float_as_uint(trs[g * 3]), d[g * 96 + 32] = __float_as_uint(trs[g * 3 + 1]), d[g * 96 + 64] = __float_as_uint(trs[g * 3 + 2]);
+	}
 }
 
 // ---- layout shuffles -----------------------------------------------------------------------------------------------------

@@ -85,6 +85,12 @@ int hgb_upload_trs(hgb_ctx *, uint32_t first, uint32_t count, const float *trs9)
 /* SetNodeWorldMatrix overrides (scene.cpp:768-786) for the NEXT hgb_update only. */
 int hgb_set_preset_world(hgb_ctx *, uint32_t n, const uint32_t *slot, const float *mat12);
 
+/* Scene::SetTransformWorldMatrix (is_local = 0, harfang/engine/component.cpp:265-281) or SetTransformLocalMatrix (is_local = 1, :236-248) for
+ * a batch of transforms, applied immediately with the reference's sequential semantics: the current world row is written, the local matrix
+ * is InverseFast(world[parent]) * world (resp. world = world[parent] * local), and Decompose (foundation/matrix4.cpp:208-252) refreshes
+ * pos / Euler rot / scale of the transform (read back with hgb_get_trs). The physics-sync and script use case of SURVEY.md §8f-2. */
+int hgb_set_matrices(hgb_ctx *, uint32_t n, const uint32_t *slot, const float *mat12, int is_local);
+
 /* MinMax table: Model::bounds of every (model, list) in use (render_pipeline.h:419-424). */
 int hgb_set_bounds(hgb_ctx *, uint32_t n_bounds, const float *minmax6);
 /* Display entries of one kind, in the reference's emission order (node index x list index, scene.cpp:330-364).
