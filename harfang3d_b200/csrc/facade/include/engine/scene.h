@@ -122,6 +122,12 @@ public:
 	void SetNodeTransform(NodeRef ref, const Transform &v) { SetNodeTransform(ref, v.ref); }
 	Mat4 GetNodeWorldMatrix(NodeRef ref) const;            // scene.cpp:750-766
 	void SetNodeWorldMatrix(NodeRef ref, const Mat4 &world); // scene.cpp:768-786: wins over ComputeWorldMatrices for this frame
+	// component.cpp:236-281: the world row is written at once and the transform's TRS is refreshed from Decompose(local). Consecutive calls
+	// are queued and reach the device as ONE batched hgb_set_matrices (sequential semantics kept) at the next read or frame.
+	void SetTransformLocalMatrix(ComponentRef ref, const Mat4 &local);
+	void SetTransformWorldMatrix(ComponentRef ref, const Mat4 &world);
+	Mat4 GetTransformWorldMatrix(uint32_t transform_idx) const;         // component.cpp:250-256
+	Mat4 GetPreviousTransformWorldMatrix(uint32_t transform_idx) const; // component.cpp:258-264
 
 	// ---- objects (scene.h:327-358) ----
 	Object CreateObject();
@@ -222,6 +228,8 @@ private:
 
 	bool EnsureContext() const;
 	void RefreshTRSFromDevice() const;
+	void QueueMatrixSet(uint32_t slot, const Mat4 &m, bool is_local);
+	void FlushMatrixSets() const;
 	bool SyncEdits(const PipelineResources *resources);
 };
 

@@ -37,6 +37,9 @@ struct Scene::Impl {
 	std::vector<Frustum> frusta;
 	std::vector<uint32_t> preset_slots;
 	std::vector<float> preset_mats;
+	std::vector<uint32_t> set_slots; // queued SetTransformWorld/LocalMatrix calls (one mode per queue)
+	std::vector<float> set_mats;
+	bool set_local{false};
 	std::vector<int64_t> play_t;        // evaluation time per play slot (HGB_NOT_PLAYING when idle)
 	std::vector<float> staging;
 	// fused culling: the entry tables given to the device (every entry, disabled ones flagged) and what they map back to
@@ -185,6 +188,7 @@ void Scene::DestroyTransform(ComponentRef ref) {
 
 // The device samples bound tracks straight into its TRS; the host copy is refreshed on the first host access after such a frame.
 void Scene::RefreshTRSFromDevice() const {
+	FlushMatrixSets();
 	if (!trs_host_stale)
 		return;
 	trs_host_stale = false;
@@ -327,6 +331,71 @@ void Scene::SetNodeWorldMatrix(NodeRef ref, const Mat4 &world) {
 	impl->preset_mats.insert(impl->preset_mats.end(), &world.m[0][0], &world.m[0][0] + 12);
 	if (worlds_valid && t.idx < transform_worlds.size())
 		transform_worlds[t.idx] = world;
+}
+
+// SetTransformLocalMatrix / SetTransformWorldMatrix (component.cpp:236-248, :265-281). The reference does the work per call on the host;
+// here calls are queued and one hgb_set_matrices launch applies the batch in call order (InverseFast(world[parent]) * world, Decompose, TRS and
+// world rows written on the device).
+void Scene::QueueMatrixSet(uint32_t slot, const Mat4 &m, bool is_local) {
+	if (!impl->set_slots.empty() && impl->set_local != is_local)
+		FlushMatrixSets();
+	impl->set_local = is_local;
+	impl->set_slots.push_back(slot);
+	impl->set_mats.insert(impl->set_mats.end(), &m.m[0][0], &m.m[0][0] + 12);
+}
+
+void Scene::FlushMatrixSets() const {
+	if (impl->set_slots.empty())
+		return;
+	std::vector<uint32_t> slots;
+	std::vector<float> mats;
+	slots.swap(impl->set_slots), mats.swap(impl->set_mats); // SyncEdits below comes back through RefreshTRSFromDevice
+	Scene *self = const_cast<Scene *>(this);
+	if (!self->SyncEdits(impl->resources))
+		return;
+	check(hgb_set_matrices(ctx, uint32_t(slots.size()), slots.data(), mats.data(), impl->set_local ? 1 : 0));
+	trs_host_stale = true; // the decomposed TRS lives on the device
+	worlds_valid = false;
+}
+
+void Scene::SetTransformLocalMatrix(ComponentRef ref, const Mat4 &local) {
+	if (!transforms.is_valid(ref)) {
+		warn("Invalid transform component");
+		return;
+	}
+	if (ref.idx >= transform_worlds.size()) { // the reference writes transform_worlds[ref.idx] unchecked; refuse instead of corrupting
+		warn("Invalid transform index");
+		return;
+	}
+	QueueMatrixSet(ref.idx, local, true);
+}
+
+void Scene::SetTransformWorldMatrix(ComponentRef ref, const Mat4 &world) {
+	if (!transforms.is_valid(ref)) {
+		warn("Invalid transform component");
+		return;
+	}
+	if (ref.idx >= transform_worlds.size()) {
+		warn("Invalid transform index");
+		return;
+	}
+	QueueMatrixSet(ref.idx, world, false);
+}
+
+Mat4 Scene::GetTransformWorldMatrix(const uint32_t transform_idx) const {
+	const std::vector<Mat4> &w = GetTransformWorldMatrices();
+	if (transform_idx < w.size())
+		return w[transform_idx];
+	warn("Invalid transform index");
+	return Mat4::Identity;
+}
+
+Mat4 Scene::GetPreviousTransformWorldMatrix(const uint32_t transform_idx) const {
+	const std::vector<Mat4> &p = GetPreviousTransformWorldMatrices();
+	if (transform_idx < p.size())
+		return p[transform_idx];
+	warn("Invalid transform index");
+	return GetTransformWorldMatrix(transform_idx);
 }
 
 // ---- objects -----------------------------------------------------------------------------------------------------------------
@@ -514,6 +583,7 @@ static void build_bounds(const PipelineResources &res, std::vector<float> &bound
 bool Scene::SyncEdits(const PipelineResources *resources) {
 	if (!EnsureContext())
 		return false;
+	FlushMatrixSets(); // queued SetTransformWorld/LocalMatrix calls come before whatever was edited after them
 	const uint32_t n = uint32_t(transforms.capacity());
 
 	if (impl->topology_dirty) {
@@ -760,6 +830,7 @@ static void download_worlds(hgb_ctx *ctx, std::vector<Mat4> &dst, size_t capacit
 }
 
 const std::vector<Mat4> &Scene::GetTransformWorldMatrices() const {
+	FlushMatrixSets();
 	if (!worlds_valid) {
 		if (ctx && !impl->topology_dirty)
 			download_worlds(ctx, transform_worlds, transforms.capacity(), false);

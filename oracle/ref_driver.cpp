@@ -399,6 +399,15 @@ void hgref_inverse_fast(const float *a12, float *out12) {
 	const Mat4 m = InverseFast(mat4_from(a12));
 	memcpy(out12, m.m, 48);
 }
+// Scene::SetTransformWorldMatrix / SetTransformLocalMatrix (engine/component.cpp:265-281, :236-248) on the transform of a node
+void hgref_set_transform_matrix(void *h, int node, const float *m12, int is_local) {
+	auto *c = static_cast<RefCtx *>(h);
+	const auto ref = c->scene->GetNodeTransformRef(c->nodes[node]);
+	if (is_local)
+		c->scene->SetTransformLocalMatrix(ref, mat4_from(m12));
+	else
+		c->scene->SetTransformWorldMatrix(ref, mat4_from(m12));
+}
 #ifndef HG_FACADE // reference-internal host math (the facade computes these on the device only)
 void hgref_minmax_transform(const float *m12, const float *mm6, float *out6) {
 	const MinMax o = mat4_from(m12) * MinMax(Vec3(mm6[0], mm6[1], mm6[2]), Vec3(mm6[3], mm6[4], mm6[5]));

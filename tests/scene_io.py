@@ -86,6 +86,10 @@ class RefScene:
         self.L.hgref_read_skinned_lists(self.h, kind, P(mi), P(bi), P(bc), P(mdl), P(lst))
         return mi[:n], bi[:n], bc[:n], mdl[:n], lst[:n]
 
+    def set_transform_matrix(self, node, m12, local=False):
+        """Scene::SetTransformWorldMatrix / SetTransformLocalMatrix"""
+        self.L.hgref_set_transform_matrix(self.h, int(node), P(np.ascontiguousarray(m12, np.float32).reshape(12)), 1 if local else 0)
+
     def sort_keys(self, view12):
         """ComputeModelDisplayListSortKeys over the list left by the last cull()"""
         v = np.ascontiguousarray(view12, np.float32).reshape(12)

@@ -272,6 +272,61 @@ def test_preset_world_matrices(hgb, oracles):
     orc.close(); ctx.close()
 
 
+def _random_affine(rng, n, negative_every=7):
+    """world matrices = T * R(YXZ euler) * S with some negative and some tiny scales (Decompose's sign fold, matrix4.cpp:226-229)"""
+    from tests import oracle_lib
+    port = oracle_lib.load_port()
+    trs = np.zeros((n, 9), np.float32)
+    trs[:, 0:3] = rng.uniform(-30, 30, (n, 3))
+    trs[:, 3:6] = rng.uniform(-np.pi, np.pi, (n, 3))
+    trs[:, 6:9] = rng.uniform(0.25, 3.0, (n, 3))
+    trs[::negative_every, 6] *= -1
+    out = np.zeros((n, 12), np.float32)
+    for i in range(n):
+        port.hgp_transformation_mat4(oracle_lib.P(trs[i]), oracle_lib.P(out[i]))
+    return out
+
+
+@pytest.mark.parametrize("local", [False, True])
+def test_set_transform_matrices_batched(hgb, oracles, local):
+    """Scene::SetTransformWorldMatrix / SetTransformLocalMatrix (component.cpp:265-281, :236-248) as one batched device call: world rows
+    bit-identical, the decomposed TRS within 1e-5 (Euler angles go through libm's double atan2), sequential semantics when a batch sets a
+    node and its parent, and the next Update propagates from the refreshed TRS."""
+    ref, _ = oracles
+    if ref is None:
+        pytest.skip("needs the compiled reference")
+    from tests.scene_io import RefScene
+    fs = scenegen.static_scene(6_000, 5, 6, n_models=2, seed=61)
+    rng = np.random.default_rng(62)
+    ctx = hgb.Context(0)
+    t = hostmirror.upload(ctx, fs)
+    orc = RefScene(ref, fs)
+    ctx.update(None, fused_cull=True)
+    orc.update(0)
+    # 500 random nodes + 200 (child, parent, child-again) chains: read-after-write and write-after-write inside one batch
+    picks = rng.choice(fs.n, 500, replace=False)
+    kids = rng.choice(np.nonzero(fs.parent >= 0)[0], 200, replace=False)
+    chain = np.stack([kids, fs.parent[kids], kids], 1).reshape(-1)
+    slots = np.concatenate([picks, chain, picks[:50]]).astype(np.uint32)
+    mats = _random_affine(rng, len(slots))
+    for s, m in zip(slots, mats):
+        orc.set_transform_matrix(int(s), m, local)
+    ctx.set_matrices(slots, mats, local)
+    w, w_ref = ctx.get_worlds(), orc.worlds()[: fs.n]
+    assert (bits(w) == bits(w_ref)).all(), "world rows after the batched set differ"
+    touched = np.unique(slots)
+    trs, trs_ref = ctx.get_trs()[touched], orc.trs(touched)
+    assert rel_err(trs, trs_ref) <= REL_TOL
+    print("set_matrices(local=%s): decomposed TRS bit-identical on %d of %d values" % (local, int((bits(trs) == bits(trs_ref)).sum()), trs.size))
+    untouched = np.setdiff1d(np.arange(fs.n), touched)
+    assert (bits(ctx.get_trs()[untouched]) == bits(np.ascontiguousarray(fs.trs, np.float32)[untouched])).all(), "rows of other transforms were disturbed"
+    # the next frame recomputes every world from the TRS (reference: Update -> ComputeWorldMatrices)
+    ctx.update(None, fused_cull=True)
+    orc.update(0)
+    assert rel_err(ctx.get_worlds(), orc.worlds()[: fs.n]) <= 1e-4  # TRS within 1e-5, composed through up to 5 levels
+    orc.close(); ctx.close()
+
+
 def test_c5_small_instance_batch(hgb, oracles):
     """BASELINE config 5 at 24 instances x 2048 nodes: one camera per instance; per-instance visible lists = the reference's
     CullModelDisplayLists run per instance scene"""
