@@ -12,7 +12,7 @@ ENTRY_DISABLED = 0x01
 KIND_OPAQUE, KIND_TRANSPARENT = 0, 1
 
 
-KERNEL_CLASSES = ("k_sample_tracks", "k_update_level", "k_compact", "k_segment_ranks", "k_cull_flags", "k_bone_matrices", "k_sort_keys")
+KERNEL_CLASSES = ("k_sample_tracks", "k_update_level", "k_compact", "k_segment_ranks", "k_cull_flags", "k_bone_matrices", "k_sort_keys", "k_minmax")
 
 
 class HgbError(RuntimeError):
@@ -57,6 +57,9 @@ SIGNATURES = {
     "hgb_cull_list": (_i, [_p, _u32, _p, _p, _u32, _p, _p, _p, _p]),
     "hgb_bone_matrices": (_i, [_p, _i]),
     "hgb_sort_keys": (_i, [_p, _i, _u32, _p]),
+    "hgb_set_objects": (_i, [_p, _u32, _p, _p, _u32, _p, _p, _u32]),
+    "hgb_minmax": (_i, [_p]),
+    "hgb_get_minmax": (_i, [_p, _p, _p]),
     "hgb_get_sort_keys": (_i, [_p, _i, _u32, _p, _u32, _p]),
     "hgb_get_worlds": (_i, [_p, _u32, _u32, _p, _i]),
     "hgb_get_trs": (_i, [_p, _u32, _u32, _p]),
@@ -214,6 +217,21 @@ class Context:
         out, n = np.empty(max(self.n_entries[kind], 1), np.uint32), C.c_uint32(0)
         self._ck(self._L.hgb_get_sort_keys(self._h, kind, view, _ptr(out, np.uint32, "out"), len(out), C.byref(n)))
         return out[: n.value]
+
+    def set_objects(self, mtx_slot, obounds_idx, obounds6, seg=None, n_seg=1):
+        """object-carrying nodes for Scene::GetMinMax / GetNodesMinMax (one segment per scene instance)"""
+        self.n_seg = n_seg
+        self._ck(self._L.hgb_set_objects(self._h, len(mtx_slot), _ptr(mtx_slot, np.uint32, "mtx_slot"), _ptr(obounds_idx, np.uint32, "obounds_idx"),
+                                         obounds6.shape[0], _ptr(obounds6, np.float32, "obounds6"), _ptr(seg, np.uint32, "seg"), n_seg))
+
+    def minmax(self, fetch=True):
+        """-> (minmax[n_seg, 6], contributing node count[n_seg])"""
+        self._ck(self._L.hgb_minmax(self._h))
+        if not fetch:
+            return None
+        out, cnt = np.zeros((self.n_seg, 6), np.float32), np.zeros(self.n_seg, np.uint32)
+        self._ck(self._L.hgb_get_minmax(self._h, _ptr(out, np.float32, "out"), _ptr(cnt, np.uint32, "cnt")))
+        return out, cnt
 
     def bone_matrices(self, with_previous=False):
         self._ck(self._L.hgb_bone_matrices(self._h, 1 if with_previous else 0))

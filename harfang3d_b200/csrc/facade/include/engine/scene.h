@@ -64,7 +64,10 @@ struct Node {
 	void SetObject(const Object &o);
 	Mat4 GetWorld() const;
 	void SetWorld(const Mat4 &m);
+	bool GetMinMax(const PipelineResources &resources, MinMax &minmax) const; // node.cpp:106-119 (object nodes; no instance views here)
 };
+// node.cpp:265-285: union of the nodes' world-space bounding boxes — a device reduction over the scene's current world matrices
+bool GetNodesMinMax(const std::vector<Node> &nodes, const PipelineResources &resources, MinMax &minmax);
 
 struct NodeAnim { // scene.h:104-107
 	NodeRef node;
@@ -94,6 +97,8 @@ public:
 	void DestroyNode(NodeRef ref);
 	void DestroyNode(const Node &node) { DestroyNode(node.ref); }
 	bool IsValidNodeRef(NodeRef ref) const { return nodes.is_valid(ref); }
+	Node GetNode(NodeRef ref) const { return nodes.is_valid(ref) ? Node{const_cast<Scene *>(this), ref} : Node{}; } // scene.cpp:421
+	std::vector<Node> GetNodesWithObject() const; // GetNodesWithComponent(NCI_Object), scene.cpp:604-640
 	void ReserveNodes(size_t count) { nodes.reserve(count); }
 	void EnableNode(NodeRef ref);
 	void DisableNode(NodeRef ref);
@@ -143,6 +148,8 @@ public:
 	bool SetObjectBone(ComponentRef ref, size_t idx, NodeRef bone_node); // component.cpp:679-691
 	NodeRef GetObjectBone(ComponentRef ref, size_t idx) const;
 	ComponentRef GetNodeObjectRef(NodeRef ref) const;
+	bool GetObjectMinMax(ComponentRef ref, const PipelineResources &resources, MinMax &minmax) const; // component.cpp:778-797
+	bool GetMinMax(const PipelineResources &resources, MinMax &minmax) const;                         // scene.cpp:1982
 	void SetNodeObject(NodeRef ref, ComponentRef cref);
 	void SetNodeObject(NodeRef ref, const Object &v) { SetNodeObject(ref, v.ref); }
 
@@ -184,6 +191,7 @@ public:
 	static void SetDefaultDevice(int device);
 
 private:
+	friend bool GetNodesMinMax(const std::vector<Node> &, const PipelineResources &, MinMax &);
 	friend void CullModelDisplayLists(const Frustum &, std::vector<ModelDisplayList> &, const std::vector<Mat4> &, const PipelineResources &);
 	friend size_t ComputeSkinMatrices(const std::vector<SkinnedModelDisplayList> &, const std::vector<Mat4> &, const PipelineResources &, std::vector<float> &, bool);
 	struct Impl;

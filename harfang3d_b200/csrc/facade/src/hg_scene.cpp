@@ -848,6 +848,92 @@ const std::vector<Mat4> &Scene::GetPreviousTransformWorldMatrices() const {
 	return previous_transform_worlds;
 }
 
+// ---- bounding boxes ----------------------------------------------------------------------------------------------------------
+// Scene::GetMinMax (scene.cpp:1982) = GetNodesMinMax(GetNodesWithComponent(NCI_Object)) (node.cpp:265-285): the per-node part
+// (world * Union(model bounds), node.cpp:106-119 + component.cpp:778-797) and the union run on the device (hgb_minmax) over the
+// scene's current world matrices; the host only lists which (transform slot, model) pairs take part, like the reference's node walk.
+std::vector<Node> Scene::GetNodesWithObject() const {
+	std::vector<Node> out;
+	for (uint32_t ni = nodes.first(); ni != nodes.invalid_idx; ni = nodes.next(ni))
+		if (objects.is_valid(nodes[ni].object))
+			out.push_back({const_cast<Scene *>(this), nodes.get_ref(ni)});
+	return out;
+}
+
+bool Scene::GetObjectMinMax(ComponentRef ref, const PipelineResources &resources, MinMax &minmax) const {
+	if (!objects.is_valid(ref)) {
+		warn("Invalid object component");
+		return false;
+	}
+	const Object_ &obj = objects[ref.idx];
+	if (!resources.models.IsValidRef(obj.model))
+		return false;
+	const Model &mdl = resources.models.Get_unsafe_(uint16_t(obj.model.ref.idx));
+	if (mdl.bounds.empty())
+		return false;
+	minmax = mdl.bounds[0];
+	for (size_t i = 1; i < mdl.bounds.size(); ++i) { // Union (minmax.h:48): Min/Max per component, `a < b ? a : b`
+		const MinMax &b = mdl.bounds[i];
+		minmax.mn = Vec3(minmax.mn.x < b.mn.x ? minmax.mn.x : b.mn.x, minmax.mn.y < b.mn.y ? minmax.mn.y : b.mn.y, minmax.mn.z < b.mn.z ? minmax.mn.z : b.mn.z);
+		minmax.mx = Vec3(minmax.mx.x > b.mx.x ? minmax.mx.x : b.mx.x, minmax.mx.y > b.mx.y ? minmax.mx.y : b.mx.y, minmax.mx.z > b.mx.z ? minmax.mx.z : b.mx.z);
+	}
+	return true;
+}
+
+bool GetNodesMinMax(const std::vector<Node> &nodes_, const PipelineResources &resources, MinMax &minmax) {
+	if (nodes_.empty())
+		return false;
+	Scene *scene = nullptr;
+	std::vector<uint32_t> slot, ob;
+	std::vector<float> obounds6;
+	std::map<uint32_t, uint32_t> ob_of_model;
+	for (const Node &n : nodes_) {
+		if (!n.scene || !n.scene->nodes.is_valid(n.ref))
+			continue;
+		if (scene && n.scene != scene) {
+			warn("GetNodesMinMax: nodes of different scenes");
+			continue;
+		}
+		scene = n.scene;
+		const Scene::Node_ &node = scene->nodes[n.ref.idx];
+		if (!scene->objects.is_valid(node.object))
+			continue; // HasObject() false and no instance view: Node::GetMinMax returns false
+		MinMax mm;
+		if (!scene->GetObjectMinMax(node.object, resources, mm))
+			continue;
+		const uint32_t mdl = scene->objects[node.object.idx].model.ref.idx;
+		auto it = ob_of_model.find(mdl);
+		if (it == ob_of_model.end()) {
+			it = ob_of_model.emplace(mdl, uint32_t(obounds6.size() / 6)).first;
+			const float v[6] = {mm.mn.x, mm.mn.y, mm.mn.z, mm.mx.x, mm.mx.y, mm.mx.z};
+			obounds6.insert(obounds6.end(), v, v + 6);
+		}
+		slot.push_back(scene->transforms.is_valid(node.transform) ? node.transform.idx : HGB_ROOT); // invalid transform: identity world
+		ob.push_back(it->second);
+	}
+	if (!scene || slot.empty())
+		return false;
+	scene->FlushMatrixSets();
+	if (!scene->ctx || scene->impl->topology_dirty) {
+		warn("GetNodesMinMax: the scene has no world matrices on the device yet (Update first)");
+		return false;
+	}
+	float out6[6];
+	uint32_t count = 0;
+	if (hgb_set_objects(scene->ctx, uint32_t(slot.size()), slot.data(), ob.data(), uint32_t(obounds6.size() / 6), obounds6.data(), nullptr, 1) ||
+		hgb_minmax(scene->ctx) || hgb_get_minmax(scene->ctx, out6, &count)) {
+		warn(hgb_last_error());
+		return false;
+	}
+	if (!count)
+		return false;
+	minmax = MinMax(Vec3(out6[0], out6[1], out6[2]), Vec3(out6[3], out6[4], out6[5]));
+	return true;
+}
+
+bool Scene::GetMinMax(const PipelineResources &resources, MinMax &minmax) const { return GetNodesMinMax(GetNodesWithObject(), resources, minmax); }
+bool Node::GetMinMax(const PipelineResources &resources, MinMax &minmax) const { return GetNodesMinMax({*this}, resources, minmax); }
+
 // ---- display lists (host walk, like the reference: it only reads flags and refs, scene.cpp:318-404) -----------------------------
 void Scene::GetModelDisplayLists(std::vector<ModelDisplayList> &out_opaque, std::vector<ModelDisplayList> &out_transparent,
 	std::vector<SkinnedModelDisplayList> &out_opaque_skinned, std::vector<SkinnedModelDisplayList> &out_transparent_skinned,

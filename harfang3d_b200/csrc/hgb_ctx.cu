@@ -164,6 +164,12 @@ struct hgb_ctx {
 	DBuf bone_mtx_pos, bone_bind_idx, bind_pose, bone_out[2];
 	std::vector<uint32_t> bone_mtx_slot;
 
+	// scene / instance bounding boxes (hgb_set_objects, hgb_minmax)
+	std::vector<uint32_t> obj_slot_h, obj_ob_h, obj_seg_h;
+	uint32_t n_obj = 0, n_obounds = 0, n_seg = 0;
+	bool obj_dirty = true;
+	DBuf obj_pos, obj_meta, obj_seg, obounds, mm_acc;
+
 	// animation
 	DBuf keys, cursor, tracks_d, play_t_d; // keys: 32-byte records, vec3 keys then quaternion keys
 	DBuf key_rec;                          // 128-byte interval records, one per key (k_build_key_records)

@@ -419,6 +419,90 @@ int hgb_bone_matrices(hgb_ctx *c, int with_previous) {
 	return 0;
 }
 
+// Scene::GetMinMax / GetNodesMinMax: objects are resolved to positions and sorted by position (the union is order-independent), so the
+// world rows are read in ascending address order
+static int resolve_objects(hgb_ctx *c) {
+	if (!c->obj_dirty)
+		return 0;
+	const uint32_t n = c->n_obj;
+	std::vector<uint64_t> order(n);
+	for (uint32_t i = 0; i < n; ++i) {
+		const uint32_t sl = c->obj_slot_h[i];
+		uint32_t p = kRoot;
+		if (sl != HGB_ROOT) {
+			if (sl >= c->n_slots || c->pos_of_slot[sl] >= c->n_pos)
+				return fail("hgb_minmax: object %u references slot %u which is not a live transform", i, sl);
+			p = c->pos_of_slot[sl];
+		}
+		order[i] = (uint64_t(p) << 32) | i;
+	}
+	std::sort(order.begin(), order.end());
+	std::vector<uint32_t> pos(n), meta(n), seg(c->obj_seg_h.empty() ? 0 : n);
+	for (uint32_t k = 0; k < n; ++k) {
+		const uint32_t i = uint32_t(order[k]);
+		pos[k] = uint32_t(order[k] >> 32);
+		meta[k] = c->obj_ob_h[i];
+		if (!seg.empty())
+			seg[k] = c->obj_seg_h[i];
+	}
+	if (upload(c, c->obj_pos, pos.data(), size_t(n) * 4) || upload(c, c->obj_meta, meta.data(), size_t(n) * 4) ||
+		upload(c, c->obj_seg, seg.data(), seg.size() * 4))
+		return 1;
+	CK(c->mm_acc.reserve(std::max<size_t>(c->n_seg, 1) * 32));
+	CK(cudaStreamSynchronize(c->stream));
+	c->obj_dirty = false;
+	return 0;
+}
+
+int hgb_minmax(hgb_ctx *c) {
+	if (!c)
+		return fail("null context");
+	CK(cudaSetDevice(c->device));
+	if (resolve_objects(c))
+		return 1;
+	if (!c->n_seg)
+		return 0;
+	k_minmax_init<<<grid_for(c->n_seg * 8), 256, 0, c->stream>>>(c->mm_acc.as<uint32_t>(), c->n_seg);
+	++c->launches;
+	if (c->n_obj) {
+		MinMaxDev d{};
+		d.obj_pos = c->obj_pos.as<uint32_t>();
+		d.obj_meta = c->obj_meta.as<uint32_t>();
+		d.obj_seg = c->obj_seg_h.empty() ? nullptr : c->obj_seg.as<uint32_t>();
+		d.world = c->world[c->cur].as<float>();
+		d.obounds6 = c->obounds.as<float>();
+		d.acc = c->mm_acc.as<uint32_t>();
+		d.n = c->n_obj;
+		prof_begin(c, HGB_K_MINMAX);
+		k_minmax<<<grid_for(d.n), 256, 0, c->stream>>>(d);
+		prof_end(c);
+		++c->launches;
+	}
+	CK(cudaGetLastError());
+	return 0;
+}
+
+int hgb_get_minmax(hgb_ctx *c, float *out6, uint32_t *out_count) {
+	if (!c)
+		return fail("null context");
+	if (!c->n_seg)
+		return 0;
+	if (!c->mm_acc.p || c->obj_dirty)
+		return fail("hgb_get_minmax: hgb_minmax has not run since the objects or the hierarchy changed");
+	CK(cudaSetDevice(c->device));
+	CK(c->staging.reserve(size_t(c->n_seg) * 32));
+	CK(cudaMemcpyAsync(c->staging.p, c->mm_acc.p, size_t(c->n_seg) * 32, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	const uint32_t *a = c->staging.as<uint32_t>();
+	for (uint32_t s = 0; s < c->n_seg; ++s) {
+		for (int j = 0; j < 6; ++j)
+			out6[size_t(s) * 6 + j] = key_float(a[size_t(s) * 8 + j]);
+		if (out_count)
+			out_count[s] = a[size_t(s) * 8 + 6];
+	}
+	return 0;
+}
+
 // ComputeModelDisplayListSortKeys for the visible list (kind, view) of the last cull
 int hgb_sort_keys(hgb_ctx *c, int kind, uint32_t view, const float *view_mat12) {
 	if (!c)

@@ -157,6 +157,7 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 	c->level_off.swap(level_off);
 	c->identity = identity;
 	c->entries_dirty = true;
+	c->obj_dirty = true;
 	invalidate_graph(c);
 	return 0;
 }
@@ -246,6 +247,37 @@ int hgb_set_matrices(hgb_ctx *c, uint32_t n, const uint32_t *slot, const float *
 	if (flush(n))
 		return 1;
 	CK(cudaStreamSynchronize(c->stream)); // pos[] and the caller's matrices are free again
+	return 0;
+}
+
+int hgb_set_objects(hgb_ctx *c, uint32_t n_obj, const uint32_t *mtx_slot, const uint32_t *obounds_idx, uint32_t n_obounds, const float *obounds6,
+	const uint32_t *seg, uint32_t n_seg) {
+	if (!c)
+		return fail("null context");
+	if (n_obounds >= (1u << 24))
+		return fail("hgb_set_objects: too many object bounds");
+	if (n_obj && n_seg == 0)
+		return fail("hgb_set_objects: at least one segment is needed");
+	for (uint32_t i = 0; i < n_obj; ++i) {
+		if (obounds_idx[i] >= n_obounds)
+			return fail("hgb_set_objects: object %u references bounds %u outside the table", i, obounds_idx[i]);
+		if (seg && seg[i] >= n_seg)
+			return fail("hgb_set_objects: object %u is in segment %u of %u", i, seg[i], n_seg);
+	}
+	CK(cudaSetDevice(c->device));
+	c->obj_slot_h.assign(mtx_slot, mtx_slot + n_obj);
+	c->obj_ob_h.assign(obounds_idx, obounds_idx + n_obj);
+	if (seg)
+		c->obj_seg_h.assign(seg, seg + n_obj);
+	else
+		c->obj_seg_h.clear();
+	c->n_obj = n_obj, c->n_obounds = n_obounds, c->n_seg = n_seg;
+	std::vector<float> il;
+	interleave_bounds(obounds6, n_obounds, il);
+	if (upload(c, c->obounds, il.data(), size_t(n_obounds) * 24))
+		return 1;
+	CK(cudaStreamSynchronize(c->stream));
+	c->obj_dirty = true;
 	return 0;
 }
 

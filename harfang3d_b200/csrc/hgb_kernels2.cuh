@@ -287,6 +287,113 @@ __global__ void __launch_bounds__(256) k_bone_matrices(BoneDev b) {
 		store_bgfx(b.out_prev + size_t(i) * 16, mat4_mul(load_mat4(b.world_prev + size_t(mp) * 12), bind));
 }
 
+// ---- scene / instance bounding boxes ---------------------------------------------------------------------------------------------
+// Scene::GetMinMax (engine/scene.cpp:1982) -> GetNodesMinMax (engine/node.cpp:265-285): union over the nodes that carry an Object of
+// world[node transform] * Union(model.bounds[*]) (Node::GetMinMax node.cpp:106-119, Scene::GetObjectMinMax component.cpp:778-797,
+// operator*(Mat4, MinMax) foundation/minmax.cpp:226-244, Union minmax.h). min/max are exact and order-independent, so the device
+// reduces in POSITION order (coalesced world rows) with segment ids = scene instances; a warp whose 32 objects share a segment
+// reduces by shuffles and issues 6 atomics, otherwise lanes are grouped with match.any. Floats are reduced as order-preserving
+// unsigned keys (atomicMin/atomicMax on u32).
+struct MinMaxDev {
+	const uint32_t *obj_pos;   // per object: position of the node's transform, kRoot = no transform (identity world), ascending
+	const uint32_t *obj_meta;  // per object: object-bounds index (bits 0..23)
+	const uint32_t *obj_seg;   // per object: segment (instance) id, or null = one segment
+	const float *world;
+	const float *obounds6;     // interleaved {mn.x, mx.x, mn.y, mx.y, mn.z, mx.z} per model: union of its lists' bounds
+	uint32_t *acc;             // per segment: 6 keys {mn.xyz (atomicMin), mx.xyz (atomicMax)} + count at [6]; 8 words per segment
+	uint32_t n;
+};
+
+__device__ __forceinline__ uint32_t float_key(float f) {
+	const uint32_t b = __float_as_uint(f);
+	return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float key_float(uint32_t k) {
+	const uint32_t b = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+#ifdef __CUDA_ARCH__
+	return __uint_as_float(b);
+#else
+	float f;
+	memcpy(&f, &b, 4);
+	return f;
+#endif
+}
+
+__global__ void __launch_bounds__(256) k_minmax_init(uint32_t *acc, uint32_t n_seg) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n_seg * 8u) {
+		const uint32_t w = i & 7u;
+		acc[i] = w < 3 ? 0xffffffffu : 0u;
+	}
+}
+
+__global__ void __launch_bounds__(256) k_minmax(MinMaxDev d) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	const bool live = i < d.n;
+	uint32_t seg = 0xffffffffu;
+	uint32_t k[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+	if (live) {
+		seg = d.obj_seg ? d.obj_seg[i] : 0u;
+		const uint32_t p = d.obj_pos[i];
+		Mat4 w;
+		if (p != kRoot) {
+			w = load_mat4(d.world + size_t(p) * 12);
+		} else { // Transform::GetWorld on an invalid transform returns Mat4::Identity (component.cpp:250-256)
+#pragma unroll
+			for (int r = 0; r < 3; ++r)
+#pragma unroll
+				for (int c = 0; c < 4; ++c)
+					w.m[r][c] = r == c ? 1.f : 0.f;
+		}
+		const Aabb bb = minmax_transform(w, d.obounds6 + size_t(d.obj_meta[i] & 0xffffffu) * 6);
+#pragma unroll
+		for (int j = 0; j < 3; ++j)
+			k[j] = float_key(bb.mn[j]), k[3 + j] = float_key(bb.mx[j]);
+	}
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t peers = __match_any_sync(0xffffffffu, seg);
+	uint32_t cnt = live ? 1u : 0u;
+	if (peers == 0xffffffffu) { // the whole warp is one segment: butterfly reduction
+#pragma unroll
+		for (int s = 16; s > 0; s >>= 1) {
+#pragma unroll
+			for (int j = 0; j < 3; ++j) {
+				k[j] = min(k[j], __shfl_xor_sync(0xffffffffu, k[j], s));
+				k[3 + j] = max(k[3 + j], __shfl_xor_sync(0xffffffffu, k[3 + j], s));
+			}
+			cnt += __shfl_xor_sync(0xffffffffu, cnt, s);
+		}
+	} else { // mixed segments: every group folds into its lowest lane
+		const uint32_t leader = __ffs(peers) - 1;
+		uint32_t rest = peers & ~(1u << leader);
+		// each lane walks the members of ITS group; all lanes take part in every shuffle (uniform trip count = largest group)
+		const uint32_t trips = __reduce_max_sync(0xffffffffu, uint32_t(__popc(rest)));
+		for (uint32_t t = 0; t < trips; ++t) {
+			const uint32_t src = rest ? __ffs(rest) - 1 : lane;
+			rest &= rest - 1;
+#pragma unroll
+			for (int j = 0; j < 3; ++j) {
+				k[j] = min(k[j], __shfl_sync(0xffffffffu, k[j], src));
+				k[3 + j] = max(k[3 + j], __shfl_sync(0xffffffffu, k[3 + j], src));
+			}
+			const uint32_t c2 = __shfl_sync(0xffffffffu, live ? 1u : 0u, src);
+			if (src != lane)
+				cnt += c2;
+		}
+		// (non-leader lanes computed partial folds of their own; only group leaders publish)
+	}
+	const bool publish = peers == 0xffffffffu ? lane == 0 : (lane == uint32_t(__ffs(peers) - 1));
+	if (publish && seg != 0xffffffffu && cnt) {
+		uint32_t *a = d.acc + size_t(seg) * 8;
+#pragma unroll
+		for (int j = 0; j < 3; ++j) {
+			atomicMin(a + j, k[j]);
+			atomicMax(a + 3 + j, k[3 + j]);
+		}
+		atomicAdd(a + 6, cnt);
+	}
+}
+
 // ---- transparent-list sort keys -------------------------------------------------------------------------------------------
 // ComputeModelDisplayListSortKeys (engine/scene_forward_pipeline.cpp:438-483) for the SURVIVORS of a culled list: model-view matrix =
 // view * world (operator*(Mat4,Mat4)), the 8 corners of the list's MinMax through operator*(Mat4,Vec3) (foundation/matrix4.cpp:78-81;

@@ -72,6 +72,26 @@ def scene_frusta(fs):
     return make_perspective_frustum(c["znear"], c["zfar"], c["fov"], c["ar_x"], c["ar_y"], c["world12"])
 
 
+# ---- bounding boxes -------------------------------------------------------------------------------------------------------------
+def object_table(fs):
+    """Arguments of Context.set_objects for Scene::GetMinMax / GetNodesMinMax: every node with an Object whose model has bounds takes
+    part (disabled nodes too: GetNodesWithComponent does not look at flags, scene.cpp:604-640); one MinMax per model = the Union of its
+    lists' bounds (Scene::GetObjectMinMax, component.cpp:778-797); one segment per scene instance."""
+    nodes = np.nonzero(fs.model >= 0)[0]
+    ob = np.zeros((max(len(fs.models), 1), 6), f32)
+    has = np.zeros(max(len(fs.models), 1), bool)
+    for mi, m in enumerate(fs.models):
+        b = np.asarray(m["bounds"], f32).reshape(-1, 6)
+        if len(b):
+            ob[mi, :3], ob[mi, 3:], has[mi] = b[:, :3].min(0), b[:, 3:].max(0), True
+    nodes = nodes[has[fs.model[nodes]]]
+    seg, n_seg = None, 1
+    if fs.instance_start is not None:
+        seg = (np.searchsorted(fs.instance_start, nodes, side="right") - 1).astype(np.uint32)
+        n_seg = len(fs.instance_start) - 1
+    return nodes.astype(np.uint32), fs.model[nodes].astype(np.uint32), ob, seg, n_seg
+
+
 # ---- tables ---------------------------------------------------------------------------------------------------------------
 def build_tables(fs):
     """FlatScene -> dict of C-ABI arrays. Node i owns transform slot i."""

@@ -128,6 +128,18 @@ int hgb_cull_list(hgb_ctx *, uint32_t n, const uint32_t *mtx_slot, const uint32_
  * survivors of list (kind, view) of the last cull: one 1-mm fixed-point key per visible entry, from the closest view-space z of the 8
  * corners of its MinMax. view_mat12 = ViewState::view (hg::Mat4). Keys are returned in visible-list order by hgb_get_sort_keys. */
 int hgb_sort_keys(hgb_ctx *, int kind, uint32_t view, const float *view_mat12);
+/* Scene::GetMinMax (harfang/engine/scene.cpp:1982) / GetNodesMinMax (engine/node.cpp:265-285) as a device reduction over the current world
+ * matrices: per segment, the union over its objects of world[mtx_slot] * object_bounds (Node::GetMinMax node.cpp:106-119,
+ * Scene::GetObjectMinMax component.cpp:778-797). hgb_set_objects describes the object-carrying nodes once (edit time): mtx_slot[i] is the
+ * node's transform slot or HGB_ROOT when it has none (identity world, like Transform::GetWorld on an invalid ref), obounds_idx[i] indexes
+ * obounds6 = one MinMax per model (the union of its lists' bounds; nodes whose model is invalid or has no bounds are left out by the caller,
+ * as the reference skips them), seg[i] (nullable) is the scene instance of the object, n_seg the number of segments.
+ * hgb_minmax enqueues the reduction; hgb_get_minmax returns per segment {mn.xyz, mx.xyz} and the number of contributing nodes
+ * (0 = GetNodesMinMax returns false, the 6 floats are then unspecified). */
+int hgb_set_objects(hgb_ctx *, uint32_t n_obj, const uint32_t *mtx_slot, const uint32_t *obounds_idx, uint32_t n_obounds, const float *obounds6,
+	const uint32_t *seg /* nullable */, uint32_t n_seg);
+int hgb_minmax(hgb_ctx *);
+int hgb_get_minmax(hgb_ctx *, float *out6 /* n_seg x 6 */, uint32_t *out_count /* n_seg, nullable */);
 /* Bone matrices of every skin record (and the previous-frame twin). */
 int hgb_bone_matrices(hgb_ctx *, int with_previous);
 
@@ -162,7 +174,8 @@ int hgb_time_end(hgb_ctx *, float *out_ms);
 #define HGB_K_CULL_FLAGS 4
 #define HGB_K_BONE_MATRICES 5
 #define HGB_K_SORT_KEYS 6
-#define HGB_K_COUNT 7
+#define HGB_K_MINMAX 7
+#define HGB_K_COUNT 8
 int hgb_set_profiling(hgb_ctx *, int on);
 int hgb_get_profile(hgb_ctx *, double *ms_by_class, uint64_t *launches_by_class, int reset);
 /* Write `bytes` bytes of a scratch buffer (allocated on first use) — L2 flush between timed iterations. */

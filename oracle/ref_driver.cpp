@@ -399,6 +399,26 @@ void hgref_inverse_fast(const float *a12, float *out12) {
 	const Mat4 m = InverseFast(mat4_from(a12));
 	memcpy(out12, m.m, 48);
 }
+// Scene::GetMinMax (engine/scene.cpp:1982) when count < 0, else GetNodesMinMax (engine/node.cpp:265-285) over nodes [first, first+count).
+// Returns 1 and the box {mn.xyz, mx.xyz} when at least one node contributed.
+int hgref_minmax(void *h, int first, int count, float *out6) {
+	auto *c = static_cast<RefCtx *>(h);
+	MinMax mm;
+	bool ok;
+	if (count < 0) {
+		ok = c->scene->GetMinMax(c->resources, mm);
+	} else {
+		std::vector<Node> nodes;
+		for (int i = first; i < first + count; ++i)
+			nodes.push_back(c->scene->GetNode(c->nodes[i]));
+		ok = GetNodesMinMax(nodes, c->resources, mm);
+	}
+	if (ok) {
+		memcpy(out6, &mm.mn, 12);
+		memcpy(out6 + 3, &mm.mx, 12);
+	}
+	return ok ? 1 : 0;
+}
 // Scene::SetTransformWorldMatrix / SetTransformLocalMatrix (engine/component.cpp:265-281, :236-248) on the transform of a node
 void hgref_set_transform_matrix(void *h, int node, const float *m12, int is_local) {
 	auto *c = static_cast<RefCtx *>(h);

@@ -69,6 +69,7 @@ def _bind_scene_driver(L, with_probes):
     _sig(L, "hgref_garbage_collect", c_i, [c_p])
     _sig(L, "hgref_set_node_world", None, [c_p, c_i, c_p])
     _sig(L, "hgref_set_transform_matrix", None, [c_p, c_i, c_p, c_i])
+    _sig(L, "hgref_minmax", c_i, [c_p, c_i, c_i, c_p])
     _sig(L, "hgref_node_transform_idx", c_i, [c_p, c_i])
     _sig(L, "hgref_add_anim", c_i, [c_p, c_i])
     _sig(L, "hgref_anim_add_vec3_track", c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p])

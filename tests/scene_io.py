@@ -90,6 +90,12 @@ class RefScene:
         """Scene::SetTransformWorldMatrix / SetTransformLocalMatrix"""
         self.L.hgref_set_transform_matrix(self.h, int(node), P(np.ascontiguousarray(m12, np.float32).reshape(12)), 1 if local else 0)
 
+    def minmax(self, first=0, count=-1):
+        """Scene::GetMinMax (count < 0) or GetNodesMinMax over nodes [first, first+count) -> (ok, minmax6)"""
+        out = np.zeros(6, np.float32)
+        ok = self.L.hgref_minmax(self.h, int(first), int(count), P(out))
+        return bool(ok), out
+
     def sort_keys(self, view12):
         """ComputeModelDisplayListSortKeys over the list left by the last cull()"""
         v = np.ascontiguousarray(view12, np.float32).reshape(12)

@@ -205,3 +205,20 @@ def test_facade_set_transform_matrices_match_reference(fac, ref, local):
         wa, wb = a.worlds()[: fs.n].astype(np.float64), b.worlds()[: fs.n]
         assert (np.abs(wa - wb) / np.maximum(np.abs(wa), 1e-6 * np.abs(wa).max())).max() <= 1e-4
     a.close(); b.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.ref
+def test_facade_scene_minmax_matches_reference(fac, ref):
+    """Scene::GetMinMax / GetNodesMinMax through the facade == the reference, exactly (device reduction over the current worlds)"""
+    fs = scenegen.static_scene(4_000, 4, 7, n_models=3, seed=95)
+    fs.model[::9] = -1
+    a, b = RefScene(ref, fs), RefScene(fac, fs)
+    a.update(0); b.update(0)
+    for first, count in ((0, -1), (100, 900), (0, 1), (3990, 10)):
+        (oka, ma), (okb, mb) = a.minmax(first, count), b.minmax(first, count)
+        assert oka == okb and (not oka or (ma == mb).all()), (first, count, ma, mb)
+    none = np.nonzero(fs.model < 0)[0]
+    (oka, _), (okb, _) = a.minmax(int(none[0]), 1), b.minmax(int(none[0]), 1)
+    assert not oka and not okb
+    a.close(); b.close()

@@ -327,6 +327,84 @@ def test_set_transform_matrices_batched(hgb, oracles, local):
     orc.close(); ctx.close()
 
 
+def _same_box(a, b):
+    """min/max are exact; only the sign of a zero may differ (Union's `a < b ? a : b` keeps whichever came first)"""
+    return bool((np.asarray(a, np.float32) == np.asarray(b, np.float32)).all())
+
+
+def test_scene_minmax_reduction(hgb, oracles):
+    """Scene::GetMinMax (scene.cpp:1982) = union over object nodes of world * Union(model bounds): device reduction == reference, exactly,
+    for a static frame, after track sampling, and after SetTransformWorldMatrix edits; GetNodesMinMax over a node range as one segment."""
+    ref, _ = oracles
+    if ref is None:
+        pytest.skip("needs the compiled reference")
+    from tests.scene_io import RefScene
+    fs = scenegen.static_scene(20_000, 5, 7, n_models=5, seed=71)
+    rng = np.random.default_rng(72)
+    fs.model[rng.choice(fs.n, 3000, replace=False)] = -1          # nodes without an Object do not take part
+    fs.models[2]["bounds"] = np.concatenate([fs.models[2]["bounds"], fs.models[2]["bounds"] * np.float32(1.7)])  # a model with two lists
+    fs.models[2]["mats"] = np.array([0, 0], np.uint16)
+    scenegen.add_position_tracks(fs, np.sort(rng.choice(fs.n, 4000, replace=False)).astype(np.int32), rng, n_keys=6)
+    ctx = hgb.Context(0)
+    t = hostmirror.upload(ctx, fs)
+    orc = RefScene(ref, fs)
+    slots, ob_idx, ob, seg, n_seg = hostmirror.object_table(fs)
+    ctx.set_objects(slots, ob_idx, ob, seg, n_seg)
+    clocks = hostmirror.PlayClocks(fs)
+    for frame in range(3):
+        ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True)
+        orc.update(scenegen.FRAME_DT)
+        mm, cnt = ctx.minmax()
+        ok, mm_ref = orc.minmax()
+        assert ok and cnt[0] == len(slots)
+        assert _same_box(mm[0], mm_ref), (mm, mm_ref)
+    # an edit that pushes one node far out must show up at once (world rows are written by the batched set)
+    far = np.array([[1, 0, 0, 900.0, 0, 1, 0, -700.0, 0, 0, 1, 1234.5]], np.float32)
+    node = int(slots[17])
+    ctx.set_matrices(np.array([node], np.uint32), far)
+    orc.set_transform_matrix(node, far[0])
+    mm, _ = ctx.minmax()
+    ok, mm_ref = orc.minmax()
+    assert ok and _same_box(mm[0], mm_ref) and mm[0][3] > 890
+    # GetNodesMinMax over a node range = the same reduction over a subset
+    lo, hi = 5000, 9000
+    sel = (slots >= lo) & (slots < hi)
+    ctx.set_objects(slots[sel], ob_idx[sel], ob, None, 1)
+    mm, cnt = ctx.minmax()
+    ok, mm_ref = orc.minmax(lo, hi - lo)
+    assert ok and cnt[0] == int(sel.sum()) and _same_box(mm[0], mm_ref)
+    # no object at all: GetNodesMinMax returns false
+    ctx.set_objects(slots[:0], ob_idx[:0], ob, None, 1)
+    _, cnt = ctx.minmax()
+    assert cnt[0] == 0
+    orc.close(); ctx.close()
+
+
+def test_instance_minmax_segments(hgb, oracles):
+    """one bounding box per scene instance of an RL-style batch (segmented reduction; instances interleave in position order)"""
+    ref, _ = oracles
+    if ref is None:
+        pytest.skip("needs the compiled reference")
+    from tests.scene_io import RefScene
+    fs = scenegen.config_c5(seed=73, n_instances=48, nodes_per_instance=300, depth=4)
+    fs.model[::13] = -1
+    ctx = hgb.Context(0)
+    hostmirror.upload(ctx, fs)
+    orc = RefScene(ref, fs)
+    ctx.update(None, fused_cull=True)
+    orc.update(0)
+    slots, ob_idx, ob, seg, n_seg = hostmirror.object_table(fs)
+    assert n_seg == 48
+    ctx.set_objects(slots, ob_idx, ob, seg, n_seg)
+    mm, cnt = ctx.minmax()
+    for i in range(n_seg):
+        lo, hi = int(fs.instance_start[i]), int(fs.instance_start[i + 1])
+        ok, mm_ref = orc.minmax(lo, hi - lo)
+        assert ok and cnt[i] == int(((slots >= lo) & (slots < hi)).sum())
+        assert _same_box(mm[i], mm_ref), "instance %d" % i
+    orc.close(); ctx.close()
+
+
 def test_c5_small_instance_batch(hgb, oracles):
     """BASELINE config 5 at 24 instances x 2048 nodes: one camera per instance; per-instance visible lists = the reference's
     CullModelDisplayLists run per instance scene"""
