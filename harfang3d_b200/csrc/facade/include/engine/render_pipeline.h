@@ -20,7 +20,7 @@ namespace hg {
 
 static const int max_skinned_model_matrix_count = 32; // render_pipeline.h:38
 
-enum BlendMode { BM_Additive, BM_Alpha, BM_Darken, BM_Lighten, BM_Multiply, BM_Opaque, BM_Screen, BM_LinearBurn, BM_Undefined };
+enum BlendMode { BM_Additive, BM_Alpha, BM_Darken, BM_Lighten, BM_Multiply, BM_Opaque, BM_Screen, BM_LinearBurn, BM_AlphaRGB_AddAlpha, BM_Undefined };
 
 struct Material { // only what GetModelDisplayLists reads: the blend mode (render_pipeline.cpp:394-417)
 	BlendMode blend_mode{BM_Opaque};

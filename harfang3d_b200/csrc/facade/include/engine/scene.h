@@ -9,6 +9,7 @@
 #include "engine/render_pipeline.h"
 #include "foundation/generational_vector_list.h"
 #include "foundation/hg_math_types.h"
+#include <map>
 #include <string>
 #include <vector>
 
@@ -82,6 +83,23 @@ struct SceneAnim { // scene.h:109-118
 };
 
 static const uint32_t NF_Disabled = 0x1, NF_InstanceDisabled = 0x2; // scene.h:166-170
+
+// engine/load_save_scene_flags.h:10-32
+static const uint32_t LSSF_Nodes = 0x1, LSSF_Scene = 0x2, LSSF_Anims = 0x4, LSSF_KeyValues = 0x8, LSSF_Physics = 0x10, LSSF_Scripts = 0x20, LSSF_All = 0xffff;
+static const uint32_t LSSF_DoNotLoadResources = 0x40000; // always in force here: resources are resolved by name, never read from disk
+
+struct SceneView { // scene.h:145-155
+	std::vector<NodeRef> nodes;
+	std::vector<AnimRef> anims;
+	std::vector<SceneAnimRef> scene_anims;
+};
+struct LoadSceneContext { // scene.h:157-161
+	int recursion_level{};
+	SceneView view;
+	std::map<uint32_t, NodeRef> node_refs;
+};
+struct PipelineInfo {}; // render_pipeline.h: shader pipeline description — not used by the scene-update path
+uint32_t GetSceneBinaryFormatVersion();
 
 class Scene {
 public:
@@ -181,6 +199,12 @@ public:
 	void StopAllAnims();
 	void UpdatePlayingAnims(time_ns dt);
 
+	// ---- scene binary (scene.h:676-677; format version 9) ----
+	// Load_binary of the reference takes a Reader/Handle pair; here the file image is parsed from memory straight into the containers
+	// (bulk, no per-node API calls) and the hierarchy reaches the device as one SoA upload. facade/src/hg_scene_load_binary.cpp
+	bool Load_binary(const void *data, size_t size, const char *name, PipelineResources &resources, const PipelineInfo &pipeline, LoadSceneContext &ctx,
+		uint32_t load_flags = LSSF_All);
+
 	// ---- extensions of the B200 path (not in the reference) ----
 	// Up to 8 frusta evaluated inside Update (fused with the world-matrix pass). GetVisibleModelDisplayLists then returns what
 	// GetModelDisplayLists + CullModelDisplayLists(view) would, without a second pass over the matrices.
@@ -236,9 +260,16 @@ private:
 
 	bool EnsureContext() const;
 	void RefreshTRSFromDevice() const;
+	void MarkBulkEdit(); // containers were filled behind the setters' back: everything is re-derived at the next sync
 	void QueueMatrixSet(uint32_t slot, const Mat4 &m, bool is_local);
 	void FlushMatrixSets() const;
 	bool SyncEdits(const PipelineResources *resources);
 };
+
+// scene.h:962-974
+bool LoadSceneBinaryFromFile(const char *path, Scene &scene, PipelineResources &resources, const PipelineInfo &pipeline, LoadSceneContext &ctx,
+	uint32_t flags = LSSF_All, bool debug = false);
+bool LoadSceneBinaryFromMemory(const void *data, size_t size, const char *name, Scene &scene, PipelineResources &resources, const PipelineInfo &pipeline,
+	LoadSceneContext &ctx, uint32_t flags = LSSF_All);
 
 } // namespace hg

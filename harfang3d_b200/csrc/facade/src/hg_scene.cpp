@@ -37,6 +37,8 @@ struct Scene::Impl {
 	std::vector<Frustum> frusta;
 	std::vector<uint32_t> preset_slots;
 	std::vector<float> preset_mats;
+	uint32_t device_slots{0};          // slots of the topology the device currently holds
+	std::vector<uint32_t> fresh_slots; // transforms created since then: their host TRS is newer than whatever the device has in that slot
 	std::vector<uint32_t> set_slots; // queued SetTransformWorld/LocalMatrix calls (one mode per queue)
 	std::vector<float> set_mats;
 	bool set_local{false};
@@ -164,6 +166,7 @@ bool Scene::IsChildOf(NodeRef node, NodeRef parent) const { // walk up from `nod
 // ---- transforms --------------------------------------------------------------------------------------------------------------
 Transform Scene::CreateTransform() {
 	const ComponentRef ref = transforms.add_ref(Transform_{});
+	impl->fresh_slots.push_back(ref.idx);
 	impl->topology_dirty = true;
 	return {this, ref};
 }
@@ -173,6 +176,7 @@ Transform Scene::CreateTransform(const Vec3 &pos, const Vec3 &rot, const Vec3 &s
 	t.TRS.pos = pos, t.TRS.rot = rot, t.TRS.scl = scl;
 	t.parent = parent;
 	const ComponentRef ref = transforms.add_ref(t);
+	impl->fresh_slots.push_back(ref.idx);
 	impl->topology_dirty = true;
 	return {this, ref};
 }
@@ -186,22 +190,41 @@ void Scene::DestroyTransform(ComponentRef ref) {
 	}
 }
 
+void Scene::MarkBulkEdit() {
+	RefreshTRSFromDevice(); // before every slot is declared fresh
+	impl->fresh_slots.clear();
+	for (uint32_t i = transforms.first(); i != transforms.invalid_idx; i = transforms.next(i))
+		impl->fresh_slots.push_back(i);
+	impl->topology_dirty = true;
+	impl->trs_all_dirty = true;
+	impl->entries_dirty = true;
+	impl->anims_dirty = true;
+}
+
 // The device samples bound tracks straight into its TRS; the host copy is refreshed on the first host access after such a frame.
 void Scene::RefreshTRSFromDevice() const {
 	FlushMatrixSets();
 	if (!trs_host_stale)
 		return;
 	trs_host_stale = false;
-	const uint32_t n = uint32_t(transforms.capacity());
-	if (!ctx || !n || impl->topology_dirty)
+	// with a pending re-layout the device still holds the OLD topology: its slots are read back (sampled values must survive the
+	// re-layout), except the ones (re)created on the host since
+	const uint32_t n = std::min(uint32_t(transforms.capacity()), impl->device_slots);
+	if (!ctx || !n)
 		return;
 	impl->staging.resize(size_t(n) * 9);
 	if (hgb_get_trs(ctx, 0, n, impl->staging.data())) {
 		warn(hgb_last_error());
 		return;
 	}
+	std::vector<uint8_t> fresh(n, 0);
+	for (uint32_t sl : impl->fresh_slots)
+		if (sl < n)
+			fresh[sl] = 1;
 	auto &trs = const_cast<generational_vector_list<Transform_> &>(transforms);
-	for (uint32_t i = transforms.first(); i != transforms.invalid_idx; i = transforms.next(i)) {
+	for (uint32_t i = transforms.first(); i != transforms.invalid_idx && i < n; i = transforms.next(i)) {
+		if (fresh[i])
+			continue;
 		const float *s = impl->staging.data() + size_t(i) * 9;
 		trs[i].TRS.pos = Vec3(s[0], s[1], s[2]), trs[i].TRS.rot = Vec3(s[3], s[4], s[5]), trs[i].TRS.scl = Vec3(s[6], s[7], s[8]);
 	}
@@ -605,6 +628,8 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 		}
 		impl->topology_dirty = false;
 		impl->trs_all_dirty = true;
+		impl->device_slots = n;
+		impl->fresh_slots.clear();
 	}
 
 	if (impl->trs_all_dirty && n) {

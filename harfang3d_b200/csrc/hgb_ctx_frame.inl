@@ -473,8 +473,13 @@ int hgb_minmax(hgb_ctx *c) {
 		d.obounds6 = c->obounds.as<float>();
 		d.acc = c->mm_acc.as<uint32_t>();
 		d.n = c->n_obj;
+		// persistent grid: 8 CTAs of 8 warps per SM at most, every warp a contiguous chunk (multiple of 32 objects)
+		const uint32_t max_warps = 148u * 8u * 8u;
+		uint32_t per_warp = (d.n + max_warps - 1) / max_warps;
+		per_warp = std::max(32u, (per_warp + 31u) & ~31u);
+		const uint32_t n_warps = (d.n + per_warp - 1) / per_warp;
 		prof_begin(c, HGB_K_MINMAX);
-		k_minmax<<<grid_for(d.n), 256, 0, c->stream>>>(d);
+		k_minmax<<<(n_warps + 7) / 8, 256, 0, c->stream>>>(d, per_warp);
 		prof_end(c);
 		++c->launches;
 	}

@@ -327,70 +327,130 @@ __global__ void __launch_bounds__(256) k_minmax_init(uint32_t *acc, uint32_t n_s
 	}
 }
 
-__global__ void __launch_bounds__(256) k_minmax(MinMaxDev d) {
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	const bool live = i < d.n;
-	uint32_t seg = 0xffffffffu;
-	uint32_t k[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
-	if (live) {
-		seg = d.obj_seg ? d.obj_seg[i] : 0u;
-		const uint32_t p = d.obj_pos[i];
-		Mat4 w;
-		if (p != kRoot) {
-			w = load_mat4(d.world + size_t(p) * 12);
-		} else { // Transform::GetWorld on an invalid transform returns Mat4::Identity (component.cpp:250-256)
+// Persistent grid (a few CTAs per SM): every WARP owns a contiguous chunk of the position-sorted objects and walks it 32 at a time
+// (32 world rows = 1536 contiguous bytes when every node carries an object). Objects of one segment form long runs in position order
+// (a level of one instance), so a warp folds each uniform group of 32 with a shuffle butterfly into a running box and touches memory
+// only when the segment changes; the 8 warps of a CTA merge their last runs in shared memory. One-segment scenes end with 7 atomics
+// per CTA; mixed warps (segment boundaries) publish their groups directly.
+__device__ __forceinline__ void minmax_publish(uint32_t *acc, uint32_t seg, const uint32_t (&k)[6], uint32_t cnt) {
+	uint32_t *a = acc + size_t(seg) * 8;
 #pragma unroll
-			for (int r = 0; r < 3; ++r)
-#pragma unroll
-				for (int c = 0; c < 4; ++c)
-					w.m[r][c] = r == c ? 1.f : 0.f;
-		}
-		const Aabb bb = minmax_transform(w, d.obounds6 + size_t(d.obj_meta[i] & 0xffffffu) * 6);
-#pragma unroll
-		for (int j = 0; j < 3; ++j)
-			k[j] = float_key(bb.mn[j]), k[3 + j] = float_key(bb.mx[j]);
+	for (int j = 0; j < 3; ++j) {
+		atomicMin(a + j, k[j]);
+		atomicMax(a + 3 + j, k[3 + j]);
 	}
-	const uint32_t lane = threadIdx.x & 31u;
-	const uint32_t peers = __match_any_sync(0xffffffffu, seg);
-	uint32_t cnt = live ? 1u : 0u;
-	if (peers == 0xffffffffu) { // the whole warp is one segment: butterfly reduction
+	atomicAdd(a + 6, cnt);
+}
+
+__global__ void __launch_bounds__(256) k_minmax(MinMaxDev d, uint32_t per_warp) {
+	__shared__ uint32_t s_run[8][8]; // per warp: seg, 6 keys, count
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const uint32_t gw = blockIdx.x * 8u + warp;
+	const uint64_t b0 = uint64_t(gw) * per_warp;
+	const uint32_t begin = uint32_t(min(b0, uint64_t(d.n))), end = uint32_t(min(b0 + per_warp, uint64_t(d.n)));
+	uint32_t run_seg = 0xffffffffu, run_cnt = 0;
+	uint32_t run[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+	for (uint32_t base = begin; base < end; base += 32) {
+		const uint32_t i = base + lane;
+		const bool live = i < end;
+		uint32_t seg = 0xffffffffu;
+		uint32_t k[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+		if (live) {
+			seg = d.obj_seg ? d.obj_seg[i] : 0u;
+			const uint32_t p = d.obj_pos[i];
+			Mat4 w;
+			if (p != kRoot) {
+				w = load_mat4(d.world + size_t(p) * 12);
+			} else { // Transform::GetWorld on an invalid transform returns Mat4::Identity (component.cpp:250-256)
 #pragma unroll
-		for (int s = 16; s > 0; s >>= 1) {
+				for (int r = 0; r < 3; ++r)
 #pragma unroll
-			for (int j = 0; j < 3; ++j) {
-				k[j] = min(k[j], __shfl_xor_sync(0xffffffffu, k[j], s));
-				k[3 + j] = max(k[3 + j], __shfl_xor_sync(0xffffffffu, k[3 + j], s));
+					for (int c = 0; c < 4; ++c)
+						w.m[r][c] = r == c ? 1.f : 0.f;
 			}
-			cnt += __shfl_xor_sync(0xffffffffu, cnt, s);
-		}
-	} else { // mixed segments: every group folds into its lowest lane
-		const uint32_t leader = __ffs(peers) - 1;
-		uint32_t rest = peers & ~(1u << leader);
-		// each lane walks the members of ITS group; all lanes take part in every shuffle (uniform trip count = largest group)
-		const uint32_t trips = __reduce_max_sync(0xffffffffu, uint32_t(__popc(rest)));
-		for (uint32_t t = 0; t < trips; ++t) {
-			const uint32_t src = rest ? __ffs(rest) - 1 : lane;
-			rest &= rest - 1;
+			const Aabb bb = minmax_transform(w, d.obounds6 + size_t(d.obj_meta[i] & 0xffffffu) * 6);
 #pragma unroll
-			for (int j = 0; j < 3; ++j) {
-				k[j] = min(k[j], __shfl_sync(0xffffffffu, k[j], src));
-				k[3 + j] = max(k[3 + j], __shfl_sync(0xffffffffu, k[3 + j], src));
-			}
-			const uint32_t c2 = __shfl_sync(0xffffffffu, live ? 1u : 0u, src);
-			if (src != lane)
-				cnt += c2;
+			for (int j = 0; j < 3; ++j)
+				k[j] = float_key(bb.mn[j]), k[3 + j] = float_key(bb.mx[j]);
 		}
-		// (non-leader lanes computed partial folds of their own; only group leaders publish)
+		// uniform when every LIVE lane has the segment of the first lane (dead lanes carry neutral keys)
+		const uint32_t seg0 = __shfl_sync(0xffffffffu, seg, 0);
+		if (__all_sync(0xffffffffu, !live || seg == seg0)) {
+			uint32_t cnt = live ? 1u : 0u;
+#pragma unroll
+			for (int s = 16; s > 0; s >>= 1) {
+#pragma unroll
+				for (int j = 0; j < 3; ++j) {
+					k[j] = min(k[j], __shfl_xor_sync(0xffffffffu, k[j], s));
+					k[3 + j] = max(k[3 + j], __shfl_xor_sync(0xffffffffu, k[3 + j], s));
+				}
+				cnt += __shfl_xor_sync(0xffffffffu, cnt, s);
+			}
+			if (seg0 != run_seg) { // a new run: the finished one goes to memory
+				if (run_cnt && lane == 0)
+					minmax_publish(d.acc, run_seg, run, run_cnt);
+				run_seg = seg0, run_cnt = 0;
+#pragma unroll
+				for (int j = 0; j < 3; ++j)
+					run[j] = 0xffffffffu, run[3 + j] = 0u;
+			}
+#pragma unroll
+			for (int j = 0; j < 3; ++j)
+				run[j] = min(run[j], k[j]), run[3 + j] = max(run[3 + j], k[3 + j]);
+			run_cnt += cnt;
+		} else { // a segment boundary inside the 32: every group folds into its lowest lane, which publishes
+			const uint32_t peers = __match_any_sync(0xffffffffu, seg);
+			const uint32_t leader = __ffs(peers) - 1;
+			uint32_t rest = peers & ~(1u << leader);
+			uint32_t cnt = live ? 1u : 0u;
+			const uint32_t trips = __reduce_max_sync(0xffffffffu, uint32_t(__popc(rest)));
+			for (uint32_t t = 0; t < trips; ++t) { // all lanes take part in every shuffle; a lane whose list is exhausted reads itself
+				const uint32_t src = rest ? __ffs(rest) - 1 : lane;
+				rest &= rest - 1;
+#pragma unroll
+				for (int j = 0; j < 3; ++j) {
+					k[j] = min(k[j], __shfl_sync(0xffffffffu, k[j], src));
+					k[3 + j] = max(k[3 + j], __shfl_sync(0xffffffffu, k[3 + j], src));
+				}
+				const uint32_t c2 = __shfl_sync(0xffffffffu, live ? 1u : 0u, src);
+				if (src != lane)
+					cnt += c2;
+			}
+			if (lane == leader && live)
+				minmax_publish(d.acc, seg, k, cnt);
+		}
 	}
-	const bool publish = peers == 0xffffffffu ? lane == 0 : (lane == uint32_t(__ffs(peers) - 1));
-	if (publish && seg != 0xffffffffu && cnt) {
-		uint32_t *a = d.acc + size_t(seg) * 8;
+	// the last run of every warp: merged across the CTA when neighbours share the segment
+	if (lane == 0) {
+		s_run[warp][0] = run_cnt ? run_seg : 0xffffffffu;
 #pragma unroll
-		for (int j = 0; j < 3; ++j) {
-			atomicMin(a + j, k[j]);
-			atomicMax(a + 3 + j, k[3 + j]);
+		for (int j = 0; j < 6; ++j)
+			s_run[warp][1 + j] = run[j];
+		s_run[warp][7] = run_cnt;
+	}
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		uint32_t seg = 0xffffffffu, cnt = 0;
+		uint32_t k[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+		for (int w = 0; w < 8; ++w) {
+			const uint32_t sw = s_run[w][0];
+			if (sw == 0xffffffffu)
+				continue;
+			if (sw != seg) {
+				if (cnt)
+					minmax_publish(d.acc, seg, k, cnt);
+				seg = sw, cnt = 0;
+#pragma unroll
+				for (int j = 0; j < 3; ++j)
+					k[j] = 0xffffffffu, k[3 + j] = 0u;
+			}
+#pragma unroll
+			for (int j = 0; j < 3; ++j)
+				k[j] = min(k[j], s_run[w][1 + j]), k[3 + j] = max(k[3 + j], s_run[w][4 + j]);
+			cnt += s_run[w][7];
 		}
-		atomicAdd(a + 6, cnt);
+		if (cnt)
+			minmax_publish(d.acc, seg, k, cnt);
 	}
 }
 

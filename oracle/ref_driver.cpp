@@ -399,6 +399,31 @@ void hgref_inverse_fast(const float *a12, float *out12) {
 	const Mat4 m = InverseFast(mat4_from(a12));
 	memcpy(out12, m.m, 48);
 }
+// Scene binary round trip. hgref_save_binary (reference build only): Scene::Save_binary through SaveSceneBinaryToFile (engine/scene.cpp:1729-1736,
+// engine/scene_load_binary.cpp:237-541). hgref_load_binary: LoadSceneBinaryFromFile (scene.cpp:1803-1811 -> Load_binary, scene_load_binary.cpp:549-905)
+// into this context's scene, with LSSF_DoNotLoadResources so that model names resolve to the models already registered through hgref_add_model
+// (ResourceCache::Add returns the existing ref, engine/resource_cache.h:28-36). Nodes / anims / scene anims of the file become this
+// context's flat indices, in file order. Returns the number of nodes loaded, -1 on failure.
+#ifndef HG_FACADE
+int hgref_save_binary(void *h, const char *path) {
+	auto *c = static_cast<RefCtx *>(h);
+	return SaveSceneBinaryToFile(path, *c->scene, c->resources, LSSF_All) ? 1 : 0;
+}
+#endif
+int hgref_load_binary(void *h, const char *path) {
+	auto *c = static_cast<RefCtx *>(h);
+	LoadSceneContext lctx;
+	PipelineInfo pipeline;
+	if (!LoadSceneBinaryFromFile(path, *c->scene, c->resources, pipeline, lctx, LSSF_All | LSSF_DoNotLoadResources))
+		return -1;
+	for (const auto &r : lctx.view.nodes)
+		c->nodes.push_back(r);
+	for (const auto &r : lctx.view.anims)
+		c->anims.push_back(r);
+	for (const auto &r : lctx.view.scene_anims)
+		c->scene_anims.push_back(r);
+	return int(lctx.view.nodes.size());
+}
 // Scene::GetMinMax (engine/scene.cpp:1982) when count < 0, else GetNodesMinMax (engine/node.cpp:265-285) over nodes [first, first+count).
 // Returns 1 and the box {mn.xyz, mx.xyz} when at least one node contributed.
 int hgref_minmax(void *h, int first, int count, float *out6) {

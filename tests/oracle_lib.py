@@ -70,6 +70,9 @@ def _bind_scene_driver(L, with_probes):
     _sig(L, "hgref_set_node_world", None, [c_p, c_i, c_p])
     _sig(L, "hgref_set_transform_matrix", None, [c_p, c_i, c_p, c_i])
     _sig(L, "hgref_minmax", c_i, [c_p, c_i, c_i, c_p])
+    _sig(L, "hgref_load_binary", c_i, [c_p, C.c_char_p])
+    if with_probes:
+        _sig(L, "hgref_save_binary", c_i, [c_p, C.c_char_p])
     _sig(L, "hgref_node_transform_idx", c_i, [c_p, c_i])
     _sig(L, "hgref_add_anim", c_i, [c_p, c_i])
     _sig(L, "hgref_anim_add_vec3_track", c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p])

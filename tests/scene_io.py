@@ -1,5 +1,6 @@
 """TEST INFRASTRUCTURE: build the reference's hg::Scene (through oracle/_ref) from a FlatScene, and run reference frames."""
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -7,7 +8,7 @@ from tests.oracle_lib import P
 
 
 class RefScene:
-    def __init__(self, ref, fs):
+    def __init__(self, ref, fs, binary=None):
         self.L, self.fs = ref, fs
         self.h = C.c_void_p(ref.hgref_create())
         for m in fs.models:
@@ -20,21 +21,30 @@ class RefScene:
             bp = m["bind_pose"]
             ref.hgref_add_model(self.h, L_, P(np.ascontiguousarray(m["bounds"], np.float32)), P(np.ascontiguousarray(m["mats"], np.uint16)),
                                 P(off), P(tbl), 0 if bp is None else bp.shape[0], None if bp is None else P(np.ascontiguousarray(bp, np.float32)))
-        ref.hgref_add_nodes(self.h, fs.n, P(np.ascontiguousarray(fs.trs)), P(fs.parent), P(fs.disabled), P(fs.model), P(fs.n_mats),
-                            P(fs.transparent_mask), None)
-        for node, b in fs.bones.items():
-            ref.hgref_set_object_bones(self.h, int(node), len(b), P(np.ascontiguousarray(b, np.int32)))
-        if len(fs.anim_node):
-            c = np.ascontiguousarray
-            ref.hgref_add_anims_bulk(self.h, len(fs.anim_node), P(c(fs.anim_use_quat, np.uint8)), len(fs.trk_anim), P(c(fs.trk_anim, np.int32)),
-                                     P(c(fs.trk_kind, np.uint8)), P(c(fs.trk_key_off, np.uint32)), P(c(fs.trk_key_count, np.uint32)), P(c(fs.v3_t, np.int64)),
-                                     P(c(fs.v3_val, np.float32)), P(c(fs.v3_tension, np.float32)), P(c(fs.v3_bias, np.float32)), P(c(fs.q_t, np.int64)),
-                                     P(c(fs.q_val, np.float32)))
-        for anims, ts, te in fs.scene_anims:
-            nodes = np.ascontiguousarray(fs.anim_node[anims], np.int32)
-            ref.hgref_add_scene_anim(self.h, len(anims), P(nodes), P(np.ascontiguousarray(anims, np.int32)), int(ts), int(te))
+        if binary is not None:
+            # the scene comes from a scene-binary file (Scene::Load_binary); models were registered above under the names the file refers to
+            n = ref.hgref_load_binary(self.h, os.fsencode(binary))
+            assert n == fs.n, "scene binary: %d nodes loaded, %d expected" % (n, fs.n)
+        else:
+            ref.hgref_add_nodes(self.h, fs.n, P(np.ascontiguousarray(fs.trs)), P(fs.parent), P(fs.disabled), P(fs.model), P(fs.n_mats),
+                                P(fs.transparent_mask), None)
+            for node, b in fs.bones.items():
+                ref.hgref_set_object_bones(self.h, int(node), len(b), P(np.ascontiguousarray(b, np.int32)))
+            if len(fs.anim_node):
+                c = np.ascontiguousarray
+                ref.hgref_add_anims_bulk(self.h, len(fs.anim_node), P(c(fs.anim_use_quat, np.uint8)), len(fs.trk_anim), P(c(fs.trk_anim, np.int32)),
+                                         P(c(fs.trk_kind, np.uint8)), P(c(fs.trk_key_off, np.uint32)), P(c(fs.trk_key_count, np.uint32)), P(c(fs.v3_t, np.int64)),
+                                         P(c(fs.v3_val, np.float32)), P(c(fs.v3_tension, np.float32)), P(c(fs.v3_bias, np.float32)), P(c(fs.q_t, np.int64)),
+                                         P(c(fs.q_val, np.float32)))
+            for anims, ts, te in fs.scene_anims:
+                nodes = np.ascontiguousarray(fs.anim_node[anims], np.int32)
+                ref.hgref_add_scene_anim(self.h, len(anims), P(nodes), P(np.ascontiguousarray(anims, np.int32)), int(ts), int(te))
         for sa, loop, scale in fs.plays:
             ref.hgref_play_anim(self.h, sa, loop, scale)
+
+    def save_binary(self, path):
+        """Scene::Save_binary (reference build only)"""
+        assert self.L.hgref_save_binary(self.h, os.fsencode(path)) == 1
 
     def close(self):
         if self.h:

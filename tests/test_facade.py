@@ -222,3 +222,101 @@ def test_facade_scene_minmax_matches_reference(fac, ref):
     (oka, _), (okb, _) = a.minmax(int(none[0]), 1), b.minmax(int(none[0]), 1)
     assert not oka and not okb
     a.close(); b.close()
+
+
+# ---- scene binary (format version 9) -----------------------------------------------------------------------------------------------------
+def _binary_scene(kind):
+    """scenes that exercise every section the loader keeps: hierarchy, disabled nodes, nodes without objects, transparent materials,
+    multi-list models, skinned objects with bone refs, Hermite and quaternion tracks, scene anims"""
+    if kind == "characters":
+        return scenegen.config_c3(seed=33, n_chars=12, n_bones=64, n_keys=8)
+    rng = np.random.default_rng(97)
+    fs = scenegen.static_scene(2_500, 5, 6, n_models=3, seed=97)
+    fs.model[rng.choice(fs.n, 200, replace=False)] = -1
+    fs.transparent_mask[rng.choice(fs.n, 300, replace=False)] = 1
+    scenegen.add_position_tracks(fs, np.sort(rng.choice(fs.n, 600, replace=False)).astype(np.int32), rng, n_keys=7)
+    return fs
+
+
+def _lists_equal(a, b):
+    (ca, la), (cb, lb) = a.display_lists(), b.display_lists()
+    assert (ca == cb).all(), (ca, cb)
+    for k in (0, 1):
+        for x, y in zip(la[k], lb[k]):
+            assert (x == y).all()
+    for kind in (2, 3):
+        for x, y in zip(a.skinned_lists(kind), b.skinned_lists(kind)):
+            assert x.shape == y.shape and (x == y).all()
+
+
+@pytest.mark.ref
+@pytest.mark.parametrize("kind", ["props", "characters"])
+def test_scene_binary_loader_host_side(fac, ref, kind, tmp_path):
+    """A file written by the reference's own Scene::Save_binary, read by (b) the reference's Load_binary and (c) the facade's bulk loader:
+    same nodes, TRS, display lists (opaque / transparent / skinned incl. resolved bone indices). No GPU needed for this half."""
+    fs = _binary_scene(kind)
+    a = RefScene(ref, fs)
+    path = str(tmp_path / "scene.scn")
+    a.save_binary(path)
+    assert os.path.getsize(path) > fs.n * 40
+    b, c = RefScene(ref, fs, binary=path), RefScene(fac, fs, binary=path)
+    every = np.arange(fs.n)
+    ta, tb, tc = a.trs(every), b.trs(every), c.trs(every)
+    assert (bits(ta) == bits(tb)).all() and (bits(tb) == bits(tc)).all()
+    _lists_equal(a, b)
+    _lists_equal(b, c)
+    for s in (a, b, c):
+        s.close()
+
+
+@pytest.mark.ref
+def test_scene_binary_loader_rejects_garbage(fac, tmp_path):
+    """wrong magic, wrong version and truncated files are refused with a warning, never a crash"""
+    ref = oracle_lib.load_ref()
+    if ref is None:
+        pytest.skip("needs the compiled reference to write a valid file")
+    fs = _binary_scene("props")
+    a = RefScene(ref, fs)
+    path = str(tmp_path / "scene.scn")
+    a.save_binary(path)
+    a.close()
+    blob = open(path, "rb").read()
+    cases = {"magic": b"XXXX" + blob[4:], "version": blob[:5] + (8).to_bytes(4, "little") + blob[9:], "cut": blob[: len(blob) // 3], "empty": b""}
+    for name, data in cases.items():
+        p = str(tmp_path / (name + ".scn"))
+        open(p, "wb").write(data)
+        h = C.c_void_p(fac.hgref_create())
+        assert fac.hgref_load_binary(h, os.fsencode(p)) == -1, name
+        fac.hgref_destroy(h)
+    h = C.c_void_p(fac.hgref_create())
+    assert fac.hgref_load_binary(h, os.fsencode(str(tmp_path / "missing.scn"))) == -1
+    fac.hgref_destroy(h)
+
+
+@pytest.mark.gpu
+@pytest.mark.ref
+@pytest.mark.parametrize("kind", ["props", "characters"])
+def test_scene_binary_loader_frames_match_reference(fac, ref, kind, tmp_path):
+    """frames of the facade scene loaded in bulk from the binary == frames of the reference scene loaded by Load_binary from the same file"""
+    fs = _binary_scene(kind)
+    a = RefScene(ref, fs)
+    path = str(tmp_path / "scene.scn")
+    a.save_binary(path)
+    a.close()
+    b, c = RefScene(ref, fs, binary=path), RefScene(fac, fs, binary=path)
+    fr = hostmirror.scene_frusta(fs)[0]
+    # "Ready Matrices" at the end of the load: worlds exist before the first Update
+    wb, wc = b.worlds()[: fs.n], c.worlds()[: fs.n]
+    assert (bits(wb) == bits(wc)).all()
+    for frame in range(4):
+        b.update(scenegen.FRAME_DT); c.update(scenegen.FRAME_DT)
+        wb, wc = b.worlds()[: fs.n].astype(np.float64), c.worlds()[: fs.n]
+        assert (np.abs(wb - wc) / np.maximum(np.abs(wb), 1e-6 * np.abs(wb).max())).max() <= 1e-5
+        if kind == "props":
+            assert (bits(b.worlds()[: fs.n]) == bits(wc)).all()
+        (pb, mb), (pc, mc) = b.cull(0, fr), c.cull(0, fr)
+        assert (pb == pc).all() and (mb == mc).all()
+    if kind == "characters":
+        bb, bc = b.bone_matrices().astype(np.float64), c.bone_matrices()
+        assert bb.shape == bc.shape and (np.abs(bb - bc) / np.maximum(np.abs(bb), 1e-6 * np.abs(bb).max())).max() <= 1e-5
+    b.close(); c.close()
