@@ -195,6 +195,8 @@ def main():
     ap.add_argument("--merge-small", action="store_true", help="A/B switch: runs of small top levels in one cooperative launch")
     ap.add_argument("--slice-nodes", type=int, default=0, help="A/B switch: slice size of big levels under the overlapped sampler (0 = no slicing)")
     ap.add_argument("--overlap", action="store_true", help="A/B switch: sample tracks by target level on a second stream, overlapped with the level kernels")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="N>1 result gather: peer = survivors stored into rank 0's memory over NVLink "
+                    "by the compaction kernel itself, flags + acks on the device, no host sync (hgb_peer_*); nccl = counts all-gathered, host-sized send/recv (A/B)")
     ap.add_argument("--row-store", action="store_true", help="A/B switch: per-thread world row stores instead of the transposed warp store")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -225,9 +227,11 @@ def main():
     # send/recv sized from the counts. The tensors are views of the context's own device buffers (no staging copy).
     gather = None
     gathered = [0]
+    peer = world > 1 and args.exchange == "peer"
     if world > 1:
         from harfang3d_b200 import sharding
-        ctx.set_stream(torch.cuda.current_stream().cuda_stream)  # one stream for our kernels and the NCCL gather
+        if not peer:
+            ctx.set_stream(torch.cuda.current_stream().cuda_stream)  # one stream for our kernels and the NCCL gather
         ctx.update(clocks.step(0), fused_cull=True)              # first frame: builds the device tables the views below point into
         ctx.sync()
         n_ent0 = len(t["ent0_mtx_slot"])
@@ -236,6 +240,14 @@ def main():
         dist.all_reduce(ent_all)
         ent_all = ent_all.cpu().numpy()
         entry_base = np.concatenate([[0], np.cumsum(ent_all)[:-1]])
+    if peer:
+        # the path's only exchange rides on the frame itself: k_compact stores the survivors into rank 0's inbox over
+        # NVLink, flags and acknowledgements are device words, rank 0 concatenates — nothing of it touches the host (hgb_kernels_peer.cuh)
+        aux = np.full(world, len(fs.instance_cameras), np.uint32) if fs.instance_cameras is not None else None
+        ctx.peer_setup(dist, ent_all, aux, dst=0)
+    elif world > 1:
+        # A/B: visible counts all-gathered, visible lists gathered to rank 0 with grouped send/recv sized from the counts (one host read
+        # per step). The tensors are views of the context's own device buffers (no staging copy).
         if fs.instance_cameras is not None:  # c5: per-instance offsets of the compacted list
             n_inst = len(fs.instance_cameras)
             bounds = np.arange(world + 1, dtype=np.int64) * n_inst
@@ -251,6 +263,7 @@ def main():
         gather = sharding.VisibilityGather(bounds, entry_base, dst=0)
 
     def barrier():
+        ctx.sync()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -313,6 +326,12 @@ def main():
         h2d = (n_nodes * 36 if full else 0) + 8 * len(fs.plays)
         e2e[name] = [dt_s, h2d, 4 + 4 * len(vis)]
 
+    if peer:
+        step_no, err = ctx.peer_status()
+        if err:
+            raise SystemExit("bench.py: peer gather error word %d on rank %d after %d frames" % (err, rank, step_no))
+        if rank == 0:
+            gathered[0] = int(ctx.peer_result(with_idx=False)[0][-1])
     clocks_rec = sampler.stop()  # sampled from the start of the timed region to the end of the e2e legs (all under load)
 
     # ---- reduce over ranks --------------------------------------------------------------------------------------------------
@@ -335,6 +354,7 @@ def main():
     for name in e2e:
         e2e[name][0] = rmax(e2e[name][0])
     launches = int(rsum(float(launches)))
+    per_step_ms = {k: rmax(per_step_ms[k]) for k in sorted(per_step_ms)}  # slowest rank per kernel class
 
     if rank == 0:
         peaks = {}
@@ -356,8 +376,11 @@ def main():
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "nodes_per_gpu": n_nodes, "display_entries_per_gpu": n_entries, "visible_fraction": f_vis,
                        "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (lvl_bytes_per_step / 1e9), "frame_graph": True,
-                       "exchange": None if world == 1 else "per step: visible counts all-gathered (NCCL), visible lists gathered to rank 0 "
-                                   "(grouped send/recv sized from the counts; %d entries gathered in the last step)" % gathered[0],
+                       "exchange": None if world == 1 else ("per step, inside the frame graph: k_compact stores the survivors into rank 0's memory over NVLink "
+                                   "(peer stores), count + step flag published on the device, rank 0 concatenates and acknowledges; no host sync "
+                                   "(%d entries gathered in the last step)" % gathered[0]) if peer else
+                                   ("per step: visible counts all-gathered (NCCL), visible lists gathered to rank 0 "
+                                   "(grouped send/recv sized from the counts; %d entries gathered in the last step)" % gathered[0]),
                        "scale": args.scale},
             "e2e": {"value": total_nodes * K / e2e["e2e"][0] / 1e6, "unit": UNIT, "h2d_bytes_per_step": e2e["e2e"][1], "d2h_bytes_per_step": e2e["e2e"][2],
                     "what": "every step: hgb_upload_trs of ALL nodes from pinned host + hgb_update + hgb_get_visible to pinned host"},
@@ -373,6 +396,7 @@ def main():
             rate, kind, sample = cpu_reference_rate(1, 1, 1_000_000, 40)  # ~10 s of one host core
             line["cpu_baseline"] = {"value": rate / 1e6, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample}
         print(json.dumps(line), flush=True)
+    barrier()  # no rank frees its inbox / mailbox while a peer may still write to it
     ctx.close()
     if world > 1:
         dist.destroy_process_group()

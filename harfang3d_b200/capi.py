@@ -57,6 +57,10 @@ SIGNATURES = {
     "hgb_cull_list": (_i, [_p, _u32, _p, _p, _u32, _p, _p, _p, _p]),
     "hgb_bone_matrices": (_i, [_p, _i]),
     "hgb_sort_keys": (_i, [_p, _i, _u32, _p]),
+    "hgb_peer_init": (_i, [_p, _u32, _u32, _u32, _p, _p, _p, _p]),
+    "hgb_peer_connect": (_i, [_p, _p, _p]),
+    "hgb_peer_status": (_i, [_p, _p, _p]),
+    "hgb_peer_result": (_i, [_p, _p, _p, _u32, _p, _u32]),
     "hgb_set_objects": (_i, [_p, _u32, _p, _p, _u32, _p, _p, _u32]),
     "hgb_minmax": (_i, [_p]),
     "hgb_get_minmax": (_i, [_p, _p, _p]),
@@ -232,6 +236,44 @@ class Context:
         out, cnt = np.zeros((self.n_seg, 6), np.float32), np.zeros(self.n_seg, np.uint32)
         self._ck(self._L.hgb_get_minmax(self._h, _ptr(out, np.float32, "out"), _ptr(cnt, np.uint32, "cnt")))
         return out, cnt
+
+    # ---- multi-GPU result gather over peer memory ----
+    def peer_init(self, rank, world, dst, entries_per_rank, aux_words_per_rank=None):
+        """-> (inbox handle, mailbox handle), 64 opaque bytes each, to be exchanged between the ranks (see peer_setup)"""
+        cap = np.ascontiguousarray(entries_per_rank, np.uint32)
+        aux = None if aux_words_per_rank is None else np.ascontiguousarray(aux_words_per_rank, np.uint32)
+        inbox, mail = C.create_string_buffer(64), C.create_string_buffer(64)
+        self._ck(self._L.hgb_peer_init(self._h, rank, world, dst, _ptr(cap, np.uint32, "cap"), _ptr(aux, np.uint32, "aux"), C.addressof(inbox), C.addressof(mail)))
+        self._peer = (rank, world, dst, int(cap.sum()), 0 if aux is None else int(aux.sum()))
+        return inbox.raw, mail.raw
+
+    def peer_connect(self, inbox_of_dst, mailboxes):
+        blob = C.create_string_buffer(b"".join(mailboxes), 64 * len(mailboxes))
+        dst = C.create_string_buffer(inbox_of_dst, 64)
+        self._ck(self._L.hgb_peer_connect(self._h, C.addressof(dst), C.addressof(blob)))
+
+    def peer_setup(self, dist, entries_per_rank, aux_words_per_rank=None, dst=0, group=None):
+        """init + handle exchange over torch.distributed + connect (collective: every rank calls it)"""
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        inbox, mail = self.peer_init(rank, world, dst, entries_per_rank, aux_words_per_rank)
+        handles = [None] * world
+        dist.all_gather_object(handles, (inbox, mail), group=group)
+        self.peer_connect(handles[dst][0], [h[1] for h in handles])
+        dist.barrier(group)
+
+    def peer_status(self):
+        step, err = C.c_uint32(0), C.c_uint32(0)
+        self._ck(self._L.hgb_peer_status(self._h, C.byref(step), C.byref(err)))
+        return step.value, err.value
+
+    def peer_result(self, with_idx=True):
+        """destination rank: (rank offsets[world+1], concatenated global entry indices, global per-instance offsets + total)"""
+        rank, world, dst, cap, n_aux = self._peer
+        off = np.zeros(world + 1, np.uint32)
+        idx = np.zeros(max(cap, 1), np.uint32) if with_idx else None
+        aux = np.zeros(n_aux + 1, np.uint32)
+        self._ck(self._L.hgb_peer_result(self._h, _ptr(off, np.uint32, "off"), _ptr(idx, np.uint32, "idx"), 0 if idx is None else len(idx), _ptr(aux, np.uint32, "aux"), len(aux)))
+        return off, (idx[: off[-1]] if with_idx else None), aux
 
     def bone_matrices(self, with_previous=False):
         self._ck(self._L.hgb_bone_matrices(self._h, 1 if with_previous else 0))

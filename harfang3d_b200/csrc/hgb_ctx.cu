@@ -4,6 +4,7 @@
 #include "../../include/hgb200.h"
 #include "hgb_kernels2.cuh"
 #include "hgb_kernels_tma.cuh"
+#include "hgb_kernels_peer.cuh"
 
 #include <algorithm>
 #include <cstdarg>
@@ -109,6 +110,20 @@ struct EntryTable {
 	uint32_t n_tiles = 0;
 };
 
+// peer-memory result gather (hgb_peer_init / hgb_peer_connect, hgb_kernels_peer.cuh)
+struct Peer {
+	bool on = false;
+	uint32_t rank = 0, world = 0, dst = 0;
+	uint32_t cap[kMaxPeers] = {}, aux_n[kMaxPeers] = {}, entry_base[kMaxPeers] = {}, list_off[kMaxPeers] = {}, aux_off[kMaxPeers] = {};
+	uint32_t aux_base[kMaxPeers + 1] = {};
+	size_t half_words = 0;
+	void *mailbox = nullptr;      // own: ack, step, error
+	void *inbox_local = nullptr;  // destination only
+	uint32_t *inbox = nullptr;    // the destination's inbox as seen from this rank (peer mapping or local)
+	uint32_t *ack_ptr[kMaxPeers] = {}; // destination only: every rank's ack word
+	std::vector<void *> opened;
+};
+
 } // namespace
 
 struct hgb_ctx {
@@ -169,6 +184,9 @@ struct hgb_ctx {
 	uint32_t n_obj = 0, n_obounds = 0, n_seg = 0;
 	bool obj_dirty = true;
 	DBuf obj_pos, obj_meta, obj_seg, obounds, mm_acc;
+
+	Peer peer;
+	DBuf peer_out_list, peer_rank_off, peer_aux_out;
 
 	// animation
 	DBuf keys, cursor, tracks_d, play_t_d; // keys: 32-byte records, vec3 keys then quaternion keys
@@ -323,18 +341,22 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 	return c;
 }
 
+static void peer_release(hgb_ctx *c);
+
 void hgb_destroy(hgb_ctx *c) {
 	if (!c)
 		return;
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
+	peer_release(c);
 	for (auto &a : c->graph_exec)
 		for (cudaGraphExec_t g : a)
 			if (g)
 				cudaGraphExecDestroy(g);
 	DBuf *bufs[] = {&c->tiles, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
 		&c->pent, &c->pos_view, &c->inst_planes, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
-		&c->bone_out[1], &c->keys, &c->cursor, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes, &c->level_barrier, &c->key_rec};
+		&c->bone_out[1], &c->keys, &c->cursor, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes, &c->level_barrier, &c->key_rec,
+		&c->obj_pos, &c->obj_meta, &c->obj_seg, &c->obounds, &c->mm_acc, &c->peer_out_list, &c->peer_rank_off, &c->peer_aux_out};
 	for (DBuf *b : bufs)
 		b->release();
 	for (auto &t : c->ent) {
@@ -431,4 +453,5 @@ int hgb_flush_l2(hgb_ctx *c, size_t bytes) {
 } // extern "C"
 
 #include "hgb_ctx_scene.inl"
+#include "hgb_ctx_peer.inl"
 #include "hgb_ctx_frame.inl"

@@ -20,8 +20,9 @@ static SceneDev scene_dev(hgb_ctx *c, bool with_preset) {
 }
 
 // compaction of every (kind, view) list from the vis bytes; returns the number of kernels enqueued through *n_k
-static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k) {
+static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false) {
 	const int n_views = c->instance_mode ? 1 : c->views.n_views;
+	with_peer = with_peer && c->peer.on;
 	for (int k = 0; k < 2; ++k) {
 		EntryTable &t = c->ent[k];
 		if (!t.n)
@@ -37,6 +38,12 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k) {
 			d.count = t.counts.as<uint32_t>() + v;
 			d.ticket = t.ticket.as<uint32_t>() + v;
 			d.status = t.status.as<uint32_t>() + size_t(v) * t.n_tiles;
+			if (with_peer && k == 0 && v == 0) { // the visible list leaves for the gather destination from the kernel that produces it
+				if (t.n > c->peer.cap[c->peer.rank])
+					return fail("peer gather: %u display entries but a region of %u was declared", t.n, c->peer.cap[c->peer.rank]);
+				d.out2 = peer_half(c) + c->peer.list_off[c->peer.rank];
+				d.add2 = c->peer.entry_base[c->peer.rank];
+			}
 			prof_begin(c, HGB_K_COMPACT);
 			k_compact<<<t.n_tiles, kCompactThreads, 0, c->stream>>>(d);
 			prof_end(c);
@@ -51,6 +58,8 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k) {
 		}
 	}
 	CK(cudaGetLastError());
+	if (with_peer)
+		return peer_enqueue_end(c, n_k);
 	return 0;
 }
 
@@ -108,6 +117,8 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	const SceneDev s = scene_dev(c, with_preset);
 	const bool do_fused = fused && (c->ent[0].n || c->ent[1].n);
 	const size_t n_levels = c->level_off.size() - 1;
+	if (c->peer.on && do_fused)
+		peer_enqueue_begin(c, n_k);
 	const bool has_anim = c->n_tracks && c->n_play;
 	AnimDev a{};
 	if (has_anim) {
@@ -211,7 +222,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		CK(cudaStreamWaitEvent(c->stream, c->ev_chunk[1], 0));
 	CK(cudaGetLastError());
 	if (do_fused)
-		return enqueue_compaction(c, n_k);
+		return enqueue_compaction(c, n_k, true);
 	return 0;
 }
 
@@ -663,6 +674,8 @@ void *hgb_device_ptr(hgb_ctx *c, int which) {
 	case 4: return c->bone_out[0].p;
 	case 5: return c->inst_rank.p;
 	case 6: return c->tiles.p;
+	case 7: return c->peer_out_list.p;
+	case 8: return c->peer_rank_off.p;
 	default: return nullptr;
 	}
 }

@@ -237,6 +237,8 @@ struct CompactDev {
 	uint32_t n;
 	uint32_t bit;             // which view bit
 	uint32_t *out;            // surviving entry indices, in order
+	uint32_t *out2;           // nullable: second copy, each index + add2 — this rank's region of the gather destination's inbox
+	uint32_t add2;            //   (peer memory over NVLink, hgb_kernels_peer.cuh): the result leaves the GPU from the kernel that produces it
 	uint32_t *count;          // total survivors
 	uint32_t *ticket;         // zeroed before launch
 	volatile uint32_t *status; // n_tiles words, zeroed before launch
@@ -244,6 +246,7 @@ struct CompactDev {
 
 __global__ void __launch_bounds__(kCompactThreads) k_compact(CompactDev c) {
 	__shared__ uint32_t s_tile, s_warp_sum[kCompactThreads / 32], s_prefix;
+	__shared__ uint32_t s_list[kCompactTile];
 	if (threadIdx.x == 0)
 		s_tile = atomicAdd(c.ticket, 1u);
 	__syncthreads();
@@ -326,10 +329,25 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact(CompactDev c) {
 	}
 	__syncthreads();
 
-	uint32_t rank = s_prefix + warp_off + (incl - cnt);
-	while (mask) { // survivors of this thread, ascending
-		c.out[rank++] = base + (__ffs(mask) - 1);
+	// survivors of this tile, ascending, staged in shared memory and written out as one contiguous run: full-line coalesced stores
+	// whatever the visible fraction — and the only form in which the copy for the gather destination (out2, peer memory over NVLink)
+	// travels well: per-thread 4-byte stores cost one fabric transaction each
+	uint32_t r = warp_off + (incl - cnt);
+	while (mask) {
+		s_list[r++] = base + (__ffs(mask) - 1);
 		mask &= mask - 1;
+	}
+	__syncthreads();
+	const uint32_t prefix = s_prefix;
+	if (c.out2) {
+		for (uint32_t i = threadIdx.x; i < tile_total; i += kCompactThreads) {
+			const uint32_t e = s_list[i];
+			c.out[prefix + i] = e;
+			c.out2[prefix + i] = e + c.add2;
+		}
+	} else {
+		for (uint32_t i = threadIdx.x; i < tile_total; i += kCompactThreads)
+			c.out[prefix + i] = s_list[i];
 	}
 }
 

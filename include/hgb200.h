@@ -154,9 +154,32 @@ int hgb_get_instance_offsets(hgb_ctx *, uint32_t *out_offsets);
 int hgb_get_bone_matrices(hgb_ctx *, float *out16, int previous);
 int hgb_get_sort_keys(hgb_ctx *, int kind, uint32_t view, uint32_t *out_keys, uint32_t capacity, uint32_t *out_count);
 
+/* ---- multi-GPU: gather of the visible lists to one rank over NVLink / NVSwitch peer memory ----
+ * One context per GPU (one process per GPU); scene instances are sharded, the only exchange is this gather of the RESULT. After
+ * hgb_peer_connect every fused hgb_update also: stores the survivors of list (kind 0, view 0), globalised with the rank's first entry
+ * index, straight from the compaction kernel into this rank's region of the destination GPU's inbox (peer stores), publishes count and a
+ * step flag, and — on the destination — waits for the step's flags, concatenates the regions in rank order and acknowledges. All of it
+ * is enqueued on the contexts' streams: no host synchronisation, no host-side sizes. Every rank must call hgb_update the same number of
+ * times. Setup: every rank calls hgb_peer_init (entries_per_rank = display entries of kind 0 on every rank = region capacities;
+ * aux_words_per_rank = scene instances per rank in instance mode, else NULL), the handles are exchanged by the caller (64 opaque bytes
+ * each, e.g. torch.distributed.all_gather_object), then hgb_peer_connect(inbox handle of dst, mailbox handles of all ranks). */
+typedef struct hgb_peer_handle {
+	unsigned char bytes[64]; /* cudaIpcMemHandle_t */
+} hgb_peer_handle;
+int hgb_peer_init(hgb_ctx *, uint32_t rank, uint32_t world, uint32_t dst, const uint32_t *entries_per_rank, const uint32_t *aux_words_per_rank /* nullable */,
+	hgb_peer_handle *inbox_out /* meaningful on dst */, hgb_peer_handle *mailbox_out);
+int hgb_peer_connect(hgb_ctx *, const hgb_peer_handle *inbox_of_dst, const hgb_peer_handle *mailboxes /* world handles, read on dst */);
+/* frames counted so far and the error word (0 = ok; 1 = a sender timed out waiting for an acknowledgement, 2 + r = the destination timed
+ * out waiting for rank r) */
+int hgb_peer_status(hgb_ctx *, uint32_t *out_step, uint32_t *out_error);
+/* destination only, after a frame: rank offsets (world + 1), the concatenated global entry indices, and the aux words (per-instance
+ * exclusive offsets of the whole batch followed by the total, like hgb_get_instance_offsets of one context holding every instance) */
+int hgb_peer_result(hgb_ctx *, uint32_t *out_rank_off, uint32_t *out_idx /* nullable */, uint32_t idx_capacity, uint32_t *out_aux /* nullable */,
+	uint32_t aux_capacity);
+
 /* ---- introspection for benchmarks / interop ---- */
 /* device pointers: 0 worlds, 1 previous worlds, 2 visible list (kind 0, view 0), 3 visible count (kind 0, view 0), 4 bone matrices,
- * 5 instance offsets, 6 TRS SoA */
+ * 5 instance offsets, 6 TRS SoA, 7 gathered visible list (peer gather destination), 8 its rank offsets */
 void *hgb_device_ptr(hgb_ctx *, int which);
 uint64_t hgb_launch_count(hgb_ctx *);   /* kernels launched by this context so far (graph launches count their kernel nodes) */
 uint32_t hgb_level_count(hgb_ctx *);
