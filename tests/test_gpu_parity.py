@@ -126,6 +126,17 @@ def test_transparent_and_multi_list(hgb, oracles):
     ctx.update(None, fused_cull=True); orc.update(0)
     n0, n1 = check_visible(ctx, t, orc, fr, 0), check_visible(ctx, t, orc, fr, 1)
     assert n0 > 0 and n1 > 0
+    # ComputeModelDisplayListSortKeys (scene_forward_pipeline.cpp:438-483) for the culled transparent list and the culled opaque list:
+    # one 1-mm fixed-point key per survivor, bit-exact (the reference side runs over the list left by its last cull)
+    if oracles[0] is not None:
+        view = hostmirror.inverse_fast(np.asarray(fs.camera["world12"], np.float32).reshape(1, 12))[0]  # ViewState::view (render_pipeline.cpp:67-81)
+        for kind, n_vis in ((1, n1), (0, n0)):
+            orc.cull(kind, fr)
+            keys_ref = orc.sort_keys(view)
+            keys = ctx.sort_keys(kind, 0, view)
+            assert len(keys) == n_vis == len(keys_ref)
+            assert (keys == keys_ref).all(), "sort keys of list kind %d differ" % kind
+        assert len(np.unique(keys)) > 10
     orc.close(); ctx.close()
 
 
