@@ -61,6 +61,9 @@ SIGNATURES = {
     "hgb_peer_connect": (_i, [_p, _p, _p]),
     "hgb_peer_status": (_i, [_p, _p, _p]),
     "hgb_peer_result": (_i, [_p, _p, _p, _u32, _p, _u32]),
+    "hgb_set_enable_tracks": (_i, [_p, _u32, _p, _u32, _p, _p]),
+    "hgb_set_enable_state": (_i, [_p, _u32, _p, _p]),
+    "hgb_get_enable_state": (_i, [_p, _u32, _p, _p, _p]),
     "hgb_set_objects": (_i, [_p, _u32, _p, _p, _u32, _p, _p, _u32]),
     "hgb_minmax": (_i, [_p]),
     "hgb_get_minmax": (_i, [_p, _p, _p]),
@@ -187,6 +190,21 @@ class Context:
 
     def set_tracks(self, tracks, n_play):
         self._ck(self._L.hgb_set_tracks(self._h, len(tracks), _ptr(tracks, TRACK_DTYPE, "tracks"), n_play))
+
+    def set_enable_tracks(self, tracks, key_t, key_v):
+        """"Enable" bool tracks (TRACK_DTYPE records, kind ignored) over the bool key pool (key_t int64, key_v uint8)"""
+        self._ck(self._L.hgb_set_enable_tracks(self._h, len(tracks), _ptr(tracks, TRACK_DTYPE, "tracks"), len(key_t), _ptr(key_t, np.int64, "key_t"), _ptr(key_v, np.uint8, "key_v")))
+        self._n_enable = len(np.unique(tracks["target_slot"])) if len(tracks) else 0
+
+    def set_enable_state(self, slots, disabled):
+        self._ck(self._L.hgb_set_enable_state(self._h, len(slots), _ptr(slots, np.uint32, "slots"), _ptr(disabled, np.uint8, "disabled")))
+
+    def get_enable_state(self):
+        """-> (target slots ascending, disabled 0/1) of the enable-tracked nodes"""
+        n = max(getattr(self, "_n_enable", 0), 1)
+        slots, dis, cnt = np.zeros(n, np.uint32), np.zeros(n, np.uint8), C.c_uint32(0)
+        self._ck(self._L.hgb_get_enable_state(self._h, n, _ptr(slots, np.uint32, "slots"), _ptr(dis, np.uint8, "dis"), C.byref(cnt)))
+        return slots[: cnt.value], dis[: cnt.value]
 
     def set_views(self, frustum24):
         f = np.ascontiguousarray(frustum24, np.float32).reshape(-1, 24)

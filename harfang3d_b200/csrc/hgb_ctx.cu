@@ -185,6 +185,16 @@ struct hgb_ctx {
 	bool obj_dirty = true;
 	DBuf obj_pos, obj_meta, obj_seg, obounds, mm_acc;
 
+	// "Enable" bool tracks (hgb_set_enable_tracks): evaluated on the device, state folded back into the host tables before any rebuild
+	std::vector<hgb_track> en_tracks_h;      // evaluation order
+	std::vector<uint32_t> en_target_slot_h;  // unique target slots, ascending
+	std::vector<uint8_t> en_disabled_h;      // last known state per target (valid after a fold)
+	std::vector<uint8_t> en_known_h;         // 1 once a fold has seen the target
+	uint32_t n_en_keys = 0;
+	bool en_state_dirty = false;             // the device sampled enable tracks since the last fold
+	bool en_resolved = false;                // device tables below match the current layout
+	DBuf en_target_pos, en_off, en_tracks_d, en_keys_d, en_scratch;
+
 	Peer peer;
 	DBuf peer_out_list, peer_rank_off, peer_aux_out;
 
@@ -356,7 +366,7 @@ void hgb_destroy(hgb_ctx *c) {
 	DBuf *bufs[] = {&c->tiles, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
 		&c->pent, &c->pos_view, &c->inst_planes, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
 		&c->bone_out[1], &c->keys, &c->cursor, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes, &c->level_barrier, &c->key_rec,
-		&c->obj_pos, &c->obj_meta, &c->obj_seg, &c->obounds, &c->mm_acc, &c->peer_out_list, &c->peer_rank_off, &c->peer_aux_out};
+		&c->en_target_pos, &c->en_off, &c->en_tracks_d, &c->en_keys_d, &c->en_scratch, &c->obj_pos, &c->obj_meta, &c->obj_seg, &c->obounds, &c->mm_acc, &c->peer_out_list, &c->peer_rank_off, &c->peer_aux_out};
 	for (DBuf *b : bufs)
 		b->release();
 	for (auto &t : c->ent) {

@@ -205,6 +205,23 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		CK(cudaEventRecord(c->ev_chunk[1], c->stream2)); // join point
 	}
 
+	if (!c->en_target_slot_h.empty() && c->n_play) { // "Enable" tracks: node / entry flags of this frame, before the level kernels read them
+		EnableDev e{};
+		e.target_pos = c->en_target_pos.as<uint32_t>();
+		e.off = c->en_off.as<uint32_t>();
+		e.tracks = c->en_tracks_d.as<uint4>();
+		e.keys = c->en_keys_d.as<uint4>();
+		e.play_t = c->play_t_d.as<int64_t>();
+		e.tiles = c->tiles.as<uint32_t>();
+		e.ent_meta0 = c->ent[0].meta.as<uint32_t>();
+		e.ent_meta1 = c->ent[1].meta.as<uint32_t>();
+		e.ent_off = c->ent_off.as<uint32_t>();
+		e.pent = c->pent.as<uint2>();
+		e.n = uint32_t(c->en_target_slot_h.size());
+		k_sample_enable<<<grid_for(e.n, 128), 128, 0, c->stream>>>(e);
+		++*n_k;
+	}
+
 	for (size_t g = 0; g < groups.size(); ++g) {
 		if (has_chunk[g])
 			CK(cudaStreamWaitEvent(c->stream, c->ev_chunk[g + 2], 0));
@@ -291,6 +308,8 @@ int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cul
 		CK(cudaMemcpyAsync(c->play_t_d.p, c->play_t_v.data(), size_t(c->n_play) * 8, cudaMemcpyHostToDevice, c->stream));
 	}
 
+	if (!c->en_target_slot_h.empty() && c->n_play)
+		c->en_state_dirty = true;
 	const bool fused = fused_cull != 0;
 	if (!c->use_graph || with_preset || c->prof.on) {
 		uint64_t k = 0;

@@ -32,11 +32,45 @@ static inline dim3 grid_for(uint32_t n, uint32_t block = 256) { return dim3((n +
 
 static int prepare_tables(hgb_ctx *c);
 
+// "Enable" tracks are evaluated on the device (k_sample_enable): before the host-side tables are rebuilt or edited, the state of the
+// tracked nodes is read back and folded into them, so that a rebuild does not resurrect a stale flag.
+static int fold_enable_state(hgb_ctx *c) {
+	if (!c->en_state_dirty)
+		return 0;
+	c->en_state_dirty = false;
+	const uint32_t n = uint32_t(c->en_target_slot_h.size());
+	if (!n || !c->en_resolved)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	CK(c->en_scratch.reserve(n));
+	k_gather_disabled<<<grid_for(n, 128), 128, 0, c->stream>>>(c->tiles.as<uint32_t>(), c->en_target_pos.as<uint32_t>(), n, c->en_scratch.as<uint8_t>());
+	++c->launches;
+	std::vector<uint8_t> st(n);
+	CK(cudaMemcpyAsync(st.data(), c->en_scratch.p, n, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	c->en_disabled_h = st;
+	c->en_known_h.assign(n, 1);
+	for (int k = 0; k < 2; ++k) { // entries of the tracked nodes take the node's state
+		EntryTable &t = c->ent[k];
+		for (uint32_t e = 0; e < t.n; ++e) {
+			const auto it = std::lower_bound(c->en_target_slot_h.begin(), c->en_target_slot_h.end(), t.mtx_slot[e]);
+			if (it != c->en_target_slot_h.end() && *it == t.mtx_slot[e]) {
+				const uint8_t dis = st[it - c->en_target_slot_h.begin()];
+				t.flags[e] = uint8_t(dis ? (t.flags[e] | HGB_ENTRY_DISABLED) : (t.flags[e] & ~HGB_ENTRY_DISABLED));
+			}
+		}
+	}
+	return 0;
+}
+
 extern "C" {
 
 int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const uint8_t *used) {
 	if (!c)
 		return fail("null context");
+	if (fold_enable_state(c)) // the tiles are about to be rebuilt
+		return 1;
+	c->en_resolved = false;
 	if (n >= 0x00ffffffu)
 		return fail("hgb_set_topology: %u slots exceeds the reference's vector_list capacity (2^24-1, foundation/vector_list.h:40)", n);
 	CK(cudaSetDevice(c->device));
@@ -323,6 +357,9 @@ int hgb_set_display_entries(hgb_ctx *c, int kind, uint32_t n, const uint32_t *mt
 int hgb_set_entry_flags(hgb_ctx *c, int kind, uint32_t first, uint32_t count, const uint8_t *flags) {
 	if (!c)
 		return fail("null context");
+	if (fold_enable_state(c)) // this explicit write must land AFTER what the tracks did so far
+		return 1;
+
 	if (kind != 0 && kind != 1)
 		return fail("hgb_set_entry_flags: bad kind");
 	EntryTable &t = c->ent[kind];
@@ -452,6 +489,83 @@ int hgb_set_tracks(hgb_ctx *c, uint32_t n, const hgb_track *tracks, uint32_t n_p
 	return 0;
 }
 
+int hgb_set_enable_tracks(hgb_ctx *c, uint32_t n_tracks, const hgb_track *tracks, uint32_t n_keys, const int64_t *key_t, const uint8_t *key_v) {
+	if (!c)
+		return fail("null context");
+	for (uint32_t i = 0; i < n_tracks; ++i) {
+		if (tracks[i].target_slot >= c->n_slots)
+			return fail("hgb_set_enable_tracks: track %u targets slot %u outside the topology", i, tracks[i].target_slot);
+		if (tracks[i].play >= c->n_play)
+			return fail("hgb_set_enable_tracks: track %u uses play slot %u of %u (hgb_set_tracks declares the play slots)", i, tracks[i].play, c->n_play);
+		if (uint64_t(tracks[i].key_off) + tracks[i].key_count > n_keys)
+			return fail("hgb_set_enable_tracks: track %u reads keys outside the pool", i);
+	}
+	if (fold_enable_state(c))
+		return 1;
+	CK(cudaSetDevice(c->device));
+	c->en_tracks_h.assign(tracks, tracks + n_tracks);
+	c->en_target_slot_h.clear();
+	for (uint32_t i = 0; i < n_tracks; ++i)
+		c->en_target_slot_h.push_back(tracks[i].target_slot);
+	std::sort(c->en_target_slot_h.begin(), c->en_target_slot_h.end());
+	c->en_target_slot_h.erase(std::unique(c->en_target_slot_h.begin(), c->en_target_slot_h.end()), c->en_target_slot_h.end());
+	c->en_disabled_h.assign(c->en_target_slot_h.size(), 0);
+	c->en_known_h.assign(c->en_target_slot_h.size(), 0);
+	std::vector<uint4> keys(n_keys);
+	for (uint32_t i = 0; i < n_keys; ++i)
+		keys[i] = make_uint4(uint32_t(uint64_t(key_t[i])), uint32_t(uint64_t(key_t[i]) >> 32), key_v[i] ? 1u : 0u, 0u);
+	if (upload(c, c->en_keys_d, keys.data(), size_t(n_keys) * 16))
+		return 1;
+	CK(cudaStreamSynchronize(c->stream));
+	c->n_en_keys = n_keys;
+	c->en_resolved = false;
+	c->entries_dirty = true; // target positions are resolved with the entries
+	invalidate_graph(c);
+	return 0;
+}
+
+int hgb_set_enable_state(hgb_ctx *c, uint32_t n, const uint32_t *slot, const uint8_t *disabled) {
+	if (!c)
+		return fail("null context");
+	if (fold_enable_state(c)) // what the tracks did so far comes first, this explicit write lands after it
+		return 1;
+	for (uint32_t i = 0; i < n; ++i) {
+		const auto it = std::lower_bound(c->en_target_slot_h.begin(), c->en_target_slot_h.end(), slot[i]);
+		if (it == c->en_target_slot_h.end() || *it != slot[i])
+			return fail("hgb_set_enable_state: slot %u is not the target of an enable track", slot[i]);
+		const size_t k = it - c->en_target_slot_h.begin();
+		c->en_disabled_h[k] = disabled[i] ? 1 : 0;
+		c->en_known_h[k] = 1;
+		for (int kind = 0; kind < 2; ++kind) {
+			EntryTable &t = c->ent[kind];
+			for (uint32_t e = 0; e < t.n; ++e)
+				if (t.mtx_slot[e] == slot[i])
+					t.flags[e] = uint8_t(disabled[i] ? (t.flags[e] | HGB_ENTRY_DISABLED) : (t.flags[e] & ~HGB_ENTRY_DISABLED));
+		}
+	}
+	c->entries_dirty = true;
+	invalidate_graph(c);
+	return 0;
+}
+
+int hgb_get_enable_state(hgb_ctx *c, uint32_t capacity, uint32_t *out_slot, uint8_t *out_disabled, uint32_t *out_count) {
+	if (!c)
+		return fail("null context");
+	if (prepare_tables(c)) // tracks set but never resolved: resolve so that the device bits can be read
+		return 1;
+	c->en_state_dirty = c->en_state_dirty || !c->en_target_slot_h.empty();
+	if (fold_enable_state(c))
+		return 1;
+	const uint32_t n = uint32_t(c->en_target_slot_h.size());
+	if (out_count)
+		*out_count = n;
+	if (n > capacity)
+		return fail("hgb_get_enable_state: %u tracked nodes but capacity %u", n, capacity);
+	for (uint32_t i = 0; i < n; ++i)
+		out_slot[i] = c->en_target_slot_h[i], out_disabled[i] = c->en_disabled_h[i];
+	return 0;
+}
+
 int hgb_set_views(hgb_ctx *c, uint32_t n_views, const float *frustum24) {
 	if (!c)
 		return fail("null context");
@@ -505,6 +619,8 @@ static int prepare_tables(hgb_ctx *c) {
 	if (!c->entries_dirty)
 		return 0;
 	CK(cudaSetDevice(c->device));
+	if (fold_enable_state(c))
+		return 1;
 	if (c->n_bound) { // give the track-driven triples their values back before rows are rewritten and tracks re-bound
 		k_bind_lanes<<<grid_for(c->n_bound), 256, 0, c->stream>>>(c->tiles.as<uint32_t>(), c->anim_val.as<float4>(), c->bind_pos_d.as<uint32_t>(),
 			c->bind_group_d.as<uint8_t>(), c->n_bound, 0);
@@ -576,6 +692,14 @@ static int prepare_tables(hgb_ctx *c) {
 			}
 		}
 	}
+	// enable-tracked nodes that own no display entry keep their state in the meta row alone
+	for (size_t i = 0; i < c->en_target_slot_h.size(); ++i) {
+		if (c->en_target_slot_h[i] >= c->n_slots)
+			return fail("enable track targets slot %u outside the topology", c->en_target_slot_h[i]);
+		const uint32_t p = c->pos_of_slot[c->en_target_slot_h[i]];
+		if (p < n_pos_all && !(row_meta[p] & kEntHas) && c->en_known_h[i] && c->en_disabled_h[i])
+			row_meta[p] |= kEntDisabled;
+	}
 	if (upload(c, c->ent_off, ent_off.data(), (size_t(n_pos_all) + 1) * 4) || upload(c, c->pent, pent.data(), size_t(total) * 8))
 		return 1;
 	if (c->instance_mode && upload(c, c->pos_view, pos_view.data(), size_t(n_pos_all) * 2))
@@ -592,6 +716,29 @@ static int prepare_tables(hgb_ctx *c) {
 		CK(cudaStreamSynchronize(c->stream));
 		rows.release();
 		c->launches += 2;
+	}
+
+	{ // enable tracks: CSR by target node, evaluation order kept inside a target
+		const uint32_t nt = uint32_t(c->en_target_slot_h.size());
+		std::vector<uint32_t> tpos(nt), off(size_t(nt) + 1, 0);
+		for (uint32_t i = 0; i < nt; ++i)
+			tpos[i] = c->pos_of_slot[c->en_target_slot_h[i]];
+		std::vector<uint32_t> tgt_of(c->en_tracks_h.size());
+		for (size_t k = 0; k < c->en_tracks_h.size(); ++k) {
+			tgt_of[k] = uint32_t(std::lower_bound(c->en_target_slot_h.begin(), c->en_target_slot_h.end(), c->en_tracks_h[k].target_slot) - c->en_target_slot_h.begin());
+			++off[tgt_of[k] + 1];
+		}
+		for (uint32_t i = 0; i < nt; ++i)
+			off[i + 1] += off[i];
+		std::vector<uint4> trk(c->en_tracks_h.size());
+		std::vector<uint32_t> fill(off.begin(), off.end() - 1);
+		for (size_t k = 0; k < c->en_tracks_h.size(); ++k)
+			trk[fill[tgt_of[k]]++] = make_uint4(c->en_tracks_h[k].key_off, c->en_tracks_h[k].key_count, c->en_tracks_h[k].play, 0u);
+		if (upload(c, c->en_target_pos, tpos.data(), size_t(nt) * 4) || upload(c, c->en_off, off.data(), off.size() * 4) ||
+			upload(c, c->en_tracks_d, trk.data(), trk.size() * 16))
+			return 1;
+		CK(cudaStreamSynchronize(c->stream));
+		c->en_resolved = true;
 	}
 
 	// bones and tracks: slot -> position

@@ -287,6 +287,74 @@ __global__ void __launch_bounds__(256) k_bone_matrices(BoneDev b) {
 		store_bgfx(b.out_prev + size_t(i) * 16, mat4_mul(load_mat4(b.world_prev + size_t(mp) * 12), bind));
 }
 
+// ---- "Enable" bool tracks ---------------------------------------------------------------------------------------------------------
+// Scene::EvaluateBoundAnim, engine/scene.cpp:2158-2162: a bound "Enable" track is evaluated with EvaluateStep (engine/animation.h:130-139:
+// the key at or before t, the first key before the track starts, the last one after it ends) and the node is enabled / disabled
+// accordingly (EnableNode / DisableNode set or clear NF_Disabled, scene.cpp:472-503). On the device the node's state is the kEntDisabled
+// bit of its tile meta row and of every display entry it owns; this kernel rewrites those words, before the level kernels of the frame
+// read them. One thread per TARGET node: its tracks are walked in the reference's evaluation order, the last playing one wins.
+struct EnableDev {
+	const uint32_t *target_pos; // per target node
+	const uint32_t *off;        // CSR: tracks of target i = [off[i], off[i+1])
+	const uint4 *tracks;        // {key_off, key_count, play slot, -}
+	const uint4 *keys;          // {t lo, t hi, value, -}
+	const int64_t *play_t;
+	uint32_t *tiles;
+	uint32_t *ent_meta0, *ent_meta1; // per entry meta of the two tables (stand-alone cull, sort keys)
+	const uint32_t *ent_off;         // overflow CSR by position
+	uint2 *pent;
+	uint32_t n;
+};
+
+__global__ void __launch_bounds__(128) k_sample_enable(EnableDev d) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= d.n)
+		return;
+	bool have = false, enable = true;
+	for (uint32_t k = d.off[i]; k < d.off[i + 1]; ++k) {
+		const uint4 trk = d.tracks[k];
+		const int64_t at = d.play_t[trk.z];
+		if (at == INT64_MIN || trk.y == 0)
+			continue; // not playing / Evaluate() returns false on an empty track
+		uint32_t lo = 0, hi = trk.y; // GetIntervalKeys: first key with key.t > at
+		while (lo < hi) {
+			const uint32_t mid = (lo + hi) >> 1;
+			const uint4 key = d.keys[trk.x + mid];
+			if (int64_t(uint64_t(key.x) | (uint64_t(key.y) << 32)) > at)
+				hi = mid;
+			else
+				lo = mid + 1;
+		}
+		enable = d.keys[trk.x + (lo > 0 ? lo - 1 : 0)].z != 0;
+		have = true;
+	}
+	if (!have)
+		return;
+	const uint32_t p = d.target_pos[i];
+	uint32_t *row = d.tiles + tile_word(p, kRowEntMeta);
+	const uint32_t meta = *row;
+	*row = enable ? (meta & ~kEntDisabled) : (meta | kEntDisabled);
+	if (meta & kEntHas) {
+		uint32_t *m = ((meta & kEntKindTransparent) ? d.ent_meta1 : d.ent_meta0) + d.tiles[tile_word(p, kRowEntIdx)];
+		*m = enable ? (*m & ~kEntDisabled) : (*m | kEntDisabled);
+		if (meta & kEntMore)
+			for (uint32_t k = d.ent_off[p]; k < d.ent_off[p + 1]; ++k) {
+				uint2 rec = d.pent[k];
+				rec.y = enable ? (rec.y & ~kEntDisabled) : (rec.y | kEntDisabled);
+				d.pent[k] = rec;
+				uint32_t *m2 = ((rec.x >> 31) ? d.ent_meta1 : d.ent_meta0) + (rec.x & 0x7fffffffu);
+				*m2 = enable ? (*m2 & ~kEntDisabled) : (*m2 | kEntDisabled);
+			}
+	}
+}
+
+// disabled bit of the given positions (state read-back of the enable-tracked nodes)
+__global__ void __launch_bounds__(128) k_gather_disabled(const uint32_t *__restrict__ tiles, const uint32_t *__restrict__ pos, uint32_t n, uint8_t *__restrict__ out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n)
+		out[i] = (tiles[tile_word(pos[i], kRowEntMeta)] & kEntDisabled) ? 1 : 0;
+}
+
 // ---- scene / instance bounding boxes ---------------------------------------------------------------------------------------------
 // Scene::GetMinMax (engine/scene.cpp:1982) -> GetNodesMinMax (engine/node.cpp:265-285): union over the nodes that carry an Object of
 // world[node transform] * Union(model.bounds[*]) (Node::GetMinMax node.cpp:106-119, Scene::GetObjectMinMax component.cpp:778-797,

@@ -108,6 +108,17 @@ int hgb_set_anim_keys(hgb_ctx *, uint32_t n_vec3_keys, const int64_t *v3_t, cons
 	uint32_t n_quat_keys, const int64_t *q_t, const float *q_val4);
 int hgb_set_tracks(hgb_ctx *, uint32_t n_tracks, const hgb_track *tracks, uint32_t n_play_slots);
 
+/* "Enable" bool tracks (BoundToNodeAnim::bool_track[NBAT_Enable], harfang/engine/scene.h:74-88), in the reference's evaluation order.
+ * Evaluated every hgb_update with EvaluateStep (engine/animation.h:130-139) at the track's play clock: the node of target_slot and all
+ * its display entries take HGB_ENTRY_DISABLED = !value before the frame's visibility is computed (Scene::EvaluateBoundAnim
+ * scene.cpp:2158-2162 -> EnableNode / DisableNode). kind is ignored; key_off / key_count index the bool key pool given here; play slots
+ * are the ones declared by hgb_set_tracks (call it first). The state persists when the track stops, like NF_Disabled. */
+int hgb_set_enable_tracks(hgb_ctx *, uint32_t n_tracks, const hgb_track *tracks, uint32_t n_keys, const int64_t *key_t, const uint8_t *key_v);
+/* EnableNode / DisableNode from the host on enable-tracked nodes (whose state otherwise lives on the device): sets the node and its entries */
+int hgb_set_enable_state(hgb_ctx *, uint32_t n, const uint32_t *slot, const uint8_t *disabled);
+/* current state of every enable-tracked node: target slots (ascending) and 1 = disabled */
+int hgb_get_enable_state(hgb_ctx *, uint32_t capacity, uint32_t *out_slot, uint8_t *out_disabled, uint32_t *out_count);
+
 /* Views. Either up to HGB_MAX_VIEWS frusta tested against every entry, or one frustum per scene instance (entry -> view[]). */
 int hgb_set_views(hgb_ctx *, uint32_t n_views, const float *frustum24);
 int hgb_set_instance_views(hgb_ctx *, uint32_t n_instances, const float *frustum24, const uint32_t *inst_entry_start /* n_instances+1, kind 0 */);
