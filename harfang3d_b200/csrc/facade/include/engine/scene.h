@@ -120,7 +120,7 @@ public:
 	void ReserveNodes(size_t count) { nodes.reserve(count); }
 	void EnableNode(NodeRef ref);
 	void DisableNode(NodeRef ref);
-	bool IsNodeEnabled(NodeRef ref) const { return nodes.is_valid(ref) ? !(nodes[ref.idx].flags & (NF_Disabled | NF_InstanceDisabled)) : false; }
+	bool IsNodeEnabled(NodeRef ref) const; // scene.h:227 (reads back device-evaluated "Enable" tracks first)
 	size_t GetNodeCount() const { return nodes.size(); }
 	bool IsChildOf(NodeRef node, NodeRef parent) const; // component.cpp:21-33
 
@@ -260,6 +260,7 @@ private:
 
 	bool EnsureContext() const;
 	void RefreshTRSFromDevice() const;
+	void RefreshFlagsFromDevice() const;
 	void MarkBulkEdit(); // containers were filled behind the setters' back: everything is re-derived at the next sync
 	void QueueMatrixSet(uint32_t slot, const Mat4 &m, bool is_local);
 	void FlushMatrixSets() const;

@@ -37,6 +37,9 @@ struct Scene::Impl {
 	std::vector<Frustum> frusta;
 	std::vector<uint32_t> preset_slots;
 	std::vector<float> preset_mats;
+	std::vector<std::pair<uint32_t, uint32_t>> enable_nodes; // (transform slot, node index) of the nodes driven by an "Enable" track
+	bool enable_state_push{false};     // the host's flags of the tracked nodes must be pushed (tracks were (re)bound or entries rebuilt)
+	bool flags_stale{false};           // the device evaluated Enable tracks: NF_Disabled of those nodes is refreshed before the host reads it
 	uint32_t device_slots{0};          // slots of the topology the device currently holds
 	std::vector<uint32_t> fresh_slots; // transforms created since then: their host TRS is newer than whatever the device has in that slot
 	std::vector<uint32_t> set_slots; // queued SetTransformWorld/LocalMatrix calls (one mode per queue)
@@ -129,13 +132,50 @@ void Scene::DestroyNode(NodeRef ref) {
 	impl->anims_dirty = true;
 }
 
+// "Enable" tracks are evaluated on the device (k_sample_enable; EvaluateBoundAnim scene.cpp:2158-2162): the host's NF_Disabled of the
+// tracked nodes is refreshed from it before anything on the host reads or edits node flags.
+void Scene::RefreshFlagsFromDevice() const {
+	if (!impl->flags_stale)
+		return;
+	impl->flags_stale = false;
+	const size_t n = impl->enable_nodes.size();
+	if (!ctx || !n)
+		return;
+	std::vector<uint32_t> slots(n);
+	std::vector<uint8_t> dis(n);
+	uint32_t cnt = 0;
+	if (hgb_get_enable_state(ctx, uint32_t(n), slots.data(), dis.data(), &cnt)) {
+		warn(hgb_last_error());
+		return;
+	}
+	auto &nd = const_cast<generational_vector_list<Node_> &>(nodes);
+	for (const auto &sn : impl->enable_nodes) {
+		const auto it = std::lower_bound(slots.begin(), slots.begin() + cnt, sn.first);
+		if (it == slots.begin() + cnt || *it != sn.first || !nodes.is_used(sn.second))
+			continue;
+		if (dis[it - slots.begin()])
+			nd[sn.second].flags |= NF_Disabled;
+		else
+			nd[sn.second].flags &= ~NF_Disabled;
+	}
+}
+
+bool Scene::IsNodeEnabled(NodeRef ref) const {
+	if (!nodes.is_valid(ref))
+		return false;
+	RefreshFlagsFromDevice();
+	return !(nodes[ref.idx].flags & (NF_Disabled | NF_InstanceDisabled));
+}
+
 void Scene::EnableNode(NodeRef ref) {
 	if (!nodes.is_valid(ref)) {
 		warn("Invalid node reference");
 		return;
 	}
+	RefreshFlagsFromDevice();
 	nodes[ref.idx].flags &= ~NF_Disabled;
 	impl->entries_dirty = true;
+	impl->enable_state_push = true;
 }
 
 void Scene::DisableNode(NodeRef ref) {
@@ -143,8 +183,10 @@ void Scene::DisableNode(NodeRef ref) {
 		warn("Invalid node reference");
 		return;
 	}
+	RefreshFlagsFromDevice();
 	nodes[ref.idx].flags |= NF_Disabled;
 	impl->entries_dirty = true;
+	impl->enable_state_push = true;
 }
 
 bool Scene::IsChildOf(NodeRef node, NodeRef parent) const { // walk up from `node`; bounded by the node count against corrupted graphs
@@ -607,6 +649,7 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 	if (!EnsureContext())
 		return false;
 	FlushMatrixSets(); // queued SetTransformWorld/LocalMatrix calls come before whatever was edited after them
+	RefreshFlagsFromDevice(); // node flags are about to be read (entry tables) and the set of tracked nodes may change
 	const uint32_t n = uint32_t(transforms.capacity());
 
 	if (impl->topology_dirty) {
@@ -662,7 +705,10 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 	if (impl->anims_dirty) {
 		std::vector<int64_t> v3_t, q_t;
 		std::vector<float> v3_val, v3_tension, v3_bias, q_val;
-		std::vector<hgb_track> tracks;
+		std::vector<hgb_track> tracks, en_tracks;
+		std::vector<int64_t> en_t;
+		std::vector<uint8_t> en_v;
+		impl->enable_nodes.clear();
 		uint32_t n_play = 0;
 		for (uint32_t pi = play_anims.first(); pi != play_anims.invalid_idx; pi = play_anims.next(pi)) {
 			ScenePlayAnim_ &p = play_anims[pi];
@@ -680,6 +726,17 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 				if (!transforms.is_valid(t))
 					continue;
 				const Anim &anim = anims[na.anim.idx];
+				int en = -1; // "Enable" bool track: the last one with that target (BindNodeAnim scene.cpp:2083-2089)
+				for (size_t i = 0; i < anim.bool_tracks.size(); ++i)
+					if (anim.bool_tracks[i].target == "Enable")
+						en = int(i);
+				if (en >= 0) {
+					const auto &keys = anim.bool_tracks[en].keys;
+					en_tracks.push_back(hgb_track{t.idx, uint32_t(en_t.size()), uint32_t(keys.size()), uint16_t(p.play_slot), 4, 0});
+					for (const auto &k : keys)
+						en_t.push_back(k.t), en_v.push_back(k.v ? 1 : 0);
+					impl->enable_nodes.push_back({t.idx, na.node.idx});
+				}
 				int pos = -1, rot = -1, scl = -1, qrot = -1;
 				for (size_t i = 0; i < anim.vec3_tracks.size(); ++i) {
 					const std::string &tg = anim.vec3_tracks[i].target;
@@ -722,6 +779,8 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 		check(hgb_set_anim_keys(ctx, uint32_t(v3_t.size()), v3_t.data(), v3_val.data(), v3_tension.data(), v3_bias.data(), uint32_t(q_t.size()), q_t.data(),
 			q_val.data()));
 		check(hgb_set_tracks(ctx, uint32_t(tracks.size()), tracks.data(), n_play));
+		check(hgb_set_enable_tracks(ctx, uint32_t(en_tracks.size()), en_tracks.data(), uint32_t(en_t.size()), en_t.data(), en_v.data()));
+		impl->enable_state_push = !impl->enable_nodes.empty();
 		impl->play_t.assign(n_play, HGB_NOT_PLAYING);
 		impl->anims_dirty = false;
 	}
@@ -763,6 +822,17 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 			check(hgb_set_display_entries(ctx, k, uint32_t(mtx[k].size()), mtx[k].data(), bidx[k].data(), impl->ent_flags[k].data(), nullptr));
 		impl->entries_dirty = false;
 	}
+	if (impl->enable_state_push && !impl->enable_nodes.empty()) { // the host's flags are the truth right now: tracked nodes take them
+		std::vector<uint32_t> slots;
+		std::vector<uint8_t> dis;
+		for (const auto &sn : impl->enable_nodes)
+			if (nodes.is_used(sn.second)) {
+				slots.push_back(sn.first);
+				dis.push_back((nodes[sn.second].flags & (NF_Disabled | NF_InstanceDisabled)) ? 1 : 0);
+			}
+		check(hgb_set_enable_state(ctx, uint32_t(slots.size()), slots.data(), dis.data()));
+	}
+	impl->enable_state_push = false;
 	if (impl->views_dirty && !impl->frusta.empty()) {
 		check(hgb_set_views(ctx, uint32_t(impl->frusta.size()), &impl->frusta[0][0].x));
 		impl->views_dirty = false;
@@ -829,6 +899,12 @@ void Scene::ComputeWorldMatrices() {
 		check(hgb_set_preset_world(ctx, uint32_t(impl->preset_slots.size()), impl->preset_slots.data(), impl->preset_mats.data()));
 	const bool fused = impl->resources && !impl->frusta.empty();
 	check(hgb_update(ctx, uint32_t(impl->play_t.size()), impl->play_t.data(), fused ? 1 : 0));
+	if (!impl->enable_nodes.empty())
+		for (const int64_t t : impl->play_t)
+			if (t != HGB_NOT_PLAYING) {
+				impl->flags_stale = true; // Enable tracks were evaluated on the device
+				break;
+			}
 	std::fill(impl->play_t.begin(), impl->play_t.end(), HGB_NOT_PLAYING); // a clock drives the sampling of ONE frame
 	if (impl->rebind_after_frame)
 		impl->anims_dirty = true, impl->rebind_after_frame = false;
@@ -963,6 +1039,7 @@ bool Node::GetMinMax(const PipelineResources &resources, MinMax &minmax) const {
 void Scene::GetModelDisplayLists(std::vector<ModelDisplayList> &out_opaque, std::vector<ModelDisplayList> &out_transparent,
 	std::vector<SkinnedModelDisplayList> &out_opaque_skinned, std::vector<SkinnedModelDisplayList> &out_transparent_skinned,
 	const PipelineResources &resources) const {
+	RefreshFlagsFromDevice();
 	out_opaque.clear(), out_transparent.clear(), out_opaque_skinned.clear(), out_transparent_skinned.clear();
 	out_opaque.reserve(nodes.size());
 	for (uint32_t ni = nodes.first(); ni != nodes.invalid_idx; ni = nodes.next(ni)) {

@@ -204,6 +204,19 @@ int hgref_anim_add_vec3_track(void *h, int anim, int kind, int n_keys, const int
 	return int(a->vec3_tracks.size()) - 1;
 }
 
+// "Enable" bool track (BindNodeAnim scene.cpp:2083-2089, evaluated by EvaluateBoundAnim :2158-2162 with EvaluateStep)
+int hgref_anim_add_enable_track(void *h, int anim, int n_keys, const int64_t *t, const uint8_t *v) {
+	auto *c = static_cast<RefCtx *>(h);
+	Anim *a = c->scene->GetAnim(c->anims[anim]);
+	AnimTrackT<bool> trk;
+	trk.target = "Enable";
+	for (int i = 0; i < n_keys; ++i)
+		trk.keys.push_back({t[i], v[i] != 0});
+	a->bool_tracks.push_back(trk);
+	return int(a->bool_tracks.size()) - 1;
+}
+int hgref_is_node_enabled(void *h, int node) { return static_cast<RefCtx *>(h)->scene->IsNodeEnabled(static_cast<RefCtx *>(h)->nodes[node]) ? 1 : 0; }
+
 int hgref_anim_add_quat_track(void *h, int anim, int n_keys, const int64_t *t, const float *v4) {
 	auto *c = static_cast<RefCtx *>(h);
 	Anim *a = c->scene->GetAnim(c->anims[anim]);

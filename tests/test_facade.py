@@ -320,3 +320,54 @@ def test_scene_binary_loader_frames_match_reference(fac, ref, kind, tmp_path):
         bb, bc = b.bone_matrices().astype(np.float64), c.bone_matrices()
         assert bb.shape == bc.shape and (np.abs(bb - bc) / np.maximum(np.abs(bb), 1e-6 * np.abs(bb).max())).max() <= 1e-5
     b.close(); c.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.ref
+def test_facade_enable_tracks_match_reference(fac, ref):
+    """"Enable" bool tracks through the facade: evaluated on the device, IsNodeEnabled / GetModelDisplayLists / CullModelDisplayLists follow
+    the reference frame by frame; EnableNode / DisableNode from the host on tracked nodes after the anim ended behave like the reference."""
+    from tests.test_gpu_parity import _enable_keys
+    rng = np.random.default_rng(121)
+    fs = scenegen.static_scene(2_000, 4, 6, n_models=2, seed=121)
+    fs.model[rng.choice(fs.n, 150, replace=False)] = -1
+    nodes = np.sort(rng.choice(fs.n, 500, replace=False)).astype(np.int32)
+    scenegen.add_position_tracks(fs, nodes, rng, n_keys=6, play_loop=False)
+    plays, fs.plays = fs.plays, []  # tracks first, PlayAnim after: the reference resolves an anim's tracks when it binds (BindNodeAnim)
+    a, b = RefScene(ref, fs), RefScene(fac, fs)
+    fs.plays = plays
+    tracked = np.arange(0, len(nodes), 3)
+    kt, kv = _enable_keys(rng, len(tracked), 5, scenegen.KEY_DT)
+    for L_, s in ((ref, a), (fac, b)):
+        for k, an in enumerate(tracked):
+            L_.hgref_anim_add_enable_track(s.h, int(an), 5, P(np.ascontiguousarray(kt[k])), P(np.ascontiguousarray(kv[k])))
+        for sa, loop, scale in fs.plays:
+            L_.hgref_play_anim(s.h, sa, loop, scale)
+    fr = hostmirror.scene_frusta(fs)[0]
+    watch = nodes[tracked]
+
+    def same(frame):
+        ea = [ref.hgref_is_node_enabled(a.h, int(n)) for n in watch]
+        eb = [fac.hgref_is_node_enabled(b.h, int(n)) for n in watch]
+        assert ea == eb, "frame %d" % frame
+        (ca, la), (cb, lb) = a.display_lists(), b.display_lists()
+        assert (ca == cb).all() and all((x == y).all() for x, y in zip(la[0], lb[0]))
+        (pa, ma), (pb, mb) = a.cull(0, fr), b.cull(0, fr)
+        assert (pa == pb).all() and (ma == mb).all()
+        return sum(ea)
+
+    counts = set()
+    for frame in range(20):
+        a.update(scenegen.FRAME_DT); b.update(scenegen.FRAME_DT)
+        counts.add(same(frame))
+    assert len(counts) > 3
+    # the anim is over: host edits on tracked nodes stick
+    for L_, s in ((ref, a), (fac, b)):
+        for n in watch[:40]:
+            L_.hgref_enable_node(s.h, int(n), 0)
+        for n in watch[40:80]:
+            L_.hgref_enable_node(s.h, int(n), 1)
+    for frame in range(20, 23):
+        a.update(scenegen.FRAME_DT); b.update(scenegen.FRAME_DT)
+        same(frame)
+    a.close(); b.close()

@@ -527,3 +527,66 @@ def test_edits_while_animated(hgb, oracles):
     ctx.set_topology(np.where(parent >= 0, parent, 0xFFFFFFFF).astype(np.uint32))
     frame(); frame()
     orc.close(); ctx.close()
+
+
+def _enable_keys(rng, n_tracks, n_keys, key_dt):
+    """bool step tracks: key times on a jittered grid (some before t=0, so 'before the first key' is exercised), random values"""
+    t = (np.arange(n_keys, dtype=np.int64)[None, :] * key_dt + rng.integers(-key_dt // 3, key_dt // 3, (n_tracks, n_keys))).astype(np.int64)
+    t[: n_tracks // 4, 0] += 2 * key_dt  # a quarter of the tracks start late
+    t.sort(axis=1)
+    v = rng.integers(0, 2, (n_tracks, n_keys)).astype(np.uint8)
+    return t, v
+
+
+def test_enable_tracks_on_device(hgb, oracles):
+    """"Enable" bool tracks (EvaluateBoundAnim scene.cpp:2158-2162, EvaluateStep animation.h:130-139): nodes switch on and off from frame to
+    frame; visible lists and the per-node state equal the reference's, the state persists after the anim ended (ALM_Once) and survives a
+    table rebuild."""
+    ref, _ = oracles
+    if ref is None:
+        pytest.skip("needs the compiled reference")
+    from harfang3d_b200.capi import TRACK_DTYPE
+    from tests.oracle_lib import P
+    from tests.scene_io import RefScene
+    rng = np.random.default_rng(111)
+    fs = scenegen.static_scene(4_000, 4, 7, n_models=3, seed=111)
+    fs.model[rng.choice(fs.n, 400, replace=False)] = -1  # some tracked nodes own no display entry
+    nodes = np.sort(rng.choice(fs.n, 900, replace=False)).astype(np.int32)
+    scenegen.add_position_tracks(fs, nodes, rng, n_keys=6, play_loop=False)  # one anim per node, one scene anim, ALM_Once: ends after 5 key intervals
+    ctx = hgb.Context(0)
+    t = hostmirror.upload(ctx, fs)
+    plays, fs.plays = fs.plays, []   # the reference resolves an anim's tracks when PlayAnim binds it (BindNodeAnim): tracks first, play after
+    orc = RefScene(ref, fs)
+    fs.plays = plays
+    tracked = np.arange(0, len(nodes), 2)  # every second anim gets an Enable track
+    kt, kv = _enable_keys(rng, len(tracked), 5, scenegen.KEY_DT)
+    tr = np.zeros(len(tracked), TRACK_DTYPE)
+    tr["target_slot"] = nodes[tracked]
+    tr["key_off"] = np.arange(len(tracked)) * 5
+    tr["key_count"] = 5
+    tr["play"] = 0
+    tr["kind"] = 4
+    ctx.set_enable_tracks(tr, np.ascontiguousarray(kt.reshape(-1)), np.ascontiguousarray(kv.reshape(-1)))
+    for k, a in enumerate(tracked):
+        ref.hgref_anim_add_enable_track(orc.h, int(a), 5, P(np.ascontiguousarray(kt[k])), P(np.ascontiguousarray(kv[k])))
+    for sa, loop, scale in fs.plays:
+        ref.hgref_play_anim(orc.h, sa, loop, scale)
+    fr = hostmirror.scene_frusta(fs)[0]
+    clocks = hostmirror.PlayClocks(fs)
+    seen = set()
+    for frame in range(24):  # the anim (250 ms) ends around frame 15: the last frames check that the state sticks
+        if frame == 9:        # a table rebuild in the middle (entry flags re-sent by the host): the tracked state must survive it
+            ctx.set_entry_flags(0, 0, t["ent0_flags"][:1].copy())
+        ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True)
+        orc.update(scenegen.FRAME_DT)
+        _, mtx_ref = orc.cull(0, fr)
+        idx = ctx.get_visible(0, 0)
+        assert len(idx) == len(mtx_ref) and (t["ent0_mtx_slot"][idx] == mtx_ref).all(), "frame %d" % frame
+        slots, dis = ctx.get_enable_state()
+        assert (slots == np.sort(nodes[tracked])).all()
+        dis_ref = np.array([0 if ref.hgref_is_node_enabled(orc.h, int(s)) else 1 for s in slots], np.uint8)
+        assert (dis == dis_ref).all(), "frame %d" % frame
+        seen.add(int(dis.sum()))
+        assert (bits(ctx.get_worlds()) == bits(orc.worlds()[: fs.n])).all()
+    assert len(seen) > 3, "the tracks are expected to switch nodes on and off over the frames"
+    orc.close(); ctx.close()
