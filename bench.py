@@ -197,6 +197,8 @@ def main():
     ap.add_argument("--overlap", action="store_true", help="A/B switch: sample tracks by target level on a second stream, overlapped with the level kernels")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="N>1 result gather: peer = survivors stored into rank 0's memory over NVLink "
                     "by the compaction kernel itself, flags + acks on the device, no host sync (hgb_peer_*); nccl = counts all-gathered, host-sized send/recv (A/B)")
+    ap.add_argument("--async-post", type=int, default=None, choices=[0, 1], help="A/B switch: compaction + gather of a frame on a second stream, overlapping "
+                    "the next frame's track sampling (hgb_options.async_post)")
     ap.add_argument("--row-store", action="store_true", help="A/B switch: per-thread world row stores instead of the transposed warp store")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -217,7 +219,8 @@ def main():
 
     fs, desc = workload(args.workload, rank, args.scale)
     n_nodes = fs.n
-    ctx = harfang3d_b200.Context(local_rank, row_store=args.row_store, lookahead=args.lookahead, tma_level=args.tma_level, merge_small=args.merge_small, overlap_sampler=args.overlap, slice_nodes=args.slice_nodes)
+    ctx = harfang3d_b200.Context(local_rank, row_store=args.row_store, lookahead=args.lookahead, tma_level=args.tma_level, merge_small=args.merge_small, overlap_sampler=args.overlap, slice_nodes=args.slice_nodes,
+                                  async_post=None if args.async_post is None else bool(args.async_post))
     t = hostmirror.upload(ctx, fs)
     n_entries = len(t["ent0_mtx_slot"]) + len(t["ent1_mtx_slot"])
     clocks = hostmirror.PlayClocks(fs)

@@ -220,7 +220,25 @@ struct hgb_ctx {
 	cudaGraphExec_t graph_exec[2][2] = {}; // [fused][world-buffer parity]
 	bool graph_valid[2][2] = {};
 	uint64_t graph_kernels[2][2] = {};
+	// Asynchronous tail (hgb_options.async_post): the frame is three graphs — pre (track sampling), levels, post (compaction + the peer
+	// gather) — and the post graph runs on stream2, so that it overlaps the NEXT frame's track sampling (which touches neither the
+	// visibility bytes nor the lists). The next frame's levels wait for it; every other entry point joins it first (join_post).
+	bool async_post = false;
+	cudaGraphExec_t phase_exec[3][2] = {}; // [phase][world-buffer parity]
+	bool phase_valid[3][2] = {};
+	uint64_t phase_kernels[3][2] = {};
+	cudaEvent_t ev_lvl_done = nullptr, ev_post_done = nullptr;
+	bool post_pending = false;
 };
+
+// the asynchronous tail of the last frame must be over before anything else touches the context's stream or tables
+static void join_post(hgb_ctx *c) {
+	if (c && c->post_pending) {
+		cudaSetDevice(c->device);
+		cudaStreamWaitEvent(c->stream, c->ev_post_done, 0);
+		c->post_pending = false;
+	}
+}
 
 // bracket one kernel launch with events when profiling (never during graph capture: profiled frames use plain launches)
 static void prof_begin(hgb_ctx *c, int cls) {
@@ -262,6 +280,9 @@ static int prof_collect(hgb_ctx *c) {
 
 static void invalidate_graph(hgb_ctx *c) {
 	for (auto &a : c->graph_valid)
+		for (bool &v : a)
+			v = false;
+	for (auto &a : c->phase_valid)
 		for (bool &v : a)
 			v = false;
 }
@@ -318,6 +339,7 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 	c->overlap_sampler = opt ? opt->overlap_sampler != 0 : false;
 	if (opt && opt->slice_nodes > 0)
 		c->slice_nodes = (uint32_t(opt->slice_nodes) + 255u) & ~255u;
+	c->async_post = opt ? opt->async_post != 0 : false;
 	c->transpose_store = opt ? opt->row_store == 0 : true; // reserved[0] = 1: per-thread 48-byte row stores (A/B switch for profiling)
 	if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
 		cudaEventCreate(&c->ev1) != cudaSuccess) {
@@ -326,7 +348,8 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		return nullptr;
 	}
 	c->stream = c->own_stream;
-	if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) {
+	if (cudaEventCreateWithFlags(&c->ev_lvl_done, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&c->ev_post_done, cudaEventDisableTiming) != cudaSuccess ||
+		cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) {
 		fail("hgb_create: stream creation failed: %s", cudaGetErrorString(cudaGetLastError()));
 		delete c;
 		return nullptr;
@@ -357,8 +380,15 @@ void hgb_destroy(hgb_ctx *c) {
 	if (!c)
 		return;
 	cudaSetDevice(c->device);
+	join_post(c);
 	cudaStreamSynchronize(c->stream);
+	if (c->stream2)
+		cudaStreamSynchronize(c->stream2);
 	peer_release(c);
+	for (auto &a : c->phase_exec)
+		for (cudaGraphExec_t g : a)
+			if (g)
+				cudaGraphExecDestroy(g);
 	for (auto &a : c->graph_exec)
 		for (cudaGraphExec_t g : a)
 			if (g)
@@ -395,6 +425,7 @@ void hgb_destroy(hgb_ctx *c) {
 int hgb_set_stream(hgb_ctx *c, void *s) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	CK(cudaStreamSynchronize(c->stream));
 	c->stream = s ? static_cast<cudaStream_t>(s) : c->own_stream;
 	invalidate_graph(c);
@@ -404,6 +435,7 @@ int hgb_set_stream(hgb_ctx *c, void *s) {
 int hgb_sync(hgb_ctx *c) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	CK(cudaSetDevice(c->device));
 	CK(cudaStreamSynchronize(c->stream));
 	return 0;
@@ -416,12 +448,14 @@ int hgb_is_identity_order(hgb_ctx *c) { return c && c->identity ? 1 : 0; }
 int hgb_time_begin(hgb_ctx *c) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	CK(cudaEventRecord(c->ev0, c->stream));
 	return 0;
 }
 int hgb_time_end(hgb_ctx *c, float *ms) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	CK(cudaEventRecord(c->ev1, c->stream));
 	CK(cudaEventSynchronize(c->ev1));
 	CK(cudaEventElapsedTime(ms, c->ev0, c->ev1));
@@ -430,6 +464,7 @@ int hgb_time_end(hgb_ctx *c, float *ms) {
 int hgb_set_profiling(hgb_ctx *c, int on) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (prof_collect(c))
 		return 1;
 	c->prof.on = on != 0;
@@ -438,6 +473,7 @@ int hgb_set_profiling(hgb_ctx *c, int on) {
 int hgb_get_profile(hgb_ctx *c, double *ms_by_class, uint64_t *launches_by_class, int reset) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (prof_collect(c))
 		return 1;
 	for (int k = 0; k < HGB_K_COUNT; ++k) {
@@ -455,6 +491,7 @@ int hgb_get_profile(hgb_ctx *c, double *ms_by_class, uint64_t *launches_by_class
 int hgb_flush_l2(hgb_ctx *c, size_t bytes) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	CK(c->flush.reserve(bytes));
 	CK(cudaMemsetAsync(c->flush.p, 0x5a, bytes, c->stream));
 	return 0;

@@ -113,11 +113,14 @@ static int launch_small_run(hgb_ctx *c, const SceneDev &s, bool do_fused, size_t
 // and issue-light, the level kernels issue-heavy: with `overlap_sampler` the tracks are sampled in chunks by TARGET LEVEL on a second
 // stream, each level group waiting only for its own chunk — so the chunk of the (huge) last level streams its keys while the upper
 // levels compute. Tracks are sorted by target position (prepare_tables), so a chunk is a contiguous track range.
-static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint64_t *n_k) {
+constexpr int kPhasePre = 1, kPhaseLevels = 2, kPhasePost = 4, kPhaseAll = 7;
+static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint64_t *n_k, int phases = kPhaseAll) {
 	const SceneDev s = scene_dev(c, with_preset);
 	const bool do_fused = fused && (c->ent[0].n || c->ent[1].n);
 	const size_t n_levels = c->level_off.size() - 1;
-	if (c->peer.on && do_fused)
+	if (phases == kPhasePost)
+		return do_fused ? enqueue_compaction(c, n_k, true) : 0;
+	if (c->peer.on && do_fused && (phases & kPhasePre))
 		peer_enqueue_begin(c, n_k);
 	const bool has_anim = c->n_tracks && c->n_play;
 	AnimDev a{};
@@ -138,7 +141,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		uint32_t b, e;   // positions (a slice when d1 == d0 + 1)
 		uint32_t widest;
 	};
-	const bool want_overlap = has_anim && c->overlap_sampler && !c->prof.on && c->round_off.size() == 2 && !c->trk_pos_h.empty();
+	const bool want_overlap = has_anim && c->overlap_sampler && !c->prof.on && c->round_off.size() == 2 && !c->trk_pos_h.empty() && phases == kPhaseAll;
 	std::vector<Group> groups;
 	for (size_t d = 0; d < n_levels;) {
 		if (c->level_off[d + 1] == c->level_off[d]) {
@@ -178,7 +181,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	}
 	const bool overlap = want_overlap;
 	std::vector<char> has_chunk(groups.size(), 0);
-	if (has_anim && !overlap) { // sequential: one launch per write round (normally one)
+	if (has_anim && !overlap && (phases & kPhasePre)) { // sequential: one launch per write round (normally one)
 		for (size_t r = 0; r + 1 < c->round_off.size(); ++r) {
 			const uint32_t first = c->round_off[r], cnt = c->round_off[r + 1] - first;
 			if (!cnt)
@@ -205,7 +208,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		CK(cudaEventRecord(c->ev_chunk[1], c->stream2)); // join point
 	}
 
-	if (!c->en_target_slot_h.empty() && c->n_play) { // "Enable" tracks: node / entry flags of this frame, before the level kernels read them
+	if (!c->en_target_slot_h.empty() && c->n_play && (phases & kPhasePre)) { // "Enable" tracks: node / entry flags of this frame, before the level kernels read them
 		EnableDev e{};
 		e.target_pos = c->en_target_pos.as<uint32_t>();
 		e.off = c->en_off.as<uint32_t>();
@@ -222,6 +225,10 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		++*n_k;
 	}
 
+	if (!(phases & kPhaseLevels)) {
+		CK(cudaGetLastError());
+		return 0;
+	}
 	for (size_t g = 0; g < groups.size(); ++g) {
 		if (has_chunk[g])
 			CK(cudaStreamWaitEvent(c->stream, c->ev_chunk[g + 2], 0));
@@ -238,8 +245,58 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	if (overlap)
 		CK(cudaStreamWaitEvent(c->stream, c->ev_chunk[1], 0));
 	CK(cudaGetLastError());
-	if (do_fused)
+	if (do_fused && (phases & kPhasePost))
 		return enqueue_compaction(c, n_k, true);
+	return 0;
+}
+
+// asynchronous tail: the frame as three graphs; pre and levels on the context's stream, post on stream2 (see hgb_ctx::async_post)
+static int launch_phase_graph(hgb_ctx *c, int phase_idx, cudaStream_t on) {
+	const int par = c->cur;
+	if (!c->phase_valid[phase_idx][par]) {
+		if (c->phase_exec[phase_idx][par]) {
+			cudaGraphExecDestroy(c->phase_exec[phase_idx][par]);
+			c->phase_exec[phase_idx][par] = nullptr;
+		}
+		cudaGraph_t g = nullptr;
+		uint64_t k = 0;
+		const cudaStream_t keep = c->stream;
+		c->stream = on; // the enqueue helpers launch on c->stream
+		cudaError_t e = cudaStreamBeginCapture(on, cudaStreamCaptureModeThreadLocal);
+		int rc = 1;
+		if (e == cudaSuccess) {
+			rc = enqueue_frame_kernels(c, true, false, &k, 1 << phase_idx);
+			e = cudaStreamEndCapture(on, &g);
+		}
+		c->stream = keep;
+		if (rc)
+			return 1;
+		if (e != cudaSuccess)
+			return fail("frame phase capture: %s", cudaGetErrorString(e));
+		CK(cudaGraphInstantiate(&c->phase_exec[phase_idx][par], g, 0));
+		cudaGraphDestroy(g);
+		c->phase_kernels[phase_idx][par] = k;
+		c->phase_valid[phase_idx][par] = true;
+	}
+	if (c->phase_kernels[phase_idx][par])
+		CK(cudaGraphLaunch(c->phase_exec[phase_idx][par], on));
+	c->launches += c->phase_kernels[phase_idx][par];
+	return 0;
+}
+
+static int launch_frame_async(hgb_ctx *c) {
+	if (launch_phase_graph(c, 0, c->stream)) // track sampling: independent of the previous frame's tail
+		return 1;
+	if (c->post_pending) // the levels overwrite the visibility bytes the previous tail compacts
+		CK(cudaStreamWaitEvent(c->stream, c->ev_post_done, 0));
+	if (launch_phase_graph(c, 1, c->stream))
+		return 1;
+	CK(cudaEventRecord(c->ev_lvl_done, c->stream));
+	CK(cudaStreamWaitEvent(c->stream2, c->ev_lvl_done, 0));
+	if (launch_phase_graph(c, 2, c->stream2))
+		return 1;
+	CK(cudaEventRecord(c->ev_post_done, c->stream2));
+	c->post_pending = true;
 	return 0;
 }
 
@@ -311,6 +368,9 @@ int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cul
 	if (!c->en_target_slot_h.empty() && c->n_play)
 		c->en_state_dirty = true;
 	const bool fused = fused_cull != 0;
+	if (c->async_post && c->use_graph && fused && !with_preset && !c->prof.on && (c->ent[0].n || c->ent[1].n))
+		return launch_frame_async(c);
+	join_post(c);
 	if (!c->use_graph || with_preset || c->prof.on) {
 		uint64_t k = 0;
 		if (enqueue_frame_kernels(c, fused, with_preset, &k))
@@ -324,6 +384,7 @@ int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cul
 int hgb_cull(hgb_ctx *c) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	CK(cudaSetDevice(c->device));
 	if (!c->instance_mode && c->views.n_views == 0)
 		return fail("hgb_cull: no views set");
@@ -362,6 +423,7 @@ int hgb_cull_list(hgb_ctx *c, uint32_t n, const uint32_t *mtx_slot, const uint32
 	uint32_t *out_idx, uint32_t *out_count) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (out_count)
 		*out_count = 0;
 	if (!n)
@@ -427,6 +489,7 @@ int hgb_cull_list(hgb_ctx *c, uint32_t n, const uint32_t *mtx_slot, const uint32
 int hgb_bone_matrices(hgb_ctx *c, int with_previous) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (!c->n_bones)
 		return 0;
 	CK(cudaSetDevice(c->device));
@@ -487,6 +550,7 @@ static int resolve_objects(hgb_ctx *c) {
 int hgb_minmax(hgb_ctx *c) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	CK(cudaSetDevice(c->device));
 	if (resolve_objects(c))
 		return 1;
@@ -520,6 +584,7 @@ int hgb_minmax(hgb_ctx *c) {
 int hgb_get_minmax(hgb_ctx *c, float *out6, uint32_t *out_count) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (!c->n_seg)
 		return 0;
 	if (!c->mm_acc.p || c->obj_dirty)
@@ -542,6 +607,7 @@ int hgb_get_minmax(hgb_ctx *c, float *out6, uint32_t *out_count) {
 int hgb_sort_keys(hgb_ctx *c, int kind, uint32_t view, const float *view_mat12) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews) || !view_mat12)
 		return fail("hgb_sort_keys: bad kind/view/matrix");
 	EntryTable &t = c->ent[kind];
@@ -591,6 +657,7 @@ int hgb_get_sort_keys(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_keys, u
 int hgb_get_worlds(hgb_ctx *c, uint32_t first, uint32_t count, float *out12, int previous) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (uint64_t(first) + count > c->n_slots)
 		return fail("hgb_get_worlds: range outside the topology");
 	if (!count)
@@ -613,6 +680,7 @@ int hgb_get_worlds(hgb_ctx *c, uint32_t first, uint32_t count, float *out12, int
 int hgb_get_trs(hgb_ctx *c, uint32_t first, uint32_t count, float *out9) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (uint64_t(first) + count > c->n_slots)
 		return fail("hgb_get_trs: range outside the topology");
 	if (!count)
@@ -630,6 +698,7 @@ int hgb_get_trs(hgb_ctx *c, uint32_t first, uint32_t count, float *out9) {
 int hgb_get_visible_count(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_count) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews))
 		return fail("hgb_get_visible_count: bad kind/view");
 	*out_count = 0;
@@ -659,6 +728,7 @@ int hgb_get_visible(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_idx, uint
 int hgb_get_instance_offsets(hgb_ctx *c, uint32_t *out) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (!c->instance_mode)
 		return fail("hgb_get_instance_offsets: not in instance mode");
 	CK(cudaSetDevice(c->device));
@@ -674,6 +744,7 @@ int hgb_get_instance_offsets(hgb_ctx *c, uint32_t *out) {
 int hgb_get_bone_matrices(hgb_ctx *c, float *out16, int previous) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (!c->n_bones)
 		return 0;
 	CK(cudaSetDevice(c->device));

@@ -8,6 +8,7 @@ int hgb_peer_init(hgb_ctx *c, uint32_t rank, uint32_t world, uint32_t dst, const
 	hgb_peer_handle *inbox_out, hgb_peer_handle *mailbox_out) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (world == 0 || world > uint32_t(kMaxPeers) || rank >= world || dst >= world)
 		return fail("hgb_peer_init: bad rank / world / dst (at most %d ranks)", kMaxPeers);
 	CK(cudaSetDevice(c->device));
@@ -57,6 +58,7 @@ int hgb_peer_init(hgb_ctx *c, uint32_t rank, uint32_t world, uint32_t dst, const
 int hgb_peer_connect(hgb_ctx *c, const hgb_peer_handle *inbox_of_dst, const hgb_peer_handle *mailboxes) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	Peer &p = c->peer;
 	if (!p.world || !p.mailbox)
 		return fail("hgb_peer_connect: hgb_peer_init first");
@@ -90,6 +92,7 @@ int hgb_peer_connect(hgb_ctx *c, const hgb_peer_handle *inbox_of_dst, const hgb_
 int hgb_peer_status(hgb_ctx *c, uint32_t *out_step, uint32_t *out_error) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	Peer &p = c->peer;
 	if (!p.mailbox)
 		return fail("hgb_peer_status: no peer gather on this context");
@@ -107,6 +110,7 @@ int hgb_peer_status(hgb_ctx *c, uint32_t *out_step, uint32_t *out_error) {
 int hgb_peer_result(hgb_ctx *c, uint32_t *out_rank_off, uint32_t *out_idx, uint32_t idx_capacity, uint32_t *out_aux, uint32_t aux_capacity) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	Peer &p = c->peer;
 	if (!p.on || p.rank != p.dst)
 		return fail("hgb_peer_result: only the gather destination holds the result");

@@ -68,6 +68,7 @@ extern "C" {
 int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const uint8_t *used) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (fold_enable_state(c)) // the tiles are about to be rebuilt
 		return 1;
 	c->en_resolved = false;
@@ -199,6 +200,7 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 int hgb_upload_trs(hgb_ctx *c, uint32_t first, uint32_t count, const float *trs9) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (uint64_t(first) + count > c->n_slots)
 		return fail("hgb_upload_trs: range [%u,%u) outside the %u slots of the topology", first, first + count, c->n_slots);
 	if (!count)
@@ -218,6 +220,7 @@ int hgb_upload_trs(hgb_ctx *c, uint32_t first, uint32_t count, const float *trs9
 int hgb_set_preset_world(hgb_ctx *c, uint32_t n, const uint32_t *slot, const float *mat12) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	CK(cudaSetDevice(c->device));
 	std::vector<uint32_t> pos(n);
 	for (uint32_t i = 0; i < n; ++i) {
@@ -239,6 +242,7 @@ int hgb_set_preset_world(hgb_ctx *c, uint32_t n, const uint32_t *slot, const flo
 int hgb_set_matrices(hgb_ctx *c, uint32_t n, const uint32_t *slot, const float *mat12, int is_local) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (!n)
 		return 0;
 	CK(cudaSetDevice(c->device));
@@ -288,6 +292,7 @@ int hgb_set_objects(hgb_ctx *c, uint32_t n_obj, const uint32_t *mtx_slot, const 
 	const uint32_t *seg, uint32_t n_seg) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (n_obounds >= (1u << 24))
 		return fail("hgb_set_objects: too many object bounds");
 	if (n_obj && n_seg == 0)
@@ -318,6 +323,7 @@ int hgb_set_objects(hgb_ctx *c, uint32_t n_obj, const uint32_t *mtx_slot, const 
 int hgb_set_bounds(hgb_ctx *c, uint32_t n, const float *minmax6) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (n >= (1u << 24))
 		return fail("hgb_set_bounds: too many bounds");
 	CK(cudaSetDevice(c->device));
@@ -333,6 +339,7 @@ int hgb_set_bounds(hgb_ctx *c, uint32_t n, const float *minmax6) {
 int hgb_set_display_entries(hgb_ctx *c, int kind, uint32_t n, const uint32_t *mtx_slot, const uint32_t *bounds_idx, const uint8_t *flags, const uint16_t *view) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (kind != 0 && kind != 1)
 		return fail("hgb_set_display_entries: kind must be 0 (opaque) or 1 (transparent)");
 	if (n >= 0x7fffffffu)
@@ -357,6 +364,7 @@ int hgb_set_display_entries(hgb_ctx *c, int kind, uint32_t n, const uint32_t *mt
 int hgb_set_entry_flags(hgb_ctx *c, int kind, uint32_t first, uint32_t count, const uint8_t *flags) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (fold_enable_state(c)) // this explicit write must land AFTER what the tracks did so far
 		return 1;
 
@@ -374,6 +382,7 @@ int hgb_set_entry_flags(hgb_ctx *c, int kind, uint32_t first, uint32_t count, co
 int hgb_set_skins(hgb_ctx *c, uint32_t n_bones, const uint32_t *mtx_slot, const uint32_t *bind_idx, uint32_t n_bind, const float *bind_pose12) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	CK(cudaSetDevice(c->device));
 	for (uint32_t i = 0; i < n_bones; ++i)
 		if (bind_idx[i] >= n_bind)
@@ -394,6 +403,7 @@ int hgb_set_anim_keys(hgb_ctx *c, uint32_t n3, const int64_t *v3_t, const float 
 	const int64_t *q_t, const float *q_val4) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	CK(cudaSetDevice(c->device));
 	// one 32-byte record per key: {t (8), v.x, v.y | v.z, tension or v.w, bias, 0}; quaternion keys after the vec3 keys
 	const size_t total = size_t(n3) + nq;
@@ -428,6 +438,7 @@ int hgb_set_anim_keys(hgb_ctx *c, uint32_t n3, const int64_t *v3_t, const float 
 int hgb_set_tracks(hgb_ctx *c, uint32_t n, const hgb_track *tracks, uint32_t n_play) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	for (uint32_t i = 0; i < n; ++i) {
 		if (tracks[i].target_slot >= c->n_slots)
 			return fail("hgb_set_tracks: track %u targets slot %u outside the topology", i, tracks[i].target_slot);
@@ -492,6 +503,7 @@ int hgb_set_tracks(hgb_ctx *c, uint32_t n, const hgb_track *tracks, uint32_t n_p
 int hgb_set_enable_tracks(hgb_ctx *c, uint32_t n_tracks, const hgb_track *tracks, uint32_t n_keys, const int64_t *key_t, const uint8_t *key_v) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	for (uint32_t i = 0; i < n_tracks; ++i) {
 		if (tracks[i].target_slot >= c->n_slots)
 			return fail("hgb_set_enable_tracks: track %u targets slot %u outside the topology", i, tracks[i].target_slot);
@@ -527,6 +539,7 @@ int hgb_set_enable_tracks(hgb_ctx *c, uint32_t n_tracks, const hgb_track *tracks
 int hgb_set_enable_state(hgb_ctx *c, uint32_t n, const uint32_t *slot, const uint8_t *disabled) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (fold_enable_state(c)) // what the tracks did so far comes first, this explicit write lands after it
 		return 1;
 	for (uint32_t i = 0; i < n; ++i) {
@@ -551,6 +564,7 @@ int hgb_set_enable_state(hgb_ctx *c, uint32_t n, const uint32_t *slot, const uin
 int hgb_get_enable_state(hgb_ctx *c, uint32_t capacity, uint32_t *out_slot, uint8_t *out_disabled, uint32_t *out_count) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (prepare_tables(c)) // tracks set but never resolved: resolve so that the device bits can be read
 		return 1;
 	c->en_state_dirty = c->en_state_dirty || !c->en_target_slot_h.empty();
@@ -569,6 +583,7 @@ int hgb_get_enable_state(hgb_ctx *c, uint32_t capacity, uint32_t *out_slot, uint
 int hgb_set_views(hgb_ctx *c, uint32_t n_views, const float *frustum24) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (n_views > kMaxViews)
 		return fail("hgb_set_views: at most %d views per pass", kMaxViews);
 	CK(cudaSetDevice(c->device));
@@ -589,6 +604,7 @@ int hgb_set_views(hgb_ctx *c, uint32_t n_views, const float *frustum24) {
 int hgb_set_instance_views(hgb_ctx *c, uint32_t n_inst, const float *frustum24, const uint32_t *inst_entry_start) {
 	if (!c)
 		return fail("null context");
+	join_post(c);
 	if (n_inst > 65535)
 		return fail("hgb_set_instance_views: at most 65535 instances per context (uint16 view id)");
 	CK(cudaSetDevice(c->device));
@@ -619,6 +635,7 @@ static int prepare_tables(hgb_ctx *c) {
 	if (!c->entries_dirty)
 		return 0;
 	CK(cudaSetDevice(c->device));
+	join_post(c); // the tables are about to be rebuilt
 	if (fold_enable_state(c))
 		return 1;
 	if (c->n_bound) { // give the track-driven triples their values back before rows are rewritten and tracks re-bound

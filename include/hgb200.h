@@ -49,7 +49,9 @@ typedef struct hgb_options {
 	int tma_level;     /* profiling A/B switch. 0 (default): level kernel with one thread per node, tile rows read with 128-byte LDGs (+ the
 	                      L2 look-ahead above); 1: persistent level kernel, node tiles staged with TMA bulk copies, world rows leave as
 	                      bulk stores (measured 3 % slower on the 16M-node batch, profiles/README.md r01c) */
-	int reserved0;
+	int async_post;    /* 1: the tail of the frame — compaction of the visible lists and the peer gather — runs on a second stream and overlaps
+	                      the NEXT frame's track sampling; the next frame's level kernels and every other entry point wait for it, so
+	                      results and API semantics are unchanged. Default 0 */
 	int merge_small;   /* 1: runs of consecutive small levels go out as one cooperative launch with grid barriers between the levels
 	                      (k_update_levels_small). Default 0: measured faster per kernel but not inside the frame graph (profiles r01c) */
 	int overlap_sampler; /* 1: tracks are sampled in chunks by target level on a second stream, overlapped with the level kernels. Default 0:
