@@ -199,7 +199,7 @@ struct hgb_ctx {
 	DBuf peer_out_list, peer_rank_off, peer_aux_out;
 
 	// animation
-	DBuf keys, cursor, tracks_d, play_t_d; // keys: 32-byte records, vec3 keys then quaternion keys
+	DBuf keys, cursor, tstate, tracks_d, play_t_d; // keys: 32-byte records, vec3 keys then quaternion keys
 	DBuf key_rec;                          // 128-byte interval records, one per key (k_build_key_records)
 	bool records_dirty = true;
 	uint32_t n_v3_keys = 0, n_q_keys = 0;
@@ -395,7 +395,7 @@ void hgb_destroy(hgb_ctx *c) {
 				cudaGraphExecDestroy(g);
 	DBuf *bufs[] = {&c->tiles, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
 		&c->pent, &c->pos_view, &c->inst_planes, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
-		&c->bone_out[1], &c->keys, &c->cursor, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes, &c->level_barrier, &c->key_rec,
+		&c->bone_out[1], &c->keys, &c->cursor, &c->tstate, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes, &c->level_barrier, &c->key_rec,
 		&c->en_target_pos, &c->en_off, &c->en_tracks_d, &c->en_keys_d, &c->en_scratch, &c->obj_pos, &c->obj_meta, &c->obj_seg, &c->obounds, &c->mm_acc, &c->peer_out_list, &c->peer_rank_off, &c->peer_aux_out};
 	for (DBuf *b : bufs)
 		b->release();

@@ -131,6 +131,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		a.rec = c->key_rec.as<uint4>();
 		a.quat_base = c->n_v3_keys;
 		a.cursor = c->cursor.as<uint32_t>();
+		a.tstate = c->tstate.as<uint4>();
 		a.anim_val = c->anim_val.as<float4>();
 	}
 	// level groups: a level, a run of small levels, or — with the overlapped sampler — a slice of a big level, so that the sampler chunk

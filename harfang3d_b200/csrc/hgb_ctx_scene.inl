@@ -495,6 +495,8 @@ int hgb_set_tracks(hgb_ctx *c, uint32_t n, const hgb_track *tracks, uint32_t n_p
 	CK(c->play_t_h.reserve(std::max<size_t>(n_play, 1) * 8));
 	CK(c->cursor.reserve(std::max<size_t>(n, 1) * 4));
 	CK(cudaMemsetAsync(c->cursor.p, 0, c->cursor.cap, c->stream));
+	CK(c->tstate.reserve(std::max<size_t>(n, 1) * 16));
+	CK(cudaMemsetAsync(c->tstate.p, 0, c->tstate.cap, c->stream));
 	c->entries_dirty = true; // target positions are resolved with the entries
 	invalidate_graph(c);
 	return 0;
@@ -815,6 +817,7 @@ static int prepare_tables(hgb_ctx *c) {
 			return 1;
 		CK(c->anim_val.reserve(size_t(n_bind) * 16));
 		CK(cudaMemsetAsync(c->cursor.p, 0, c->cursor.cap, c->stream));
+		CK(cudaMemsetAsync(c->tstate.p, 0, c->tstate.cap, c->stream));
 		k_bind_lanes<<<grid_for(n_bind), 256, 0, c->stream>>>(c->tiles.as<uint32_t>(), c->anim_val.as<float4>(), c->bind_pos_d.as<uint32_t>(),
 			c->bind_group_d.as<uint8_t>(), n_bind, 1);
 		++c->launches;

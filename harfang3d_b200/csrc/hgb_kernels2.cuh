@@ -29,6 +29,7 @@ struct AnimDev {
 	const uint4 *rec;         // interval records: 8 x uint4 (128 B, aligned) per key, see k_build_key_records
 	uint32_t quat_base;       // first quaternion key in the pool
 	uint32_t *cursor;         // per track: lower key of the interval found last frame (search hint only, never changes a result)
+	uint4 *tstate;            // per track: {time of key cursor, time of key cursor+1 (INT64_MAX past the end)} — hint, verified against the record
 	float4 *anim_val;         // output: one float4 per driven (node, triple); consecutive tracks write consecutive slots
 };
 
@@ -142,7 +143,7 @@ __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src) {
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
 }
 
-__global__ void __launch_bounds__(kSampleWarps * 32) k_sample_tracks(AnimDev a, uint32_t first, uint32_t n_tracks) {
+__global__ void __launch_bounds__(kSampleWarps * 32, 6) k_sample_tracks(AnimDev a, uint32_t first, uint32_t n_tracks) {
 	__shared__ __align__(16) uint8_t s_win[kSampleWarps][32 * kWinStride];
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 	const uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
@@ -165,10 +166,20 @@ __global__ void __launch_bounds__(kSampleWarps * 32) k_sample_tracks(AnimDev a, 
 	const uint8_t *pool = reinterpret_cast<const uint8_t *>(a.rec);
 	auto t_of = [](const uint4 &k) { return int64_t(uint64_t(k.x) | (uint64_t(k.y) << 32)); };
 
-	uint32_t kf1 = active ? min(a.cursor[i], n - 1) : 0u; // record wanted
-	uint32_t ub = 0, sh = 0;                              // sh = 1: interval advanced by one key, slots shift by one
-	uint4 nDa = make_uint4(0, 0, 0, 0), nDb = nDa;        // ... and this is the new fourth key
+	// Which record? The per-track state {time of the cursor's key, time of the next key} (16 bytes, read coalesced) tells BEFORE the
+	// fetch whether this frame stays in last frame's interval or enters the next one, so that one aligned 128-byte record per track is
+	// all a frame reads, whether or not the track advances (a frame that advanced used to pay a second, dependent fetch: 205 instead
+	// of 106 µs for the 4M tracks of the c4 batch, profiles/README.md r01d). The state is a hint: the fetched record carries the key
+	// times and is verified; anything unexpected (time jump, loop wrap, state never written) falls back to the binary search + refetch.
+	uint32_t cur = 0, kf1 = 0, ub = 0;
+	int64_t t_cur = 0, t_next = 0;
 	bool want = active;
+	if (active) {
+		cur = min(a.cursor[i], n - 1);
+		const uint4 st = a.tstate[i];
+		t_cur = int64_t(uint64_t(st.x) | (uint64_t(st.y) << 32)), t_next = int64_t(uint64_t(st.z) | (uint64_t(st.w) << 32));
+		kf1 = (cur + 1 < n && at >= t_next && t_next > t_cur) ? cur + 1 : cur;
+	}
 #pragma unroll 1
 	for (int pass = 0; pass < 2; ++pass) {
 		// cooperative fetch: round r serves tracks 4r..4r+3
@@ -184,36 +195,38 @@ __global__ void __launch_bounds__(kSampleWarps * 32) k_sample_tracks(AnimDev a, 
 		__syncwarp();
 		if (pass == 1)
 			break;
-		// interval: the one found last frame, or the next one (a frame rarely advances more than one key), else the binary search
 		want = false;
 		if (active) {
-			const uint32_t cur = kf1;
+			// record kf1 = keys {kf1-1, kf1, kf1+1, kf1+2} (clamped): the interval [key kf1, key kf1+1) is the right one when
+			// key kf1 <= at < key kf1+1, or at/after the last key, or before the first one
 			const int64_t tB = t_of(win[2]), tC = t_of(win[4]);
-			if (tB <= at && (cur + 1 == n || at < tC)) {
-				ub = cur + 1;
-			} else if (cur + 1 < n && tC <= at && (cur + 2 == n || at < t_of(win[6]))) {
-				// next interval: its record is this one shifted by a key; only its fourth key (32 bytes) is new
-				ub = cur + 2;
-				sh = 1;
-				nDa = rec[size_t(cur + 1) * 8 + 6], nDb = rec[size_t(cur + 1) * 8 + 7];
-				a.cursor[i] = cur + 1;
+			if (tB <= at && (kf1 + 1 == n || at < tC)) {
+				ub = kf1 + 1;
+			} else if (kf1 == 0 && at < tB) {
+				ub = 0;
 			} else {
 				ub = upper_bound_rec(rec, n, at);
-				kf1 = ub > 0 ? ub - 1 : 0; // ub == 0: before the first key -> key 0; ub == n: at/after the last key -> key n-1
-				if (kf1 != cur) {
-					a.cursor[i] = kf1;
-					want = true;
-				}
+				const uint32_t k = ub > 0 ? ub - 1 : 0; // ub == 0: before the first key -> key 0; ub == n: at/after the last key -> key n-1
+				want = k != kf1;
+				kf1 = k;
 			}
 		}
 		if (!__any_sync(0xffffffffu, want))
 			break;
 		__syncwarp(); // every lane has read its pass-0 record before pass 1 overwrites windows
 	}
+	if (active) { // the hint of the next frame (written only when it changes: once per interval)
+		const int64_t tB = t_of(win[2]);
+		const int64_t tC = kf1 + 1 < n ? t_of(win[4]) : INT64_MAX;
+		if (kf1 != cur)
+			a.cursor[i] = kf1;
+		if (tB != t_cur || tC != t_next)
+			a.tstate[i] = make_uint4(uint32_t(uint64_t(tB)), uint32_t(uint64_t(tB) >> 32), uint32_t(uint64_t(tC)), uint32_t(uint64_t(tC) >> 32));
+	}
 	if (!active)
 		return;
 	// slots kf0, kf1, kf2, kf3 of EvaluateHermite (animation.h:155-169), neighbours clamped to the track
-	const uint4 *w = win + sh * 2;
+	const uint4 *w = win;
 	const uint4 kBa = w[2], kBb = w[3];
 	float4 *dst = a.anim_val + trk.out_slot;
 
@@ -238,7 +251,7 @@ __global__ void __launch_bounds__(kSampleWarps * 32) k_sample_tracks(AnimDev a, 
 		ox = __uint_as_float(kBa.z), oy = __uint_as_float(kBa.w), oz = __uint_as_float(kBb.x);
 	} else {
 		const uint4 kAa = w[0], kAb = w[1], kCa = w[4], kCb = w[5];
-		const uint4 kDa = sh ? nDa : win[6], kDb = sh ? nDb : win[7];
+		const uint4 kDa = win[6], kDb = win[7];
 		const int64_t t1 = t_of(kBa), t2 = t_of(kCa);
 		const float u = time_to_sec_f(at - t1) / time_to_sec_f(t2 - t1);
 		const float tension = __uint_as_float(kBb.y), bias = __uint_as_float(kBb.z);
