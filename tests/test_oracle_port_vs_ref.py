@@ -157,4 +157,15 @@ def test_world_matrices_and_cull_scene(port, ref):
     k_port = port.hgp_cull(int(counts[0]), P(mtx), P(mdl.astype(np.uint32)), P(np.stack(bounds)), P(w_port), P(fr), P(vis))
     assert k_ref == k_port and 0 < k_ref < counts[0]
     assert (pos[:k_ref] == vis[:k_port]).all()
+
+    # Scene::GetMinMax (scene.cpp:1982) = union over object nodes (disabled ones too) of world * bounds, restated with the port's Arvo
+    # transform; min / max are exact, so the boxes agree as values (Union keeps whichever signed zero came first)
+    mm_ref = np.zeros(6, np.float32)
+    assert ref.hgref_minmax(h, 0, -1, P(mm_ref)) == 1
+    boxes = np.zeros((n, 6), np.float32)
+    for i in range(n):
+        port.hgp_minmax_transform(P(np.ascontiguousarray(w_port[i])), P(bounds[model[i]]), P(boxes[i]))
+    assert (np.concatenate([boxes[:, :3].min(0), boxes[:, 3:].max(0)]) == mm_ref).all()
+    assert ref.hgref_minmax(h, 100, 50, P(mm_ref)) == 1  # GetNodesMinMax over a node range
+    assert (np.concatenate([boxes[100:150, :3].min(0), boxes[100:150, 3:].max(0)]) == mm_ref).all()
     ref.hgref_destroy(h)
