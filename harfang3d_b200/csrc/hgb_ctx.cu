@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -223,6 +224,7 @@ struct hgb_ctx {
 	// Asynchronous tail (hgb_options.async_post): the frame is three graphs — pre (track sampling), levels, post (compaction + the peer
 	// gather) — and the post graph runs on stream2, so that it overlaps the NEXT frame's track sampling (which touches neither the
 	// visibility bytes nor the lists). The next frame's levels wait for it; every other entry point joins it first (join_post).
+	bool pdl_levels = true; // level d+1 launched with a programmatic dependency on level d (HGB_PDL=0 in the environment: plain, A/B)
 	bool async_post = false;
 	cudaGraphExec_t phase_exec[3][2] = {}; // [phase][world-buffer parity]
 	bool phase_valid[3][2] = {};
@@ -340,6 +342,8 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 	if (opt && opt->slice_nodes > 0)
 		c->slice_nodes = (uint32_t(opt->slice_nodes) + 255u) & ~255u;
 	c->async_post = opt ? opt->async_post != 0 : false;
+	if (const char *e_pdl = getenv("HGB_PDL"))
+		c->pdl_levels = e_pdl[0] != '0';
 	c->transpose_store = opt ? opt->row_store == 0 : true; // reserved[0] = 1: per-thread 48-byte row stores (A/B switch for profiling)
 	if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
 		cudaEventCreate(&c->ev1) != cudaSuccess) {

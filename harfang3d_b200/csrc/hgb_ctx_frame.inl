@@ -63,7 +63,7 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false)
 	return 0;
 }
 
-static void launch_level(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t b, uint32_t e) {
+static void launch_level(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t b, uint32_t e, bool pdl = false) {
 	if (c->tma_level) { // persistent warps, TMA-staged tiles (hgb_kernels_tma.cuh)
 		const uint32_t n_lt = ((e - 1u) >> 5) - (b >> 5) + 1u;
 		const dim3 g(std::min((n_lt + kTmaWarps - 1u) / kTmaWarps, c->persistent_ctas));
@@ -74,13 +74,22 @@ static void launch_level(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t 
 		else
 			k_update_level_tma<true, false><<<g, kTmaWarps * 32, 0, c->stream>>>(s, c->views, b, e);
 	} else {
-		const dim3 g = grid_for(e - b);
+		// pdl: programmatic dependent launch on the previous level's kernel (see the griddepcontrol pair in k_update_level)
+		cudaLaunchConfig_t cfg{};
+		cfg.gridDim = grid_for(e - b);
+		cfg.blockDim = dim3(256);
+		cfg.stream = c->stream;
+		cudaLaunchAttribute at[1];
+		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+		at[0].val.programmaticStreamSerializationAllowed = 1;
+		cfg.attrs = at;
+		cfg.numAttrs = pdl ? 1 : 0;
 		if (!do_fused)
-			k_update_level<false, false><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
+			cudaLaunchKernelEx(&cfg, k_update_level<false, false>, s, c->views, b, e);
 		else if (c->instance_mode)
-			k_update_level<true, true><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
+			cudaLaunchKernelEx(&cfg, k_update_level<true, true>, s, c->views, b, e);
 		else
-			k_update_level<true, false><<<g, 256, 0, c->stream>>>(s, c->views, b, e);
+			cudaLaunchKernelEx(&cfg, k_update_level<true, false>, s, c->views, b, e);
 	}
 }
 
@@ -238,7 +247,9 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 			if (launch_small_run(c, s, do_fused, groups[g].d0, groups[g].d1 - groups[g].d0, groups[g].widest))
 				return 1;
 		} else {
-			launch_level(c, s, do_fused, groups[g].b, groups[g].e);
+			// a level that directly follows another level's plain launch may start while that one drains
+			const bool pdl = c->pdl_levels && !c->prof.on && !c->tma_level && g > 0 && !has_chunk[g] && groups[g - 1].d1 - groups[g - 1].d0 == 1;
+			launch_level(c, s, do_fused, groups[g].b, groups[g].e, pdl);
 		}
 		prof_end(c);
 		++*n_k;

@@ -93,6 +93,9 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 		stage_planes(s_planes, views);
 		__syncthreads();
 	}
+	// Programmatic dependent launch: the next level's grid may start while this one drains (it only reads its own tile rows before its
+	// griddepcontrol.wait below), which hides launch latency and the first DRAM round trip of the dependent chain of levels.
+	asm volatile("griddepcontrol.launch_dependents;");
 	const uint32_t p = begin + blockIdx.x * blockDim.x + threadIdx.x;
 	const bool live = p < end;
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -120,6 +123,9 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 			float ex = __uint_as_float(t[96]), ey = __uint_as_float(t[128]), ez = __uint_as_float(t[160]);
 			float sx = __uint_as_float(t[192]), sy = __uint_as_float(t[224]), sz = __uint_as_float(t[256]);
 			const uint32_t par = t[kRowParent * 32];
+			// everything above reads edit-time data; from here on the previous level's world rows are read (no-op without a
+			// programmatic dependency)
+			asm volatile("griddepcontrol.wait;" ::: "memory");
 			if (par != kRoot) { // start the parent row on its way while the trigonometry runs (no registers held)
 				prefetch_l1(s.world + size_t(par) * 12);
 				prefetch_l1(s.world + size_t(par) * 12 + 11);

@@ -6,7 +6,9 @@ tail -8 gpurun_out/pytest_gpu.log
 IFS=';' read -ra V <<< "$VARIANTS"
 i=0
 for v in "${V[@]}"; do
-  timeout 600 python bench.py --no-cpu-baseline $v > gpurun_out/ab_$i.json 2> gpurun_out/ab_$i.err; echo "variant [$v] exit $?"
+  # "VAR=val|args" sets an environment variable for that variant
+  e=""; case "$v" in *"|"*) e="${v%%|*}"; v="${v#*|}";; esac
+  timeout 600 env $e python bench.py --no-cpu-baseline $v > gpurun_out/ab_$i.json 2> gpurun_out/ab_$i.err; echo "variant [$e $v] exit $?"
   python - <<PY
 import json
 try:
