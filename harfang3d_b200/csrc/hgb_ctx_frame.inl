@@ -19,16 +19,47 @@ static SceneDev scene_dev(hgb_ctx *c, bool with_preset) {
 	return s;
 }
 
-// compaction of every (kind, view) list from the vis bytes; returns the number of kernels enqueued through *n_k
-static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false) {
+// Launch on the context's stream; with `pdl` as a programmatic dependent of the kernel enqueued just before it: the grid may be
+// scheduled while that kernel drains, and its griddepcontrol.wait holds it until the predecessor's writes are visible. Only for
+// kernels that execute griddepcontrol.wait before they touch anything the predecessor (or, transitively, its predecessors) wrote.
+template <typename... P, typename... A> static void launch_after(hgb_ctx *c, bool pdl, void (*kernel)(P...), dim3 grid, dim3 block, A... args) {
+	cudaLaunchConfig_t cfg{};
+	cfg.gridDim = grid;
+	cfg.blockDim = block;
+	cfg.stream = c->stream;
+	cudaLaunchAttribute at[1];
+	at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	at[0].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = at;
+	cfg.numAttrs = pdl ? 1 : 0;
+	cudaLaunchKernelEx(&cfg, kernel, P(args)...);
+}
+
+// ticket and look-back state of every compaction of the frame (enqueued ahead of the level kernels when the compaction is chained to
+// the last level by a programmatic dependency: a memset node between the two kernels would turn that edge into a full one)
+static int enqueue_compaction_reset(hgb_ctx *c) {
 	const int n_views = c->instance_mode ? 1 : c->views.n_views;
-	with_peer = with_peer && c->peer.on;
 	for (int k = 0; k < 2; ++k) {
 		EntryTable &t = c->ent[k];
 		if (!t.n)
 			continue;
 		CK(cudaMemsetAsync(t.ticket.p, 0, kMaxViews * 4, c->stream));
 		CK(cudaMemsetAsync(t.status.p, 0, size_t(t.n_tiles) * n_views * 4, c->stream));
+	}
+	return 0;
+}
+
+// compaction of every (kind, view) list from the vis bytes; returns the number of kernels enqueued through *n_k. `chained`: the reset
+// went out earlier and the kernel enqueued just before this call signals its dependents (a level kernel)
+static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false, bool chained = false) {
+	const int n_views = c->instance_mode ? 1 : c->views.n_views;
+	with_peer = with_peer && c->peer.on;
+	if (!chained && enqueue_compaction_reset(c))
+		return 1;
+	for (int k = 0; k < 2; ++k) {
+		EntryTable &t = c->ent[k];
+		if (!t.n)
+			continue;
 		for (int v = 0; v < n_views; ++v) {
 			CompactDev d{};
 			d.vis = t.vis.as<uint8_t>();
@@ -45,13 +76,13 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false)
 				d.add2 = c->peer.entry_base[c->peer.rank];
 			}
 			prof_begin(c, HGB_K_COMPACT);
-			k_compact<<<t.n_tiles, kCompactThreads, 0, c->stream>>>(d);
+			launch_after(c, chained, k_compact, dim3(t.n_tiles), dim3(kCompactThreads), d);
 			prof_end(c);
 			++*n_k;
 		}
 		if (c->instance_mode && k == 0 && c->n_inst) {
 			prof_begin(c, HGB_K_SEGMENT_RANKS);
-			k_segment_ranks<<<grid_for(c->n_inst * 32), 256, 0, c->stream>>>(t.vis.as<uint8_t>(), 0, c->inst_start.as<uint32_t>(), c->n_inst,
+			launch_after(c, chained, k_segment_ranks, grid_for(c->n_inst * 32), dim3(256), t.vis.as<uint8_t>(), 0u, c->inst_start.as<uint32_t>(), c->n_inst,
 				t.status.as<uint32_t>(), c->inst_rank.as<uint32_t>());
 			prof_end(c);
 			++*n_k;
@@ -74,22 +105,13 @@ static void launch_level(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t 
 		else
 			k_update_level_tma<true, false><<<g, kTmaWarps * 32, 0, c->stream>>>(s, c->views, b, e);
 	} else {
-		// pdl: programmatic dependent launch on the previous level's kernel (see the griddepcontrol pair in k_update_level)
-		cudaLaunchConfig_t cfg{};
-		cfg.gridDim = grid_for(e - b);
-		cfg.blockDim = dim3(256);
-		cfg.stream = c->stream;
-		cudaLaunchAttribute at[1];
-		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-		at[0].val.programmaticStreamSerializationAllowed = 1;
-		cfg.attrs = at;
-		cfg.numAttrs = pdl ? 1 : 0;
+		const dim3 g = grid_for(e - b);
 		if (!do_fused)
-			cudaLaunchKernelEx(&cfg, k_update_level<false, false>, s, c->views, b, e);
+			launch_after(c, pdl, k_update_level<false, false>, g, dim3(256), s, c->views, b, e);
 		else if (c->instance_mode)
-			cudaLaunchKernelEx(&cfg, k_update_level<true, true>, s, c->views, b, e);
+			launch_after(c, pdl, k_update_level<true, true>, g, dim3(256), s, c->views, b, e);
 		else
-			cudaLaunchKernelEx(&cfg, k_update_level<true, false>, s, c->views, b, e);
+			launch_after(c, pdl, k_update_level<true, false>, g, dim3(256), s, c->views, b, e);
 	}
 }
 
@@ -191,6 +213,12 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	}
 	const bool overlap = want_overlap;
 	std::vector<char> has_chunk(groups.size(), 0);
+	// programmatic dependencies (kernel -> kernel, nothing enqueued in between): sampler -> first level -> ... -> last level -> compactions
+	const bool chain = c->pdl_levels && !c->prof.on && !c->tma_level && !overlap;
+	const bool chain_post = chain && do_fused && phases == kPhaseAll && !groups.empty() && groups.back().d1 - groups.back().d0 == 1;
+	if (chain_post && enqueue_compaction_reset(c))
+		return 1;
+	bool prev_signals = false; // the kernel enqueued last executes griddepcontrol.launch_dependents
 	if (has_anim && !overlap && (phases & kPhasePre)) { // sequential: one launch per write round (normally one)
 		for (size_t r = 0; r + 1 < c->round_off.size(); ++r) {
 			const uint32_t first = c->round_off[r], cnt = c->round_off[r + 1] - first;
@@ -200,6 +228,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 			k_sample_tracks<<<grid_for(cnt, kSampleWarps * 32), kSampleWarps * 32, 0, c->stream>>>(a, first, cnt);
 			prof_end(c);
 			++*n_k;
+			prev_signals = true;
 		}
 	} else if (overlap) {
 		CK(cudaEventRecord(c->ev_chunk[0], c->stream)); // fork (also orders the chunks behind this frame's play-clock upload)
@@ -233,6 +262,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		e.n = uint32_t(c->en_target_slot_h.size());
 		k_sample_enable<<<grid_for(e.n, 128), 128, 0, c->stream>>>(e);
 		++*n_k;
+		prev_signals = false; // writes the flag rows the level kernels read before their wait: a full dependency
 	}
 
 	if (!(phases & kPhaseLevels)) {
@@ -246,10 +276,12 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		if (groups[g].d1 - groups[g].d0 >= 2) {
 			if (launch_small_run(c, s, do_fused, groups[g].d0, groups[g].d1 - groups[g].d0, groups[g].widest))
 				return 1;
+			prev_signals = false;
 		} else {
-			// a level that directly follows another level's plain launch may start while that one drains
-			const bool pdl = c->pdl_levels && !c->prof.on && !c->tma_level && g > 0 && !has_chunk[g] && groups[g - 1].d1 - groups[g - 1].d0 == 1;
-			launch_level(c, s, do_fused, groups[g].b, groups[g].e, pdl);
+			// a level that directly follows the sampler or another level may start while that one drains (k_update_level waits before
+			// it reads sampled values or parent rows)
+			launch_level(c, s, do_fused, groups[g].b, groups[g].e, chain && prev_signals);
+			prev_signals = true;
 		}
 		prof_end(c);
 		++*n_k;
@@ -258,7 +290,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		CK(cudaStreamWaitEvent(c->stream, c->ev_chunk[1], 0));
 	CK(cudaGetLastError());
 	if (do_fused && (phases & kPhasePost))
-		return enqueue_compaction(c, n_k, true);
+		return enqueue_compaction(c, n_k, true, chain_post && prev_signals);
 	return 0;
 }
 

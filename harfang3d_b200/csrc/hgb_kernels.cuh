@@ -253,6 +253,10 @@ struct CompactDev {
 __global__ void __launch_bounds__(kCompactThreads) k_compact(CompactDev c) {
 	__shared__ uint32_t s_tile, s_warp_sum[kCompactThreads / 32], s_prefix;
 	__shared__ uint32_t s_list[kCompactTile];
+	// chained to the last level kernel (or the previous compaction) by a programmatic dependency: resident early, held here until the
+	// visibility bytes are complete (both are no-ops in a plain launch)
+	asm volatile("griddepcontrol.launch_dependents;");
+	asm volatile("griddepcontrol.wait;" ::: "memory");
 	if (threadIdx.x == 0)
 		s_tile = atomicAdd(c.ticket, 1u);
 	__syncthreads();
@@ -364,6 +368,7 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact(CompactDev c) {
 __global__ void __launch_bounds__(256) k_segment_ranks(const uint8_t *__restrict__ vis, uint32_t bit, const uint32_t *__restrict__ seg_start, uint32_t n_seg,
 	const volatile uint32_t *status, uint32_t *__restrict__ seg_rank) {
 	const uint32_t seg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+	asm volatile("griddepcontrol.wait;" ::: "memory"); // see k_compact
 	if (seg >= n_seg)
 		return;
 	const uint32_t e = seg_start[seg];

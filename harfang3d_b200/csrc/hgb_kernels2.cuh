@@ -145,6 +145,8 @@ __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src) {
 
 __global__ void __launch_bounds__(kSampleWarps * 32, 6) k_sample_tracks(AnimDev a, uint32_t first, uint32_t n_tracks) {
 	__shared__ __align__(16) uint8_t s_win[kSampleWarps][32 * kWinStride];
+	// the first level kernel may become resident while the last wave of this grid drains (it waits before reading anim_val)
+	asm volatile("griddepcontrol.launch_dependents;");
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 	const uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
 	bool active = i < first + n_tracks;
