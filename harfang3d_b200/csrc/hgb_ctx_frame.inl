@@ -7,6 +7,7 @@ static SceneDev scene_dev(hgb_ctx *c, bool with_preset) {
 	s.anim_val = c->anim_val.as<float4>();
 	s.transpose_store = c->transpose_store ? 1 : 0;
 	s.lookahead = c->lookahead;
+	s.late_wait = c->pdl_late_wait ? 1 : 0;
 	s.world = c->world[c->cur].as<float>();
 	s.preset = with_preset ? c->preset.as<uint8_t>() : nullptr;
 	s.ent_off = c->ent_off.as<uint32_t>();
@@ -228,7 +229,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 			k_sample_tracks<<<grid_for(cnt, kSampleWarps * 32), kSampleWarps * 32, 0, c->stream>>>(a, first, cnt);
 			prof_end(c);
 			++*n_k;
-			prev_signals = true;
+			prev_signals = !c->pdl_late_wait; // with the late wait a level reads sampled values ahead of its wait: the first one is a plain launch
 		}
 	} else if (overlap) {
 		CK(cudaEventRecord(c->ev_chunk[0], c->stream)); // fork (also orders the chunks behind this frame's play-clock upload)

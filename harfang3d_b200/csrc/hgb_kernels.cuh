@@ -53,6 +53,7 @@ struct SceneDev {
 	const uint16_t *pos_view;   // per position: which instance frustum (only with inst_planes)
 	int transpose_store;        // 1: world rows leave the SM as 3 contiguous 512-byte warp stores (shared-memory transpose)
 	uint32_t lookahead;         // positions: a warp asks L2 for the tile (and its parents' rows) this far ahead of its own; 0 = off
+	int late_wait;              // 1: the programmatic-dependency wait sits after the local matrix is built (the first level is then a plain launch)
 };
 
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -125,10 +126,16 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 			const uint32_t par = t[kRowParent * 32];
 			// everything above reads edit-time data; from here on the previous level's world rows are read (no-op without a
 			// programmatic dependency)
-			asm volatile("griddepcontrol.wait;" ::: "memory");
+			if (!s.late_wait)
+				asm volatile("griddepcontrol.wait;" ::: "memory");
 			if (par != kRoot) { // start the parent row on its way while the trigonometry runs (no registers held)
-				prefetch_l1(s.world + size_t(par) * 12);
-				prefetch_l1(s.world + size_t(par) * 12 + 11);
+				if (s.late_wait) { // not into L1 ahead of the wait: the row may not have been written yet and L1 would keep the old line
+					prefetch_l2(s.world + size_t(par) * 12);
+					prefetch_l2(s.world + size_t(par) * 12 + 11);
+				} else {
+					prefetch_l1(s.world + size_t(par) * 12);
+					prefetch_l1(s.world + size_t(par) * 12 + 11);
+				}
 			}
 			if (meta & kLaneAnimatedMask) { // track-driven triples: fetch the value sampled this frame (or the last one sampled)
 				if (meta & kLaneAnimated) {
@@ -145,6 +152,8 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 				}
 			}
 			world = transformation_mat4(px, py, pz, ex, ey, ez, sx, sy, sz);
+			if (s.late_wait)
+				asm volatile("griddepcontrol.wait;" ::: "memory");
 			if (par != kRoot)
 				world = mat4_mul(load_mat4(s.world + size_t(par) * 12), world);
 		}
