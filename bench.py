@@ -247,8 +247,15 @@ def main():
         # the path's only exchange rides on the frame itself: k_compact stores the survivors into rank 0's inbox over
         # NVLink, flags and acknowledgements are device words, rank 0 concatenates — nothing of it touches the host (hgb_kernels_peer.cuh)
         aux = np.full(world, len(fs.instance_cameras), np.uint32) if fs.instance_cameras is not None else None
-        ctx.peer_setup(dist, ent_all, aux, dst=0)
-    elif world > 1:
+        try:
+            ctx.peer_setup(dist, ent_all, aux, dst=0)
+        except harfang3d_b200.capi.HgbError as e:  # raised on every rank or on none: the other device-side exchange takes over, and the line says so
+            peer = False
+            args.exchange = "nccl"
+            if rank == 0:
+                print("bench: %s -> --exchange nccl" % e, file=sys.stderr)
+            ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    if world > 1 and not peer:
         # A/B: visible counts all-gathered, visible lists gathered to rank 0 with grouped send/recv sized from the counts (one host read
         # per step). The tensors are views of the context's own device buffers (no staging copy).
         if fs.instance_cameras is not None:  # c5: per-instance offsets of the compacted list

@@ -59,6 +59,7 @@ SIGNATURES = {
     "hgb_sort_keys": (_i, [_p, _i, _u32, _p]),
     "hgb_peer_init": (_i, [_p, _u32, _u32, _u32, _p, _p, _p, _p]),
     "hgb_peer_connect": (_i, [_p, _p, _p]),
+    "hgb_peer_close": (_i, [_p]),
     "hgb_peer_status": (_i, [_p, _p, _p]),
     "hgb_peer_result": (_i, [_p, _p, _p, _u32, _p, _u32]),
     "hgb_set_enable_tracks": (_i, [_p, _u32, _p, _u32, _p, _p]),
@@ -272,13 +273,33 @@ class Context:
         dst = C.create_string_buffer(inbox_of_dst, 64)
         self._ck(self._L.hgb_peer_connect(self._h, C.addressof(dst), C.addressof(blob)))
 
+    def peer_close(self):
+        self._ck(self._L.hgb_peer_close(self._h))
+        self._peer = None
+
     def peer_setup(self, dist, entries_per_rank, aux_words_per_rank=None, dst=0, group=None):
-        """init + handle exchange over torch.distributed + connect (collective: every rank calls it)"""
+        """init + handle exchange over torch.distributed + connect. Collective: every rank calls it, and every rank leaves it the same
+        way — a failure on ANY rank (no IPC on the box, no peer access between two GPUs) closes the gather on all of them and raises
+        HgbError everywhere, so the callers can take the same decision (bench.py: the NCCL exchange instead)."""
         rank, world = dist.get_rank(group), dist.get_world_size(group)
-        inbox, mail = self.peer_init(rank, world, dst, entries_per_rank, aux_words_per_rank)
+        inbox = mail = err = None
+        try:
+            inbox, mail = self.peer_init(rank, world, dst, entries_per_rank, aux_words_per_rank)
+        except HgbError as e:
+            err = "rank %d, init: %s" % (rank, e)
         handles = [None] * world
-        dist.all_gather_object(handles, (inbox, mail), group=group)
-        self.peer_connect(handles[dst][0], [h[1] for h in handles])
+        dist.all_gather_object(handles, (inbox, mail, err), group=group)
+        if not any(h[2] for h in handles):
+            try:
+                self.peer_connect(handles[dst][0], [h[1] for h in handles])
+            except HgbError as e:
+                err = "rank %d, connect: %s" % (rank, e)
+        errs = [None] * world
+        dist.all_gather_object(errs, err or handles[rank][2], group=group)
+        failed = [e for e in errs if e] + [h[2] for h in handles if h[2]]
+        if failed:
+            self.peer_close()
+            raise HgbError("peer gather unavailable: " + failed[0])
         dist.barrier(group)
 
     def peer_status(self):

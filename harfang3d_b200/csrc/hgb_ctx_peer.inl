@@ -12,8 +12,10 @@ int hgb_peer_init(hgb_ctx *c, uint32_t rank, uint32_t world, uint32_t dst, const
 	if (world == 0 || world > uint32_t(kMaxPeers) || rank >= world || dst >= world)
 		return fail("hgb_peer_init: bad rank / world / dst (at most %d ranks)", kMaxPeers);
 	CK(cudaSetDevice(c->device));
+	CK(cudaStreamSynchronize(c->stream));
+	peer_release(c); // a second init replaces the first
+	invalidate_graph(c);
 	Peer &p = c->peer;
-	p = Peer{};
 	p.rank = rank, p.world = world, p.dst = dst;
 	// one inbox half: world header lines, then every rank's list region (capacity = its entry count) and aux region, 128-byte aligned
 	size_t w = size_t(world) * kPeerHdrWords;
@@ -85,6 +87,17 @@ int hgb_peer_connect(hgb_ctx *c, const hgb_peer_handle *inbox_of_dst, const hgb_
 		}
 	}
 	p.on = true;
+	invalidate_graph(c);
+	return 0;
+}
+
+int hgb_peer_close(hgb_ctx *c) {
+	if (!c)
+		return fail("null context");
+	join_post(c);
+	CK(cudaSetDevice(c->device));
+	CK(cudaStreamSynchronize(c->stream));
+	peer_release(c);
 	invalidate_graph(c);
 	return 0;
 }

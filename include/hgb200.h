@@ -182,6 +182,9 @@ typedef struct hgb_peer_handle {
 int hgb_peer_init(hgb_ctx *, uint32_t rank, uint32_t world, uint32_t dst, const uint32_t *entries_per_rank, const uint32_t *aux_words_per_rank /* nullable */,
 	hgb_peer_handle *inbox_out /* meaningful on dst */, hgb_peer_handle *mailbox_out);
 int hgb_peer_connect(hgb_ctx *, const hgb_peer_handle *inbox_of_dst, const hgb_peer_handle *mailboxes /* world handles, read on dst */);
+/* undo hgb_peer_init / hgb_peer_connect (also after a setup that failed on this or another rank): waits for the frames in flight, unmaps
+ * and frees the peer buffers; later frames run without the gather */
+int hgb_peer_close(hgb_ctx *);
 /* frames counted so far and the error word (0 = ok; 1 = a sender timed out waiting for an acknowledgement, 2 + r = the destination timed
  * out waiting for rank r) */
 int hgb_peer_status(hgb_ctx *, uint32_t *out_step, uint32_t *out_error);

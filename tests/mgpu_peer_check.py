@@ -97,6 +97,26 @@ def main():
         assert (off == np.concatenate([[0], np.cumsum(counts)])).all()
         assert (idx == want).all()
         print("peer gather (shared camera): %d ranks, %d visible entries: identical to the per-rank lists" % (world, len(idx)))
+
+    # ---- close, then a setup that fails on ONE rank: every rank must leave peer_setup with the same error and keep running frames ----
+    before = ctx.get_visible(0, 0).copy()
+    dist.barrier()
+    ctx.peer_close()
+    ctx.update(None, fused_cull=True)
+    assert (ctx.get_visible(0, 0) == before).all()
+    if rank == world - 1:
+        def broken(*a, **k):
+            raise harfang3d_b200.capi.HgbError("injected: no IPC on this rank")
+        ctx.peer_init = broken
+    try:
+        ctx.peer_setup(dist, ent, None, dst=0)
+        raise AssertionError("peer_setup succeeded with a broken rank")
+    except harfang3d_b200.capi.HgbError as e:
+        assert "injected" in str(e), e
+    ctx.update(None, fused_cull=True)
+    assert (ctx.get_visible(0, 0) == before).all()
+    if rank == 0:
+        print("peer close + one-rank setup failure: every rank fell back together, frames unchanged")
     ctx.close()
     dist.barrier()
     dist.destroy_process_group()
