@@ -51,6 +51,26 @@ struct Object {
 	ComponentRef ref;
 	bool IsValid() const;
 };
+struct CameraZRange { // node.h:71-73
+	float znear{0.01f}, zfar{1000.f};
+};
+struct Camera { // node.h:77-100: the view the culling frusta of a frame come from (Scene::ComputeCurrentCameraViewState)
+	Scene *scene{nullptr};
+	ComponentRef ref;
+	bool IsValid() const;
+	float GetZNear() const;
+	void SetZNear(float v);
+	float GetZFar() const;
+	void SetZFar(float v);
+	CameraZRange GetZRange() const;
+	void SetZRange(CameraZRange v);
+	float GetFov() const;
+	void SetFov(float v);
+	bool GetIsOrthographic() const;
+	void SetIsOrthographic(bool v);
+	float GetSize() const;
+	void SetSize(float v);
+};
 struct Node {
 	Scene *scene{nullptr};
 	NodeRef ref;
@@ -63,6 +83,8 @@ struct Node {
 	void SetTransform(const Transform &t);
 	Object GetObject() const;
 	void SetObject(const Object &o);
+	Camera GetCamera() const;
+	void SetCamera(const Camera &c);
 	Mat4 GetWorld() const;
 	void SetWorld(const Mat4 &m);
 	bool GetMinMax(const PipelineResources &resources, MinMax &minmax) const; // node.cpp:106-119 (object nodes; no instance views here)
@@ -152,6 +174,38 @@ public:
 	Mat4 GetTransformWorldMatrix(uint32_t transform_idx) const;         // component.cpp:250-256
 	Mat4 GetPreviousTransformWorldMatrix(uint32_t transform_idx) const; // component.cpp:258-264
 
+	// ---- cameras (scene.h:295-324,594-599): host-side component; its view state is built from the DEVICE-computed world matrix of
+	// the camera node with the reference's own projection / frustum arithmetic (scene.cpp:240-263, render_pipeline.cpp:67-81) ----
+	Camera CreateCamera();
+	Camera CreateCamera(float znear, float zfar, float fov = 0.78539816339f); // Deg(45)
+	Camera CreateOrthographicCamera(float znear, float zfar, float size = 1.f);
+	void DestroyCamera(ComponentRef ref);
+	void DestroyCamera(const Camera &c) { DestroyCamera(c.ref); }
+	bool IsValidCameraRef(ComponentRef ref) const { return cameras.is_valid(ref); }
+	float GetCameraZNear(ComponentRef ref) const;
+	void SetCameraZNear(ComponentRef ref, float v);
+	float GetCameraZFar(ComponentRef ref) const;
+	void SetCameraZFar(ComponentRef ref, float v);
+	CameraZRange GetCameraZRange(ComponentRef ref) const;
+	void SetCameraZRange(ComponentRef ref, CameraZRange v);
+	float GetCameraFov(ComponentRef ref) const;
+	void SetCameraFov(ComponentRef ref, float v);
+	float GetCameraSize(ComponentRef ref) const;
+	void SetCameraSize(ComponentRef ref, float v);
+	bool GetCameraIsOrthographic(ComponentRef ref) const;
+	void SetCameraIsOrthographic(ComponentRef ref, const bool &v);
+	void SetCameraCenterOffset(ComponentRef ref, const Vec2 &v);
+	Vec2 GetCameraCenterOffset(ComponentRef ref) const;
+	ComponentRef GetNodeCameraRef(NodeRef ref) const;
+	void SetNodeCamera(NodeRef ref, ComponentRef cref);
+	Camera GetNodeCamera(NodeRef ref) const { return {const_cast<Scene *>(this), GetNodeCameraRef(ref)}; }
+	void SetNodeCamera(NodeRef ref, const Camera &v) { SetNodeCamera(ref, v.ref); }
+	Node GetCurrentCamera() const { return {const_cast<Scene *>(this), current_camera}; }
+	void SetCurrentCamera(NodeRef ref) { current_camera = ref; }
+	void SetCurrentCamera(const Node &n) { current_camera = n.ref; }
+	ViewState ComputeCurrentCameraViewState(const Vec2 &aspect_ratio) const { return ComputeCameraViewState(current_camera, aspect_ratio); }
+	ViewState ComputeCameraViewState(NodeRef ref, const Vec2 &aspect_ratio) const;
+
 	// ---- objects (scene.h:327-358) ----
 	Object CreateObject();
 	Object CreateObject(const ModelRef &model, std::vector<Material> materials = {});
@@ -223,7 +277,14 @@ private:
 	struct Node_ { // scene.h:698-702
 		std::string name;
 		uint32_t flags{0};
-		ComponentRef transform, object;
+		ComponentRef transform, object, camera;
+	};
+	struct Camera_ { // scene.h:739-745
+		CameraZRange zrange;
+		float fov{0.69813170079f}; // Deg(40)
+		bool ortho{false};
+		float size{1.f};
+		Vec2 center_offset{0.f, 0.f};
 	};
 	struct Transform_ { // scene.h:734-737
 		TransformTRS TRS;
@@ -246,6 +307,8 @@ private:
 	generational_vector_list<Node_> nodes;
 	generational_vector_list<Transform_> transforms;
 	generational_vector_list<Object_> objects;
+	generational_vector_list<Camera_> cameras;
+	NodeRef current_camera;
 	generational_vector_list<Anim> anims;
 	generational_vector_list<SceneAnim> scene_anims;
 	generational_vector_list<ScenePlayAnim_> play_anims;

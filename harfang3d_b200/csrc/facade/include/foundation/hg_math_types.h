@@ -80,11 +80,21 @@ Mat4 InverseFast(const Mat4 &m);                                           // fo
 Mat4 TransformationMat4(const Vec3 &p, const Vec3 &e, const Vec3 &s = Vec3(1, 1, 1)); // matrix4.cpp:176-183, RO_YXZ
 Mat4 TranslationMat4(const Vec3 &p);
 float FovToZoomFactor(float fov);                                          // foundation/projection.cpp:19
-Mat44 ComputePerspectiveProjectionMatrix(float znear, float zfar, float zoom_factor, const Vec2 &aspect_ratio);  // projection.cpp:29-37
-Mat44 ComputeOrthographicProjectionMatrix(float znear, float zfar, float size, const Vec2 &aspect_ratio);       // projection.cpp:21-27
+Mat44 ComputePerspectiveProjectionMatrix(float znear, float zfar, float zoom_factor, const Vec2 &aspect_ratio, const Vec2 &offset = Vec2(),
+	const Vec2 &center_offset = Vec2());                                    // projection.cpp:29-37
+Mat44 ComputeOrthographicProjectionMatrix(float znear, float zfar, float size, const Vec2 &aspect_ratio, const Vec2 &offset = Vec2()); // projection.cpp:21-27
 Frustum MakeFrustum(const Mat44 &projection);                              // foundation/frustum.cpp:17-23
 Frustum MakeFrustum(const Mat44 &projection, const Mat4 &world);           // frustum.cpp:25
 Frustum TransformFrustum(const Frustum &frustum, const Mat4 &mtx);         // frustum.cpp:27-28
 void SetNDCInfos(bool origin_bottom_left, bool homogeneous_depth);         // projection.cpp:9-16 (default false,false)
+
+struct ViewState { // engine/render_pipeline.h:55-59
+	Frustum frustum;
+	Mat44 proj;
+	Mat4 view;
+};
+ViewState ComputeOrthographicViewState(const Mat4 &world, float size, float znear, float zfar, const Vec2 &aspect_ratio, const Vec2 &offset = Vec2()); // render_pipeline.cpp:67-73
+ViewState ComputePerspectiveViewState(const Mat4 &world, float fov, float znear, float zfar, const Vec2 &aspect_ratio, const Vec2 &offset = Vec2(),
+	const Vec2 &center_offset = Vec2()); // render_pipeline.cpp:75-81
 
 } // namespace hg

@@ -81,10 +81,10 @@ void SetNDCInfos(bool origin_bottom_left, bool homogeneous_depth) { g_ndc_origin
 float FovToZoomFactor(float fov) {
 	const float lo = 0.1f / 180.f * 3.1415926535f, hi = 179.9f / 180.f * 3.1415926535f;
 	const float cf = fov < lo ? lo : (fov > hi ? hi : fov);
-	return 1.f / tanf(cf * 0.5f);
+	return 1.f / float(tan(double(cf * 0.5f))); // math.cpp:93-95: Tan() is the DOUBLE tan, rounded
 }
 
-Mat44 ComputePerspectiveProjectionMatrix(float znear, float zfar, float zoom, const Vec2 &ar) {
+Mat44 ComputePerspectiveProjectionMatrix(float znear, float zfar, float zoom, const Vec2 &ar, const Vec2 &offset, const Vec2 &center_offset) {
 	const float qA = g_ndc_homogeneous_depth ? ((zfar + znear) / (zfar - znear)) : (zfar / (zfar - znear));
 	const float qB = g_ndc_homogeneous_depth ? (-2 * zfar * znear / (zfar - znear)) : (-qA * znear);
 	Mat44 o{};
@@ -92,10 +92,12 @@ Mat44 ComputePerspectiveProjectionMatrix(float znear, float zfar, float zoom, co
 	o.m[1][1] = zoom / ar.y;
 	o.m[2][2] = qA, o.m[2][3] = qB;
 	o.m[3][2] = 1.f;
+	o.m[0][2] = center_offset.x, o.m[1][2] = center_offset.y; // third column
+	o.m[0][3] = offset.x, o.m[1][3] = offset.y;               // fourth column
 	return o;
 }
 
-Mat44 ComputeOrthographicProjectionMatrix(float znear, float zfar, float size, const Vec2 &ar) {
+Mat44 ComputeOrthographicProjectionMatrix(float znear, float zfar, float size, const Vec2 &ar, const Vec2 &offset) {
 	const float qA = g_ndc_homogeneous_depth ? (2.f / (zfar - znear)) : (1.f / (zfar - znear));
 	const float qB = g_ndc_homogeneous_depth ? (-(zfar + znear) / (zfar - znear)) : (-qA * znear);
 	Mat44 o{};
@@ -103,6 +105,7 @@ Mat44 ComputeOrthographicProjectionMatrix(float znear, float zfar, float size, c
 	o.m[1][1] = 2.f / size / ar.y;
 	o.m[2][2] = qA, o.m[2][3] = qB;
 	o.m[3][3] = 1.f;
+	o.m[0][3] = offset.x, o.m[1][3] = offset.y;
 	return o;
 }
 
@@ -139,5 +142,22 @@ Frustum TransformFrustum(const Frustum &frustum, const Mat4 &m) { // plane' = tr
 }
 
 Frustum MakeFrustum(const Mat44 &projection, const Mat4 &world) { return TransformFrustum(MakeFrustum(projection), world); }
+
+// ---- view states (render_pipeline.cpp:67-81): frustum, projection and view matrix of a camera world matrix ----
+ViewState ComputeOrthographicViewState(const Mat4 &world, float size, float znear, float zfar, const Vec2 &aspect_ratio, const Vec2 &offset) {
+	ViewState vs;
+	vs.view = InverseFast(world);
+	vs.proj = ComputeOrthographicProjectionMatrix(znear, zfar, size, aspect_ratio, offset);
+	vs.frustum = MakeFrustum(vs.proj, world);
+	return vs;
+}
+
+ViewState ComputePerspectiveViewState(const Mat4 &world, float fov, float znear, float zfar, const Vec2 &aspect_ratio, const Vec2 &offset, const Vec2 &center_offset) {
+	ViewState vs;
+	vs.view = InverseFast(world);
+	vs.proj = ComputePerspectiveProjectionMatrix(znear, zfar, FovToZoomFactor(fov), aspect_ratio, offset, center_offset);
+	vs.frustum = MakeFrustum(vs.proj, world);
+	return vs;
+}
 
 } // namespace hg

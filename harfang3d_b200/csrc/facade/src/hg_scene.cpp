@@ -101,6 +101,8 @@ void Node::Disable() { if (scene) scene->DisableNode(ref); }
 bool Node::IsEnabled() const { return scene && scene->IsNodeEnabled(ref); }
 Transform Node::GetTransform() const { return scene ? Transform{scene, scene->GetNodeTransformRef(ref)} : Transform{}; }
 void Node::SetTransform(const Transform &t) { if (scene) scene->SetNodeTransform(ref, t.ref); }
+Camera Node::GetCamera() const { return scene ? Camera{scene, scene->GetNodeCameraRef(ref)} : Camera{}; }
+void Node::SetCamera(const Camera &c) { if (scene) scene->SetNodeCamera(ref, c.ref); }
 Object Node::GetObject() const { return scene ? Object{scene, scene->GetNodeObjectRef(ref)} : Object{}; }
 void Node::SetObject(const Object &o) { if (scene) scene->SetNodeObject(ref, o.ref); }
 Mat4 Node::GetWorld() const { return scene ? scene->GetNodeWorldMatrix(ref) : Mat4::Identity; }
@@ -448,6 +450,13 @@ void Scene::SetTransformWorldMatrix(ComponentRef ref, const Mat4 &world) {
 }
 
 Mat4 Scene::GetTransformWorldMatrix(const uint32_t transform_idx) const {
+	FlushMatrixSets();
+	if (!worlds_valid && ctx && !impl->topology_dirty && transform_idx < transforms.capacity()) { // one 48-byte row, not the whole mirror
+		Mat4 row;
+		if (hgb_get_worlds(ctx, transform_idx, 1, &row.m[0][0], 0) == 0)
+			return row;
+		warn(hgb_last_error());
+	}
 	const std::vector<Mat4> &w = GetTransformWorldMatrices();
 	if (transform_idx < w.size())
 		return w[transform_idx];
@@ -464,6 +473,101 @@ Mat4 Scene::GetPreviousTransformWorldMatrix(const uint32_t transform_idx) const 
 }
 
 // ---- objects -----------------------------------------------------------------------------------------------------------------
+// ---- cameras (component.cpp:306-499, scene.cpp:240-263) -------------------------------------------------------------------------------
+bool Camera::IsValid() const { return scene && scene->IsValidCameraRef(ref); }
+float Camera::GetZNear() const { return scene ? scene->GetCameraZNear(ref) : 0.01f; }
+void Camera::SetZNear(float v) { if (scene) scene->SetCameraZNear(ref, v); }
+float Camera::GetZFar() const { return scene ? scene->GetCameraZFar(ref) : 1000.f; }
+void Camera::SetZFar(float v) { if (scene) scene->SetCameraZFar(ref, v); }
+CameraZRange Camera::GetZRange() const { return scene ? scene->GetCameraZRange(ref) : CameraZRange{}; }
+void Camera::SetZRange(CameraZRange v) { if (scene) scene->SetCameraZRange(ref, v); }
+float Camera::GetFov() const { return scene ? scene->GetCameraFov(ref) : 40.f / 180.f * 3.1415926535f; }
+void Camera::SetFov(float v) { if (scene) scene->SetCameraFov(ref, v); }
+bool Camera::GetIsOrthographic() const { return scene && scene->GetCameraIsOrthographic(ref); }
+void Camera::SetIsOrthographic(bool v) { if (scene) scene->SetCameraIsOrthographic(ref, v); }
+float Camera::GetSize() const { return scene ? scene->GetCameraSize(ref) : 1.f; }
+void Camera::SetSize(float v) { if (scene) scene->SetCameraSize(ref, v); }
+
+Camera Scene::CreateCamera() { return {this, cameras.add_ref(Camera_{})}; }
+Camera Scene::CreateCamera(float znear, float zfar, float fov) {
+	Camera_ c;
+	c.zrange = {znear, zfar};
+	c.fov = fov;
+	return {this, cameras.add_ref(c)};
+}
+Camera Scene::CreateOrthographicCamera(float znear, float zfar, float size) {
+	Camera_ c;
+	c.zrange = {znear, zfar};
+	c.ortho = true;
+	c.size = size;
+	return {this, cameras.add_ref(c)};
+}
+void Scene::DestroyCamera(ComponentRef ref) { cameras.remove_ref(ref); }
+
+#define HG_CAM_GET(EXPR, NEUTRAL)                                                                                                                             \
+	if (cameras.is_valid(ref))                                                                                                                                 \
+		return cameras[ref.idx].EXPR;                                                                                                                          \
+	warn("Invalid camera component");                                                                                                                          \
+	return NEUTRAL;
+#define HG_CAM_SET(EXPR)                                                                                                                                      \
+	if (cameras.is_valid(ref))                                                                                                                                 \
+		cameras[ref.idx].EXPR = v;                                                                                                                             \
+	else                                                                                                                                                       \
+		warn("Invalid camera component");
+float Scene::GetCameraZNear(ComponentRef ref) const { HG_CAM_GET(zrange.znear, 0.01f) }
+void Scene::SetCameraZNear(ComponentRef ref, float v) { HG_CAM_SET(zrange.znear) }
+float Scene::GetCameraZFar(ComponentRef ref) const { HG_CAM_GET(zrange.zfar, 1000.f) }
+void Scene::SetCameraZFar(ComponentRef ref, float v) { HG_CAM_SET(zrange.zfar) }
+CameraZRange Scene::GetCameraZRange(ComponentRef ref) const { HG_CAM_GET(zrange, CameraZRange{}) }
+void Scene::SetCameraZRange(ComponentRef ref, CameraZRange v) { HG_CAM_SET(zrange) }
+float Scene::GetCameraFov(ComponentRef ref) const { HG_CAM_GET(fov, 40.f / 180.f * 3.1415926535f) }
+void Scene::SetCameraFov(ComponentRef ref, float v) { HG_CAM_SET(fov) }
+float Scene::GetCameraSize(ComponentRef ref) const { HG_CAM_GET(size, 1.f) }
+void Scene::SetCameraSize(ComponentRef ref, float v) { HG_CAM_SET(size) }
+bool Scene::GetCameraIsOrthographic(ComponentRef ref) const { HG_CAM_GET(ortho, false) }
+void Scene::SetCameraIsOrthographic(ComponentRef ref, const bool &v) { HG_CAM_SET(ortho) }
+Vec2 Scene::GetCameraCenterOffset(ComponentRef ref) const { HG_CAM_GET(center_offset, Vec2()) }
+void Scene::SetCameraCenterOffset(ComponentRef ref, const Vec2 &v) { HG_CAM_SET(center_offset) }
+#undef HG_CAM_GET
+#undef HG_CAM_SET
+
+ComponentRef Scene::GetNodeCameraRef(NodeRef ref) const {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node");
+		return InvalidComponentRef;
+	}
+	return nodes[ref.idx].camera;
+}
+void Scene::SetNodeCamera(NodeRef ref, ComponentRef cref) {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node");
+		return;
+	}
+	nodes[ref.idx].camera = cref;
+}
+
+// scene.cpp:240-261: the camera node's world matrix is the one the device computed this frame (one 48-byte row comes back through the
+// lazily refreshed host mirror); projection and planes are built on the host with the reference's operation order (hg_math.cpp)
+ViewState Scene::ComputeCameraViewState(NodeRef ref, const Vec2 &aspect_ratio) const {
+	if (!nodes.is_valid(ref)) {
+		warn("Invalid node");
+		return {};
+	}
+	const Node_ &n = nodes[ref.idx];
+	if (!transforms.is_valid(n.transform)) {
+		warn("Invalid node transform");
+		return {};
+	}
+	if (!cameras.is_valid(n.camera)) {
+		warn("Invalid node camera");
+		return {};
+	}
+	const Camera_ &cam = cameras[n.camera.idx];
+	const Mat4 world = GetTransformWorldMatrix(n.transform.idx);
+	return cam.ortho ? ComputeOrthographicViewState(world, cam.size, cam.zrange.znear, cam.zrange.zfar, aspect_ratio)
+					 : ComputePerspectiveViewState(world, cam.fov, cam.zrange.znear, cam.zrange.zfar, aspect_ratio, Vec2(), cam.center_offset);
+}
+
 Object Scene::CreateObject() { return {this, objects.add_ref(Object_{})}; }
 
 Object Scene::CreateObject(const ModelRef &model, std::vector<Material> materials) {
@@ -1190,6 +1294,18 @@ size_t Scene::GarbageCollect() {
 			objects.remove_ref(objects.get_ref(i));
 			++removed;
 			impl->entries_dirty = true;
+		}
+		i = nx;
+	}
+	std::vector<uint8_t> cam_used(cameras.capacity(), 0); // scene.cpp:92-237 runs the same pass over every component list
+	for (uint32_t ni = nodes.first(); ni != nodes.invalid_idx; ni = nodes.next(ni))
+		if (cameras.is_valid(nodes[ni].camera))
+			cam_used[nodes[ni].camera.idx] = 1;
+	for (uint32_t i = cameras.first(); i != cameras.invalid_idx;) {
+		const uint32_t nx = cameras.next(i);
+		if (!cam_used[i]) {
+			cameras.remove_ref(cameras.get_ref(i));
+			++removed;
 		}
 		i = nx;
 	}

@@ -399,6 +399,31 @@ void hgref_make_ortho_frustum(float znear, float zfar, float size, float ar_x, f
 	memcpy(out24, f.data(), 96);
 }
 
+// ---- camera component + view state (scene.h:295-324,594-599; scene.cpp:240-263; render_pipeline.cpp:67-81) ----
+// kind 0: perspective (p = fov), 1: orthographic (p = size)
+int hgref_set_node_camera(void *h, int node, int kind, float znear, float zfar, float p) {
+	auto *c = static_cast<RefCtx *>(h);
+	Camera cam = kind == 1 ? c->scene->CreateOrthographicCamera(znear, zfar, p) : c->scene->CreateCamera(znear, zfar, p);
+	c->scene->SetNodeCamera(c->nodes[node], cam.ref);
+	return cam.IsValid() ? 1 : 0;
+}
+void hgref_set_camera_fov(void *h, int node, float fov) {
+	auto *c = static_cast<RefCtx *>(h);
+	c->scene->SetCameraFov(c->scene->GetNodeCameraRef(c->nodes[node]), fov);
+}
+float hgref_get_camera_fov(void *h, int node) {
+	auto *c = static_cast<RefCtx *>(h);
+	return c->scene->GetCameraFov(c->scene->GetNodeCameraRef(c->nodes[node]));
+}
+void hgref_set_current_camera(void *h, int node) { static_cast<RefCtx *>(h)->scene->SetCurrentCamera(static_cast<RefCtx *>(h)->nodes[node]); }
+// out: 24 frustum plane floats, 16 projection floats (m[row][col]), 12 view floats
+void hgref_current_camera_view_state(void *h, float ar_x, float ar_y, float *out52) {
+	const ViewState vs = static_cast<RefCtx *>(h)->scene->ComputeCurrentCameraViewState(Vec2(ar_x, ar_y));
+	memcpy(out52, vs.frustum.data(), 96);
+	memcpy(out52 + 24, vs.proj.m, 64);
+	memcpy(out52 + 40, vs.view.m, 48);
+}
+
 // ---- math probes: let tests pin the port / GPU path against the reference's own functions and golden vectors ----
 void hgref_transformation_mat4(const float *trs9, float *out12) {
 	const Mat4 m = TransformationMat4(Vec3(trs9[0], trs9[1], trs9[2]), Vec3(trs9[3], trs9[4], trs9[5]), Vec3(trs9[6], trs9[7], trs9[8]));

@@ -92,6 +92,11 @@ def _bind_scene_driver(L, with_probes):
     _sig(L, "hgref_read_skinned_lists", c_i, [c_p, c_i, c_p, c_p, c_p, c_p, c_p])
     _sig(L, "hgref_cull", c_i, [c_p, c_i, c_p, c_p, c_p])
     _sig(L, "hgref_bone_matrices", c_i, [c_p, c_i, c_i, c_p])
+    _sig(L, "hgref_set_node_camera", c_i, [c_p, c_i, c_i, c_f, c_f, c_f])
+    _sig(L, "hgref_set_camera_fov", None, [c_p, c_i, c_f])
+    _sig(L, "hgref_get_camera_fov", c_f, [c_p, c_i])
+    _sig(L, "hgref_set_current_camera", None, [c_p, c_i])
+    _sig(L, "hgref_current_camera_view_state", None, [c_p, c_f, c_f, c_p])
     _sig(L, "hgref_make_perspective_frustum", None, [c_f] * 5 + [c_p, c_p])
     _sig(L, "hgref_make_ortho_frustum", None, [c_f] * 5 + [c_p, c_p])
     for n in ("hgref_transformation_mat4", "hgref_inverse_fast"):

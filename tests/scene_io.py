@@ -100,6 +100,19 @@ class RefScene:
         """Scene::SetTransformWorldMatrix / SetTransformLocalMatrix"""
         self.L.hgref_set_transform_matrix(self.h, int(node), P(np.ascontiguousarray(m12, np.float32).reshape(12)), 1 if local else 0)
 
+    def set_camera(self, node, znear, zfar, fov=None, size=None, current=True):
+        """Scene::CreateCamera / CreateOrthographicCamera + SetNodeCamera (+ SetCurrentCamera)"""
+        ok = self.L.hgref_set_node_camera(self.h, int(node), 1 if size is not None else 0, float(znear), float(zfar), float(size if size is not None else fov))
+        if current:
+            self.L.hgref_set_current_camera(self.h, int(node))
+        return bool(ok)
+
+    def view_state(self, ar_x, ar_y):
+        """Scene::ComputeCurrentCameraViewState -> (frustum[6,4], proj[4,4], view[3,4])"""
+        out = np.zeros(52, np.float32)
+        self.L.hgref_current_camera_view_state(self.h, float(ar_x), float(ar_y), P(out))
+        return out[:24].reshape(6, 4).copy(), out[24:40].reshape(4, 4).copy(), out[40:].reshape(3, 4).copy()
+
     def minmax(self, first=0, count=-1):
         """Scene::GetMinMax (count < 0) or GetNodesMinMax over nodes [first, first+count) -> (ok, minmax6)"""
         out = np.zeros(6, np.float32)

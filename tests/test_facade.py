@@ -371,3 +371,39 @@ def test_facade_enable_tracks_match_reference(fac, ref):
         a.update(scenegen.FRAME_DT); b.update(scenegen.FRAME_DT)
         same(frame)
     a.close(); b.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.ref
+def test_facade_camera_view_state_matches_reference(fac, ref):
+    """Camera component + Scene::ComputeCurrentCameraViewState (scene.cpp:240-263, render_pipeline.cpp:67-81): frustum planes, projection and
+    view matrix bit-identical to the reference for a camera deep in the hierarchy (its world matrix comes from the device), perspective and
+    orthographic, and the culls with those frusta keep the same lists; an invalid current camera yields the neutral view state on both."""
+    fs = scenegen.static_scene(6_000, 5, 6, n_models=3, seed=123)
+    a, b = RefScene(ref, fs), RefScene(fac, fs)
+    za, zb = a.view_state(16, 9), b.view_state(16, 9)  # no current camera: warn + {}
+    for x, y in zip(za, zb):
+        assert (bits(x) == bits(y)).all()
+    depth = np.zeros(fs.n, np.int32)
+    for i in range(fs.n):
+        depth[i] = 0 if fs.parent[i] < 0 else depth[fs.parent[i]] + 1
+    deep = np.nonzero(depth == depth.max())[0]
+    cams = [(int(deep[0]), dict(fov=1.1)), (int(deep[-1]), dict(size=35.0)), (0, dict(fov=0.0005)), (int(deep[3]), dict(fov=3.5))]  # fov clamps: Deg(0.1), Deg(179.9)
+    a.update(0); b.update(0)
+    for frame in range(2):
+        for node, kw in cams:
+            for s in (a, b):
+                assert s.set_camera(node, 0.1, 400.0, **kw)
+            (fa, pa, va), (fb, pb, vb) = a.view_state(16, 9), b.view_state(16, 9)
+            assert (bits(pa) == bits(pb)).all(), (node, kw)
+            assert (bits(va) == bits(vb)).all(), (node, kw)
+            assert (bits(fa) == bits(fb)).all(), (node, kw)
+            for kind in (0, 1):
+                (qa, ma), (qb, mb) = a.cull(kind, fa), b.cull(kind, fb)
+                assert (qa == qb).all() and (ma == mb).all()
+        t = np.ascontiguousarray(fs.trs[cams[0][0]] + np.float32(0.25), np.float32)  # move the first camera, next frame
+        for s in (a, b):
+            s.L.hgref_set_trs(s.h, cams[0][0], P(t))
+            s.update(scenegen.FRAME_DT)
+    assert a.L.hgref_garbage_collect(a.h) == b.L.hgref_garbage_collect(b.h)  # replaced camera components are collected alike
+    a.close(); b.close()

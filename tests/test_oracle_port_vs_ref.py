@@ -169,3 +169,34 @@ def test_world_matrices_and_cull_scene(port, ref):
     assert ref.hgref_minmax(h, 100, 50, P(mm_ref)) == 1  # GetNodesMinMax over a node range
     assert (np.concatenate([boxes[100:150, :3].min(0), boxes[100:150, 3:].max(0)]) == mm_ref).all()
     ref.hgref_destroy(h)
+
+
+def test_reference_camera_view_state(port, ref):
+    """The reference's own Scene::ComputeCurrentCameraViewState (scene.cpp:240-263; Compute*ViewState render_pipeline.cpp:67-81, which only
+    fetch bgfx::getCaps() and never read it) equals, bit for bit, the frustum the port, the host mirror and the flat probe build from the same
+    camera world matrix: the camera-driven frusta of the GPU tests are the reference's."""
+    from harfang3d_b200 import hostmirror, scenegen
+    from tests.scene_io import RefScene
+    fs = scenegen.static_scene(800, 4, 5, n_models=2, seed=321)
+    a = RefScene(ref, fs)
+    a.update(0)
+    for node, fov in ((777, 0.9), (5, 2.4), (300, 0.001)):
+        assert a.set_camera(node, 0.2, 350.0, fov=fov)
+        fr, proj, view = a.view_state(16, 9)
+        w = np.ascontiguousarray(a.worlds()[ref.hgref_node_transform_idx(a.h, node)])
+        probe, inv = np.zeros(24, np.float32), np.zeros(12, np.float32)
+        ref.hgref_make_perspective_frustum(0.2, 350.0, fov, 16, 9, P(w), P(probe))
+        ref.hgref_inverse_fast(P(w), P(inv))
+        assert (bits(probe) == bits(fr.reshape(-1))).all() and (bits(inv) == bits(view.reshape(-1))).all()
+        fp = np.zeros(24, np.float32)
+        port.hgp_make_perspective_frustum(0.2, 350.0, fov, 16, 9, P(w), P(fp))
+        assert (bits(fp) == bits(probe)).all()
+        assert (bits(hostmirror.make_perspective_frustum(0.2, 350.0, fov, 16, 9, w).reshape(-1)) == bits(probe)).all()
+        assert proj[3, 2] == 1 and proj[3, 3] == 0 and proj[0, 0] * 16 == pytest.approx(proj[1, 1] * 9, rel=1e-6)
+    assert a.set_camera(9, 0.5, 90.0, size=12.0)
+    fr, proj, _ = a.view_state(4, 3)
+    w = np.ascontiguousarray(a.worlds()[ref.hgref_node_transform_idx(a.h, 9)])
+    probe = np.zeros(24, np.float32)
+    ref.hgref_make_ortho_frustum(0.5, 90.0, 12.0, 4, 3, P(w), P(probe))
+    assert (bits(probe) == bits(fr.reshape(-1))).all() and proj[3, 3] == 1
+    a.close()
