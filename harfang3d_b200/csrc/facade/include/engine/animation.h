@@ -33,6 +33,7 @@ static const uint8_t AF_UseQuaternionForRotation = 0x01;
 
 struct Anim {
 	std::vector<AnimTrackT<bool>> bool_tracks;           // "Enable" (not on the metric path)
+	std::vector<AnimTrackHermiteT<float>> float_tracks;   // "Camera.Fov": one value per camera, evaluated on the host (EvaluateHermite, animation.h:155-169)
 	std::vector<AnimTrackHermiteT<Vec3>> vec3_tracks;     // "Position", "Rotation" (Euler), "Scale"
 	std::vector<AnimTrackT<Quaternion>> quat_tracks;     // "Rotation" when AF_UseQuaternionForRotation
 	time_ns t_start{0}, t_end{0};

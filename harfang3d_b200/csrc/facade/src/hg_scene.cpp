@@ -30,6 +30,13 @@ struct Scene::Impl {
 	bool trs_all_dirty{true};
 	std::vector<uint32_t> dirty_trs;
 	bool anims_dirty{true};
+	struct CamTrack { // a playing "Camera.Fov" float track: evaluated on the host every frame (one float per camera)
+		uint32_t play_idx;
+		ComponentRef cam;
+		AnimRef anim;
+		int track;
+	};
+	std::vector<CamTrack> cam_tracks; // in evaluation order (plays, then node anims), rebuilt with the bindings
 	bool entries_dirty{true};
 	bool views_dirty{false};
 	bool in_frame{false}; // between ReadyWorldMatrices and ComputeWorldMatrices: SetNodeWorldMatrix records presets
@@ -544,23 +551,27 @@ void Scene::SetNodeCamera(NodeRef ref, ComponentRef cref) {
 		return;
 	}
 	nodes[ref.idx].camera = cref;
+	impl->anims_dirty = true; // a playing "Camera.Fov" track may now have (or have lost) its target
 }
 
 // scene.cpp:240-261: the camera node's world matrix is the one the device computed this frame (one 48-byte row comes back through the
 // lazily refreshed host mirror); projection and planes are built on the host with the reference's operation order (hg_math.cpp)
 ViewState Scene::ComputeCameraViewState(NodeRef ref, const Vec2 &aspect_ratio) const {
+	ViewState neutral{}; // the reference returns a value-initialised ViewState: every float zero (its Mat4 has no default initialiser)
+	neutral.view = Mat4::Zero;
+	neutral.frustum.fill(Vec4(0, 0, 0, 0));
 	if (!nodes.is_valid(ref)) {
 		warn("Invalid node");
-		return {};
+		return neutral;
 	}
 	const Node_ &n = nodes[ref.idx];
 	if (!transforms.is_valid(n.transform)) {
 		warn("Invalid node transform");
-		return {};
+		return neutral;
 	}
 	if (!cameras.is_valid(n.camera)) {
 		warn("Invalid node camera");
-		return {};
+		return neutral;
 	}
 	const Camera_ &cam = cameras[n.camera.idx];
 	const Mat4 world = GetTransformWorldMatrix(n.transform.idx);
@@ -699,6 +710,33 @@ void Scene::StopAllAnims() {
 
 // Clock half of UpdatePlayingAnims (scene.cpp:2380-2431): exact int64 arithmetic on the host, O(#playing anims). The evaluation half
 // (EvaluateBoundAnim -> Evaluate*) is the device's k_sample_tracks, fed with the times computed here.
+// EvaluateHermite for a float track (animation.h:155-169 with GetIntervalKeys :109-128 and HermiteInterpolate, foundation/math.h:137-149):
+// same interval rule (first key later than t), same operation order, time ratio through float(double(ns) / 1e9) like time_to_sec_f
+static bool evaluate_hermite(const AnimTrackHermiteT<float> &track, time_ns t, float &v) {
+	const int n = int(track.keys.size());
+	if (n == 0)
+		return false;
+	int i = 0;
+	while (i < n && !(track.keys[i].t > t))
+		++i;
+	if (i == 0 || i == n) {
+		v = track.keys[i == 0 ? 0 : n - 1].v;
+		return true;
+	}
+	const int k1 = i - 1, k2 = i, k0 = k1 > 0 ? k1 - 1 : 0, k3 = k2 + 1 < n ? k2 + 1 : n - 1;
+	const float u = float(double(t - track.keys[k1].t) / 1000000000.0) / float(double(track.keys[k2].t - track.keys[k1].t) / 1000000000.0);
+	const float y0 = track.keys[k0].v, y1 = track.keys[k1].v, y2 = track.keys[k2].v, y3 = track.keys[k3].v;
+	const float tension = track.keys[k1].tension, bias = track.keys[k1].bias;
+	const float u2 = u * u, u3 = u2 * u;
+	float m0 = (y1 - y0) * (1.f + bias) * (1.f - tension) / 2.f;
+	m0 += (y2 - y1) * (1.f - bias) * (1.f - tension) / 2.f;
+	float m1 = (y2 - y1) * (1.f + bias) * (1.f - tension) / 2.f;
+	m1 += (y3 - y2) * (1.f - bias) * (1.f - tension) / 2.f;
+	const float a0 = 2.f * u3 - 3.f * u2 + 1.f, a1 = u3 - 2.f * u2 + u, a2 = u3 - u2, a3 = -2.f * u3 + 3.f * u2;
+	v = y1 * a0 + m0 * a1 + m1 * a2 + y2 * a3;
+	return true;
+}
+
 void Scene::UpdatePlayingAnims(time_ns dt) {
 	if (impl->anims_dirty)
 		SyncEdits(impl->resources); // (re)binds tracks and assigns play slots
@@ -726,6 +764,9 @@ void Scene::UpdatePlayingAnims(time_ns dt) {
 		if (p.play_slot < impl->play_t.size())
 			impl->play_t[p.play_slot] = p.t;
 	}
+	for (const Impl::CamTrack &ct : impl->cam_tracks) // finished plays are evaluated one last time, like every other target
+		if (play_anims.is_used(ct.play_idx) && cameras.is_valid(ct.cam) && anims.is_valid(ct.anim) && size_t(ct.track) < anims[ct.anim.idx].float_tracks.size())
+			evaluate_hermite(anims[ct.anim.idx].float_tracks[ct.track], play_anims[ct.play_idx].t, cameras[ct.cam.idx].fov);
 	for (uint32_t i : finished)
 		play_anims.remove(i);
 	if (!finished.empty())
@@ -813,6 +854,7 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 		std::vector<int64_t> en_t;
 		std::vector<uint8_t> en_v;
 		impl->enable_nodes.clear();
+		impl->cam_tracks.clear();
 		uint32_t n_play = 0;
 		for (uint32_t pi = play_anims.first(); pi != play_anims.invalid_idx; pi = play_anims.next(pi)) {
 			ScenePlayAnim_ &p = play_anims[pi];
@@ -826,10 +868,18 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 			for (const NodeAnim &na : scene_anims[p.scene_anim.idx].node_anims) {
 				if (!anims.is_valid(na.anim) || !nodes.is_valid(na.node))
 					continue;
+				const Anim &anim = anims[na.anim.idx];
+				if (cameras.is_valid(nodes[na.node.idx].camera)) { // the last "Camera.Fov" float track (BindNodeAnim scene.cpp:2091-2101)
+					int fov = -1;
+					for (size_t i = 0; i < anim.float_tracks.size(); ++i)
+						if (anim.float_tracks[i].target == "Camera.Fov")
+							fov = int(i);
+					if (fov >= 0)
+						impl->cam_tracks.push_back({pi, nodes[na.node.idx].camera, na.anim, fov});
+				}
 				const ComponentRef t = nodes[na.node.idx].transform;
 				if (!transforms.is_valid(t))
 					continue;
-				const Anim &anim = anims[na.anim.idx];
 				int en = -1; // "Enable" bool track: the last one with that target (BindNodeAnim scene.cpp:2083-2089)
 				for (size_t i = 0; i < anim.bool_tracks.size(); ++i)
 					if (anim.bool_tracks[i].target == "Enable")

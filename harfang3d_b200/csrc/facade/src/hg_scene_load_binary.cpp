@@ -142,7 +142,25 @@ void read_anim(Cursor &c, Anim &anim) { // LoadAnimFromBinary, anim_load_binary.
 		}
 	}
 	skip_tracks(c, 8 + 4);         // int
-	skip_tracks(c, 8 + 4 + 8);     // float, Hermite
+	{                              // float, Hermite: "Camera.Fov" (the light intensities have no component here)
+		const uint32_t n = c.get<uint32_t>();
+		anim.float_tracks.resize(c.ok ? n : 0);
+		for (auto &t : anim.float_tracks) {
+			t.target = c.str();
+			const uint32_t k = c.get<uint32_t>();
+			if (!c.ok || size_t(c.end - c.p) < size_t(k) * 20) {
+				c.ok = false;
+				return;
+			}
+			t.keys.resize(k);
+			for (auto &key : t.keys) {
+				key.t = c.get<int64_t>();
+				key.v = c.get<float>();
+				key.tension = c.get<float>(), key.bias = c.get<float>();
+			}
+			sort_keys(t);
+		}
+	}
 	skip_tracks(c, 8 + 8 + 8);     // vec2, Hermite
 	{                              // vec3, Hermite: "Position", "Rotation", "Scale"
 		const uint32_t n = c.get<uint32_t>();
@@ -239,7 +257,17 @@ bool Scene::Load_binary(const void *data, size_t size, const char *name, Pipelin
 		transform_refs[i] = transforms.add_ref(t);
 	}
 	const uint32_t camera_count = c.get<uint32_t>();
-	c.skip(size_t(camera_count) * 17); // zrange 8, fov 4, ortho 1, size 4
+	if (!c.ok || size_t(c.end - c.p) < size_t(camera_count) * 17)
+		return refuse("truncated camera table");
+	std::vector<ComponentRef> camera_refs(camera_count);
+	for (uint32_t i = 0; i < camera_count; ++i) { // zrange 8, fov 4, ortho 1, size 4 (scene_load_binary.cpp: SaveComponent(Camera_))
+		Camera_ cam;
+		cam.zrange.znear = c.get<float>(), cam.zrange.zfar = c.get<float>();
+		cam.fov = c.get<float>();
+		cam.ortho = c.get<uint8_t>() != 0;
+		cam.size = c.get<float>();
+		camera_refs[i] = cameras.add_ref(cam);
+	}
 	const uint32_t object_count = c.get<uint32_t>();
 	std::vector<ComponentRef> object_refs;
 	object_refs.reserve(std::min<size_t>(object_count, size_t(c.end - c.p)));
@@ -314,13 +342,15 @@ bool Scene::Load_binary(const void *data, size_t size, const char *name, Pipelin
 			n.name = c.str();
 			const uint32_t node_flags = c.get<uint32_t>();
 			const uint32_t transform_idx = c.get<uint32_t>();
-			c.skip(4); // camera
+			const uint32_t camera_idx = c.get<uint32_t>();
 			const uint32_t object_idx = c.get<uint32_t>();
 			c.skip(4); // light
 			if (transform_idx != 0xffffffffu && transform_idx < transform_refs.size())
 				n.transform = transform_refs[transform_idx];
 			if (object_idx != 0xffffffffu && object_idx < object_refs.size())
 				n.object = object_refs[object_idx];
+			if (camera_idx != 0xffffffffu && camera_idx < camera_refs.size())
+				n.camera = camera_refs[camera_idx];
 			if (file_flags & LSSF_Physics) {
 				c.skip(4); // rigid body
 				const uint32_t n_col = c.get<uint32_t>();
@@ -365,8 +395,12 @@ bool Scene::Load_binary(const void *data, size_t size, const char *name, Pipelin
 
 	// ---- scene block (environment, canvas): nothing the update path reads ----
 	if (file_flags & LSSF_Scene) {
-		if (file_flags & LSSF_Nodes)
-			c.skip(4); // current camera
+		if (file_flags & LSSF_Nodes) { // current camera: a saved node index (scene_load_binary.cpp:752-757)
+			const uint32_t camera_idx = c.get<uint32_t>();
+			const auto it = ctx.node_refs.find(camera_idx);
+			if (camera_idx != 0xffffffffu && it != ctx.node_refs.end())
+				current_camera = it->second;
+		}
 		c.skip(16 + 4 + 4 + 16); // ambient, fog near / far, fog colour
 		c.str(), c.str();        // probe maps
 		c.skip(1 + 1 + 36);      // probe type, parallax, TRS

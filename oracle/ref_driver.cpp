@@ -204,6 +204,24 @@ int hgref_anim_add_vec3_track(void *h, int anim, int kind, int n_keys, const int
 	return int(a->vec3_tracks.size()) - 1;
 }
 
+// float Hermite track with a free target name ("Camera.Fov": BindNodeAnim scene.cpp:2091-2101, evaluated by EvaluateBoundAnim :2194-2197)
+int hgref_anim_add_float_track(void *h, int anim, const char *target, int n_keys, const int64_t *t, const float *v, const float *tension, const float *bias) {
+	auto *c = static_cast<RefCtx *>(h);
+	Anim *a = c->scene->GetAnim(c->anims[anim]);
+	AnimTrackHermiteT<float> trk;
+	trk.target = target;
+	for (int i = 0; i < n_keys; ++i) {
+		AnimKeyHermiteT<float> k;
+		k.t = t[i];
+		k.v = v[i];
+		k.tension = tension ? tension[i] : 0.f;
+		k.bias = bias ? bias[i] : 0.f;
+		trk.keys.push_back(k);
+	}
+	a->float_tracks.push_back(trk);
+	return int(a->float_tracks.size()) - 1;
+}
+
 // "Enable" bool track (BindNodeAnim scene.cpp:2083-2089, evaluated by EvaluateBoundAnim :2158-2162 with EvaluateStep)
 int hgref_anim_add_enable_track(void *h, int anim, int n_keys, const int64_t *t, const uint8_t *v) {
 	auto *c = static_cast<RefCtx *>(h);

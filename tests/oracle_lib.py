@@ -78,6 +78,7 @@ def _bind_scene_driver(L, with_probes):
     _sig(L, "hgref_anim_add_vec3_track", c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p])
     _sig(L, "hgref_anim_add_quat_track", c_i, [c_p, c_i, c_i, c_p, c_p])
     _sig(L, "hgref_anim_add_enable_track", c_i, [c_p, c_i, c_i, c_p, c_p])
+    _sig(L, "hgref_anim_add_float_track", c_i, [c_p, c_i, C.c_char_p, c_i, c_p, c_p, c_p, c_p])
     _sig(L, "hgref_is_node_enabled", c_i, [c_p, c_i])
     _sig(L, "hgref_add_anims_bulk", c_i, [c_p, c_i, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p])
     _sig(L, "hgref_add_scene_anim", c_i, [c_p, c_i, c_p, c_p, c_i64, c_i64])

@@ -407,3 +407,44 @@ def test_facade_camera_view_state_matches_reference(fac, ref):
             s.update(scenegen.FRAME_DT)
     assert a.L.hgref_garbage_collect(a.h) == b.L.hgref_garbage_collect(b.h)  # replaced camera components are collected alike
     a.close(); b.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.ref
+def test_facade_camera_fov_track_matches_reference(fac, ref):
+    """"Camera.Fov" float tracks (Hermite, BindNodeAnim scene.cpp:2091-2101 / EvaluateBoundAnim :2194-2197): evaluated on the host by the
+    facade; the camera nodes also carry Position tracks sampled on the device. Fov and the whole view state of the current camera stay
+    bit-identical to the reference frame by frame (before the first key, between keys, after the anim ended), the last track of that
+    target wins and other float targets are ignored."""
+    rng = np.random.default_rng(131)
+    fs = scenegen.static_scene(3_000, 4, 6, n_models=2, seed=131)
+    nodes = np.sort(rng.choice(np.nonzero(fs.parent >= 0)[0], 300, replace=False)).astype(np.int32)
+    scenegen.add_position_tracks(fs, nodes, rng, n_keys=6, play_loop=False)
+    plays, fs.plays = fs.plays, []
+    a, b = RefScene(ref, fs), RefScene(fac, fs)
+    fs.plays = plays
+    cam_anims = [3, 77, 200]
+    kt = (np.arange(5, dtype=np.int64) * int(scenegen.KEY_DT * 1.3) + scenegen.KEY_DT // 3)
+    tracks = []
+    for _ in cam_anims:
+        tracks.append([(tg, rng.uniform(0.3, 2.2, 5).astype(np.float32), rng.uniform(-0.5, 0.5, 5).astype(np.float32), rng.uniform(-0.5, 0.5, 5).astype(np.float32))
+                       for tg in (b"Camera.Fov", b"Light.DiffuseIntensity", b"Camera.Fov")])
+    for L_, s in ((ref, a), (fac, b)):
+        for an, trk in zip(cam_anims, tracks):
+            assert s.set_camera(int(nodes[an]), 0.1, 300.0, fov=0.8, current=False)
+            for tg, v, te, bi in trk:
+                L_.hgref_anim_add_float_track(s.h, an, tg, 5, P(kt), P(v), P(te), P(bi))
+        for sa, loop, scale in fs.plays:
+            L_.hgref_play_anim(s.h, sa, loop, scale)
+    seen = set()
+    for frame in range(14):
+        a.update(scenegen.FRAME_DT * 2); b.update(scenegen.FRAME_DT * 2)
+        for an in cam_anims:
+            fa, fb = ref.hgref_get_camera_fov(a.h, int(nodes[an])), fac.hgref_get_camera_fov(b.h, int(nodes[an]))
+            assert np.float32(fa).view(np.uint32) == np.float32(fb).view(np.uint32), (frame, an, fa, fb)
+            seen.add(fa)
+            ref.hgref_set_current_camera(a.h, int(nodes[an])); fac.hgref_set_current_camera(b.h, int(nodes[an]))
+            for x, y in zip(a.view_state(16, 9), b.view_state(16, 9)):
+                assert (bits(x) == bits(y)).all(), (frame, an)
+    assert len(seen) > 12  # the value really moves
+    a.close(); b.close()
