@@ -301,6 +301,13 @@ def test_scene_binary_loader_frames_match_reference(fac, ref, kind, tmp_path):
     fs = _binary_scene(kind)
     a = RefScene(ref, fs)
     path = str(tmp_path / "scene.scn")
+    cams = []
+    if kind == "props":  # camera components, the current camera and a "Camera.Fov" float track travel through the file too
+        cams = [int(fs.anim_node[9]), int(fs.anim_node[5])]
+        assert a.set_camera(cams[0], 0.5, 80.0, size=20.0, current=False) and a.set_camera(cams[1], 0.2, 250.0, fov=0.7)
+        kt = np.arange(4, dtype=np.int64) * int(scenegen.KEY_DT * 0.8)
+        ref.hgref_anim_add_float_track(a.h, 5, b"Camera.Fov", 4, P(kt), P(np.array([0.5, 1.4, 0.9, 2.0], np.float32)), P(np.array([0.2, -0.3, 0.1, 0], np.float32)),
+                                       P(np.array([-0.1, 0.4, 0, 0.2], np.float32)))
     a.save_binary(path)
     a.close()
     b, c = RefScene(ref, fs, binary=path), RefScene(fac, fs, binary=path)
@@ -316,6 +323,15 @@ def test_scene_binary_loader_frames_match_reference(fac, ref, kind, tmp_path):
             assert (bits(b.worlds()[: fs.n]) == bits(wc)).all()
         (pb, mb), (pc, mc) = b.cull(0, fr), c.cull(0, fr)
         assert (pb == pc).all() and (mb == mc).all()
+        if cams:  # the current camera of the file, its fov driven by the loaded track
+            fb, fc = ref.hgref_get_camera_fov(b.h, cams[1]), fac.hgref_get_camera_fov(c.h, cams[1])
+            assert fb == fc and (frame == 0 or fb != np.float32(0.7)), (frame, fb, fc)
+            for x, y in zip(b.view_state(16, 9), c.view_state(16, 9)):
+                assert (bits(x) == bits(y)).all() and np.abs(x).max() > 0, frame
+    if cams:  # the orthographic one
+        ref.hgref_set_current_camera(b.h, cams[0]); fac.hgref_set_current_camera(c.h, cams[0])
+        for x, y in zip(b.view_state(4, 3), c.view_state(4, 3)):
+            assert (bits(x) == bits(y)).all() and np.abs(x).max() > 0
     if kind == "characters":
         bb, bc = b.bone_matrices().astype(np.float64), c.bone_matrices()
         assert bb.shape == bc.shape and (np.abs(bb - bc) / np.maximum(np.abs(bb), 1e-6 * np.abs(bb).max())).max() <= 1e-5
