@@ -225,6 +225,7 @@ struct hgb_ctx {
 	// gather) — and the post graph runs on stream2, so that it overlaps the NEXT frame's track sampling (which touches neither the
 	// visibility bytes nor the lists). The next frame's levels wait for it; every other entry point joins it first (join_post).
 	bool pdl_levels = true; // level d+1 launched with a programmatic dependency on level d (HGB_PDL=0 in the environment: plain, A/B)
+	bool pdl_first = true; // the first level is chained to the track sampler (HGB_PDL_FIRST=0: plain launch; A/B)
 	bool pdl_late_wait = true; // see SceneDev::late_wait (HGB_PDL_LATE=0: wait ahead of the sampled values, sampler -> first level chained instead; A/B)
 	bool async_post = false;
 	cudaGraphExec_t phase_exec[3][2] = {}; // [phase][world-buffer parity]
@@ -345,6 +346,8 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 	c->async_post = opt ? opt->async_post != 0 : false;
 	if (const char *e_pdl = getenv("HGB_PDL"))
 		c->pdl_levels = e_pdl[0] != '0';
+	if (const char *e_first = getenv("HGB_PDL_FIRST"))
+		c->pdl_first = e_first[0] != '0';
 	if (const char *e_late = getenv("HGB_PDL_LATE"))
 		c->pdl_late_wait = e_late[0] != '0';
 	c->transpose_store = opt ? opt->row_store == 0 : true; // reserved[0] = 1: per-thread 48-byte row stores (A/B switch for profiling)

@@ -220,6 +220,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	if (chain_post && enqueue_compaction_reset(c))
 		return 1;
 	bool prev_signals = false; // the kernel enqueued last executes griddepcontrol.launch_dependents
+	bool prev_is_sampler = false;
 	if (has_anim && !overlap && (phases & kPhasePre)) { // sequential: one launch per write round (normally one)
 		for (size_t r = 0; r + 1 < c->round_off.size(); ++r) {
 			const uint32_t first = c->round_off[r], cnt = c->round_off[r + 1] - first;
@@ -229,7 +230,10 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 			k_sample_tracks<<<grid_for(cnt, kSampleWarps * 32), kSampleWarps * 32, 0, c->stream>>>(a, first, cnt);
 			prof_end(c);
 			++*n_k;
-			prev_signals = !c->pdl_late_wait; // with the late wait a level reads sampled values ahead of its wait: the first one is a plain launch
+			// with the late wait a level reads sampled values ahead of its wait: the level chained to the sampler waits first thing and
+			// releases its own dependents only behind that wait (late_wait = 2)
+			prev_signals = !c->pdl_late_wait || c->pdl_first;
+			prev_is_sampler = true;
 		}
 	} else if (overlap) {
 		CK(cudaEventRecord(c->ev_chunk[0], c->stream)); // fork (also orders the chunks behind this frame's play-clock upload)
@@ -263,7 +267,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		e.n = uint32_t(c->en_target_slot_h.size());
 		k_sample_enable<<<grid_for(e.n, 128), 128, 0, c->stream>>>(e);
 		++*n_k;
-		prev_signals = false; // writes the flag rows the level kernels read before their wait: a full dependency
+		prev_signals = prev_is_sampler = false; // writes the flag rows the level kernels read before their wait: a full dependency
 	}
 
 	if (!(phases & kPhaseLevels)) {
@@ -277,12 +281,16 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		if (groups[g].d1 - groups[g].d0 >= 2) {
 			if (launch_small_run(c, s, do_fused, groups[g].d0, groups[g].d1 - groups[g].d0, groups[g].widest))
 				return 1;
-			prev_signals = false;
+			prev_signals = prev_is_sampler = false;
 		} else {
 			// a level that directly follows the sampler or another level may start while that one drains (k_update_level waits before
 			// it reads sampled values or parent rows)
-			launch_level(c, s, do_fused, groups[g].b, groups[g].e, chain && prev_signals);
+			SceneDev sl = s;
+			if (chain && prev_signals && prev_is_sampler && c->pdl_late_wait)
+				sl.late_wait = 2;
+			launch_level(c, sl, do_fused, groups[g].b, groups[g].e, chain && prev_signals);
 			prev_signals = true;
+			prev_is_sampler = false;
 		}
 		prof_end(c);
 		++*n_k;

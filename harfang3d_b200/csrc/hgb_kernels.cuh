@@ -53,7 +53,8 @@ struct SceneDev {
 	const uint16_t *pos_view;   // per position: which instance frustum (only with inst_planes)
 	int transpose_store;        // 1: world rows leave the SM as 3 contiguous 512-byte warp stores (shared-memory transpose)
 	uint32_t lookahead;         // positions: a warp asks L2 for the tile (and its parents' rows) this far ahead of its own; 0 = off
-	int late_wait;              // 1: the programmatic-dependency wait sits after the local matrix is built (the first level is then a plain launch)
+	int late_wait;              // where griddepcontrol.wait sits: 0 ahead of the sampled values; 1 behind the local matrix (levels behind a level);
+	                            // 2 like 0 and dependents are released only behind it (the level chained to the track sampler)
 };
 
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -96,7 +97,8 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 	}
 	// Programmatic dependent launch: the next level's grid may start while this one drains (it only reads its own tile rows before its
 	// griddepcontrol.wait below), which hides launch latency and the first DRAM round trip of the dependent chain of levels.
-	asm volatile("griddepcontrol.launch_dependents;");
+	if (s.late_wait != 2)
+		asm volatile("griddepcontrol.launch_dependents;");
 	const uint32_t p = begin + blockIdx.x * blockDim.x + threadIdx.x;
 	const bool live = p < end;
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -126,10 +128,13 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 			const uint32_t par = t[kRowParent * 32];
 			// everything above reads edit-time data; from here on the previous level's world rows are read (no-op without a
 			// programmatic dependency)
-			if (!s.late_wait)
+			if (s.late_wait != 1) {
 				asm volatile("griddepcontrol.wait;" ::: "memory");
+				if (s.late_wait == 2) // the next level reads sampled values ahead of ITS wait: it may only start once the sampler is complete
+					asm volatile("griddepcontrol.launch_dependents;");
+			}
 			if (par != kRoot) { // start the parent row on its way while the trigonometry runs (no registers held)
-				if (s.late_wait) { // not into L1 ahead of the wait: the row may not have been written yet and L1 would keep the old line
+				if (s.late_wait == 1) { // not into L1 ahead of the wait: the row may not have been written yet and L1 would keep the old line
 					prefetch_l2(s.world + size_t(par) * 12);
 					prefetch_l2(s.world + size_t(par) * 12 + 11);
 				} else {
@@ -152,7 +157,7 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 				}
 			}
 			world = transformation_mat4(px, py, pz, ex, ey, ez, sx, sy, sz);
-			if (s.late_wait)
+			if (s.late_wait == 1)
 				asm volatile("griddepcontrol.wait;" ::: "memory");
 			if (par != kRoot)
 				world = mat4_mul(load_mat4(s.world + size_t(par) * 12), world);
