@@ -59,6 +59,10 @@ typedef struct hgb_options {
 	int slice_nodes;   /* with overlap_sampler, levels larger than this are cut into slices of this many nodes, each waiting only for its
 	                      own track chunk (0 = no slicing; rounded up to a multiple of 256) */
 } hgb_options;
+/* Environment switches read by hgb_create, for A/B measurements only (defaults are the fast settings; results are identical in every
+ * mode): HGB_PDL=0 launches the frame's kernels with plain stream dependencies instead of programmatic dependent launches;
+ * HGB_PDL_LATE=0 puts the level kernel's dependency wait ahead of the sampled values; HGB_PDL_FIRST=0 keeps the first level a plain
+ * launch behind the track sampler ("Programmatic dependent launch"). */
 
 /* one bound animation track (BoundToNodeAnim entry, harfang/engine/scene.h:74-88) */
 typedef struct hgb_track {
