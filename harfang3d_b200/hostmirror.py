@@ -72,6 +72,28 @@ def scene_frusta(fs):
     return make_perspective_frustum(c["znear"], c["zfar"], c["fov"], c["ar_x"], c["ar_y"], c["world12"])
 
 
+def plane_margins(t, worlds12, frustum24, kind=0, sample=None):
+    """Diagnostic of SURVEY.md §8(d): how close the cull predicate of the enabled entries comes to flipping. For every entry and plane
+    TestVisibility (frustum.cpp:59-79) compares d - r (outside) and d + r (clipped) with -2w, d = n.(mn+mx), r = |n|.(mx-mn) over the
+    transformed box (minmax.cpp:226-244). Returns (min |d - r + 2w|, min |d + r + 2w|, entries looked at), computed in float64 from the
+    float32 world rows — a statistic for logs (a visible list that differs from the reference's with a margin of 1e-3 is a bug, not rounding),
+    not part of the result. `sample`: every n-th entry only."""
+    f64 = np.float64
+    slot, bidx, flags = t["ent%d_mtx_slot" % kind], t["ent%d_bounds_idx" % kind], t["ent%d_flags" % kind]
+    sel = np.nonzero(flags == 0)[0][:: (sample or 1)]
+    if len(sel) == 0:
+        return float("inf"), float("inf"), 0
+    W = np.asarray(worlds12, f32).reshape(-1, 3, 4)[slot[sel]].astype(f64)
+    b = np.asarray(t["bounds"], f32)[bidx[sel]].astype(f64)
+    lo, hi = W[:, :, :3] * b[:, None, 0:3], W[:, :, :3] * b[:, None, 3:6]
+    mn = W[:, :, 3] + np.minimum(lo, hi).sum(2)
+    mx = W[:, :, 3] + np.maximum(lo, hi).sum(2)
+    fr = np.asarray(frustum24, f32).reshape(6, 4).astype(f64)
+    d = (mn + mx) @ fr[:, :3].T
+    r = (mx - mn) @ np.abs(fr[:, :3]).T
+    return float(np.abs(d - r + 2 * fr[:, 3]).min()), float(np.abs(d + r + 2 * fr[:, 3]).min()), int(len(sel))
+
+
 # ---- bounding boxes -------------------------------------------------------------------------------------------------------------
 def object_table(fs):
     """Arguments of Context.set_objects for Scene::GetMinMax / GetNodesMinMax: every node with an Object whose model has bounds takes

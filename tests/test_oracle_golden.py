@@ -122,6 +122,36 @@ def test_golden_scenes_port(port, gs, name):
         assert (bits(sc.bone_matrices(previous=True)) == bits(gs[name + "_bones_prev"])).all()
 
 
+def test_plane_margin_statistic(port):
+    """hostmirror.plane_margins (SURVEY.md §8d diagnostic): a float64 re-evaluation of the cull predicate classifies every entry whose margin
+    is above float32 noise exactly like the oracle's visible list, and the reported minimum is the smallest of those margins"""
+    from harfang3d_b200 import scenegen
+    fs = scenegen.config_c1()
+    sc = PortScene(port, fs)
+    sc.update(0)
+    fr = hostmirror.scene_frusta(fs)[0]
+    m_out, m_clip, n = hostmirror.plane_margins(sc.t, sc.worlds(), fr)
+    assert n == int((sc.t["ent0_flags"] == 0).sum()) and 0 <= m_out < 1 and 0 <= m_clip < 1  # 10k boxes against 6 planes: some come close
+    _, _, n4 = hostmirror.plane_margins(sc.t, sc.worlds(), fr, sample=4)
+    assert n4 == (n + 3) // 4
+    # independent float64 classification of the enabled entries
+    t = sc.t
+    sel = np.nonzero(t["ent0_flags"] == 0)[0]
+    W = sc.worlds().reshape(-1, 3, 4)[t["ent0_mtx_slot"][sel]].astype(np.float64)
+    b = t["bounds"][t["ent0_bounds_idx"][sel]].astype(np.float64)
+    lo, hi = W[:, :, :3] * b[:, None, :3], W[:, :, :3] * b[:, None, 3:]
+    mn, mx = W[:, :, 3] + np.minimum(lo, hi).sum(2), W[:, :, 3] + np.maximum(lo, hi).sum(2)
+    f = fr.reshape(6, 4).astype(np.float64)
+    s_out = (mn + mx) @ f[:, :3].T - (mx - mn) @ np.abs(f[:, :3]).T + 2 * f[:, 3]
+    assert np.abs(s_out).min() == pytest.approx(m_out, rel=1e-12)
+    inside64 = ~(s_out > 0).any(1)
+    pos, _ = sc.cull(0, fr)
+    inside_port = np.zeros(len(sel), bool)
+    inside_port[pos] = True
+    sure = np.abs(s_out).min(1) > 1e-3
+    assert sure.sum() > 0.99 * len(sel) and (inside64[sure] == inside_port[sure]).all()
+
+
 # ---- (2) the reference's own unit-test expectations ---------------------------------------------------------------------------
 def almost(a, b, eps):
     return np.all(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64)) <= eps)
