@@ -95,8 +95,10 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 		stage_planes(s_planes, views);
 		__syncthreads();
 	}
-	// Programmatic dependent launch: the next level's grid may start while this one drains (it only reads its own tile rows before its
-	// griddepcontrol.wait below), which hides launch latency and the first DRAM round trip of the dependent chain of levels.
+	// Programmatic dependent launch: the next level's grid may become resident while this one drains — ahead of its own
+	// griddepcontrol.wait it reads only edit-time rows and sampled values — which hides the launch latency, the first DRAM round trip and
+	// the local-matrix arithmetic of the dependent chain of levels. The level chained to the track sampler (late_wait == 2) releases its
+	// dependents only behind its wait, so that no later level can run ahead of the sampler.
 	if (s.late_wait != 2)
 		asm volatile("griddepcontrol.launch_dependents;");
 	const uint32_t p = begin + blockIdx.x * blockDim.x + threadIdx.x;
