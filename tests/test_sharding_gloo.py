@@ -109,3 +109,61 @@ def test_partition_instances():
     assert sharding.partition_instances(2, 3).tolist() == [0, 1, 2, 2]
     b = sharding.partition_instances(1000, 7)
     assert b[0] == 0 and b[-1] == 1000 and np.diff(b).max() - np.diff(b).min() <= 1
+
+
+# ---- peer-gather setup: the host-side handshake (capi.Context.peer_setup) must leave every rank the same way ----
+class _FakePeerContext:
+    """the device calls of the handshake stubbed out (no GPU here); peer_setup itself is the product's"""
+
+    def __init__(self, rank, fail_init_on, fail_connect_on):
+        self.rank, self.fail_init_on, self.fail_connect_on = rank, fail_init_on, fail_connect_on
+        self.connected = self.closed = False
+
+    def peer_init(self, rank, world, dst, entries_per_rank, aux_words_per_rank=None):
+        from harfang3d_b200 import capi
+        if rank == self.fail_init_on:
+            raise capi.HgbError("no IPC here")
+        return bytes([rank]) * 64, bytes([100 + rank]) * 64
+
+    def peer_connect(self, inbox_of_dst, mailboxes):
+        from harfang3d_b200 import capi
+        assert inbox_of_dst == bytes([0]) * 64 and [m[0] for m in mailboxes] == [100 + r for r in range(len(mailboxes))]
+        if self.rank == self.fail_connect_on:
+            raise capi.HgbError("no peer access")
+        self.connected = True
+
+    def peer_close(self):
+        self.closed, self.connected = True, False
+
+
+def _peer_worker(rank, world, port, fail_init_on, fail_connect_on, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from harfang3d_b200 import capi
+        c = _FakePeerContext(rank, fail_init_on, fail_connect_on)
+        try:
+            capi.Context.peer_setup(c, dist, np.full(world, 10, np.uint32), None, dst=0)
+            q.put((rank, "ok", c.connected, c.closed))
+        except capi.HgbError as e:
+            q.put((rank, str(e), c.connected, c.closed))
+        dist.barrier()  # every rank is still in step with the others
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,fail_init_on,fail_connect_on", [(2, None, None), (2, 1, None), (3, None, 2), (3, 0, None)])
+def test_peer_setup_fails_on_every_rank_or_none(world, fail_init_on, fail_connect_on):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_peer_worker, args=(r, world, port, fail_init_on, fail_connect_on, q)) for r in range(world)]
+    [p.start() for p in procs]
+    got = sorted(q.get(timeout=120) for _ in range(world))
+    [p.join(60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    if fail_init_on is None and fail_connect_on is None:
+        assert all(g[1] == "ok" and g[2] and not g[3] for g in got)
+    else:
+        what = "no IPC here" if fail_init_on is not None else "no peer access"
+        assert all(what in g[1] and "peer gather unavailable" in g[1] and not g[2] and g[3] for g in got), got
