@@ -54,6 +54,27 @@ def test_facade_display_list_counts_like_reference_unit_test(fac):
 
 
 @pytest.mark.ref
+def test_facade_camera_component_host_side(fac, ref):
+    """Camera component bookkeeping without a device: fov get / set, replaced components collected by GarbageCollect like in the reference,
+    and the neutral (all-zero) view state for a missing current camera / a node without camera (scene.cpp:240-263 warn paths)"""
+    fs = six_objects()
+    a, b = RefScene(ref, fs), RefScene(fac, fs)
+    for L_, s in ((ref, a), (fac, b)):
+        for x in s.view_state(16, 9):  # no current camera
+            assert (bits(x) == 0).all()
+        assert s.set_camera(2, 0.1, 100.0, fov=0.9) and s.set_camera(2, 0.1, 100.0, size=4.0, current=False)  # the first one is orphaned
+        assert s.set_camera(4, 0.5, 50.0, fov=1.2, current=False)
+        L_.hgref_set_camera_fov(s.h, 4, 0.33)
+        assert L_.hgref_get_camera_fov(s.h, 4) == np.float32(0.33)
+        L_.hgref_set_current_camera(s.h, 1)  # a node without a camera component
+        for x in s.view_state(16, 9):
+            assert (bits(x) == 0).all()
+    assert ref.hgref_garbage_collect(a.h) == fac.hgref_garbage_collect(b.h) == 1
+    assert ref.hgref_get_camera_fov(a.h, 4) == fac.hgref_get_camera_fov(b.h, 4) == np.float32(0.33)
+    a.close(); b.close()
+
+
+@pytest.mark.ref
 def test_facade_slot_reuse_and_lists_match_reference(fac, ref):
     """destroy nodes + garbage collect + create again: transform slots are reused in the reference's order (LIFO free list), so the
     mtx_idx sequence of the display lists is identical (host-side)"""
