@@ -192,7 +192,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--lookahead", type=int, default=0, help="A/B switch: L2 prefetch distance in positions (0 = default, -1 = off)")
     ap.add_argument("--tma-level", action="store_true", help="A/B switch: persistent TMA-staged level kernel instead of one thread per node (LDG rows)")
-    ap.add_argument("--merge-small", action="store_true", help="A/B switch: runs of small top levels in one cooperative launch")
+    ap.add_argument("--top-walk", type=int, default=0, help="A/B switch: budget (node evaluations) of the one-launch top of the hierarchy (0 = default, -1 = one launch per level)")
     ap.add_argument("--slice-nodes", type=int, default=0, help="A/B switch: slice size of big levels under the overlapped sampler (0 = no slicing)")
     ap.add_argument("--overlap", action="store_true", help="A/B switch: sample tracks by target level on a second stream, overlapped with the level kernels")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="N>1 result gather: peer = survivors stored into rank 0's memory over NVLink "
@@ -219,7 +219,7 @@ def main():
 
     fs, desc = workload(args.workload, rank, args.scale)
     n_nodes = fs.n
-    ctx = harfang3d_b200.Context(local_rank, row_store=args.row_store, lookahead=args.lookahead, tma_level=args.tma_level, merge_small=args.merge_small, overlap_sampler=args.overlap, slice_nodes=args.slice_nodes,
+    ctx = harfang3d_b200.Context(local_rank, row_store=args.row_store, lookahead=args.lookahead, tma_level=args.tma_level, top_walk=args.top_walk, overlap_sampler=args.overlap, slice_nodes=args.slice_nodes,
                                   async_post=None if args.async_post is None else bool(args.async_post))
     t = hostmirror.upload(ctx, fs)
     n_entries = len(t["ent0_mtx_slot"]) + len(t["ent1_mtx_slot"])

@@ -116,13 +116,13 @@ def _ptr(a, dtype, what):
 class Context:
     """One hgb_ctx = one hg::Scene (or one batch of scene instances)."""
 
-    def __init__(self, device=0, use_graph=True, row_store=False, lookahead=0, tma_level=False, merge_small=False, overlap_sampler=False, slice_nodes=0, async_post=None):
+    def __init__(self, device=0, use_graph=True, row_store=False, lookahead=0, tma_level=False, top_walk=0, overlap_sampler=False, slice_nodes=0, async_post=None):
         """row_store=True: world rows are stored per thread (3 x 16 B at a 48-byte stride) instead of through the shared-memory
         transpose — an A/B switch for profiling (hgb_options.reserved[0])"""
         self._L = lib()
         if async_post is None:
             async_post = os.environ.get("HGB_ASYNC_POST", "0") == "1"  # test switch: run any script with the asynchronous frame tail
-        opt = (C.c_int * 8)(1 if use_graph else 0, 1 if row_store else 0, lookahead, 1 if tma_level else 0, 1 if async_post else 0, 1 if merge_small else 0, 1 if overlap_sampler else 0, slice_nodes)  # lookahead: 0 default, -1 off, n positions
+        opt = (C.c_int * 8)(1 if use_graph else 0, 1 if row_store else 0, lookahead, 1 if tma_level else 0, 1 if async_post else 0, top_walk, 1 if overlap_sampler else 0, slice_nodes)  # lookahead: 0 default, -1 off, n positions
         self._h = self._L.hgb_create(device, C.cast(opt, C.c_void_p))
         if not self._h:
             raise HgbError(self._L.hgb_last_error().decode())

@@ -148,14 +148,13 @@ struct hgb_ctx {
 	uint32_t n_tiles = 0;
 	bool transpose_store = true;
 	bool tma_level = false;   // A/B switch: persistent TMA-staged level kernel instead of one thread per node with LDG rows (measured slower: r01c)
-	bool merge_small = false; // runs of small levels in one cooperative launch (k_update_levels_small); opt-in: no gain inside a CUDA graph
+	uint64_t top_budget = 2500000; // k_update_top covers the leading levels whose recomputed work (sum of nodes x depth) stays below this; 0 = one launch per level
+	int level_minb = 6;            // resident CTAs per SM the level kernel's registers are held to (HGB_LEVEL_MINB=5: 48 registers; A/B)
 	bool overlap_sampler = false; // opt-in: sample tracks by target level on a second stream, overlapped with the level kernels (measured slower: r01c)
 	cudaStream_t stream2 = nullptr;
 	std::vector<cudaEvent_t> ev_chunk; // [0] fork, [1] join, [2+g] chunk of level group g
 	std::vector<uint32_t> trk_pos_h;   // target position of every round-0 track, ascending (chunk boundaries of the overlapped sampler)
 	uint32_t slice_nodes = 0;          // >0: with the overlapped sampler, big levels are cut into slices of this many positions (multiple of 256)
-	uint32_t small_level_max = 0, small_ctas = 0; // a level is small when it fits one grid-stride pass of the co-resident grid
-	DBuf level_barrier;
 	uint32_t persistent_ctas = 148 * 6; // resident CTAs of the device for the persistent level kernel
 	uint32_t lookahead = 0; // positions (see SceneDev::lookahead)
 	int cur = 0; // world[cur] = current frame
@@ -326,20 +325,17 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		{
 			c->lookahead = uint32_t(prop.multiProcessorCount) * 6u * 256u; // one wave of resident CTAs (6 x 256 threads per SM)
 			c->persistent_ctas = uint32_t(prop.multiProcessorCount) * 6u;
-			int per_sm = 0, coop = 0;
-			cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
-			if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_update_levels_small<true, false>, 256, 0) == cudaSuccess && per_sm > 0) {
-				int per_sm2 = per_sm;
-				cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, k_update_levels_small<true, true>, 256, 0);
-				c->small_ctas = uint32_t(prop.multiProcessorCount) * uint32_t(std::min(per_sm, per_sm2));
-				c->small_level_max = c->small_ctas * 256u;
-			}
 		}
 		if (opt && opt->lookahead != 0)
 			c->lookahead = opt->lookahead < 0 ? 0u : uint32_t(opt->lookahead); // A/B switch: -1 = off, n = positions
 	}
 	c->tma_level = opt ? opt->tma_level != 0 : false;
-	c->merge_small = opt ? opt->merge_small != 0 : false;
+	if (opt && opt->top_walk != 0)
+		c->top_budget = opt->top_walk < 0 ? 0u : uint64_t(opt->top_walk); // A/B switch: -1 = one launch per level, n = budget
+	if (const char *e_top = getenv("HGB_TOP_BUDGET"))
+		c->top_budget = strtoull(e_top, nullptr, 10);
+	if (const char *e_minb = getenv("HGB_LEVEL_MINB"))
+		c->level_minb = atoi(e_minb) == 5 ? 5 : 6;
 	c->overlap_sampler = opt ? opt->overlap_sampler != 0 : false;
 	if (opt && opt->slice_nodes > 0)
 		c->slice_nodes = (uint32_t(opt->slice_nodes) + 255u) & ~255u;
@@ -368,11 +364,6 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		cudaEvent_t e = nullptr;
 		if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess)
 			c->ev_chunk.push_back(e);
-	}
-	if (c->level_barrier.reserve(256) != cudaSuccess) { // grid-barrier word of k_update_levels_small (allocated here: never during graph capture)
-		fail("hgb_create: cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError()));
-		delete c;
-		return nullptr;
 	}
 	c->views.n_views = 0;
 	if (c->view_planes.reserve(kMaxViews * 96) != cudaSuccess) {
@@ -405,7 +396,7 @@ void hgb_destroy(hgb_ctx *c) {
 				cudaGraphExecDestroy(g);
 	DBuf *bufs[] = {&c->tiles, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
 		&c->pent, &c->pos_view, &c->inst_planes, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
-		&c->bone_out[1], &c->keys, &c->cursor, &c->tstate, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes, &c->level_barrier, &c->key_rec,
+		&c->bone_out[1], &c->keys, &c->cursor, &c->tstate, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes, &c->key_rec,
 		&c->en_target_pos, &c->en_off, &c->en_tracks_d, &c->en_keys_d, &c->en_scratch, &c->obj_pos, &c->obj_meta, &c->obj_seg, &c->obounds, &c->mm_acc, &c->peer_out_list, &c->peer_rank_off, &c->peer_aux_out};
 	for (DBuf *b : bufs)
 		b->release();

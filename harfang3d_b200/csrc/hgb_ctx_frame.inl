@@ -95,6 +95,16 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 	return 0;
 }
 
+template <int MINB> static void launch_level_v(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t b, uint32_t e, bool pdl) {
+	const dim3 g = grid_for(e - b);
+	if (!do_fused)
+		launch_after(c, pdl, k_update_level<false, false, MINB>, g, dim3(256), s, c->views, b, e);
+	else if (c->instance_mode)
+		launch_after(c, pdl, k_update_level<true, true, MINB>, g, dim3(256), s, c->views, b, e);
+	else
+		launch_after(c, pdl, k_update_level<true, false, MINB>, g, dim3(256), s, c->views, b, e);
+}
+
 static void launch_level(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t b, uint32_t e, bool pdl = false) {
 	if (c->tma_level) { // persistent warps, TMA-staged tiles (hgb_kernels_tma.cuh)
 		const uint32_t n_lt = ((e - 1u) >> 5) - (b >> 5) + 1u;
@@ -105,40 +115,40 @@ static void launch_level(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t 
 			k_update_level_tma<true, true><<<g, kTmaWarps * 32, 0, c->stream>>>(s, c->views, b, e);
 		else
 			k_update_level_tma<true, false><<<g, kTmaWarps * 32, 0, c->stream>>>(s, c->views, b, e);
+	} else if (c->level_minb == 5) {
+		launch_level_v<5>(c, s, do_fused, b, e, pdl);
 	} else {
-		const dim3 g = grid_for(e - b);
-		if (!do_fused)
-			launch_after(c, pdl, k_update_level<false, false>, g, dim3(256), s, c->views, b, e);
-		else if (c->instance_mode)
-			launch_after(c, pdl, k_update_level<true, true>, g, dim3(256), s, c->views, b, e);
-		else
-			launch_after(c, pdl, k_update_level<true, false>, g, dim3(256), s, c->views, b, e);
+		launch_level_v<6>(c, s, do_fused, b, e, pdl);
 	}
 }
 
-static int launch_small_run(hgb_ctx *c, const SceneDev &s, bool do_fused, size_t d, size_t run, uint32_t widest) {
-	SmallLevels lv{};
-	lv.n = uint32_t(run);
-	for (size_t k = 0; k <= run; ++k)
-		lv.off[k] = c->level_off[d + k];
-	CK(cudaMemsetAsync(c->level_barrier.p, 0, 4, c->stream));
-	cudaLaunchConfig_t cfg{};
-	cfg.gridDim = dim3(std::min((widest + 255u) / 256u, c->small_ctas));
-	cfg.blockDim = dim3(256);
-	cfg.stream = c->stream;
-	cudaLaunchAttribute at[1];
-	at[0].id = cudaLaunchAttributeCooperative;
-	at[0].val.cooperative = 1;
-	cfg.attrs = at;
-	cfg.numAttrs = 1;
-	uint32_t *bar = c->level_barrier.as<uint32_t>();
+// the first `top_levels` levels in one launch (k_update_top): positions [0, e)
+static void launch_top(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t e, bool pdl) {
+	const dim3 g = grid_for(e);
 	if (!do_fused)
-		CK(cudaLaunchKernelEx(&cfg, k_update_levels_small<false, false>, s, c->views, lv, bar));
+		launch_after(c, pdl, k_update_top<false, false>, g, dim3(256), s, c->views, e);
 	else if (c->instance_mode)
-		CK(cudaLaunchKernelEx(&cfg, k_update_levels_small<true, true>, s, c->views, lv, bar));
+		launch_after(c, pdl, k_update_top<true, true>, g, dim3(256), s, c->views, e);
 	else
-		CK(cudaLaunchKernelEx(&cfg, k_update_levels_small<true, false>, s, c->views, lv, bar));
-	return 0;
+		launch_after(c, pdl, k_update_top<true, false>, g, dim3(256), s, c->views, e);
+}
+
+// How many leading levels k_update_top covers: as many as keep the recomputed work (every node of level d evaluates d + 1 local
+// matrices) inside the budget, at most kMaxWalk. 1 = the first level alone (no recomputation).
+static size_t plan_top_levels(const hgb_ctx *c) {
+	const size_t n_levels = c->level_off.size() - 1;
+	if (c->top_budget == 0 || c->tma_level)
+		return 0;
+	uint64_t evals = 0;
+	size_t d = 0;
+	while (d < n_levels && d < size_t(kMaxWalk)) {
+		const uint64_t add = uint64_t(c->level_off[d + 1] - c->level_off[d]) * (d + 1);
+		if (d >= 1 && evals + add > c->top_budget)
+			break;
+		evals += add;
+		++d;
+	}
+	return d;
 }
 
 // One frame. Level groups (a level, or a run of small levels) go out in order on the context's stream. The track sampler is HBM-bound
@@ -170,41 +180,24 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	// of slice k+1 streams its keys while slice k computes (the level kernel is issue-bound and leaves HBM headroom, the sampler is
 	// HBM-bound and leaves issue slots)
 	struct Group {
-		size_t d0, d1;   // levels [d0, d1)
+		size_t d0, d1;   // levels [d0, d1): more than one = the top of the hierarchy in one launch (k_update_top)
 		uint32_t b, e;   // positions (a slice when d1 == d0 + 1)
-		uint32_t widest;
 	};
 	const bool want_overlap = has_anim && c->overlap_sampler && !c->prof.on && c->round_off.size() == 2 && !c->trk_pos_h.empty() && phases == kPhaseAll;
 	std::vector<Group> groups;
-	for (size_t d = 0; d < n_levels;) {
-		if (c->level_off[d + 1] == c->level_off[d]) {
-			++d;
+	const size_t n_top = want_overlap ? 0 : plan_top_levels(c);
+	if (n_top >= 1 && c->level_off[n_top] > 0)
+		groups.push_back({0, n_top, 0u, c->level_off[n_top]});
+	for (size_t d = n_top; d < n_levels; ++d) {
+		if (c->level_off[d + 1] == c->level_off[d])
 			continue;
-		}
-		size_t run = 0;
-		uint32_t widest = 0;
-		if (c->merge_small) {
-			while (d + run < n_levels && run < size_t(kMaxSmallRun)) {
-				const uint32_t sz = c->level_off[d + run + 1] - c->level_off[d + run];
-				if (sz == 0 || sz > c->small_level_max)
-					break;
-				widest = std::max(widest, sz);
-				++run;
-			}
-		}
-		if (run >= 2) {
-			groups.push_back({d, d + run, c->level_off[d], c->level_off[d + run], widest});
-			d += run;
-			continue;
-		}
 		const uint32_t lb = c->level_off[d], le = c->level_off[d + 1];
 		const uint32_t slice = want_overlap && c->slice_nodes ? c->slice_nodes : 0xffffff00u;
 		for (uint32_t p0 = lb; p0 < le;) {
 			const uint32_t p1 = (le - p0 <= slice + slice / 2) ? le : p0 + slice; // slice is a multiple of 256: warps keep their tile alignment
-			groups.push_back({d, d + 1, p0, p1, 0});
+			groups.push_back({d, d + 1, p0, p1});
 			p0 = p1;
 		}
-		++d;
 	}
 
 	while (want_overlap && c->ev_chunk.size() < groups.size() + 2) { // 96 exist from hgb_create; more only for very deep or very large scenes
@@ -216,7 +209,7 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	std::vector<char> has_chunk(groups.size(), 0);
 	// programmatic dependencies (kernel -> kernel, nothing enqueued in between): sampler -> first level -> ... -> last level -> compactions
 	const bool chain = c->pdl_levels && !c->prof.on && !c->tma_level && !overlap;
-	const bool chain_post = chain && do_fused && phases == kPhaseAll && !groups.empty() && groups.back().d1 - groups.back().d0 == 1;
+	const bool chain_post = chain && do_fused && phases == kPhaseAll && !groups.empty();
 	if (chain_post && enqueue_compaction_reset(c))
 		return 1;
 	bool prev_signals = false; // the kernel enqueued last executes griddepcontrol.launch_dependents
@@ -278,10 +271,11 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		if (has_chunk[g])
 			CK(cudaStreamWaitEvent(c->stream, c->ev_chunk[g + 2], 0));
 		prof_begin(c, HGB_K_UPDATE_LEVEL);
-		if (groups[g].d1 - groups[g].d0 >= 2) {
-			if (launch_small_run(c, s, do_fused, groups[g].d0, groups[g].d1 - groups[g].d0, groups[g].widest))
-				return 1;
-			prev_signals = prev_is_sampler = false;
+		if (n_top >= 1 && g == 0) {
+			// waits first thing and releases its dependents behind the wait (it reads sampled values throughout)
+			launch_top(c, s, do_fused, groups[g].e, chain && prev_signals);
+			prev_signals = true;
+			prev_is_sampler = false;
 		} else {
 			// a level that directly follows the sampler or another level may start while that one drains (k_update_level waits before
 			// it reads sampled values or parent rows)

@@ -80,6 +80,77 @@ __device__ __forceinline__ void stage_planes(float4 *s_planes, const Views &view
 		expand_plane(views.planes[threadIdx.x], s_planes[threadIdx.x * 2], s_planes[threadIdx.x * 2 + 1]);
 }
 
+// ---- per-node pieces shared by the level kernels ----------------------------------------------------------------------------
+// TRS of one node: its nine tile rows, with the track-driven triples replaced by the values sampled this frame (k_sample_tracks).
+// The position triple comes back as a pending gather (`pos_slot`), consumed only once the rotation is built: the translation is the
+// last thing TransformationMat4 needs, so the L2 round trip of that gather hides behind the three sincos.
+struct NodeTrs {
+	float px, py, pz, ex, ey, ez, sx, sy, sz;
+};
+__device__ __forceinline__ NodeTrs load_trs(const SceneDev &s, const uint32_t *t, uint32_t meta) {
+	NodeTrs n;
+	n.px = __uint_as_float(t[0]), n.py = __uint_as_float(t[32]), n.pz = __uint_as_float(t[64]);
+	n.ex = __uint_as_float(t[96]), n.ey = __uint_as_float(t[128]), n.ez = __uint_as_float(t[160]);
+	n.sx = __uint_as_float(t[192]), n.sy = __uint_as_float(t[224]), n.sz = __uint_as_float(t[256]);
+	if (meta & kLaneAnimatedMask) { // track-driven triples: the x row holds the anim_val slot
+		if (meta & (kLaneAnimated << 1)) {
+			const float4 v = s.anim_val[__float_as_uint(n.ex)];
+			n.ex = v.x, n.ey = v.y, n.ez = v.z;
+		}
+		if (meta & (kLaneAnimated << 2)) {
+			const float4 v = s.anim_val[__float_as_uint(n.sx)];
+			n.sx = v.x, n.sy = v.y, n.sz = v.z;
+		}
+	}
+	return n;
+}
+// local = TransformationMat4(pos, rot, scl) (foundation/matrix4.cpp:176-183)
+__device__ __forceinline__ Mat4 node_local(const SceneDev &s, const uint32_t *t, uint32_t meta) {
+	const NodeTrs n = load_trs(s, t, meta);
+	float4 vp = make_float4(n.px, n.py, n.pz, 0.f);
+	if (meta & kLaneAnimated)
+		vp = s.anim_val[__float_as_uint(n.px)];
+	Mat4 m = transformation_mat4(0.f, 0.f, 0.f, n.ex, n.ey, n.ez, n.sx, n.sy, n.sz);
+	m.m[0][3] = vp.x, m.m[1][3] = vp.y, m.m[2][3] = vp.z;
+	return m;
+}
+
+// world rows of a warp's 32 consecutive positions: through a shared-memory transpose they leave the SM as 3 contiguous 512-byte stores
+__device__ __forceinline__ void store_world_rows(const SceneDev &s, float4 *so, const Mat4 &world, bool live, uint32_t p, uint32_t lane, uint32_t end) {
+	if (s.transpose_store) {
+		if (live) {
+			so[lane * 3 + 0] = make_float4(world.m[0][0], world.m[0][1], world.m[0][2], world.m[0][3]);
+			so[lane * 3 + 1] = make_float4(world.m[1][0], world.m[1][1], world.m[1][2], world.m[1][3]);
+			so[lane * 3 + 2] = make_float4(world.m[2][0], world.m[2][1], world.m[2][2], world.m[2][3]);
+		}
+		__syncwarp();
+		const uint32_t p0 = p - lane;                              // first position of the warp
+		const uint32_t n_f4 = (min(end, p0 + 32u) - p0) * 3u;       // float4s this warp owns
+		float4 *dst = reinterpret_cast<float4 *>(s.world) + size_t(p0) * 3;
+#pragma unroll
+		for (int j = 0; j < 3; ++j)
+			if (lane + 32u * j < n_f4)
+				dst[lane + 32u * j] = so[lane + 32u * j];
+	} else if (live) {
+		store_mat4(s.world + size_t(p) * 12, world);
+	}
+}
+
+// GetModelDisplayLists flag logic + CullModelDisplayLists for every display entry attached to position p, world matrix in registers
+template <bool PER_INSTANCE>
+__device__ __forceinline__ void cull_node_entries(const SceneDev &s, const Mat4 &world, uint32_t meta, uint32_t eidx, const float4 *s_planes, int n_views, uint32_t p) {
+	const uint32_t bits = entry_visibility<PER_INSTANCE>(s, world, meta, s_planes, n_views, p);
+	((meta & kEntKindTransparent) ? s.vis1 : s.vis0)[eidx] = uint8_t(bits);
+	if (meta & kEntMore) {
+		const uint32_t e0 = s.ent_off[p], e1 = s.ent_off[p + 1];
+		for (uint32_t k = e0; k < e1; ++k) {
+			const uint2 rec = s.pent[k];
+			const uint32_t b = entry_visibility<PER_INSTANCE>(s, world, rec.y, s_planes, n_views, p);
+			((rec.x >> 31) ? s.vis1 : s.vis0)[rec.x & 0x7fffffffu] = uint8_t(b);
+		}
+	}
+}
+
 // ---- world-matrix propagation, one level per launch ---------------------------------------------------------------------
 // Replaces Scene::ComputeTransformWorldMatrix (engine/scene.cpp:263-277) for the positions [begin, end) of one hierarchy
 // level: local = TransformationMat4(pos, rot, scl); world = parent ? world[parent] * local : local. Parents were written
@@ -87,8 +158,9 @@ __device__ __forceinline__ void stage_planes(float4 *s_planes, const Views &view
 // view frusta for every display entry attached to the position (GetModelDisplayLists flag logic + CullModelDisplayLists,
 // engine/scene.cpp:330-364, engine/render_pipeline.cpp:2098-2104) and only a 1-byte visibility mask per entry is written.
 // `begin` is a multiple of 32 relative to the grid (blockDim = 256), so a warp covers 32 consecutive positions.
-template <bool FUSED, bool PER_INSTANCE>
-__global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views, uint32_t begin, uint32_t end) {
+// MINB = resident CTAs per SM the register allocation is held to (A/B: 6 -> 40 registers, 5 -> 48).
+template <bool FUSED, bool PER_INSTANCE, int MINB>
+__global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views views, uint32_t begin, uint32_t end) {
 	__shared__ float4 s_planes[kMaxViews * 12];
 	__shared__ float4 s_out[8][96]; // per warp: 32 world matrices = 1536 B, for the transposed store
 	if (FUSED && !PER_INSTANCE) { // the shared view frusta: broadcast LDS.128s instead of global loads
@@ -108,12 +180,95 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 		return;
 	// Software prefetch into L2: CTAs are dispatched in position order, so the tile `lookahead` positions ahead belongs to a CTA that
 	// starts about one CTA lifetime from now. Its 12 rows are requested by 12 lanes here, which turns the first (and otherwise fully
-	// exposed) DRAM latency of that CTA into an L2 hit.
+	// exposed) DRAM latency of that CTA into an L2 hit. Lanes 0..2 also start the load of that tile's first parent index: it is consumed
+	// at the very end of the kernel (prefetch of the parents' rows), by when it has long arrived.
 	const uint32_t pf = p - lane + s.lookahead;
 	const bool do_pf = s.lookahead != 0 && pf < end;
-	if (do_pf && lane < kTileRows)
+	uint32_t par_f = kRoot;
+	if (do_pf && lane < kTileRows) {
 		prefetch_l2(s.tiles + tile_word(pf & ~31u, lane));
+		if (lane < 3)
+			par_f = __ldcg(s.tiles + tile_word(pf, kRowParent));
+	}
 
+	// every live warp passes the dependency wait at warp level — preset rows too: a grid in which no thread waits could complete ahead
+	// of its predecessor and break the transitive completion the chain relies on
+	Mat4 world;
+	uint32_t meta = 0, eidx = 0, par = kRoot;
+	bool preset = false;
+	const uint32_t *t = s.tiles + tile_word(live ? p : begin, 0);
+	if (s.late_wait != 1) { // ahead of the sampled values (the level chained to the sampler, or HGB_PDL_LATE=0)
+		asm volatile("griddepcontrol.wait;" ::: "memory");
+		if (s.late_wait == 2) // the next level reads sampled values ahead of ITS wait: it may only start once the sampler is complete
+			asm volatile("griddepcontrol.launch_dependents;");
+	}
+	if (live) {
+		meta = t[kRowEntMeta * 32];
+		if (FUSED)
+			eidx = t[kRowEntIdx * 32];
+		preset = s.preset && s.preset[p];
+		if (!preset) {
+			par = t[kRowParent * 32];
+			if (par != kRoot) { // start the parent row on its way while the trigonometry runs (no registers held)
+				if (s.late_wait == 1) { // not into L1 ahead of the wait: the row may not have been written yet and L1 would keep the old line
+					prefetch_l2(s.world + size_t(par) * 12);
+					prefetch_l2(s.world + size_t(par) * 12 + 11);
+				} else {
+					prefetch_l1(s.world + size_t(par) * 12);
+					prefetch_l1(s.world + size_t(par) * 12 + 11);
+				}
+			}
+			world = node_local(s, t, meta);
+		}
+	}
+	// everything above reads edit-time data and sampled values; from here on the previous level's world rows are read
+	if (s.late_wait == 1)
+		asm volatile("griddepcontrol.wait;" ::: "memory");
+	if (live) {
+		if (preset)
+			world = load_mat4(s.world + size_t(p) * 12); // written by k_apply_presets ahead of the frame's kernels
+		else if (par != kRoot)
+			world = mat4_mul(load_mat4(s.world + size_t(par) * 12), world);
+	}
+
+	// store the world rows (a preset row is rewritten with its own value)
+	store_world_rows(s, s_out[warp], world, live, p, lane, end);
+
+	if (FUSED && live && (meta & kEntHas))
+		cull_node_entries<PER_INSTANCE>(s, world, meta, eidx, s_planes, views.n_views, p);
+
+	if (par_f != kRoot) // ... and the rows of the look-ahead tile's parents (siblings are adjacent: a few hundred contiguous bytes)
+		prefetch_l2(s.world + size_t(par_f) * 12 + lane * 32);
+}
+
+// ---- the top of the hierarchy in ONE launch ---------------------------------------------------------------------------------
+// The upper levels of a hierarchy hold 1 ... ~10^5 nodes each; one launch per level costs ~7 µs apiece there (launch ramp plus the
+// dependent tile -> parent -> math chain), far more than their bytes. This kernel covers the positions [0, end) of the first few
+// levels with NO dependency between its threads: every node walks up its ancestor chain (parent rows are edit-time data) and
+// multiplies the local matrices down again, world = ((L_root * L_1) * L_2) ... * L_node — the very sequence of operations
+// ComputeTransformWorldMatrix performs through its recursion (scene.cpp:263-277: world[parent] is itself world[grandparent] * local),
+// so every row is bit-identical to the level-by-level result; it is only recomputed by each descendant instead of read back. The
+// host bounds the redundant work (sum over the covered levels of nodes x depth, hgb_options.top_walk) and the chain length
+// (kMaxWalk). A chain stops at a preset ancestor (SetNodeWorldMatrix), whose row k_apply_presets wrote ahead of the frame.
+constexpr int kMaxWalk = 12;
+
+template <bool FUSED, bool PER_INSTANCE>
+__global__ void __launch_bounds__(256) k_update_top(SceneDev s, Views views, uint32_t end) {
+	__shared__ float4 s_planes[kMaxViews * 12];
+	__shared__ float4 s_out[8][96];
+	if (FUSED && !PER_INSTANCE) {
+		stage_planes(s_planes, views);
+		__syncthreads();
+	}
+	// chained behind the track sampler (or plain): it reads sampled values throughout, so it waits first thing and releases its
+	// dependents only behind the wait (they read sampled values ahead of THEIR wait)
+	asm volatile("griddepcontrol.wait;" ::: "memory");
+	asm volatile("griddepcontrol.launch_dependents;");
+	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	const bool live = p < end;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	if (__ballot_sync(0xffffffffu, live) == 0)
+		return;
 	Mat4 world;
 	uint32_t meta = 0, eidx = 0;
 	if (live) {
@@ -124,86 +279,30 @@ __global__ void __launch_bounds__(256, 6) k_update_level(SceneDev s, Views views
 		if (s.preset && s.preset[p]) {
 			world = load_mat4(s.world + size_t(p) * 12);
 		} else {
-			float px = __uint_as_float(t[0]), py = __uint_as_float(t[32]), pz = __uint_as_float(t[64]);
-			float ex = __uint_as_float(t[96]), ey = __uint_as_float(t[128]), ez = __uint_as_float(t[160]);
-			float sx = __uint_as_float(t[192]), sy = __uint_as_float(t[224]), sz = __uint_as_float(t[256]);
-			const uint32_t par = t[kRowParent * 32];
-			// everything above reads edit-time data; from here on the previous level's world rows are read (no-op without a
-			// programmatic dependency)
-			if (s.late_wait != 1) {
-				asm volatile("griddepcontrol.wait;" ::: "memory");
-				if (s.late_wait == 2) // the next level reads sampled values ahead of ITS wait: it may only start once the sampler is complete
-					asm volatile("griddepcontrol.launch_dependents;");
+			uint32_t chain[kMaxWalk]; // ancestors that must be recomputed, nearest first
+			int n = 0;
+			uint32_t q = t[kRowParent * 32];
+			while (q != kRoot && !(s.preset && s.preset[q]) && n < kMaxWalk) {
+				chain[n++] = q;
+				q = s.tiles[tile_word(q, kRowParent)];
 			}
-			if (par != kRoot) { // start the parent row on its way while the trigonometry runs (no registers held)
-				if (s.late_wait == 1) { // not into L1 ahead of the wait: the row may not have been written yet and L1 would keep the old line
-					prefetch_l2(s.world + size_t(par) * 12);
-					prefetch_l2(s.world + size_t(par) * 12 + 11);
-				} else {
-					prefetch_l1(s.world + size_t(par) * 12);
-					prefetch_l1(s.world + size_t(par) * 12 + 11);
-				}
+			bool have = q != kRoot; // stopped at a preset ancestor: its row is the base
+			if (have)
+				world = load_mat4(s.world + size_t(q) * 12);
+			for (int i = n - 1; i >= 0; --i) {
+				const uint32_t a = chain[i];
+				const uint32_t *ta = s.tiles + tile_word(a, 0);
+				const Mat4 la = node_local(s, ta, ta[kRowEntMeta * 32]);
+				world = have ? mat4_mul(world, la) : la;
+				have = true;
 			}
-			if (meta & kLaneAnimatedMask) { // track-driven triples: fetch the value sampled this frame (or the last one sampled)
-				if (meta & kLaneAnimated) {
-					const float4 v = s.anim_val[__float_as_uint(px)];
-					px = v.x, py = v.y, pz = v.z;
-				}
-				if (meta & (kLaneAnimated << 1)) {
-					const float4 v = s.anim_val[__float_as_uint(ex)];
-					ex = v.x, ey = v.y, ez = v.z;
-				}
-				if (meta & (kLaneAnimated << 2)) {
-					const float4 v = s.anim_val[__float_as_uint(sx)];
-					sx = v.x, sy = v.y, sz = v.z;
-				}
-			}
-			world = transformation_mat4(px, py, pz, ex, ey, ez, sx, sy, sz);
-			if (s.late_wait == 1)
-				asm volatile("griddepcontrol.wait;" ::: "memory");
-			if (par != kRoot)
-				world = mat4_mul(load_mat4(s.world + size_t(par) * 12), world);
+			const Mat4 local = node_local(s, t, meta);
+			world = have ? mat4_mul(world, local) : local;
 		}
 	}
-
-	// store the world rows (a preset row is rewritten with its own value)
-	if (s.transpose_store) {
-		float4 *so = s_out[warp];
-		if (live) {
-			so[lane * 3 + 0] = make_float4(world.m[0][0], world.m[0][1], world.m[0][2], world.m[0][3]);
-			so[lane * 3 + 1] = make_float4(world.m[1][0], world.m[1][1], world.m[1][2], world.m[1][3]);
-			so[lane * 3 + 2] = make_float4(world.m[2][0], world.m[2][1], world.m[2][2], world.m[2][3]);
-		}
-		__syncwarp();
-		const uint32_t p0 = p - lane;                              // first position of the warp
-		const uint32_t n_f4 = (min(end, p0 + 32u) - p0) * 3u;       // float4s this warp owns
-		float4 *dst = reinterpret_cast<float4 *>(s.world) + size_t(p0) * 3;
-#pragma unroll
-		for (int j = 0; j < 3; ++j)
-			if (lane + 32u * j < n_f4)
-				dst[lane + 32u * j] = so[lane + 32u * j];
-	} else if (live) {
-		store_mat4(s.world + size_t(p) * 12, world);
-	}
-
-	if (do_pf && lane < 3) { // ... and the rows of that tile's parents (siblings are adjacent: a few hundred contiguous bytes)
-		const uint32_t par_f = s.tiles[tile_word(pf, kRowParent)];
-		if (par_f != kRoot)
-			prefetch_l2(s.world + size_t(par_f) * 12 + lane * 32);
-	}
-
-	if (FUSED && live && (meta & kEntHas)) {
-		const uint32_t bits = entry_visibility<PER_INSTANCE>(s, world, meta, s_planes, views.n_views, p);
-		((meta & kEntKindTransparent) ? s.vis1 : s.vis0)[eidx] = uint8_t(bits);
-		if (meta & kEntMore) {
-			const uint32_t e0 = s.ent_off[p], e1 = s.ent_off[p + 1];
-			for (uint32_t k = e0; k < e1; ++k) {
-				const uint2 rec = s.pent[k];
-				const uint32_t b = entry_visibility<PER_INSTANCE>(s, world, rec.y, s_planes, views.n_views, p);
-				((rec.x >> 31) ? s.vis1 : s.vis0)[rec.x & 0x7fffffffu] = uint8_t(b);
-			}
-		}
-	}
+	store_world_rows(s, s_out[warp], world, live, p, lane, end);
+	if (FUSED && live && (meta & kEntHas))
+		cull_node_entries<PER_INSTANCE>(s, world, meta, eidx, s_planes, views.n_views, p);
 }
 
 // ---- stand-alone cull predicate (entry order) -------------------------------------------------------------------------------

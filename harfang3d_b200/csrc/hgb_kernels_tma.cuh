@@ -1,4 +1,5 @@
-// Persistent, TMA-staged form of the level kernel (default). Same arithmetic and outputs as k_update_level (hgb_kernels.cuh); what
+// Persistent, TMA-staged form of the level kernel (OPT-IN A/B variant, hgb_options.tma_level: measured 4 % slower than the default
+// one-thread-per-node kernel on the 16M-node batch, profiles/README.md r01c). Same arithmetic and outputs as k_update_level (hgb_kernels.cuh); what
 // changes is how bytes move:
 //   * a node tile is 1536 contiguous bytes (12 rows x 32 positions), so one lane fetches it with ONE bulk copy
 //     (cp.async.bulk global -> shared, completion on an mbarrier) instead of twelve 128-byte LDGs per warp plus their address math;
@@ -162,97 +163,6 @@ __global__ void __launch_bounds__(kTmaWarps * 32, 6) k_update_level_tma(SceneDev
 				fence_proxy_async();
 		}
 		__syncwarp();
-	}
-}
-
-// ---- runs of small levels in ONE launch --------------------------------------------------------------------------------------
-// The top of a hierarchy is a handful of levels with 1 ... ~10^5 nodes. One launch per level costs ~7 µs each there (launch ramp +
-// the dependent tile -> parent -> math chain), far more than their bytes. This kernel walks a run of consecutive small levels with a
-// grid-wide barrier between them: the grid is launched cooperatively (all CTAs co-resident), a level is a grid-stride loop, and
-// children read their parents' freshly written rows with ld.global.cg (L2 — never a stale L1 line).
-constexpr int kMaxSmallRun = 16;
-struct SmallLevels {
-	uint32_t n;                      // levels in the run
-	uint32_t off[kMaxSmallRun + 1];  // positions [off[k], off[k+1])
-};
-
-__device__ __forceinline__ Mat4 load_mat4_cg(const float *p) {
-	const float4 *q = reinterpret_cast<const float4 *>(p);
-	const float4 a = __ldcg(q), b = __ldcg(q + 1), c = __ldcg(q + 2);
-	Mat4 o;
-	o.m[0][0] = a.x, o.m[0][1] = a.y, o.m[0][2] = a.z, o.m[0][3] = a.w;
-	o.m[1][0] = b.x, o.m[1][1] = b.y, o.m[1][2] = b.z, o.m[1][3] = b.w;
-	o.m[2][0] = c.x, o.m[2][1] = c.y, o.m[2][2] = c.z, o.m[2][3] = c.w;
-	return o;
-}
-
-__device__ __forceinline__ void grid_barrier(uint32_t *counter, uint32_t target) {
-	__syncthreads();
-	if (threadIdx.x == 0) {
-		__threadfence(); // this CTA's world rows are visible device-wide before it arrives
-		atomicAdd(counter, 1u);
-		uint32_t seen;
-		do {
-			asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
-		} while (seen < target);
-	}
-	__syncthreads();
-}
-
-template <bool FUSED, bool PER_INSTANCE>
-__global__ void __launch_bounds__(256, 4) k_update_levels_small(SceneDev s, Views views, SmallLevels lv, uint32_t *barrier) {
-	__shared__ float4 s_planes[kMaxViews * 12];
-	if (FUSED && !PER_INSTANCE) {
-		stage_planes(s_planes, views);
-		__syncthreads();
-	}
-	for (uint32_t k = 0; k < lv.n; ++k) {
-		const uint32_t end = lv.off[k + 1];
-		for (uint32_t p = lv.off[k] + blockIdx.x * blockDim.x + threadIdx.x; p < end; p += gridDim.x * blockDim.x) {
-			const uint32_t *t = s.tiles + tile_word(p, 0);
-			const uint32_t meta = t[kRowEntMeta * 32];
-			Mat4 world;
-			if (s.preset && s.preset[p]) {
-				world = load_mat4_cg(s.world + size_t(p) * 12);
-			} else {
-				float px = __uint_as_float(t[0]), py = __uint_as_float(t[32]), pz = __uint_as_float(t[64]);
-				float ex = __uint_as_float(t[96]), ey = __uint_as_float(t[128]), ez = __uint_as_float(t[160]);
-				float sx = __uint_as_float(t[192]), sy = __uint_as_float(t[224]), sz = __uint_as_float(t[256]);
-				const uint32_t par = t[kRowParent * 32];
-				if (meta & kLaneAnimatedMask) {
-					if (meta & kLaneAnimated) {
-						const float4 v = s.anim_val[__float_as_uint(px)];
-						px = v.x, py = v.y, pz = v.z;
-					}
-					if (meta & (kLaneAnimated << 1)) {
-						const float4 v = s.anim_val[__float_as_uint(ex)];
-						ex = v.x, ey = v.y, ez = v.z;
-					}
-					if (meta & (kLaneAnimated << 2)) {
-						const float4 v = s.anim_val[__float_as_uint(sx)];
-						sx = v.x, sy = v.y, sz = v.z;
-					}
-				}
-				world = transformation_mat4(px, py, pz, ex, ey, ez, sx, sy, sz);
-				if (par != kRoot)
-					world = mat4_mul(load_mat4_cg(s.world + size_t(par) * 12), world);
-			}
-			store_mat4(s.world + size_t(p) * 12, world);
-			if (FUSED && (meta & kEntHas)) {
-				const uint32_t bits = entry_visibility<PER_INSTANCE>(s, world, meta, s_planes, views.n_views, p);
-				((meta & kEntKindTransparent) ? s.vis1 : s.vis0)[t[kRowEntIdx * 32]] = uint8_t(bits);
-				if (meta & kEntMore) {
-					const uint32_t e0 = s.ent_off[p], e1 = s.ent_off[p + 1];
-					for (uint32_t e = e0; e < e1; ++e) {
-						const uint2 rec = s.pent[e];
-						const uint32_t b = entry_visibility<PER_INSTANCE>(s, world, rec.y, s_planes, views.n_views, p);
-						((rec.x >> 31) ? s.vis1 : s.vis0)[rec.x & 0x7fffffffu] = uint8_t(b);
-					}
-				}
-			}
-		}
-		if (k + 1 < lv.n)
-			grid_barrier(barrier, (k + 1) * gridDim.x);
 	}
 }
 

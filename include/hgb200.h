@@ -52,8 +52,9 @@ typedef struct hgb_options {
 	int async_post;    /* 1: the tail of the frame — compaction of the visible lists and the peer gather — runs on a second stream and overlaps
 	                      the NEXT frame's track sampling; the next frame's level kernels and every other entry point wait for it, so
 	                      results and API semantics are unchanged. Default 0 */
-	int merge_small;   /* 1: runs of consecutive small levels go out as one cooperative launch with grid barriers between the levels
-	                      (k_update_levels_small). Default 0: measured faster per kernel but not inside the frame graph (profiles r01c) */
+	int top_walk;      /* the leading levels of the hierarchy go out as ONE launch (k_update_top: every node recomputes its ancestor chain, no
+	                      dependency between threads). 0 = default budget (levels are added while sum(nodes x depth) <= 2.5 M), -1 = off (one
+	                      launch per level), n = budget in node evaluations */
 	int overlap_sampler; /* 1: tracks are sampled in chunks by target level on a second stream, overlapped with the level kernels. Default 0:
 	                        both kernels lean on HBM, running them together measured 1-8 % slower than back to back (profiles r01c) */
 	int slice_nodes;   /* with overlap_sampler, levels larger than this are cut into slices of this many nodes, each waiting only for its

@@ -49,7 +49,7 @@ def test_c4_full_16m_batch(hgb):
     sub = scenegen.extract_range(fs, k * n_per, (k + 1) * n_per)
     orc = _oracle(sub)
     ctx = hgb.Context(0)
-    ctx2 = hgb.Context(0, tma_level=True, merge_small=True, overlap_sampler=True, slice_nodes=1 << 20)
+    ctx2 = hgb.Context(0, tma_level=True, top_walk=-1, overlap_sampler=True, slice_nodes=1 << 20)
     t = hostmirror.upload(ctx, fs)
     hostmirror.upload(ctx2, fs, tables=t)
     clocks, clocks2 = hostmirror.PlayClocks(fs), hostmirror.PlayClocks(fs)

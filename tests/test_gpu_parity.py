@@ -466,18 +466,27 @@ def test_multi_view_cull(hgb, oracles):
 
 def test_profile_counters(hgb):
     fs = scenegen.config_c1()
-    ctx = hgb.Context(0)
+    ctx = hgb.Context(0, top_walk=-1)
     hostmirror.upload(ctx, fs)
     ctx.set_profiling(True)
     ctx.update(None, fused_cull=True)
     prof = ctx.get_profile()
     assert prof["k_update_level"][1] == 4 and prof["k_update_level"][0] > 0 and prof["k_compact"][1] == 1  # one launch per level
+    w4 = ctx.get_worlds()
     ctx.close()
-    ctx = hgb.Context(0, merge_small=True)  # the four small levels of the 10k-node scene as ONE cooperative launch
+    ctx = hgb.Context(0)  # default: the four small levels of the 10k-node scene as ONE launch (k_update_top, ancestor walk)
     hostmirror.upload(ctx, fs)
     ctx.set_profiling(True)
     ctx.update(None, fused_cull=True)
     assert ctx.get_profile()["k_update_level"][1] == 1
+    assert (bits(ctx.get_worlds()) == bits(w4)).all()
+    ctx.close()
+    ctx = hgb.Context(0, top_walk=25_000)  # budget reached after three levels (1 + 21*2 + 441*3): top launch + one level launch
+    hostmirror.upload(ctx, fs)
+    ctx.set_profiling(True)
+    ctx.update(None, fused_cull=True)
+    assert ctx.get_profile()["k_update_level"][1] == 2
+    assert (bits(ctx.get_worlds()) == bits(w4)).all()
     ctx.close()
 
 
