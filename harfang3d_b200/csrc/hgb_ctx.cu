@@ -157,6 +157,7 @@ struct hgb_ctx {
 	uint32_t slice_nodes = 0;          // >0: with the overlapped sampler, big levels are cut into slices of this many positions (multiple of 256)
 	uint32_t persistent_ctas = 148 * 6; // resident CTAs of the device for the persistent level kernel
 	uint32_t lookahead = 0; // positions (see SceneDev::lookahead)
+	bool la_parents = true;
 	int cur = 0; // world[cur] = current frame
 	bool preset_pending = false, preset_dirty = false;
 	DBuf preset_pos, preset_mat;
@@ -334,6 +335,8 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		c->top_budget = opt->top_walk < 0 ? 0u : uint64_t(opt->top_walk); // A/B switch: -1 = one launch per level, n = budget
 	if (const char *e_top = getenv("HGB_TOP_BUDGET"))
 		c->top_budget = strtoull(e_top, nullptr, 10);
+	if (const char *e_lap = getenv("HGB_LA_PARENTS"))
+		c->la_parents = e_lap[0] != '0';
 	if (const char *e_minb = getenv("HGB_LEVEL_MINB"))
 		c->level_minb = atoi(e_minb) == 5 ? 5 : 6;
 	c->overlap_sampler = opt ? opt->overlap_sampler != 0 : false;

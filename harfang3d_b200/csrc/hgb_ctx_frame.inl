@@ -7,6 +7,7 @@ static SceneDev scene_dev(hgb_ctx *c, bool with_preset) {
 	s.anim_val = c->anim_val.as<float4>();
 	s.transpose_store = c->transpose_store ? 1 : 0;
 	s.lookahead = c->lookahead;
+	s.la_parents = c->la_parents ? 1 : 0;
 	s.late_wait = c->pdl_late_wait ? 1 : 0;
 	s.world = c->world[c->cur].as<float>();
 	s.preset = with_preset ? c->preset.as<uint8_t>() : nullptr;

@@ -53,6 +53,7 @@ struct SceneDev {
 	const uint16_t *pos_view;   // per position: which instance frustum (only with inst_planes)
 	int transpose_store;        // 1: world rows leave the SM as 3 contiguous 512-byte warp stores (shared-memory transpose)
 	uint32_t lookahead;         // positions: a warp asks L2 for the tile (and its parents' rows) this far ahead of its own; 0 = off
+	int la_parents;             // 1: the look-ahead also covers the world rows of that tile's parents (HGB_LA_PARENTS=0: tiles only; A/B)
 	int late_wait;              // where griddepcontrol.wait sits: 0 ahead of the sampled values; 1 behind the local matrix (levels behind a level);
 	                            // 2 like 0 and dependents are released only behind it (the level chained to the track sampler)
 };
@@ -104,15 +105,13 @@ __device__ __forceinline__ NodeTrs load_trs(const SceneDev &s, const uint32_t *t
 	}
 	return n;
 }
-// local = TransformationMat4(pos, rot, scl) (foundation/matrix4.cpp:176-183)
-__device__ __forceinline__ Mat4 node_local(const SceneDev &s, const uint32_t *t, uint32_t meta) {
+// local = TransformationMat4(pos, rot, scl) (foundation/matrix4.cpp:176-183), in the row-pair form mat4_mul_p consumes
+__device__ __forceinline__ Mat4p node_local(const SceneDev &s, const uint32_t *t, uint32_t meta) {
 	const NodeTrs n = load_trs(s, t, meta);
 	float4 vp = make_float4(n.px, n.py, n.pz, 0.f);
 	if (meta & kLaneAnimated)
 		vp = s.anim_val[__float_as_uint(n.px)];
-	Mat4 m = transformation_mat4(0.f, 0.f, 0.f, n.ex, n.ey, n.ez, n.sx, n.sy, n.sz);
-	m.m[0][3] = vp.x, m.m[1][3] = vp.y, m.m[2][3] = vp.z;
-	return m;
+	return transformation_mat4p(vp.x, vp.y, vp.z, n.ex, n.ey, n.ez, n.sx, n.sy, n.sz);
 }
 
 // world rows of a warp's 32 consecutive positions: through a shared-memory transpose they leave the SM as 3 contiguous 512-byte stores
@@ -137,18 +136,33 @@ __device__ __forceinline__ void store_world_rows(const SceneDev &s, float4 *so, 
 }
 
 // GetModelDisplayLists flag logic + CullModelDisplayLists for every display entry attached to position p, world matrix in registers
+// further display entries of a node (multi-list models): rare, kept out of line — and fed with values, not with a reference to the
+// kernel's parameter block, which would force the whole block into local memory
+struct MoreEntries {
+	const uint32_t *ent_off;
+	const uint2 *pent;
+	const float *bounds6;
+	uint8_t *vis0, *vis1;
+	const float4 *inst_planes;
+	const uint16_t *pos_view;
+};
+template <bool PER_INSTANCE>
+__device__ __noinline__ void cull_more_entries(MoreEntries m, Mat4 world, const float4 *s_planes, int n_views, uint32_t p) {
+	SceneDev s{};
+	s.bounds6 = m.bounds6, s.inst_planes = m.inst_planes, s.pos_view = m.pos_view;
+	const uint32_t e0 = m.ent_off[p], e1 = m.ent_off[p + 1];
+	for (uint32_t k = e0; k < e1; ++k) {
+		const uint2 rec = m.pent[k];
+		const uint32_t b = entry_visibility<PER_INSTANCE>(s, world, rec.y, s_planes, n_views, p);
+		((rec.x >> 31) ? m.vis1 : m.vis0)[rec.x & 0x7fffffffu] = uint8_t(b);
+	}
+}
 template <bool PER_INSTANCE>
 __device__ __forceinline__ void cull_node_entries(const SceneDev &s, const Mat4 &world, uint32_t meta, uint32_t eidx, const float4 *s_planes, int n_views, uint32_t p) {
 	const uint32_t bits = entry_visibility<PER_INSTANCE>(s, world, meta, s_planes, n_views, p);
 	((meta & kEntKindTransparent) ? s.vis1 : s.vis0)[eidx] = uint8_t(bits);
-	if (meta & kEntMore) {
-		const uint32_t e0 = s.ent_off[p], e1 = s.ent_off[p + 1];
-		for (uint32_t k = e0; k < e1; ++k) {
-			const uint2 rec = s.pent[k];
-			const uint32_t b = entry_visibility<PER_INSTANCE>(s, world, rec.y, s_planes, n_views, p);
-			((rec.x >> 31) ? s.vis1 : s.vis0)[rec.x & 0x7fffffffu] = uint8_t(b);
-		}
-	}
+	if (meta & kEntMore)
+		cull_more_entries<PER_INSTANCE>(MoreEntries{s.ent_off, s.pent, s.bounds6, s.vis0, s.vis1, s.inst_planes, s.pos_view}, world, s_planes, n_views, p);
 }
 
 // ---- world-matrix propagation, one level per launch ---------------------------------------------------------------------
@@ -187,28 +201,33 @@ __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views vi
 	uint32_t par_f = kRoot;
 	if (do_pf && lane < kTileRows) {
 		prefetch_l2(s.tiles + tile_word(pf & ~31u, lane));
-		if (lane < 3)
+		if (lane < 3 && s.la_parents)
 			par_f = __ldcg(s.tiles + tile_word(pf, kRowParent));
 	}
 
-	// every live warp passes the dependency wait at warp level — preset rows too: a grid in which no thread waits could complete ahead
-	// of its predecessor and break the transitive completion the chain relies on
 	Mat4 world;
-	uint32_t meta = 0, eidx = 0, par = kRoot;
-	bool preset = false;
-	const uint32_t *t = s.tiles + tile_word(live ? p : begin, 0);
-	if (s.late_wait != 1) { // ahead of the sampled values (the level chained to the sampler, or HGB_PDL_LATE=0)
-		asm volatile("griddepcontrol.wait;" ::: "memory");
-		if (s.late_wait == 2) // the next level reads sampled values ahead of ITS wait: it may only start once the sampler is complete
-			asm volatile("griddepcontrol.launch_dependents;");
-	}
+	uint32_t meta = 0, eidx = 0;
 	if (live) {
+		const uint32_t *t = s.tiles + tile_word(p, 0);
 		meta = t[kRowEntMeta * 32];
 		if (FUSED)
 			eidx = t[kRowEntIdx * 32];
-		preset = s.preset && s.preset[p];
-		if (!preset) {
-			par = t[kRowParent * 32];
+		if (s.preset && s.preset[p]) {
+			// a preset row (SetNodeWorldMatrix) is kept as it is — but the thread still passes the dependency wait: a grid in which no
+			// thread waits could complete ahead of its predecessor and break the transitive completion the chain of levels relies on
+			asm volatile("griddepcontrol.wait;" ::: "memory");
+			if (s.late_wait == 2)
+				asm volatile("griddepcontrol.launch_dependents;");
+			world = load_mat4(s.world + size_t(p) * 12);
+		} else {
+			const uint32_t par = t[kRowParent * 32];
+			// everything above reads edit-time data; from here on sampled values and the previous level's world rows are read (no-op
+			// without a programmatic dependency)
+			if (s.late_wait != 1) {
+				asm volatile("griddepcontrol.wait;" ::: "memory");
+				if (s.late_wait == 2) // the next level reads sampled values ahead of ITS wait: it may only start once the sampler is complete
+					asm volatile("griddepcontrol.launch_dependents;");
+			}
 			if (par != kRoot) { // start the parent row on its way while the trigonometry runs (no registers held)
 				if (s.late_wait == 1) { // not into L1 ahead of the wait: the row may not have been written yet and L1 would keep the old line
 					prefetch_l2(s.world + size_t(par) * 12);
@@ -218,17 +237,14 @@ __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views vi
 					prefetch_l1(s.world + size_t(par) * 12 + 11);
 				}
 			}
-			world = node_local(s, t, meta);
+			const Mat4p local = node_local(s, t, meta);
+			if (s.late_wait == 1)
+				asm volatile("griddepcontrol.wait;" ::: "memory");
+			if (par != kRoot)
+				world = mat4_mul_p(load_mat4(s.world + size_t(par) * 12), local);
+			else
+				world = unpack_mat4(local);
 		}
-	}
-	// everything above reads edit-time data and sampled values; from here on the previous level's world rows are read
-	if (s.late_wait == 1)
-		asm volatile("griddepcontrol.wait;" ::: "memory");
-	if (live) {
-		if (preset)
-			world = load_mat4(s.world + size_t(p) * 12); // written by k_apply_presets ahead of the frame's kernels
-		else if (par != kRoot)
-			world = mat4_mul(load_mat4(s.world + size_t(par) * 12), world);
 	}
 
 	// store the world rows (a preset row is rewritten with its own value)
@@ -292,12 +308,12 @@ __global__ void __launch_bounds__(256) k_update_top(SceneDev s, Views views, uin
 			for (int i = n - 1; i >= 0; --i) {
 				const uint32_t a = chain[i];
 				const uint32_t *ta = s.tiles + tile_word(a, 0);
-				const Mat4 la = node_local(s, ta, ta[kRowEntMeta * 32]);
-				world = have ? mat4_mul(world, la) : la;
+				const Mat4p la = node_local(s, ta, ta[kRowEntMeta * 32]);
+				world = have ? mat4_mul_p(world, la) : unpack_mat4(la);
 				have = true;
 			}
-			const Mat4 local = node_local(s, t, meta);
-			world = have ? mat4_mul(world, local) : local;
+			const Mat4p local = node_local(s, t, meta);
+			world = have ? mat4_mul_p(world, local) : unpack_mat4(local);
 		}
 	}
 	store_world_rows(s, s_out[warp], world, live, p, lane, end);

@@ -1,6 +1,7 @@
 // Animation key sampling, skin bone matrices and the layout shuffles around host uploads/downloads.
 #pragma once
 #include "hgb_kernels.cuh"
+#include "hgb_atan2_exact.h"
 
 namespace hgb {
 
@@ -45,29 +46,38 @@ __device__ __forceinline__ float hermite1(float y0, float y1, float y2, float y3
 }
 
 // ToEuler(Mat3, RO_YXZ) foundation/matrix3.cpp:91-137,141-163 (euler_order_yxz: i=1 j=0 k=2; the odd and the left-handed negations
-// cancel). atan2 is the double libm function in the reference (float arguments promoted, result narrowed); CUDA's double atan2
-// (<= 2 ulp) narrows to the same float except when the double result sits within ~1e-16 relative of a float rounding boundary —
-// covered by the 1e-5 matrix tolerance.
+// cancel). atan2 is the DOUBLE libm function in the reference (float arguments promoted, result narrowed to float). CUDA's double atan2
+// (<= 2 ulp) narrows to the same float except when it sits within a few double-ulps of a float rounding boundary; those evaluations
+// (~3e-8 of all) are redone in double-double arithmetic and rounded the way a correctly rounded libm rounds (hgb_atan2_exact.h,
+// checked on the host against the reference's libm by oracle/exhaustive_atan2.cpp), so the Euler angles are bit-identical.
+__device__ __noinline__ float atan2f_ref_slow(float y, float x) {
+	const hgb_exact::dd r = hgb_exact::atan2_dd(double(y), double(x));
+	return __double2float_rn(r.hi);
+}
+__device__ __forceinline__ float atan2f_ref(float y, float x) {
+	const double lib = atan2(double(y), double(x));
+	if (hgb_exact::near_float_midpoint(lib) && x != 0.f && y != 0.f && fabsf(x) <= 3.402823466e+38f && fabsf(y) <= 3.402823466e+38f)
+		return atan2f_ref_slow(y, x);
+	return __double2float_rn(lib);
+}
 __device__ __forceinline__ void mat3_to_euler_yxz(float m00, float m02, float m10, float m11, float m12, float m20, float m22, float &ex, float &ey, float &ez) {
 	const float s1 = -m12;
 	const float c1 = sqrtf(m11 * m11 + m10 * m10);
 	float a0, a2;
-	const float a1 = __double2float_rn(atan2(double(s1), double(c1)));
+	const float a1 = atan2f_ref(s1, c1);
 	if (c1 > 1.1920929e-07f) {
-		a0 = __double2float_rn(atan2(double(m02), double(m22)));
-		a2 = __double2float_rn(atan2(double(m10), double(m11)));
+		a0 = atan2f_ref(m02, m22);
+		a2 = atan2f_ref(m10, m11);
 	} else {
 		a0 = 0.F;
 		const float sign_s1 = s1 < 0.F ? -1.F : (s1 > 0.F ? 1.F : 0.F);
-		a2 = __double2float_rn(__dmul_rn(double(-sign_s1), atan2(double(-m20), double(m00))));
+		a2 = __double2float_rn(__dmul_rn(double(-sign_s1), double(atan2f_ref(-m20, m00)))); // float * double in the reference: exact, then narrowed
 	}
 	ex = a1, ey = a0, ez = a2;
 }
 
 // ToEuler(Normalize(q)) engine/scene.cpp:2172 : foundation/quaternion.cpp:57-60 (Normalize), :141-166 (ToMatrix3),
-// foundation/matrix3.cpp:91-137 (ToEuler, euler_order_yxz: i=1 j=0 k=2). atan2 is the double libm function in the reference
-// (float args promoted, result narrowed); CUDA's double atan2 (<= 2 ulp) narrows to the same float except when the double
-// result sits within ~1e-16 relative of a float rounding boundary — covered by the 1e-5 matrix tolerance.
+// foundation/matrix3.cpp:91-137 (ToEuler, euler_order_yxz: i=1 j=0 k=2), atan2 as above.
 __device__ __forceinline__ void quat_to_euler(float x, float y, float z, float w, float &ex, float &ey, float &ez) {
 	const float l = sqrtf(x * x + y * y + z * z + w * w);
 	if (l != 0.f) {

@@ -130,6 +130,41 @@ __device__ __forceinline__ void sincos_libm(float y, float &s_out, float &c_out)
 	c_out = tiny ? 1.0f : c;
 }
 
+// The three Euler angles of a node at once: ONE range test and one branch instead of three (|y| >= 120, inf and nan of any angle send
+// all three through the general path below), and the three fast evaluations form one straight-line block, so the polynomial
+// coefficients are fetched once. Results are those of three sincos_libm calls.
+__device__ __noinline__ void sincos3_libm_slow(float y0, float y1, float y2, float *sc6) {
+	sincos_libm(y0, sc6[0], sc6[1]);
+	sincos_libm(y1, sc6[2], sc6[3]);
+	sincos_libm(y2, sc6[4], sc6[5]);
+}
+__device__ __forceinline__ void sincos_fast(float y, float &s_out, float &c_out) { // |y| < 120 (sincos_libm without the range test)
+	const double x = double(y);
+	const double r = __dmul_rn(x, c_sc[8]);
+	const int n = (__double2int_rz(r) + 0x800000) >> 24;
+	const double xr = fma(-double(n), c_sc[9], x);
+	const double x2 = __dmul_rn(xr, xr);
+	const float sp = sc_sin_poly(xr, x2), cp = sc_cos_poly(x2);
+	float s = (n & 1) ? cp : sp, c = (n & 1) ? sp : cp;
+	s = (n & 2) ? -s : s;
+	c = ((n + 1) & 2) ? -c : c;
+	const bool tiny = abstop12(y) < 0x398u; // |y| < 2^-12
+	s_out = tiny ? y : s;
+	c_out = tiny ? 1.0f : c;
+}
+__device__ __forceinline__ void sincos3_libm(float y0, float y1, float y2, float &s0, float &c0, float &s1, float &c1, float &s2, float &c2) {
+	const uint32_t big = max(max(__float_as_uint(y0) & 0x7fffffffu, __float_as_uint(y1) & 0x7fffffffu), __float_as_uint(y2) & 0x7fffffffu);
+	if (big >= 0x42f00000u) { // 120.0f
+		float sc[6];
+		sincos3_libm_slow(y0, y1, y2, sc);
+		s0 = sc[0], c0 = sc[1], s1 = sc[2], c1 = sc[3], s2 = sc[4], c2 = sc[5];
+		return;
+	}
+	sincos_fast(y0, s0, c0);
+	sincos_fast(y1, s1, c1);
+	sincos_fast(y2, s2, c2);
+}
+
 // ---- TransformationMat4(pos, euler, scale) ------------------------------------------------------------------------
 // foundation/matrix4.cpp:176-183 -> RotationMat3(e, RO_YXZ) foundation/matrix3.cpp:180-260. For euler_order_yxz the unpacked
 // axes are i=1 j=0 k=2 (odd, no repeat); the left-handed and the odd negations cancel exactly, leaving
@@ -180,6 +215,58 @@ __device__ __forceinline__ Mat4 mat4_mul(const Mat4 &a, const Mat4 &b) {
 		o.m[r][2] = p2 + q2 + t2;
 		o.m[r][3] = p3 + q3 + t3 + a.m[r][3];
 	}
+	return o;
+}
+
+// ---- row-pair form (level kernels) ------------------------------------------------------------------------------------------------
+// The same two functions with the LOCAL matrix kept as the register pairs mul.f32x2 consumes — a[i] = (m[i][0], m[i][1]),
+// b[i] = (m[i][2], m[i][3]) — so that no pair has to be assembled from scalars of two other pairs (profiles r02a: a third of the
+// packed products' gain was going into MOVs). Same factors, same roundings, same sums as the scalar forms above.
+struct Mat4p {
+	f32x2_t a[3], b[3];
+};
+__device__ __forceinline__ Mat4p transformation_mat4p(float px, float py, float pz, float ex, float ey, float ez, float sx, float sy, float sz) {
+	float s0, c0, s1, c1, s2, c2;
+	sincos3_libm(ey, ex, ez, s0, c0, s1, c1, s2, c2);
+	const f32x2_t s2c2 = pk2(s2, c2), sxy = pk2(sx, sy);
+	const f32x2_t s0x = mul2(pk2(s0, s0), s2c2); // (s0s2, s0c2)
+	const f32x2_t c0x = mul2(pk2(c0, c0), s2c2); // (c0s2, c0c2)
+	float s0s2, s0c2, c0s2, c0c2, a00, a01, a20, a21, r02, r22;
+	upk2(s0x, s0s2, s0c2);
+	upk2(c0x, c0s2, c0c2);
+	upk2(mul2(pk2(s1, s1), s0x), a00, a01);
+	upk2(mul2(pk2(s1, s1), c0x), a20, a21);
+	upk2(mul2(pk2(c1, c1), pk2(s0, c0)), r02, r22);
+	Mat4p o;
+	o.a[0] = mul2(pk2(a00 + c0c2, a01 - c0s2), sxy);
+	o.a[1] = mul2(mul2(pk2(c1, c1), s2c2), sxy);
+	o.a[2] = mul2(pk2(a20 - s0c2, a21 + s0s2), sxy);
+	o.b[0] = pk2(r02 * sz, px);
+	o.b[1] = pk2(-s1 * sz, py);
+	o.b[2] = pk2(r22 * sz, pz);
+	return o;
+}
+__device__ __forceinline__ Mat4 mat4_mul_p(const Mat4 &a, const Mat4p &b) {
+	Mat4 o;
+#pragma unroll
+	for (int r = 0; r < 3; ++r) {
+		const f32x2_t a0 = pk2(a.m[r][0], a.m[r][0]), a1 = pk2(a.m[r][1], a.m[r][1]), a2 = pk2(a.m[r][2], a.m[r][2]);
+		float p0, p1, p2, p3, q0, q1, q2, q3, t0, t1, t2, t3;
+		upk2(mul2(a0, b.a[0]), p0, p1), upk2(mul2(a0, b.b[0]), p2, p3);
+		upk2(mul2(a1, b.a[1]), q0, q1), upk2(mul2(a1, b.b[1]), q2, q3);
+		upk2(mul2(a2, b.a[2]), t0, t1), upk2(mul2(a2, b.b[2]), t2, t3);
+		o.m[r][0] = p0 + q0 + t0;
+		o.m[r][1] = p1 + q1 + t1;
+		o.m[r][2] = p2 + q2 + t2;
+		o.m[r][3] = p3 + q3 + t3 + a.m[r][3];
+	}
+	return o;
+}
+__device__ __forceinline__ Mat4 unpack_mat4(const Mat4p &p) {
+	Mat4 o;
+#pragma unroll
+	for (int r = 0; r < 3; ++r)
+		upk2(p.a[r], o.m[r][0], o.m[r][1]), upk2(p.b[r], o.m[r][2], o.m[r][3]);
 	return o;
 }
 
@@ -255,7 +342,7 @@ __device__ __forceinline__ bool survives_frustum_x(const float4 *__restrict__ pl
 	const f32x2_t cex = pk2(bb.mn[0] + bb.mx[0], bb.mx[0] - bb.mn[0]);
 	const f32x2_t cey = pk2(bb.mn[1] + bb.mx[1], bb.mx[1] - bb.mn[1]);
 	const f32x2_t cez = pk2(bb.mn[2] + bb.mx[2], bb.mx[2] - bb.mn[2]);
-	bool inside = true;
+	bool outside = false; // accumulated in the compare itself (FSETP ... OR): no early out, no select chain
 #pragma unroll
 	for (int n = 0; n < 6; ++n) {
 		const float4 a = planes2[2 * n], b = planes2[2 * n + 1];
@@ -265,9 +352,9 @@ __device__ __forceinline__ bool survives_frustum_x(const float4 *__restrict__ pl
 		upk2(mul2(pk2(b.x, b.y), cez), dz, rz);
 		const float d = dx + dy + dz;
 		const float r = rx + ry + rz;
-		inside = inside && !(d - r > b.z);
+		outside = outside | (d - r > b.z);
 	}
-	return inside;
+	return !outside;
 }
 
 } // namespace hgb
