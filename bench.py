@@ -220,7 +220,7 @@ def main():
     fs, desc = workload(args.workload, rank, args.scale)
     n_nodes = fs.n
     ctx = harfang3d_b200.Context(local_rank, row_store=args.row_store, lookahead=args.lookahead, tma_level=args.tma_level, top_walk=args.top_walk, overlap_sampler=args.overlap, slice_nodes=args.slice_nodes,
-                                  async_post=None if args.async_post is None else bool(args.async_post))
+                                  async_post=(False if (world > 1 and args.exchange == "nccl") else None) if args.async_post is None else bool(args.async_post))  # the NCCL A/B reads the lists on the caller's stream: no asynchronous tail there
     t = hostmirror.upload(ctx, fs)
     n_entries = len(t["ent0_mtx_slot"]) + len(t["ent1_mtx_slot"])
     clocks = hostmirror.PlayClocks(fs)

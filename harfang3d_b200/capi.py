@@ -120,9 +120,8 @@ class Context:
         """row_store=True: world rows are stored per thread (3 x 16 B at a 48-byte stride) instead of through the shared-memory
         transpose — an A/B switch for profiling (hgb_options.reserved[0])"""
         self._L = lib()
-        if async_post is None:
-            async_post = os.environ.get("HGB_ASYNC_POST", "0") == "1"  # test switch: run any script with the asynchronous frame tail
-        opt = (C.c_int * 8)(1 if use_graph else 0, 1 if row_store else 0, lookahead, 1 if tma_level else 0, 1 if async_post else 0, top_walk, 1 if overlap_sampler else 0, slice_nodes)  # lookahead: 0 default, -1 off, n positions
+        # async_post: None = the library default (on; HGB_ASYNC_POST=0/1 in the environment overrides), True / False = forced
+        opt = (C.c_int * 8)(1 if use_graph else 0, 1 if row_store else 0, lookahead, 1 if tma_level else 0, (0 if async_post is None else (1 if async_post else -1)), top_walk, 1 if overlap_sampler else 0, slice_nodes)  # lookahead: 0 default, -1 off, n positions
         self._h = self._L.hgb_create(device, C.cast(opt, C.c_void_p))
         if not self._h:
             raise HgbError(self._L.hgb_last_error().decode())

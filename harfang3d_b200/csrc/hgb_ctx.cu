@@ -7,6 +7,7 @@
 #include "hgb_kernels_peer.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -103,7 +104,9 @@ struct EntryTable {
 	std::vector<uint32_t> mtx_slot, bounds_idx;
 	std::vector<uint8_t> flags;
 	std::vector<uint16_t> view;
-	DBuf mtx_pos, meta, view_d, vis; // per entry (entry order)
+	DBuf mtx_pos, meta, view_d;      // per entry (entry order)
+	DBuf vis[2];                     // per entry visibility byte, one buffer per world-buffer parity: the tail of frame N (compaction,
+	                                 // gather) may still read its bytes while the level kernels of frame N + 1 write theirs
 	DBuf out[kMaxViews];             // surviving indices per view
 	DBuf keys[kMaxViews];            // sort keys of the survivors (hgb_sort_keys)
 	DBuf counts;                     // kMaxViews uint32
@@ -149,6 +152,7 @@ struct hgb_ctx {
 	bool transpose_store = true;
 	bool tma_level = false;   // A/B switch: persistent TMA-staged level kernel instead of one thread per node with LDG rows (measured slower: r01c)
 	uint64_t top_budget = 2500000; // k_update_top covers the leading levels whose recomputed work (sum of nodes x depth) stays below this; 0 = one launch per level
+	uint32_t level_block = 256;    // threads per CTA of the level kernel (HGB_LEVEL_BLOCK=128: smaller CTAs recycle their slots sooner; A/B)
 	int level_minb = 6;            // resident CTAs per SM the level kernel's registers are held to (HGB_LEVEL_MINB=5: 48 registers; A/B)
 	bool overlap_sampler = false; // opt-in: sample tracks by target level on a second stream, overlapped with the level kernels (measured slower: r01c)
 	cudaStream_t stream2 = nullptr;
@@ -157,7 +161,6 @@ struct hgb_ctx {
 	uint32_t slice_nodes = 0;          // >0: with the overlapped sampler, big levels are cut into slices of this many positions (multiple of 256)
 	uint32_t persistent_ctas = 148 * 6; // resident CTAs of the device for the persistent level kernel
 	uint32_t lookahead = 0; // positions (see SceneDev::lookahead)
-	bool la_parents = true;
 	int cur = 0; // world[cur] = current frame
 	bool preset_pending = false, preset_dirty = false;
 	DBuf preset_pos, preset_mat;
@@ -170,10 +173,10 @@ struct hgb_ctx {
 	DBuf ent_off, pent, pos_view; // overflow CSR of nodes with several entries; per-position instance id
 
 	Views views{};          // planes -> view_planes (device)
-	DBuf view_planes;
+	DBuf view_planes, view_planes_x; // plain {x,y,z,-2w} and expanded {x,|x|,y,|y|} {z,|z|,-2w,0} forms
 	bool instance_mode = false;
 	uint32_t n_inst = 0;
-	DBuf inst_planes, inst_start, inst_rank;
+	DBuf inst_planes, inst_planes_x, inst_start, inst_rank;
 
 	// skins
 	uint32_t n_bones = 0;
@@ -221,27 +224,31 @@ struct hgb_ctx {
 	cudaGraphExec_t graph_exec[2][2] = {}; // [fused][world-buffer parity]
 	bool graph_valid[2][2] = {};
 	uint64_t graph_kernels[2][2] = {};
-	// Asynchronous tail (hgb_options.async_post): the frame is three graphs — pre (track sampling), levels, post (compaction + the peer
-	// gather) — and the post graph runs on stream2, so that it overlaps the NEXT frame's track sampling (which touches neither the
-	// visibility bytes nor the lists). The next frame's levels wait for it; every other entry point joins it first (join_post).
+	// Asynchronous tail (hgb_options.async_post): the frame is two graphs — main (track sampling + levels) on the context's stream and
+	// post (compaction + the peer gather) on stream2 — and the post graph of frame N overlaps the main graph of frame N + 1: the two
+	// touch different visibility buffers (EntryTable::vis[parity]). Frame N + 2 reuses the buffers of frame N and waits for its tail;
+	// every other entry point joins the pending tails first (join_post).
 	bool pdl_levels = true; // level d+1 launched with a programmatic dependency on level d (HGB_PDL=0 in the environment: plain, A/B)
 	bool pdl_first = true; // the first level is chained to the track sampler (HGB_PDL_FIRST=0: plain launch; A/B)
 	bool pdl_late_wait = true; // see SceneDev::late_wait (HGB_PDL_LATE=0: wait ahead of the sampled values, sampler -> first level chained instead; A/B)
-	bool async_post = false;
+	bool async_post = true;
 	cudaGraphExec_t phase_exec[3][2] = {}; // [phase][world-buffer parity]
 	bool phase_valid[3][2] = {};
 	uint64_t phase_kernels[3][2] = {};
-	cudaEvent_t ev_lvl_done = nullptr, ev_post_done = nullptr;
-	bool post_pending = false;
+	cudaEvent_t ev_lvl_done = nullptr, ev_post_done[2] = {};
+	bool post_pending[2] = {};
 };
 
 // the asynchronous tail of the last frame must be over before anything else touches the context's stream or tables
 static void join_post(hgb_ctx *c) {
-	if (c && c->post_pending) {
-		cudaSetDevice(c->device);
-		cudaStreamWaitEvent(c->stream, c->ev_post_done, 0);
-		c->post_pending = false;
-	}
+	if (!c)
+		return;
+	for (int par = 0; par < 2; ++par)
+		if (c->post_pending[par]) {
+			cudaSetDevice(c->device);
+			cudaStreamWaitEvent(c->stream, c->ev_post_done[par], 0);
+			c->post_pending[par] = false;
+		}
 }
 
 // bracket one kernel launch with events when profiling (never during graph capture: profiled frames use plain launches)
@@ -335,14 +342,17 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		c->top_budget = opt->top_walk < 0 ? 0u : uint64_t(opt->top_walk); // A/B switch: -1 = one launch per level, n = budget
 	if (const char *e_top = getenv("HGB_TOP_BUDGET"))
 		c->top_budget = strtoull(e_top, nullptr, 10);
-	if (const char *e_lap = getenv("HGB_LA_PARENTS"))
-		c->la_parents = e_lap[0] != '0';
+	if (const char *e_blk = getenv("HGB_LEVEL_BLOCK"))
+		c->level_block = atoi(e_blk) == 128 ? 128u : (atoi(e_blk) == 64 ? 64u : 256u);
 	if (const char *e_minb = getenv("HGB_LEVEL_MINB"))
 		c->level_minb = atoi(e_minb) == 5 ? 5 : 6;
 	c->overlap_sampler = opt ? opt->overlap_sampler != 0 : false;
 	if (opt && opt->slice_nodes > 0)
 		c->slice_nodes = (uint32_t(opt->slice_nodes) + 255u) & ~255u;
-	c->async_post = opt ? opt->async_post != 0 : false;
+	if (opt && opt->async_post != 0)
+		c->async_post = opt->async_post > 0; // 0 = default (on), 1 = on, -1 = off
+	if (const char *e_ap = getenv("HGB_ASYNC_POST"))
+		c->async_post = e_ap[0] != '0';
 	if (const char *e_pdl = getenv("HGB_PDL"))
 		c->pdl_levels = e_pdl[0] != '0';
 	if (const char *e_first = getenv("HGB_PDL_FIRST"))
@@ -357,8 +367,11 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		return nullptr;
 	}
 	c->stream = c->own_stream;
-	if (cudaEventCreateWithFlags(&c->ev_lvl_done, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&c->ev_post_done, cudaEventDisableTiming) != cudaSuccess ||
-		cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) {
+	int prio_lo = 0, prio_hi = 0;
+	cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+	if (cudaEventCreateWithFlags(&c->ev_lvl_done, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&c->ev_post_done[0], cudaEventDisableTiming) != cudaSuccess ||
+		cudaEventCreateWithFlags(&c->ev_post_done[1], cudaEventDisableTiming) != cudaSuccess ||
+		cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prio_hi) != cudaSuccess) { // the tail is short and somebody waits for it: ahead of the next frame's CTAs
 		fail("hgb_create: stream creation failed: %s", cudaGetErrorString(cudaGetLastError()));
 		delete c;
 		return nullptr;
@@ -369,12 +382,13 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 			c->ev_chunk.push_back(e);
 	}
 	c->views.n_views = 0;
-	if (c->view_planes.reserve(kMaxViews * 96) != cudaSuccess) {
+	if (c->view_planes.reserve(kMaxViews * 96) != cudaSuccess || c->view_planes_x.reserve(kMaxViews * 192) != cudaSuccess) {
 		fail("hgb_create: out of device memory");
 		delete c;
 		return nullptr;
 	}
 	c->views.planes = c->view_planes.as<float4>();
+	c->views.planes_x = c->view_planes_x.as<float4>();
 	return c;
 }
 
@@ -398,13 +412,13 @@ void hgb_destroy(hgb_ctx *c) {
 			if (g)
 				cudaGraphExecDestroy(g);
 	DBuf *bufs[] = {&c->tiles, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
-		&c->pent, &c->pos_view, &c->inst_planes, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
+		&c->pent, &c->pos_view, &c->inst_planes, &c->inst_planes_x, &c->view_planes_x, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
 		&c->bone_out[1], &c->keys, &c->cursor, &c->tstate, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes, &c->key_rec,
 		&c->en_target_pos, &c->en_off, &c->en_tracks_d, &c->en_keys_d, &c->en_scratch, &c->obj_pos, &c->obj_meta, &c->obj_seg, &c->obounds, &c->mm_acc, &c->peer_out_list, &c->peer_rank_off, &c->peer_aux_out};
 	for (DBuf *b : bufs)
 		b->release();
 	for (auto &t : c->ent) {
-		DBuf *eb[] = {&t.mtx_pos, &t.meta, &t.view_d, &t.vis, &t.counts, &t.ticket, &t.status};
+		DBuf *eb[] = {&t.mtx_pos, &t.meta, &t.view_d, &t.vis[0], &t.vis[1], &t.counts, &t.ticket, &t.status};
 		for (DBuf *b : eb)
 			b->release();
 		for (auto &o : t.out)

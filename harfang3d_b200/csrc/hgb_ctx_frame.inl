@@ -7,16 +7,16 @@ static SceneDev scene_dev(hgb_ctx *c, bool with_preset) {
 	s.anim_val = c->anim_val.as<float4>();
 	s.transpose_store = c->transpose_store ? 1 : 0;
 	s.lookahead = c->lookahead;
-	s.la_parents = c->la_parents ? 1 : 0;
 	s.late_wait = c->pdl_late_wait ? 1 : 0;
 	s.world = c->world[c->cur].as<float>();
 	s.preset = with_preset ? c->preset.as<uint8_t>() : nullptr;
 	s.ent_off = c->ent_off.as<uint32_t>();
 	s.pent = c->pent.as<uint2>();
 	s.bounds6 = c->bounds.as<float>();
-	s.vis0 = c->ent[0].vis.as<uint8_t>();
-	s.vis1 = c->ent[1].vis.as<uint8_t>();
+	s.vis0 = c->ent[0].vis[c->cur].as<uint8_t>();
+	s.vis1 = c->ent[1].vis[c->cur].as<uint8_t>();
 	s.inst_planes = c->inst_planes.as<float4>();
+	s.inst_planes_x = c->inst_planes_x.as<float4>();
 	s.pos_view = c->pos_view.as<uint16_t>();
 	return s;
 }
@@ -64,7 +64,7 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 			continue;
 		for (int v = 0; v < n_views; ++v) {
 			CompactDev d{};
-			d.vis = t.vis.as<uint8_t>();
+			d.vis = t.vis[c->cur].as<uint8_t>();
 			d.n = t.n;
 			d.bit = uint32_t(v);
 			d.out = t.out[v].as<uint32_t>();
@@ -74,8 +74,10 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 			if (with_peer && k == 0 && v == 0) { // the visible list leaves for the gather destination from the kernel that produces it
 				if (t.n > c->peer.cap[c->peer.rank])
 					return fail("peer gather: %u display entries but a region of %u was declared", t.n, c->peer.cap[c->peer.rank]);
-				d.out2 = peer_half(c) + c->peer.list_off[c->peer.rank];
+				d.out2 = c->peer.inbox + c->peer.list_off[c->peer.rank];
 				d.add2 = c->peer.entry_base[c->peer.rank];
+				d.out2_half = uint32_t(c->peer.half_words);
+				d.out2_step = static_cast<const uint32_t *>(c->peer.mailbox) + 1;
 			}
 			prof_begin(c, HGB_K_COMPACT);
 			launch_after(c, chained, k_compact, dim3(t.n_tiles), dim3(kCompactThreads), d);
@@ -84,7 +86,7 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 		}
 		if (c->instance_mode && k == 0 && c->n_inst) {
 			prof_begin(c, HGB_K_SEGMENT_RANKS);
-			launch_after(c, chained, k_segment_ranks, grid_for(c->n_inst * 32), dim3(256), t.vis.as<uint8_t>(), 0u, c->inst_start.as<uint32_t>(), c->n_inst,
+			launch_after(c, chained, k_segment_ranks, grid_for(c->n_inst * 32), dim3(256), t.vis[c->cur].as<uint8_t>(), 0u, c->inst_start.as<uint32_t>(), c->n_inst,
 				t.status.as<uint32_t>(), c->inst_rank.as<uint32_t>());
 			prof_end(c);
 			++*n_k;
@@ -97,13 +99,13 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 }
 
 template <int MINB> static void launch_level_v(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t b, uint32_t e, bool pdl) {
-	const dim3 g = grid_for(e - b);
+	const dim3 blk(c->level_block), g = grid_for(e - b, c->level_block);
 	if (!do_fused)
-		launch_after(c, pdl, k_update_level<false, false, MINB>, g, dim3(256), s, c->views, b, e);
+		launch_after(c, pdl, k_update_level<false, false, MINB>, g, blk, s, c->views, b, e);
 	else if (c->instance_mode)
-		launch_after(c, pdl, k_update_level<true, true, MINB>, g, dim3(256), s, c->views, b, e);
+		launch_after(c, pdl, k_update_level<true, true, MINB>, g, blk, s, c->views, b, e);
 	else
-		launch_after(c, pdl, k_update_level<true, false, MINB>, g, dim3(256), s, c->views, b, e);
+		launch_after(c, pdl, k_update_level<true, false, MINB>, g, blk, s, c->views, b, e);
 }
 
 static void launch_level(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t b, uint32_t e, bool pdl = false) {
@@ -161,10 +163,14 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	const SceneDev s = scene_dev(c, with_preset);
 	const bool do_fused = fused && (c->ent[0].n || c->ent[1].n);
 	const size_t n_levels = c->level_off.size() - 1;
-	if (phases == kPhasePost)
-		return do_fused ? enqueue_compaction(c, n_k, true) : 0;
-	if (c->peer.on && do_fused && (phases & kPhasePre))
+	// a rank without display entries still takes part in the gather (it publishes an empty list)
+	const bool do_post = do_fused || (fused && c->peer.on);
+	// The gather's step is counted by the first kernel of whichever graph holds the frame's tail: all peer kernels of a frame then sit
+	// in ONE stream-ordered sequence (the whole frame, or the tail on stream2), and none of them can see another frame's step.
+	if (c->peer.on && fused && (phases & kPhasePost))
 		peer_enqueue_begin(c, n_k);
+	if (phases == kPhasePost)
+		return do_post ? enqueue_compaction(c, n_k, true) : 0;
 	const bool has_anim = c->n_tracks && c->n_play;
 	AnimDev a{};
 	if (has_anim) {
@@ -293,13 +299,13 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	if (overlap)
 		CK(cudaStreamWaitEvent(c->stream, c->ev_chunk[1], 0));
 	CK(cudaGetLastError());
-	if (do_fused && (phases & kPhasePost))
+	if (do_post && (phases & kPhasePost))
 		return enqueue_compaction(c, n_k, true, chain_post && prev_signals);
 	return 0;
 }
 
-// asynchronous tail: the frame as three graphs; pre and levels on the context's stream, post on stream2 (see hgb_ctx::async_post)
-static int launch_phase_graph(hgb_ctx *c, int phase_idx, cudaStream_t on) {
+// asynchronous tail: the frame as two graphs; main (pre + levels) on the context's stream, post on stream2 (see hgb_ctx::async_post)
+static int launch_phase_graph(hgb_ctx *c, int phase_idx, int phase_mask, cudaStream_t on) {
 	const int par = c->cur;
 	if (!c->phase_valid[phase_idx][par]) {
 		if (c->phase_exec[phase_idx][par]) {
@@ -313,7 +319,7 @@ static int launch_phase_graph(hgb_ctx *c, int phase_idx, cudaStream_t on) {
 		cudaError_t e = cudaStreamBeginCapture(on, cudaStreamCaptureModeThreadLocal);
 		int rc = 1;
 		if (e == cudaSuccess) {
-			rc = enqueue_frame_kernels(c, true, false, &k, 1 << phase_idx);
+			rc = enqueue_frame_kernels(c, true, false, &k, phase_mask);
 			e = cudaStreamEndCapture(on, &g);
 		}
 		c->stream = keep;
@@ -333,18 +339,19 @@ static int launch_phase_graph(hgb_ctx *c, int phase_idx, cudaStream_t on) {
 }
 
 static int launch_frame_async(hgb_ctx *c) {
-	if (launch_phase_graph(c, 0, c->stream)) // track sampling: independent of the previous frame's tail
-		return 1;
-	if (c->post_pending) // the levels overwrite the visibility bytes the previous tail compacts
-		CK(cudaStreamWaitEvent(c->stream, c->ev_post_done, 0));
-	if (launch_phase_graph(c, 1, c->stream))
+	const int par = c->cur;
+	if (c->post_pending[par]) { // the tail of the frame before last compacts the visibility bytes this frame's levels are about to overwrite
+		CK(cudaStreamWaitEvent(c->stream, c->ev_post_done[par], 0));
+		c->post_pending[par] = false;
+	}
+	if (launch_phase_graph(c, 0, kPhasePre | kPhaseLevels, c->stream))
 		return 1;
 	CK(cudaEventRecord(c->ev_lvl_done, c->stream));
 	CK(cudaStreamWaitEvent(c->stream2, c->ev_lvl_done, 0));
-	if (launch_phase_graph(c, 2, c->stream2))
+	if (launch_phase_graph(c, 2, kPhasePost, c->stream2)) // stream2 is in order: tails never overtake each other
 		return 1;
-	CK(cudaEventRecord(c->ev_post_done, c->stream2));
-	c->post_pending = true;
+	CK(cudaEventRecord(c->ev_post_done[par], c->stream2));
+	c->post_pending[par] = true;
 	return 0;
 }
 
@@ -416,7 +423,7 @@ int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cul
 	if (!c->en_target_slot_h.empty() && c->n_play)
 		c->en_state_dirty = true;
 	const bool fused = fused_cull != 0;
-	if (c->async_post && c->use_graph && fused && !with_preset && !c->prof.on && (c->ent[0].n || c->ent[1].n))
+	if (c->async_post && c->use_graph && fused && !with_preset && !c->prof.on && (c->ent[0].n || c->ent[1].n || c->peer.on))
 		return launch_frame_async(c);
 	join_post(c);
 	if (!c->use_graph || with_preset || c->prof.on) {
@@ -450,7 +457,7 @@ int hgb_cull(hgb_ctx *c) {
 		d.world = c->world[c->cur].as<float>();
 		d.bounds6 = c->bounds.as<float>();
 		d.inst_planes = c->inst_planes.as<float4>();
-		d.vis = t.vis.as<uint8_t>();
+		d.vis = t.vis[c->cur].as<uint8_t>();
 		d.n = t.n;
 		prof_begin(c, HGB_K_CULL_FLAGS);
 		if (c->instance_mode)

@@ -1,6 +1,5 @@
 // Host side of the peer-memory result gather (hgb_kernels_peer.cuh). Included by hgb_ctx.cu.
 
-static size_t peer_half_words(const Peer &p) { return p.half_words; }
 
 extern "C" {
 
@@ -30,7 +29,7 @@ int hgb_peer_init(hgb_ctx *c, uint32_t rank, uint32_t world, uint32_t dst, const
 		p.aux_off[r] = uint32_t(w);
 		w += (size_t(p.aux_n[r]) + 31) & ~size_t(31);
 	}
-	if (base >= (1ull << 32) || w >= (1ull << 31))
+	if (base >= (1ull << 32) || w >= (1ull << 30))
 		return fail("hgb_peer_init: the gathered entry table exceeds 32-bit indices");
 	p.half_words = w;
 	p.aux_base[0] = 0;
@@ -129,8 +128,13 @@ int hgb_peer_result(hgb_ctx *c, uint32_t *out_rank_off, uint32_t *out_idx, uint3
 		return fail("hgb_peer_result: only the gather destination holds the result");
 	CK(cudaSetDevice(c->device));
 	std::vector<uint32_t> off(p.world + 1);
+	uint32_t mw[4] = {};
+	CK(cudaMemcpyAsync(mw, p.mailbox, 16, cudaMemcpyDeviceToHost, c->stream));
 	CK(cudaMemcpyAsync(off.data(), c->peer_rank_off.p, off.size() * 4, cudaMemcpyDeviceToHost, c->stream));
 	CK(cudaStreamSynchronize(c->stream));
+	if (mw[2] != 0)
+		return fail("hgb_peer_result: the gather failed at step %u (error word %u: %s); the result on the device is not this step's", mw[1], mw[2],
+			mw[2] == 1 ? "a sender timed out waiting for an acknowledgement" : "the destination timed out waiting for a rank");
 	if (out_rank_off)
 		memcpy(out_rank_off, off.data(), off.size() * 4);
 	if (out_idx) {
@@ -161,30 +165,31 @@ static void peer_release(hgb_ctx *c) {
 }
 
 // ---- per frame ----
-static uint32_t *peer_half(hgb_ctx *c) { return c->peer.inbox + size_t(c->cur) * peer_half_words(c->peer); }
-
 static void peer_enqueue_begin(hgb_ctx *c, uint64_t *n_k) {
 	k_peer_begin<<<1, 1, 0, c->stream>>>(static_cast<uint32_t *>(c->peer.mailbox));
 	++*n_k;
 }
 
-// after the compaction of the frame: aux (per-instance ranks), count + flag; on the destination: wait, concatenate, acknowledge
+// after the compaction of the frame: aux (per-instance ranks), count + flag; on the destination: wait, concatenate, acknowledge.
+// The inbox half is chosen on the device from the step counter (k_peer_begin), never from host state.
 static int peer_enqueue_end(hgb_ctx *c, uint64_t *n_k) {
 	Peer &p = c->peer;
-	uint32_t *half = peer_half(c);
 	uint32_t *mail = static_cast<uint32_t *>(p.mailbox);
+	const uint32_t half_words = uint32_t(p.half_words);
 	if (p.aux_n[p.rank]) {
 		if (!c->instance_mode || p.aux_n[p.rank] != c->n_inst)
 			return fail("peer gather: %u aux words declared but the context has %u instances", p.aux_n[p.rank], c->instance_mode ? c->n_inst : 0);
-		k_peer_copy<<<std::min<uint32_t>((p.aux_n[p.rank] + 255) / 256, 148u), 256, 0, c->stream>>>(half + p.aux_off[p.rank], c->inst_rank.as<uint32_t>(), p.aux_n[p.rank]);
+		k_peer_copy<<<std::min<uint32_t>((p.aux_n[p.rank] + 255) / 256, 148u), 256, 0, c->stream>>>(p.inbox, half_words, p.aux_off[p.rank], c->inst_rank.as<uint32_t>(),
+			p.aux_n[p.rank], mail);
 		++*n_k;
 	}
-	k_peer_publish<<<1, 1, 0, c->stream>>>(half + size_t(p.rank) * kPeerHdrWords, c->ent[0].counts.as<uint32_t>(), mail);
+	k_peer_publish<<<1, 1, 0, c->stream>>>(p.inbox, half_words, p.rank * kPeerHdrWords, c->ent[0].n ? c->ent[0].counts.as<uint32_t>() : nullptr, mail);
 	++*n_k;
 	if (p.rank == p.dst) {
-		k_peer_wait<<<1, 32, 0, c->stream>>>(half, p.world, mail);
+		k_peer_wait<<<1, 32, 0, c->stream>>>(p.inbox, half_words, p.world, mail);
 		PeerConcat pc{};
-		pc.inbox = half;
+		pc.inbox = p.inbox;
+		pc.half_words = half_words;
 		pc.world = p.world;
 		for (uint32_t r = 0; r < p.world; ++r)
 			pc.list_off[r] = p.list_off[r], pc.aux_off[r] = p.aux_off[r], pc.aux_n[r] = p.aux_n[r];
@@ -193,6 +198,7 @@ static int peer_enqueue_end(hgb_ctx *c, uint64_t *n_k) {
 		pc.out_list = c->peer_out_list.as<uint32_t>();
 		pc.rank_off = c->peer_rank_off.as<uint32_t>();
 		pc.aux_out = c->peer_aux_out.as<uint32_t>();
+		pc.mailbox = mail;
 		k_peer_concat<<<148 * 4, 256, 0, c->stream>>>(pc);
 		PeerAck a{};
 		a.world = p.world;

@@ -28,6 +28,16 @@ static void interleave_bounds(const float *in, size_t n, std::vector<float> &out
 		}
 }
 
+// conditioned planes -> the expanded form of survives_frustum_x: {x, |x|, y, |y|} {z, |z|, -2w, 0}
+static void expand_planes(const float *cond, uint32_t n_planes, float *out) {
+	for (uint32_t i = 0; i < n_planes; ++i) {
+		const float *p = cond + i * 4;
+		float *o = out + i * 8;
+		o[0] = p[0], o[1] = fabsf(p[0]), o[2] = p[1], o[3] = fabsf(p[1]);
+		o[4] = p[2], o[5] = fabsf(p[2]), o[6] = p[3], o[7] = 0.f;
+	}
+}
+
 static inline dim3 grid_for(uint32_t n, uint32_t block = 256) { return dim3((n + block - 1) / block); }
 
 static int prepare_tables(hgb_ctx *c);
@@ -151,6 +161,21 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 		++c->launches;
 		CK(cudaStreamSynchronize(c->stream));
 	}
+	// ... and both world buffers: transform_worlds / previous_transform_worlds are indexed by slot in the reference and survive hierarchy
+	// edits (scene.cpp:280-304), so the frame after an edit still sees the right previous-frame matrices (motion vectors, bone twins).
+	// Nothing to do when old and new order are both the slot order and the buffers do not grow.
+	DBuf carry_w[2];
+	const bool grow = c->world[0].cap < std::max<size_t>(n, 1) * 48 || c->world[1].cap < std::max<size_t>(n, 1) * 48;
+	const bool carry_worlds = carry && c->world[0].p && c->world[1].p && !(c->identity && identity && !grow);
+	if (carry_worlds) {
+		for (int i = 0; i < 2; ++i) {
+			CK(carry_w[i].reserve(size_t(keep) * 48));
+			k_gather_worlds<<<grid_for(keep * 3), 256, 0, c->stream>>>(c->world[i].as<float4>(), c->identity ? nullptr : c->pos_of_slot_d.as<uint32_t>(), 0, keep,
+				carry_w[i].as<float4>());
+			++c->launches;
+		}
+		CK(cudaStreamSynchronize(c->stream));
+	}
 
 	const uint32_t n_tiles = (n + 31) / 32;
 	DBuf new_tiles, rows;
@@ -177,8 +202,18 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 		const size_t bytes = std::max<size_t>(n, 1) * 48;
 		if (c->world[i].cap < bytes) {
 			CK(c->world[i].reserve(bytes));
-			CK(cudaMemsetAsync(c->world[i].p, 0, c->world[i].cap, c->stream));
+			CK(cudaMemsetAsync(c->world[i].p, 0, c->world[i].cap, c->stream)); // new slots: value-initialised rows, like std::vector::resize
 		}
+		if (carry_worlds) {
+			k_scatter_worlds<<<grid_for(keep * 3), 256, 0, c->stream>>>(carry_w[i].as<float4>(), identity ? nullptr : c->pos_of_slot_d.as<uint32_t>(), keep,
+				c->world[i].as<float4>());
+			++c->launches;
+		}
+	}
+	if (carry_worlds) {
+		CK(cudaStreamSynchronize(c->stream));
+		carry_w[0].release();
+		carry_w[1].release();
 	}
 	CK(c->preset.reserve(std::max<size_t>(n, 4)));
 	CK(cudaMemsetAsync(c->preset.p, 0, c->preset.cap, c->stream));
@@ -598,7 +633,10 @@ int hgb_set_views(hgb_ctx *c, uint32_t n_views, const float *frustum24) {
 	if (n_views) { // pageable source: staged by the runtime before returning
 		float cond[kMaxViews * 24];
 		precondition_planes(frustum24, n_views * 6, cond);
+		float condx[kMaxViews * 48];
+		expand_planes(cond, n_views * 6, condx);
 		CK(cudaMemcpyAsync(c->view_planes.p, cond, size_t(n_views) * 96, cudaMemcpyHostToDevice, c->stream));
+		CK(cudaMemcpyAsync(c->view_planes_x.p, condx, size_t(n_views) * 192, cudaMemcpyHostToDevice, c->stream));
 	}
 	return 0;
 }
@@ -613,7 +651,9 @@ int hgb_set_instance_views(hgb_ctx *c, uint32_t n_inst, const float *frustum24, 
 	const bool shape_change = !c->instance_mode || c->n_inst != n_inst;
 	std::vector<float> cond(size_t(n_inst) * 24);
 	precondition_planes(frustum24, n_inst * 6, cond.data());
-	if (upload(c, c->inst_planes, cond.data(), size_t(n_inst) * 96))
+	std::vector<float> condx(size_t(n_inst) * 48);
+	expand_planes(cond.data(), n_inst * 6, condx.data());
+	if (upload(c, c->inst_planes, cond.data(), size_t(n_inst) * 96) || upload(c, c->inst_planes_x, condx.data(), size_t(n_inst) * 192))
 		return 1;
 	if (inst_entry_start && upload(c, c->inst_start, inst_entry_start, size_t(n_inst + 1) * 4))
 		return 1;
@@ -669,8 +709,10 @@ static int prepare_tables(hgb_ctx *c) {
 			return 1;
 		t.n_tiles = (t.n + kCompactTile - 1) / kCompactTile;
 		const size_t vis_bytes = size_t(t.n_tiles + 1) * kCompactTile;
-		CK(t.vis.reserve(vis_bytes));
-		CK(cudaMemsetAsync(t.vis.p, 0, t.vis.cap, c->stream));
+		for (int par = 0; par < 2; ++par) {
+			CK(t.vis[par].reserve(vis_bytes));
+			CK(cudaMemsetAsync(t.vis[par].p, 0, t.vis[par].cap, c->stream));
+		}
 		const int n_out = c->instance_mode ? 1 : std::max(c->views.n_views, 1);
 		for (int v = 0; v < n_out; ++v)
 			CK(t.out[v].reserve(std::max<size_t>(t.n, 1) * 4));

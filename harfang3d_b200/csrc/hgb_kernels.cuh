@@ -35,8 +35,9 @@ constexpr uint32_t kEntKindTransparent = 1u << 31; // which of the two entry tab
 // View frusta live in device memory (6 float4 per view: Top,Bottom,Left,Right,Near,Far, foundation/frustum.h:14; w holds -2*w) so that a camera
 // move is a 96-byte copy and never invalidates the captured frame graph.
 struct Views {
-	const float4 *planes;
+	const float4 *planes;   // 6 float4 per view
 	int n_views;
+	const float4 *planes_x; // the same planes expanded for the packed test (survives_frustum_x): 12 float4 per view
 };
 
 struct SceneDev {
@@ -50,10 +51,10 @@ struct SceneDev {
 	const float *bounds6;       // MinMax table, 6 floats per (model, list)
 	uint8_t *vis0, *vis1;       // per entry table (opaque, transparent): bit v set -> survives view v
 	const float4 *inst_planes;  // per-instance frusta (6 float4 each) or null
+	const float4 *inst_planes_x; // ... expanded (12 float4 each)
 	const uint16_t *pos_view;   // per position: which instance frustum (only with inst_planes)
 	int transpose_store;        // 1: world rows leave the SM as 3 contiguous 512-byte warp stores (shared-memory transpose)
 	uint32_t lookahead;         // positions: a warp asks L2 for the tile (and its parents' rows) this far ahead of its own; 0 = off
-	int la_parents;             // 1: the look-ahead also covers the world rows of that tile's parents (HGB_LA_PARENTS=0: tiles only; A/B)
 	int late_wait;              // where griddepcontrol.wait sits: 0 ahead of the sampled values; 1 behind the local matrix (levels behind a level);
 	                            // 2 like 0 and dependents are released only behind it (the level chained to the track sampler)
 };
@@ -62,16 +63,17 @@ __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefe
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
 // visibility mask of one display entry against the shared views (shared memory) or the node's instance frustum
+// `planes_x`: expanded planes (2 float4 per plane) in shared memory
 template <bool PER_INSTANCE>
-__device__ __forceinline__ uint32_t entry_visibility(const SceneDev &s, const Mat4 &world, uint32_t meta, const float4 *s_planes, int n_views, uint32_t p) {
+__device__ __forceinline__ uint32_t entry_visibility(const SceneDev &s, const Mat4 &world, uint32_t meta, const float4 *planes_x, int n_views, uint32_t p) {
 	if (meta & kEntDisabled)
 		return 0;
 	const Aabb bb = minmax_transform(world, s.bounds6 + size_t(meta & 0xffffffu) * 6);
 	if (PER_INSTANCE)
-		return survives_frustum(s.inst_planes + size_t(s.pos_view[p]) * 6, bb) ? 1u : 0u;
-	uint32_t bits = 0;
-	for (int v = 0; v < n_views; ++v)
-		bits |= survives_frustum_x(s_planes + v * 12, bb) ? (1u << v) : 0u; // s_planes: expanded form, 2 float4 per plane
+		return survives_frustum_x(s.inst_planes_x + size_t(s.pos_view[p]) * 12, bb) ? 1u : 0u;
+	uint32_t bits = survives_frustum_x(planes_x, bb) ? 1u : 0u;
+	for (int v = 1; v < n_views; ++v)
+		bits |= survives_frustum_x(planes_x + v * 12, bb) ? (1u << v) : 0u;
 	return bits;
 }
 
@@ -143,13 +145,13 @@ struct MoreEntries {
 	const uint2 *pent;
 	const float *bounds6;
 	uint8_t *vis0, *vis1;
-	const float4 *inst_planes;
+	const float4 *inst_planes_x;
 	const uint16_t *pos_view;
 };
 template <bool PER_INSTANCE>
 __device__ __noinline__ void cull_more_entries(MoreEntries m, Mat4 world, const float4 *s_planes, int n_views, uint32_t p) {
 	SceneDev s{};
-	s.bounds6 = m.bounds6, s.inst_planes = m.inst_planes, s.pos_view = m.pos_view;
+	s.bounds6 = m.bounds6, s.inst_planes_x = m.inst_planes_x, s.pos_view = m.pos_view;
 	const uint32_t e0 = m.ent_off[p], e1 = m.ent_off[p + 1];
 	for (uint32_t k = e0; k < e1; ++k) {
 		const uint2 rec = m.pent[k];
@@ -162,7 +164,7 @@ __device__ __forceinline__ void cull_node_entries(const SceneDev &s, const Mat4 
 	const uint32_t bits = entry_visibility<PER_INSTANCE>(s, world, meta, s_planes, n_views, p);
 	((meta & kEntKindTransparent) ? s.vis1 : s.vis0)[eidx] = uint8_t(bits);
 	if (meta & kEntMore)
-		cull_more_entries<PER_INSTANCE>(MoreEntries{s.ent_off, s.pent, s.bounds6, s.vis0, s.vis1, s.inst_planes, s.pos_view}, world, s_planes, n_views, p);
+		cull_more_entries<PER_INSTANCE>(MoreEntries{s.ent_off, s.pent, s.bounds6, s.vis0, s.vis1, s.inst_planes_x, s.pos_view}, world, s_planes, n_views, p);
 }
 
 // ---- world-matrix propagation, one level per launch ---------------------------------------------------------------------
@@ -175,10 +177,12 @@ __device__ __forceinline__ void cull_node_entries(const SceneDev &s, const Mat4 
 // MINB = resident CTAs per SM the register allocation is held to (A/B: 6 -> 40 registers, 5 -> 48).
 template <bool FUSED, bool PER_INSTANCE, int MINB>
 __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views views, uint32_t begin, uint32_t end) {
-	__shared__ float4 s_planes[kMaxViews * 12];
 	__shared__ float4 s_out[8][96]; // per warp: 32 world matrices = 1536 B, for the transposed store
-	if (FUSED && !PER_INSTANCE) { // the shared view frusta: broadcast LDS.128s instead of global loads
-		stage_planes(s_planes, views);
+	__shared__ float4 s_planes[kMaxViews * 12];
+	if (FUSED && !PER_INSTANCE) { // the shared view frusta (host-expanded form): broadcast LDS.128s in the cull tail
+		if (threadIdx.x < 32u) // a real branch: the other warps spend two instructions here, not a predicated-off copy loop
+			for (uint32_t i = threadIdx.x; i < uint32_t(views.n_views) * 12u; i += 32u)
+				s_planes[i] = views.planes_x[i];
 		__syncthreads();
 	}
 	// Programmatic dependent launch: the next level's grid may become resident while this one drains — ahead of its own
@@ -194,16 +198,9 @@ __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views vi
 		return;
 	// Software prefetch into L2: CTAs are dispatched in position order, so the tile `lookahead` positions ahead belongs to a CTA that
 	// starts about one CTA lifetime from now. Its 12 rows are requested by 12 lanes here, which turns the first (and otherwise fully
-	// exposed) DRAM latency of that CTA into an L2 hit. Lanes 0..2 also start the load of that tile's first parent index: it is consumed
-	// at the very end of the kernel (prefetch of the parents' rows), by when it has long arrived.
-	const uint32_t pf = p - lane + s.lookahead;
-	const bool do_pf = s.lookahead != 0 && pf < end;
-	uint32_t par_f = kRoot;
-	if (do_pf && lane < kTileRows) {
-		prefetch_l2(s.tiles + tile_word(pf & ~31u, lane));
-		if (lane < 3 && s.la_parents)
-			par_f = __ldcg(s.tiles + tile_word(pf, kRowParent));
-	}
+	// exposed) DRAM latency of that CTA into an L2 hit.
+	if (s.lookahead != 0 && lane < kTileRows && p - lane + s.lookahead < end)
+		prefetch_l2(s.tiles + tile_word((p - lane + s.lookahead) & ~31u, lane));
 
 	Mat4 world;
 	uint32_t meta = 0, eidx = 0;
@@ -252,9 +249,6 @@ __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views vi
 
 	if (FUSED && live && (meta & kEntHas))
 		cull_node_entries<PER_INSTANCE>(s, world, meta, eidx, s_planes, views.n_views, p);
-
-	if (par_f != kRoot) // ... and the rows of the look-ahead tile's parents (siblings are adjacent: a few hundred contiguous bytes)
-		prefetch_l2(s.world + size_t(par_f) * 12 + lane * 32);
 }
 
 // ---- the top of the hierarchy in ONE launch ---------------------------------------------------------------------------------
@@ -270,10 +264,12 @@ constexpr int kMaxWalk = 12;
 
 template <bool FUSED, bool PER_INSTANCE>
 __global__ void __launch_bounds__(256) k_update_top(SceneDev s, Views views, uint32_t end) {
-	__shared__ float4 s_planes[kMaxViews * 12];
 	__shared__ float4 s_out[8][96];
+	__shared__ float4 s_planes[kMaxViews * 12];
 	if (FUSED && !PER_INSTANCE) {
-		stage_planes(s_planes, views);
+		if (threadIdx.x < 32u)
+			for (uint32_t i = threadIdx.x; i < uint32_t(views.n_views) * 12u; i += 32u)
+				s_planes[i] = views.planes_x[i];
 		__syncthreads();
 	}
 	// chained behind the track sampler (or plain): it reads sampled values throughout, so it waits first thing and releases its
@@ -376,6 +372,8 @@ struct CompactDev {
 	uint32_t *out;            // surviving entry indices, in order
 	uint32_t *out2;           // nullable: second copy, each index + add2 — this rank's region of the gather destination's inbox
 	uint32_t add2;            //   (peer memory over NVLink, hgb_kernels_peer.cuh): the result leaves the GPU from the kernel that produces it
+	uint32_t out2_half;       //   words between the two inbox halves; the half is the parity of *out2_step (the gather's step counter)
+	const uint32_t *out2_step;
 	uint32_t *count;          // total survivors
 	uint32_t *ticket;         // zeroed before launch
 	volatile uint32_t *status; // n_tiles words, zeroed before launch
@@ -481,10 +479,11 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact(CompactDev c) {
 	__syncthreads();
 	const uint32_t prefix = s_prefix;
 	if (c.out2) {
+		uint32_t *out2 = c.out2 + size_t(*c.out2_step & 1u) * c.out2_half;
 		for (uint32_t i = threadIdx.x; i < tile_total; i += kCompactThreads) {
 			const uint32_t e = s_list[i];
 			c.out[prefix + i] = e;
-			c.out2[prefix + i] = e + c.add2;
+			out2[prefix + i] = e + c.add2;
 		}
 	} else {
 		for (uint32_t i = threadIdx.x; i < tile_total; i += kCompactThreads)

@@ -742,7 +742,17 @@ __global__ void __launch_bounds__(256) k_gather_worlds(const float4 *__restrict_
 	if (i >= count * 3)
 		return;
 	const uint32_t s = i / 3, r = i - s * 3;
-	out[i] = world[size_t(pos_of_slot[first_slot + s]) * 3 + r];
+	out[i] = world[size_t(pos_of_slot ? pos_of_slot[first_slot + s] : first_slot + s) * 3 + r];
+}
+
+// the inverse: SLOT order -> POSITION order (hierarchy edits carry both world buffers over to the new order)
+__global__ void __launch_bounds__(256) k_scatter_worlds(const float4 *__restrict__ in, const uint32_t *__restrict__ pos_of_slot, uint32_t count,
+	float4 *__restrict__ world) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= count * 3)
+		return;
+	const uint32_t s = i / 3, r = i - s * 3;
+	world[size_t(pos_of_slot ? pos_of_slot[s] : s) * 3 + r] = in[i];
 }
 
 // SetNodeWorldMatrix overrides (engine/scene.cpp:768-786): write the matrix and mark the position as updated for this frame

@@ -49,9 +49,10 @@ typedef struct hgb_options {
 	int tma_level;     /* profiling A/B switch. 0 (default): level kernel with one thread per node, tile rows read with 128-byte LDGs (+ the
 	                      L2 look-ahead above); 1: persistent level kernel, node tiles staged with TMA bulk copies, world rows leave as
 	                      bulk stores (measured 3 % slower on the 16M-node batch, profiles/README.md r01c) */
-	int async_post;    /* 1: the tail of the frame — compaction of the visible lists and the peer gather — runs on a second stream and overlaps
-	                      the NEXT frame's track sampling; the next frame's level kernels and every other entry point wait for it, so
-	                      results and API semantics are unchanged. Default 0 */
+	int async_post;    /* the tail of the frame — compaction of the visible lists and the peer gather — runs as its own graph on a second stream
+	                      and overlaps the NEXT frame's track sampling and level kernels (visibility bytes are double-buffered by world-buffer
+	                      parity; frame N + 2 waits for the tail of frame N, every other entry point joins the pending tails first), so
+	                      results and API semantics are unchanged. 0 = default (on), 1 = on, -1 = off (one graph per frame) */
 	int top_walk;      /* the leading levels of the hierarchy go out as ONE launch (k_update_top: every node recomputes its ancestor chain, no
 	                      dependency between threads). 0 = default budget (levels are added while sum(nodes x depth) <= 2.5 M), -1 = off (one
 	                      launch per level), n = budget in node evaluations */
