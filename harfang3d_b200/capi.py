@@ -57,6 +57,7 @@ SIGNATURES = {
     "hgb_cull_list": (_i, [_p, _u32, _p, _p, _u32, _p, _p, _p, _p]),
     "hgb_bone_matrices": (_i, [_p, _i]),
     "hgb_sort_keys": (_i, [_p, _i, _u32, _p]),
+    "hgb_get_visible_ptr": (_i, [_p, _i, _u32, _p, _p]),
     "hgb_peer_init": (_i, [_p, _u32, _u32, _u32, _p, _p, _p, _p]),
     "hgb_peer_connect": (_i, [_p, _p, _p]),
     "hgb_peer_close": (_i, [_p]),

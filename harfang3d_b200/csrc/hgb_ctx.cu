@@ -38,6 +38,8 @@ static int fail(const char *fmt, ...) {
 
 namespace {
 
+constexpr uint32_t kClockRing = 8;
+
 // device buffer that only grows; contents are NOT preserved across a grow
 struct DBuf {
 	void *p = nullptr;
@@ -110,6 +112,7 @@ struct EntryTable {
 	DBuf out[kMaxViews];             // surviving indices per view
 	DBuf keys[kMaxViews];            // sort keys of the survivors (hgb_sort_keys)
 	DBuf counts;                     // kMaxViews uint32
+	uint32_t last_count[kMaxViews] = {}; // what the host last read: sizes the next one-round-trip fetch (fetch_visible)
 	DBuf ticket, status;             // compaction scratch (per view slices)
 	uint32_t n_tiles = 0;
 };
@@ -212,8 +215,11 @@ struct hgb_ctx {
 	uint32_t n_tracks = 0, n_play = 0;
 	std::vector<hgb_track> tracks_h;
 	std::vector<uint32_t> round_off; // tracks sorted so that tracks sharing a target lane fall in successive rounds
-	HBuf play_t_h;
-	std::vector<int64_t> play_t_v;
+	HBuf play_t_h; // kClockRing slots of n_play clocks
+	cudaEvent_t clock_ev[8] = {};
+	bool clock_used[8] = {};
+	uint32_t clock_slot = 0;
+	HBuf count_h, visible_h[2]; // pinned landing zones of hgb_get_visible / hgb_get_visible_ptr
 
 	HBuf staging;  // pinned host staging for uploads/downloads
 	DBuf staging_d; // device staging (slot-order data before scatter / after gather)
@@ -376,6 +382,8 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		delete c;
 		return nullptr;
 	}
+	for (cudaEvent_t &e : c->clock_ev)
+		cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
 	for (int i = 0; i < 96; ++i) { // fork/join/chunk events of the overlapped sampler, created up front (never during graph capture)
 		cudaEvent_t e = nullptr;
 		if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess)
@@ -430,6 +438,12 @@ void hgb_destroy(hgb_ctx *c) {
 		cudaEventDestroy(e);
 	c->staging.release();
 	c->play_t_h.release();
+	c->count_h.release();
+	c->visible_h[0].release();
+	c->visible_h[1].release();
+	for (cudaEvent_t e : c->clock_ev)
+		if (e)
+			cudaEventDestroy(e);
 	cudaEventDestroy(c->ev0);
 	cudaEventDestroy(c->ev1);
 	for (cudaEvent_t e : c->ev_chunk)

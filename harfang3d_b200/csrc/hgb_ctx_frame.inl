@@ -412,12 +412,17 @@ int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cul
 		c->preset_dirty = true;
 	}
 	if (c->n_play) {
-		// pageable source on purpose: the runtime stages small pageable copies before returning, so the vector can be reused next
-		// frame without waiting for this frame's copy
-		c->play_t_v.resize(c->n_play);
+		// the clocks go up from a ring of pinned slots (a plain DMA, nothing staged by the runtime); a slot is reused only once the copy
+		// that read it has run (its event: long done in practice, the ring is 8 frames deep)
+		const uint32_t slot = c->clock_slot++ % kClockRing;
+		if (c->clock_used[slot])
+			CK(cudaEventSynchronize(c->clock_ev[slot]));
+		int64_t *dst = c->play_t_h.as<int64_t>() + size_t(slot) * c->n_play;
 		for (uint32_t i = 0; i < c->n_play; ++i)
-			c->play_t_v[i] = i < n_play ? play_t[i] : INT64_MIN;
-		CK(cudaMemcpyAsync(c->play_t_d.p, c->play_t_v.data(), size_t(c->n_play) * 8, cudaMemcpyHostToDevice, c->stream));
+			dst[i] = i < n_play ? play_t[i] : INT64_MIN;
+		CK(cudaMemcpyAsync(c->play_t_d.p, dst, size_t(c->n_play) * 8, cudaMemcpyHostToDevice, c->stream));
+		CK(cudaEventRecord(c->clock_ev[slot], c->stream));
+		c->clock_used[slot] = true;
 	}
 
 	if (!c->en_target_slot_h.empty() && c->n_play)
@@ -765,19 +770,57 @@ int hgb_get_visible_count(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_cou
 	return 0;
 }
 
-int hgb_get_visible(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_idx, uint32_t capacity, uint32_t *out_count) {
-	uint32_t n = 0;
-	if (hgb_get_visible_count(c, kind, view, &n))
-		return 1;
+// The list comes down in ONE round trip: its length is only known on the device, so the copy is sized from the previous call's count
+// (+25 %, at least 4096 entries, at most the capacity) and goes out together with the 4-byte count, one stream synchronisation for
+// both; only when the list outgrew the guess does a second copy fetch the rest.
+static int fetch_visible(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_idx, uint32_t capacity, uint32_t *out_count) {
+	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews))
+		return fail("hgb_get_visible: bad kind/view");
+	EntryTable &t = c->ent[kind];
+	if (out_count)
+		*out_count = 0;
+	if (!t.n)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	CK(c->count_h.reserve(64));
+	uint32_t *cnt = c->count_h.as<uint32_t>();
+	const uint64_t want = uint64_t(t.last_count[view]) + t.last_count[view] / 4 + 4096;
+	const uint32_t guess = uint32_t(std::min<uint64_t>(std::min<uint64_t>(want, capacity), t.n));
+	CK(cudaMemcpyAsync(cnt, t.counts.as<uint32_t>() + view, 4, cudaMemcpyDeviceToHost, c->stream));
+	if (guess)
+		CK(cudaMemcpyAsync(out_idx, t.out[view].p, size_t(guess) * 4, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	const uint32_t n = *cnt;
 	if (out_count)
 		*out_count = n;
 	if (n > capacity)
 		return fail("hgb_get_visible: %u survivors but capacity %u", n, capacity);
-	if (n) {
-		CK(cudaMemcpyAsync(out_idx, c->ent[kind].out[view].p, size_t(n) * 4, cudaMemcpyDeviceToHost, c->stream));
+	if (n > guess) {
+		CK(cudaMemcpyAsync(out_idx + guess, t.out[view].as<uint32_t>() + guess, size_t(n - guess) * 4, cudaMemcpyDeviceToHost, c->stream));
 		CK(cudaStreamSynchronize(c->stream));
 	}
+	t.last_count[view] = n;
 	return 0;
+}
+
+int hgb_get_visible(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_idx, uint32_t capacity, uint32_t *out_count) {
+	if (!c)
+		return fail("null context");
+	join_post(c);
+	return fetch_visible(c, kind, view, out_idx, capacity, out_count);
+}
+
+int hgb_get_visible_ptr(hgb_ctx *c, int kind, uint32_t view, const uint32_t **out_idx, uint32_t *out_count) {
+	if (!c)
+		return fail("null context");
+	join_post(c);
+	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews))
+		return fail("hgb_get_visible_ptr: bad kind/view");
+	CK(cudaSetDevice(c->device));
+	HBuf &h = c->visible_h[kind];
+	CK(h.reserve(std::max<size_t>(c->ent[kind].n, 1) * 4)); // pinned, owned by the context: the copy is a plain DMA
+	*out_idx = h.as<uint32_t>();
+	return fetch_visible(c, kind, view, h.as<uint32_t>(), c->ent[kind].n, out_count);
 }
 
 int hgb_get_instance_offsets(hgb_ctx *c, uint32_t *out) {

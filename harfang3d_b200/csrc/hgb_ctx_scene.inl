@@ -527,7 +527,10 @@ int hgb_set_tracks(hgb_ctx *c, uint32_t n, const hgb_track *tracks, uint32_t n_p
 	}
 	c->records_dirty = true;
 	CK(c->play_t_d.reserve(std::max<size_t>(n_play, 1) * 8));
-	CK(c->play_t_h.reserve(std::max<size_t>(n_play, 1) * 8));
+	CK(cudaStreamSynchronize(c->stream)); // no clock copy in flight reads the ring that is about to be replaced
+	CK(c->play_t_h.reserve(std::max<size_t>(n_play, 1) * 8 * kClockRing));
+	for (bool &u : c->clock_used)
+		u = false;
 	CK(c->cursor.reserve(std::max<size_t>(n, 1) * 4));
 	CK(cudaMemsetAsync(c->cursor.p, 0, c->cursor.cap, c->stream));
 	CK(c->tstate.reserve(std::max<size_t>(n, 1) * 16));
@@ -840,9 +843,9 @@ static int prepare_tables(hgb_ctx *c) {
 		for (size_t i = 0; i < tr.size(); ++i)
 			c->trk_pos_h[i] = uint32_t(uniq[tr[i].out_slot] >> 2);
 	}
-	if (c->records_dirty && !tr.empty()) { // 128-byte interval records from the compact key pool (device side, once per key/track edit)
+	if (c->records_dirty && !tr.empty()) { // 64-byte interval records from the compact key pool (device side, once per key/track edit)
 		const size_t total = size_t(c->n_v3_keys) + c->n_q_keys;
-		CK(c->key_rec.reserve((total + 1) * 128));
+		CK(c->key_rec.reserve((total + 1) * 64));
 		k_build_key_records<<<grid_for(uint32_t(tr.size())), 256, 0, c->stream>>>(c->tracks_d.as<Track>(), uint32_t(tr.size()), c->keys.as<uint4>(), c->n_v3_keys,
 			c->key_rec.as<uint4>());
 		++c->launches;

@@ -179,11 +179,12 @@ template <bool FUSED, bool PER_INSTANCE, int MINB>
 __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views views, uint32_t begin, uint32_t end) {
 	__shared__ float4 s_out[8][96]; // per warp: 32 world matrices = 1536 B, for the transposed store
 	__shared__ float4 s_planes[kMaxViews * 12];
-	if (FUSED && !PER_INSTANCE) { // the shared view frusta (host-expanded form): broadcast LDS.128s in the cull tail
-		if (threadIdx.x < 32u) // a real branch: the other warps spend two instructions here, not a predicated-off copy loop
-			for (uint32_t i = threadIdx.x; i < uint32_t(views.n_views) * 12u; i += 32u)
-				s_planes[i] = views.planes_x[i];
-		__syncthreads();
+	// The shared view frusta (host-expanded form) are needed only by the cull tail: warp 0 starts an asynchronous copy into shared memory
+	// here (cp.async: no registers, nobody waits) and the CTA meets at a barrier just ahead of the tail, long after the copy has landed.
+	if (FUSED && !PER_INSTANCE && threadIdx.x < 32u) {
+		for (uint32_t i = threadIdx.x; i < uint32_t(views.n_views) * 12u; i += 32u)
+			asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(uint32_t(__cvta_generic_to_shared(s_planes + i))), "l"(views.planes_x + i) : "memory");
+		asm volatile("cp.async.commit_group;" ::: "memory");
 	}
 	// Programmatic dependent launch: the next level's grid may become resident while this one drains — ahead of its own
 	// griddepcontrol.wait it reads only edit-time rows and sampled values — which hides the launch latency, the first DRAM round trip and
@@ -247,6 +248,11 @@ __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views vi
 	// store the world rows (a preset row is rewritten with its own value)
 	store_world_rows(s, s_out[warp], world, live, p, lane, end);
 
+	if (FUSED && !PER_INSTANCE) { // the frusta have landed (warps that left above no longer count at the barrier)
+		if (threadIdx.x < 32u)
+			asm volatile("cp.async.wait_all;" ::: "memory");
+		__syncthreads();
+	}
 	if (FUSED && live && (meta & kEntHas))
 		cull_node_entries<PER_INSTANCE>(s, world, meta, eidx, s_planes, views.n_views, p);
 }
@@ -263,7 +269,7 @@ __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views vi
 constexpr int kMaxWalk = 12;
 
 template <bool FUSED, bool PER_INSTANCE>
-__global__ void __launch_bounds__(256) k_update_top(SceneDev s, Views views, uint32_t end) {
+__global__ void __launch_bounds__(256, 6) k_update_top(SceneDev s, Views views, uint32_t end) {
 	__shared__ float4 s_out[8][96];
 	__shared__ float4 s_planes[kMaxViews * 12];
 	if (FUSED && !PER_INSTANCE) {

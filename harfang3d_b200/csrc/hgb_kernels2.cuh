@@ -27,7 +27,7 @@ struct AnimDev {
 	const Track *tracks;
 	const int64_t *play_t;    // per playing anim: evaluation time (ns), INT64_MIN = not playing
 	const uint4 *keys;        // compact pool: 2 x uint4 per key (source of the records)
-	const uint4 *rec;         // interval records: 8 x uint4 (128 B, aligned) per key, see k_build_key_records
+	const uint4 *rec;         // interval records: 4 x uint4 (64 B, aligned) per key, see k_build_key_records
 	uint32_t quat_base;       // first quaternion key in the pool
 	uint32_t *cursor;         // per track: lower key of the interval found last frame (search hint only, never changes a result)
 	uint4 *tstate;            // per track: {time of key cursor, time of key cursor+1 (INT64_MAX past the end)} — hint, verified against the record
@@ -35,15 +35,6 @@ struct AnimDev {
 };
 
 __device__ __forceinline__ float time_to_sec_f(int64_t t) { return __double2float_rn(__ddiv_rn(double(t), 1000000000.0)); } // foundation/time.h:13
-
-// HermiteInterpolate foundation/math.h:137-149 on one component
-__device__ __forceinline__ float hermite1(float y0, float y1, float y2, float y3, float a0, float a1, float a2, float a3, float tension, float bias) {
-	float m0 = (y1 - y0) * (1.F + bias) * (1.F - tension) / 2.F;
-	m0 += (y2 - y1) * (1.F - bias) * (1.F - tension) / 2.F;
-	float m1 = (y2 - y1) * (1.F + bias) * (1.F - tension) / 2.F;
-	m1 += (y3 - y2) * (1.F - bias) * (1.F - tension) / 2.F;
-	return y1 * a0 + m0 * a1 + m1 * a2 + y2 * a3;
-}
 
 // ToEuler(Mat3, RO_YXZ) foundation/matrix3.cpp:91-137,141-163 (euler_order_yxz: i=1 j=0 k=2; the odd and the left-handed negations
 // cancel). atan2 is the DOUBLE libm function in the reference (float arguments promoted, result narrowed to float). CUDA's double atan2
@@ -101,32 +92,61 @@ __device__ __forceinline__ void quat_to_euler(float x, float y, float z, float w
 }
 
 // Interval records. The sampler's HBM traffic is one gather per track per frame; measured on the B200 (profiles/README.md r01c), a
-// 128-byte window that crosses a 128-byte line costs 70 % more time than an aligned one, and with 32-byte keys three windows out of
-// four cross. So the device keeps, next to the compact pool, one 128-BYTE-ALIGNED RECORD PER KEY: record k of a track holds the
-// keys {k-1, k, k+1, k+2} (clamped to the track) = everything EvaluateHermite / EvaluateLinear need for the interval that starts at
-// key k, plus the time of key k+2 to recognise "advanced by one interval". One frame = one aligned line per track. Costs 4x the
-// key memory (HBM is 180 GB; the 16M-node batch's 64M keys take 8 GB), built on the device by k_build_key_records at bind time.
+// window that crosses a 128-byte line costs 70 % more time than an aligned one. So the device keeps, next to the compact pool, one
+// 64-BYTE-ALIGNED RECORD PER KEY = everything the evaluation of the interval that starts at key k needs, and nothing else:
+//   Hermite vec3 track:  {t(k), t(k+1)} {y1.xyz, y2.x} {y2.yz, m0.xy} {m0.z, m1.xyz}
+//   quaternion track:    {t(k), t(k+1)} {q(k)} {q(k+1)} {-}
+// y1 / y2 = values of keys k / k+1; m0 / m1 = the two tangents of HermiteInterpolate (foundation/math.h:137-149), which depend on the
+// keys k-1 ... k+2 and on tension / bias of key k but NOT on the evaluation time: k_build_key_records computes them once, with the
+// very operations (and this TU's -fmad=false) the evaluation would use, so hoisting them changes no bit of any result — and the
+// per-frame gather shrinks from four whole keys (128 bytes) to 64. t(k+1) is INT64_MAX in a track's last record. One frame = half an
+// aligned line per track. Costs 2x the key memory (the 16M-node batch's 64M keys take 4 GB), built on the device at bind time.
+constexpr uint32_t kRecU4 = 4; // uint4s per record
+
+// tangents of one component of HermiteInterpolate (foundation/math.h:137-149), in the reference's operation order
+__device__ __forceinline__ void hermite_tangents(float y0, float y1, float y2, float y3, float tension, float bias, float &m0, float &m1) {
+	m0 = (y1 - y0) * (1.F + bias) * (1.F - tension) / 2.F;
+	m0 += (y2 - y1) * (1.F - bias) * (1.F - tension) / 2.F;
+	m1 = (y2 - y1) * (1.F + bias) * (1.F - tension) / 2.F;
+	m1 += (y3 - y2) * (1.F - bias) * (1.F - tension) / 2.F;
+}
+
 __global__ void __launch_bounds__(256) k_build_key_records(const Track *__restrict__ tracks, uint32_t n_tracks, const uint4 *__restrict__ keys,
 	uint32_t quat_base, uint4 *__restrict__ rec) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n_tracks)
 		return;
 	const uint32_t n = tracks[i].key_count;
-	const size_t base = size_t(tracks[i].key_off) + (tracks[i].kind == 3 ? quat_base : 0u);
+	const bool quat = tracks[i].kind == 3;
+	const size_t base = size_t(tracks[i].key_off) + (quat ? quat_base : 0u);
 	for (uint32_t k = 0; k < n; ++k) {
-		const uint32_t src[4] = {k > 0 ? k - 1 : 0u, k, min(k + 1, n - 1), min(k + 2, n - 1)};
-		uint4 *d = rec + (base + k) * 8;
-#pragma unroll
-		for (int j = 0; j < 4; ++j) {
-			d[j * 2] = keys[(base + src[j]) * 2];
-			d[j * 2 + 1] = keys[(base + src[j]) * 2 + 1];
+		const uint32_t k0 = k > 0 ? k - 1 : 0u, k2 = min(k + 1, n - 1), k3 = min(k + 2, n - 1);
+		const uint4 a1 = keys[(base + k) * 2], b1 = keys[(base + k) * 2 + 1];
+		const uint4 a2 = keys[(base + k2) * 2], b2 = keys[(base + k2) * 2 + 1];
+		uint4 *d = rec + (base + k) * kRecU4;
+		d[0] = k + 1 < n ? make_uint4(a1.x, a1.y, a2.x, a2.y) : make_uint4(a1.x, a1.y, 0xffffffffu, 0x7fffffffu);
+		if (quat) { // AnimKeyT<Quaternion>: {t, x, y | z, w}
+			d[1] = make_uint4(a1.z, a1.w, b1.x, b1.y);
+			d[2] = make_uint4(a2.z, a2.w, b2.x, b2.y);
+			d[3] = make_uint4(0, 0, 0, 0);
+			continue;
 		}
+		const uint4 a0 = keys[(base + k0) * 2], b0 = keys[(base + k0) * 2 + 1];
+		const uint4 a3 = keys[(base + k3) * 2], b3 = keys[(base + k3) * 2 + 1];
+		const float tension = __uint_as_float(b1.y), bias = __uint_as_float(b1.z);
+		float m0x, m0y, m0z, m1x, m1y, m1z;
+		hermite_tangents(__uint_as_float(a0.z), __uint_as_float(a1.z), __uint_as_float(a2.z), __uint_as_float(a3.z), tension, bias, m0x, m1x);
+		hermite_tangents(__uint_as_float(a0.w), __uint_as_float(a1.w), __uint_as_float(a2.w), __uint_as_float(a3.w), tension, bias, m0y, m1y);
+		hermite_tangents(__uint_as_float(b0.x), __uint_as_float(b1.x), __uint_as_float(b2.x), __uint_as_float(b3.x), tension, bias, m0z, m1z);
+		d[1] = make_uint4(a1.z, a1.w, b1.x, a2.z);
+		d[2] = make_uint4(a2.w, b2.x, __float_as_uint(m0x), __float_as_uint(m0y));
+		d[3] = make_uint4(__float_as_uint(m0z), __float_as_uint(m1x), __float_as_uint(m1y), __float_as_uint(m1z));
 	}
 }
 
-// time of key k of a track, read from its record (slot 1 of record k is key k itself)
+// time of key k of a track, read from its record
 __device__ __forceinline__ int64_t rec_key_time(const uint4 *rec, uint32_t k) {
-	const uint2 t = *reinterpret_cast<const uint2 *>(rec + size_t(k) * 8 + 2);
+	const uint2 t = *reinterpret_cast<const uint2 *>(rec + size_t(k) * kRecU4);
 	return int64_t(uint64_t(t.x) | (uint64_t(t.y) << 32));
 }
 __device__ __forceinline__ uint32_t upper_bound_rec(const uint4 *rec, uint32_t n, int64_t at) {
@@ -141,13 +161,13 @@ __device__ __forceinline__ uint32_t upper_bound_rec(const uint4 *rec, uint32_t n
 	return lo;
 }
 
-// One thread per bound track; a warp fetches its 32 records cooperatively — 8 lanes per record, 16 bytes per lane, straight into
-// shared memory with cp.async (LDGSTS, L1 bypassed) — so one load instruction covers four complete 128-byte lines (per-thread
-// 16-byte gathers are bound by L1 wavefronts at 89 % of the data-pipe peak, profiles/r01b). Each lane then reads its own record
-// (144-byte stride: conflict-free LDS.128). Pass 0 fetches the record of last frame's interval (cursor); when the interval moved
-// (next key, time jump, loop wrap) pass 1 fetches the record of the new one for the lanes that need it.
+// One thread per bound track; a warp fetches its 32 records cooperatively — 4 lanes per record, 16 bytes per lane, straight into
+// shared memory with cp.async (LDGSTS, L1 bypassed) — so one load instruction covers eight complete records (per-thread 16-byte
+// gathers are bound by L1 wavefronts at 89 % of the data-pipe peak, profiles/r01b). Each lane then reads its own record (80-byte
+// stride: conflict-free LDS.128). Pass 0 fetches the record the per-track state predicts; when the prediction fails (time jump, loop
+// wrap, state never written) pass 1 fetches the right one for the lanes that need it.
 constexpr int kSampleWarps = 8;
-constexpr uint32_t kWinStride = 144;
+constexpr uint32_t kWinStride = 80;
 
 __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src) {
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
@@ -171,37 +191,37 @@ __global__ void __launch_bounds__(kSampleWarps * 32, 6) k_sample_tracks(AnimDev 
 		return;
 	const uint32_t n = trk.key_count;
 	const uint32_t kbase = trk.key_off + (trk.kind == 3 ? a.quat_base : 0u);
-	const uint4 *rec = a.rec + size_t(kbase) * 8;
+	const uint4 *rec = a.rec + size_t(kbase) * kRecU4;
 	uint8_t *sw = s_win[warp];
 	const uint4 *win = reinterpret_cast<const uint4 *>(sw + lane * kWinStride);
-	const uint32_t sub = lane & 7u, grp = lane >> 3;
+	const uint32_t sub = lane & 3u, grp = lane >> 2;
 	const uint8_t *pool = reinterpret_cast<const uint8_t *>(a.rec);
-	auto t_of = [](const uint4 &k) { return int64_t(uint64_t(k.x) | (uint64_t(k.y) << 32)); };
+	auto t_lo = [](const uint4 &k) { return int64_t(uint64_t(k.x) | (uint64_t(k.y) << 32)); };
+	auto t_hi = [](const uint4 &k) { return int64_t(uint64_t(k.z) | (uint64_t(k.w) << 32)); };
 
 	// Which record? The per-track state {time of the cursor's key, time of the next key} (16 bytes, read coalesced) tells BEFORE the
-	// fetch whether this frame stays in last frame's interval or enters the next one, so that one aligned 128-byte record per track is
-	// all a frame reads, whether or not the track advances (a frame that advanced used to pay a second, dependent fetch: 205 instead
-	// of 106 µs for the 4M tracks of the c4 batch, profiles/README.md r01d). The state is a hint: the fetched record carries the key
-	// times and is verified; anything unexpected (time jump, loop wrap, state never written) falls back to the binary search + refetch.
+	// fetch whether this frame stays in last frame's interval or enters the next one, so that one aligned record per track is all a
+	// frame reads, whether or not the track advances. The state is a hint: the fetched record carries both key times and is verified;
+	// anything unexpected (time jump, loop wrap, state never written) falls back to the binary search + refetch.
 	uint32_t cur = 0, kf1 = 0, ub = 0;
 	int64_t t_cur = 0, t_next = 0;
 	bool want = active;
 	if (active) {
 		cur = min(a.cursor[i], n - 1);
 		const uint4 st = a.tstate[i];
-		t_cur = int64_t(uint64_t(st.x) | (uint64_t(st.y) << 32)), t_next = int64_t(uint64_t(st.z) | (uint64_t(st.w) << 32));
+		t_cur = t_lo(st), t_next = t_hi(st);
 		kf1 = (cur + 1 < n && at >= t_next && t_next > t_cur) ? cur + 1 : cur;
 	}
 #pragma unroll 1
 	for (int pass = 0; pass < 2; ++pass) {
-		// cooperative fetch: round r serves tracks 4r..4r+3
+		// cooperative fetch: round r serves tracks 8r..8r+7
 		const uint32_t want_rec = want ? kbase + kf1 : 0xffffffffu;
 #pragma unroll
-		for (int r = 0; r < 8; ++r) {
-			const uint32_t tr = r * 4 + grp;
+		for (int r = 0; r < 4; ++r) {
+			const uint32_t tr = r * 8 + grp;
 			const uint32_t k = __shfl_sync(0xffffffffu, want_rec, tr);
 			if (k != 0xffffffffu)
-				cp_async16(uint32_t(__cvta_generic_to_shared(sw + tr * kWinStride + sub * 16)), pool + size_t(k) * 128 + sub * 16);
+				cp_async16(uint32_t(__cvta_generic_to_shared(sw + tr * kWinStride + sub * 16)), pool + size_t(k) * 64 + sub * 16);
 		}
 		asm volatile("cp.async.wait_all;" ::: "memory");
 		__syncwarp();
@@ -209,10 +229,11 @@ __global__ void __launch_bounds__(kSampleWarps * 32, 6) k_sample_tracks(AnimDev 
 			break;
 		want = false;
 		if (active) {
-			// record kf1 = keys {kf1-1, kf1, kf1+1, kf1+2} (clamped): the interval [key kf1, key kf1+1) is the right one when
-			// key kf1 <= at < key kf1+1, or at/after the last key, or before the first one
-			const int64_t tB = t_of(win[2]), tC = t_of(win[4]);
-			if (tB <= at && (kf1 + 1 == n || at < tC)) {
+			// record kf1 covers [key kf1, key kf1+1): the right one when key kf1 <= at < key kf1+1, or at/after the last key (its
+			// t(k+1) is INT64_MAX), or before the first one
+			const uint4 h = win[0];
+			const int64_t tB = t_lo(h), tC = t_hi(h);
+			if (tB <= at && at < tC) {
 				ub = kf1 + 1;
 			} else if (kf1 == 0 && at < tB) {
 				ub = 0;
@@ -227,28 +248,24 @@ __global__ void __launch_bounds__(kSampleWarps * 32, 6) k_sample_tracks(AnimDev 
 			break;
 		__syncwarp(); // every lane has read its pass-0 record before pass 1 overwrites windows
 	}
-	if (active) { // the hint of the next frame (written only when it changes: once per interval)
-		const int64_t tB = t_of(win[2]);
-		const int64_t tC = kf1 + 1 < n ? t_of(win[4]) : INT64_MAX;
+	if (!active)
+		return;
+	const uint4 h = win[0], r1 = win[1], r2 = win[2];
+	{ // the hint of the next frame (written only when it changes: once per interval)
+		const int64_t tB = t_lo(h), tC = t_hi(h);
 		if (kf1 != cur)
 			a.cursor[i] = kf1;
 		if (tB != t_cur || tC != t_next)
-			a.tstate[i] = make_uint4(uint32_t(uint64_t(tB)), uint32_t(uint64_t(tB) >> 32), uint32_t(uint64_t(tC)), uint32_t(uint64_t(tC) >> 32));
+			a.tstate[i] = h;
 	}
-	if (!active)
-		return;
-	// slots kf0, kf1, kf2, kf3 of EvaluateHermite (animation.h:155-169), neighbours clamped to the track
-	const uint4 *w = win;
-	const uint4 kBa = w[2], kBb = w[3];
 	float4 *dst = a.anim_val + trk.out_slot;
+	const int64_t t1 = t_lo(h), t2 = t_hi(h);
 
 	if (trk.kind == 3) { // AnimTrackT<Quaternion>: EvaluateLinear animation.h:141-153, then ToEuler(Normalize())
-		float4 q = make_float4(__uint_as_float(kBa.z), __uint_as_float(kBa.w), __uint_as_float(kBb.x), __uint_as_float(kBb.y));
+		float4 q = make_float4(__uint_as_float(r1.x), __uint_as_float(r1.y), __uint_as_float(r1.z), __uint_as_float(r1.w));
 		if (!(ub == 0 || ub == n)) {
-			const uint4 kCa = w[4], kCb = w[5];
 			const float4 q0 = q;
-			const float4 q1 = make_float4(__uint_as_float(kCa.z), __uint_as_float(kCa.w), __uint_as_float(kCb.x), __uint_as_float(kCb.y));
-			const int64_t t1 = t_of(kBa), t2 = t_of(kCa);
+			const float4 q1 = make_float4(__uint_as_float(r2.x), __uint_as_float(r2.y), __uint_as_float(r2.z), __uint_as_float(r2.w));
 			const float k = time_to_sec_f(at - t1) / time_to_sec_f(t2 - t1);
 			q = make_float4(q0.x + (q1.x - q0.x) * k, q0.y + (q1.y - q0.y) * k, q0.z + (q1.z - q0.z) * k, q0.w + (q1.w - q0.w) * k);
 		}
@@ -257,24 +274,19 @@ __global__ void __launch_bounds__(kSampleWarps * 32, 6) k_sample_tracks(AnimDev 
 		*dst = make_float4(ex, ey, ez, 0.f);
 		return;
 	}
-	// AnimTrackHermiteT<Vec3>: EvaluateHermite animation.h:155-169
-	float ox, oy, oz;
-	if (ub == 0 || ub == n) {
-		ox = __uint_as_float(kBa.z), oy = __uint_as_float(kBa.w), oz = __uint_as_float(kBb.x);
-	} else {
-		const uint4 kAa = w[0], kAb = w[1], kCa = w[4], kCb = w[5];
-		const uint4 kDa = win[6], kDb = win[7];
-		const int64_t t1 = t_of(kBa), t2 = t_of(kCa);
+	// AnimTrackHermiteT<Vec3>: EvaluateHermite animation.h:155-169 with the tangents taken from the record
+	float ox = __uint_as_float(r1.x), oy = __uint_as_float(r1.y), oz = __uint_as_float(r1.z); // key kf1 itself: before the first / after the last key
+	if (!(ub == 0 || ub == n)) {
+		const uint4 r3 = win[3];
 		const float u = time_to_sec_f(at - t1) / time_to_sec_f(t2 - t1);
-		const float tension = __uint_as_float(kBb.y), bias = __uint_as_float(kBb.z);
 		const float t2_ = u * u, t3 = t2_ * u;
 		const float a0 = 2.F * t3 - 3.F * t2_ + 1.F;
 		const float a1 = t3 - 2.F * t2_ + u;
 		const float a2 = t3 - t2_;
 		const float a3 = -2.F * t3 + 3.F * t2_;
-		ox = hermite1(__uint_as_float(kAa.z), __uint_as_float(kBa.z), __uint_as_float(kCa.z), __uint_as_float(kDa.z), a0, a1, a2, a3, tension, bias);
-		oy = hermite1(__uint_as_float(kAa.w), __uint_as_float(kBa.w), __uint_as_float(kCa.w), __uint_as_float(kDa.w), a0, a1, a2, a3, tension, bias);
-		oz = hermite1(__uint_as_float(kAb.x), __uint_as_float(kBb.x), __uint_as_float(kCb.x), __uint_as_float(kDb.x), a0, a1, a2, a3, tension, bias);
+		ox = ox * a0 + __uint_as_float(r2.z) * a1 + __uint_as_float(r3.y) * a2 + __uint_as_float(r1.w) * a3;
+		oy = oy * a0 + __uint_as_float(r2.w) * a1 + __uint_as_float(r3.z) * a2 + __uint_as_float(r2.x) * a3;
+		oz = oz * a0 + __uint_as_float(r3.x) * a1 + __uint_as_float(r3.w) * a2 + __uint_as_float(r2.y) * a3;
 	}
 	*dst = make_float4(ox, oy, oz, 0.f);
 }

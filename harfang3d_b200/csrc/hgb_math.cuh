@@ -342,7 +342,7 @@ __device__ __forceinline__ bool survives_frustum_x(const float4 *__restrict__ pl
 	const f32x2_t cex = pk2(bb.mn[0] + bb.mx[0], bb.mx[0] - bb.mn[0]);
 	const f32x2_t cey = pk2(bb.mn[1] + bb.mx[1], bb.mx[1] - bb.mn[1]);
 	const f32x2_t cez = pk2(bb.mn[2] + bb.mx[2], bb.mx[2] - bb.mn[2]);
-	bool outside = false; // accumulated in the compare itself (FSETP ... OR): no early out, no select chain
+	uint32_t outside = 0; // all-ones per failed plane, OR-ed: no early out, no select chain
 #pragma unroll
 	for (int n = 0; n < 6; ++n) {
 		const float4 a = planes2[2 * n], b = planes2[2 * n + 1];
@@ -352,9 +352,11 @@ __device__ __forceinline__ bool survives_frustum_x(const float4 *__restrict__ pl
 		upk2(mul2(pk2(b.x, b.y), cez), dz, rz);
 		const float d = dx + dy + dz;
 		const float r = rx + ry + rz;
-		outside = outside | (d - r > b.z);
+		uint32_t o;
+		asm("set.gt.u32.f32 %0, %1, %2;" : "=r"(o) : "f"(d - r), "f"(b.z));
+		outside |= o;
 	}
-	return !outside;
+	return outside == 0;
 }
 
 } // namespace hgb

@@ -168,6 +168,9 @@ int hgb_get_trs(hgb_ctx *, uint32_t first, uint32_t count, float *out9);
 int hgb_get_visible_count(hgb_ctx *, int kind, uint32_t view, uint32_t *out_count);
 /* surviving entry indices (into the table given to hgb_set_display_entries), ascending = reference order */
 int hgb_get_visible(hgb_ctx *, int kind, uint32_t view, uint32_t *out_idx, uint32_t capacity, uint32_t *out_count);
+/* the same list in a pinned buffer OWNED by the context (valid until the next call for this kind, or hgb_destroy): count and list come down
+ * in one round trip and land by plain DMA whatever memory the caller would have offered */
+int hgb_get_visible_ptr(hgb_ctx *, int kind, uint32_t view, const uint32_t **out_idx, uint32_t *out_count);
 /* instance mode: exclusive offsets of every instance's survivors inside the kind-0 list, n_instances+1 values */
 int hgb_get_instance_offsets(hgb_ctx *, uint32_t *out_offsets);
 int hgb_get_bone_matrices(hgb_ctx *, float *out16, int previous);
