@@ -343,6 +343,12 @@ class Context:
         self._ck(self._L.hgb_get_visible(self._h, kind, view, _ptr(out, np.uint32, "out"), len(out), C.byref(n)))
         return out[: n.value]
 
+    def get_visible_ptr(self, kind=0, view=0):
+        """the visible list in the context's own pinned buffer (valid until the next call for this kind): one round trip"""
+        ptr, n = C.POINTER(C.c_uint32)(), C.c_uint32(0)
+        self._ck(self._L.hgb_get_visible_ptr(self._h, kind, view, C.byref(ptr), C.byref(n)))
+        return np.ctypeslib.as_array(ptr, shape=(n.value,)) if n.value else np.zeros(0, np.uint32)
+
     def get_instance_offsets(self):
         out = np.empty(self.n_inst + 1, np.uint32)
         self._ck(self._L.hgb_get_instance_offsets(self._h, _ptr(out, np.uint32, "out")))

@@ -1,16 +1,17 @@
-// TEST INFRASTRUCTURE ONLY (oracle). Flat C ABI over the UNMODIFIED reference hg::Scene so that tests and the
-// cpu_baseline leg of bench.py can build a scene from plain arrays, run the reference's own
-//   Scene::Update                (harfang/engine/scene.cpp:307-315)
-//   Scene::GetModelDisplayLists  (harfang/engine/scene.cpp:318-404)
-//   CullModelDisplayLists        (harfang/engine/render_pipeline.cpp:2098-2104)
-// and read back worlds / display lists / visible lists. This file is OUR code; it only #includes reference
-// headers. The only restated arithmetic is the bone-matrix product (render_pipeline.cpp:2172-2173 + to_bgfx
-// :59-62) because the reference function is static and interleaved with bgfx calls.
-// Never loaded by the product (harfang3d_b200/).
-//
-// The same file also compiles, unchanged, against the hg::Scene FACADE of the product (harfang3d_b200/csrc/facade/include, -DHG_FACADE):
-// that build (oracle/_facade/libhg_facade_driver.so, `make -C oracle facade_driver`) is how tests/test_facade.py drives the facade
-// through the very calls that drive the reference. Only the probes of reference-internal host math are compiled out there.
+// Flat C binding over the hg::Scene API: builds a scene from plain arrays, runs frames, reads worlds / display lists / visible lists /
+// bone matrices back — what a ctypes / FFI caller (tests, bench.py) needs instead of C++ handles. The file uses nothing but the PUBLIC
+// hg::Scene interface, so it compiles unchanged against two implementations of it:
+//   * the product's hg::Scene facade (csrc/facade/include, -DHG_FACADE)  -> harfang3d_b200/libhg_facade_flat.so (`make facade_flat`);
+//     this is the library bench.py's `e2e_facade` leg and tests/test_facade.py drive;
+//   * the UNMODIFIED reference headers + sources under /root/reference    -> the oracle's build of the reference (`make -C oracle ref`), the parity
+//     oracle and the CPU baseline: the reference's own
+//       Scene::Update                (harfang/engine/scene.cpp:307-315)
+//       Scene::GetModelDisplayLists  (harfang/engine/scene.cpp:318-404)
+//       CullModelDisplayLists        (harfang/engine/render_pipeline.cpp:2098-2104)
+//     behind the very calls that drive the facade. The only restated arithmetic in that build is the bone-matrix product
+//     (render_pipeline.cpp:2172-2173 + to_bgfx :59-62): the reference function is static and interleaved with bgfx calls.
+// Entry points keep the hgref_ prefix in both builds (one ctypes table); the probes of reference-internal host math are compiled out
+// of the facade build, the fused-frame entry points (hgfacade_*) out of the reference build.
 #include "engine/animation.h"
 #include "engine/render_pipeline.h"
 #include "engine/scene.h"
@@ -624,5 +625,43 @@ int hgref_time_frames(void *h, int frames, int64_t dt, const float *frustum24, i
 	}
 	return visible;
 }
+
+#ifdef HG_FACADE
+// ---- the product's own per-frame API, timed end to end (bench.py `e2e_facade`): SetCullingFrustums once, then every frame
+// Scene::Update(dt) (visibility evaluated inside the update pass) + GetVisibleModelDisplayLists = the std::vector<ModelDisplayList>
+// that GetModelDisplayLists + CullModelDisplayLists leave behind in the reference (render_pipeline.cpp:2098-2104), materialised on the host.
+// out3 = seconds in {Update, GetVisibleModelDisplayLists (opaque + transparent), total wall}; returns the visible count of the last frame.
+int hgfacade_time_fused_frames(void *h, int frames, int64_t dt, const float *frustum24, double *out3) {
+	auto *c = static_cast<RefCtx *>(h);
+	Frustum f;
+	memcpy(f.data(), frustum24, 96);
+	c->scene->SetCullingFrustums({f}, c->resources);
+	out3[0] = out3[1] = out3[2] = 0;
+	int visible = 0;
+	std::vector<ModelDisplayList> tr;
+	const double w0 = now_s();
+	for (int i = 0; i < frames; ++i) {
+		const double t0 = now_s();
+		c->scene->Update(dt);
+		const double t1 = now_s();
+		c->scene->GetVisibleModelDisplayLists(0, false, c->culled, c->resources);
+		c->scene->GetVisibleModelDisplayLists(0, true, tr, c->resources);
+		const double t2 = now_s();
+		visible = int(c->culled.size() + tr.size());
+		out3[0] += t1 - t0;
+		out3[1] += t2 - t1;
+	}
+	out3[2] = now_s() - w0;
+	return visible;
+}
+// the list of the last fused frame, as mtx_idx per entry (parity check of the leg above)
+int hgfacade_read_visible(void *h, uint32_t *out_mtx, int capacity) {
+	auto *c = static_cast<RefCtx *>(h);
+	const int n = int(c->culled.size());
+	for (int i = 0; i < n && i < capacity; ++i)
+		out_mtx[i] = c->culled[i].mtx_idx;
+	return n;
+}
+#endif
 
 } // extern "C"

@@ -330,6 +330,14 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		fail("cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
 		return nullptr;
 	}
+	if (const char *e_l2 = getenv("HGB_L2_FETCH")) { // A/B: DRAM -> L2 fetch granularity in bytes (32 / 64 / 128); device-wide limit
+		size_t before = 0;
+		cudaDeviceGetLimit(&before, cudaLimitMaxL2FetchGranularity);
+		const cudaError_t el = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, size_t(atoi(e_l2)));
+		size_t after = 0;
+		cudaDeviceGetLimit(&after, cudaLimitMaxL2FetchGranularity);
+		fprintf(stderr, "hgb: L2 fetch granularity %zu -> %zu (%s)\n", before, after, cudaGetErrorString(el));
+	}
 	hgb_ctx *c = new hgb_ctx;
 	c->device = device;
 	c->use_graph = opt ? opt->use_graph != 0 : true;

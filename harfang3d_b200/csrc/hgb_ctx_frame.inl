@@ -488,6 +488,8 @@ int hgb_cull_list(hgb_ctx *c, uint32_t n, const uint32_t *mtx_slot, const uint32
 		*out_count = 0;
 	if (!n)
 		return 0;
+	if (n_bounds > 0x00ffffffu) // the entry meta word keeps the bounds index in its low 24 bits, flags above (like hgb_set_bounds)
+		return fail("hgb_cull_list: %u bounds exceed the 2^24-1 the entry word can index", n_bounds);
 	CK(cudaSetDevice(c->device));
 	std::vector<uint32_t> pos(n);
 	for (uint32_t e = 0; e < n; ++e) {

@@ -98,6 +98,56 @@ def main():
         assert (idx == want).all()
         print("peer gather (shared camera): %d ranks, %d visible entries: identical to the per-rank lists" % (world, len(idx)))
 
+    # ---- asynchronous tail + skewed host submission + a rank WITHOUT display entries ----
+    # (the gather's step counter lives in the tail's own stream-ordered sequence: ranks that run ahead or behind on the host, and a rank
+    # that publishes an empty list, must all land in the same step)
+    import time
+    dist.barrier()
+    ctx.peer_close()
+    ctx.close()
+    fs3 = scenegen.static_scene(40_000, 6, 6, n_models=3, seed=900 + rank)
+    if rank == world - 1:
+        fs3.model[:] = -1  # no object anywhere: zero display entries on this rank
+    ctx = harfang3d_b200.Context(local, async_post=True)
+    t = hostmirror.upload(ctx, fs3)
+    ctx.update(None, fused_cull=True)
+    ctx.sync()
+    ent = torch.zeros(world, dtype=torch.int64, device="cuda")
+    ent[rank] = len(t["ent0_mtx_slot"])
+    dist.all_reduce(ent)
+    ent = ent.cpu().numpy()
+    assert ent[world - 1] == 0
+    ctx.peer_setup(dist, ent, None, dst=0)
+    for f in range(16):
+        if (f + rank) % 3 == 0:
+            time.sleep(0.003 * (1 + rank % 3))  # host-side skew between the ranks
+        if f % 4 == 1:
+            trs = fs3.trs.copy()
+            trs[:, 2] += 0.21 * (f + 1)
+            ctx.upload_trs(np.ascontiguousarray(trs, np.float32))
+        ctx.update(None, fused_cull=True)
+    ctx.sync()
+    st, err = ctx.peer_status()
+    assert err == 0 and st == 16, (st, err)
+    local_idx = torch.from_numpy(ctx.get_visible(0, 0).astype(np.int64)).cuda()
+    n_loc = torch.tensor([local_idx.numel()], device="cuda")
+    counts = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
+    dist.all_gather(counts, n_loc)
+    counts = [int(c.item()) for c in counts]
+    pad = torch.zeros(max(max(counts), 1), dtype=torch.int64, device="cuda")
+    pad[: local_idx.numel()] = local_idx
+    allp = [torch.zeros_like(pad) for _ in range(world)]
+    dist.all_gather(allp, pad)
+    if rank == 0:
+        off, idx, _ = ctx.peer_result()
+        base = np.concatenate([[0], np.cumsum(ent)[:-1]])
+        want = np.concatenate([allp[r][: counts[r]].cpu().numpy() + base[r] for r in range(world)]).astype(np.uint32)
+        assert counts[world - 1] == 0
+        assert (off == np.concatenate([[0], np.cumsum(counts)])).all(), (off, counts)
+        assert len(idx) == len(want) and (idx == want).all()
+        print("peer gather (asynchronous tail, skewed hosts, one empty rank): %d ranks, %d visible entries, 16 frames: identical to the per-rank lists" % (world, len(idx)))
+    ent_keep = ent
+
     # ---- close, then a setup that fails on ONE rank: every rank must leave peer_setup with the same error and keep running frames ----
     before = ctx.get_visible(0, 0).copy()
     dist.barrier()

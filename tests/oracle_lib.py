@@ -55,65 +55,8 @@ def load_port():
 
 
 def _bind_scene_driver(L, with_probes):
-    """signatures of oracle/ref_driver.cpp (same file for the reference build and the facade build)"""
-    _sig(L, "hgref_create", c_p, [])
-    _sig(L, "hgref_destroy", None, [c_p])
-    _sig(L, "hgref_add_model", c_i, [c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_p])
-    _sig(L, "hgref_add_nodes", c_i, [c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p])
-    _sig(L, "hgref_set_object_bones", c_i, [c_p, c_i, c_i, c_p])
-    _sig(L, "hgref_set_trs", None, [c_p, c_i, c_p])
-    _sig(L, "hgref_get_trs", None, [c_p, c_i, c_p])
-    _sig(L, "hgref_set_parent", None, [c_p, c_i, c_i])
-    _sig(L, "hgref_enable_node", None, [c_p, c_i, c_i])
-    _sig(L, "hgref_destroy_node", None, [c_p, c_i])
-    _sig(L, "hgref_garbage_collect", c_i, [c_p])
-    _sig(L, "hgref_set_node_world", None, [c_p, c_i, c_p])
-    _sig(L, "hgref_set_transform_matrix", None, [c_p, c_i, c_p, c_i])
-    _sig(L, "hgref_minmax", c_i, [c_p, c_i, c_i, c_p])
-    _sig(L, "hgref_load_binary", c_i, [c_p, C.c_char_p])
-    if with_probes:
-        _sig(L, "hgref_save_binary", c_i, [c_p, C.c_char_p])
-    _sig(L, "hgref_node_transform_idx", c_i, [c_p, c_i])
-    _sig(L, "hgref_add_anim", c_i, [c_p, c_i])
-    _sig(L, "hgref_anim_add_vec3_track", c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p])
-    _sig(L, "hgref_anim_add_quat_track", c_i, [c_p, c_i, c_i, c_p, c_p])
-    _sig(L, "hgref_anim_add_enable_track", c_i, [c_p, c_i, c_i, c_p, c_p])
-    _sig(L, "hgref_anim_add_float_track", c_i, [c_p, c_i, C.c_char_p, c_i, c_p, c_p, c_p, c_p])
-    _sig(L, "hgref_is_node_enabled", c_i, [c_p, c_i])
-    _sig(L, "hgref_add_anims_bulk", c_i, [c_p, c_i, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p])
-    _sig(L, "hgref_add_scene_anim", c_i, [c_p, c_i, c_p, c_p, c_i64, c_i64])
-    _sig(L, "hgref_play_anim", c_i, [c_p, c_i, c_i, c_f])
-    _sig(L, "hgref_is_playing", c_i, [c_p, c_i])
-    _sig(L, "hgref_update", None, [c_p, c_i64])
-    _sig(L, "hgref_update_phase", None, [c_p, c_i, c_i64])
-    _sig(L, "hgref_world_count", c_i, [c_p])
-    _sig(L, "hgref_get_worlds", c_i, [c_p, c_p, c_i])
-    _sig(L, "hgref_get_model_display_lists", None, [c_p, c_p])
-    _sig(L, "hgref_read_display_lists", c_i, [c_p, c_i, c_p, c_p, c_p])
-    _sig(L, "hgref_read_skinned_lists", c_i, [c_p, c_i, c_p, c_p, c_p, c_p, c_p])
-    _sig(L, "hgref_cull", c_i, [c_p, c_i, c_p, c_p, c_p])
-    _sig(L, "hgref_bone_matrices", c_i, [c_p, c_i, c_i, c_p])
-    _sig(L, "hgref_set_node_camera", c_i, [c_p, c_i, c_i, c_f, c_f, c_f])
-    _sig(L, "hgref_set_camera_fov", None, [c_p, c_i, c_f])
-    _sig(L, "hgref_get_camera_fov", c_f, [c_p, c_i])
-    _sig(L, "hgref_set_current_camera", None, [c_p, c_i])
-    _sig(L, "hgref_current_camera_view_state", None, [c_p, c_f, c_f, c_p])
-    _sig(L, "hgref_make_perspective_frustum", None, [c_f] * 5 + [c_p, c_p])
-    _sig(L, "hgref_make_ortho_frustum", None, [c_f] * 5 + [c_p, c_p])
-    for n in ("hgref_transformation_mat4", "hgref_inverse_fast"):
-        _sig(L, n, None, [c_p, c_p])
-    _sig(L, "hgref_mat4_mul", None, [c_p, c_p, c_p])
-    _sig(L, "hgref_sinf", c_f, [c_f])
-    _sig(L, "hgref_cosf", c_f, [c_f])
-    _sig(L, "hgref_time_frames", c_i, [c_p, c_i, c_i64, c_p, c_i, c_p])
-    if with_probes:  # reference-internal host math: compiled out of the facade build
-        _sig(L, "hgref_minmax_transform", None, [c_p, c_p, c_p])
-        _sig(L, "hgref_quat_to_euler", None, [c_p, c_p])
-        _sig(L, "hgref_test_visibility", c_i, [c_p, c_p])
-        _sig(L, "hgref_sort_keys", c_i, [c_p, c_p, c_p])
-        _sig(L, "hgref_eval_vec3_track", c_i, [c_i, c_p, c_p, c_p, c_p, c_i64, c_p, c_p])
-        _sig(L, "hgref_eval_quat_track", c_i, [c_i, c_p, c_p, c_i64, c_p])
-    return L
+    from harfang3d_b200 import flatscene
+    return flatscene.bind(L, with_probes)
 
 
 def load_ref():
@@ -124,12 +67,13 @@ def load_ref():
 
 
 def load_facade_driver():
-    """oracle/ref_driver.cpp compiled against the PRODUCT's hg::Scene facade (make -C oracle facade_driver): same flat calls, so
+    """the flat binding compiled against the PRODUCT's hg::Scene facade (harfang3d_b200/libhg_facade_flat.so): same flat calls, so
     tests.scene_io.RefScene drives the facade exactly like it drives the reference. None when not built."""
-    so = os.path.join(ORACLE, "_facade", "libhg_facade_driver.so")
-    if not os.path.exists(so):
+    from harfang3d_b200 import flatscene
+    try:
+        return flatscene.load()
+    except RuntimeError:
         return None
-    return _bind_scene_driver(C.CDLL(so), False)
 
 
 def bits(a):
