@@ -13,12 +13,13 @@ gathered to rank 0 inside every step (the path has no other exchange). The other
 (configs[0]), c2 (configs[1]), c3 (configs[2]) and c5 [--strong] (configs[4]: 8192 instances partitioned over the ranks).
 
   value          nodes/s with the scene resident in HBM, CUDA events on the launching stream, max over ranks
-  e2e            the same metric through the product's hg::Scene facade — Scene::Update(dt) + GetVisibleModelDisplayLists, the call a
-                 HARFANG user makes and the object (std::vector<ModelDisplayList>) the reference arm leaves behind — with host buffers
-                 inside the timed region: play clocks and frusta go up from host memory every step, the visible list comes down
-                 to pinned host memory and is materialised on the host. Falls back to the C-ABI leg when the facade leg does not apply.
-  e2e_capi       the C ABI underneath: hgb_set_views + hgb_update(clocks) + hgb_get_visible into pinned host memory (index list)
-  e2e_full_upload  as e2e_capi, plus hgb_upload_trs of EVERY node from pinned host memory each step (all transforms host-edited: the
+  e2e            the same metric through the C ABI (the drop-in boundary, include/hgb200.h) with HOST buffers inside the timed region,
+                 scene resident like the reference's hg::Scene: every step hgb_set_views (frusta) + hgb_update (play clocks) from host
+                 memory, hgb_get_visible into pinned host memory (the visible index list)
+  e2e_facade     one layer up, the call a HARFANG user makes: hg::Scene::Update(dt) + GetVisibleModelDisplayLists through the C++ facade,
+                 result = the std::vector<ModelDisplayList> the reference arm's GetModelDisplayLists + CullModelDisplayLists leave behind,
+                 materialised on the host (16 bytes per visible entry gathered by host threads)
+  e2e_full_upload  as e2e, plus hgb_upload_trs of EVERY node from pinned host memory each step (all transforms host-edited: the
                  physics / script-driven worst case; PCIe-bound)
   roofline       k_update_level (fused update+cull), algorithmic bytes per node / CUDA-event time per launch
   cpu_baseline   the UNMODIFIED reference (oracle/_ref) on this box's host cores, bounded sample of the same workload
@@ -603,14 +604,15 @@ def main():
                                    ("per step: visible counts all-gathered (NCCL), visible lists gathered to rank 0 "
                                    "(grouped send/recv sized from the counts; %d entries gathered in the last step)" % gathered[0]),
                        "scale": args.scale},
-            "e2e": leg("e2e_facade", what_fac) if "e2e_facade" in e2e else leg("e2e_capi", what_capi),
-            "e2e_capi": leg("e2e_capi", what_capi),
+            "e2e": leg("e2e_capi", what_capi),
             "gpu_launches": launches,
             "roofline": roof,
             "clocks": clocks_rec,
         }
+        if "e2e_facade" in e2e:
+            line["e2e_facade"] = leg("e2e_facade", what_fac)
         if "e2e_full_upload" in e2e:
-            line["e2e_full_upload"] = leg("e2e_full_upload", "as e2e_capi plus hgb_upload_trs of ALL nodes from pinned host memory every step (every transform host-edited; PCIe-bound)")
+            line["e2e_full_upload"] = leg("e2e_full_upload", "as e2e plus hgb_upload_trs of ALL nodes from pinned host memory every step (every transform host-edited; PCIe-bound)")
         if facade_note:
             line["e2e_facade_note"] = facade_note
         if others:

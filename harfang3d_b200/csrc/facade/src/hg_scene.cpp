@@ -32,7 +32,7 @@ static std::map<const void *, Scene *> g_registry;
 
 // A few persistent host threads for the one per-frame host loop that is worth it: turning the visible INDEX list the device returns
 // into the std::vector<ModelDisplayList> the caller asked for (1.6 M x 16 bytes per frame on the 16M-node batch: a gather from a 256 MB
-// table, memory-bound, ~10x faster on 8 threads than on one). The scene itself stays single-threaded like the reference's
+// table, memory-latency-bound: software prefetch + up to 16 threads). The scene itself stays single-threaded like the reference's
 // (SURVEY.md §8b): the workers only ever run inside GetVisibleModelDisplayLists and touch nothing but its input and output arrays.
 namespace {
 class GatherPool {
@@ -66,7 +66,7 @@ public:
 private:
 	GatherPool() {
 		const unsigned hw = std::thread::hardware_concurrency();
-		const unsigned n = hw > 1 ? std::min(hw, 8u) - 1 : 0;
+		const unsigned n = hw > 1 ? std::min(hw, 16u) - 1 : 0;
 		for (unsigned i = 0; i < n; ++i)
 			workers.emplace_back([this] { loop(); });
 	}
@@ -1123,11 +1123,14 @@ bool Scene::GetVisibleModelDisplayLists(uint32_t view, bool transparent, std::ve
 	out.resize(n);
 	const ModelDisplayList *table = impl->ent[k].data();
 	ModelDisplayList *dst = out.data();
-	const uint32_t chunk = 1u << 16, n_chunks = (n + chunk - 1) / chunk;
+	const uint32_t chunk = 1u << 15, n_chunks = (n + chunk - 1) / chunk;
 	GatherPool::get().run(n_chunks, [=](uint32_t c) {
 		const uint32_t e = std::min(n, (c + 1) * chunk);
-		for (uint32_t i = c * chunk; i < e; ++i)
+		for (uint32_t i = c * chunk; i < e; ++i) {
+			if (i + 32 < e)
+				__builtin_prefetch(table + idx[i + 32]); // the table rows are a sparse ascending walk through 16 bytes per entry: keep misses in flight
 			dst[i] = table[idx[i]];
+		}
 	});
 	return true;
 }

@@ -155,7 +155,7 @@ struct hgb_ctx {
 	bool transpose_store = true;
 	bool tma_level = false;   // A/B switch: persistent TMA-staged level kernel instead of one thread per node with LDG rows (measured slower: r01c)
 	uint64_t top_budget = 2500000; // k_update_top covers the leading levels whose recomputed work (sum of nodes x depth) stays below this; 0 = one launch per level
-	uint32_t level_block = 256;    // threads per CTA of the level kernel (HGB_LEVEL_BLOCK=128: smaller CTAs recycle their slots sooner; A/B)
+	uint32_t level_block = 128;    // threads per CTA of the level kernel: small CTAs recycle their slots sooner (HGB_LEVEL_BLOCK=256: A/B, +2.5 % frame time)
 	int level_minb = 6;            // resident CTAs per SM the level kernel's registers are held to (HGB_LEVEL_MINB=5: 48 registers; A/B)
 	bool overlap_sampler = false; // opt-in: sample tracks by target level on a second stream, overlapped with the level kernels (measured slower: r01c)
 	cudaStream_t stream2 = nullptr;
@@ -357,7 +357,7 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 	if (const char *e_top = getenv("HGB_TOP_BUDGET"))
 		c->top_budget = strtoull(e_top, nullptr, 10);
 	if (const char *e_blk = getenv("HGB_LEVEL_BLOCK"))
-		c->level_block = atoi(e_blk) == 128 ? 128u : (atoi(e_blk) == 64 ? 64u : 256u);
+		c->level_block = atoi(e_blk) == 256 ? 256u : (atoi(e_blk) == 64 ? 64u : 128u);
 	if (const char *e_minb = getenv("HGB_LEVEL_MINB"))
 		c->level_minb = atoi(e_minb) == 5 ? 5 : 6;
 	c->overlap_sampler = opt ? opt->overlap_sampler != 0 : false;

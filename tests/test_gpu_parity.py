@@ -710,7 +710,7 @@ def test_cull_list_rejects_oversized_bounds_table(hgb):
 
     class Big:  # claims 2^24 bounds without allocating them: the count alone must be refused
         shape = (1 << 24, 6)
-    with pytest.raises(hgb.HgbError, match="2\^24-1"):
+    with pytest.raises(hgb.HgbError, match=r"2\^24-1"):
         n = C.c_uint32(0)
         out = np.zeros(4, np.uint32)
         rc = ctx._L.hgb_cull_list(ctx._h, 1, np.zeros(1, np.uint32).ctypes.data_as(C.c_void_p), np.zeros(1, np.uint32).ctypes.data_as(C.c_void_p), 1 << 24,
