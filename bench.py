@@ -504,20 +504,23 @@ def main():
         try:
             from harfang3d_b200 import flatscene  # ctypes table of the product's flat binding over the facade
             fac = flatscene.load()
+            fac.hgfacade_set_default_device(local_rank)  # one process per GPU: the facade's scenes live on this rank's device
             sc = flatscene.SceneHandle(fac, fs)
             fr0 = np.ascontiguousarray(frusta[0])
             out3 = np.zeros(3)
             fac.hgfacade_time_fused_frames(sc.h, 5, FRAME_DT, flatscene.P(fr0), flatscene.P(out3))  # warm-up (the first frame uploads the scene)
-            barrier()
+            # no collective inside this leg (a rank that fails it must not strand the others): every call below ends with the list on the host
             nvis = fac.hgfacade_time_fused_frames(sc.h, KE, FRAME_DT, flatscene.P(fr0), flatscene.P(out3))
-            barrier()
             e2e["e2e_facade"] = [float(out3[2]) / KE, 8 * len(fs.plays) + 96, 4 + 4 * int(nvis),
                                  {"update_ms": float(out3[0]) / KE * 1e3, "visible_lists_ms": float(out3[1]) / KE * 1e3, "visible": int(nvis),
                                   "list_bytes_materialised_on_host": 16 * int(nvis)}]
             sc.close()
         except Exception as e:  # the line says why there is no facade number
             facade_note = "%s: %s" % (type(e).__name__, e)
-    elif not args.no_facade:
+    torch.cuda.set_device(local_rank)
+    if args.no_facade:
+        pass
+    elif facade_note is None and "e2e_facade" not in e2e:
         facade_note = "the facade leg covers the single-camera rigid workloads (c4, c2, c1); %s is measured through the C ABI" % args.workload
 
     # ---- reduce over ranks --------------------------------------------------------------------------------------------------

@@ -654,6 +654,8 @@ int hgfacade_time_fused_frames(void *h, int frames, int64_t dt, const float *fru
 	out3[2] = now_s() - w0;
 	return visible;
 }
+// one process per GPU: scenes created after this call live on `device` (Scene::SetDefaultDevice)
+void hgfacade_set_default_device(int device) { Scene::SetDefaultDevice(device); }
 // the list of the last fused frame, as mtx_idx per entry (parity check of the leg above)
 int hgfacade_read_visible(void *h, uint32_t *out_mtx, int capacity) {
 	auto *c = static_cast<RefCtx *>(h);

@@ -30,12 +30,22 @@ template <typename T> struct AnimTrackHermiteT {
 };
 
 static const uint8_t AF_UseQuaternionForRotation = 0x01;
+static const uint8_t AF_Instantiated = 0x10; // non-serialized: the anim came with an instantiated scene (animation.h:202)
+
+struct InstanceAnimKey { // animation.h:171-175: which anim of an instantiated scene plays from this key on
+	std::string anim_name;
+	AnimLoopMode loop_mode{ALM_Once};
+	float t_scale{1.f};
+};
 
 struct Anim {
-	std::vector<AnimTrackT<bool>> bool_tracks;           // "Enable" (not on the metric path)
-	std::vector<AnimTrackHermiteT<float>> float_tracks;   // "Camera.Fov": one value per camera, evaluated on the host (EvaluateHermite, animation.h:155-169)
-	std::vector<AnimTrackHermiteT<Vec3>> vec3_tracks;     // "Position", "Rotation" (Euler), "Scale"
-	std::vector<AnimTrackT<Quaternion>> quat_tracks;     // "Rotation" when AF_UseQuaternionForRotation
+	std::vector<AnimTrackT<bool>> bool_tracks;           // "Enable": evaluated on the device (k_sample_enable)
+	std::vector<AnimTrackHermiteT<float>> float_tracks;   // "Camera.Fov", "Light.DiffuseIntensity", "Light.SpecularIntensity": single host-side values
+	std::vector<AnimTrackHermiteT<Vec3>> vec3_tracks;     // "Position", "Rotation" (Euler), "Scale": evaluated on the device (k_sample_tracks)
+	std::vector<AnimTrackHermiteT<Vec4>> vec4_tracks;     // "Material.<slot>.<value>": single host-side values
+	std::vector<AnimTrackT<Quaternion>> quat_tracks;     // "Rotation" when AF_UseQuaternionForRotation (device)
+	std::vector<AnimTrackHermiteT<Color>> color_tracks;   // "Light.Diffuse", "Light.Specular": single host-side values
+	AnimTrackT<InstanceAnimKey> instance_anim_track;      // step track driving the anims of the node's instantiated scene (scene.cpp:2217-2268)
 	time_ns t_start{0}, t_end{0};
 	uint8_t flags{0};
 };

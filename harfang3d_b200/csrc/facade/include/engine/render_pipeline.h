@@ -22,9 +22,17 @@ static const int max_skinned_model_matrix_count = 32; // render_pipeline.h:38
 
 enum BlendMode { BM_Additive, BM_Alpha, BM_Darken, BM_Lighten, BM_Multiply, BM_Opaque, BM_Screen, BM_LinearBurn, BM_AlphaRGB_AddAlpha, BM_Undefined };
 
-struct Material { // only what GetModelDisplayLists reads: the blend mode (render_pipeline.cpp:394-417)
-	BlendMode blend_mode{BM_Opaque};
+struct MaterialValue { // render_pipeline.h: a named uniform of a material; `value` holds 1..16 floats
+	int type{3};      // bgfx::UniformType::Vec4
+	std::vector<float> value;
+	uint16_t count{1};
 };
+struct Material { // what the scene-update path reads: the blend mode (GetModelDisplayLists, render_pipeline.cpp:394-417) and the named
+                  // values "Material.<slot>.<name>" vec4 tracks animate (scene.cpp:2199-2215)
+	BlendMode blend_mode{BM_Opaque};
+	std::map<std::string, MaterialValue> values;
+};
+inline void SetMaterialValue(Material &m, const char *name, const Vec4 &v) { m.values[name] = MaterialValue{3, {v.x, v.y, v.z, v.w}, 1}; }
 inline BlendMode GetMaterialBlendMode(const Material &m) { return m.blend_mode; }
 inline void SetMaterialBlendMode(Material &m, BlendMode mode) { m.blend_mode = mode; }
 

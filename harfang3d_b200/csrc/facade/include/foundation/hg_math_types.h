@@ -38,6 +38,13 @@ struct Vec4 {
 	Vec4(float x_, float y_, float z_, float w_) : x(x_), y(y_), z(z_), w(w_) {}
 };
 
+struct Color { // foundation/color.h:17-32
+	float r{0}, g{0}, b{0}, a{0};
+	Color() = default;
+	Color(float r_, float g_, float b_, float a_ = 1.f) : r(r_), g(g_), b(b_), a(a_) {}
+};
+inline bool operator==(const Color &x, const Color &y) { return x.r == y.r && x.g == y.g && x.b == y.b && x.a == y.a; }
+
 struct Quaternion {
 	float x{0}, y{0}, z{0}, w{1};
 	Quaternion() = default;
