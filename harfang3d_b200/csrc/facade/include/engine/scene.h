@@ -71,14 +71,52 @@ struct Camera { // node.h:77-100: the view the culling frusta of a frame come fr
 	float GetSize() const;
 	void SetSize(float v);
 };
+enum LightType { LT_Point, LT_Spot, LT_Linear }; // node.h:135-136
+enum LightShadowType { LST_None, LST_Map };
+static const float default_shadow_bias = 0.0001f;
+struct Light { // node.h:138-180: host-side component; colours and intensities are animation targets (scene.cpp:2183-2192)
+	Scene *scene{nullptr};
+	ComponentRef ref;
+	bool IsValid() const;
+	LightType GetType() const;
+	void SetType(LightType v);
+	Color GetDiffuseColor() const;
+	void SetDiffuseColor(const Color &v);
+	float GetDiffuseIntensity() const;
+	void SetDiffuseIntensity(float v);
+	Color GetSpecularColor() const;
+	void SetSpecularColor(const Color &v);
+	float GetSpecularIntensity() const;
+	void SetSpecularIntensity(float v);
+	float GetRadius() const;
+	void SetRadius(float v);
+};
+struct Instance { // node.h: a node that instantiates another scene file under itself
+	Scene *scene{nullptr};
+	ComponentRef ref;
+	bool IsValid() const;
+	std::string GetPath() const;
+	void SetPath(const std::string &path);
+	void SetOnInstantiateAnim(const std::string &anim);
+	void SetOnInstantiateAnimLoopMode(AnimLoopMode loop_mode);
+	std::string GetOnInstantiateAnim() const;
+};
 struct Node {
 	Scene *scene{nullptr};
 	NodeRef ref;
 	bool IsValid() const;
 	uint32_t GetUid() const { return ref.idx; } // node.h:289
+	std::string GetName() const;
+	void SetName(const std::string &v);
 	void Enable();
 	void Disable();
 	bool IsEnabled() const;
+	bool IsItselfEnabled() const;
+	Light GetLight() const;
+	void SetLight(const Light &l);
+	Instance GetInstance() const;
+	void SetInstance(const Instance &i);
+	bool IsInstantiatedBy() const;
 	Transform GetTransform() const;
 	void SetTransform(const Transform &t);
 	Object GetObject() const;
@@ -89,6 +127,7 @@ struct Node {
 	void SetWorld(const Mat4 &m);
 	bool GetMinMax(const PipelineResources &resources, MinMax &minmax) const; // node.cpp:106-119 (object nodes; no instance views here)
 };
+inline bool operator==(const Node &a, const Node &b) { return a.scene == b.scene && a.ref == b.ref; }
 // node.cpp:265-285: union of the nodes' world-space bounding boxes — a device reduction over the scene's current world matrices
 bool GetNodesMinMax(const std::vector<Node> &nodes, const PipelineResources &resources, MinMax &minmax);
 
@@ -102,18 +141,22 @@ struct SceneAnim { // scene.h:109-118
 	AnimRef scene_anim;
 	std::vector<NodeAnim> node_anims;
 	time_ns frame_duration{50000000}; // 20 fps
+	uint8_t flags{0};
 };
 
-static const uint32_t NF_Disabled = 0x1, NF_InstanceDisabled = 0x2; // scene.h:166-170
+static const uint32_t NF_Disabled = 0x1, NF_InstanceDisabled = 0x2, NF_Instantiated = 0x4; // scene.h:166-170
+static const uint8_t SAF_Instantiated = 0x10;
 
 // engine/load_save_scene_flags.h:10-32
 static const uint32_t LSSF_Nodes = 0x1, LSSF_Scene = 0x2, LSSF_Anims = 0x4, LSSF_KeyValues = 0x8, LSSF_Physics = 0x10, LSSF_Scripts = 0x20, LSSF_All = 0xffff;
 static const uint32_t LSSF_DoNotLoadResources = 0x40000; // always in force here: resources are resolved by name, never read from disk
 
+extern const SceneAnimRef InvalidSceneAnimRef;
 struct SceneView { // scene.h:145-155
 	std::vector<NodeRef> nodes;
 	std::vector<AnimRef> anims;
 	std::vector<SceneAnimRef> scene_anims;
+	SceneAnimRef GetSceneAnim(const Scene &scene, const std::string &name) const; // scene.cpp: first scene anim of the view with that name
 };
 struct LoadSceneContext { // scene.h:157-161
 	int recursion_level{};
@@ -145,6 +188,68 @@ public:
 	bool IsNodeEnabled(NodeRef ref) const; // scene.h:227 (reads back device-evaluated "Enable" tracks first)
 	size_t GetNodeCount() const { return nodes.size(); }
 	bool IsChildOf(NodeRef node, NodeRef parent) const; // component.cpp:21-33
+	bool IsNodeItselfEnabled(NodeRef ref) const; // NF_Disabled alone (scene.h:228)
+	std::string GetNodeName(NodeRef ref) const;
+	void SetNodeName(NodeRef ref, const std::string &v);
+	Node GetNode(const std::string &name) const;                // scene.cpp:522-528: first node with that name
+	Node GetNodeEx(const std::string &path) const;              // scene.cpp:530-579: "a/b" walks children, "a:b" enters an instance
+	std::vector<NodeRef> GetNodeChildRefs(NodeRef ref) const;   // nodes whose transform's parent is `ref`
+	bool IsRoot(NodeRef ref) const;                             // no transform, or no valid parent
+	std::vector<Node> GetNodes() const;                         // instantiated nodes are left out (scene.cpp:583-595)
+	std::vector<Node> GetAllNodes() const;
+
+	// ---- lights (scene.h:363-423): host-side component, colours / intensities are animation targets ----
+	Light CreateLight();
+	void DestroyLight(ComponentRef ref);
+	void DestroyLight(const Light &l) { DestroyLight(l.ref); }
+	bool IsValidLightRef(ComponentRef ref) const { return lights.is_valid(ref); }
+	LightType GetLightType(ComponentRef ref) const;
+	void SetLightType(ComponentRef ref, LightType v);
+	Color GetLightDiffuseColor(ComponentRef ref) const;
+	void SetLightDiffuseColor(ComponentRef ref, const Color &v);
+	float GetLightDiffuseIntensity(ComponentRef ref) const;
+	void SetLightDiffuseIntensity(ComponentRef ref, float v);
+	Color GetLightSpecularColor(ComponentRef ref) const;
+	void SetLightSpecularColor(ComponentRef ref, const Color &v);
+	float GetLightSpecularIntensity(ComponentRef ref) const;
+	void SetLightSpecularIntensity(ComponentRef ref, float v);
+	float GetLightRadius(ComponentRef ref) const;
+	void SetLightRadius(ComponentRef ref, float v);
+	Light CreatePointLight(float radius, const Color &diffuse = {1, 1, 1}, float diffuse_intensity = 1, const Color &specular = {1, 1, 1},
+		float specular_intensity = 1, float priority = 0, LightShadowType shadow_type = LST_None, float shadow_bias = default_shadow_bias);
+	std::vector<Node> GetLights() const;
+	ComponentRef GetNodeLightRef(NodeRef ref) const;
+	void SetNodeLight(NodeRef ref, ComponentRef cref);
+	Light GetNodeLight(NodeRef ref) const { return {const_cast<Scene *>(this), GetNodeLightRef(ref)}; }
+	void SetNodeLight(NodeRef ref, const Light &v) { SetNodeLight(ref, v.ref); }
+
+	// ---- scene instances (scene.h:437-476; scene.cpp:1190-1430): a node that loads another scene under itself. Disabling the host node
+	// propagates NF_InstanceDisabled to the instantiated nodes (EnableNode_/DisableNode_, scene.cpp:472-503); an Anim's
+	// instance_anim_track plays the instantiated scene's anims at a nested clock (scene.cpp:2217-2268) ----
+	Instance CreateInstance();
+	Instance CreateInstance(const std::string &path);
+	void DestroyInstance(ComponentRef ref);
+	bool IsValidInstanceRef(ComponentRef ref) const { return instances.is_valid(ref); }
+	void SetInstancePath(ComponentRef ref, const std::string &path);
+	std::string GetInstancePath(ComponentRef ref) const;
+	void SetOnInstantiateAnim(ComponentRef ref, const std::string &anim);
+	void SetOnInstantiateAnimLoopMode(ComponentRef ref, AnimLoopMode loop_mode);
+	std::string GetOnInstantiateAnim(ComponentRef ref) const;
+	AnimLoopMode GetOnInstantiateAnimLoopMode(ComponentRef ref) const;
+	ScenePlayAnimRef GetOnInstantiatePlayAnimRef(ComponentRef ref) const;
+	ComponentRef GetNodeInstanceRef(NodeRef ref) const;
+	void SetNodeInstance(NodeRef ref, ComponentRef cref);
+	Instance GetNodeInstance(NodeRef ref) const;
+	bool NodeSetupInstanceFromFile(NodeRef ref, PipelineResources &resources, const PipelineInfo &pipeline, uint32_t flags = LSSF_All, int recursion_level = 0);
+	bool NodeSetupInstanceFromMemory(NodeRef ref, const void *data, size_t size, PipelineResources &resources, const PipelineInfo &pipeline, uint32_t flags = LSSF_All,
+		int recursion_level = 0);
+	void NodeDestroyInstance(NodeRef ref);
+	ScenePlayAnimRef NodeStartOnInstantiateAnim(NodeRef ref);
+	void NodeStopOnInstantiateAnim(NodeRef ref);
+	const SceneView &GetNodeInstanceSceneView(NodeRef ref) const;
+	NodeRef IsInstantiatedBy(NodeRef ref) const;
+	SceneAnimRef GetSceneAnim(const std::string &name) const;
+	const SceneAnim *GetSceneAnim(SceneAnimRef ref) const { return scene_anims.is_valid(ref) ? &scene_anims[ref.idx] : nullptr; }
 
 	// ---- transforms (scene.h:242-284) ----
 	Transform CreateTransform();
@@ -277,7 +382,25 @@ private:
 	struct Node_ { // scene.h:698-702
 		std::string name;
 		uint32_t flags{0};
-		ComponentRef transform, object, camera;
+		ComponentRef transform, object, camera, light;
+	};
+	struct Light_ { // scene.h:759-774
+		LightType type{LT_Point};
+		LightShadowType shadow_type{LST_None};
+		Color diffuse{1.f, 1.f, 1.f, 1.f};
+		float diffuse_intensity{1.f};
+		Color specular{1.f, 1.f, 1.f, 1.f};
+		float specular_intensity{1.f};
+		float radius{0.f};
+		float inner_angle{0.5235987756f}, outer_angle{0.7853981634f}; // Deg(30), Deg(45)
+		Vec4 pssm_split{10.f, 50.f, 100.f, 200.f};
+		float priority{0.f};
+		float shadow_bias{default_shadow_bias};
+	};
+	struct Instance_ { // scene.h: path of the instantiated scene + the anim started on instantiation
+		std::string name, anim;
+		AnimLoopMode loop_mode{ALM_Once};
+		ScenePlayAnimRef play_anim_ref;
 	};
 	struct Camera_ { // scene.h:739-745
 		CameraZRange zrange;
@@ -308,6 +431,10 @@ private:
 	generational_vector_list<Transform_> transforms;
 	generational_vector_list<Object_> objects;
 	generational_vector_list<Camera_> cameras;
+	generational_vector_list<Light_> lights;
+	generational_vector_list<Instance_> instances;
+	std::map<NodeRef, ComponentRef> node_instance;    // scene.h: instance component of a node
+	std::map<NodeRef, SceneView> node_instance_view;  // what the instance brought into this scene
 	NodeRef current_camera;
 	generational_vector_list<Anim> anims;
 	generational_vector_list<SceneAnim> scene_anims;
@@ -321,6 +448,12 @@ private:
 	int device{0};
 	Impl *impl; // dirty tracking + staging (facade/src/hg_scene.cpp)
 
+	void EnableNode_(NodeRef ref, bool through_instance);
+	void DisableNode_(NodeRef ref, bool through_instance);
+	NodeRef GetNodeEx_(const std::vector<NodeRef> &refs, const std::string &path) const;
+	bool NodeSetupInstance_(NodeRef ref, const void *data, size_t size, const char *name, PipelineResources &resources, const PipelineInfo &pipeline, uint32_t flags,
+		int recursion_level);
+	void EvaluateHostTracks(); // light / camera / material values and nested instance anims of the playing anims (host-side single values)
 	bool EnsureContext() const;
 	void RefreshTRSFromDevice() const;
 	void RefreshFlagsFromDevice() const;
@@ -329,6 +462,13 @@ private:
 	void FlushMatrixSets() const;
 	bool SyncEdits(const PipelineResources *resources);
 };
+
+// scene.h:915-933: a node with a transform (TRS decomposed from `mtx` by the device-free Decompose) and one component
+Node CreateObject(Scene &scene, const Mat4 &mtx, const ModelRef &model, std::vector<Material> materials = {});
+Node CreatePointLight(Scene &scene, const Mat4 &mtx, float radius, const Color &diffuse = {1, 1, 1}, float diffuse_intensity = 1,
+	const Color &specular = {1, 1, 1}, float specular_intensity = 1, float priority = 0.f, LightShadowType shadow_type = LST_None,
+	float shadow_bias = default_shadow_bias);
+Node CreateCamera(Scene &scene, const Mat4 &mtx, float znear, float zfar, float fov = 0.69813170079f);
 
 // scene.h:962-974
 bool LoadSceneBinaryFromFile(const char *path, Scene &scene, PipelineResources &resources, const PipelineInfo &pipeline, LoadSceneContext &ctx,

@@ -4,6 +4,7 @@
 // Nothing in this file computes a world matrix, samples a key or tests a frustum: without a CUDA device those members warn and return.
 #include "engine/scene.h"
 #include "foundation/log.h"
+#include "hg_scene_impl.h"
 #include "hgb200.h"
 
 #include <algorithm>
@@ -122,45 +123,6 @@ private:
 	bool quit{false};
 };
 } // namespace
-
-struct Scene::Impl {
-	bool topology_dirty{true};
-	bool trs_all_dirty{true};
-	std::vector<uint32_t> dirty_trs;
-	bool anims_dirty{true};
-	struct CamTrack { // a playing "Camera.Fov" float track: evaluated on the host every frame (one float per camera)
-		uint32_t play_idx;
-		ComponentRef cam;
-		AnimRef anim;
-		int track;
-	};
-	std::vector<CamTrack> cam_tracks; // in evaluation order (plays, then node anims), rebuilt with the bindings
-	bool entries_dirty{true};
-	bool views_dirty{false};
-	bool in_frame{false}; // between ReadyWorldMatrices and ComputeWorldMatrices: SetNodeWorldMatrix records presets
-	const PipelineResources *resources{nullptr};
-	std::vector<Frustum> frusta;
-	std::vector<uint32_t> preset_slots;
-	std::vector<float> preset_mats;
-	std::vector<std::pair<uint32_t, uint32_t>> enable_nodes; // (transform slot, node index) of the nodes driven by an "Enable" track
-	bool enable_state_push{false};     // the host's flags of the tracked nodes must be pushed (tracks were (re)bound or entries rebuilt)
-	bool flags_stale{false};           // the device evaluated Enable tracks: NF_Disabled of those nodes is refreshed before the host reads it
-	uint32_t device_slots{0};          // slots of the topology the device currently holds
-	std::vector<uint32_t> fresh_slots; // transforms created since then: their host TRS is newer than whatever the device has in that slot
-	std::vector<uint32_t> set_slots; // queued SetTransformWorld/LocalMatrix calls (one mode per queue)
-	std::vector<float> set_mats;
-	bool set_local{false};
-	std::vector<int64_t> play_t;        // evaluation time per play slot (HGB_NOT_PLAYING when idle)
-	std::vector<float> staging;
-	// fused culling: the entry tables given to the device (every entry, disabled ones flagged) and what they map back to
-	std::vector<ModelDisplayList> ent[2];
-	std::vector<uint8_t> ent_flags[2];
-	// ComputeSkinMatrices cache
-	std::vector<uint32_t> skin_mtx, skin_bind;
-	size_t skin_bind_count{0};
-	bool warned_no_device{false};
-	bool rebind_after_frame{false}; // a finished ALM_Once anim is evaluated one last time, then its tracks are unbound
-};
 
 static void check(int rc) {
 	if (rc)
@@ -835,10 +797,113 @@ static bool evaluate_hermite(const AnimTrackHermiteT<float> &track, time_ns t, f
 	return true;
 }
 
+// Evaluate* for the single-value targets, generic over the number of float components (float, Color, Vec4): EvaluateHermite above
+// component by component (the reference's operators on Color / Vec4 are component-wise, foundation/color.cpp:13-21, vector4.h:153-154)
+template <typename T, int N> static bool evaluate_hermite_n(const AnimTrackHermiteT<T> &track, time_ns t, float *out) {
+	AnimTrackHermiteT<float> one;
+	one.keys.resize(track.keys.size());
+	if (track.keys.empty())
+		return false;
+	for (int c = 0; c < N; ++c) {
+		for (size_t k = 0; k < track.keys.size(); ++k) {
+			const float *v = reinterpret_cast<const float *>(&track.keys[k].v);
+			one.keys[k].t = track.keys[k].t, one.keys[k].v = v[c], one.keys[k].tension = track.keys[k].tension, one.keys[k].bias = track.keys[k].bias;
+		}
+		evaluate_hermite(one, t, out[c]);
+	}
+	return true;
+}
+
+// EvaluateStep (animation.h:130-139) over GetIntervalKeys (:109-128): the key at or before t, the first key before the track starts
+template <typename Key> static int step_key(const std::vector<Key> &keys, time_ns t) {
+	int i = 0;
+	const int n = int(keys.size());
+	while (i < n && !(keys[i].t > t))
+		++i;
+	return i > 0 ? i - 1 : 0;
+}
+
+// clock of a nested instance anim (scene.cpp:2243-2264), exact integer arithmetic
+static time_ns nested_time(const AnimKeyT<InstanceAnimKey> &key, time_ns t, const SceneAnim *sub) {
+	time_ns sub_t = ((t - key.t) * time_ns(key.v.t_scale * 256.f)) / 256;
+	if ((key.v.t_scale < 0.f || key.v.loop_mode == ALM_Loop) && sub) {
+		if (key.v.t_scale < 0.f)
+			sub_t += sub->t_end;
+		if (key.v.loop_mode == ALM_Loop && sub->t_end > sub->t_start) {
+			if (key.v.t_scale >= 0) {
+				while (sub_t >= sub->t_end)
+					sub_t -= sub->t_end - sub->t_start;
+			} else {
+				while (sub_t <= sub->t_start)
+					sub_t += sub->t_end - sub->t_start;
+			}
+		}
+	}
+	return sub_t;
+}
+// the key of an instance_anim_track in force at t: the last key with key.t <= t, -1 before the first (scene.cpp:2222-2225)
+static int instance_key(const Anim &anim, time_ns t) {
+	int kf = int(anim.instance_anim_track.keys.size()) - 1;
+	for (; kf >= 0; --kf)
+		if (t >= anim.instance_anim_track.keys[kf].t)
+			break;
+	return kf;
+}
+
+void Scene::EvaluateHostTracks() {
+	for (const Impl::HostTrack &ht : impl->host_tracks) {
+		if (ht.clock >= impl->play_t.size() || impl->play_t[ht.clock] == HGB_NOT_PLAYING || !anims.is_valid(ht.anim))
+			continue;
+		const time_ns t = impl->play_t[ht.clock];
+		const Anim &anim = anims[ht.anim.idx];
+		switch (ht.target) {
+		case Impl::HT_CameraFov:
+			if (cameras.is_valid(ht.comp) && size_t(ht.track) < anim.float_tracks.size())
+				evaluate_hermite(anim.float_tracks[ht.track], t, cameras[ht.comp.idx].fov);
+			break;
+		case Impl::HT_LightDiffuseIntensity:
+			if (lights.is_valid(ht.comp) && size_t(ht.track) < anim.float_tracks.size())
+				evaluate_hermite(anim.float_tracks[ht.track], t, lights[ht.comp.idx].diffuse_intensity);
+			break;
+		case Impl::HT_LightSpecularIntensity:
+			if (lights.is_valid(ht.comp) && size_t(ht.track) < anim.float_tracks.size())
+				evaluate_hermite(anim.float_tracks[ht.track], t, lights[ht.comp.idx].specular_intensity);
+			break;
+		case Impl::HT_LightDiffuse:
+			if (lights.is_valid(ht.comp) && size_t(ht.track) < anim.color_tracks.size())
+				evaluate_hermite_n<Color, 4>(anim.color_tracks[ht.track], t, &lights[ht.comp.idx].diffuse.r);
+			break;
+		case Impl::HT_LightSpecular:
+			if (lights.is_valid(ht.comp) && size_t(ht.track) < anim.color_tracks.size())
+				evaluate_hermite_n<Color, 4>(anim.color_tracks[ht.track], t, &lights[ht.comp.idx].specular.r);
+			break;
+		case Impl::HT_MaterialValue:
+			if (objects.is_valid(ht.comp) && size_t(ht.track) < anim.vec4_tracks.size()) {
+				Object_ &obj = objects[ht.comp.idx];
+				if (ht.mat_slot >= obj.materials.size())
+					break; // invalid material slot
+				auto i = obj.materials[ht.mat_slot].values.find(ht.mat_value);
+				if (i == obj.materials[ht.mat_slot].values.end())
+					break; // invalid material value name
+				float v[4];
+				if (evaluate_hermite_n<Vec4, 4>(anim.vec4_tracks[ht.track], t, v))
+					i->second.value = {v[0], v[1], v[2], v[3]};
+			}
+			break;
+		case Impl::HT_EnableInstanceHost: // "Enable" on a node that hosts an instance: the switch propagates to the instantiated nodes
+			if (nodes.is_valid(ht.node) && size_t(ht.track) < anim.bool_tracks.size() && !anim.bool_tracks[ht.track].keys.empty()) {
+				const auto &keys = anim.bool_tracks[ht.track].keys;
+				const bool enable = keys[step_key(keys, t)].v;
+				if (enable != IsNodeItselfEnabled(ht.node))
+					enable ? EnableNode(ht.node) : DisableNode(ht.node);
+			}
+			break;
+		}
+	}
+}
+
 void Scene::UpdatePlayingAnims(time_ns dt) {
-	if (impl->anims_dirty)
-		SyncEdits(impl->resources); // (re)binds tracks and assigns play slots
-	std::fill(impl->play_t.begin(), impl->play_t.end(), HGB_NOT_PLAYING);
+	// clocks first (scene.cpp:2386-2413): they do not depend on the bindings
 	std::vector<uint32_t> finished;
 	for (uint32_t i = play_anims.first(); i != play_anims.invalid_idx; i = play_anims.next(i)) {
 		ScenePlayAnim_ &p = play_anims[i];
@@ -859,12 +924,56 @@ void Scene::UpdatePlayingAnims(time_ns dt) {
 				finished.push_back(i); // evaluated one last time this frame, then removed
 			}
 		}
-		if (p.play_slot < impl->play_t.size())
-			impl->play_t[p.play_slot] = p.t;
 	}
-	for (const Impl::CamTrack &ct : impl->cam_tracks) // finished plays are evaluated one last time, like every other target
-		if (play_anims.is_used(ct.play_idx) && cameras.is_valid(ct.cam) && anims.is_valid(ct.anim) && size_t(ct.track) < anims[ct.anim.idx].float_tracks.size())
-			evaluate_hermite(anims[ct.anim.idx].float_tracks[ct.track], play_anims[ct.play_idx].t, cameras[ct.cam.idx].fov);
+	if (impl->anims_dirty)
+		SyncEdits(impl->resources); // (re)binds tracks and assigns play slots
+
+	// nested instance anims: the key in force may have moved on -> the tracks of another scene anim must be bound
+	std::vector<time_ns> nt;
+	std::vector<uint8_t> active;
+	auto walk_nested = [&]() -> bool {
+		bool changed = false;
+		nt.assign(impl->nested.size(), 0);
+		active.assign(impl->nested.size(), 0);
+		for (size_t i = 0; i < impl->nested.size(); ++i) {
+			Impl::Nested &r = impl->nested[i];
+			time_ns t_parent;
+			if (r.parent < 0) {
+				if (!play_anims.is_used(r.play_idx))
+					continue;
+				t_parent = play_anims[r.play_idx].t;
+			} else {
+				if (!active[r.parent] || !scene_anims.is_valid(impl->nested[r.parent].sub))
+					continue;
+				t_parent = nt[r.parent];
+			}
+			if (!anims.is_valid(r.anim))
+				continue;
+			const Anim &anim = anims[r.anim.idx];
+			const int kf = instance_key(anim, t_parent);
+			if (kf != r.kf)
+				changed = true;
+			active[i] = 1;
+			if (kf >= 0 && kf == r.kf && scene_anims.is_valid(r.sub))
+				nt[i] = nested_time(anim.instance_anim_track.keys[kf], t_parent, &scene_anims[r.sub.idx]);
+		}
+		return changed;
+	};
+	if (walk_nested()) {
+		impl->anims_dirty = true;
+		SyncEdits(impl->resources);
+		walk_nested();
+	}
+
+	std::fill(impl->play_t.begin(), impl->play_t.end(), HGB_NOT_PLAYING);
+	for (uint32_t i = play_anims.first(); i != play_anims.invalid_idx; i = play_anims.next(i))
+		if (play_anims[i].play_slot < impl->play_t.size())
+			impl->play_t[play_anims[i].play_slot] = play_anims[i].t;
+	for (size_t i = 0; i < impl->nested.size(); ++i)
+		if (active[i] && impl->nested[i].kf >= 0 && scene_anims.is_valid(impl->nested[i].sub) && impl->nested[i].play_slot < impl->play_t.size())
+			impl->play_t[impl->nested[i].play_slot] = nt[i];
+
+	EvaluateHostTracks(); // finished plays are evaluated one last time, like every other target
 	for (uint32_t i : finished)
 		play_anims.remove(i);
 	if (!finished.empty())
@@ -952,82 +1061,137 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 		std::vector<int64_t> en_t;
 		std::vector<uint8_t> en_v;
 		impl->enable_nodes.clear();
-		impl->cam_tracks.clear();
+		impl->host_tracks.clear();
+		impl->nested.clear();
 		uint32_t n_play = 0;
-		for (uint32_t pi = play_anims.first(); pi != play_anims.invalid_idx; pi = play_anims.next(pi)) {
-			ScenePlayAnim_ &p = play_anims[pi];
-			p.play_slot = n_play++;
-			if (p.play_slot >= 65535) {
-				warn("Too many playing anims for one device context (65535)");
-				break;
-			}
-			if (!scene_anims.is_valid(p.scene_anim))
-				continue;
-			for (const NodeAnim &na : scene_anims[p.scene_anim.idx].node_anims) {
-				if (!anims.is_valid(na.anim) || !nodes.is_valid(na.node))
+		for (uint32_t pi = play_anims.first(); pi != play_anims.invalid_idx; pi = play_anims.next(pi))
+			play_anims[pi].play_slot = n_play++;
+		if (n_play >= 65535)
+			warn("Too many playing anims for one device context (65535)");
+
+		// one scene anim evaluated at the clock of `slot` (a play, or a nested instance anim): its node anims in order, for each the
+		// host-side single values, the "Enable" switch, Position / Rotation / Scale, then the instantiated scene's anim its
+		// instance_anim_track selects at `t_now` (recursion, like EvaluateBoundAnim scene.cpp:2154-2268)
+		std::function<void(const SceneAnim &, uint32_t, time_ns, int, uint32_t, int)> flatten = [&](const SceneAnim &sa, uint32_t slot, time_ns t_now, int parent,
+																									 uint32_t play_idx, int depth) {
+			for (const NodeAnim &na : sa.node_anims) {
+				if (!anims.is_valid(na.anim) || !nodes.is_valid(na.node) || slot >= 65535)
 					continue;
 				const Anim &anim = anims[na.anim.idx];
-				if (cameras.is_valid(nodes[na.node.idx].camera)) { // the last "Camera.Fov" float track (BindNodeAnim scene.cpp:2091-2101)
+				const Node_ &node = nodes[na.node.idx];
+				const bool hosts_instance = node_instance_view.find(na.node) != node_instance_view.end();
+				int en = -1; // "Enable" bool track: the last one with that target (BindNodeAnim scene.cpp:2083-2089)
+				for (size_t i = 0; i < anim.bool_tracks.size(); ++i)
+					if (anim.bool_tracks[i].target == "Enable")
+						en = int(i);
+				const ComponentRef t = node.transform;
+				if (en >= 0 && (hosts_instance || !transforms.is_valid(t))) { // the switch reaches other nodes too / has no device row: host side
+					impl->host_tracks.push_back({Impl::HT_EnableInstanceHost, slot, InvalidComponentRef, na.node, na.anim, en, 0, {}});
+				} else if (en >= 0) {
+					const auto &keys = anim.bool_tracks[en].keys;
+					en_tracks.push_back(hgb_track{t.idx, uint32_t(en_t.size()), uint32_t(keys.size()), uint16_t(slot), 4, 0});
+					for (const auto &k : keys)
+						en_t.push_back(k.t), en_v.push_back(k.v ? 1 : 0);
+					impl->enable_nodes.push_back({t.idx, na.node.idx});
+				}
+				if (transforms.is_valid(t)) {
+					int pos = -1, rot = -1, scl = -1, qrot = -1;
+					for (size_t i = 0; i < anim.vec3_tracks.size(); ++i) {
+						const std::string &tg = anim.vec3_tracks[i].target;
+						if (tg == "Position") pos = int(i);
+						else if (tg == "Rotation") rot = int(i);
+						else if (tg == "Scale") scl = int(i);
+					}
+					for (size_t i = 0; i < anim.quat_tracks.size(); ++i)
+						if (anim.quat_tracks[i].target == "Rotation")
+							qrot = int(i);
+					auto add_v3 = [&](int idx, uint8_t kind) {
+						if (idx < 0)
+							return;
+						const auto &keys = anim.vec3_tracks[idx].keys;
+						hgb_track tr{t.idx, uint32_t(v3_t.size()), uint32_t(keys.size()), uint16_t(slot), kind, 0};
+						for (const auto &k : keys) {
+							v3_t.push_back(k.t);
+							v3_val.push_back(k.v.x), v3_val.push_back(k.v.y), v3_val.push_back(k.v.z);
+							v3_tension.push_back(k.tension), v3_bias.push_back(k.bias);
+						}
+						tracks.push_back(tr);
+					};
+					add_v3(pos, 0);
+					if (anim.flags & AF_UseQuaternionForRotation) {
+						if (qrot >= 0) {
+							const auto &keys = anim.quat_tracks[qrot].keys;
+							hgb_track tr{t.idx, uint32_t(q_t.size()), uint32_t(keys.size()), uint16_t(slot), 3, 0};
+							for (const auto &k : keys) {
+								q_t.push_back(k.t);
+								q_val.push_back(k.v.x), q_val.push_back(k.v.y), q_val.push_back(k.v.z), q_val.push_back(k.v.w);
+							}
+							tracks.push_back(tr);
+						}
+					} else {
+						add_v3(rot, 1);
+					}
+					add_v3(scl, 2);
+				}
+				// single host-side values, in the reference's order: light, camera, material (the LAST track with a matching target wins)
+				if (lights.is_valid(node.light)) {
+					int dif = -1, spc = -1, dif_i = -1, spc_i = -1;
+					for (size_t i = 0; i < anim.color_tracks.size(); ++i) {
+						if (anim.color_tracks[i].target == "Light.Diffuse") dif = int(i);
+						else if (anim.color_tracks[i].target == "Light.Specular") spc = int(i);
+					}
+					for (size_t i = 0; i < anim.float_tracks.size(); ++i) {
+						if (anim.float_tracks[i].target == "Light.DiffuseIntensity") dif_i = int(i);
+						else if (anim.float_tracks[i].target == "Light.SpecularIntensity") spc_i = int(i);
+					}
+					if (dif >= 0) impl->host_tracks.push_back({Impl::HT_LightDiffuse, slot, node.light, na.node, na.anim, dif, 0, {}});
+					if (spc >= 0) impl->host_tracks.push_back({Impl::HT_LightSpecular, slot, node.light, na.node, na.anim, spc, 0, {}});
+					if (dif_i >= 0) impl->host_tracks.push_back({Impl::HT_LightDiffuseIntensity, slot, node.light, na.node, na.anim, dif_i, 0, {}});
+					if (spc_i >= 0) impl->host_tracks.push_back({Impl::HT_LightSpecularIntensity, slot, node.light, na.node, na.anim, spc_i, 0, {}});
+				}
+				if (cameras.is_valid(node.camera)) { // the last "Camera.Fov" float track (BindNodeAnim scene.cpp:2091-2101)
 					int fov = -1;
 					for (size_t i = 0; i < anim.float_tracks.size(); ++i)
 						if (anim.float_tracks[i].target == "Camera.Fov")
 							fov = int(i);
 					if (fov >= 0)
-						impl->cam_tracks.push_back({pi, nodes[na.node.idx].camera, na.anim, fov});
+						impl->host_tracks.push_back({Impl::HT_CameraFov, slot, node.camera, na.node, na.anim, fov, 0, {}});
 				}
-				const ComponentRef t = nodes[na.node.idx].transform;
-				if (!transforms.is_valid(t))
-					continue;
-				int en = -1; // "Enable" bool track: the last one with that target (BindNodeAnim scene.cpp:2083-2089)
-				for (size_t i = 0; i < anim.bool_tracks.size(); ++i)
-					if (anim.bool_tracks[i].target == "Enable")
-						en = int(i);
-				if (en >= 0) {
-					const auto &keys = anim.bool_tracks[en].keys;
-					en_tracks.push_back(hgb_track{t.idx, uint32_t(en_t.size()), uint32_t(keys.size()), uint16_t(p.play_slot), 4, 0});
-					for (const auto &k : keys)
-						en_t.push_back(k.t), en_v.push_back(k.v ? 1 : 0);
-					impl->enable_nodes.push_back({t.idx, na.node.idx});
-				}
-				int pos = -1, rot = -1, scl = -1, qrot = -1;
-				for (size_t i = 0; i < anim.vec3_tracks.size(); ++i) {
-					const std::string &tg = anim.vec3_tracks[i].target;
-					if (tg == "Position") pos = int(i);
-					else if (tg == "Rotation") rot = int(i);
-					else if (tg == "Scale") scl = int(i);
-				}
-				for (size_t i = 0; i < anim.quat_tracks.size(); ++i)
-					if (anim.quat_tracks[i].target == "Rotation")
-						qrot = int(i);
-				auto add_v3 = [&](int idx, uint8_t kind) {
-					if (idx < 0)
-						return;
-					const auto &keys = anim.vec3_tracks[idx].keys;
-					hgb_track tr{t.idx, uint32_t(v3_t.size()), uint32_t(keys.size()), uint16_t(p.play_slot), kind, 0};
-					for (const auto &k : keys) {
-						v3_t.push_back(k.t);
-						v3_val.push_back(k.v.x), v3_val.push_back(k.v.y), v3_val.push_back(k.v.z);
-						v3_tension.push_back(k.tension), v3_bias.push_back(k.bias);
+				if (objects.is_valid(node.object))
+					for (size_t i = 0; i < anim.vec4_tracks.size(); ++i) { // "Material.<slot>.<value>" (SplitMaterialPropertyName scene.cpp:2056-2068)
+						const std::string &tg = anim.vec4_tracks[i].target;
+						if (tg.compare(0, 9, "Material.") != 0)
+							continue;
+						const size_t dot = tg.find('.', 9);
+						if (dot == std::string::npos || tg.find('.', dot + 1) != std::string::npos)
+							continue;
+						impl->host_tracks.push_back({Impl::HT_MaterialValue, slot, node.object, na.node, na.anim, int(i), uint8_t(atoi(tg.substr(9, dot - 9).c_str())),
+							tg.substr(dot + 1)});
 					}
-					tracks.push_back(tr);
-				};
-				add_v3(pos, 0);
-				if (anim.flags & AF_UseQuaternionForRotation) {
-					if (qrot >= 0) {
-						const auto &keys = anim.quat_tracks[qrot].keys;
-						hgb_track tr{t.idx, uint32_t(q_t.size()), uint32_t(keys.size()), uint16_t(p.play_slot), 3, 0};
-						for (const auto &k : keys) {
-							q_t.push_back(k.t);
-							q_val.push_back(k.v.x), q_val.push_back(k.v.y), q_val.push_back(k.v.z), q_val.push_back(k.v.w);
-						}
-						tracks.push_back(tr);
+				// the instantiated scene's anim selected by the step track (scene.cpp:2217-2268)
+				if (!anim.instance_anim_track.keys.empty() && hosts_instance && depth < 8) {
+					const SceneView &view = node_instance_view.find(na.node)->second;
+					Impl::Nested r{parent, play_idx, na.node, na.anim, instance_key(anim, t_now), InvalidSceneAnimRef, 0};
+					if (r.kf >= 0)
+						r.sub = view.GetSceneAnim(*this, anim.instance_anim_track.keys[r.kf].v.anim_name);
+					const bool bound = scene_anims.is_valid(r.sub);
+					if (bound)
+						r.play_slot = n_play++;
+					impl->nested.push_back(r);
+					if (bound) {
+						const int me = int(impl->nested.size()) - 1;
+						const SceneAnim &sub = scene_anims[r.sub.idx];
+						flatten(sub, r.play_slot, nested_time(anim.instance_anim_track.keys[r.kf], t_now, &sub), me, play_idx, depth + 1);
 					}
-				} else {
-					add_v3(rot, 1);
 				}
-				add_v3(scl, 2);
 			}
+		};
+		for (uint32_t pi = play_anims.first(); pi != play_anims.invalid_idx; pi = play_anims.next(pi)) {
+			const ScenePlayAnim_ &p = play_anims[pi];
+			if (scene_anims.is_valid(p.scene_anim))
+				flatten(scene_anims[p.scene_anim.idx], p.play_slot, p.t, -1, pi, 0);
 		}
+		impl->n_play_slots = n_play;
 		check(hgb_set_anim_keys(ctx, uint32_t(v3_t.size()), v3_t.data(), v3_val.data(), v3_tension.data(), v3_bias.data(), uint32_t(q_t.size()), q_t.data(),
 			q_val.data()));
 		check(hgb_set_tracks(ctx, uint32_t(tracks.size()), tracks.data(), n_play));

@@ -8,7 +8,7 @@ timeout 900 $TR tests/mgpu_peer_check.py > gpurun_out/peer_check_n$N.log 2>&1; e
 run() { n=$1; shift; timeout 900 env $ENVV $TR bench.py --gpus $N --no-cpu-baseline "$@" > gpurun_out/${n}_n$N.json 2> gpurun_out/${n}_n$N.err; echo "$n exit $?"; python - <<PY
 import json
 try:
-    d=json.load(open("gpurun_out/${n}_n$N.json"))
+    d=json.loads([l for l in open("gpurun_out/${n}_n$N.json") if l.startswith("{")][-1])
     print("  ms/step %.4f value %.0f e2e %.0f exch %s"%(d["ms_per_step"],d["value"],d["e2e"]["value"],d.get("exchange_check")), {k:round(v,4) for k,v in d["roofline"]["kernel_ms_per_step"].items()})
 except Exception as e:
     print("  failed", e); print(open("gpurun_out/${n}_n$N.err").read()[-1500:])
