@@ -236,28 +236,6 @@ bool Scene::IsNodeEnabled(NodeRef ref) const {
 	return !(nodes[ref.idx].flags & (NF_Disabled | NF_InstanceDisabled));
 }
 
-void Scene::EnableNode(NodeRef ref) {
-	if (!nodes.is_valid(ref)) {
-		warn("Invalid node reference");
-		return;
-	}
-	RefreshFlagsFromDevice();
-	nodes[ref.idx].flags &= ~NF_Disabled;
-	impl->entries_dirty = true;
-	impl->enable_state_push = true;
-}
-
-void Scene::DisableNode(NodeRef ref) {
-	if (!nodes.is_valid(ref)) {
-		warn("Invalid node reference");
-		return;
-	}
-	RefreshFlagsFromDevice();
-	nodes[ref.idx].flags |= NF_Disabled;
-	impl->entries_dirty = true;
-	impl->enable_state_push = true;
-}
-
 bool Scene::IsChildOf(NodeRef node, NodeRef parent) const { // walk up from `node`; bounded by the node count against corrupted graphs
 	size_t guard = nodes.capacity() + 1;
 	while (guard--) {
@@ -1629,6 +1607,30 @@ size_t Scene::GarbageCollect() {
 		const uint32_t nx = cameras.next(i);
 		if (!cam_used[i]) {
 			cameras.remove_ref(cameras.get_ref(i));
+			++removed;
+		}
+		i = nx;
+	}
+	std::vector<uint8_t> lgt_used(lights.capacity(), 0);
+	for (uint32_t ni = nodes.first(); ni != nodes.invalid_idx; ni = nodes.next(ni))
+		if (lights.is_valid(nodes[ni].light))
+			lgt_used[nodes[ni].light.idx] = 1;
+	for (uint32_t i = lights.first(); i != lights.invalid_idx;) {
+		const uint32_t nx = lights.next(i);
+		if (!lgt_used[i]) {
+			lights.remove_ref(lights.get_ref(i));
+			++removed;
+		}
+		i = nx;
+	}
+	std::vector<uint8_t> inst_used(instances.capacity(), 0);
+	for (const auto &ni : node_instance)
+		if (nodes.is_valid(ni.first) && instances.is_valid(ni.second))
+			inst_used[ni.second.idx] = 1;
+	for (uint32_t i = instances.first(); i != instances.invalid_idx;) {
+		const uint32_t nx = instances.next(i);
+		if (!inst_used[i]) {
+			instances.remove_ref(instances.get_ref(i));
 			++removed;
 		}
 		i = nx;

@@ -5,7 +5,8 @@
 // Byte layout follows what the reference WRITES (harfang/engine/scene_load_binary.cpp:237-541 Save_binary, :16-98 SaveComponent,
 // harfang/engine/render_pipeline.cpp:1317-1349 SaveMaterial, harfang/engine/anim_load_binary.cpp:42-98 SaveAnim*, strings =
 // u16 length + bytes, harfang/foundation/rw_interface.cpp:34-37) and is consumed in the order Load_binary reads it (:549-905).
-// Components this path has no use for (cameras, lights, physics, scripts, instances, environment, key/values) are parsed and dropped.
+// Components this path has no use for (physics, scripts, environment, key/values) are parsed and dropped; lights and instances are kept
+// (animation targets, NF_InstanceDisabled propagation, nested instance anims).
 // Resources are never loaded from disk here: a model name resolves to the model registered under that name in `resources`, or to an
 // empty placeholder registered now (LSSF_DoNotLoadResources behaviour, render_pipeline.cpp:1669-1672).
 #include "engine/scene.h"
@@ -181,7 +182,25 @@ void read_anim(Cursor &c, Anim &anim) { // LoadAnimFromBinary, anim_load_binary.
 			sort_keys(t);
 		}
 	}
-	skip_tracks(c, 8 + 16 + 8); // vec4, Hermite
+	{                           // vec4, Hermite: "Material.<slot>.<value>"
+		const uint32_t n = c.get<uint32_t>();
+		anim.vec4_tracks.resize(c.ok ? n : 0);
+		for (auto &t : anim.vec4_tracks) {
+			t.target = c.str();
+			const uint32_t k = c.get<uint32_t>();
+			if (!c.ok || size_t(c.end - c.p) < size_t(k) * 32) {
+				c.ok = false;
+				return;
+			}
+			t.keys.resize(k);
+			for (auto &key : t.keys) {
+				key.t = c.get<int64_t>();
+				key.v.x = c.get<float>(), key.v.y = c.get<float>(), key.v.z = c.get<float>(), key.v.w = c.get<float>();
+				key.tension = c.get<float>(), key.bias = c.get<float>();
+			}
+			sort_keys(t);
+		}
+	}
 	{                           // quaternion, linear
 		const uint32_t n = c.get<uint32_t>();
 		anim.quat_tracks.resize(c.ok ? n : 0);
@@ -200,7 +219,25 @@ void read_anim(Cursor &c, Anim &anim) { // LoadAnimFromBinary, anim_load_binary.
 			sort_keys(t);
 		}
 	}
-	skip_tracks(c, 8 + 16 + 8); // colour, Hermite
+	{                           // colour, Hermite: "Light.Diffuse", "Light.Specular"
+		const uint32_t n = c.get<uint32_t>();
+		anim.color_tracks.resize(c.ok ? n : 0);
+		for (auto &t : anim.color_tracks) {
+			t.target = c.str();
+			const uint32_t k = c.get<uint32_t>();
+			if (!c.ok || size_t(c.end - c.p) < size_t(k) * 32) {
+				c.ok = false;
+				return;
+			}
+			t.keys.resize(k);
+			for (auto &key : t.keys) {
+				key.t = c.get<int64_t>();
+				key.v.r = c.get<float>(), key.v.g = c.get<float>(), key.v.b = c.get<float>(), key.v.a = c.get<float>();
+				key.tension = c.get<float>(), key.bias = c.get<float>();
+			}
+			sort_keys(t);
+		}
+	}
 	{                           // string tracks: variable-size keys
 		const uint32_t n = c.get<uint32_t>();
 		for (uint32_t i = 0; i < n && c.ok; ++i) {
@@ -215,10 +252,15 @@ void read_anim(Cursor &c, Anim &anim) { // LoadAnimFromBinary, anim_load_binary.
 	if (version >= 2) { // instance anim track
 		const uint32_t k = c.get<uint32_t>();
 		for (uint32_t j = 0; j < k && c.ok; ++j) {
-			c.skip(8);
-			c.str();
-			c.skip(1 + 4);
+			AnimKeyT<InstanceAnimKey> key;
+			key.t = c.get<int64_t>();
+			key.v.anim_name = c.str();
+			key.v.loop_mode = AnimLoopMode(c.get<uint8_t>());
+			key.v.t_scale = c.get<float>();
+			if (c.ok)
+				anim.instance_anim_track.keys.push_back(std::move(key));
 		}
+		sort_keys(anim.instance_anim_track);
 	}
 }
 
@@ -226,7 +268,7 @@ void read_anim(Cursor &c, Anim &anim) { // LoadAnimFromBinary, anim_load_binary.
 
 uint32_t GetSceneBinaryFormatVersion() { return 9; }
 
-bool Scene::Load_binary(const void *data, size_t size, const char *name, PipelineResources &resources, const PipelineInfo &, LoadSceneContext &ctx, uint32_t load_flags) {
+bool Scene::Load_binary(const void *data, size_t size, const char *name, PipelineResources &resources, const PipelineInfo &pipeline, LoadSceneContext &ctx, uint32_t load_flags) {
 	Cursor c{static_cast<const uint8_t *>(data), static_cast<const uint8_t *>(data) + size};
 	char msg[256];
 	auto refuse = [&](const char *why) {
@@ -293,8 +335,23 @@ bool Scene::Load_binary(const void *data, size_t size, const char *name, Pipelin
 			b = NodeRef{c.get<uint32_t>(), 0xffffffffu};
 		object_refs.push_back(objects.add_ref(std::move(o)));
 	}
-	const uint32_t light_count = c.get<uint32_t>();
-	c.skip(size_t(light_count) * 84); // type, shadow type, 2 x (colour + intensity), radius, 2 angles, pssm split, priority, shadow bias
+	const uint32_t light_count = c.get<uint32_t>(); // scene_load_binary.cpp:148-161: 84 bytes each
+	if (size_t(c.end - c.p) < size_t(light_count) * 84)
+		c.ok = false;
+	std::vector<ComponentRef> light_refs(c.ok ? light_count : 0);
+	for (uint32_t i = 0; i < light_count && c.ok; ++i) {
+		Light_ l;
+		l.type = LightType(c.get<uint32_t>());
+		l.shadow_type = LightShadowType(c.get<uint32_t>());
+		l.diffuse.r = c.get<float>(), l.diffuse.g = c.get<float>(), l.diffuse.b = c.get<float>(), l.diffuse.a = c.get<float>();
+		l.diffuse_intensity = c.get<float>();
+		l.specular.r = c.get<float>(), l.specular.g = c.get<float>(), l.specular.b = c.get<float>(), l.specular.a = c.get<float>();
+		l.specular_intensity = c.get<float>();
+		l.radius = c.get<float>(), l.inner_angle = c.get<float>(), l.outer_angle = c.get<float>();
+		l.pssm_split.x = c.get<float>(), l.pssm_split.y = c.get<float>(), l.pssm_split.z = c.get<float>(), l.pssm_split.w = c.get<float>();
+		l.priority = c.get<float>(), l.shadow_bias = c.get<float>();
+		light_refs[i] = lights.add_ref(l);
+	}
 	if (file_flags & LSSF_Physics) {
 		const uint32_t rigid_body_count = c.get<uint32_t>();
 		c.skip(size_t(rigid_body_count) * 6);
@@ -322,17 +379,20 @@ bool Scene::Load_binary(const void *data, size_t size, const char *name, Pipelin
 			}
 		}
 	}
-	const uint32_t instance_count = c.get<uint32_t>();
+	const uint32_t instance_count = c.get<uint32_t>(); // scene_load_binary.cpp:203-207
+	std::vector<ComponentRef> instance_refs;
 	for (uint32_t i = 0; i < instance_count && c.ok; ++i) {
-		c.str();
-		c.str();
-		c.skip(1);
+		Instance_ inst;
+		inst.name = c.str();
+		inst.anim = c.str();
+		inst.loop_mode = AnimLoopMode(c.get<uint8_t>());
+		instance_refs.push_back(instances.add_ref(std::move(inst)));
 	}
 	if (!c.ok)
 		return refuse("truncated component tables");
 
 	// ---- nodes ----
-	std::vector<NodeRef> nodes_to_disable;
+	std::vector<NodeRef> nodes_to_disable, nodes_with_instance;
 	if (file_flags & LSSF_Nodes) {
 		const uint32_t node_count = c.get<uint32_t>();
 		nodes.reserve(nodes.capacity() + std::min<size_t>(node_count, size_t(c.end - c.p)));
@@ -344,7 +404,9 @@ bool Scene::Load_binary(const void *data, size_t size, const char *name, Pipelin
 			const uint32_t transform_idx = c.get<uint32_t>();
 			const uint32_t camera_idx = c.get<uint32_t>();
 			const uint32_t object_idx = c.get<uint32_t>();
-			c.skip(4); // light
+			const uint32_t light_idx = c.get<uint32_t>();
+			if (light_idx != 0xffffffffu && light_idx < light_refs.size())
+				n.light = light_refs[light_idx];
 			if (transform_idx != 0xffffffffu && transform_idx < transform_refs.size())
 				n.transform = transform_refs[transform_idx];
 			if (object_idx != 0xffffffffu && object_idx < object_refs.size())
@@ -360,10 +422,14 @@ bool Scene::Load_binary(const void *data, size_t size, const char *name, Pipelin
 				const uint32_t n_scr = c.get<uint32_t>();
 				c.skip(size_t(n_scr) * 4);
 			}
-			c.skip(4); // instance
+			const uint32_t instance_idx = c.get<uint32_t>();
 			if (!c.ok)
 				break;
 			const NodeRef ref = nodes.add_ref(std::move(n));
+			if (instance_idx != 0xffffffffu && instance_idx < instance_refs.size()) {
+				node_instance[ref] = instance_refs[instance_idx];
+				nodes_with_instance.push_back(ref);
+			}
 			ctx.node_refs[saved_idx] = ref;
 			ctx.view.nodes.push_back(ref);
 			if (node_flags & NF_Disabled)
@@ -391,6 +457,18 @@ bool Scene::Load_binary(const void *data, size_t size, const char *name, Pipelin
 	} else {
 		for (const ComponentRef &r : transform_refs)
 			transforms[r.idx].parent = InvalidNodeRef;
+	}
+
+	// ---- instances (scene_load_binary.cpp:714-722): each instance node loads its scene file under itself, then starts its
+	// on-instantiate anim. Like the reference, not under LSSF_DoNotLoadResources. ----
+	if (!(load_flags & LSSF_DoNotLoadResources) && c.ok) {
+		for (const NodeRef &ref : nodes_to_disable) // the host's state decides NF_InstanceDisabled of what it instantiates
+			if (nodes.is_valid(ref))
+				nodes[ref.idx].flags |= NF_Disabled;
+		for (const NodeRef &ref : nodes_with_instance) {
+			NodeSetupInstanceFromFile(ref, resources, pipeline, LSSF_All | (load_flags & LSSF_DoNotLoadResources), ctx.recursion_level + 1);
+			NodeStartOnInstantiateAnim(ref);
+		}
 	}
 
 	// ---- scene block (environment, canvas): nothing the update path reads ----

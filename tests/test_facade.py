@@ -485,3 +485,21 @@ def test_facade_camera_fov_track_matches_reference(fac, ref):
                 assert (bits(x) == bits(y)).all(), (frame, an)
     assert len(seen) > 12  # the value really moves
     a.close(); b.close()
+
+
+def test_reference_unit_tests_against_facade():
+    """the reference's own scene unit tests (harfang/tests/engine/scene.cpp: ComponentGarbageCollection :27-33, WalkHierarchy :55-81,
+    DisableObjectNodes :115-154), cut out of the reference source at build time and compiled UNCHANGED against the facade headers with the
+    reference's test framework (oracle/facade_unit.cpp, `make -C oracle facade_unit`). Host only: no device call is reached."""
+    import subprocess
+    oracle_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle")
+    exe = os.path.join(oracle_dir, "_ref", "facade_unit")
+    if os.path.isdir("/root/reference/harfang"):
+        subprocess.check_call(["make", "-C", oracle_dir, "facade_unit"], stdout=subprocess.DEVNULL)
+    if not os.path.exists(exe):
+        pytest.skip("needs the reference sources (or the prebuilt oracle/_ref/facade_unit)")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    for name in ("ComponentGarbageCollection", "WalkHierarchy", "DisableObjectNodes"):
+        assert ("engine.scene.%s" % name) in r.stdout and "[ OK ]" in r.stdout
+    assert "All unit tests have passed" in r.stdout
