@@ -289,6 +289,116 @@ int hgref_is_playing(void *h, int play) {
 	return c->scene->IsPlaying(c->play_anims[play]) ? 1 : 0;
 }
 
+// ---- lights, material values, scene instances (single-value animation targets and NF_InstanceDisabled propagation) --------------------
+int hgref_add_point_light(void *h, int node, float radius) {
+	auto *c = static_cast<RefCtx *>(h);
+	c->scene->SetNodeLight(c->nodes[node], c->scene->CreatePointLight(radius).ref);
+	return 1;
+}
+// out10: diffuse rgba, diffuse intensity, specular rgba, specular intensity
+void hgref_get_light(void *h, int node, float *out10) {
+	auto *c = static_cast<RefCtx *>(h);
+	const auto l = c->scene->GetNodeLightRef(c->nodes[node]);
+	const Color d = c->scene->GetLightDiffuseColor(l), s = c->scene->GetLightSpecularColor(l);
+	const float o[10] = {d.r, d.g, d.b, d.a, c->scene->GetLightDiffuseIntensity(l), s.r, s.g, s.b, s.a, c->scene->GetLightSpecularIntensity(l)};
+	memcpy(out10, o, sizeof(o));
+}
+int hgref_anim_add_color_track(void *h, int anim, const char *target, int n_keys, const int64_t *t, const float *v4, const float *tension, const float *bias) {
+	auto *c = static_cast<RefCtx *>(h);
+	Anim *a = c->scene->GetAnim(c->anims[anim]);
+	AnimTrackHermiteT<Color> trk;
+	trk.target = target;
+	for (int i = 0; i < n_keys; ++i) {
+		AnimKeyHermiteT<Color> k;
+		k.t = t[i];
+		k.v = Color(v4[i * 4], v4[i * 4 + 1], v4[i * 4 + 2], v4[i * 4 + 3]);
+		k.tension = tension ? tension[i] : 0.f;
+		k.bias = bias ? bias[i] : 0.f;
+		trk.keys.push_back(k);
+	}
+	a->color_tracks.push_back(trk);
+	return int(a->color_tracks.size()) - 1;
+}
+int hgref_anim_add_vec4_track(void *h, int anim, const char *target, int n_keys, const int64_t *t, const float *v4, const float *tension, const float *bias) {
+	auto *c = static_cast<RefCtx *>(h);
+	Anim *a = c->scene->GetAnim(c->anims[anim]);
+	AnimTrackHermiteT<Vec4> trk;
+	trk.target = target;
+	for (int i = 0; i < n_keys; ++i) {
+		AnimKeyHermiteT<Vec4> k;
+		k.t = t[i];
+		k.v = Vec4(v4[i * 4], v4[i * 4 + 1], v4[i * 4 + 2], v4[i * 4 + 3]);
+		k.tension = tension ? tension[i] : 0.f;
+		k.bias = bias ? bias[i] : 0.f;
+		trk.keys.push_back(k);
+	}
+	a->vec4_tracks.push_back(trk);
+	return int(a->vec4_tracks.size()) - 1;
+}
+void hgref_set_material_value(void *h, int node, int slot, const char *name, const float *v4) {
+	auto *c = static_cast<RefCtx *>(h);
+	SetMaterialValue(c->scene->GetObjectMaterial(c->scene->GetNodeObjectRef(c->nodes[node]), size_t(slot)), name, Vec4(v4[0], v4[1], v4[2], v4[3]));
+}
+int hgref_get_material_value(void *h, int node, int slot, const char *name, float *out4) {
+	auto *c = static_cast<RefCtx *>(h);
+	Material &m = c->scene->GetObjectMaterial(c->scene->GetNodeObjectRef(c->nodes[node]), size_t(slot));
+	const auto i = m.values.find(name);
+	if (i == m.values.end() || i->second.value.size() < 4)
+		return 0;
+	memcpy(out4, i->second.value.data(), 16);
+	return 1;
+}
+void hgref_set_scene_anim_name(void *h, int scene_anim, const char *name) {
+	auto *c = static_cast<RefCtx *>(h);
+	if (SceneAnim *sa = c->scene->GetSceneAnim(c->scene_anims[scene_anim]))
+		sa->name = name;
+}
+// an Instance component on `node`: scene file `path`, anim started on instantiation (may be empty)
+int hgref_add_instance(void *h, int node, const char *path, const char *anim, int loop_mode) {
+	auto *c = static_cast<RefCtx *>(h);
+	Instance inst = c->scene->CreateInstance(path);
+	inst.SetOnInstantiateAnim(anim ? anim : "");
+	inst.SetOnInstantiateAnimLoopMode(AnimLoopMode(loop_mode));
+	c->scene->SetNodeInstance(c->nodes[node], inst.ref);
+	return inst.IsValid() ? 1 : 0;
+}
+// NodeSetupInstanceFromFile (scene.cpp:1304-1348,1390) + NodeStartOnInstantiateAnim (:1350-1373). The instantiated nodes / anims / scene
+// anims are appended to the context's flat indices, in view order. Returns the number of instantiated nodes, -1 on failure.
+int hgref_setup_instance(void *h, int node) {
+	auto *c = static_cast<RefCtx *>(h);
+	PipelineInfo pipeline;
+	if (!c->scene->NodeSetupInstanceFromFile(c->nodes[node], c->resources, pipeline, LSSF_All | LSSF_DoNotLoadResources, 0))
+		return -1;
+	const SceneView &view = c->scene->GetNodeInstanceSceneView(c->nodes[node]);
+	for (const auto &r : view.nodes)
+		c->nodes.push_back(r);
+	for (const auto &r : view.anims)
+		c->anims.push_back(r);
+	for (const auto &r : view.scene_anims)
+		c->scene_anims.push_back(r);
+	const auto play = c->scene->NodeStartOnInstantiateAnim(c->nodes[node]);
+	if (c->scene->IsPlaying(play))
+		c->play_anims.push_back(play);
+	return int(view.nodes.size());
+}
+int hgref_node_count(void *h) { return int(static_cast<RefCtx *>(h)->nodes.size()); }
+// instance_anim_track of an Anim: names = n_keys zero-terminated strings back to back
+int hgref_anim_set_instance_track(void *h, int anim, int n_keys, const int64_t *t, const char *names, const uint8_t *loop_mode, const float *t_scale) {
+	auto *c = static_cast<RefCtx *>(h);
+	Anim *a = c->scene->GetAnim(c->anims[anim]);
+	a->instance_anim_track.keys.clear();
+	for (int i = 0; i < n_keys; ++i) {
+		AnimKeyT<InstanceAnimKey> k;
+		k.t = t[i];
+		k.v.anim_name = names;
+		names += strlen(names) + 1;
+		k.v.loop_mode = AnimLoopMode(loop_mode[i]);
+		k.v.t_scale = t_scale[i];
+		a->instance_anim_track.keys.push_back(k);
+	}
+	return n_keys;
+}
+
 // ---- per-frame path ------------------------------------------------------------------------------------------
 void hgref_update(void *h, int64_t dt) { static_cast<RefCtx *>(h)->scene->Update(dt); }
 

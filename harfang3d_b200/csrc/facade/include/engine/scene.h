@@ -320,6 +320,7 @@ public:
 	ModelRef GetObjectModel(ComponentRef ref) const;
 	void SetObjectMaterialCount(ComponentRef ref, size_t count);
 	void SetObjectMaterial(ComponentRef ref, size_t slot, Material mat);
+	Material &GetObjectMaterial(ComponentRef ref, size_t slot_idx); // scene.h:342; an invalid ref / slot yields a scratch material
 	size_t GetObjectBoneCount(ComponentRef ref) const;
 	void SetObjectBoneCount(ComponentRef ref, size_t count);
 	bool SetObjectBone(ComponentRef ref, size_t idx, NodeRef bone_node); // component.cpp:679-691

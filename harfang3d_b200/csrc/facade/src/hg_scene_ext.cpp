@@ -451,3 +451,15 @@ Node CreateCamera(Scene &scene, const Mat4 &mtx, float znear, float zfar, float 
 }
 
 } // namespace hg
+
+namespace hg {
+Material &Scene::GetObjectMaterial(ComponentRef ref, size_t slot_idx) { // component.cpp: warn + dummy on an invalid ref / slot
+	static Material dummy;
+	if (!objects.is_valid(ref) || slot_idx >= objects[ref.idx].materials.size()) {
+		warn("Invalid object or material slot");
+		dummy = Material{};
+		return dummy;
+	}
+	return objects[ref.idx].materials[slot_idx];
+}
+} // namespace hg

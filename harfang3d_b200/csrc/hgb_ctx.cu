@@ -156,6 +156,7 @@ struct hgb_ctx {
 	bool tma_level = false;   // A/B switch: persistent TMA-staged level kernel instead of one thread per node with LDG rows (measured slower: r01c)
 	uint64_t top_budget = 2500000; // k_update_top covers the leading levels whose recomputed work (sum of nodes x depth) stays below this; 0 = one launch per level
 	uint32_t level_block = 128;    // threads per CTA of the level kernel: small CTAs recycle their slots sooner (HGB_LEVEL_BLOCK=256: A/B, +2.5 % frame time)
+	bool multi_compact = true;     // all views of an entry table compacted in one pass (HGB_MULTI_COMPACT=0: one k_compact launch per view; A/B)
 	int level_minb = 6;            // resident CTAs per SM the level kernel's registers are held to (HGB_LEVEL_MINB=5: 48 registers; A/B)
 	bool overlap_sampler = false; // opt-in: sample tracks by target level on a second stream, overlapped with the level kernels (measured slower: r01c)
 	cudaStream_t stream2 = nullptr;
@@ -356,6 +357,8 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		c->top_budget = opt->top_walk < 0 ? 0u : uint64_t(opt->top_walk); // A/B switch: -1 = one launch per level, n = budget
 	if (const char *e_top = getenv("HGB_TOP_BUDGET"))
 		c->top_budget = strtoull(e_top, nullptr, 10);
+	if (const char *e_mc = getenv("HGB_MULTI_COMPACT"))
+		c->multi_compact = e_mc[0] != '0';
 	if (const char *e_blk = getenv("HGB_LEVEL_BLOCK"))
 		c->level_block = atoi(e_blk) == 256 ? 256u : (atoi(e_blk) == 64 ? 64u : 128u);
 	if (const char *e_minb = getenv("HGB_LEVEL_MINB"))

@@ -46,7 +46,7 @@ static int enqueue_compaction_reset(hgb_ctx *c) {
 		if (!t.n)
 			continue;
 		CK(cudaMemsetAsync(t.ticket.p, 0, kMaxViews * 4, c->stream));
-		CK(cudaMemsetAsync(t.status.p, 0, size_t(t.n_tiles) * n_views * 4, c->stream));
+		CK(cudaMemsetAsync(t.status.p, 0, size_t(t.n_tiles) * (n_views > 1 ? kMaxViews : 1) * 4, c->stream)); // the one-pass kernel walks 2 / 4 / 8 chains
 	}
 	return 0;
 }
@@ -62,6 +62,28 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 		EntryTable &t = c->ent[k];
 		if (!t.n)
 			continue;
+		const bool peer_here = with_peer && k == 0;
+		if (n_views > 1 && !peer_here && c->multi_compact) { // every view of the table in one pass over the visibility bytes
+			CompactMultiDev d{};
+			d.vis = t.vis[c->cur].as<uint8_t>();
+			d.n = t.n;
+			for (int v = 0; v < kMaxViews; ++v)
+				d.out[v] = v < n_views ? t.out[v].as<uint32_t>() : nullptr;
+			d.count = t.counts.as<uint32_t>();
+			d.ticket = t.ticket.as<uint32_t>();
+			d.status = t.status.as<uint32_t>();
+			d.n_tiles = t.n_tiles;
+			prof_begin(c, HGB_K_COMPACT);
+			if (n_views <= 2)
+				launch_after(c, chained, k_compact_multi<2>, dim3(t.n_tiles), dim3(kCompactThreads), d);
+			else if (n_views <= 4)
+				launch_after(c, chained, k_compact_multi<4>, dim3(t.n_tiles), dim3(kCompactThreads), d);
+			else
+				launch_after(c, chained, k_compact_multi<8>, dim3(t.n_tiles), dim3(kCompactThreads), d);
+			prof_end(c);
+			++*n_k;
+			continue;
+		}
 		for (int v = 0; v < n_views; ++v) {
 			CompactDev d{};
 			d.vis = t.vis[c->cur].as<uint8_t>();

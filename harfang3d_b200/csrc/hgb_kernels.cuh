@@ -497,6 +497,129 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact(CompactDev c) {
 	}
 }
 
+// ---- all views of an entry table in ONE pass -----------------------------------------------------------------------------------------
+// The forward pipeline culls the same opaque list against up to 6 frusta per frame (view + 4 PSSM splits + spot,
+// engine/forward_pipeline.cpp:331-332,380-381). One launch per view re-reads the visibility bytes and walks its own look-back chain, one
+// after the other; here a tile's bytes are read ONCE, every view's bit is peeled off the same registers, and the NV look-back chains
+// advance side by side — warp v resolves view v (8 warps, up to 8 views). Output lists, counts and status words are per view, laid out
+// like NV independent k_compact launches would leave them (k_segment_ranks and hgb_get_visible read them unchanged).
+struct CompactMultiDev {
+	const uint8_t *vis;
+	uint32_t n;
+	uint32_t *out[kMaxViews];  // surviving entry indices per view, in order
+	uint32_t *count;           // kMaxViews totals
+	uint32_t *ticket;          // one word, zeroed before launch
+	volatile uint32_t *status; // [view][n_tiles] words, zeroed before launch
+	uint32_t n_tiles;
+};
+
+template <int NV> __global__ void __launch_bounds__(kCompactThreads) k_compact_multi(CompactMultiDev c) {
+	__shared__ uint32_t s_tile, s_warp_sum[NV][kCompactThreads / 32], s_prefix[NV], s_total[NV];
+	__shared__ uint32_t s_list[kCompactTile];
+	asm volatile("griddepcontrol.launch_dependents;");
+	asm volatile("griddepcontrol.wait;" ::: "memory");
+	if (threadIdx.x == 0)
+		s_tile = atomicAdd(c.ticket, 1u);
+	__syncthreads();
+	const uint32_t tile = s_tile;
+	const uint32_t base = tile * kCompactTile + threadIdx.x * kCompactItems;
+	const uint4 *src = reinterpret_cast<const uint4 *>(c.vis + base);
+	const uint4 ra = src[0], rb = src[1];
+	const uint32_t w[8] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
+	uint32_t valid_mask = 0xffffffffu;
+	if (base + kCompactItems > c.n) { // ragged tail: drop bits past n
+		const uint32_t valid = base < c.n ? c.n - base : 0;
+		valid_mask = valid >= 32 ? 0xffffffffu : (1u << valid) - 1u;
+	}
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint32_t mask[NV], excl[NV];
+#pragma unroll
+	for (int v = 0; v < NV; ++v) {
+		uint32_t m = 0;
+#pragma unroll
+		for (int i = 0; i < 8; ++i)
+			m |= ((((w[i] >> v) & 0x01010101u) * 0x10204080u) >> 28) << (4 * i);
+		m &= valid_mask;
+		mask[v] = m;
+		const uint32_t cnt = __popc(m);
+		uint32_t incl = cnt;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+			if (lane >= d)
+				incl += t;
+		}
+		if (lane == 31)
+			s_warp_sum[v][warp] = incl;
+		excl[v] = incl - cnt;
+	}
+	__syncthreads();
+	// warp v: decoupled look-back of view v
+	if (warp < NV) {
+		const int v = int(warp);
+		volatile uint32_t *status = c.status + size_t(v) * c.n_tiles;
+		uint32_t tile_total = 0;
+#pragma unroll
+		for (int k = 0; k < kCompactThreads / 32; ++k)
+			tile_total += s_warp_sum[v][k];
+		if (lane == 0) {
+			status[tile] = (tile == 0 ? 2u << 30 : 1u << 30) | tile_total;
+			__threadfence();
+		}
+		uint32_t prefix = 0;
+		if (tile > 0) {
+			int look = int(tile) - 1 - int(lane);
+			while (true) {
+				uint32_t st = look >= 0 ? status[look] : (2u << 30);
+				while (__any_sync(0xffffffffu, (st >> 30) == 0)) {
+					if ((st >> 30) == 0)
+						st = status[look];
+				}
+				const uint32_t has_incl = __ballot_sync(0xffffffffu, (st >> 30) == 2);
+				const int first = has_incl ? __ffs(has_incl) - 1 : 32;
+				uint32_t contrib = (int(lane) <= first) ? (st & 0x3fffffffu) : 0u;
+#pragma unroll
+				for (int d = 16; d > 0; d >>= 1)
+					contrib += __shfl_xor_sync(0xffffffffu, contrib, d);
+				prefix += contrib;
+				if (has_incl)
+					break;
+				look -= 32;
+			}
+			if (lane == 0) {
+				status[tile] = (2u << 30) | (prefix + tile_total);
+				__threadfence();
+			}
+		}
+		if (lane == 0) {
+			s_prefix[v] = prefix;
+			s_total[v] = tile_total;
+			if (uint64_t(tile + 1) * kCompactTile >= c.n)
+				c.count[v] = prefix + tile_total;
+		}
+	}
+	__syncthreads();
+	// survivors, one view after the other through the same staging buffer
+#pragma unroll
+	for (int v = 0; v < NV; ++v) {
+		uint32_t warp_off = 0;
+#pragma unroll
+		for (int k = 0; k < kCompactThreads / 32; ++k)
+			warp_off += k < int(warp) ? s_warp_sum[v][k] : 0u;
+		uint32_t r = warp_off + excl[v], m = mask[v];
+		while (m) {
+			s_list[r++] = base + (__ffs(m) - 1);
+			m &= m - 1;
+		}
+		__syncthreads();
+		const uint32_t total = s_total[v], prefix = s_prefix[v];
+		uint32_t *out = c.out[v];
+		for (uint32_t i = threadIdx.x; i < total; i += kCompactThreads)
+			out[prefix + i] = s_list[i];
+		__syncthreads();
+	}
+}
+
 // Batched scene instances (one camera per instance): the global stable compaction already keeps each instance's survivors
 // contiguous; the exclusive rank of every instance's first entry gives the per-instance offsets/counts. One warp per
 // instance: inclusive prefix of the preceding tile (left in status[] by k_compact) + popcount of the flags between the tile

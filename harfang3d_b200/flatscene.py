@@ -76,6 +76,17 @@ def bind(L, with_probes):
     _sig(L, "hgref_mat4_mul", None, [c_p, c_p, c_p])
     _sig(L, "hgref_sinf", c_f, [c_f])
     _sig(L, "hgref_cosf", c_f, [c_f])
+    _sig(L, "hgref_add_point_light", c_i, [c_p, c_i, c_f])
+    _sig(L, "hgref_get_light", None, [c_p, c_i, c_p])
+    _sig(L, "hgref_anim_add_color_track", c_i, [c_p, c_i, C.c_char_p, c_i, c_p, c_p, c_p, c_p])
+    _sig(L, "hgref_anim_add_vec4_track", c_i, [c_p, c_i, C.c_char_p, c_i, c_p, c_p, c_p, c_p])
+    _sig(L, "hgref_set_material_value", None, [c_p, c_i, c_i, C.c_char_p, c_p])
+    _sig(L, "hgref_get_material_value", c_i, [c_p, c_i, c_i, C.c_char_p, c_p])
+    _sig(L, "hgref_set_scene_anim_name", None, [c_p, c_i, C.c_char_p])
+    _sig(L, "hgref_add_instance", c_i, [c_p, c_i, C.c_char_p, C.c_char_p, c_i])
+    _sig(L, "hgref_setup_instance", c_i, [c_p, c_i])
+    _sig(L, "hgref_node_count", c_i, [c_p])
+    _sig(L, "hgref_anim_set_instance_track", c_i, [c_p, c_i, c_i, c_p, C.c_char_p, c_p, c_p])
     _sig(L, "hgref_time_frames", c_i, [c_p, c_i, c_i64, c_p, c_i, c_p])
     if with_probes:  # reference-internal host math: compiled out of the facade build
         _sig(L, "hgref_minmax_transform", None, [c_p, c_p, c_p])

@@ -503,3 +503,117 @@ def test_reference_unit_tests_against_facade():
     for name in ("ComponentGarbageCollection", "WalkHierarchy", "DisableObjectNodes"):
         assert ("engine.scene.%s" % name) in r.stdout and "[ OK ]" in r.stdout
     assert "All unit tests have passed" in r.stdout
+
+
+@pytest.mark.gpu
+def test_facade_light_and_material_tracks_match_reference(fac, ref):
+    """the remaining single-value animation targets of BoundToNodeAnim (scene.h:74-88): "Light.Diffuse" / "Light.Specular" colour tracks,
+    "Light.DiffuseIntensity" / "Light.SpecularIntensity" float tracks (EvaluateBoundAnim scene.cpp:2183-2192) and "Material.<slot>.<value>"
+    vec4 tracks (:2199-2215), evaluated on the host by the facade while Position tracks of the same anims run on the device: every value
+    bit-identical to the reference frame by frame, unknown slots / value names ignored like the reference ignores them."""
+    rng = np.random.default_rng(141)
+    fs = scenegen.static_scene(400, 3, 6, n_models=2, seed=141)
+    nodes = np.sort(rng.choice(np.nonzero((fs.parent >= 0) & (fs.model >= 0))[0], 40, replace=False)).astype(np.int32)
+    scenegen.add_position_tracks(fs, nodes, rng, n_keys=6, play_loop=True)
+    plays, fs.plays = fs.plays, []
+    a, b = RefScene(ref, fs), RefScene(fac, fs)
+    fs.plays = plays
+    lit = [0, 7, 19]  # anim indices whose node gets a light + an animated material value
+    kt = (np.arange(5, dtype=np.int64) * int(scenegen.KEY_DT * 0.9) + scenegen.KEY_DT // 4)
+    col = [(tg, rng.uniform(0, 1, (5, 4)).astype(np.float32), rng.uniform(-0.5, 0.5, 5).astype(np.float32), rng.uniform(-0.5, 0.5, 5).astype(np.float32))
+           for tg in (b"Light.Diffuse", b"Light.Specular", b"Light.Diffuse")]
+    flt = [(tg, rng.uniform(0.2, 4, 5).astype(np.float32), rng.uniform(-0.5, 0.5, 5).astype(np.float32), rng.uniform(-0.5, 0.5, 5).astype(np.float32))
+           for tg in (b"Light.DiffuseIntensity", b"Light.SpecularIntensity")]
+    v4 = [(tg, rng.uniform(-2, 2, (5, 4)).astype(np.float32), rng.uniform(-0.5, 0.5, 5).astype(np.float32), rng.uniform(-0.5, 0.5, 5).astype(np.float32))
+          for tg in (b"Material.0.uColor", b"Material.3.uColor", b"Material.0.uMissing", b"Material.0.uColor")]
+    start = np.array([0.1, 0.2, 0.3, 0.4], np.float32)
+    for L_, s in ((ref, a), (fac, b)):
+        for an in lit:
+            nd = int(nodes[an])
+            L_.hgref_add_point_light(s.h, nd, 2.5)
+            L_.hgref_set_material_value(s.h, nd, 0, b"uColor", P(start))
+            for tg, v, te, bi in col:
+                L_.hgref_anim_add_color_track(s.h, an, tg, 5, P(kt), P(np.ascontiguousarray(v)), P(te), P(bi))
+            for tg, v, te, bi in flt:
+                L_.hgref_anim_add_float_track(s.h, an, tg, 5, P(kt), P(v), P(te), P(bi))
+            for tg, v, te, bi in v4:
+                L_.hgref_anim_add_vec4_track(s.h, an, tg, 5, P(kt), P(np.ascontiguousarray(v)), P(te), P(bi))
+        for sa, loop, scale in fs.plays:
+            L_.hgref_play_anim(s.h, sa, loop, scale)
+    seen = set()
+    for frame in range(16):
+        a.update(scenegen.FRAME_DT * 2); b.update(scenegen.FRAME_DT * 2)
+        assert (bits(a.worlds()[: fs.n]) == bits(b.worlds()[: fs.n])).all()
+        for an in lit:
+            la, lb, ma, mb = np.zeros(10, np.float32), np.zeros(10, np.float32), np.zeros(4, np.float32), np.zeros(4, np.float32)
+            ref.hgref_get_light(a.h, int(nodes[an]), P(la)); fac.hgref_get_light(b.h, int(nodes[an]), P(lb))
+            assert (bits(la) == bits(lb)).all(), (frame, an, la, lb)
+            assert ref.hgref_get_material_value(a.h, int(nodes[an]), 0, b"uColor", P(ma)) == fac.hgref_get_material_value(b.h, int(nodes[an]), 0, b"uColor", P(mb)) == 1
+            assert (bits(ma) == bits(mb)).all(), (frame, an, ma, mb)
+            seen.add(float(la[0])); seen.add(float(ma[1]))
+    assert len(seen) > 20  # the values really move
+    a.close(); b.close()
+
+
+@pytest.mark.gpu
+def test_facade_scene_instances_match_reference(fac, ref, tmp_path):
+    """Scene instances (scene.cpp:1304-1388): a node instantiates another scene file under itself (written here by the reference's own
+    Save_binary). Checked against the reference through the shared flat binding: the instantiated nodes, their display lists and world
+    matrices; NF_InstanceDisabled propagation when the host node is disabled / re-enabled (EnableNode_/DisableNode_ scene.cpp:472-503);
+    the on-instantiate anim; and an instance_anim_track (scene.cpp:2217-2268) that switches the instantiated scene between two of its
+    anims at a nested clock (looping, then reversed at half speed) — worlds bit-identical frame by frame."""
+    rng = np.random.default_rng(151)
+    # the instantiated scene: 60 nodes, two named scene anims driving different nodes
+    sub = scenegen.static_scene(60, 3, 4, n_models=2, seed=152, disabled_frac=0.0)
+    n_a = np.sort(rng.choice(np.arange(1, 60), 20, replace=False)).astype(np.int32)
+    scenegen.add_position_tracks(sub, n_a[:10], rng, n_keys=8, play_loop=True)
+    scenegen.add_position_tracks(sub, n_a[10:], rng, n_keys=8, play_loop=True)
+    sub.plays = []
+    w = RefScene(ref, sub)
+    ref.hgref_set_scene_anim_name(w.h, 0, b"idle")
+    ref.hgref_set_scene_anim_name(w.h, 1, b"run")
+    path = str(tmp_path / "sub.scn")
+    w.save_binary(path)
+    w.close()
+    # the host scene: 12 nodes; nodes 3 and 7 instantiate the file (3 starts "idle" on instantiation), node 7's anim carries the step track
+    fs = scenegen.static_scene(12, 2, 11, n_models=2, seed=153, disabled_frac=0.0)
+    fs.models = sub.models
+    a, b = RefScene(ref, fs), RefScene(fac, fs)
+    kt = np.array([0, int(0.35e9), int(0.9e9)], np.int64)
+    names = b"idle\0run\0idle\0"
+    loop = np.array([2, 2, 0], np.uint8)
+    scale = np.array([1.0, -0.5, 2.0], np.float32)
+    for L_, s in ((ref, a), (fac, b)):
+        assert L_.hgref_add_instance(s.h, 3, path.encode(), b"idle", 2) == 1
+        assert L_.hgref_add_instance(s.h, 7, path.encode(), b"", 0) == 1
+        assert L_.hgref_setup_instance(s.h, 3) == 60
+        assert L_.hgref_setup_instance(s.h, 7) == 60
+        assert L_.hgref_node_count(s.h) == 12 + 120
+        an = L_.hgref_add_anim(s.h, 0)
+        L_.hgref_anim_set_instance_track(s.h, an, 3, P(kt), names, P(loop), P(scale))
+        sa = L_.hgref_add_scene_anim(s.h, 1, P(np.array([7], np.int32)), P(np.array([an], np.int32)), 0, int(1.4e9))
+        L_.hgref_play_anim(s.h, sa, 0, 1.0)
+    n_all = 132
+
+    def same(frame):
+        wa, wb = a.worlds(), b.worlds()
+        assert wa.shape == wb.shape and (bits(wa) == bits(wb)).all(), "frame %s: worlds differ" % (frame,)
+        (ca, la), (cb, lb) = a.display_lists(), b.display_lists()
+        assert (ca == cb).all(), (frame, ca, cb)
+        for k in (0, 1):
+            for x, y in zip(la[k], lb[k]):
+                assert (x == y).all()
+        for nd in range(n_all):
+            assert ref.hgref_is_node_enabled(a.h, nd) == fac.hgref_is_node_enabled(b.h, nd), (frame, nd)
+        return int(ca[0])
+
+    counts = []
+    for frame in range(50):
+        if frame == 10:
+            ref.hgref_enable_node(a.h, 3, 0); fac.hgref_enable_node(b.h, 3, 0)   # the host of the first instance goes dark with all it instantiated
+        if frame == 20:
+            ref.hgref_enable_node(a.h, 3, 1); fac.hgref_enable_node(b.h, 3, 1)
+        a.update(scenegen.FRAME_DT * 2); b.update(scenegen.FRAME_DT * 2)
+        counts.append(same(frame))
+    assert counts[15] < counts[5] and counts[25] == counts[5]  # the instantiated objects left and came back
+    a.close(); b.close()
