@@ -1,0 +1,26 @@
+"""Cost of a hierarchy edit: hgb_set_topology (full depth re-sort: host BFS + device gather/scatter of TRS and both
+world buffers) and the first hgb_update after it (tables + graph re-captured), at 1M and 16M nodes, for one re-parented leaf."""
+import json, os, sys, time
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import harfang3d_b200
+from harfang3d_b200 import hostmirror, scenegen
+
+out = {}
+for name, fs in (("1M", scenegen.config_c2(seed=2, n_nodes=1_000_000)), ("16M", scenegen.config_c4(seed=4, n_scenes=16, nodes_per_scene=1_000_000, animated_frac=0.25, n_keys=16))):
+    ctx = harfang3d_b200.Context(0)
+    t = hostmirror.upload(ctx, fs)
+    clocks = hostmirror.PlayClocks(fs)
+    for _ in range(3):
+        ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True)
+    ctx.sync()
+    t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); steady = time.perf_counter() - t0
+    parent = t["parent_slot"].copy()
+    leaf = fs.n - 1
+    parent[leaf] = parent[leaf - 5]  # re-parent one leaf inside its level
+    t0 = time.perf_counter(); ctx.set_topology(parent); ctx.sync(); topo = time.perf_counter() - t0
+    t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); first = time.perf_counter() - t0
+    t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); second = time.perf_counter() - t0
+    out[name] = {"steady_frame_ms": steady * 1e3, "set_topology_ms": topo * 1e3, "first_update_after_edit_ms": first * 1e3, "second_update_ms": second * 1e3}
+    ctx.close()
+print(json.dumps(out))

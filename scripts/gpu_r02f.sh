@@ -1,0 +1,12 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
+tail -25 gpurun_out/pytest_gpu.log
+timeout 600 python scripts/multiview_compact.py > gpurun_out/multiview_1.json 2> gpurun_out/multiview_1.err; cat gpurun_out/multiview_1.json; tail -2 gpurun_out/multiview_1.err
+HGB_MULTI_COMPACT=0 timeout 600 python scripts/multiview_compact.py > gpurun_out/multiview_0.json 2> gpurun_out/multiview_0.err; cat gpurun_out/multiview_0.json
+timeout 600 python scripts/edit_cost.py > gpurun_out/edit_cost.json 2> gpurun_out/edit_cost.err; cat gpurun_out/edit_cost.json; tail -2 gpurun_out/edit_cost.err
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/bench_c4.json 2> gpurun_out/bench_c4.err; echo "bench exit $?"; python - <<PY
+import json
+d=json.loads([l for l in open("gpurun_out/bench_c4.json") if l.startswith("{")][-1])
+print("ms/step %.4f value %.0f e2e %.0f facade %s frac %.3f"%(d["ms_per_step"],d["value"],d["e2e"]["value"],d.get("e2e_facade"),d["roofline"]["frac"]), d["roofline"]["kernel_ms_per_step"])
+PY
