@@ -57,6 +57,7 @@ SIGNATURES = {
     "hgb_cull_list": (_i, [_p, _u32, _p, _p, _u32, _p, _p, _p, _p]),
     "hgb_bone_matrices": (_i, [_p, _i]),
     "hgb_sort_keys": (_i, [_p, _i, _u32, _p]),
+    "hgb_cull_skinned_list": (_i, [_p, _u32, _p, _p, _p, _u32, _p, _p, _u32, _p, _p, _p, _p]),
     "hgb_get_visible_ptr": (_i, [_p, _i, _u32, _p, _p]),
     "hgb_peer_init": (_i, [_p, _u32, _u32, _u32, _p, _p, _p, _p]),
     "hgb_peer_connect": (_i, [_p, _p, _p]),
@@ -342,6 +343,17 @@ class Context:
         n = C.c_uint32(0)
         self._ck(self._L.hgb_get_visible(self._h, kind, view, _ptr(out, np.uint32, "out"), len(out), C.byref(n)))
         return out[: n.value]
+
+    def cull_skinned_list(self, bone_off, mtx_slot, bind_idx, bind_pose12, bounds_idx, bounds6, frustum24):
+        """opt-in cull of skinned display lists (union of the per-bone boxes) -> surviving list indices, in order"""
+        n = len(bone_off) - 1
+        out, cnt = np.empty(max(n, 1), np.uint32), C.c_uint32(0)
+        f = np.ascontiguousarray(frustum24, np.float32).reshape(24)
+        self._ck(self._L.hgb_cull_skinned_list(self._h, n, _ptr(bone_off, np.uint32, "bone_off"), _ptr(mtx_slot, np.uint32, "mtx_slot"), _ptr(bind_idx, np.uint32, "bind_idx"),
+                                               bind_pose12.shape[0], _ptr(bind_pose12, np.float32, "bind_pose12"), _ptr(bounds_idx, np.uint32, "bounds_idx"),
+                                               bounds6.shape[0], _ptr(bounds6, np.float32, "bounds6"), _ptr(f, np.float32, "frustum24"), _ptr(out, np.uint32, "out"),
+                                               C.byref(cnt)))
+        return out[: cnt.value]
 
     def get_visible_ptr(self, kind=0, view=0):
         """the visible list in the context's own pinned buffer (valid until the next call for this kind): one round trip"""

@@ -337,7 +337,9 @@ int hgref_anim_add_vec4_track(void *h, int anim, const char *target, int n_keys,
 }
 void hgref_set_material_value(void *h, int node, int slot, const char *name, const float *v4) {
 	auto *c = static_cast<RefCtx *>(h);
-	SetMaterialValue(c->scene->GetObjectMaterial(c->scene->GetNodeObjectRef(c->nodes[node]), size_t(slot)), name, Vec4(v4[0], v4[1], v4[2], v4[3]));
+	// written straight into the value map: the reference's SetMaterialValue also creates a bgfx uniform, which needs a renderer
+	auto &mv = c->scene->GetObjectMaterial(c->scene->GetNodeObjectRef(c->nodes[node]), size_t(slot)).values[name];
+	mv.value = {v4[0], v4[1], v4[2], v4[3]};
 }
 int hgref_get_material_value(void *h, int node, int slot, const char *name, float *out4) {
 	auto *c = static_cast<RefCtx *>(h);

@@ -106,6 +106,11 @@ struct SkinnedModelDisplayList { // render_pipeline.h:596-603
 
 // Stable in-place removal of the entries whose transformed bounds are V_Outside (render_pipeline.cpp:2098-2104). `mtxs` must be the
 // vector returned by Scene::GetTransformWorldMatrices() of a live scene: it identifies the device context holding the matrices.
+// OPT-IN (not in the reference, which never culls skinned lists: scene_forward_pipeline.cpp:560-562): stable in-place removal of the
+// skinned lists whose bound — the union over the list's bones of Model::bounds[lst_idx] carried through the bone's skinning matrix — is
+// V_Outside. Nothing calls it by default.
+void CullSkinnedModelDisplayLists(const Frustum &frustum, std::vector<SkinnedModelDisplayList> &display_lists, const std::vector<Mat4> &mtxs,
+	const PipelineResources &resources);
 void CullModelDisplayLists(const Frustum &frustum, std::vector<ModelDisplayList> &display_lists, const std::vector<Mat4> &mtxs, const PipelineResources &resources);
 
 // The bone-matrix loop of _DrawSkinnedModelDisplayLists (render_pipeline.cpp:2157-2188) as a callable: 16 floats per (list, bone) in

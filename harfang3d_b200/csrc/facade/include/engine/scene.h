@@ -377,6 +377,7 @@ public:
 private:
 	friend bool GetNodesMinMax(const std::vector<Node> &, const PipelineResources &, MinMax &);
 	friend void CullModelDisplayLists(const Frustum &, std::vector<ModelDisplayList> &, const std::vector<Mat4> &, const PipelineResources &);
+	friend void CullSkinnedModelDisplayLists(const Frustum &, std::vector<SkinnedModelDisplayList> &, const std::vector<Mat4> &, const PipelineResources &);
 	friend size_t ComputeSkinMatrices(const std::vector<SkinnedModelDisplayList> &, const std::vector<Mat4> &, const PipelineResources &, std::vector<float> &, bool);
 	struct Impl;
 

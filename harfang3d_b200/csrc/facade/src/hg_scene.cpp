@@ -1571,6 +1571,49 @@ size_t ComputeSkinMatrices(const std::vector<SkinnedModelDisplayList> &display_l
 	return mtx.size();
 }
 
+// opt-in cull of skinned lists (see render_pipeline.h): hgb_cull_skinned_list over the caller's vector
+void CullSkinnedModelDisplayLists(const Frustum &frustum, std::vector<SkinnedModelDisplayList> &display_lists, const std::vector<Mat4> &mtxs,
+	const PipelineResources &resources) {
+	if (display_lists.empty())
+		return;
+	Scene *scene = scene_of(mtxs);
+	if (!scene || !scene->ctx) {
+		warn("CullSkinnedModelDisplayLists: the matrices do not belong to a live hg::Scene with a device context; list left unculled");
+		return;
+	}
+	std::vector<float> pool, bounds6;
+	std::vector<uint32_t> bind_base(0x10000, 0), bounds_base;
+	build_bounds(resources, bounds6, bounds_base);
+	for (uint32_t m = resources.models.first(); m != 0xffffffffu; m = resources.models.next(m)) {
+		const Model &mdl = resources.models.Get_unsafe_(uint16_t(m));
+		bind_base[m] = uint32_t(pool.size() / 12);
+		for (const Mat4 &b : mdl.bind_pose)
+			pool.insert(pool.end(), &b.m[0][0], &b.m[0][0] + 12);
+	}
+	std::vector<uint32_t> off{0}, mtx, bind, bidx;
+	for (const SkinnedModelDisplayList &dl : display_lists) {
+		for (uint16_t j = 0; j < dl.bone_count; ++j) {
+			mtx.push_back(dl.mtx_idxs[j]);
+			bind.push_back(bind_base[dl.mdl_idx] + dl.bones_idxs[j]);
+		}
+		off.push_back(uint32_t(mtx.size()));
+		bidx.push_back(bounds_base[dl.mdl_idx] + dl.lst_idx);
+	}
+	if (pool.empty() || bounds6.empty())
+		return;
+	std::vector<uint32_t> keep(display_lists.size());
+	uint32_t n = 0;
+	if (hgb_cull_skinned_list(scene->ctx, uint32_t(display_lists.size()), off.data(), mtx.data(), bind.data(), uint32_t(pool.size() / 12), pool.data(), bidx.data(),
+			uint32_t(bounds6.size() / 6), bounds6.data(), &frustum[0].x, keep.data(), &n)) {
+		warn(hgb_last_error());
+		return;
+	}
+	for (uint32_t i = 0; i < n; ++i) // ascending indices: an in-place stable compaction, like std::remove_if
+		if (keep[i] != i)
+			display_lists[i] = display_lists[keep[i]];
+	display_lists.resize(n);
+}
+
 // ---- garbage collection (scene.cpp:92-237): components no node refers to, anims no scene anim refers to -----------------------
 size_t Scene::GarbageCollect() {
 	size_t removed = 0;

@@ -570,6 +570,74 @@ int hgb_cull_list(hgb_ctx *c, uint32_t n, const uint32_t *mtx_slot, const uint32
 	return 0;
 }
 
+// Opt-in culling of skinned display lists (see k_cull_skinned): stateless like hgb_cull_list. List i owns the bones
+// [bone_off[i], bone_off[i+1]) = (mtx_slot, bind_idx) pairs in SkinnedModelDisplayList order; bounds_idx[i] selects the list's MinMax.
+int hgb_cull_skinned_list(hgb_ctx *c, uint32_t n_lists, const uint32_t *bone_off, const uint32_t *mtx_slot, const uint32_t *bind_idx, uint32_t n_bind,
+	const float *bind_pose12, const uint32_t *bounds_idx, uint32_t n_bounds, const float *bounds6, const float *frustum24, uint32_t *out_idx, uint32_t *out_count) {
+	if (!c)
+		return fail("null context");
+	join_post(c);
+	if (out_count)
+		*out_count = 0;
+	if (!n_lists)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	const uint32_t n_bones = bone_off[n_lists];
+	std::vector<uint32_t> pos(std::max(n_bones, 1u));
+	for (uint32_t i = 0; i < n_lists; ++i) {
+		if (bone_off[i + 1] < bone_off[i] || bone_off[i + 1] - bone_off[i] > 32)
+			return fail("hgb_cull_skinned_list: list %u has %u bones (at most 32, render_pipeline.h:38)", i, bone_off[i + 1] - bone_off[i]);
+		if (bounds_idx[i] >= n_bounds)
+			return fail("hgb_cull_skinned_list: list %u references bounds %u outside the table", i, bounds_idx[i]);
+	}
+	for (uint32_t b = 0; b < n_bones; ++b) {
+		if (mtx_slot[b] >= c->n_slots)
+			return fail("hgb_cull_skinned_list: bone %u references slot %u outside the topology", b, mtx_slot[b]);
+		if (bind_idx[b] >= n_bind)
+			return fail("hgb_cull_skinned_list: bone %u references bind pose %u outside the pool", b, bind_idx[b]);
+		pos[b] = c->pos_of_slot[mtx_slot[b]];
+	}
+	float cond[24];
+	precondition_planes(frustum24, 6, cond);
+	interleave_bounds(bounds6, n_bounds, c->bounds_stage);
+	DBuf d_off, d_pos, d_bind, d_pose, d_bidx, d_vis;
+	int rc = upload(c, d_off, bone_off, size_t(n_lists + 1) * 4) || upload(c, d_pos, pos.data(), size_t(n_bones) * 4) || upload(c, d_bind, bind_idx, size_t(n_bones) * 4) ||
+			 upload(c, d_pose, bind_pose12, size_t(n_bind) * 48) || upload(c, d_bidx, bounds_idx, size_t(n_lists) * 4) ||
+			 upload(c, c->adhoc_bounds, c->bounds_stage.data(), size_t(n_bounds) * 24) || upload(c, c->adhoc_planes, cond, 96);
+	if (!rc && d_vis.reserve(n_lists) != cudaSuccess)
+		rc = fail("hgb_cull_skinned_list: out of device memory");
+	std::vector<uint8_t> vis(n_lists);
+	if (!rc) {
+		SkinCullDev d{};
+		d.bone_off = d_off.as<uint32_t>(), d.mtx_pos = d_pos.as<uint32_t>(), d.bind_idx = d_bind.as<uint32_t>(), d.bind_pose = d_pose.as<float>();
+		d.bounds_idx = d_bidx.as<uint32_t>(), d.bounds6 = c->adhoc_bounds.as<float>(), d.world = c->world[c->cur].as<float>();
+		d.planes = c->adhoc_planes.as<float4>(), d.vis = d_vis.as<uint8_t>(), d.n_lists = n_lists;
+		k_cull_skinned<<<grid_for(n_lists * 32), 256, 0, c->stream>>>(d);
+		++c->launches;
+		cudaError_t e = cudaGetLastError();
+		if (e == cudaSuccess)
+			e = cudaMemcpyAsync(vis.data(), d_vis.p, n_lists, cudaMemcpyDeviceToHost, c->stream);
+		if (e == cudaSuccess)
+			e = cudaStreamSynchronize(c->stream);
+		if (e != cudaSuccess)
+			rc = fail("hgb_cull_skinned_list: %s", cudaGetErrorString(e));
+	} else {
+		cudaStreamSynchronize(c->stream);
+	}
+	DBuf *tmp[] = {&d_off, &d_pos, &d_bind, &d_pose, &d_bidx, &d_vis};
+	for (DBuf *b : tmp)
+		b->release();
+	if (rc)
+		return 1;
+	uint32_t n = 0;
+	for (uint32_t i = 0; i < n_lists; ++i)
+		if (vis[i])
+			out_idx[n++] = i; // order-preserving, like std::remove_if
+	if (out_count)
+		*out_count = n;
+	return 0;
+}
+
 int hgb_bone_matrices(hgb_ctx *c, int with_previous) {
 	if (!c)
 		return fail("null context");

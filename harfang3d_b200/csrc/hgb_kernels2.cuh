@@ -324,6 +324,54 @@ __global__ void __launch_bounds__(256) k_bone_matrices(BoneDev b) {
 		store_bgfx(b.out_prev + size_t(i) * 16, mat4_mul(load_mat4(b.world_prev + size_t(mp) * 12), bind));
 }
 
+// ---- opt-in culling of skinned display lists ----------------------------------------------------------------------------------------
+// The reference never culls skinned lists (engine/scene_forward_pipeline.cpp:560-562, "FIXME cull skinned models !!!"); the default here
+// is the same. This is the opt-in: a skinned list survives unless the UNION over its bones of the list's MinMax carried through the
+// bone's skinning matrix world[mtx_idxs[j]] * bind_pose[bones_idxs[j]] (render_pipeline.cpp:2172-2173) — a conservative bound of every
+// skinned vertex, whatever its weights — is V_Outside (TestVisibility, foundation/frustum.cpp:59-79). One warp per list (<= 32 bones,
+// render_pipeline.h:38): lane j builds its bone's box with the path's own operator*(Mat4,Mat4) and operator*(Mat4,MinMax), the boxes
+// are joined by shuffles (min / max are exact), lane 0 tests the planes.
+struct SkinCullDev {
+	const uint32_t *bone_off;  // n_lists + 1: bones of list i = [bone_off[i], bone_off[i+1])
+	const uint32_t *mtx_pos;   // per bone: position of the bone's transform
+	const uint32_t *bind_idx;  // per bone: index into bind_pose
+	const float *bind_pose;    // 12 floats each
+	const uint32_t *bounds_idx; // per list
+	const float *bounds6;      // interleaved MinMax table
+	const float *world;
+	const float4 *planes;      // 6 conditioned planes
+	uint8_t *vis;              // per list: 1 = survives
+	uint32_t n_lists;
+};
+__global__ void __launch_bounds__(256) k_cull_skinned(SkinCullDev d) {
+	const uint32_t list = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+	if (list >= d.n_lists)
+		return;
+	const uint32_t b0 = d.bone_off[list], nb = min(d.bone_off[list + 1] - b0, 32u);
+	float mn[3] = {3.402823466e+38f, 3.402823466e+38f, 3.402823466e+38f}, mx[3] = {-3.402823466e+38f, -3.402823466e+38f, -3.402823466e+38f};
+	if (lane < nb) {
+		const Mat4 m = mat4_mul(load_mat4(d.world + size_t(d.mtx_pos[b0 + lane]) * 12), load_mat4(d.bind_pose + size_t(d.bind_idx[b0 + lane]) * 12));
+		const Aabb bb = minmax_transform(m, d.bounds6 + size_t(d.bounds_idx[list]) * 6);
+#pragma unroll
+		for (int k = 0; k < 3; ++k)
+			mn[k] = bb.mn[k], mx[k] = bb.mx[k];
+	}
+#pragma unroll
+	for (int s = 16; s > 0; s >>= 1)
+#pragma unroll
+		for (int k = 0; k < 3; ++k) {
+			mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], s));
+			mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], s));
+		}
+	if (lane == 0) {
+		Aabb u;
+#pragma unroll
+		for (int k = 0; k < 3; ++k)
+			u.mn[k] = mn[k], u.mx[k] = mx[k];
+		d.vis[list] = (nb == 0 || survives_frustum(d.planes, u)) ? 1 : 0; // a list without bones is never dropped
+	}
+}
+
 // ---- "Enable" bool tracks ---------------------------------------------------------------------------------------------------------
 // Scene::EvaluateBoundAnim, engine/scene.cpp:2158-2162: a bound "Enable" track is evaluated with EvaluateStep (engine/animation.h:130-139:
 // the key at or before t, the first key before the track starts, the last one after it ends) and the node is enabled / disabled

@@ -143,6 +143,14 @@ int hgb_cull(hgb_ctx *);
  * indices are written to out_idx in order (capacity n) and their number to *out_count. Independent of the entry tables above. */
 int hgb_cull_list(hgb_ctx *, uint32_t n, const uint32_t *mtx_slot, const uint32_t *bounds_idx, uint32_t n_bounds, const float *bounds6,
 	const float *frustum24, uint32_t *out_idx, uint32_t *out_count);
+/* OPT-IN culling of skinned display lists. The reference never culls them (harfang/engine/scene_forward_pipeline.cpp:560-562 "FIXME cull skinned
+ * models !!!") and neither does anything here unless this is called. A skinned list (<= 32 bones, render_pipeline.h:38) survives unless the
+ * union over its bones of bounds6[bounds_idx[i]] carried through world[mtx_slot] * bind_pose[bind_idx] (the skinning matrix of
+ * render_pipeline.cpp:2172-2173) is V_Outside — a conservative bound of every skinned vertex. List i owns the bone records
+ * [bone_off[i], bone_off[i+1]); surviving list indices come back in order. Stateless, like hgb_cull_list. */
+int hgb_cull_skinned_list(hgb_ctx *, uint32_t n_lists, const uint32_t *bone_off /* n_lists + 1 */, const uint32_t *mtx_slot, const uint32_t *bind_idx,
+	uint32_t n_bind, const float *bind_pose12, const uint32_t *bounds_idx /* per list */, uint32_t n_bounds, const float *bounds6, const float *frustum24,
+	uint32_t *out_idx, uint32_t *out_count);
 /* ComputeModelDisplayListSortKeys (harfang/engine/scene_forward_pipeline.cpp:438-483, ComputeSortKey render_pipeline.cpp:89-94) for the
  * survivors of list (kind, view) of the last cull: one 1-mm fixed-point key per visible entry, from the closest view-space z of the 8
  * corners of its MinMax. view_mat12 = ViewState::view (hg::Mat4). Keys are returned in visible-list order by hgb_get_sort_keys. */

@@ -717,3 +717,44 @@ def test_cull_list_rejects_oversized_bounds_table(hgb):
                                   fake.ctypes.data_as(C.c_void_p), np.zeros(24, np.float32).ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), C.byref(n))
         ctx._ck(rc)
     ctx.close()
+
+
+def test_skinned_list_cull_opt_in(hgb):
+    """OPT-IN culling of skinned display lists (the reference never culls them, scene_forward_pipeline.cpp:560-562; neither does the
+    default path here). hgb_cull_skinned_list keeps a list unless the union over its bones of bounds[lst] carried through
+    world[mtx_idx] * bind_pose[bone] is V_Outside. Expected result: the same definition composed from the oracle port's bit-exact
+    operator*(Mat4,Mat4), operator*(Mat4,MinMax) and TestVisibility (min / max of the union are exact)."""
+    port = oracle_lib.load_port()
+    P = oracle_lib.P
+    fs = scenegen.config_c3(n_chars=96, n_bones=64, n_keys=8)
+    ctx = hgb.Context(0)
+    t = hostmirror.upload(ctx, fs)
+    clocks = hostmirror.PlayClocks(fs)
+    for _ in range(3):
+        ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True)
+    w = ctx.get_worlds()
+    n_lists = 96 * 2
+    bone_off = (np.arange(n_lists + 1) * 32).astype(np.uint32)
+    bounds_idx = np.tile(np.array([0, 1], np.uint32), 96)
+    mtx, bind, pose, bounds = t["skin_mtx_slot"], t["skin_bind_idx"], np.ascontiguousarray(t["bind_pose"], np.float32), np.ascontiguousarray(t["bounds"], np.float32)
+    assert len(mtx) == n_lists * 32
+    got_all = []
+    for cam_z in (0.0, -40.0, 150.0):
+        fr = hostmirror.make_perspective_frustum(0.1, 90.0, 0.9, 16.0, 9.0, np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, cam_z], np.float32))[0]
+        got = ctx.cull_skinned_list(bone_off, mtx, bind, pose, bounds_idx, bounds, fr)
+        want = []
+        for li in range(n_lists):
+            mn, mx = np.full(3, np.inf, np.float32), np.full(3, -np.inf, np.float32)
+            for b in range(bone_off[li], bone_off[li + 1]):
+                m, box = np.zeros(12, np.float32), np.zeros(6, np.float32)
+                port.hgp_mat4_mul(P(np.ascontiguousarray(w[mtx[b]])), P(np.ascontiguousarray(pose[bind[b]])), P(m))
+                port.hgp_minmax_transform(P(m), P(np.ascontiguousarray(bounds[bounds_idx[li]])), P(box))
+                mn, mx = np.minimum(mn, box[:3]), np.maximum(mx, box[3:])
+            if port.hgp_test_visibility(P(np.ascontiguousarray(fr, np.float32)), P(np.concatenate([mn, mx]).astype(np.float32))) != 0:
+                want.append(li)
+        assert len(got) == len(want) and (got == np.array(want, np.uint32)).all(), cam_z
+        got_all.append(len(got))
+    assert 0 < min(got_all) < n_lists, got_all  # the frusta really cut the crowd
+    with pytest.raises(hgb.HgbError, match="at most 32"):
+        ctx.cull_skinned_list(np.array([0, 40], np.uint32), mtx[:40], bind[:40], pose, bounds_idx[:1], bounds, fr)
+    ctx.close()
