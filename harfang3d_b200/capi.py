@@ -42,6 +42,7 @@ SIGNATURES = {
     "hgb_sync": (_i, [_p]),
     "hgb_set_topology": (_i, [_p, _u32, _p, _p]),
     "hgb_upload_trs": (_i, [_p, _u32, _u32, _p]),
+    "hgb_set_parents": (_i, [_p, _u32, _p, _p, _p]),
     "hgb_set_preset_world": (_i, [_p, _u32, _p, _p]),
     "hgb_set_matrices": (_i, [_p, _u32, _p, _p, _i]),
     "hgb_set_bounds": (_i, [_p, _u32, _p]),
@@ -159,6 +160,12 @@ class Context:
         n = len(parent_slot)
         self._ck(self._L.hgb_set_topology(self._h, n, _ptr(parent_slot, np.uint32, "parent_slot"), _ptr(used, np.uint8, "used")))
         self.n_slots = n
+
+    def set_parents(self, slots, parent_slots):
+        """incremental SetTransformParent; returns True when the layout had to be rebuilt (a level changed)"""
+        rebuilt = C.c_int(0)
+        self._ck(self._L.hgb_set_parents(self._h, len(slots), _ptr(slots, np.uint32, "slots"), _ptr(parent_slots, np.uint32, "parent_slots"), C.byref(rebuilt)))
+        return bool(rebuilt.value)
 
     def upload_trs(self, trs9, first=0):
         assert trs9.ndim == 2 and trs9.shape[1] == 9

@@ -196,7 +196,7 @@ void Scene::DestroyNode(NodeRef ref) {
 	if (!nodes.is_valid(ref))
 		return;
 	nodes.remove_ref(ref);
-	impl->topology_dirty = true; // children of its transform become roots (a stale parent ref is a root, scene.cpp:268-272)
+	impl->topology_dirty = true, impl->topology_reparent_only = false; // children of its transform become roots (a stale parent ref is a root, scene.cpp:268-272)
 	impl->entries_dirty = true;
 	impl->anims_dirty = true;
 }
@@ -256,7 +256,7 @@ bool Scene::IsChildOf(NodeRef node, NodeRef parent) const { // walk up from `nod
 Transform Scene::CreateTransform() {
 	const ComponentRef ref = transforms.add_ref(Transform_{});
 	impl->fresh_slots.push_back(ref.idx);
-	impl->topology_dirty = true;
+	impl->topology_dirty = true, impl->topology_reparent_only = false;
 	return {this, ref};
 }
 
@@ -266,14 +266,14 @@ Transform Scene::CreateTransform(const Vec3 &pos, const Vec3 &rot, const Vec3 &s
 	t.parent = parent;
 	const ComponentRef ref = transforms.add_ref(t);
 	impl->fresh_slots.push_back(ref.idx);
-	impl->topology_dirty = true;
+	impl->topology_dirty = true, impl->topology_reparent_only = false;
 	return {this, ref};
 }
 
 void Scene::DestroyTransform(ComponentRef ref) {
 	if (transforms.is_valid(ref)) {
 		transforms.remove_ref(ref);
-		impl->topology_dirty = true;
+		impl->topology_dirty = true, impl->topology_reparent_only = false;
 		impl->entries_dirty = true;
 		impl->anims_dirty = true;
 	}
@@ -284,7 +284,7 @@ void Scene::MarkBulkEdit() {
 	impl->fresh_slots.clear();
 	for (uint32_t i = transforms.first(); i != transforms.invalid_idx; i = transforms.next(i))
 		impl->fresh_slots.push_back(i);
-	impl->topology_dirty = true;
+	impl->topology_dirty = true, impl->topology_reparent_only = false;
 	impl->trs_all_dirty = true;
 	impl->entries_dirty = true;
 	impl->anims_dirty = true;
@@ -388,6 +388,10 @@ void Scene::SetTransformParent(ComponentRef ref, const NodeRef &v) {
 		walk = transforms[t.idx].parent;
 	}
 	transforms[ref.idx].parent = v;
+	if (!impl->topology_dirty) // first hierarchy edit since the last sync: a candidate for the incremental path (hgb_set_parents)
+		impl->topology_reparent_only = true, impl->reparented.clear();
+	if (impl->topology_reparent_only)
+		impl->reparented.push_back(ref.idx);
 	impl->topology_dirty = true;
 }
 
@@ -405,7 +409,7 @@ void Scene::SetNodeTransform(NodeRef ref, ComponentRef cref) {
 		return;
 	}
 	nodes[ref.idx].transform = cref;
-	impl->topology_dirty = true; // children reach their parent's transform through the parent NODE (scene.cpp:268)
+	impl->topology_dirty = true, impl->topology_reparent_only = false; // children reach their parent's transform through the parent NODE (scene.cpp:268)
 	impl->entries_dirty = true;
 	impl->anims_dirty = true;
 }
@@ -982,6 +986,34 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 	RefreshFlagsFromDevice(); // node flags are about to be read (entry tables) and the set of tracked nodes may change
 	const uint32_t n = uint32_t(transforms.capacity());
 
+	if (impl->topology_dirty && impl->topology_reparent_only && !impl->reparented.empty() && impl->device_slots == n && impl->fresh_slots.empty()) {
+		// only SetTransformParent calls since the last sync: the incremental path (parent rows only when no level changes)
+		std::vector<uint32_t> slots, parents;
+		for (uint32_t i : impl->reparented) {
+			if (!transforms.is_used(i))
+				continue;
+			uint32_t par = HGB_ROOT;
+			const NodeRef pn = transforms[i].parent;
+			if (nodes.is_valid(pn)) {
+				const ComponentRef pt = nodes[pn.idx].transform;
+				if (transforms.is_valid(pt) && pt.idx != i)
+					par = pt.idx;
+			}
+			slots.push_back(i), parents.push_back(par);
+		}
+		int rebuilt = 0;
+		if (slots.empty() || hgb_set_parents(ctx, uint32_t(slots.size()), slots.data(), parents.data(), &rebuilt) == 0) {
+			impl->topology_dirty = false;
+			if (rebuilt) {
+				RefreshTRSFromDevice();
+				impl->trs_all_dirty = true;
+			}
+		} else {
+			warn(hgb_last_error());
+		}
+	}
+	impl->topology_reparent_only = false;
+	impl->reparented.clear();
 	if (impl->topology_dirty) {
 		RefreshTRSFromDevice(); // sampled values must survive the re-layout: they are re-uploaded below
 		std::vector<uint32_t> parent(n, HGB_ROOT);
@@ -1629,7 +1661,7 @@ size_t Scene::GarbageCollect() {
 		if (!trs_used[i]) {
 			transforms.remove_ref(transforms.get_ref(i));
 			++removed;
-			impl->topology_dirty = true;
+			impl->topology_dirty = true, impl->topology_reparent_only = false;
 		}
 		i = nx;
 	}

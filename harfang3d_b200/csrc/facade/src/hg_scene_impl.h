@@ -9,6 +9,8 @@ namespace hg {
 
 struct Scene::Impl {
 	bool topology_dirty{true};
+	bool topology_reparent_only{false}; // since the last sync the only hierarchy edits were SetTransformParent calls on `reparented`
+	std::vector<uint32_t> reparented;
 	bool trs_all_dirty{true};
 	std::vector<uint32_t> dirty_trs;
 	bool anims_dirty{true};

@@ -237,6 +237,62 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 	return 0;
 }
 
+// Incremental hierarchy edit: new parents for a few transforms. When every moved transform stays in its hierarchy LEVEL (its new parent
+// sits one level above it, or it was and stays a root) the depth-sorted layout is still valid: only the parent row of those positions
+// is rewritten — a few bytes, no re-sort, no table rebuild, no graph re-capture (parent rows are data the kernels read). A same-level
+// move cannot close a cycle (the new parent is not below the node). Anything else falls back to the full hgb_set_topology rebuild.
+int hgb_set_parents(hgb_ctx *c, uint32_t n, const uint32_t *slot, const uint32_t *parent_slot, int *out_rebuilt) {
+	if (!c)
+		return fail("null context");
+	if (out_rebuilt)
+		*out_rebuilt = 0;
+	if (!n)
+		return 0;
+	join_post(c);
+	CK(cudaSetDevice(c->device));
+	auto level_of = [&](uint32_t pos) { return uint32_t(std::upper_bound(c->level_off.begin(), c->level_off.end(), pos) - c->level_off.begin()) - 1u; };
+	std::vector<uint32_t> pos(n), par(n);
+	bool fast = true;
+	for (uint32_t i = 0; i < n; ++i) {
+		if (slot[i] >= c->n_slots || c->pos_of_slot[slot[i]] >= c->n_pos)
+			return fail("hgb_set_parents: slot %u is not a live transform", slot[i]);
+		pos[i] = c->pos_of_slot[slot[i]];
+		const uint32_t ps = parent_slot[i];
+		const bool root = ps == HGB_ROOT || ps >= c->n_slots || c->pos_of_slot[ps] >= c->n_pos || ps == slot[i]; // stale / unused parent = root (scene.cpp:268-272)
+		par[i] = root ? kRoot : c->pos_of_slot[ps];
+		const uint32_t lv = level_of(pos[i]);
+		if (root ? lv != 0 : level_of(par[i]) + 1 != lv)
+			fast = false;
+	}
+	if (!fast) { // levels change: full rebuild from the current parents with the edits applied
+		std::vector<uint32_t> parent(c->n_slots, HGB_ROOT);
+		std::vector<uint8_t> used(c->n_slots, 0);
+		for (uint32_t p = 0; p < c->n_pos; ++p) {
+			const uint32_t s_ = c->slot_of_pos[p];
+			used[s_] = 1;
+			parent[s_] = c->parent_pos_h[p] == kRoot ? HGB_ROOT : c->slot_of_pos[c->parent_pos_h[p]];
+		}
+		for (uint32_t i = 0; i < n; ++i)
+			parent[slot[i]] = parent_slot[i];
+		if (out_rebuilt)
+			*out_rebuilt = 1;
+		return hgb_set_topology(c, c->n_slots, parent.data(), used.data());
+	}
+	for (uint32_t i = 0; i < n; ++i)
+		c->parent_pos_h[pos[i]] = par[i];
+	CK(c->staging.reserve(size_t(n) * 8));
+	uint32_t *st = c->staging.as<uint32_t>();
+	CK(cudaStreamSynchronize(c->stream)); // the pinned staging block may still feed an earlier copy
+	memcpy(st, pos.data(), size_t(n) * 4);
+	memcpy(st + n, par.data(), size_t(n) * 4);
+	CK(c->staging_d.reserve(size_t(n) * 8));
+	CK(cudaMemcpyAsync(c->staging_d.p, st, size_t(n) * 8, cudaMemcpyHostToDevice, c->stream));
+	k_set_parent_rows<<<grid_for(n, 128), 128, 0, c->stream>>>(c->tiles.as<uint32_t>(), c->staging_d.as<uint32_t>(), c->staging_d.as<uint32_t>() + n, n);
+	++c->launches;
+	CK(cudaGetLastError());
+	return 0;
+}
+
 int hgb_upload_trs(hgb_ctx *c, uint32_t first, uint32_t count, const float *trs9) {
 	if (!c)
 		return fail("null context");

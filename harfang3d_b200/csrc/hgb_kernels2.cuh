@@ -795,6 +795,13 @@ __global__ void __launch_bounds__(256) k_fill_rows(uint32_t *__restrict__ tiles,
 		tiles[tile_word(p, row)] = src[p];
 }
 
+// re-parenting inside a level (hgb_set_parents): only the parent row of the moved positions changes
+__global__ void __launch_bounds__(128) k_set_parent_rows(uint32_t *__restrict__ tiles, const uint32_t *__restrict__ pos, const uint32_t *__restrict__ par, uint32_t n) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n)
+		tiles[tile_word(pos[i], kRowParent)] = par[i];
+}
+
 // worlds in POSITION order -> SLOT order (only when the permutation is not the identity); one thread per float4
 __global__ void __launch_bounds__(256) k_gather_worlds(const float4 *__restrict__ world, const uint32_t *__restrict__ pos_of_slot, uint32_t first_slot,
 	uint32_t count, float4 *__restrict__ out) {

@@ -88,6 +88,11 @@ int hgb_sync(hgb_ctx *);
 /* Transform hierarchy. parent_slot[i] = slot of the parent's transform (node->transform hop already resolved,
  * scene.cpp:268) or HGB_ROOT; used[i]==0 marks holes of the slot list (vector_list.h). Rebuilds the depth-sorted layout. */
 int hgb_set_topology(hgb_ctx *, uint32_t n_slots, const uint32_t *parent_slot, const uint8_t *used /* nullable */);
+/* Incremental form for SetTransformParent (harfang/engine/component.cpp:184-203) on a few transforms: new parent slot (or HGB_ROOT) per listed slot.
+ * When every moved transform stays in its hierarchy level (new parent one level above; roots stay roots) only the parent rows change on the
+ * device — no re-sort, no table rebuild, no graph re-capture; *out_rebuilt = 0. Otherwise the layout is rebuilt as by hgb_set_topology and
+ * *out_rebuilt = 1 (the caller then re-derives what it derives after hgb_set_topology). */
+int hgb_set_parents(hgb_ctx *, uint32_t n, const uint32_t *slot, const uint32_t *parent_slot, int *out_rebuilt /* nullable */);
 /* TRS of slots [first, first+count) — dirty-range upload. */
 int hgb_upload_trs(hgb_ctx *, uint32_t first, uint32_t count, const float *trs9);
 /* SetNodeWorldMatrix overrides (scene.cpp:768-786) for the NEXT hgb_update only. */

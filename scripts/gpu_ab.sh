@@ -13,7 +13,7 @@ for v in "${V[@]}"; do
 import json
 try:
     d=json.load(open("gpurun_out/ab_$i.json"))
-    print("  ms/step %.4f value %.0f e2e %.0f resident %.0f frac %.3f"%(d["ms_per_step"],d["value"],d["e2e"]["value"],d["e2e_resident"]["value"],d["roofline"]["frac"]), d["roofline"]["kernel_ms_per_step"])
+    print("  ms/step %.4f value %.0f e2e %.0f resident %.0f frac %.3f"%(d["ms_per_step"],d["value"],d["e2e"]["value"],d.get("e2e_facade",{}).get("value",0),d["roofline"]["frac"]), d["roofline"]["kernel_ms_per_step"])
 except Exception as e:
     print("  failed", e); print(open("gpurun_out/ab_$i.err").read()[-800:])
 PY
