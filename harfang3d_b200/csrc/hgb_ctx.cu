@@ -150,7 +150,6 @@ struct hgb_ctx {
 	bool entries_dirty = true; // CSR by position must be rebuilt
 
 	// device scene
-	DBuf top_local; // scratch: local matrices of the positions k_update_top covers (sized in hgb_set_topology)
 	DBuf tiles, world[2], preset, pos_of_slot_d; // tiles: node tiles (TRS rows, parent, first entry), see hgb_kernels.cuh
 	uint32_t n_tiles = 0;
 	bool transpose_store = true;
@@ -431,7 +430,7 @@ void hgb_destroy(hgb_ctx *c) {
 		for (cudaGraphExec_t g : a)
 			if (g)
 				cudaGraphExecDestroy(g);
-	DBuf *bufs[] = {&c->top_local, &c->tiles, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
+	DBuf *bufs[] = {&c->tiles, &c->world[0], &c->world[1], &c->preset, &c->pos_of_slot_d, &c->preset_pos, &c->preset_mat, &c->bounds, &c->ent_off,
 		&c->pent, &c->pos_view, &c->inst_planes, &c->inst_planes_x, &c->view_planes_x, &c->inst_start, &c->inst_rank, &c->bone_mtx_pos, &c->bone_bind_idx, &c->bind_pose, &c->bone_out[0],
 		&c->bone_out[1], &c->keys, &c->cursor, &c->tstate, &c->anim_val, &c->bind_pos_d, &c->bind_group_d, &c->tracks_d, &c->play_t_d, &c->staging_d, &c->flush, &c->adhoc_pos, &c->adhoc_meta, &c->adhoc_bounds, &c->adhoc_planes, &c->adhoc_vis, &c->adhoc_out, &c->adhoc_scratch, &c->view_planes, &c->key_rec,
 		&c->en_target_pos, &c->en_off, &c->en_tracks_d, &c->en_keys_d, &c->en_scratch, &c->obj_pos, &c->obj_meta, &c->obj_seg, &c->obounds, &c->mm_acc, &c->peer_out_list, &c->peer_rank_off, &c->peer_aux_out};

@@ -147,18 +147,15 @@ static void launch_level(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t 
 	}
 }
 
-// the first `top_levels` levels (positions [0, e)): local matrices, then chain products (k_top_locals -> k_update_top)
+// the first `top_levels` levels in one launch (k_update_top): positions [0, e)
 static void launch_top(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t e, bool pdl) {
 	const dim3 g = grid_for(e);
-	float *scratch = c->top_local.as<float>();
-	launch_after(c, pdl, k_top_locals, g, dim3(256), s, scratch, e);
-	const bool chain = c->pdl_levels && !c->prof.on;
 	if (!do_fused)
-		launch_after(c, chain, k_update_top<false, false>, g, dim3(256), s, c->views, (const float *)scratch, e);
+		launch_after(c, pdl, k_update_top<false, false>, g, dim3(256), s, c->views, e);
 	else if (c->instance_mode)
-		launch_after(c, chain, k_update_top<true, true>, g, dim3(256), s, c->views, (const float *)scratch, e);
+		launch_after(c, pdl, k_update_top<true, true>, g, dim3(256), s, c->views, e);
 	else
-		launch_after(c, chain, k_update_top<true, false>, g, dim3(256), s, c->views, (const float *)scratch, e);
+		launch_after(c, pdl, k_update_top<true, false>, g, dim3(256), s, c->views, e);
 }
 
 // How many leading levels k_update_top covers: as many as keep the recomputed work (every node of level d evaluates d + 1 local
@@ -176,7 +173,7 @@ static size_t plan_top_levels(const hgb_ctx *c) {
 		evals += add;
 		++d;
 	}
-	return d >= 2 ? d : 0; // a single level gains nothing from the two-launch form
+	return d;
 }
 
 // One frame. Level groups (a level, or a run of small levels) go out in order on the context's stream. The track sampler is HBM-bound
@@ -308,7 +305,6 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 			launch_top(c, s, do_fused, groups[g].e, chain && prev_signals);
 			prev_signals = true;
 			prev_is_sampler = false;
-			++*n_k; // two kernels
 		} else {
 			// a level that directly follows the sampler or another level may start while that one drains (k_update_level waits before
 			// it reads sampled values or parent rows)

@@ -41,7 +41,6 @@ static void expand_planes(const float *cond, uint32_t n_planes, float *out) {
 static inline dim3 grid_for(uint32_t n, uint32_t block = 256) { return dim3((n + block - 1) / block); }
 
 static int prepare_tables(hgb_ctx *c);
-static size_t plan_top_levels(const hgb_ctx *c);
 
 // "Enable" tracks are evaluated on the device (k_sample_enable): before the host-side tables are rebuilt or edited, the state of the
 // tracked nodes is read back and folded into them, so that a rebuild does not resurrect a stale flag.
@@ -230,10 +229,6 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 	c->entries_dirty = true;
 	c->obj_dirty = true;
 	invalidate_graph(c);
-	{ // scratch rows of the top of the hierarchy (never allocated inside a graph capture)
-		const size_t n_top = plan_top_levels(c);
-		CK(c->top_local.reserve(std::max<size_t>(n_top ? c->level_off[n_top] : 0, 1) * 48));
-	}
 	return 0;
 }
 

@@ -257,34 +257,19 @@ __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views vi
 		cull_node_entries<PER_INSTANCE>(s, world, meta, eidx, s_planes, views.n_views, p);
 }
 
-// ---- the top of the hierarchy in TWO launches, whatever its depth -----------------------------------------------------------------------
+// ---- the top of the hierarchy in ONE launch ---------------------------------------------------------------------------------
 // The upper levels of a hierarchy hold 1 ... ~10^5 nodes each; one launch per level costs ~7 µs apiece there (launch ramp plus the
-// dependent tile -> parent -> math chain), far more than their bytes. The positions [0, end) of the first few levels are covered by
-//   k_top_locals : every node's LOCAL matrix (TransformationMat4: the three sincos, all of the arithmetic) into a scratch row — no
-//                  dependency between threads at all;
-//   k_update_top : every node walks up its ancestor chain (parent rows are edit-time data) and multiplies the scratch rows down again,
-//                  world = ((L_root * L_1) * L_2) ... * L_node — the very sequence of products ComputeTransformWorldMatrix performs through
-//                  its recursion (scene.cpp:263-277: world[parent] is itself world[grandparent] * local), so every row is bit-identical
-//                  to the level-by-level result; a product is only recomputed by each descendant instead of read back. No dependency
-//                  between threads either: a chain of d loads + d 3x4 products per node.
-// The host bounds the redundant work (sum over the covered levels of nodes x depth, hgb_options.top_walk) and the chain length
+// dependent tile -> parent -> math chain), far more than their bytes. This kernel covers the positions [0, end) of the first few
+// levels with NO dependency between its threads: every node walks up its ancestor chain (parent rows are edit-time data) and
+// multiplies the local matrices down again, world = ((L_root * L_1) * L_2) ... * L_node — the very sequence of operations
+// ComputeTransformWorldMatrix performs through its recursion (scene.cpp:263-277: world[parent] is itself world[grandparent] * local),
+// so every row is bit-identical to the level-by-level result; it is only recomputed by each descendant instead of read back. The
+// host bounds the redundant work (sum over the covered levels of nodes x depth, hgb_options.top_walk) and the chain length
 // (kMaxWalk). A chain stops at a preset ancestor (SetNodeWorldMatrix), whose row k_apply_presets wrote ahead of the frame.
 constexpr int kMaxWalk = 12;
 
-__global__ void __launch_bounds__(256, 6) k_top_locals(SceneDev s, float *__restrict__ top_local, uint32_t end) {
-	// chained behind the track sampler (or plain): it reads sampled values, so it waits first thing and releases its dependent only
-	// behind the wait
-	asm volatile("griddepcontrol.wait;" ::: "memory");
-	asm volatile("griddepcontrol.launch_dependents;");
-	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-	if (p >= end)
-		return;
-	const uint32_t *t = s.tiles + tile_word(p, 0);
-	store_mat4(top_local + size_t(p) * 12, unpack_mat4(node_local(s, t, t[kRowEntMeta * 32])));
-}
-
 template <bool FUSED, bool PER_INSTANCE>
-__global__ void __launch_bounds__(256, 6) k_update_top(SceneDev s, Views views, const float *__restrict__ top_local, uint32_t end) {
+__global__ void __launch_bounds__(256, 6) k_update_top(SceneDev s, Views views, uint32_t end) {
 	__shared__ float4 s_out[8][96];
 	__shared__ float4 s_planes[kMaxViews * 12];
 	if (FUSED && !PER_INSTANCE) {
@@ -293,49 +278,44 @@ __global__ void __launch_bounds__(256, 6) k_update_top(SceneDev s, Views views, 
 				s_planes[i] = views.planes_x[i];
 		__syncthreads();
 	}
+	// chained behind the track sampler (or plain): it reads sampled values throughout, so it waits first thing and releases its
+	// dependents only behind the wait (they read sampled values ahead of THEIR wait)
+	asm volatile("griddepcontrol.wait;" ::: "memory");
+	asm volatile("griddepcontrol.launch_dependents;");
 	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
 	const bool live = p < end;
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-	// the chain is edit-time data: walked (and the scratch rows it names asked for) while k_top_locals still runs
-	uint32_t chain[kMaxWalk]; // ancestors whose local matrices enter the product, nearest first
-	int n = 0;
-	uint32_t q = kRoot, meta = 0, eidx = 0;
-	bool preset = false;
+	if (__ballot_sync(0xffffffffu, live) == 0)
+		return;
+	Mat4 world;
+	uint32_t meta = 0, eidx = 0;
 	if (live) {
 		const uint32_t *t = s.tiles + tile_word(p, 0);
 		meta = t[kRowEntMeta * 32];
 		if (FUSED)
 			eidx = t[kRowEntIdx * 32];
-		preset = s.preset && s.preset[p];
-		if (!preset) {
-			q = t[kRowParent * 32];
-			while (q != kRoot && !(s.preset && s.preset[q]) && n < kMaxWalk) {
-				chain[n++] = q;
-				prefetch_l2(top_local + size_t(q) * 12);
-				prefetch_l2(top_local + size_t(q) * 12 + 11);
-				q = s.tiles[tile_word(q, kRowParent)];
-			}
-		}
-	}
-	asm volatile("griddepcontrol.wait;" ::: "memory"); // the scratch rows are complete (and, transitively, the sampler)
-	asm volatile("griddepcontrol.launch_dependents;");
-	if (__ballot_sync(0xffffffffu, live) == 0)
-		return;
-	Mat4 world;
-	if (live) {
-		if (preset) {
+		if (s.preset && s.preset[p]) {
 			world = load_mat4(s.world + size_t(p) * 12);
 		} else {
+			uint32_t chain[kMaxWalk]; // ancestors that must be recomputed, nearest first
+			int n = 0;
+			uint32_t q = t[kRowParent * 32];
+			while (q != kRoot && !(s.preset && s.preset[q]) && n < kMaxWalk) {
+				chain[n++] = q;
+				q = s.tiles[tile_word(q, kRowParent)];
+			}
 			bool have = q != kRoot; // stopped at a preset ancestor: its row is the base
 			if (have)
 				world = load_mat4(s.world + size_t(q) * 12);
 			for (int i = n - 1; i >= 0; --i) {
-				const Mat4 la = load_mat4(top_local + size_t(chain[i]) * 12);
-				world = have ? mat4_mul(world, la) : la;
+				const uint32_t a = chain[i];
+				const uint32_t *ta = s.tiles + tile_word(a, 0);
+				const Mat4p la = node_local(s, ta, ta[kRowEntMeta * 32]);
+				world = have ? mat4_mul_p(world, la) : unpack_mat4(la);
 				have = true;
 			}
-			const Mat4 local = load_mat4(top_local + size_t(p) * 12);
-			world = have ? mat4_mul(world, local) : local;
+			const Mat4p local = node_local(s, t, meta);
+			world = have ? mat4_mul_p(world, local) : unpack_mat4(local);
 		}
 	}
 	store_world_rows(s, s_out[warp], world, live, p, lane, end);
