@@ -54,7 +54,7 @@ typedef struct hgb_options {
 	                      parity; frame N + 2 waits for the tail of frame N, every other entry point joins the pending tails first), so
 	                      results and API semantics are unchanged. 0 = default (on), 1 = on, -1 = off (one graph per frame) */
 	int top_walk;      /* the leading levels of the hierarchy go out as ONE launch (k_update_top: every node recomputes its ancestor chain, no
-	                      dependency between threads). 0 = default budget (levels are added while sum(nodes x depth) <= 2.5 M), -1 = off (one
+	                      dependency between threads). 0 = default budget (levels are added while sum(nodes x depth) <= 250 K: measured best on the 16M-node batch, profiles/README.md r02), -1 = off (one
 	                      launch per level), n = budget in node evaluations */
 	int overlap_sampler; /* 1: tracks are sampled in chunks by target level on a second stream, overlapped with the level kernels. Default 0:
 	                        both kernels lean on HBM, running them together measured 1-8 % slower than back to back (profiles r01c) */

@@ -21,6 +21,11 @@ for name, fs in (("1M", scenegen.config_c2(seed=2, n_nodes=1_000_000)), ("16M", 
     t0 = time.perf_counter(); ctx.set_topology(parent); ctx.sync(); topo = time.perf_counter() - t0
     t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); first = time.perf_counter() - t0
     t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); second = time.perf_counter() - t0
-    out[name] = {"steady_frame_ms": steady * 1e3, "set_topology_ms": topo * 1e3, "first_update_after_edit_ms": first * 1e3, "second_update_ms": second * 1e3}
+    # the incremental path: the same leaf moved under another parent of its level (hgb_set_parents: parent rows only)
+    slot = np.array([leaf], np.uint32)
+    newp = np.array([parent[leaf - 9]], np.uint32)
+    t0 = time.perf_counter(); rebuilt = ctx.set_parents(slot, newp); ctx.sync(); inc = time.perf_counter() - t0
+    t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); inc_first = time.perf_counter() - t0
+    out[name] = {"incremental_reparent_ms": inc * 1e3, "incremental_rebuilt": bool(rebuilt), "first_update_after_incremental_ms": inc_first * 1e3,"steady_frame_ms": steady * 1e3, "set_topology_ms": topo * 1e3, "first_update_after_edit_ms": first * 1e3, "second_update_ms": second * 1e3}
     ctx.close()
 print(json.dumps(out))
