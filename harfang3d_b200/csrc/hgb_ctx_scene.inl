@@ -886,10 +886,28 @@ static int prepare_tables(hgb_ctx *c) {
 	for (size_t i = 0; i < tr.size(); ++i) {
 		const hgb_track &h = c->tracks_h[i];
 		const uint32_t slot = uint32_t(std::lower_bound(uniq.begin(), uniq.end(), keys_pg[i]) - uniq.begin());
-		tr[i] = Track{slot, h.key_off, h.key_count, h.play, h.kind, 0};
+		tr[i] = Track{slot, h.key_off + (h.kind == 3 ? c->n_v3_keys : 0u), h.key_count, h.play, h.kind, 1}; // key_off: compact-pool key for now
 	}
 	for (size_t r = 0; r + 1 < c->round_off.size(); ++r)
 		std::sort(tr.begin() + c->round_off[r], tr.begin() + c->round_off[r + 1], [](const Track &a, const Track &b) { return a.out_slot < b.out_slot; });
+	// interval records: neighbour tracks of a round are paired and share their 128-byte lines (see k_build_key_records)
+	std::vector<TrackBuild> tb(tr.size());
+	uint64_t rec_units = 0;
+	for (size_t r = 0; r + 1 < c->round_off.size(); ++r)
+		for (size_t i = c->round_off[r]; i < c->round_off[r + 1];) {
+			const bool pair = i + 1 < c->round_off[r + 1];
+			const uint32_t n0 = tr[i].key_count, n1 = pair ? tr[i + 1].key_count : 0u;
+			for (int h = 0; h < (pair ? 2 : 1); ++h) {
+				Track &t_ = tr[i + h];
+				tb[i + h] = TrackBuild{t_.key_off, uint32_t(rec_units) + uint32_t(h), t_.key_count, t_.kind, uint8_t(pair ? 2 : 1), {0, 0}};
+				t_.key_off = uint32_t(rec_units) + uint32_t(h);
+				t_.stride = uint8_t(pair ? 2 : 1);
+			}
+			rec_units += pair ? 2ull * std::max(n0, n1) : n0;
+			i += pair ? 2 : 1;
+		}
+	if (rec_units >= (1ull << 32))
+		return fail("the interval records of the bound tracks exceed 2^32 x 64 bytes");
 	if (upload(c, c->tracks_d, tr.data(), tr.size() * sizeof(Track)))
 		return 1;
 	// chunk boundaries of the overlapped sampler: target position of every round-0 track (ascending: tracks are sorted by slot = position)
@@ -899,13 +917,16 @@ static int prepare_tables(hgb_ctx *c) {
 		for (size_t i = 0; i < tr.size(); ++i)
 			c->trk_pos_h[i] = uint32_t(uniq[tr[i].out_slot] >> 2);
 	}
-	if (c->records_dirty && !tr.empty()) { // 64-byte interval records from the compact key pool (device side, once per key/track edit)
-		const size_t total = size_t(c->n_v3_keys) + c->n_q_keys;
-		CK(c->key_rec.reserve((total + 1) * 64));
-		k_build_key_records<<<grid_for(uint32_t(tr.size())), 256, 0, c->stream>>>(c->tracks_d.as<Track>(), uint32_t(tr.size()), c->keys.as<uint4>(), c->n_v3_keys,
-			c->key_rec.as<uint4>());
+	if (!tr.empty()) { // 64-byte interval records from the compact key pool (device side, at every re-bind: the layout follows the track order)
+		DBuf tb_d;
+		if (upload(c, tb_d, tb.data(), tb.size() * sizeof(TrackBuild)))
+			return 1;
+		CK(c->key_rec.reserve((rec_units + 2) * 64));
+		k_build_key_records<<<grid_for(uint32_t(tr.size())), 256, 0, c->stream>>>(tb_d.as<TrackBuild>(), uint32_t(tr.size()), c->keys.as<uint4>(), c->key_rec.as<uint4>());
 		++c->launches;
 		CK(cudaGetLastError());
+		CK(cudaStreamSynchronize(c->stream));
+		tb_d.release();
 		c->records_dirty = false;
 	}
 	const uint32_t n_bind = uint32_t(uniq.size());

@@ -12,11 +12,17 @@ namespace hgb {
 //   below returns the same index (upper_bound) because keys are sorted by time.
 struct alignas(16) Track { // 16 B, read as one uint4
 	uint32_t out_slot;   // anim_val[] slot of the (node, pos|rot|scale) triple this track drives
-	uint32_t key_off;    // first key in the pool of its kind
+	uint32_t key_off;    // first interval record of the track, in 64-byte units (k_build_key_records lays the records out)
 	uint32_t key_count;
 	uint16_t play;       // index into play_t[]
 	uint8_t kind;        // 0 Position, 1 Rotation (Euler vec3), 2 Scale, 3 Rotation (quaternion)
-	uint8_t pad;
+	uint8_t stride;      // 64-byte units between two records of the track: 2 when it shares its 128-byte lines with its neighbour track
+};
+struct TrackBuild { // bind time: where a track's keys are and where its records go
+	uint32_t key_first;  // first key in the compact pool (quaternion keys already offset)
+	uint32_t rec_off;    // = Track::key_off
+	uint32_t key_count;
+	uint8_t kind, stride, pad[2];
 };
 
 // One key = one 32-byte record (one DRAM sector), vec3 Hermite and quaternion keys alike:
@@ -99,8 +105,12 @@ __device__ __forceinline__ void quat_to_euler(float x, float y, float z, float w
 // y1 / y2 = values of keys k / k+1; m0 / m1 = the two tangents of HermiteInterpolate (foundation/math.h:137-149), which depend on the
 // keys k-1 ... k+2 and on tension / bias of key k but NOT on the evaluation time: k_build_key_records computes them once, with the
 // very operations (and this TU's -fmad=false) the evaluation would use, so hoisting them changes no bit of any result — and the
-// per-frame gather shrinks from four whole keys (128 bytes) to 64. t(k+1) is INT64_MAX in a track's last record. One frame = half an
-// aligned line per track. Costs 2x the key memory (the 16M-node batch's 64M keys take 4 GB), built on the device at bind time.
+// per-frame gather shrinks from four whole keys (128 bytes) to 64. t(k+1) is INT64_MAX in a track's last record.
+// DRAM moves 128-byte lines (measured: 64-byte records laid out track after track still cost 128 bytes of DRAM read each, profiles r02),
+// so the records of two NEIGHBOUR tracks (consecutive threads of the sampler) are interleaved: record k of the pair's first track is the
+// lower half of line k, record k of the second the upper half. Tracks that advance together — the tracks of one anim, instanced anims —
+// then share every line they fetch. Every track owns its records (a key range shared by several tracks is laid out once per track).
+// Costs 2x the key memory (the 16M-node batch's 64M keys take 4 GB), built on the device at bind time.
 constexpr uint32_t kRecU4 = 4; // uint4s per record
 
 // tangents of one component of HermiteInterpolate (foundation/math.h:137-149), in the reference's operation order
@@ -111,19 +121,20 @@ __device__ __forceinline__ void hermite_tangents(float y0, float y1, float y2, f
 	m1 += (y3 - y2) * (1.F - bias) * (1.F - tension) / 2.F;
 }
 
-__global__ void __launch_bounds__(256) k_build_key_records(const Track *__restrict__ tracks, uint32_t n_tracks, const uint4 *__restrict__ keys,
-	uint32_t quat_base, uint4 *__restrict__ rec) {
+__global__ void __launch_bounds__(256) k_build_key_records(const TrackBuild *__restrict__ tracks, uint32_t n_tracks, const uint4 *__restrict__ keys,
+	uint4 *__restrict__ rec) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n_tracks)
 		return;
 	const uint32_t n = tracks[i].key_count;
 	const bool quat = tracks[i].kind == 3;
-	const size_t base = size_t(tracks[i].key_off) + (quat ? quat_base : 0u);
+	const size_t base = tracks[i].key_first;
+	const size_t rec_off = tracks[i].rec_off, stride = tracks[i].stride;
 	for (uint32_t k = 0; k < n; ++k) {
 		const uint32_t k0 = k > 0 ? k - 1 : 0u, k2 = min(k + 1, n - 1), k3 = min(k + 2, n - 1);
 		const uint4 a1 = keys[(base + k) * 2], b1 = keys[(base + k) * 2 + 1];
 		const uint4 a2 = keys[(base + k2) * 2], b2 = keys[(base + k2) * 2 + 1];
-		uint4 *d = rec + (base + k) * kRecU4;
+		uint4 *d = rec + (rec_off + k * stride) * kRecU4;
 		d[0] = k + 1 < n ? make_uint4(a1.x, a1.y, a2.x, a2.y) : make_uint4(a1.x, a1.y, 0xffffffffu, 0x7fffffffu);
 		if (quat) { // AnimKeyT<Quaternion>: {t, x, y | z, w}
 			d[1] = make_uint4(a1.z, a1.w, b1.x, b1.y);
@@ -145,15 +156,15 @@ __global__ void __launch_bounds__(256) k_build_key_records(const Track *__restri
 }
 
 // time of key k of a track, read from its record
-__device__ __forceinline__ int64_t rec_key_time(const uint4 *rec, uint32_t k) {
-	const uint2 t = *reinterpret_cast<const uint2 *>(rec + size_t(k) * kRecU4);
+__device__ __forceinline__ int64_t rec_key_time(const uint4 *rec, uint32_t k, uint32_t stride) {
+	const uint2 t = *reinterpret_cast<const uint2 *>(rec + size_t(k) * stride * kRecU4);
 	return int64_t(uint64_t(t.x) | (uint64_t(t.y) << 32));
 }
-__device__ __forceinline__ uint32_t upper_bound_rec(const uint4 *rec, uint32_t n, int64_t at) {
+__device__ __forceinline__ uint32_t upper_bound_rec(const uint4 *rec, uint32_t n, int64_t at, uint32_t stride) {
 	uint32_t lo = 0, hi = n;
 	while (lo < hi) {
 		const uint32_t mid = (lo + hi) >> 1;
-		if (rec_key_time(rec, mid) > at)
+		if (rec_key_time(rec, mid, stride) > at)
 			hi = mid;
 		else
 			lo = mid + 1;
@@ -190,7 +201,7 @@ __global__ void __launch_bounds__(kSampleWarps * 32, 6) k_sample_tracks(AnimDev 
 	if (!__any_sync(0xffffffffu, active))
 		return;
 	const uint32_t n = trk.key_count;
-	const uint32_t kbase = trk.key_off + (trk.kind == 3 ? a.quat_base : 0u);
+	const uint32_t kbase = trk.key_off, kstride = trk.stride;
 	const uint4 *rec = a.rec + size_t(kbase) * kRecU4;
 	uint8_t *sw = s_win[warp];
 	const uint4 *win = reinterpret_cast<const uint4 *>(sw + lane * kWinStride);
@@ -215,7 +226,7 @@ __global__ void __launch_bounds__(kSampleWarps * 32, 6) k_sample_tracks(AnimDev 
 #pragma unroll 1
 	for (int pass = 0; pass < 2; ++pass) {
 		// cooperative fetch: round r serves tracks 8r..8r+7
-		const uint32_t want_rec = want ? kbase + kf1 : 0xffffffffu;
+		const uint32_t want_rec = want ? kbase + kf1 * kstride : 0xffffffffu;
 #pragma unroll
 		for (int r = 0; r < 4; ++r) {
 			const uint32_t tr = r * 8 + grp;
@@ -238,7 +249,7 @@ __global__ void __launch_bounds__(kSampleWarps * 32, 6) k_sample_tracks(AnimDev 
 			} else if (kf1 == 0 && at < tB) {
 				ub = 0;
 			} else {
-				ub = upper_bound_rec(rec, n, at);
+				ub = upper_bound_rec(rec, n, at, kstride);
 				const uint32_t k = ub > 0 ? ub - 1 : 0; // ub == 0: before the first key -> key 0; ub == n: at/after the last key -> key n-1
 				want = k != kf1;
 				kf1 = k;
