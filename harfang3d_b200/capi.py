@@ -59,6 +59,8 @@ SIGNATURES = {
     "hgb_bone_matrices": (_i, [_p, _i]),
     "hgb_sort_keys": (_i, [_p, _i, _u32, _p]),
     "hgb_cull_skinned_list": (_i, [_p, _u32, _p, _p, _p, _u32, _p, _p, _u32, _p, _p, _p, _p]),
+    "hgb_set_entry_records": (_i, [_p, _i, _u32, _p]),
+    "hgb_get_visible_records_ptr": (_i, [_p, _i, _u32, _p, _p]),
     "hgb_get_visible_ptr": (_i, [_p, _i, _u32, _p, _p]),
     "hgb_peer_init": (_i, [_p, _u32, _u32, _u32, _p, _p, _p, _p]),
     "hgb_peer_connect": (_i, [_p, _p, _p]),
@@ -367,6 +369,19 @@ class Context:
         ptr, n = C.POINTER(C.c_uint32)(), C.c_uint32(0)
         self._ck(self._L.hgb_get_visible_ptr(self._h, kind, view, C.byref(ptr), C.byref(n)))
         return np.ctypeslib.as_array(ptr, shape=(n.value,)) if n.value else np.zeros(0, np.uint32)
+
+    def set_entry_records(self, kind, rec16):
+        """one opaque 16-byte record per entry of `kind` ((n, 16) uint8 or (n, 4) uint32)"""
+        r = np.ascontiguousarray(rec16).view(np.uint8).reshape(-1, 16)
+        self._ck(self._L.hgb_set_entry_records(self._h, kind, r.shape[0], r.ctypes.data_as(C.c_void_p)))
+
+    def get_visible_records(self, kind=0, view=0):
+        """the visible list as the entries' 16-byte records (device-side gather) -> (n, 16) uint8 view of the context's pinned buffer"""
+        ptr, n = C.c_void_p(), C.c_uint32(0)
+        self._ck(self._L.hgb_get_visible_records_ptr(self._h, kind, view, C.byref(ptr), C.byref(n)))
+        if not n.value:
+            return np.zeros((0, 16), np.uint8)
+        return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(n.value * 16,)).reshape(-1, 16)
 
     def get_instance_offsets(self):
         out = np.empty(self.n_inst + 1, np.uint32)

@@ -32,8 +32,8 @@ static std::mutex g_registry_mutex;
 static std::map<const void *, Scene *> g_registry;
 
 // A few persistent host threads for the one per-frame host loop that is worth it: turning the visible INDEX list the device returns
-// into the std::vector<ModelDisplayList> the caller asked for (1.6 M x 16 bytes per frame on the 16M-node batch: a gather from a 256 MB
-// table, memory-latency-bound: software prefetch + up to 16 threads). The scene itself stays single-threaded like the reference's
+// into the std::vector<ModelDisplayList> the caller asked for (1.6 M x 16 bytes per frame on the 16M-node batch: the records arrive
+// contiguous in pinned memory — the device did the gather — and are copied into the caller's vector in 1 MB chunks). The scene itself stays single-threaded like the reference's
 // (SURVEY.md §8b): the workers only ever run inside GetVisibleModelDisplayLists and touch nothing but its input and output arrays.
 namespace {
 class GatherPool {
@@ -1244,8 +1244,12 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 			}
 		}
 		check(hgb_set_bounds(ctx, uint32_t(bounds6.size() / 6), bounds6.data()));
-		for (int k = 0; k < 2; ++k)
+		static_assert(sizeof(ModelDisplayList) == 16, "the device keeps one 16-byte record per entry");
+		for (int k = 0; k < 2; ++k) {
 			check(hgb_set_display_entries(ctx, k, uint32_t(mtx[k].size()), mtx[k].data(), bidx[k].data(), impl->ent_flags[k].data(), nullptr));
+			if (!impl->ent[k].empty()) // the display lists themselves: survivors come back as these records (GetVisibleModelDisplayLists)
+				check(hgb_set_entry_records(ctx, k, uint32_t(impl->ent[k].size()), impl->ent[k].data()));
+		}
 		impl->entries_dirty = false;
 	}
 	if (impl->enable_state_push && !impl->enable_nodes.empty()) { // the host's flags are the truth right now: tracked nodes take them
@@ -1285,26 +1289,25 @@ bool Scene::GetVisibleModelDisplayLists(uint32_t view, bool transparent, std::ve
 		warn("GetVisibleModelDisplayLists: no fused culling result for this view (SetCullingFrustums + Update first)");
 		return false;
 	}
-	const uint32_t *idx = nullptr; // pinned buffer owned by the context: count and list in one round trip
+	// the survivors' ModelDisplayList records, gathered on the device (a sparse walk through a table of 16 bytes per entry is what a GPU
+	// is good at) and landed contiguously in a pinned buffer: count and records in one round trip
+	const void *rec = nullptr;
 	uint32_t n = 0;
-	if (hgb_get_visible_ptr(ctx, k, view, &idx, &n)) {
+	if (hgb_get_visible_records_ptr(ctx, k, view, &rec, &n)) {
 		warn(hgb_last_error());
 		return false;
 	}
 	// ModelDisplayList is trivially copyable: size the vector once (a caller that reuses its vector pays no re-initialisation when
-	// the count barely moves) and let the pool gather the 16-byte records
-	static_assert(std::is_trivially_copyable<ModelDisplayList>::value, "gathered with plain stores");
+	// the count barely moves) and let the pool copy the contiguous records in
+	static_assert(std::is_trivially_copyable<ModelDisplayList>::value, "copied with memcpy");
 	out.resize(n);
-	const ModelDisplayList *table = impl->ent[k].data();
-	ModelDisplayList *dst = out.data();
-	const uint32_t chunk = 1u << 15, n_chunks = (n + chunk - 1) / chunk;
+	const uint8_t *src = static_cast<const uint8_t *>(rec);
+	uint8_t *dst = reinterpret_cast<uint8_t *>(out.data());
+	const size_t bytes = size_t(n) * sizeof(ModelDisplayList), chunk = size_t(1) << 20;
+	const uint32_t n_chunks = uint32_t((bytes + chunk - 1) / chunk);
 	GatherPool::get().run(n_chunks, [=](uint32_t c) {
-		const uint32_t e = std::min(n, (c + 1) * chunk);
-		for (uint32_t i = c * chunk; i < e; ++i) {
-			if (i + 32 < e)
-				__builtin_prefetch(table + idx[i + 32]); // the table rows are a sparse ascending walk through 16 bytes per entry: keep misses in flight
-			dst[i] = table[idx[i]];
-		}
+		const size_t b = size_t(c) * chunk;
+		memcpy(dst + b, src + b, std::min(chunk, bytes - b));
 	});
 	return true;
 }

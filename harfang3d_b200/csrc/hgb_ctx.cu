@@ -112,6 +112,9 @@ struct EntryTable {
 	DBuf out[kMaxViews];             // surviving indices per view
 	DBuf keys[kMaxViews];            // sort keys of the survivors (hgb_sort_keys)
 	DBuf counts;                     // kMaxViews uint32
+	DBuf records, records_out;       // optional: one opaque 16-byte record per entry (hgb_set_entry_records) and the gathered survivors
+	uint32_t n_records = 0;
+	HBuf records_h;                  // pinned landing zone of hgb_get_visible_records_ptr
 	uint32_t last_count[kMaxViews] = {}; // what the host last read: sizes the next one-round-trip fetch (fetch_visible)
 	DBuf ticket, status;             // compaction scratch (per view slices)
 	uint32_t n_tiles = 0;
@@ -437,7 +440,8 @@ void hgb_destroy(hgb_ctx *c) {
 	for (DBuf *b : bufs)
 		b->release();
 	for (auto &t : c->ent) {
-		DBuf *eb[] = {&t.mtx_pos, &t.meta, &t.view_d, &t.vis[0], &t.vis[1], &t.counts, &t.ticket, &t.status};
+		DBuf *eb[] = {&t.mtx_pos, &t.meta, &t.view_d, &t.vis[0], &t.vis[1], &t.counts, &t.ticket, &t.status, &t.records, &t.records_out};
+		t.records_h.release();
 		for (DBuf *b : eb)
 			b->release();
 		for (auto &o : t.out)

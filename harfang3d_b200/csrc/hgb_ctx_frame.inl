@@ -915,6 +915,67 @@ int hgb_get_visible_ptr(hgb_ctx *c, int kind, uint32_t view, const uint32_t **ou
 	return fetch_visible(c, kind, view, h.as<uint32_t>(), c->ent[kind].n, out_count);
 }
 
+// One opaque 16-byte record per display entry of a kind (the facade stores its ModelDisplayList there: material pointer, mtx_idx,
+// mdl_idx, lst_idx — render_pipeline.h:577-582), so that the visible list can come back as the records themselves.
+int hgb_set_entry_records(hgb_ctx *c, int kind, uint32_t n, const void *rec16) {
+	if (!c)
+		return fail("null context");
+	join_post(c);
+	if (kind != 0 && kind != 1)
+		return fail("hgb_set_entry_records: bad kind");
+	EntryTable &t = c->ent[kind];
+	if (n != t.n)
+		return fail("hgb_set_entry_records: %u records for a table of %u entries (hgb_set_display_entries first)", n, t.n);
+	CK(cudaSetDevice(c->device));
+	if (upload(c, t.records, rec16, size_t(n) * 16))
+		return 1;
+	CK(cudaStreamSynchronize(c->stream));
+	t.n_records = n;
+	return 0;
+}
+
+// The visible list of (kind, view) as the 16-byte records of the surviving entries, in order, in a pinned buffer owned by the context
+// (valid until the next call for this kind). Gathered on the device, one round trip like hgb_get_visible_ptr.
+int hgb_get_visible_records_ptr(hgb_ctx *c, int kind, uint32_t view, const void **out_rec16, uint32_t *out_count) {
+	if (!c)
+		return fail("null context");
+	join_post(c);
+	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews))
+		return fail("hgb_get_visible_records_ptr: bad kind/view");
+	EntryTable &t = c->ent[kind];
+	*out_count = 0;
+	*out_rec16 = nullptr;
+	if (!t.n)
+		return 0;
+	if (t.n_records != t.n || !t.records.p)
+		return fail("hgb_get_visible_records_ptr: no records for this table (hgb_set_entry_records)");
+	CK(cudaSetDevice(c->device));
+	CK(t.records_out.reserve(size_t(t.n) * 16));
+	CK(t.records_h.reserve(size_t(t.n) * 16));
+	CK(c->count_h.reserve(64));
+	uint32_t *cnt = c->count_h.as<uint32_t>();
+	k_gather_records<<<148 * 8, 256, 0, c->stream>>>(t.records.as<uint4>(), t.out[view].as<uint32_t>(), t.counts.as<uint32_t>() + view, t.n, t.records_out.as<uint4>());
+	++c->launches;
+	CK(cudaGetLastError());
+	const uint64_t want = uint64_t(t.last_count[view]) + t.last_count[view] / 4 + 4096;
+	const uint32_t guess = uint32_t(std::min<uint64_t>(want, t.n));
+	CK(cudaMemcpyAsync(cnt, t.counts.as<uint32_t>() + view, 4, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaMemcpyAsync(t.records_h.p, t.records_out.p, size_t(guess) * 16, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	const uint32_t n = *cnt;
+	if (n > t.n)
+		return fail("hgb_get_visible_records_ptr: internal error (count %u > entries %u)", n, t.n);
+	if (n > guess) {
+		CK(cudaMemcpyAsync(static_cast<uint8_t *>(t.records_h.p) + size_t(guess) * 16, t.records_out.as<uint8_t>() + size_t(guess) * 16, size_t(n - guess) * 16,
+			cudaMemcpyDeviceToHost, c->stream));
+		CK(cudaStreamSynchronize(c->stream));
+	}
+	t.last_count[view] = n;
+	*out_count = n;
+	*out_rec16 = t.records_h.p;
+	return 0;
+}
+
 int hgb_get_instance_offsets(hgb_ctx *c, uint32_t *out) {
 	if (!c)
 		return fail("null context");

@@ -806,6 +806,15 @@ __global__ void __launch_bounds__(256) k_fill_rows(uint32_t *__restrict__ tiles,
 		tiles[tile_word(p, row)] = src[p];
 }
 
+// visible entry indices -> the caller's 16-byte records of those entries (hgb_get_visible_records_ptr): the sparse gather runs here,
+// where random 16-byte reads are cheap, and the host receives one contiguous array
+__global__ void __launch_bounds__(256) k_gather_records(const uint4 *__restrict__ table, const uint32_t *__restrict__ visible, const uint32_t *__restrict__ count,
+	uint32_t capacity, uint4 *__restrict__ out) {
+	const uint32_t n = min(*count, capacity);
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+		out[i] = table[visible[i]];
+}
+
 // re-parenting inside a level (hgb_set_parents): only the parent row of the moved positions changes
 __global__ void __launch_bounds__(128) k_set_parent_rows(uint32_t *__restrict__ tiles, const uint32_t *__restrict__ pos, const uint32_t *__restrict__ par, uint32_t n) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -184,6 +184,11 @@ int hgb_get_visible(hgb_ctx *, int kind, uint32_t view, uint32_t *out_idx, uint3
 /* the same list in a pinned buffer OWNED by the context (valid until the next call for this kind, or hgb_destroy): count and list come down
  * in one round trip and land by plain DMA whatever memory the caller would have offered */
 int hgb_get_visible_ptr(hgb_ctx *, int kind, uint32_t view, const uint32_t **out_idx, uint32_t *out_count);
+/* Optional: one opaque 16-byte record per display entry of a kind (what the caller wants back per survivor — the facade stores its
+ * hg::ModelDisplayList, harfang/engine/render_pipeline.h:577-582), and the visible list of (kind, view) returned AS those records, in order:
+ * gathered on the device, one round trip, pinned buffer owned by the context (valid until the next call for this kind). */
+int hgb_set_entry_records(hgb_ctx *, int kind, uint32_t n, const void *rec16);
+int hgb_get_visible_records_ptr(hgb_ctx *, int kind, uint32_t view, const void **out_rec16, uint32_t *out_count);
 /* instance mode: exclusive offsets of every instance's survivors inside the kind-0 list, n_instances+1 values */
 int hgb_get_instance_offsets(hgb_ctx *, uint32_t *out_offsets);
 int hgb_get_bone_matrices(hgb_ctx *, float *out16, int previous);

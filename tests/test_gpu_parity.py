@@ -685,6 +685,13 @@ def test_async_tail_and_one_round_trip_fetch(hgb):
     ca, cb = hostmirror.PlayClocks(fs), hostmirror.PlayClocks(fs)
     fr = hostmirror.scene_frusta(fs)
     wide = fr.copy()
+    # one opaque 16-byte record per entry: the survivors come back as their records, gathered on the device
+    rec_table = rng.integers(0, 2**32, (a.n_entries[0], 4), dtype=np.uint32)
+    with pytest.raises(hgb.HgbError, match="records for a table"):
+        a.set_entry_records(0, rec_table[:-1])
+    with pytest.raises(hgb.HgbError, match="no records"):
+        a.get_visible_records(0, 0)
+    a.set_entry_records(0, rec_table)
     for frame in range(12):
         if frame == 6:  # a far wider frustum: the visible list grows well past the +25 % guess of the fetch
             wide = hostmirror.make_perspective_frustum(0.1, 5000.0, 2.8, 1.0, 1.0, np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, -400], np.float32))
@@ -696,6 +703,8 @@ def test_async_tail_and_one_round_trip_fetch(hgb):
         assert len(ia) == len(ib) and (ia == ib).all(), "frame %d" % frame
         ip = a.get_visible_ptr(0, 0)
         assert len(ip) == len(ia) and (ip == ia).all()
+        got = a.get_visible_records(0, 0).view(np.uint32).reshape(-1, 4)
+        assert got.shape[0] == len(ia) and (got == rec_table[ia]).all(), "records, frame %d" % frame
         assert (bits(a.get_worlds()) == bits(b.get_worlds())).all()
     assert len(ia) > 0
     a.close(); b.close()
