@@ -510,9 +510,14 @@ def main():
             out3 = np.zeros(3)
             fac.hgfacade_time_fused_frames(sc.h, 5, FRAME_DT, flatscene.P(fr0), flatscene.P(out3))  # warm-up (the first frame uploads the scene)
             # no collective inside this leg (a rank that fails it must not strand the others): every call below ends with the list on the host
+            bd = np.zeros(3)
+            fac.hgfacade_visible_breakdown(flatscene.P(bd))  # clear what the warm-up accumulated
             nvis = fac.hgfacade_time_fused_frames(sc.h, KE, FRAME_DT, flatscene.P(fr0), flatscene.P(out3))
+            fac.hgfacade_visible_breakdown(flatscene.P(bd))
             e2e["e2e_facade"] = [float(out3[2]) / KE, 8 * len(fs.plays) + 96, 4 + 4 * int(nvis),
-                                 {"update_ms": float(out3[0]) / KE * 1e3, "visible_lists_ms": float(out3[1]) / KE * 1e3, "visible": int(nvis),
+                                 {"update_ms": float(out3[0]) / KE * 1e3, "visible_lists_ms": float(out3[1]) / KE * 1e3,
+                                  "visible_lists_breakdown_ms": {"device_round_trip": float(bd[0]) / KE * 1e3, "vector_resize": float(bd[1]) / KE * 1e3,
+                                                                 "copy_into_vector": float(bd[2]) / KE * 1e3}, "visible": int(nvis),
                                   "list_bytes_materialised_on_host": 16 * int(nvis)}]
             sc.close()
         except Exception as e:  # the line says why there is no facade number

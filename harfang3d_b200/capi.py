@@ -43,6 +43,9 @@ SIGNATURES = {
     "hgb_set_topology": (_i, [_p, _u32, _p, _p]),
     "hgb_upload_trs": (_i, [_p, _u32, _u32, _p]),
     "hgb_set_parents": (_i, [_p, _u32, _p, _p, _p]),
+    "hgb_append_nodes": (_i, [_p, _u32, _p, _p, _p, _p]),
+    "hgb_remove_nodes": (_i, [_p, _u32, _p, _p]),
+    "hgb_append_display_entries": (_i, [_p, _i, _u32, _p, _p, _p, _p, _p]),
     "hgb_set_preset_world": (_i, [_p, _u32, _p, _p]),
     "hgb_set_matrices": (_i, [_p, _u32, _p, _p, _i]),
     "hgb_set_bounds": (_i, [_p, _u32, _p]),
@@ -59,7 +62,7 @@ SIGNATURES = {
     "hgb_bone_matrices": (_i, [_p, _i]),
     "hgb_sort_keys": (_i, [_p, _i, _u32, _p]),
     "hgb_cull_skinned_list": (_i, [_p, _u32, _p, _p, _p, _u32, _p, _p, _u32, _p, _p, _p, _p]),
-    "hgb_set_entry_records": (_i, [_p, _i, _u32, _p]),
+    "hgb_set_entry_records": (_i, [_p, _i, _u32, _u32, _p]),
     "hgb_get_visible_records_ptr": (_i, [_p, _i, _u32, _p, _p]),
     "hgb_get_visible_ptr": (_i, [_p, _i, _u32, _p, _p]),
     "hgb_peer_init": (_i, [_p, _u32, _u32, _u32, _p, _p, _p, _p]),
@@ -121,12 +124,12 @@ def _ptr(a, dtype, what):
 class Context:
     """One hgb_ctx = one hg::Scene (or one batch of scene instances)."""
 
-    def __init__(self, device=0, use_graph=True, row_store=False, lookahead=0, tma_level=False, top_walk=0, overlap_sampler=False, slice_nodes=0, async_post=None):
+    def __init__(self, device=0, use_graph=True, row_store=False, lookahead=0, tma_level=False, top_walk=0, overlap_sampler=False, slice_nodes=0, async_post=None, append_slack=0):
         """row_store=True: world rows are stored per thread (3 x 16 B at a 48-byte stride) instead of through the shared-memory
         transpose — an A/B switch for profiling (hgb_options.reserved[0])"""
         self._L = lib()
         # async_post: None = the library default (on; HGB_ASYNC_POST=0/1 in the environment overrides), True / False = forced
-        opt = (C.c_int * 8)(1 if use_graph else 0, 1 if row_store else 0, lookahead, 1 if tma_level else 0, (0 if async_post is None else (1 if async_post else -1)), top_walk, 1 if overlap_sampler else 0, slice_nodes)  # lookahead: 0 default, -1 off, n positions
+        opt = (C.c_int * 9)(1 if use_graph else 0, 1 if row_store else 0, lookahead, 1 if tma_level else 0, (0 if async_post is None else (1 if async_post else -1)), top_walk, 1 if overlap_sampler else 0, slice_nodes, append_slack)  # lookahead: 0 default, -1 off, n positions
         self._h = self._L.hgb_create(device, C.cast(opt, C.c_void_p))
         if not self._h:
             raise HgbError(self._L.hgb_last_error().decode())
@@ -167,6 +170,28 @@ class Context:
         """incremental SetTransformParent; returns True when the layout had to be rebuilt (a level changed)"""
         rebuilt = C.c_int(0)
         self._ck(self._L.hgb_set_parents(self._h, len(slots), _ptr(slots, np.uint32, "slots"), _ptr(parent_slots, np.uint32, "parent_slots"), C.byref(rebuilt)))
+        return bool(rebuilt.value)
+
+    def append_nodes(self, slots, parent_slots, trs9):
+        """new leaf transforms in free slots; returns True when the layout had to be rebuilt"""
+        rebuilt = C.c_int(0)
+        trs9 = np.ascontiguousarray(trs9, np.float32).reshape(-1, 9)
+        assert trs9.shape[0] == len(slots)
+        self._ck(self._L.hgb_append_nodes(self._h, len(slots), _ptr(slots, np.uint32, "slots"), _ptr(parent_slots, np.uint32, "parent_slots"),
+                                          _ptr(trs9, np.float32, "trs9"), C.byref(rebuilt)))
+        self.n_slots = max(self.n_slots, int(np.max(slots)) + 1) if len(slots) else self.n_slots
+        return bool(rebuilt.value)
+
+    def remove_nodes(self, slots):
+        rebuilt = C.c_int(0)
+        self._ck(self._L.hgb_remove_nodes(self._h, len(slots), _ptr(slots, np.uint32, "slots"), C.byref(rebuilt)))
+        return bool(rebuilt.value)
+
+    def append_display_entries(self, kind, mtx_slot, bounds_idx, flags=None, view=None):
+        rebuilt = C.c_int(0)
+        self._ck(self._L.hgb_append_display_entries(self._h, kind, len(mtx_slot), _ptr(mtx_slot, np.uint32, "mtx_slot"), _ptr(bounds_idx, np.uint32, "bounds_idx"),
+                                                    _ptr(flags, np.uint8, "flags"), _ptr(view, np.uint16, "view"), C.byref(rebuilt)))
+        self.n_entries[kind] += len(mtx_slot)
         return bool(rebuilt.value)
 
     def upload_trs(self, trs9, first=0):
@@ -370,10 +395,10 @@ class Context:
         self._ck(self._L.hgb_get_visible_ptr(self._h, kind, view, C.byref(ptr), C.byref(n)))
         return np.ctypeslib.as_array(ptr, shape=(n.value,)) if n.value else np.zeros(0, np.uint32)
 
-    def set_entry_records(self, kind, rec16):
-        """one opaque 16-byte record per entry of `kind` ((n, 16) uint8 or (n, 4) uint32)"""
+    def set_entry_records(self, kind, rec16, first=0):
+        """opaque 16-byte records of entries [first, first + n) of `kind` ((n, 16) uint8 or (n, 4) uint32)"""
         r = np.ascontiguousarray(rec16).view(np.uint8).reshape(-1, 16)
-        self._ck(self._L.hgb_set_entry_records(self._h, kind, r.shape[0], r.ctypes.data_as(C.c_void_p)))
+        self._ck(self._L.hgb_set_entry_records(self._h, kind, first, r.shape[0], r.ctypes.data_as(C.c_void_p)))
 
     def get_visible_records(self, kind=0, view=0):
         """the visible list as the entries' 16-byte records (device-side gather) -> (n, 16) uint8 view of the context's pinned buffer"""

@@ -62,6 +62,11 @@ double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock:
 
 } // namespace
 
+#ifdef HG_FACADE
+namespace hg {
+extern double g_visible_breakdown[3];
+}
+#endif
 extern "C" {
 
 void *hgref_create() {
@@ -765,6 +770,11 @@ int hgfacade_time_fused_frames(void *h, int frames, int64_t dt, const float *fru
 	}
 	out3[2] = now_s() - w0;
 	return visible;
+}
+// seconds spent in GetVisibleModelDisplayLists since the last call of this function: device round trip, vector sizing, copy
+void hgfacade_visible_breakdown(double *out3) {
+	for (int i = 0; i < 3; ++i)
+		out3[i] = hg::g_visible_breakdown[i], hg::g_visible_breakdown[i] = 0;
 }
 // one process per GPU: scenes created after this call live on `device` (Scene::SetDefaultDevice)
 void hgfacade_set_default_device(int device) { Scene::SetDefaultDevice(device); }

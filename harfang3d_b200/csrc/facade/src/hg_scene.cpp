@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cstring>
 #include <functional>
@@ -1248,7 +1249,7 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 		for (int k = 0; k < 2; ++k) {
 			check(hgb_set_display_entries(ctx, k, uint32_t(mtx[k].size()), mtx[k].data(), bidx[k].data(), impl->ent_flags[k].data(), nullptr));
 			if (!impl->ent[k].empty()) // the display lists themselves: survivors come back as these records (GetVisibleModelDisplayLists)
-				check(hgb_set_entry_records(ctx, k, uint32_t(impl->ent[k].size()), impl->ent[k].data()));
+				check(hgb_set_entry_records(ctx, k, 0, uint32_t(impl->ent[k].size()), impl->ent[k].data()));
 		}
 		impl->entries_dirty = false;
 	}
@@ -1282,8 +1283,14 @@ void Scene::SetCullingFrustums(const std::vector<Frustum> &frustums, const Pipel
 	impl->views_dirty = true;
 }
 
+// where the time of GetVisibleModelDisplayLists goes (seconds, accumulated): [0] the device round trip (frame tail + gather + copy to
+// pinned memory), [1] sizing the caller's vector, [2] the copy into it. Read and cleared by the flat binding's timing leg.
+double g_visible_breakdown[3] = {0, 0, 0};
+static inline double now_sec() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
 bool Scene::GetVisibleModelDisplayLists(uint32_t view, bool transparent, std::vector<ModelDisplayList> &out, const PipelineResources &) {
 	const int k = transparent ? 1 : 0;
+	const double t0 = now_sec();
 	if (!ctx || impl->frusta.empty() || view >= impl->frusta.size() || impl->entries_dirty) {
 		out.clear();
 		warn("GetVisibleModelDisplayLists: no fused culling result for this view (SetCullingFrustums + Update first)");
@@ -1300,7 +1307,9 @@ bool Scene::GetVisibleModelDisplayLists(uint32_t view, bool transparent, std::ve
 	// ModelDisplayList is trivially copyable: size the vector once (a caller that reuses its vector pays no re-initialisation when
 	// the count barely moves) and let the pool copy the contiguous records in
 	static_assert(std::is_trivially_copyable<ModelDisplayList>::value, "copied with memcpy");
+	const double t1 = now_sec();
 	out.resize(n);
+	const double t2 = now_sec();
 	const uint8_t *src = static_cast<const uint8_t *>(rec);
 	uint8_t *dst = reinterpret_cast<uint8_t *>(out.data());
 	const size_t bytes = size_t(n) * sizeof(ModelDisplayList), chunk = size_t(1) << 20;
@@ -1309,6 +1318,8 @@ bool Scene::GetVisibleModelDisplayLists(uint32_t view, bool transparent, std::ve
 		const size_t b = size_t(c) * chunk;
 		memcpy(dst + b, src + b, std::min(chunk, bytes - b));
 	});
+	const double t3 = now_sec();
+	g_visible_breakdown[0] += t1 - t0, g_visible_breakdown[1] += t2 - t1, g_visible_breakdown[2] += t3 - t2;
 	return true;
 }
 

@@ -118,6 +118,8 @@ struct EntryTable {
 	uint32_t last_count[kMaxViews] = {}; // what the host last read: sizes the next one-round-trip fetch (fetch_visible)
 	DBuf ticket, status;             // compaction scratch (per view slices)
 	uint32_t n_tiles = 0;
+	uint32_t n_dev = 0;              // entries the device tables and the compaction cover: n at the last table build + the append slack
+	                                 // (entries [n, n_dev) are disabled and their visibility bytes stay zero)
 };
 
 // peer-memory result gather (hgb_peer_init / hgb_peer_connect, hgb_kernels_peer.cuh)
@@ -165,6 +167,14 @@ struct hgb_ctx {
 	cudaStream_t stream2 = nullptr;
 	std::vector<cudaEvent_t> ev_chunk; // [0] fork, [1] join, [2+g] chunk of level group g
 	std::vector<uint32_t> trk_pos_h;   // target position of every round-0 track, ascending (chunk boundaries of the overlapped sampler)
+	// in-place edits (hgb_options.append_slack > 0): free positions behind the last level, free entries behind each table
+	uint32_t append_slack = 0;
+	uint32_t cap_slots = 0;            // device arrays hold this many slots / positions (n_slots at the last depth sort + append_slack)
+	std::vector<uint8_t> live_h;       // per position: computed node (sorted region or append region)
+	std::vector<uint8_t> late_depth_h; // per position of the append region: ancestors inside the region (chain length of k_update_top)
+	std::vector<uint32_t> child_cnt_h; // per position: live children
+	std::vector<uint8_t> has_entry_h;  // per position: rows 10 / 11 hold an entry
+	DBuf edit_d;                       // scratch of the in-place edit kernels
 	uint32_t slice_nodes = 0;          // >0: with the overlapped sampler, big levels are cut into slices of this many positions (multiple of 256)
 	uint32_t persistent_ctas = 148 * 6; // resident CTAs of the device for the persistent level kernel
 	uint32_t lookahead = 0; // positions (see SceneDev::lookahead)
@@ -369,6 +379,8 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 	c->overlap_sampler = opt ? opt->overlap_sampler != 0 : false;
 	if (opt && opt->slice_nodes > 0)
 		c->slice_nodes = (uint32_t(opt->slice_nodes) + 255u) & ~255u;
+	if (opt && opt->append_slack > 0)
+		c->append_slack = uint32_t(opt->append_slack);
 	if (opt && opt->async_post != 0)
 		c->async_post = opt->async_post > 0; // 0 = default (on), 1 = on, -1 = off
 	if (const char *e_ap = getenv("HGB_ASYNC_POST"))

@@ -43,7 +43,7 @@ static int enqueue_compaction_reset(hgb_ctx *c) {
 	const int n_views = c->instance_mode ? 1 : c->views.n_views;
 	for (int k = 0; k < 2; ++k) {
 		EntryTable &t = c->ent[k];
-		if (!t.n)
+		if (!t.n_dev)
 			continue;
 		CK(cudaMemsetAsync(t.ticket.p, 0, kMaxViews * 4, c->stream));
 		CK(cudaMemsetAsync(t.status.p, 0, size_t(t.n_tiles) * (n_views > 1 ? kMaxViews : 1) * 4, c->stream)); // the one-pass kernel walks 2 / 4 / 8 chains
@@ -60,13 +60,13 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 		return 1;
 	for (int k = 0; k < 2; ++k) {
 		EntryTable &t = c->ent[k];
-		if (!t.n)
+		if (!t.n_dev)
 			continue;
 		const bool peer_here = with_peer && k == 0;
 		if (n_views > 1 && !peer_here && c->multi_compact) { // every view of the table in one pass over the visibility bytes
 			CompactMultiDev d{};
 			d.vis = t.vis[c->cur].as<uint8_t>();
-			d.n = t.n;
+			d.n = t.n_dev;
 			for (int v = 0; v < kMaxViews; ++v)
 				d.out[v] = v < n_views ? t.out[v].as<uint32_t>() : nullptr;
 			d.count = t.counts.as<uint32_t>();
@@ -87,15 +87,15 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 		for (int v = 0; v < n_views; ++v) {
 			CompactDev d{};
 			d.vis = t.vis[c->cur].as<uint8_t>();
-			d.n = t.n;
+			d.n = t.n_dev;
 			d.bit = uint32_t(v);
 			d.out = t.out[v].as<uint32_t>();
 			d.count = t.counts.as<uint32_t>() + v;
 			d.ticket = t.ticket.as<uint32_t>() + v;
 			d.status = t.status.as<uint32_t>() + size_t(v) * t.n_tiles;
 			if (with_peer && k == 0 && v == 0) { // the visible list leaves for the gather destination from the kernel that produces it
-				if (t.n > c->peer.cap[c->peer.rank])
-					return fail("peer gather: %u display entries but a region of %u was declared", t.n, c->peer.cap[c->peer.rank]);
+				if (t.n_dev > c->peer.cap[c->peer.rank])
+					return fail("peer gather: %u display entries but a region of %u was declared", t.n_dev, c->peer.cap[c->peer.rank]);
 				d.out2 = c->peer.inbox + c->peer.list_off[c->peer.rank];
 				d.add2 = c->peer.entry_base[c->peer.rank];
 				d.out2_half = uint32_t(c->peer.half_words);
@@ -147,15 +147,16 @@ static void launch_level(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t 
 	}
 }
 
-// the first `top_levels` levels in one launch (k_update_top): positions [0, e)
-static void launch_top(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t e, bool pdl) {
-	const dim3 g = grid_for(e);
+// the first `top_levels` levels in one launch (k_update_top): positions [0, e); or the append region [b, e) behind the last level,
+// whose chains stop at the first ancestor below b
+static void launch_top(hgb_ctx *c, const SceneDev &s, bool do_fused, uint32_t b, uint32_t e, bool pdl) {
+	const dim3 g = grid_for(e - b);
 	if (!do_fused)
-		launch_after(c, pdl, k_update_top<false, false>, g, dim3(256), s, c->views, e);
+		launch_after(c, pdl, k_update_top<false, false>, g, dim3(256), s, c->views, b, e, b);
 	else if (c->instance_mode)
-		launch_after(c, pdl, k_update_top<true, true>, g, dim3(256), s, c->views, e);
+		launch_after(c, pdl, k_update_top<true, true>, g, dim3(256), s, c->views, b, e, b);
 	else
-		launch_after(c, pdl, k_update_top<true, false>, g, dim3(256), s, c->views, e);
+		launch_after(c, pdl, k_update_top<true, false>, g, dim3(256), s, c->views, b, e, b);
 }
 
 // How many leading levels k_update_top covers: as many as keep the recomputed work (every node of level d evaluates d + 1 local
@@ -183,7 +184,7 @@ static size_t plan_top_levels(const hgb_ctx *c) {
 constexpr int kPhasePre = 1, kPhaseLevels = 2, kPhasePost = 4, kPhaseAll = 7;
 static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint64_t *n_k, int phases = kPhaseAll) {
 	const SceneDev s = scene_dev(c, with_preset);
-	const bool do_fused = fused && (c->ent[0].n || c->ent[1].n);
+	const bool do_fused = fused && (c->ent[0].n_dev || c->ent[1].n_dev);
 	const size_t n_levels = c->level_off.size() - 1;
 	// a rank without display entries still takes part in the gather (it publishes an empty list)
 	const bool do_post = do_fused || (fused && c->peer.on);
@@ -211,12 +212,13 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	struct Group {
 		size_t d0, d1;   // levels [d0, d1): more than one = the top of the hierarchy in one launch (k_update_top)
 		uint32_t b, e;   // positions (a slice when d1 == d0 + 1)
+		bool top;        // k_update_top: the leading levels, or the append region behind the last level
 	};
 	const bool want_overlap = has_anim && c->overlap_sampler && !c->prof.on && c->round_off.size() == 2 && !c->trk_pos_h.empty() && phases == kPhaseAll;
 	std::vector<Group> groups;
 	const size_t n_top = want_overlap ? 0 : plan_top_levels(c);
 	if (n_top >= 1 && c->level_off[n_top] > 0)
-		groups.push_back({0, n_top, 0u, c->level_off[n_top]});
+		groups.push_back({0, n_top, 0u, c->level_off[n_top], true});
 	for (size_t d = n_top; d < n_levels; ++d) {
 		if (c->level_off[d + 1] == c->level_off[d])
 			continue;
@@ -224,10 +226,12 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		const uint32_t slice = want_overlap && c->slice_nodes ? c->slice_nodes : 0xffffff00u;
 		for (uint32_t p0 = lb; p0 < le;) {
 			const uint32_t p1 = (le - p0 <= slice + slice / 2) ? le : p0 + slice; // slice is a multiple of 256: warps keep their tile alignment
-			groups.push_back({d, d + 1, p0, p1});
+			groups.push_back({d, d + 1, p0, p1, false});
 			p0 = p1;
 		}
 	}
+	if (c->append_slack && c->cap_slots > c->n_pos) // nodes appended since the last depth sort (and the free positions among them)
+		groups.push_back({n_levels, n_levels + 1, c->n_pos, c->cap_slots, true});
 
 	while (want_overlap && c->ev_chunk.size() < groups.size() + 2) { // 96 exist from hgb_create; more only for very deep or very large scenes
 		cudaEvent_t e = nullptr;
@@ -300,9 +304,9 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 		if (has_chunk[g])
 			CK(cudaStreamWaitEvent(c->stream, c->ev_chunk[g + 2], 0));
 		prof_begin(c, HGB_K_UPDATE_LEVEL);
-		if (n_top >= 1 && g == 0) {
+		if (groups[g].top) {
 			// waits first thing and releases its dependents behind the wait (it reads sampled values throughout)
-			launch_top(c, s, do_fused, groups[g].e, chain && prev_signals);
+			launch_top(c, s, do_fused, groups[g].b, groups[g].e, chain && prev_signals);
 			prev_signals = true;
 			prev_is_sampler = false;
 		} else {
@@ -412,7 +416,7 @@ int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cul
 	if (!c->n_slots)
 		return 0;
 	CK(cudaSetDevice(c->device));
-	if (fused_cull && !c->instance_mode && c->views.n_views == 0 && (c->ent[0].n || c->ent[1].n))
+	if (fused_cull && !c->instance_mode && c->views.n_views == 0 && (c->ent[0].n_dev || c->ent[1].n_dev))
 		return fail("hgb_update(fused_cull): no views set (hgb_set_views / hgb_set_instance_views)");
 	if (prepare_tables(c))
 		return 1;
@@ -450,7 +454,7 @@ int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cul
 	if (!c->en_target_slot_h.empty() && c->n_play)
 		c->en_state_dirty = true;
 	const bool fused = fused_cull != 0;
-	if (c->async_post && c->use_graph && fused && !with_preset && !c->prof.on && (c->ent[0].n || c->ent[1].n || c->peer.on))
+	if (c->async_post && c->use_graph && fused && !with_preset && !c->prof.on && (c->ent[0].n_dev || c->ent[1].n_dev || c->peer.on))
 		return launch_frame_async(c);
 	join_post(c);
 	if (!c->use_graph || with_preset || c->prof.on) {
@@ -916,21 +920,31 @@ int hgb_get_visible_ptr(hgb_ctx *c, int kind, uint32_t view, const uint32_t **ou
 }
 
 // One opaque 16-byte record per display entry of a kind (the facade stores its ModelDisplayList there: material pointer, mtx_idx,
-// mdl_idx, lst_idx — render_pipeline.h:577-582), so that the visible list can come back as the records themselves.
-int hgb_set_entry_records(hgb_ctx *c, int kind, uint32_t n, const void *rec16) {
+// mdl_idx, lst_idx — render_pipeline.h:577-582), so that the visible list can come back as the records themselves. Records
+// [first, first + count): the whole table after hgb_set_display_entries, the new tail after hgb_append_display_entries.
+int hgb_set_entry_records(hgb_ctx *c, int kind, uint32_t first, uint32_t count, const void *rec16) {
 	if (!c)
 		return fail("null context");
 	join_post(c);
 	if (kind != 0 && kind != 1)
 		return fail("hgb_set_entry_records: bad kind");
 	EntryTable &t = c->ent[kind];
-	if (n != t.n)
-		return fail("hgb_set_entry_records: %u records for a table of %u entries (hgb_set_display_entries first)", n, t.n);
+	if (uint64_t(first) + count > t.n)
+		return fail("hgb_set_entry_records: records [%u, %u) for a table of %u entries (hgb_set_display_entries first)", first, first + count, t.n);
+	if (first > t.n_records)
+		return fail("hgb_set_entry_records: records [%u, %u) leave a gap behind the %u already set", first, first + count, t.n_records);
+	if (!count)
+		return 0;
 	CK(cudaSetDevice(c->device));
-	if (upload(c, t.records, rec16, size_t(n) * 16))
-		return 1;
+	const size_t cap = size_t(std::max(t.n_dev, t.n)) * 16;
+	if (t.records.cap < cap) { // grows only with the table (hgb_set_display_entries resets n_records)
+		if (first)
+			return fail("hgb_set_entry_records: the table grew past its slack; set all records again");
+		CK(t.records.reserve(cap));
+	}
+	CK(cudaMemcpyAsync(t.records.as<uint8_t>() + size_t(first) * 16, rec16, size_t(count) * 16, cudaMemcpyHostToDevice, c->stream));
 	CK(cudaStreamSynchronize(c->stream));
-	t.n_records = n;
+	t.n_records = std::max(t.n_records, first + count);
 	return 0;
 }
 

@@ -183,7 +183,7 @@ static int peer_enqueue_end(hgb_ctx *c, uint64_t *n_k) {
 			p.aux_n[p.rank], mail);
 		++*n_k;
 	}
-	k_peer_publish<<<1, 1, 0, c->stream>>>(p.inbox, half_words, p.rank * kPeerHdrWords, c->ent[0].n ? c->ent[0].counts.as<uint32_t>() : nullptr, mail);
+	k_peer_publish<<<1, 1, 0, c->stream>>>(p.inbox, half_words, p.rank * kPeerHdrWords, c->ent[0].n_dev ? c->ent[0].counts.as<uint32_t>() : nullptr, mail);
 	++*n_k;
 	if (p.rank == p.dst) {
 		k_peer_wait<<<1, 32, 0, c->stream>>>(p.inbox, half_words, p.world, mail);

@@ -73,6 +73,23 @@ static int fold_enable_state(hgb_ctx *c) {
 	return 0;
 }
 
+// the hierarchy as it stands (parents by slot, used flags) — the input of a full depth sort after an edit the fast paths cannot take
+static void snapshot_parents(const hgb_ctx *c, std::vector<uint32_t> &parent, std::vector<uint8_t> &used) {
+	parent.assign(c->n_slots, HGB_ROOT);
+	used.assign(c->n_slots, 0);
+	const uint32_t n_all = c->append_slack ? c->cap_slots : c->n_pos;
+	for (uint32_t p = 0; p < n_all; ++p) {
+		if (c->append_slack && !c->live_h[p])
+			continue;
+		const uint32_t s_ = c->slot_of_pos[p];
+		if (s_ >= c->n_slots)
+			continue;
+		used[s_] = 1;
+		parent[s_] = c->parent_pos_h[p] == kRoot ? HGB_ROOT : c->slot_of_pos[c->parent_pos_h[p]];
+	}
+}
+static inline bool pos_is_live(const hgb_ctx *c, uint32_t pos) { return c->append_slack ? (pos < c->cap_slots && c->live_h[pos]) : pos < c->n_pos; }
+
 extern "C" {
 
 int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const uint8_t *used) {
@@ -138,14 +155,21 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 	for (uint32_t s = 0; s < n; ++s)
 		if (!is_used(s))
 			slot_of_pos.push_back(s); // holes live after the last level and are never computed
+	// in-place edits (hgb_options.append_slack): the holes and `slack` further positions behind them form the append region — free
+	// positions (parent row kDead) that hgb_append_nodes hands out; slots >= n map to positions of the same index
+	const uint32_t slack = c->append_slack, cap = n + slack;
+	if (cap >= 0x00ffffffu)
+		return fail("hgb_set_topology: %u slots + %u positions of append slack exceed 2^24-1", n, slack);
+	for (uint32_t s = n; s < cap; ++s)
+		slot_of_pos.push_back(s);
 
-	std::vector<uint32_t> pos_of_slot(n);
+	std::vector<uint32_t> pos_of_slot(cap);
 	bool identity = true;
-	for (uint32_t p = 0; p < n; ++p) {
+	for (uint32_t p = 0; p < cap; ++p) {
 		pos_of_slot[slot_of_pos[p]] = p;
 		identity = identity && slot_of_pos[p] == p;
 	}
-	std::vector<uint32_t> parent_pos(n, kRoot);
+	std::vector<uint32_t> parent_pos(cap, slack ? kDead : kRoot);
 	for (uint32_t p = 0; p < n_pos; ++p) {
 		const uint32_t par = parent_of(slot_of_pos[p]);
 		parent_pos[p] = par == HGB_ROOT ? kRoot : pos_of_slot[par];
@@ -165,7 +189,7 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 	// edits (scene.cpp:280-304), so the frame after an edit still sees the right previous-frame matrices (motion vectors, bone twins).
 	// Nothing to do when old and new order are both the slot order and the buffers do not grow.
 	DBuf carry_w[2];
-	const bool grow = c->world[0].cap < std::max<size_t>(n, 1) * 48 || c->world[1].cap < std::max<size_t>(n, 1) * 48;
+	const bool grow = c->world[0].cap < std::max<size_t>(cap, 1) * 48 || c->world[1].cap < std::max<size_t>(cap, 1) * 48;
 	const bool carry_worlds = carry && c->world[0].p && c->world[1].p && !(c->identity && identity && !grow);
 	if (carry_worlds) {
 		for (int i = 0; i < 2; ++i) {
@@ -177,14 +201,14 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 		CK(cudaStreamSynchronize(c->stream));
 	}
 
-	const uint32_t n_tiles = (n + 31) / 32;
+	const uint32_t n_tiles = (cap + 31) / 32;
 	DBuf new_tiles, rows;
 	CK(new_tiles.reserve(std::max<size_t>(n_tiles, 1) * kTileWords * 4));
 	CK(cudaMemsetAsync(new_tiles.p, 0, new_tiles.cap, c->stream));
-	if (upload(c, c->pos_of_slot_d, pos_of_slot.data(), size_t(n) * 4) || upload(c, rows, parent_pos.data(), size_t(n) * 4))
+	if (upload(c, c->pos_of_slot_d, pos_of_slot.data(), size_t(cap) * 4) || upload(c, rows, parent_pos.data(), size_t(cap) * 4))
 		return 1;
-	if (n) {
-		k_fill_rows<<<grid_for(n), 256, 0, c->stream>>>(new_tiles.as<uint32_t>(), kRowParent, rows.as<uint32_t>(), n);
+	if (cap) {
+		k_fill_rows<<<grid_for(cap), 256, 0, c->stream>>>(new_tiles.as<uint32_t>(), kRowParent, rows.as<uint32_t>(), cap);
 		++c->launches;
 	}
 	if (carry) {
@@ -199,7 +223,7 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 	c->n_tiles = n_tiles;
 	c->n_bound = 0;
 	for (int i = 0; i < 2; ++i) {
-		const size_t bytes = std::max<size_t>(n, 1) * 48;
+		const size_t bytes = std::max<size_t>(cap, 1) * 48;
 		if (c->world[i].cap < bytes) {
 			CK(c->world[i].reserve(bytes));
 			CK(cudaMemsetAsync(c->world[i].p, 0, c->world[i].cap, c->stream)); // new slots: value-initialised rows, like std::vector::resize
@@ -215,10 +239,21 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 		carry_w[0].release();
 		carry_w[1].release();
 	}
-	CK(c->preset.reserve(std::max<size_t>(n, 4)));
+	CK(c->preset.reserve(std::max<size_t>(cap, 4)));
 	CK(cudaMemsetAsync(c->preset.p, 0, c->preset.cap, c->stream));
 	c->preset_dirty = false;
 
+	c->cap_slots = cap;
+	if (slack) { // host mirror of what the in-place edits need to know
+		c->live_h.assign(cap, 0);
+		std::fill(c->live_h.begin(), c->live_h.begin() + n_pos, uint8_t(1));
+		c->late_depth_h.assign(cap, 0);
+		c->child_cnt_h.assign(cap, 0);
+		for (uint32_t s = 0; s < n; ++s)
+			if (is_used(s))
+				c->child_cnt_h[pos_of_slot[s]] = child_cnt[s + 1] - child_cnt[s];
+		c->has_entry_h.assign(cap, 0);
+	}
 	c->n_slots = n;
 	c->n_pos = n_pos;
 	c->pos_of_slot.swap(pos_of_slot);
@@ -246,35 +281,68 @@ int hgb_set_parents(hgb_ctx *c, uint32_t n, const uint32_t *slot, const uint32_t
 	join_post(c);
 	CK(cudaSetDevice(c->device));
 	auto level_of = [&](uint32_t pos) { return uint32_t(std::upper_bound(c->level_off.begin(), c->level_off.end(), pos) - c->level_off.begin()) - 1u; };
+	struct Undo {
+		uint32_t pos, par;
+		uint8_t depth;
+	};
+	std::vector<Undo> undo; // host mirror of the append region: edits are applied one by one and rolled back when the batch needs a rebuild
 	std::vector<uint32_t> pos(n), par(n);
 	bool fast = true;
 	for (uint32_t i = 0; i < n; ++i) {
-		if (slot[i] >= c->n_slots || c->pos_of_slot[slot[i]] >= c->n_pos)
+		if (slot[i] >= c->n_slots || !pos_is_live(c, c->pos_of_slot[slot[i]]))
 			return fail("hgb_set_parents: slot %u is not a live transform", slot[i]);
 		pos[i] = c->pos_of_slot[slot[i]];
 		const uint32_t ps = parent_slot[i];
-		const bool root = ps == HGB_ROOT || ps >= c->n_slots || c->pos_of_slot[ps] >= c->n_pos || ps == slot[i]; // stale / unused parent = root (scene.cpp:268-272)
+		const bool root = ps == HGB_ROOT || ps >= c->n_slots || !pos_is_live(c, c->pos_of_slot[ps]) || ps == slot[i]; // stale / unused parent = root (scene.cpp:268-272)
 		par[i] = root ? kRoot : c->pos_of_slot[ps];
-		const uint32_t lv = level_of(pos[i]);
-		if (root ? lv != 0 : level_of(par[i]) + 1 != lv)
-			fast = false;
+		if (!fast)
+			continue;
+		uint8_t depth = 0;
+		if (pos[i] >= c->n_pos) { // a node of the append region: anywhere, as long as it has no children and its chain stays short
+			if (c->child_cnt_h[pos[i]])
+				fast = false;
+			else if (!root && par[i] >= c->n_pos) {
+				if (c->late_depth_h[par[i]] + 1 >= kMaxWalk)
+					fast = false;
+				depth = uint8_t(c->late_depth_h[par[i]] + 1);
+			}
+		} else { // sorted region: the node must stay in its level
+			const uint32_t lv = level_of(pos[i]);
+			if (root ? lv != 0 : (par[i] >= c->n_pos || level_of(par[i]) + 1 != lv))
+				fast = false;
+		}
+		if (fast && c->append_slack) {
+			undo.push_back({pos[i], c->parent_pos_h[pos[i]], c->late_depth_h[pos[i]]});
+			if (c->parent_pos_h[pos[i]] != kRoot)
+				--c->child_cnt_h[c->parent_pos_h[pos[i]]];
+			if (!root)
+				++c->child_cnt_h[par[i]];
+			c->parent_pos_h[pos[i]] = par[i];
+			c->late_depth_h[pos[i]] = depth;
+		}
 	}
 	if (!fast) { // levels change: full rebuild from the current parents with the edits applied
-		std::vector<uint32_t> parent(c->n_slots, HGB_ROOT);
-		std::vector<uint8_t> used(c->n_slots, 0);
-		for (uint32_t p = 0; p < c->n_pos; ++p) {
-			const uint32_t s_ = c->slot_of_pos[p];
-			used[s_] = 1;
-			parent[s_] = c->parent_pos_h[p] == kRoot ? HGB_ROOT : c->slot_of_pos[c->parent_pos_h[p]];
+		for (size_t k = undo.size(); k-- > 0;) {
+			const uint32_t now = c->parent_pos_h[undo[k].pos];
+			if (now != kRoot)
+				--c->child_cnt_h[now];
+			if (undo[k].par != kRoot)
+				++c->child_cnt_h[undo[k].par];
+			c->parent_pos_h[undo[k].pos] = undo[k].par;
+			c->late_depth_h[undo[k].pos] = undo[k].depth;
 		}
+		std::vector<uint32_t> parent;
+		std::vector<uint8_t> used;
+		snapshot_parents(c, parent, used);
 		for (uint32_t i = 0; i < n; ++i)
 			parent[slot[i]] = parent_slot[i];
 		if (out_rebuilt)
 			*out_rebuilt = 1;
 		return hgb_set_topology(c, c->n_slots, parent.data(), used.data());
 	}
-	for (uint32_t i = 0; i < n; ++i)
-		c->parent_pos_h[pos[i]] = par[i];
+	if (!c->append_slack)
+		for (uint32_t i = 0; i < n; ++i)
+			c->parent_pos_h[pos[i]] = par[i];
 	CK(c->staging.reserve(size_t(n) * 8));
 	uint32_t *st = c->staging.as<uint32_t>();
 	CK(cudaStreamSynchronize(c->stream)); // the pinned staging block may still feed an earlier copy
@@ -285,6 +353,180 @@ int hgb_set_parents(hgb_ctx *c, uint32_t n, const uint32_t *slot, const uint32_t
 	k_set_parent_rows<<<grid_for(n, 128), 128, 0, c->stream>>>(c->tiles.as<uint32_t>(), c->staging_d.as<uint32_t>(), c->staging_d.as<uint32_t>() + n, n);
 	++c->launches;
 	CK(cudaGetLastError());
+	return 0;
+}
+
+// small host table -> device scratch on the context's stream (the copy is staged by the driver before the call returns: the caller's
+// vector may go out of scope)
+static int edit_upload(hgb_ctx *c, DBuf &dst, const void *src, size_t bytes) {
+	CK(dst.reserve(bytes));
+	CK(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, c->stream));
+	return 0;
+}
+
+// New LEAF transforms (Scene::CreateNode + CreateTransform + SetParent of a fresh node, scene.cpp:92-137, component.cpp:184-193) without
+// a depth sort: each takes a free position of the append region, which k_update_top computes behind the last level by walking up to
+// the first ancestor in the sorted part. Falls back to the full rebuild when the context has no append slack, the region is full, a
+// slot is out of range or a chain inside the region would exceed kMaxWalk.
+int hgb_append_nodes(hgb_ctx *c, uint32_t n, const uint32_t *slot, const uint32_t *parent_slot, const float *trs9, int *out_rebuilt) {
+	if (!c)
+		return fail("null context");
+	if (out_rebuilt)
+		*out_rebuilt = 0;
+	if (!n)
+		return 0;
+	join_post(c);
+	CK(cudaSetDevice(c->device));
+	std::vector<NodeWrite> w;
+	w.reserve(n);
+	bool fast = c->append_slack && c->tiles.p;
+	uint32_t n_slots = c->n_slots;
+	for (uint32_t i = 0; i < n && fast; ++i) {
+		if (slot[i] >= c->cap_slots) {
+			fast = false;
+			break;
+		}
+		const uint32_t p = c->pos_of_slot[slot[i]];
+		if (c->live_h[p]) {
+			for (const NodeWrite &x : w) // roll the batch back before reporting
+				c->live_h[x.pos] = 0;
+			return fail("hgb_append_nodes: slot %u already holds a live transform", slot[i]);
+		}
+		const uint32_t ps = parent_slot ? parent_slot[i] : HGB_ROOT;
+		const bool root = ps == HGB_ROOT || ps >= c->cap_slots || !c->live_h[c->pos_of_slot[ps]] || ps == slot[i];
+		const uint32_t par = root ? kRoot : c->pos_of_slot[ps];
+		uint8_t depth = 0;
+		if (!root && par >= c->n_pos) {
+			if (c->late_depth_h[par] + 1 >= kMaxWalk) {
+				fast = false;
+				break;
+			}
+			depth = uint8_t(c->late_depth_h[par] + 1);
+		}
+		NodeWrite x{};
+		x.pos = p, x.parent = par, x.zero_world = 1;
+		memcpy(x.trs, trs9 + size_t(i) * 9, 36);
+		w.push_back(x);
+		c->live_h[p] = 1; // a later node of the batch may hang below this one
+		c->late_depth_h[p] = depth;
+		n_slots = std::max(n_slots, slot[i] + 1);
+	}
+	if (!fast) {
+		for (const NodeWrite &x : w)
+			c->live_h[x.pos] = 0;
+		std::vector<uint32_t> parent;
+		std::vector<uint8_t> used;
+		snapshot_parents(c, parent, used);
+		uint32_t n_new = c->n_slots;
+		for (uint32_t i = 0; i < n; ++i)
+			n_new = std::max(n_new, slot[i] + 1);
+		parent.resize(n_new, HGB_ROOT);
+		used.resize(n_new, 0);
+		for (uint32_t i = 0; i < n; ++i) {
+			if (used[slot[i]])
+				return fail("hgb_append_nodes: slot %u already holds a live transform", slot[i]);
+			used[slot[i]] = 1;
+			parent[slot[i]] = parent_slot ? parent_slot[i] : HGB_ROOT;
+		}
+		if (out_rebuilt)
+			*out_rebuilt = 1;
+		if (hgb_set_topology(c, n_new, parent.data(), used.data()))
+			return 1;
+		for (uint32_t i = 0; i < n; ++i)
+			if (hgb_upload_trs(c, slot[i], 1, trs9 + size_t(i) * 9))
+				return 1;
+		return 0;
+	}
+	for (const NodeWrite &x : w) {
+		c->parent_pos_h[x.pos] = x.parent;
+		c->child_cnt_h[x.pos] = 0;
+		c->has_entry_h[x.pos] = 0;
+		if (x.parent != kRoot)
+			++c->child_cnt_h[x.parent];
+	}
+	c->n_slots = n_slots;
+	if (edit_upload(c, c->edit_d, w.data(), w.size() * sizeof(NodeWrite)))
+		return 1;
+	k_write_nodes<<<grid_for(uint32_t(w.size()), 128), 128, 0, c->stream>>>(c->tiles.as<uint32_t>(), c->world[0].as<float>(), c->world[1].as<float>(),
+		c->preset.as<uint8_t>(), c->edit_d.as<NodeWrite>(), uint32_t(w.size()));
+	++c->launches;
+	CK(cudaGetLastError());
+	return 0;
+}
+
+// Remove transforms (Scene::DestroyNode / DestroyTransform + GarbageCollect, scene.cpp:139-237). A childless node goes in place: its
+// display entries are disabled on the device, a position of the append region becomes free again, a position of the sorted part idles as a
+// childless root until the next depth sort. A node that still has children re-roots them (scene.cpp:268-272: a stale parent ref is no
+// parent), which changes their levels: full rebuild.
+int hgb_remove_nodes(hgb_ctx *c, uint32_t n, const uint32_t *slot, int *out_rebuilt) {
+	if (!c)
+		return fail("null context");
+	if (out_rebuilt)
+		*out_rebuilt = 0;
+	if (!n)
+		return 0;
+	join_post(c);
+	CK(cudaSetDevice(c->device));
+	for (uint32_t i = 0; i < n; ++i)
+		if (slot[i] >= c->n_slots || !pos_is_live(c, c->pos_of_slot[slot[i]]))
+			return fail("hgb_remove_nodes: slot %u is not a live transform", slot[i]);
+	bool fast = c->append_slack != 0;
+	std::vector<uint32_t> pos;
+	if (fast) { // children removed earlier in the batch no longer count
+		std::vector<uint32_t> cnt_undo;
+		for (uint32_t i = 0; i < n && fast; ++i) {
+			const uint32_t p = c->pos_of_slot[slot[i]];
+			if (c->child_cnt_h[p] || !c->live_h[p]) {
+				fast = false;
+				break;
+			}
+			pos.push_back(p);
+			c->live_h[p] = 0;
+			if (c->parent_pos_h[p] != kRoot)
+				--c->child_cnt_h[c->parent_pos_h[p]];
+		}
+		if (!fast)
+			for (uint32_t p : pos) {
+				c->live_h[p] = 1;
+				if (c->parent_pos_h[p] != kRoot)
+					++c->child_cnt_h[c->parent_pos_h[p]];
+			}
+	}
+	if (!fast) {
+		std::vector<uint32_t> parent;
+		std::vector<uint8_t> used;
+		snapshot_parents(c, parent, used);
+		for (uint32_t i = 0; i < n; ++i)
+			used[slot[i]] = 0;
+		if (out_rebuilt)
+			*out_rebuilt = 1;
+		return hgb_set_topology(c, c->n_slots, parent.data(), used.data());
+	}
+	for (uint32_t p : pos) {
+		c->parent_pos_h[p] = p >= c->n_pos ? kDead : kRoot;
+		c->late_depth_h[p] = 0;
+		if (p >= c->n_pos)
+			c->has_entry_h[p] = 0;
+	}
+	if (edit_upload(c, c->edit_d, pos.data(), pos.size() * 4))
+		return 1;
+	RetireDev d{};
+	d.tiles = c->tiles.as<uint32_t>();
+	if (!c->entries_dirty) // else the tables are rebuilt from the host arrays before the next frame (entries of dead slots come out disabled)
+		for (int k = 0; k < 2; ++k) {
+			d.ent_meta[k] = c->ent[k].meta.as<uint32_t>();
+			d.vis[k][0] = c->ent[k].vis[0].as<uint8_t>();
+			d.vis[k][1] = c->ent[k].vis[1].as<uint8_t>();
+		}
+	d.ent_off = c->ent_off.as<uint32_t>();
+	d.pent = c->pent.as<uint2>();
+	d.pos = c->edit_d.as<uint32_t>();
+	d.n = uint32_t(pos.size());
+	d.dead_from = c->n_pos;
+	k_retire_nodes<<<grid_for(d.n, 128), 128, 0, c->stream>>>(d);
+	++c->launches;
+	CK(cudaGetLastError());
+	// the host arrays follow, so that a later table rebuild does not resurrect the entries (prepare_tables disables entries of dead slots)
 	return 0;
 }
 
@@ -437,6 +679,8 @@ int hgb_set_display_entries(hgb_ctx *c, int kind, uint32_t n, const uint32_t *mt
 		return fail("hgb_set_display_entries: too many entries");
 	EntryTable &t = c->ent[kind];
 	t.n = n;
+	t.n_dev = n + c->append_slack; // free entries behind the table for hgb_append_display_entries
+	t.n_records = 0;
 	t.mtx_slot.assign(mtx_slot, mtx_slot + n);
 	t.bounds_idx.assign(bounds_idx, bounds_idx + n);
 	if (flags)
@@ -465,8 +709,88 @@ int hgb_set_entry_flags(hgb_ctx *c, int kind, uint32_t first, uint32_t count, co
 	if (uint64_t(first) + count > t.n)
 		return fail("hgb_set_entry_flags: range outside the table");
 	std::copy(flags, flags + count, t.flags.begin() + first);
-	c->entries_dirty = true;
-	invalidate_graph(c);
+	if (!count || c->entries_dirty) // the tables are rebuilt from the host arrays before the next frame anyway
+		return 0;
+	// tables are live: flip the disabled bit where the kernels read it (entry table, the node's tile row or its overflow record) —
+	// EnableNode / DisableNode of a few nodes costs a few bytes, no table rebuild and no graph capture
+	CK(cudaSetDevice(c->device));
+	std::vector<uint8_t> dis(count);
+	for (uint32_t i = 0; i < count; ++i)
+		dis[i] = (flags[i] & HGB_ENTRY_DISABLED) ? 1 : 0;
+	if (edit_upload(c, c->edit_d, dis.data(), count))
+		return 1;
+	k_set_entry_flags<<<grid_for(count, 128), 128, 0, c->stream>>>(c->tiles.as<uint32_t>(), t.mtx_pos.as<uint32_t>(), t.meta.as<uint32_t>(), c->ent_off.as<uint32_t>(),
+		c->pent.as<uint2>(), c->edit_d.as<uint8_t>(), first, count, kind ? kEntKindTransparent : 0u);
+	++c->launches;
+	CK(cudaGetLastError());
+	return 0;
+}
+
+// New display entries behind the last one of a table (a node created at the end of the scene's node list lands at the end of
+// GetModelDisplayLists' output, scene.cpp:318-404). In place when the context has append slack, the tables are live, the views are
+// shared (no per-instance segments) and each entry is the first one of its node; else the tables are rebuilt before the next frame.
+int hgb_append_display_entries(hgb_ctx *c, int kind, uint32_t n, const uint32_t *mtx_slot, const uint32_t *bounds_idx, const uint8_t *flags, const uint16_t *view,
+	int *out_rebuilt) {
+	if (!c)
+		return fail("null context");
+	if (out_rebuilt)
+		*out_rebuilt = 0;
+	if (!n)
+		return 0;
+	join_post(c);
+	if (kind != 0 && kind != 1)
+		return fail("hgb_append_display_entries: kind must be 0 (opaque) or 1 (transparent)");
+	EntryTable &t = c->ent[kind];
+	if (uint64_t(t.n) + n >= 0x7fffffffu)
+		return fail("hgb_append_display_entries: too many entries");
+	if ((view != nullptr) != !t.view.empty() && t.n)
+		return fail("hgb_append_display_entries: per-entry view ids must be given for all entries of a table or for none");
+	for (uint32_t i = 0; i < n; ++i) {
+		if (mtx_slot[i] >= c->n_slots)
+			return fail("hgb_append_display_entries: entry %u references slot %u outside the topology", i, mtx_slot[i]);
+		if (bounds_idx[i] >= c->n_bounds)
+			return fail("hgb_append_display_entries: entry %u references bounds %u outside the table", i, bounds_idx[i]);
+	}
+	const uint32_t first = t.n;
+	bool fast = c->append_slack && !c->entries_dirty && !c->instance_mode && !view && uint64_t(first) + n <= t.n_dev && t.meta.p;
+	std::vector<EntryWrite> w(fast ? n : 0);
+	std::vector<uint32_t> marked;
+	for (uint32_t i = 0; i < n && fast; ++i) {
+		const uint32_t p = c->pos_of_slot[mtx_slot[i]];
+		if (!c->live_h[p] || c->has_entry_h[p]) { // a second entry of a node lives in the overflow CSR: table rebuild
+			fast = false;
+			break;
+		}
+		c->has_entry_h[p] = 1;
+		marked.push_back(p);
+		w[i] = EntryWrite{first + i, p, bounds_idx[i] | ((flags && (flags[i] & HGB_ENTRY_DISABLED)) ? kEntDisabled : 0u)};
+	}
+	t.mtx_slot.insert(t.mtx_slot.end(), mtx_slot, mtx_slot + n);
+	t.bounds_idx.insert(t.bounds_idx.end(), bounds_idx, bounds_idx + n);
+	if (flags)
+		t.flags.insert(t.flags.end(), flags, flags + n);
+	else
+		t.flags.insert(t.flags.end(), n, uint8_t(0));
+	if (view)
+		t.view.insert(t.view.end(), view, view + n);
+	t.n = first + n;
+	if (!fast) {
+		for (uint32_t p : marked)
+			c->has_entry_h[p] = 0;
+		t.n_dev = std::max(t.n_dev, t.n + c->append_slack);
+		c->entries_dirty = true;
+		invalidate_graph(c);
+		if (out_rebuilt)
+			*out_rebuilt = 1;
+		return 0;
+	}
+	CK(cudaSetDevice(c->device));
+	if (edit_upload(c, c->edit_d, w.data(), w.size() * sizeof(EntryWrite)))
+		return 1;
+	k_append_entries<<<grid_for(n, 128), 128, 0, c->stream>>>(c->tiles.as<uint32_t>(), t.mtx_pos.as<uint32_t>(), t.meta.as<uint32_t>(), t.vis[0].as<uint8_t>(),
+		t.vis[1].as<uint8_t>(), c->edit_d.as<EntryWrite>(), n, kind ? kEntKindTransparent : 0u);
+	++c->launches;
+	CK(cudaGetLastError());
 	return 0;
 }
 
@@ -752,21 +1076,25 @@ static int prepare_tables(hgb_ctx *c) {
 		EntryTable &t = c->ent[k];
 		if (c->instance_mode && t.n && t.view.size() != t.n)
 			return fail("instance views are set but entry table %d has no per-entry view ids", k);
-		std::vector<uint32_t> mtx_pos(t.n), meta(t.n);
+		if (t.n_dev < t.n + c->append_slack)
+			t.n_dev = t.n + c->append_slack;
+		std::vector<uint32_t> mtx_pos(t.n_dev, 0u), meta(t.n_dev, 1u << 24); // free entries behind the table: disabled
 		for (uint32_t e = 0; e < t.n; ++e) {
 			if (t.mtx_slot[e] >= c->n_slots)
 				return fail("display entry %u (kind %d) references slot %u outside the topology", e, k, t.mtx_slot[e]);
 			if (t.bounds_idx[e] >= c->n_bounds)
 				return fail("display entry %u (kind %d) references bounds %u outside the table", e, k, t.bounds_idx[e]);
 			mtx_pos[e] = c->pos_of_slot[t.mtx_slot[e]];
+			if (!pos_is_live(c, mtx_pos[e])) // its node was removed (hgb_remove_nodes) or never existed: the entry stays, disabled
+				t.flags[e] |= HGB_ENTRY_DISABLED;
 			meta[e] = t.bounds_idx[e] | (uint32_t(t.flags[e] & HGB_ENTRY_DISABLED ? 1 : 0) << 24);
 			++ent_off[mtx_pos[e] + 1];
 		}
-		if (upload(c, t.mtx_pos, mtx_pos.data(), size_t(t.n) * 4) || upload(c, t.meta, meta.data(), size_t(t.n) * 4))
+		if (upload(c, t.mtx_pos, mtx_pos.data(), size_t(t.n_dev) * 4) || upload(c, t.meta, meta.data(), size_t(t.n_dev) * 4))
 			return 1;
 		if (!t.view.empty() && upload(c, t.view_d, t.view.data(), size_t(t.n) * 2))
 			return 1;
-		t.n_tiles = (t.n + kCompactTile - 1) / kCompactTile;
+		t.n_tiles = (t.n_dev + kCompactTile - 1) / kCompactTile;
 		const size_t vis_bytes = size_t(t.n_tiles + 1) * kCompactTile;
 		for (int par = 0; par < 2; ++par) {
 			CK(t.vis[par].reserve(vis_bytes));
@@ -774,7 +1102,7 @@ static int prepare_tables(hgb_ctx *c) {
 		}
 		const int n_out = c->instance_mode ? 1 : std::max(c->views.n_views, 1);
 		for (int v = 0; v < n_out; ++v)
-			CK(t.out[v].reserve(std::max<size_t>(t.n, 1) * 4));
+			CK(t.out[v].reserve(std::max<size_t>(t.n_dev, 1) * 4));
 		CK(t.counts.reserve(kMaxViews * 4));
 		CK(cudaMemsetAsync(t.counts.p, 0, t.counts.cap, c->stream));
 		CK(t.ticket.reserve(kMaxViews * 4));
@@ -822,6 +1150,9 @@ static int prepare_tables(hgb_ctx *c) {
 	}
 	if (upload(c, c->ent_off, ent_off.data(), (size_t(n_pos_all) + 1) * 4) || upload(c, c->pent, pent.data(), size_t(total) * 8))
 		return 1;
+	if (c->append_slack)
+		for (uint32_t p = 0; p < c->cap_slots; ++p)
+			c->has_entry_h[p] = p < n_pos_all && (row_meta[p] & kEntHas) ? 1 : 0;
 	if (c->instance_mode && upload(c, c->pos_view, pos_view.data(), size_t(n_pos_all) * 2))
 		return 1;
 	if (n_pos_all) {

@@ -8,6 +8,7 @@
 namespace hgb {
 
 constexpr uint32_t kRoot = 0xffffffffu;
+constexpr uint32_t kDead = 0xfffffffeu; // parent row of a free position of the append region (never seen by the level kernels)
 constexpr int kMaxViews = 8;
 
 // ---- node tiles -------------------------------------------------------------------------------------------------------------
@@ -58,6 +59,22 @@ struct SceneDev {
 	int late_wait;              // where griddepcontrol.wait sits: 0 ahead of the sampled values; 1 behind the local matrix (levels behind a level);
 	                            // 2 like 0 and dependents are released only behind it (the level chained to the track sampler)
 };
+
+// mbarrier + 1-D bulk copy (TMA) helpers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+	uint32_t ok;
+	asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+	return ok != 0;
+}
+__device__ __forceinline__ void bulk_load(uint32_t dst_smem, const void *src, uint32_t bytes, uint32_t bar) {
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem), "l"(src), "r"(bytes), "r"(bar)
+				 : "memory");
+}
 
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
@@ -178,13 +195,22 @@ __device__ __forceinline__ void cull_node_entries(const SceneDev &s, const Mat4 
 template <bool FUSED, bool PER_INSTANCE, int MINB>
 __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views views, uint32_t begin, uint32_t end) {
 	__shared__ float4 s_out[8][96]; // per warp: 32 world matrices = 1536 B, for the transposed store
-	__shared__ float4 s_planes[kMaxViews * 12];
-	// The shared view frusta (host-expanded form) are needed only by the cull tail: warp 0 starts an asynchronous copy into shared memory
-	// here (cp.async: no registers, nobody waits) and the CTA meets at a barrier just ahead of the tail, long after the copy has landed.
-	if (FUSED && !PER_INSTANCE && threadIdx.x < 32u) {
-		for (uint32_t i = threadIdx.x; i < uint32_t(views.n_views) * 12u; i += 32u)
-			asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(uint32_t(__cvta_generic_to_shared(s_planes + i))), "l"(views.planes_x + i) : "memory");
-		asm volatile("cp.async.commit_group;" ::: "memory");
+	__shared__ __align__(128) float4 s_planes[kMaxViews * 12];
+	// The shared view frusta (host-expanded form) are needed only by the cull tail: one thread starts a bulk copy (TMA, completion counted
+	// on an mbarrier: no registers, nobody waits) and every warp merely tests the barrier's phase when it reaches the tail, hundreds of
+	// instructions later. The only CTA-wide barrier is the one right here, which publishes the initialised mbarrier while all warps are
+	// still in step; a __syncthreads() ahead of the tail instead cost 5.7 % of the stall samples (warps of a CTA drift apart).
+	__shared__ __align__(8) uint64_t s_bar;
+	if (FUSED && !PER_INSTANCE) {
+		if (threadIdx.x == 0) {
+			const uint32_t bar = smem_u32(&s_bar), bytes = uint32_t(views.n_views) * 192u;
+			mbar_init(bar, 1);
+			asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+			mbar_arrive_expect_tx(bar, bytes); // (0 views: the phase completes right here)
+			if (bytes)
+				bulk_load(smem_u32(s_planes), views.planes_x, bytes, bar);
+		}
+		__syncthreads();
 	}
 	// Programmatic dependent launch: the next level's grid may become resident while this one drains — ahead of its own
 	// griddepcontrol.wait it reads only edit-time rows and sampled values — which hides the launch latency, the first DRAM round trip and
@@ -248,11 +274,9 @@ __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views vi
 	// store the world rows (a preset row is rewritten with its own value)
 	store_world_rows(s, s_out[warp], world, live, p, lane, end);
 
-	if (FUSED && !PER_INSTANCE) { // the frusta have landed (warps that left above no longer count at the barrier)
-		if (threadIdx.x < 32u)
-			asm volatile("cp.async.wait_all;" ::: "memory");
-		__syncthreads();
-	}
+	if (FUSED && !PER_INSTANCE) // the frusta have landed long ago: one successful phase test
+		while (!mbar_try_wait(smem_u32(&s_bar), 0u)) {
+		}
 	if (FUSED && live && (meta & kEntHas))
 		cull_node_entries<PER_INSTANCE>(s, world, meta, eidx, s_planes, views.n_views, p);
 }
@@ -266,10 +290,14 @@ __global__ void __launch_bounds__(256, MINB) k_update_level(SceneDev s, Views vi
 // so every row is bit-identical to the level-by-level result; it is only recomputed by each descendant instead of read back. The
 // host bounds the redundant work (sum over the covered levels of nodes x depth, hgb_options.top_walk) and the chain length
 // (kMaxWalk). A chain stops at a preset ancestor (SetNodeWorldMatrix), whose row k_apply_presets wrote ahead of the frame.
+//
+// The same kernel computes the APPEND REGION behind the last level (hgb_append_nodes): positions [begin, end) hold nodes added since
+// the last depth sort, in no particular order, and free positions (parent row kDead). It runs after the last level, so a chain stops at
+// the first ancestor below `base` — a sorted position, final for this frame — and only ancestors inside the region are recomputed.
 constexpr int kMaxWalk = 12;
 
 template <bool FUSED, bool PER_INSTANCE>
-__global__ void __launch_bounds__(256, 6) k_update_top(SceneDev s, Views views, uint32_t end) {
+__global__ void __launch_bounds__(256, 6) k_update_top(SceneDev s, Views views, uint32_t begin, uint32_t end, uint32_t base) {
 	__shared__ float4 s_out[8][96];
 	__shared__ float4 s_planes[kMaxViews * 12];
 	if (FUSED && !PER_INSTANCE) {
@@ -282,7 +310,7 @@ __global__ void __launch_bounds__(256, 6) k_update_top(SceneDev s, Views views, 
 	// dependents only behind the wait (they read sampled values ahead of THEIR wait)
 	asm volatile("griddepcontrol.wait;" ::: "memory");
 	asm volatile("griddepcontrol.launch_dependents;");
-	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t p = begin + blockIdx.x * blockDim.x + threadIdx.x;
 	const bool live = p < end;
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 	if (__ballot_sync(0xffffffffu, live) == 0)
@@ -291,20 +319,27 @@ __global__ void __launch_bounds__(256, 6) k_update_top(SceneDev s, Views views, 
 	uint32_t meta = 0, eidx = 0;
 	if (live) {
 		const uint32_t *t = s.tiles + tile_word(p, 0);
+		uint32_t q = t[kRowParent * 32];
 		meta = t[kRowEntMeta * 32];
 		if (FUSED)
 			eidx = t[kRowEntIdx * 32];
-		if (s.preset && s.preset[p]) {
+		if (q == kDead) { // free position of the append region: a zero row, no entry
+			meta = 0;
+#pragma unroll
+			for (int i = 0; i < 3; ++i)
+#pragma unroll
+				for (int j = 0; j < 4; ++j)
+					world.m[i][j] = 0.f;
+		} else if (s.preset && s.preset[p]) {
 			world = load_mat4(s.world + size_t(p) * 12);
 		} else {
 			uint32_t chain[kMaxWalk]; // ancestors that must be recomputed, nearest first
 			int n = 0;
-			uint32_t q = t[kRowParent * 32];
-			while (q != kRoot && !(s.preset && s.preset[q]) && n < kMaxWalk) {
+			while (q != kRoot && q >= base && !(s.preset && s.preset[q]) && n < kMaxWalk) {
 				chain[n++] = q;
 				q = s.tiles[tile_word(q, kRowParent)];
 			}
-			bool have = q != kRoot; // stopped at a preset ancestor: its row is the base
+			bool have = q != kRoot; // stopped at a preset ancestor or below the region: its row is the base
 			if (have)
 				world = load_mat4(s.world + size_t(q) * 12);
 			for (int i = n - 1; i >= 0; --i) {

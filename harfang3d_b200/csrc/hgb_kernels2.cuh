@@ -806,6 +806,113 @@ __global__ void __launch_bounds__(256) k_fill_rows(uint32_t *__restrict__ tiles,
 		tiles[tile_word(p, row)] = src[p];
 }
 
+// ---- incremental edits (hgb_append_nodes / hgb_remove_nodes / hgb_append_display_entries / hgb_set_entry_flags) --------------------
+// A few threads each: the point is that nothing else moves — no re-sort, no table rebuild, no graph capture.
+struct NodeWrite {
+	uint32_t pos, parent; // parent position, kRoot or kDead (free the position)
+	float trs[9];
+	uint32_t zero_world;  // 1: new node — both world rows start from zero like a std::vector::resize'd slot
+};
+__global__ void __launch_bounds__(128) k_write_nodes(uint32_t *__restrict__ tiles, float *__restrict__ world0, float *__restrict__ world1, uint8_t *__restrict__ preset,
+	const NodeWrite *__restrict__ w, uint32_t n) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n)
+		return;
+	const NodeWrite x = w[i];
+	uint32_t *t = tiles + tile_word(x.pos, 0);
+#pragma unroll
+	for (int r = 0; r < 9; ++r)
+		t[r * 32] = __float_as_uint(x.trs[r]);
+	t[kRowParent * 32] = x.parent;
+	t[kRowEntMeta * 32] = 0;
+	t[kRowEntIdx * 32] = 0;
+	preset[x.pos] = 0;
+	if (x.zero_world)
+		for (int k = 0; k < 12; ++k)
+			world0[size_t(x.pos) * 12 + k] = 0.f, world1[size_t(x.pos) * 12 + k] = 0.f;
+}
+
+// A removed node: its display entries are disabled for good (entry tables, tile row, overflow records; visibility bytes of both
+// parities cleared, since nobody rewrites them once the node is gone). In the SORTED region the position stays until the next depth
+// sort as a childless root that owns a disabled entry; in the append region it becomes a free position (kDead).
+struct RetireDev {
+	uint32_t *tiles;
+	uint32_t *ent_meta[2];
+	uint8_t *vis[2][2]; // [kind][parity]
+	const uint32_t *ent_off;
+	uint2 *pent;
+	const uint32_t *pos;
+	uint32_t n, dead_from;
+};
+__global__ void __launch_bounds__(128) k_retire_nodes(RetireDev d) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= d.n)
+		return;
+	const uint32_t p = d.pos[i];
+	uint32_t *row = d.tiles + tile_word(p, kRowEntMeta);
+	const uint32_t m = *row;
+	if ((m & kEntHas) && d.ent_meta[0]) {
+		const int k = (m & kEntKindTransparent) ? 1 : 0;
+		const uint32_t e = d.tiles[tile_word(p, kRowEntIdx)];
+		d.ent_meta[k][e] |= kEntDisabled;
+		d.vis[k][0][e] = 0, d.vis[k][1][e] = 0;
+		if (m & kEntMore)
+			for (uint32_t j = d.ent_off[p]; j < d.ent_off[p + 1]; ++j) {
+				const uint2 rec = d.pent[j];
+				const int k2 = int(rec.x >> 31);
+				d.pent[j].y = rec.y | kEntDisabled;
+				d.ent_meta[k2][rec.x & 0x7fffffffu] |= kEntDisabled;
+				d.vis[k2][0][rec.x & 0x7fffffffu] = 0, d.vis[k2][1][rec.x & 0x7fffffffu] = 0;
+			}
+	}
+	if (p >= d.dead_from) {
+		d.tiles[tile_word(p, kRowParent)] = kDead;
+		*row = 0;
+	} else {
+		d.tiles[tile_word(p, kRowParent)] = kRoot;
+		*row = m | kEntDisabled; // bound triples keep their anim_val slots (the sampler still writes them)
+	}
+}
+
+struct EntryWrite {
+	uint32_t entry, pos, meta; // meta: bounds index | kEntDisabled
+};
+// new display entries at the end of a table, each the FIRST entry of its node (rows 10 / 11 of the node's tile)
+__global__ void __launch_bounds__(128) k_append_entries(uint32_t *__restrict__ tiles, uint32_t *__restrict__ mtx_pos, uint32_t *__restrict__ ent_meta, uint8_t *__restrict__ vis_a,
+	uint8_t *__restrict__ vis_b, const EntryWrite *__restrict__ w, uint32_t n, uint32_t kind_bit) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n)
+		return;
+	const EntryWrite x = w[i];
+	mtx_pos[x.entry] = x.pos;
+	ent_meta[x.entry] = x.meta;
+	vis_a[x.entry] = 0, vis_b[x.entry] = 0;
+	uint32_t *row = tiles + tile_word(x.pos, kRowEntMeta);
+	*row = (*row & kLaneAnimatedMask) | x.meta | kEntHas | kind_bit;
+	tiles[tile_word(x.pos, kRowEntIdx)] = x.entry;
+}
+
+// disabled flag of entries [first, first + n) of one table: the entry table (stand-alone cull) and wherever the fused pass reads it —
+// the node's tile row when it is the node's first entry, else its record in the overflow CSR
+__global__ void __launch_bounds__(128) k_set_entry_flags(uint32_t *__restrict__ tiles, const uint32_t *__restrict__ mtx_pos, uint32_t *__restrict__ ent_meta,
+	const uint32_t *__restrict__ ent_off, uint2 *__restrict__ pent, const uint8_t *__restrict__ disabled, uint32_t first, uint32_t n, uint32_t kind_bit) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n)
+		return;
+	const uint32_t e = first + i, dis = disabled[i] ? kEntDisabled : 0u;
+	ent_meta[e] = (ent_meta[e] & ~kEntDisabled) | dis;
+	const uint32_t p = mtx_pos[e];
+	uint32_t *row = tiles + tile_word(p, kRowEntMeta);
+	const uint32_t m = *row;
+	if ((m & kEntHas) && (m & kEntKindTransparent) == kind_bit && tiles[tile_word(p, kRowEntIdx)] == e) {
+		*row = (m & ~kEntDisabled) | dis;
+	} else if (m & kEntMore) {
+		for (uint32_t k = ent_off[p]; k < ent_off[p + 1]; ++k)
+			if (pent[k].x == (e | kind_bit))
+				pent[k].y = (pent[k].y & ~kEntDisabled) | dis;
+	}
+}
+
 // visible entry indices -> the caller's 16-byte records of those entries (hgb_get_visible_records_ptr): the sparse gather runs here,
 // where random 16-byte reads are cheap, and the host receives one contiguous array
 __global__ void __launch_bounds__(256) k_gather_records(const uint4 *__restrict__ table, const uint32_t *__restrict__ visible, const uint32_t *__restrict__ count,

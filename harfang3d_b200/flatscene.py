@@ -108,6 +108,7 @@ def load():
     _sig(L, "hgfacade_time_fused_frames", c_i, [c_p, c_i, c_i64, c_p, c_p])
     _sig(L, "hgfacade_read_visible", c_i, [c_p, c_p, c_i])
     _sig(L, "hgfacade_set_default_device", None, [c_i])
+    _sig(L, "hgfacade_visible_breakdown", None, [c_p])
     return L
 
 

@@ -60,6 +60,10 @@ typedef struct hgb_options {
 	                        both kernels lean on HBM, running them together measured 1-8 % slower than back to back (profiles r01c) */
 	int slice_nodes;   /* with overlap_sampler, levels larger than this are cut into slices of this many nodes, each waiting only for its
 	                      own track chunk (0 = no slicing; rounded up to a multiple of 256) */
+	int append_slack;  /* > 0: every depth sort (hgb_set_topology) reserves this many free positions behind the last level — the APPEND REGION —
+	                      and this many free entries behind each display-entry table, so that hgb_append_nodes / hgb_remove_nodes /
+	                      hgb_append_display_entries edit a live scene in place: no re-sort, no table rebuild, no graph capture. The region is
+	                      computed by one extra launch per frame (k_update_top over its positions). 0 (default): those calls rebuild */
 } hgb_options;
 /* Environment switches read by hgb_create, for A/B measurements only (defaults are the fast settings; results are identical in every
  * mode): HGB_PDL=0 launches the frame's kernels with plain stream dependencies instead of programmatic dependent launches;
@@ -93,6 +97,19 @@ int hgb_set_topology(hgb_ctx *, uint32_t n_slots, const uint32_t *parent_slot, c
  * device — no re-sort, no table rebuild, no graph re-capture; *out_rebuilt = 0. Otherwise the layout is rebuilt as by hgb_set_topology and
  * *out_rebuilt = 1 (the caller then re-derives what it derives after hgb_set_topology). */
 int hgb_set_parents(hgb_ctx *, uint32_t n, const uint32_t *slot, const uint32_t *parent_slot, int *out_rebuilt /* nullable */);
+/* In-place edits of a live scene (spawn / despawn per episode). With hgb_options.append_slack > 0 these cost a few bytes and one tiny
+ * launch: no depth sort, no table rebuild, no graph capture; *out_rebuilt = 0. Without slack, or when the fast path does not apply (region
+ * full, chain inside the append region longer than 11, node with children removed, second entry of a node, per-instance views), they fall
+ * back to the full rebuild and *out_rebuilt = 1. Results are the same either way.
+ *   hgb_append_nodes: new LEAF transforms in free slots (Scene::CreateNode + CreateTransform + SetParent, scene.cpp:92-137,
+ *     component.cpp:184-193): slot, parent slot (or HGB_ROOT) and TRS (9 floats) per node; a slot may be one past the current end.
+ *   hgb_remove_nodes: DestroyNode / DestroyTransform + GarbageCollect (scene.cpp:139-237). Display entries of the node are disabled
+ *     for good; children of a removed node become roots (scene.cpp:268-272), which is a rebuild.
+ *   hgb_append_display_entries: entries behind the last one of a table, same arguments as hgb_set_display_entries. */
+int hgb_append_nodes(hgb_ctx *, uint32_t n, const uint32_t *slot, const uint32_t *parent_slot /* nullable: roots */, const float *trs9, int *out_rebuilt /* nullable */);
+int hgb_remove_nodes(hgb_ctx *, uint32_t n, const uint32_t *slot, int *out_rebuilt /* nullable */);
+int hgb_append_display_entries(hgb_ctx *, int kind, uint32_t n, const uint32_t *mtx_slot, const uint32_t *bounds_idx, const uint8_t *flags /* nullable */,
+	const uint16_t *view /* nullable */, int *out_rebuilt /* nullable */);
 /* TRS of slots [first, first+count) — dirty-range upload. */
 int hgb_upload_trs(hgb_ctx *, uint32_t first, uint32_t count, const float *trs9);
 /* SetNodeWorldMatrix overrides (scene.cpp:768-786) for the NEXT hgb_update only. */
@@ -187,7 +204,7 @@ int hgb_get_visible_ptr(hgb_ctx *, int kind, uint32_t view, const uint32_t **out
 /* Optional: one opaque 16-byte record per display entry of a kind (what the caller wants back per survivor — the facade stores its
  * hg::ModelDisplayList, harfang/engine/render_pipeline.h:577-582), and the visible list of (kind, view) returned AS those records, in order:
  * gathered on the device, one round trip, pinned buffer owned by the context (valid until the next call for this kind). */
-int hgb_set_entry_records(hgb_ctx *, int kind, uint32_t n, const void *rec16);
+int hgb_set_entry_records(hgb_ctx *, int kind, uint32_t first, uint32_t count, const void *rec16); /* contiguous from 0: the whole table, or the tail behind the records already set */
 int hgb_get_visible_records_ptr(hgb_ctx *, int kind, uint32_t view, const void **out_rec16, uint32_t *out_count);
 /* instance mode: exclusive offsets of every instance's survivors inside the kind-0 list, n_instances+1 values */
 int hgb_get_instance_offsets(hgb_ctx *, uint32_t *out_offsets);

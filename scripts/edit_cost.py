@@ -28,4 +28,26 @@ for name, fs in (("1M", scenegen.config_c2(seed=2, n_nodes=1_000_000)), ("16M", 
     t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); inc_first = time.perf_counter() - t0
     out[name] = {"incremental_reparent_ms": inc * 1e3, "incremental_rebuilt": bool(rebuilt), "first_update_after_incremental_ms": inc_first * 1e3,"steady_frame_ms": steady * 1e3, "set_topology_ms": topo * 1e3, "first_update_after_edit_ms": first * 1e3, "second_update_ms": second * 1e3}
     ctx.close()
+    # in-place spawn / despawn (hgb_options.append_slack): one leaf with a display entry appended under a deep node, then removed again
+    ctx = harfang3d_b200.Context(0, append_slack=65536)
+    t = hostmirror.upload(ctx, fs)
+    clocks = hostmirror.PlayClocks(fs)
+    for _ in range(3):
+        ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True)
+    ctx.sync()
+    t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); steady_slack = time.perf_counter() - t0
+    slot = np.array([fs.n], np.uint32)
+    par = np.array([fs.n - 7], np.uint32)
+    trs = np.array([[1, 2, 3, 0.1, 0.2, 0.3, 1, 1, 1]], np.float32)
+    t0 = time.perf_counter()
+    r1 = ctx.append_nodes(slot, par, trs)
+    r2 = ctx.append_display_entries(0, slot, np.array([0], np.uint32), np.array([0], np.uint8))
+    ctx.sync(); app = time.perf_counter() - t0
+    t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); app_first = time.perf_counter() - t0
+    t0 = time.perf_counter(); r3 = ctx.remove_nodes(slot); ctx.sync(); rem = time.perf_counter() - t0
+    t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); rem_first = time.perf_counter() - t0
+    out[name].update({"append_leaf_with_entry_ms": app * 1e3, "append_rebuilt": bool(r1 or r2), "first_update_after_append_ms": app_first * 1e3,
+                      "remove_leaf_ms": rem * 1e3, "remove_rebuilt": bool(r3), "first_update_after_remove_ms": rem_first * 1e3,
+                      "steady_frame_with_append_region_ms": steady_slack * 1e3})
+    ctx.close()
 print(json.dumps(out))

@@ -814,3 +814,136 @@ def test_incremental_reparent_inside_a_level(hgb, oracles):
     assert (bits(ctx.get_worlds(previous=True)) == bits(orc.worlds(previous=True)[: fs.n])).all()
     check_visible(ctx, t, orc, fr)
     orc.close(); ctx.close()
+
+
+def _extend_scene(fs, trs, parent, model):
+    """a FlatScene with the given nodes appended (static, single-list opaque objects or none)"""
+    import dataclasses
+    k = len(parent)
+    return dataclasses.replace(
+        fs, trs=np.concatenate([fs.trs, trs]).astype(np.float32), parent=np.concatenate([fs.parent, parent]).astype(np.int32),
+        disabled=np.concatenate([fs.disabled, np.zeros(k, np.uint8)]), model=np.concatenate([fs.model, model]).astype(np.int32),
+        n_mats=np.concatenate([fs.n_mats, np.ones(k, np.uint8)]), transparent_mask=np.concatenate([fs.transparent_mask, np.zeros(k, np.uint32)]))
+
+
+def test_append_and_remove_nodes_in_place(hgb, oracles):
+    """hgb_append_nodes / hgb_append_display_entries / hgb_remove_nodes with append slack: leaves spawned under any node (also under nodes
+    spawned a moment ago) and despawned again without a depth sort, a table rebuild or a graph capture; worlds, previous worlds and visible
+    lists equal the reference's (CreateNode + SetParent / DestroyNode + GarbageCollect, scene.cpp:92-237) after every step. A chain too long
+    for the append region, or no slack at all, falls back to the rebuild with the same results."""
+    ref, _ = oracles
+    if ref is None:
+        pytest.skip("needs the compiled reference")
+    from tests.scene_io import RefScene
+    rng = np.random.default_rng(97)
+    fs = scenegen.static_scene(20_000, 6, 7, n_models=2, seed=97)
+    n0 = fs.n
+    ctx = hgb.Context(0, append_slack=2048)
+    plain = hgb.Context(0)  # no slack: every edit rebuilds
+    t = hostmirror.upload(ctx, fs)
+    hostmirror.upload(plain, fs, tables=t)
+    orc = RefScene(ref, fs)
+    fr = hostmirror.scene_frusta(fs)[0]
+    for _ in range(2):
+        ctx.update(None, fused_cull=True); plain.update(None, fused_cull=True); orc.update(0)
+    check_visible(ctx, t, orc, fr)
+
+    # ---- spawn: 300 leaves under random old nodes, 60 more under freshly spawned ones (chains up to 3 deep), 10 roots
+    k = 370
+    parent = np.empty(k, np.int32)
+    parent[:300] = rng.integers(0, n0, 300)
+    parent[300:330] = n0 + rng.integers(0, 300, 30)
+    parent[330:360] = n0 + 300 + rng.integers(0, 30, 30)
+    parent[360:] = -1
+    trs = scenegen.random_trs(rng, k, parent)
+    trs[:, 6:9] = rng.uniform(0.8, 1.25, (k, 3))
+    trs[360:, 0:3] = rng.uniform(-2, 2, (10, 3))
+    model = rng.integers(0, 2, k).astype(np.int32)
+    fs2 = _extend_scene(fs, trs, parent, model)
+    t2 = hostmirror.build_tables(fs2)
+    n_old_ent = len(t["ent0_mtx_slot"])
+    assert (t2["ent0_mtx_slot"][:n_old_ent] == t["ent0_mtx_slot"]).all()  # new nodes sit behind the old ones in the display lists
+    ref.hgref_add_nodes(orc.h, k, oracle_lib.P(np.ascontiguousarray(trs)), oracle_lib.P(parent), None, oracle_lib.P(model),
+                        oracle_lib.P(np.ones(k, np.uint8)), oracle_lib.P(np.zeros(k, np.uint32)), None)
+    slots = np.arange(n0, n0 + k, dtype=np.uint32)
+    par_slot = np.where(parent >= 0, parent, 0xFFFFFFFF).astype(np.uint32)
+    before = ctx.launch_count
+    assert ctx.append_nodes(slots, par_slot, trs) is False
+    assert ctx.append_display_entries(0, t2["ent0_mtx_slot"][n_old_ent:], t2["ent0_bounds_idx"][n_old_ent:], t2["ent0_flags"][n_old_ent:]) is False
+    assert plain.append_nodes(slots, par_slot, trs) is True
+    assert plain.append_display_entries(0, t2["ent0_mtx_slot"][n_old_ent:], t2["ent0_bounds_idx"][n_old_ent:], t2["ent0_flags"][n_old_ent:]) is True
+    for frame in range(2):
+        ctx.update(None, fused_cull=True); plain.update(None, fused_cull=True); orc.update(0)
+        w_ref = orc.worlds()[: n0 + k]
+        assert (bits(ctx.get_worlds()) == bits(w_ref)).all(), "frame %d" % frame
+        assert (bits(plain.get_worlds()) == bits(w_ref)).all()
+        if frame:  # the first frame after the spawn: the reference's previous rows of new slots are whatever resize() left
+            assert (bits(ctx.get_worlds(previous=True)) == bits(orc.worlds(previous=True)[: n0 + k])).all()
+        check_visible(ctx, t2, orc, fr)
+        check_visible(plain, t2, orc, fr)
+    assert ctx.launch_count - before < 16  # two edit kernels + two frames: nothing was re-sorted, rebuilt or captured piecemeal
+
+    # ---- EnableNode / DisableNode of a few entries on live tables: flags only
+    tog = rng.choice(len(t2["ent0_flags"]), 40, replace=False)
+    for e in tog:
+        node = int(t2["ent0_mtx_slot"][e])
+        now = 0 if t2["ent0_flags"][e] else 1
+        t2["ent0_flags"][e] = now
+        ref.hgref_enable_node(orc.h, node, 0 if now else 1)
+        ctx.set_entry_flags(0, int(e), np.array([now], np.uint8))
+    ctx.update(None, fused_cull=True); orc.update(0)
+    check_visible(ctx, t2, orc, fr)
+    assert ctx.launch_count - before < 16 + 40 + 8
+
+    # ---- despawn: childless nodes of the append region and of the sorted part
+    has_child = np.zeros(n0 + k, bool)
+    has_child[fs2.parent[fs2.parent >= 0]] = True
+    gone = np.concatenate([rng.choice(np.nonzero(~has_child[n0:])[0] + n0, 80, replace=False), rng.choice(np.nonzero(~has_child[:n0])[0], 80, replace=False)]).astype(np.uint32)
+    for nd in gone:
+        ref.hgref_destroy_node(orc.h, int(nd))
+    ref.hgref_garbage_collect(orc.h)
+    before = ctx.launch_count
+    assert ctx.remove_nodes(gone) is False
+    assert plain.remove_nodes(gone) is True
+    live = np.ones(n0 + k, bool)
+    live[gone] = False
+    for kind in (0,):
+        t2["ent%d_flags" % kind][~live[t2["ent%d_mtx_slot" % kind]]] = 1  # gone from the reference's lists: like a disabled entry for the rank check
+    for frame in range(2):
+        ctx.update(None, fused_cull=True); plain.update(None, fused_cull=True); orc.update(0)
+        w_ref = orc.worlds()[: n0 + k]
+        assert (bits(ctx.get_worlds())[live] == bits(w_ref)[live]).all()
+        assert (bits(plain.get_worlds())[live] == bits(w_ref)[live]).all()
+        check_visible(ctx, t2, orc, fr)
+        check_visible(plain, t2, orc, fr)
+    assert ctx.launch_count - before < 12
+    # the stand-alone cull reads the entry tables: the removed nodes' entries are disabled there as well
+    ctx.update(None, fused_cull=False); ctx.cull(); orc.update(0)
+    check_visible(ctx, t2, orc, fr)
+
+    # ---- freed positions of the append region are handed out again; a chain too long for the region rebuilds
+    back = gone[:40]  # 40 of the despawned slots of the append region
+    ptrs = scenegen.random_trs(rng, 40, np.zeros(40, np.int32))
+    ppar = rng.integers(0, n0, 40).astype(np.uint32)
+    ppar[np.isin(ppar, gone)] = 0
+    assert ctx.append_nodes(back, ppar, ptrs) is False
+    chain = np.arange(n0 + k, n0 + k + 14, dtype=np.uint32)
+    cpar = np.concatenate([[5], chain[:-1]]).astype(np.uint32)
+    ctrs = scenegen.random_trs(rng, 14, np.zeros(14, np.int32))
+    ctrs[:, 6:9] = 1.0
+    assert ctx.append_nodes(chain, cpar, ctrs) is True  # 13 ancestors inside the region > kMaxWalk - 1
+    # the same final hierarchy built from scratch
+    fs3 = _extend_scene(fs2, ctrs, cpar.astype(np.int32), np.full(14, -1, np.int32))
+    fs3.trs[back] = ptrs
+    fs3.parent[back] = ppar.astype(np.int32)
+    scratch = hgb.Context(0)
+    par3 = np.where(fs3.parent >= 0, fs3.parent, 0xFFFFFFFF).astype(np.uint32)
+    used3 = np.ones(fs3.n, np.uint8)
+    used3[gone[40:]] = 0
+    scratch.set_topology(par3, used3)
+    scratch.upload_trs(np.ascontiguousarray(fs3.trs, np.float32))
+    for _ in range(2):
+        ctx.update(None, fused_cull=False); scratch.update(None, fused_cull=False)
+    sel = used3.astype(bool)
+    assert (bits(ctx.get_worlds())[sel] == bits(scratch.get_worlds())[sel]).all()
+    orc.close(); ctx.close(); plain.close(); scratch.close()
