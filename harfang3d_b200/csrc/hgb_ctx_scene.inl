@@ -681,6 +681,11 @@ int hgb_set_display_entries(hgb_ctx *c, int kind, uint32_t n, const uint32_t *mt
 	t.n = n;
 	t.n_dev = n + c->append_slack; // free entries behind the table for hgb_append_display_entries
 	t.n_records = 0;
+	if (c->append_slack) { // appended entries must not re-allocate 16M-element host arrays
+		t.mtx_slot.reserve(t.n_dev), t.bounds_idx.reserve(t.n_dev), t.flags.reserve(t.n_dev);
+		if (view)
+			t.view.reserve(t.n_dev);
+	}
 	t.mtx_slot.assign(mtx_slot, mtx_slot + n);
 	t.bounds_idx.assign(bounds_idx, bounds_idx + n);
 	if (flags)

@@ -42,11 +42,22 @@ for name, fs in (("1M", scenegen.config_c2(seed=2, n_nodes=1_000_000)), ("16M", 
     t0 = time.perf_counter()
     r1 = ctx.append_nodes(slot, par, trs)
     r2 = ctx.append_display_entries(0, slot, np.array([0], np.uint32), np.array([0], np.uint8))
+    ctx.sync(); app_first_call = time.perf_counter() - t0  # allocates the edit scratch
+    slot = slot + 1
+    t0 = time.perf_counter()
+    r1 = ctx.append_nodes(slot, par, trs) or r1
+    r2 = ctx.append_display_entries(0, slot, np.array([0], np.uint32), np.array([0], np.uint8)) or r2
     ctx.sync(); app = time.perf_counter() - t0
+    batch = np.arange(int(slot[0]) + 1, int(slot[0]) + 1 + 1024, dtype=np.uint32)  # an episode's worth: 1024 leaves under random nodes
+    bpar = np.random.default_rng(1).integers(0, fs.n, 1024).astype(np.uint32)
+    t0 = time.perf_counter()
+    r1 = ctx.append_nodes(batch, bpar, np.tile(trs, (1024, 1))) or r1
+    r2 = ctx.append_display_entries(0, batch, np.zeros(1024, np.uint32), np.zeros(1024, np.uint8)) or r2
+    ctx.sync(); app_batch = time.perf_counter() - t0
     t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); app_first = time.perf_counter() - t0
     t0 = time.perf_counter(); r3 = ctx.remove_nodes(slot); ctx.sync(); rem = time.perf_counter() - t0
     t0 = time.perf_counter(); ctx.update(clocks.step(scenegen.FRAME_DT), fused_cull=True); ctx.sync(); rem_first = time.perf_counter() - t0
-    out[name].update({"append_leaf_with_entry_ms": app * 1e3, "append_rebuilt": bool(r1 or r2), "first_update_after_append_ms": app_first * 1e3,
+    out[name].update({"append_leaf_with_entry_ms": app * 1e3, "append_first_call_ms": app_first_call * 1e3, "append_1024_leaves_with_entries_ms": app_batch * 1e3, "append_rebuilt": bool(r1 or r2), "first_update_after_append_ms": app_first * 1e3,
                       "remove_leaf_ms": rem * 1e3, "remove_rebuilt": bool(r3), "first_update_after_remove_ms": rem_first * 1e3,
                       "steady_frame_with_append_region_ms": steady_slack * 1e3})
     ctx.close()

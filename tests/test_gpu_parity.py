@@ -687,11 +687,14 @@ def test_async_tail_and_one_round_trip_fetch(hgb):
     wide = fr.copy()
     # one opaque 16-byte record per entry: the survivors come back as their records, gathered on the device
     rec_table = rng.integers(0, 2**32, (a.n_entries[0], 4), dtype=np.uint32)
-    with pytest.raises(hgb.HgbError, match="records for a table"):
-        a.set_entry_records(0, rec_table[:-1])
+    with pytest.raises(hgb.HgbError, match="for a table of"):
+        a.set_entry_records(0, np.concatenate([rec_table, rec_table[:1]]))
+    a.set_entry_records(0, rec_table[:-5])  # a prefix ...
     with pytest.raises(hgb.HgbError, match="no records"):
         a.get_visible_records(0, 0)
-    a.set_entry_records(0, rec_table)
+    with pytest.raises(hgb.HgbError, match="leave a gap"):
+        a.set_entry_records(0, rec_table[-2:], first=len(rec_table) - 2)
+    a.set_entry_records(0, rec_table[-5:], first=len(rec_table) - 5)  # ... and the tail behind it
     for frame in range(12):
         if frame == 6:  # a far wider frustum: the visible list grows well past the +25 % guess of the fetch
             wide = hostmirror.make_perspective_frustum(0.1, 5000.0, 2.8, 1.0, 1.0, np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, -400], np.float32))
