@@ -894,8 +894,10 @@ def test_append_and_remove_nodes_in_place(hgb, oracles):
         t2["ent0_flags"][e] = now
         ref.hgref_enable_node(orc.h, node, 0 if now else 1)
         ctx.set_entry_flags(0, int(e), np.array([now], np.uint8))
-    ctx.update(None, fused_cull=True); orc.update(0)
+        plain.set_entry_flags(0, int(e), np.array([now], np.uint8))
+    ctx.update(None, fused_cull=True); plain.update(None, fused_cull=True); orc.update(0)
     check_visible(ctx, t2, orc, fr)
+    check_visible(plain, t2, orc, fr)
     assert ctx.launch_count - before < 16 + 40 + 8
 
     # ---- despawn: childless nodes of the append region and of the sorted part
