@@ -44,6 +44,7 @@ SIGNATURES = {
     "hgb_upload_trs": (_i, [_p, _u32, _u32, _p]),
     "hgb_set_parents": (_i, [_p, _u32, _p, _p, _p]),
     "hgb_append_nodes": (_i, [_p, _u32, _p, _p, _p, _p]),
+    "hgb_slot_capacity": (_i, [_p, _p]),
     "hgb_remove_nodes": (_i, [_p, _u32, _p, _p]),
     "hgb_append_display_entries": (_i, [_p, _i, _u32, _p, _p, _p, _p, _p]),
     "hgb_set_preset_world": (_i, [_p, _u32, _p, _p]),
@@ -64,6 +65,8 @@ SIGNATURES = {
     "hgb_cull_skinned_list": (_i, [_p, _u32, _p, _p, _p, _u32, _p, _p, _u32, _p, _p, _p, _p]),
     "hgb_set_entry_records": (_i, [_p, _i, _u32, _u32, _p]),
     "hgb_get_visible_records_ptr": (_i, [_p, _i, _u32, _p, _p]),
+    "hgb_get_visible_records_begin": (_i, [_p, _i, _u32, _u32, _p, _p]),
+    "hgb_visible_records_wait": (_i, [_p, _i, _u32]),
     "hgb_get_visible_ptr": (_i, [_p, _i, _u32, _p, _p]),
     "hgb_peer_init": (_i, [_p, _u32, _u32, _u32, _p, _p, _p, _p]),
     "hgb_peer_connect": (_i, [_p, _p, _p]),
@@ -85,6 +88,7 @@ SIGNATURES = {
     "hgb_get_bone_matrices": (_i, [_p, _p, _i]),
     "hgb_device_ptr": (_p, [_p, _i]),
     "hgb_launch_count": (C.c_uint64, [_p]),
+    "hgb_rebuild_count": (C.c_uint64, [_p]),
     "hgb_level_count": (_u32, [_p]),
     "hgb_is_identity_order": (_i, [_p]),
     "hgb_time_begin": (_i, [_p]),
@@ -425,6 +429,10 @@ class Context:
     @property
     def launch_count(self):
         return self._L.hgb_launch_count(self._h)
+
+    @property
+    def rebuild_count(self):
+        return self._L.hgb_rebuild_count(self._h)
 
     @property
     def level_count(self):

@@ -63,6 +63,7 @@ double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock:
 } // namespace
 
 #ifdef HG_FACADE
+#include "hgb200.h"
 namespace hg {
 extern double g_visible_breakdown[3];
 }
@@ -778,6 +779,16 @@ void hgfacade_visible_breakdown(double *out3) {
 }
 // one process per GPU: scenes created after this call live on `device` (Scene::SetDefaultDevice)
 void hgfacade_set_default_device(int device) { Scene::SetDefaultDevice(device); }
+void hgfacade_set_default_append_slack(int slots) { Scene::SetDefaultAppendSlack(slots); }
+// kernels the scene's device context has launched so far (tests: an in-place edit must not re-sort, rebuild or re-capture)
+uint64_t hgfacade_launch_count(void *h) {
+	hgb_ctx *ctx = static_cast<RefCtx *>(h)->scene->GetDeviceContext();
+	return ctx ? hgb_launch_count(ctx) : 0;
+}
+uint64_t hgfacade_rebuild_count(void *h) {
+	hgb_ctx *ctx = static_cast<RefCtx *>(h)->scene->GetDeviceContext();
+	return ctx ? hgb_rebuild_count(ctx) : 0;
+}
 // the list of the last fused frame, as mtx_idx per entry (parity check of the leg above)
 int hgfacade_read_visible(void *h, uint32_t *out_mtx, int capacity) {
 	auto *c = static_cast<RefCtx *>(h);

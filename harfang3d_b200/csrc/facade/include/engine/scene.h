@@ -373,6 +373,9 @@ public:
 	hgb_ctx *GetDeviceContext() const { return ctx; }
 	int GetDeviceIndex() const { return device; }
 	static void SetDefaultDevice(int device);
+	// Extension: scenes created after this call reserve `slots` free transform slots / display entries on the device (hgb_options.append_slack)
+	// so that nodes spawned at the end of a live scene, and Enable / DisableNode, are applied in place. 0 (default) = off.
+	static void SetDefaultAppendSlack(int slots);
 
 private:
 	friend bool GetNodesMinMax(const std::vector<Node> &, const PipelineResources &, MinMax &);
@@ -458,6 +461,7 @@ private:
 	void EvaluateHostTracks(); // light / camera / material values and nested instance anims of the playing anims (host-side single values)
 	bool EnsureContext() const;
 	void RefreshTRSFromDevice() const;
+	void NoteFreshTransform(uint32_t idx);
 	void RefreshFlagsFromDevice() const;
 	void MarkBulkEdit(); // containers were filled behind the setters' back: everything is re-derived at the next sync
 	void QueueMatrixSet(uint32_t slot, const Mat4 &m, bool is_local);

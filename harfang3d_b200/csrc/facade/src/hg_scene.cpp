@@ -16,6 +16,7 @@
 #include <map>
 #include <mutex>
 #include <thread>
+#include <unordered_map>
 
 namespace hg {
 
@@ -26,6 +27,8 @@ time_ns UnspecifiedAnimTime = INT64_MIN; // scene.cpp: "unspecified" sentinel of
 
 static int g_default_device = 0;
 void Scene::SetDefaultDevice(int device) { g_default_device = device; }
+static int g_default_append_slack = 0;
+void Scene::SetDefaultAppendSlack(int slots) { g_default_append_slack = slots > 0 ? slots : 0; }
 
 // CullModelDisplayLists / ComputeSkinMatrices receive the world-matrix vector, not the scene (render_pipeline.h:584): the vector's
 // address identifies the scene whose device context holds the matrices.
@@ -152,7 +155,10 @@ bool Scene::EnsureContext() const {
 	if (ctx)
 		return true;
 	Scene *self = const_cast<Scene *>(this);
-	self->ctx = hgb_create(device, nullptr);
+	hgb_options opt{};
+	opt.use_graph = 1;
+	opt.append_slack = g_default_append_slack;
+	self->ctx = hgb_create(device, &opt);
 	if (!ctx) {
 		if (!impl->warned_no_device)
 			warn(hgb_last_error()); // no CPU fallback: the per-frame members do nothing without a device
@@ -189,16 +195,18 @@ bool Object::IsValid() const { return scene && scene->IsValidObjectRef(ref); }
 Node Scene::CreateNode(std::string name) {
 	Node_ n;
 	n.name = std::move(name);
-	impl->entries_dirty = true;
-	return {this, nodes.add_ref(std::move(n))};
+	const NodeRef ref = nodes.add_ref(std::move(n));
+	impl->fresh_nodes.insert(ref.idx);
+	impl->touch_entries(ref.idx); // a node behind the last one of the entry tables only appends to them
+	return {this, ref};
 }
 
 void Scene::DestroyNode(NodeRef ref) {
 	if (!nodes.is_valid(ref))
 		return;
 	nodes.remove_ref(ref);
-	impl->topology_dirty = true, impl->topology_reparent_only = false; // children of its transform become roots (a stale parent ref is a root, scene.cpp:268-272)
-	impl->entries_dirty = true;
+	impl->topology_dirty = true, impl->topology_reparent_only = impl->topology_append_only = false; // children of its transform become roots (a stale parent ref is a root, scene.cpp:268-272)
+	impl->touch_entries_all();
 	impl->anims_dirty = true;
 }
 
@@ -254,10 +262,19 @@ bool Scene::IsChildOf(NodeRef node, NodeRef parent) const { // walk up from `nod
 }
 
 // ---- transforms --------------------------------------------------------------------------------------------------------------
+// a transform created since the last sync: the first hierarchy edit of a batch that may be appended in place (SyncEdits)
+void Scene::NoteFreshTransform(uint32_t idx) {
+	impl->fresh_slots.push_back(idx);
+	impl->fresh_set.insert(idx);
+	if (!impl->topology_dirty)
+		impl->topology_append_only = true;
+	impl->topology_reparent_only = false;
+	impl->topology_dirty = true;
+}
+
 Transform Scene::CreateTransform() {
 	const ComponentRef ref = transforms.add_ref(Transform_{});
-	impl->fresh_slots.push_back(ref.idx);
-	impl->topology_dirty = true, impl->topology_reparent_only = false;
+	NoteFreshTransform(ref.idx);
 	return {this, ref};
 }
 
@@ -266,16 +283,15 @@ Transform Scene::CreateTransform(const Vec3 &pos, const Vec3 &rot, const Vec3 &s
 	t.TRS.pos = pos, t.TRS.rot = rot, t.TRS.scl = scl;
 	t.parent = parent;
 	const ComponentRef ref = transforms.add_ref(t);
-	impl->fresh_slots.push_back(ref.idx);
-	impl->topology_dirty = true, impl->topology_reparent_only = false;
+	NoteFreshTransform(ref.idx);
 	return {this, ref};
 }
 
 void Scene::DestroyTransform(ComponentRef ref) {
 	if (transforms.is_valid(ref)) {
 		transforms.remove_ref(ref);
-		impl->topology_dirty = true, impl->topology_reparent_only = false;
-		impl->entries_dirty = true;
+		impl->topology_dirty = true, impl->topology_reparent_only = impl->topology_append_only = false;
+		impl->touch_entries_all();
 		impl->anims_dirty = true;
 	}
 }
@@ -285,9 +301,9 @@ void Scene::MarkBulkEdit() {
 	impl->fresh_slots.clear();
 	for (uint32_t i = transforms.first(); i != transforms.invalid_idx; i = transforms.next(i))
 		impl->fresh_slots.push_back(i);
-	impl->topology_dirty = true, impl->topology_reparent_only = false;
+	impl->topology_dirty = true, impl->topology_reparent_only = impl->topology_append_only = false;
 	impl->trs_all_dirty = true;
-	impl->entries_dirty = true;
+	impl->touch_entries_all();
 	impl->anims_dirty = true;
 }
 
@@ -389,6 +405,9 @@ void Scene::SetTransformParent(ComponentRef ref, const NodeRef &v) {
 		walk = transforms[t.idx].parent;
 	}
 	transforms[ref.idx].parent = v;
+	if (impl->topology_dirty && impl->topology_append_only && impl->fresh_set.count(ref.idx))
+		return; // a fresh transform finds its place: still an append (its parent is read at the sync)
+	impl->topology_append_only = false;
 	if (!impl->topology_dirty) // first hierarchy edit since the last sync: a candidate for the incremental path (hgb_set_parents)
 		impl->topology_reparent_only = true, impl->reparented.clear();
 	if (impl->topology_reparent_only)
@@ -410,8 +429,12 @@ void Scene::SetNodeTransform(NodeRef ref, ComponentRef cref) {
 		return;
 	}
 	nodes[ref.idx].transform = cref;
-	impl->topology_dirty = true, impl->topology_reparent_only = false; // children reach their parent's transform through the parent NODE (scene.cpp:268)
-	impl->entries_dirty = true;
+	if (impl->fresh_nodes.count(ref.idx) && impl->fresh_set.count(cref.idx) && impl->topology_dirty && impl->topology_append_only) {
+		impl->touch_entries(ref.idx); // a node created a moment ago takes a transform created a moment ago: nothing refers to either yet
+		return;
+	}
+	impl->topology_dirty = true, impl->topology_reparent_only = impl->topology_append_only = false; // children reach their parent's transform through the parent NODE (scene.cpp:268)
+	impl->touch_entries_all();
 	impl->anims_dirty = true;
 }
 
@@ -634,7 +657,7 @@ Object Scene::CreateObject(const ModelRef &model, std::vector<Material> material
 void Scene::DestroyObject(ComponentRef ref) {
 	if (objects.is_valid(ref)) {
 		objects.remove_ref(ref);
-		impl->entries_dirty = true;
+		impl->touch_entries_all();
 	}
 }
 
@@ -646,7 +669,7 @@ void Scene::DestroyObject(ComponentRef ref) {
 void Scene::SetObjectModel(ComponentRef ref, const ModelRef &model) {
 	HG_OBJ()
 	objects[ref.idx].model = model;
-	impl->entries_dirty = true;
+	impl->touch_entries_all();
 }
 ModelRef Scene::GetObjectModel(ComponentRef ref) const {
 	HG_OBJ(InvalidModelRef)
@@ -655,7 +678,7 @@ ModelRef Scene::GetObjectModel(ComponentRef ref) const {
 void Scene::SetObjectMaterialCount(ComponentRef ref, size_t count) {
 	HG_OBJ()
 	objects[ref.idx].materials.resize(count);
-	impl->entries_dirty = true;
+	impl->touch_entries_all();
 }
 void Scene::SetObjectMaterial(ComponentRef ref, size_t slot, Material mat) {
 	HG_OBJ()
@@ -664,7 +687,7 @@ void Scene::SetObjectMaterial(ComponentRef ref, size_t slot, Material mat) {
 		return;
 	}
 	objects[ref.idx].materials[slot] = mat;
-	impl->entries_dirty = true;
+	impl->touch_entries_all();
 }
 size_t Scene::GetObjectBoneCount(ComponentRef ref) const {
 	HG_OBJ(0)
@@ -673,7 +696,7 @@ size_t Scene::GetObjectBoneCount(ComponentRef ref) const {
 void Scene::SetObjectBoneCount(ComponentRef ref, size_t count) {
 	HG_OBJ()
 	objects[ref.idx].bones.resize(count);
-	impl->entries_dirty = true;
+	impl->touch_entries_all();
 }
 bool Scene::SetObjectBone(ComponentRef ref, size_t idx, NodeRef bone_node) {
 	HG_OBJ(false)
@@ -682,7 +705,7 @@ bool Scene::SetObjectBone(ComponentRef ref, size_t idx, NodeRef bone_node) {
 		return false;
 	}
 	objects[ref.idx].bones[idx] = bone_node;
-	impl->entries_dirty = true;
+	impl->touch_entries_all();
 	return true;
 }
 NodeRef Scene::GetObjectBone(ComponentRef ref, size_t idx) const {
@@ -702,7 +725,7 @@ void Scene::SetNodeObject(NodeRef ref, ComponentRef cref) {
 		return;
 	}
 	nodes[ref.idx].object = cref;
-	impl->entries_dirty = true;
+	impl->touch_entries(ref.idx);
 }
 
 // ---- animation ---------------------------------------------------------------------------------------------------------------
@@ -1015,6 +1038,68 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 	}
 	impl->topology_reparent_only = false;
 	impl->reparented.clear();
+	if (impl->topology_dirty && impl->topology_append_only && impl->device_slots > 0 && !impl->fresh_slots.empty()) {
+		// only transforms created (and parented) since the last sync: they take free positions of the device's append region
+		uint32_t cap = 0;
+		if (hgb_slot_capacity(ctx, &cap) == 0 && n <= cap) {
+			std::vector<uint32_t> slots, parents;
+			std::vector<float> trs;
+			for (uint32_t i : impl->fresh_slots) {
+				if (!transforms.is_used(i))
+					continue;
+				uint32_t par = HGB_ROOT;
+				const NodeRef pn = transforms[i].parent;
+				if (nodes.is_valid(pn)) {
+					const ComponentRef pt = nodes[pn.idx].transform;
+					if (transforms.is_valid(pt) && pt.idx != i)
+						par = pt.idx;
+				}
+				slots.push_back(i), parents.push_back(par);
+				const float *t9 = &transforms[i].TRS.pos.x;
+				trs.insert(trs.end(), t9, t9 + 9);
+			}
+			// a parent created in the same batch must precede its children: hgb_append_nodes resolves parents in order
+			std::vector<uint32_t> order(slots.size());
+			for (size_t k = 0; k < order.size(); ++k)
+				order[k] = uint32_t(k);
+			{
+				std::unordered_map<uint32_t, uint32_t> at;
+				for (size_t k = 0; k < slots.size(); ++k)
+					at[slots[k]] = uint32_t(k);
+				std::vector<uint8_t> done(slots.size(), 0);
+				std::vector<uint32_t> sorted;
+				sorted.reserve(slots.size());
+				for (size_t k = 0; k < slots.size(); ++k) { // emit the chain of not-yet-emitted fresh ancestors, root first
+					std::vector<uint32_t> chain;
+					uint32_t cur = uint32_t(k);
+					while (!done[cur] && chain.size() <= slots.size()) {
+						chain.push_back(cur);
+						done[cur] = 1;
+						const auto it = at.find(parents[cur]);
+						if (it == at.end())
+							break;
+						cur = it->second;
+					}
+					sorted.insert(sorted.end(), chain.rbegin(), chain.rend());
+				}
+				order.swap(sorted);
+			}
+			std::vector<uint32_t> s2(slots.size()), p2(slots.size());
+			std::vector<float> t2(trs.size());
+			for (size_t k = 0; k < order.size(); ++k) {
+				s2[k] = slots[order[k]], p2[k] = parents[order[k]];
+				memcpy(&t2[k * 9], &trs[size_t(order[k]) * 9], 36);
+			}
+			int rebuilt = 0;
+			if (s2.empty() || (hgb_append_nodes(ctx, uint32_t(s2.size()), s2.data(), p2.data(), t2.data(), &rebuilt) == 0 && !rebuilt)) {
+				impl->topology_dirty = false;
+				impl->device_slots = n;
+				impl->fresh_slots.clear();
+			}
+		}
+	}
+	impl->topology_append_only = false;
+	impl->fresh_set.clear();
 	if (impl->topology_dirty) {
 		RefreshTRSFromDevice(); // sampled values must survive the re-layout: they are re-uploaded below
 		std::vector<uint32_t> parent(n, HGB_ROOT);
@@ -1214,14 +1299,51 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 
 	// fused culling (extension): the device entry tables = every rigid display entry in GetModelDisplayLists order, disabled nodes
 	// flagged instead of skipped, so that Enable/DisableNode only changes a flag
-	if (resources && !impl->frusta.empty() && impl->entries_dirty) {
+	const bool can_fuse = resources && !impl->frusta.empty();
+	const bool append = can_fuse && impl->entries_dirty && impl->entries_append_only && impl->ent_built;
+	if (can_fuse && impl->ent_built && (!impl->entries_dirty || append) && !impl->flag_nodes.empty()) {
+		// Enable / DisableNode since the last sync: the entries of those nodes flip their flag where the kernels read it
+		std::vector<uint32_t> &fn = impl->flag_nodes;
+		std::sort(fn.begin(), fn.end());
+		fn.erase(std::unique(fn.begin(), fn.end()), fn.end());
+		for (uint32_t ni : fn) {
+			if (!nodes.is_used(ni))
+				continue;
+			const uint8_t flag = (nodes[ni].flags & (NF_Disabled | NF_InstanceDisabled)) ? HGB_ENTRY_DISABLED : 0;
+			for (int k = 0; k < 2; ++k) {
+				const auto r = std::equal_range(impl->ent_node[k].begin(), impl->ent_node[k].end(), ni);
+				const uint32_t e0 = uint32_t(r.first - impl->ent_node[k].begin()), e1 = uint32_t(r.second - impl->ent_node[k].begin());
+				if (e0 == e1 || impl->ent_flags[k][e0] == flag)
+					continue;
+				std::fill(impl->ent_flags[k].begin() + e0, impl->ent_flags[k].begin() + e1, flag);
+				check(hgb_set_entry_flags(ctx, k, e0, e1 - e0, impl->ent_flags[k].data() + e0));
+			}
+		}
+	}
+	impl->flag_nodes.clear();
+	if (can_fuse && impl->entries_dirty) {
 		std::vector<float> bounds6;
 		std::vector<uint32_t> base_of_model;
 		build_bounds(*resources, bounds6, base_of_model);
 		std::vector<uint32_t> mtx[2], bidx[2];
+		size_t old_n[2] = {0, 0};
+		if (!append)
+			for (int k = 0; k < 2; ++k)
+				impl->ent[k].clear(), impl->ent_flags[k].clear(), impl->ent_node[k].clear();
 		for (int k = 0; k < 2; ++k)
-			impl->ent[k].clear(), impl->ent_flags[k].clear();
-		for (uint32_t ni = nodes.first(); ni != nodes.invalid_idx; ni = nodes.next(ni)) {
+			old_n[k] = impl->ent[k].size();
+		// an append walks only the nodes behind the last one the tables cover (touch_entries saw no edit below it)
+		uint32_t ni = nodes.first();
+		if (append) {
+			ni = impl->ent_nodes_end;
+			while (ni < nodes.capacity() && !nodes.is_used(ni))
+				++ni;
+			if (ni >= nodes.capacity())
+				ni = nodes.invalid_idx;
+		}
+		uint32_t last_node = append && impl->ent_nodes_end ? impl->ent_nodes_end - 1 : 0;
+		for (; ni != nodes.invalid_idx; ni = nodes.next(ni)) {
+			last_node = ni;
 			const Node_ &node = nodes[ni];
 			if (!transforms.is_valid(node.transform) || !objects.is_valid(node.object))
 				continue;
@@ -1240,19 +1362,42 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 				const int k = GetMaterialBlendMode(obj.materials[mat_idx]) != BM_Opaque ? 1 : 0;
 				impl->ent[k].push_back({&obj.materials[mat_idx], node.transform.idx, mdl_idx, uint16_t(i)});
 				impl->ent_flags[k].push_back(flag);
+				impl->ent_node[k].push_back(ni);
 				mtx[k].push_back(node.transform.idx);
 				bidx[k].push_back(base_of_model[mdl_idx] + uint32_t(i));
 			}
 		}
-		check(hgb_set_bounds(ctx, uint32_t(bounds6.size() / 6), bounds6.data()));
 		static_assert(sizeof(ModelDisplayList) == 16, "the device keeps one 16-byte record per entry");
+		if (!append || bounds6.size() / 6 != impl->ent_bounds_count) {
+			check(hgb_set_bounds(ctx, uint32_t(bounds6.size() / 6), bounds6.data()));
+			impl->ent_bounds_count = bounds6.size() / 6;
+		}
 		for (int k = 0; k < 2; ++k) {
+			if (append) {
+				const uint32_t cnt = uint32_t(mtx[k].size());
+				if (!cnt)
+					continue;
+				int rebuilt = 0;
+				check(hgb_append_display_entries(ctx, k, cnt, mtx[k].data(), bidx[k].data(), impl->ent_flags[k].data() + old_n[k], nullptr, &rebuilt));
+				if (hgb_set_entry_records(ctx, k, uint32_t(old_n[k]), cnt, impl->ent[k].data() + old_n[k])) // the table outgrew its slack: all of them again
+					check(hgb_set_entry_records(ctx, k, 0, uint32_t(impl->ent[k].size()), impl->ent[k].data()));
+				continue;
+			}
 			check(hgb_set_display_entries(ctx, k, uint32_t(mtx[k].size()), mtx[k].data(), bidx[k].data(), impl->ent_flags[k].data(), nullptr));
 			if (!impl->ent[k].empty()) // the display lists themselves: survivors come back as these records (GetVisibleModelDisplayLists)
 				check(hgb_set_entry_records(ctx, k, 0, uint32_t(impl->ent[k].size()), impl->ent[k].data()));
 		}
+		if (!append && g_default_append_slack) // later appends must not re-allocate (and copy) the whole table
+			for (int k = 0; k < 2; ++k) {
+				const size_t want = impl->ent[k].size() + size_t(g_default_append_slack);
+				impl->ent[k].reserve(want), impl->ent_flags[k].reserve(want), impl->ent_node[k].reserve(want);
+			}
+		impl->ent_nodes_end = last_node + 1;
+		impl->ent_built = true;
 		impl->entries_dirty = false;
 	}
+	impl->entries_append_only = false;
+	impl->fresh_nodes.clear();
 	if (impl->enable_state_push && !impl->enable_nodes.empty()) { // the host's flags are the truth right now: tracked nodes take them
 		std::vector<uint32_t> slots;
 		std::vector<uint8_t> dis;
@@ -1277,7 +1422,7 @@ void Scene::SetCullingFrustums(const std::vector<Frustum> &frustums, const Pipel
 		return;
 	}
 	if (impl->resources != &resources || impl->frusta.empty() != frustums.empty())
-		impl->entries_dirty = true;
+		impl->touch_entries_all();
 	impl->resources = &resources;
 	impl->frusta = frustums;
 	impl->views_dirty = true;
@@ -1300,24 +1445,35 @@ bool Scene::GetVisibleModelDisplayLists(uint32_t view, bool transparent, std::ve
 	// is good at) and landed contiguously in a pinned buffer: count and records in one round trip
 	const void *rec = nullptr;
 	uint32_t n = 0;
-	if (hgb_get_visible_records_ptr(ctx, k, view, &rec, &n)) {
+	constexpr uint32_t kChunkRecords = 1u << 16; // 1 MB
+	if (hgb_get_visible_records_begin(ctx, k, view, kChunkRecords, &rec, &n)) {
 		warn(hgb_last_error());
 		return false;
 	}
-	// ModelDisplayList is trivially copyable: size the vector once (a caller that reuses its vector pays no re-initialisation when
-	// the count barely moves) and let the pool copy the contiguous records in
+	// The count is known, the records are still arriving chunk by chunk. ModelDisplayList is trivially copyable: size the vector (a
+	// caller that reuses its vector pays no re-initialisation when the count barely moves) and let the pool copy every chunk the
+	// moment it has landed — the copy into the caller's vector hides behind the link
 	static_assert(std::is_trivially_copyable<ModelDisplayList>::value, "copied with memcpy");
 	const double t1 = now_sec();
 	out.resize(n);
 	const double t2 = now_sec();
 	const uint8_t *src = static_cast<const uint8_t *>(rec);
 	uint8_t *dst = reinterpret_cast<uint8_t *>(out.data());
-	const size_t bytes = size_t(n) * sizeof(ModelDisplayList), chunk = size_t(1) << 20;
+	const size_t bytes = size_t(n) * sizeof(ModelDisplayList), chunk = size_t(kChunkRecords) * sizeof(ModelDisplayList);
 	const uint32_t n_chunks = uint32_t((bytes + chunk - 1) / chunk);
-	GatherPool::get().run(n_chunks, [=](uint32_t c) {
+	hgb_ctx *dev = ctx;
+	std::atomic<int> failed{0};
+	GatherPool::get().run(n_chunks, [=, &failed](uint32_t c) {
+		if (hgb_visible_records_wait(dev, k, c))
+			failed.store(1);
 		const size_t b = size_t(c) * chunk;
 		memcpy(dst + b, src + b, std::min(chunk, bytes - b));
 	});
+	if (failed.load()) {
+		warn("GetVisibleModelDisplayLists: the device copy failed");
+		out.clear();
+		return false;
+	}
 	const double t3 = now_sec();
 	g_visible_breakdown[0] += t1 - t0, g_visible_breakdown[1] += t2 - t1, g_visible_breakdown[2] += t3 - t2;
 	return true;
@@ -1675,7 +1831,7 @@ size_t Scene::GarbageCollect() {
 		if (!trs_used[i]) {
 			transforms.remove_ref(transforms.get_ref(i));
 			++removed;
-			impl->topology_dirty = true, impl->topology_reparent_only = false;
+			impl->topology_dirty = true, impl->topology_reparent_only = impl->topology_append_only = false;
 		}
 		i = nx;
 	}
@@ -1684,7 +1840,7 @@ size_t Scene::GarbageCollect() {
 		if (!obj_used[i]) {
 			objects.remove_ref(objects.get_ref(i));
 			++removed;
-			impl->entries_dirty = true;
+			impl->touch_entries_all();
 		}
 		i = nx;
 	}

@@ -202,6 +202,7 @@ void Scene::EnableNode_(NodeRef ref, bool through_instance) {
 		return;
 	}
 	nodes[ref.idx].flags &= through_instance ? ~NF_InstanceDisabled : ~NF_Disabled;
+	impl->flag_nodes.push_back(ref.idx);
 	if (nodes[ref.idx].flags & (NF_Disabled | NF_InstanceDisabled)) // instance content comes back only when the host is fully enabled
 		return;
 	const auto i = node_instance_view.find(ref);
@@ -215,6 +216,7 @@ void Scene::DisableNode_(NodeRef ref, bool through_instance) {
 		return;
 	}
 	nodes[ref.idx].flags |= through_instance ? NF_InstanceDisabled : NF_Disabled;
+	impl->flag_nodes.push_back(ref.idx);
 	const auto i = node_instance_view.find(ref);
 	if (i != node_instance_view.end())
 		for (const NodeRef &n : i->second.nodes)
@@ -222,14 +224,12 @@ void Scene::DisableNode_(NodeRef ref, bool through_instance) {
 }
 void Scene::EnableNode(NodeRef ref) {
 	RefreshFlagsFromDevice(); // device-evaluated "Enable" tracks first: this explicit call lands after them
-	EnableNode_(ref, false);
-	impl->entries_dirty = true;
+	EnableNode_(ref, false); // the entries of the flipped nodes change their flag in place at the next sync (flag_nodes)
 	impl->enable_state_push = true;
 }
 void Scene::DisableNode(NodeRef ref) {
 	RefreshFlagsFromDevice();
 	DisableNode_(ref, false);
-	impl->entries_dirty = true;
 	impl->enable_state_push = true;
 }
 

@@ -3,6 +3,7 @@
 #include "engine/scene.h"
 #include <map>
 #include <string>
+#include <unordered_set>
 #include <vector>
 
 namespace hg {
@@ -11,6 +12,27 @@ struct Scene::Impl {
 	bool topology_dirty{true};
 	bool topology_reparent_only{false}; // since the last sync the only hierarchy edits were SetTransformParent calls on `reparented`
 	std::vector<uint32_t> reparented;
+	// In-place spawning (hgb_options.append_slack, Scene::SetDefaultAppendSlack): while the only hierarchy edits since the last sync are
+	// CreateTransform calls and SetTransformParent / SetNodeTransform on those fresh transforms, the sync appends them (hgb_append_nodes)
+	// instead of re-sorting the hierarchy; while the only display-list edits touch nodes behind the last node of the entry tables, it
+	// appends their entries; Enable / DisableNode flips entry flags in place.
+	bool topology_append_only{false};
+	bool entries_append_only{false};
+	uint32_t ent_nodes_end{0};               // node slots [0, ent_nodes_end) were walked by the last entry-table build
+	bool ent_built{false};
+	size_t ent_bounds_count{0};              // bounds rows the device holds
+	std::vector<uint32_t> ent_node[2];       // node index of every entry (ascending): a node's entries are found by binary search
+	std::vector<uint32_t> flag_nodes;        // nodes whose enabled state may have flipped since the last sync
+	std::unordered_set<uint32_t> fresh_set;  // = fresh_slots
+	std::unordered_set<uint32_t> fresh_nodes;
+	void touch_entries(uint32_t node_idx) {  // an edit that changes the display entries of ONE node
+		if (!entries_dirty)
+			entries_append_only = true;
+		if (node_idx < ent_nodes_end)
+			entries_append_only = false;
+		entries_dirty = true;
+	}
+	void touch_entries_all() { entries_dirty = true, entries_append_only = false; }
 	bool trs_all_dirty{true};
 	std::vector<uint32_t> dirty_trs;
 	bool anims_dirty{true};

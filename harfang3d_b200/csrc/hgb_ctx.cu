@@ -115,6 +115,9 @@ struct EntryTable {
 	DBuf records, records_out;       // optional: one opaque 16-byte record per entry (hgb_set_entry_records) and the gathered survivors
 	uint32_t n_records = 0;
 	HBuf records_h;                  // pinned landing zone of hgb_get_visible_records_ptr
+	cudaEvent_t rec_count_ev = nullptr; // pipelined fetch: count known / chunk i landed
+	std::vector<cudaEvent_t> rec_ev;
+	uint32_t rec_chunks = 0;
 	uint32_t last_count[kMaxViews] = {}; // what the host last read: sizes the next one-round-trip fetch (fetch_visible)
 	DBuf ticket, status;             // compaction scratch (per view slices)
 	uint32_t n_tiles = 0;
@@ -144,6 +147,7 @@ struct hgb_ctx {
 	cudaStream_t own_stream = nullptr, stream = nullptr;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	uint64_t launches = 0;
+	uint64_t rebuilds = 0; // depth sorts + table rebuilds + graph captures so far (hgb_rebuild_count)
 	Prof prof;
 
 	// topology (host)
@@ -454,6 +458,10 @@ void hgb_destroy(hgb_ctx *c) {
 	for (auto &t : c->ent) {
 		DBuf *eb[] = {&t.mtx_pos, &t.meta, &t.view_d, &t.vis[0], &t.vis[1], &t.counts, &t.ticket, &t.status, &t.records, &t.records_out};
 		t.records_h.release();
+		if (t.rec_count_ev)
+			cudaEventDestroy(t.rec_count_ev);
+		for (cudaEvent_t e : t.rec_ev)
+			cudaEventDestroy(e);
 		for (DBuf *b : eb)
 			b->release();
 		for (auto &o : t.out)
@@ -501,6 +509,7 @@ int hgb_sync(hgb_ctx *c) {
 }
 
 uint64_t hgb_launch_count(hgb_ctx *c) { return c ? c->launches : 0; }
+uint64_t hgb_rebuild_count(hgb_ctx *c) { return c ? c->rebuilds : 0; }
 uint32_t hgb_level_count(hgb_ctx *c) { return c && !c->level_off.empty() ? uint32_t(c->level_off.size() - 1) : 0; }
 int hgb_is_identity_order(hgb_ctx *c) { return c && c->identity ? 1 : 0; }
 

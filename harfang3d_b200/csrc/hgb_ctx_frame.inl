@@ -354,6 +354,7 @@ static int launch_phase_graph(hgb_ctx *c, int phase_idx, int phase_mask, cudaStr
 		if (e != cudaSuccess)
 			return fail("frame phase capture: %s", cudaGetErrorString(e));
 		CK(cudaGraphInstantiate(&c->phase_exec[phase_idx][par], g, 0));
+		++c->rebuilds;
 		cudaGraphDestroy(g);
 		c->phase_kernels[phase_idx][par] = k;
 		c->phase_valid[phase_idx][par] = true;
@@ -399,6 +400,7 @@ static int launch_frame_graph(hgb_ctx *c, bool fused) {
 		if (e != cudaSuccess)
 			return fail("cudaStreamEndCapture: %s", cudaGetErrorString(e));
 		CK(cudaGraphInstantiate(&c->graph_exec[f][par], g, 0));
+		++c->rebuilds;
 		cudaGraphDestroy(g);
 		c->graph_kernels[f][par] = k;
 		c->graph_valid[f][par] = true;
@@ -679,7 +681,7 @@ static int resolve_objects(hgb_ctx *c) {
 		const uint32_t sl = c->obj_slot_h[i];
 		uint32_t p = kRoot;
 		if (sl != HGB_ROOT) {
-			if (sl >= c->n_slots || c->pos_of_slot[sl] >= c->n_pos)
+			if (sl >= c->n_slots || !pos_is_live(c, c->pos_of_slot[sl]))
 				return fail("hgb_minmax: object %u references slot %u which is not a live transform", i, sl);
 			p = c->pos_of_slot[sl];
 		}
@@ -810,11 +812,19 @@ int hgb_get_sort_keys(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_keys, u
 }
 
 // ---- getters -------------------------------------------------------------------------------------------------------------
+// slots the device arrays hold: the topology's slot count plus the append slack of the last depth sort (hgb_append_nodes takes free slots below it)
+int hgb_slot_capacity(hgb_ctx *c, uint32_t *out_capacity) {
+	if (!c)
+		return fail("null context");
+	*out_capacity = slot_limit(c);
+	return 0;
+}
+
 int hgb_get_worlds(hgb_ctx *c, uint32_t first, uint32_t count, float *out12, int previous) {
 	if (!c)
 		return fail("null context");
 	join_post(c);
-	if (uint64_t(first) + count > c->n_slots)
+	if (uint64_t(first) + count > slot_limit(c))
 		return fail("hgb_get_worlds: range outside the topology");
 	if (!count)
 		return 0;
@@ -837,7 +847,7 @@ int hgb_get_trs(hgb_ctx *c, uint32_t first, uint32_t count, float *out9) {
 	if (!c)
 		return fail("null context");
 	join_post(c);
-	if (uint64_t(first) + count > c->n_slots)
+	if (uint64_t(first) + count > slot_limit(c))
 		return fail("hgb_get_trs: range outside the topology");
 	if (!count)
 		return 0;
@@ -948,45 +958,81 @@ int hgb_set_entry_records(hgb_ctx *c, int kind, uint32_t first, uint32_t count, 
 	return 0;
 }
 
-// The visible list of (kind, view) as the 16-byte records of the surviving entries, in order, in a pinned buffer owned by the context
-// (valid until the next call for this kind). Gathered on the device, one round trip like hgb_get_visible_ptr.
-int hgb_get_visible_records_ptr(hgb_ctx *c, int kind, uint32_t view, const void **out_rec16, uint32_t *out_count) {
+// Pipelined form: the records land in chunks of `chunk_records`, each with its own event, so the caller copies chunk i out of the pinned
+// buffer while chunk i + 1 is still on the link. Returns once the COUNT is known (one short wait behind the frame's tail); chunk i is
+// complete when hgb_visible_records_wait(ctx, kind, i) returns (callable from any thread). The size guess follows the last count; a
+// list that outgrew it gets its remaining chunks issued before this returns.
+int hgb_get_visible_records_begin(hgb_ctx *c, int kind, uint32_t view, uint32_t chunk_records, const void **out_rec16, uint32_t *out_count) {
 	if (!c)
 		return fail("null context");
 	join_post(c);
 	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews))
-		return fail("hgb_get_visible_records_ptr: bad kind/view");
+		return fail("hgb_get_visible_records: bad kind/view");
+	if (chunk_records < 1024)
+		return fail("hgb_get_visible_records: chunks of at least 1024 records");
 	EntryTable &t = c->ent[kind];
 	*out_count = 0;
 	*out_rec16 = nullptr;
+	t.rec_chunks = 0;
 	if (!t.n)
 		return 0;
 	if (t.n_records != t.n || !t.records.p)
-		return fail("hgb_get_visible_records_ptr: no records for this table (hgb_set_entry_records)");
+		return fail("hgb_get_visible_records: no records for this table (hgb_set_entry_records)");
 	CK(cudaSetDevice(c->device));
-	CK(t.records_out.reserve(size_t(t.n) * 16));
-	CK(t.records_h.reserve(size_t(t.n) * 16));
+	const uint32_t max_chunks = (t.n + chunk_records - 1) / chunk_records;
+	CK(t.records_out.reserve(size_t(max_chunks) * chunk_records * 16)); // whole chunks travel: the tail of the last one is scratch
+	CK(t.records_h.reserve(size_t(max_chunks) * chunk_records * 16));
 	CK(c->count_h.reserve(64));
+	if (!t.rec_count_ev)
+		CK(cudaEventCreateWithFlags(&t.rec_count_ev, cudaEventDisableTiming));
 	uint32_t *cnt = c->count_h.as<uint32_t>();
 	k_gather_records<<<148 * 8, 256, 0, c->stream>>>(t.records.as<uint4>(), t.out[view].as<uint32_t>(), t.counts.as<uint32_t>() + view, t.n, t.records_out.as<uint4>());
 	++c->launches;
 	CK(cudaGetLastError());
-	const uint64_t want = uint64_t(t.last_count[view]) + t.last_count[view] / 4 + 4096;
-	const uint32_t guess = uint32_t(std::min<uint64_t>(want, t.n));
 	CK(cudaMemcpyAsync(cnt, t.counts.as<uint32_t>() + view, 4, cudaMemcpyDeviceToHost, c->stream));
-	CK(cudaMemcpyAsync(t.records_h.p, t.records_out.p, size_t(guess) * 16, cudaMemcpyDeviceToHost, c->stream));
-	CK(cudaStreamSynchronize(c->stream));
+	CK(cudaEventRecord(t.rec_count_ev, c->stream));
+	auto issue = [&](uint32_t upto) -> int { // chunks [t.rec_chunks, upto)
+		while (t.rec_ev.size() < upto) {
+			cudaEvent_t e = nullptr;
+			CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+			t.rec_ev.push_back(e);
+		}
+		for (uint32_t i = t.rec_chunks; i < upto; ++i) {
+			const size_t off = size_t(i) * chunk_records * 16;
+			CK(cudaMemcpyAsync(static_cast<uint8_t *>(t.records_h.p) + off, t.records_out.as<uint8_t>() + off, size_t(chunk_records) * 16, cudaMemcpyDeviceToHost, c->stream));
+			CK(cudaEventRecord(t.rec_ev[i], c->stream));
+		}
+		t.rec_chunks = std::max(t.rec_chunks, upto);
+		return 0;
+	};
+	const uint64_t want = uint64_t(t.last_count[view]) + t.last_count[view] / 32 + 1024; // 16 bytes a record: a tighter guess than the index fetch
+	const uint32_t guess_chunks = uint32_t(std::min<uint64_t>((want + chunk_records - 1) / chunk_records, max_chunks));
+	if (issue(guess_chunks))
+		return 1;
+	CK(cudaEventSynchronize(t.rec_count_ev));
 	const uint32_t n = *cnt;
 	if (n > t.n)
-		return fail("hgb_get_visible_records_ptr: internal error (count %u > entries %u)", n, t.n);
-	if (n > guess) {
-		CK(cudaMemcpyAsync(static_cast<uint8_t *>(t.records_h.p) + size_t(guess) * 16, t.records_out.as<uint8_t>() + size_t(guess) * 16, size_t(n - guess) * 16,
-			cudaMemcpyDeviceToHost, c->stream));
-		CK(cudaStreamSynchronize(c->stream));
-	}
+		return fail("hgb_get_visible_records: internal error (count %u > entries %u)", n, t.n);
+	if (issue((n + chunk_records - 1) / chunk_records))
+		return 1;
 	t.last_count[view] = n;
 	*out_count = n;
 	*out_rec16 = t.records_h.p;
+	return 0;
+}
+
+int hgb_visible_records_wait(hgb_ctx *c, int kind, uint32_t chunk) {
+	if (!c || (kind != 0 && kind != 1) || chunk >= c->ent[kind].rec_chunks)
+		return 1; // (no message: may be called from worker threads)
+	return cudaEventSynchronize(c->ent[kind].rec_ev[chunk]) == cudaSuccess ? 0 : 1;
+}
+
+// The visible list of (kind, view) as the 16-byte records of the surviving entries, in order, in a pinned buffer owned by the context
+// (valid until the next call for this kind). Gathered on the device, one round trip like hgb_get_visible_ptr.
+int hgb_get_visible_records_ptr(hgb_ctx *c, int kind, uint32_t view, const void **out_rec16, uint32_t *out_count) {
+	if (hgb_get_visible_records_begin(c, kind, view, 1u << 16, out_rec16, out_count))
+		return 1;
+	CK(cudaStreamSynchronize(c->stream));
 	return 0;
 }
 

@@ -89,6 +89,8 @@ static void snapshot_parents(const hgb_ctx *c, std::vector<uint32_t> &parent, st
 	}
 }
 static inline bool pos_is_live(const hgb_ctx *c, uint32_t pos) { return c->append_slack ? (pos < c->cap_slots && c->live_h[pos]) : pos < c->n_pos; }
+// slots a range call may name: the topology's, or — with append slack — every slot the device arrays hold (rows of free slots are scratch)
+static inline uint32_t slot_limit(const hgb_ctx *c) { return std::max(c->n_slots, c->cap_slots); }
 
 extern "C" {
 
@@ -98,6 +100,7 @@ int hgb_set_topology(hgb_ctx *c, uint32_t n, const uint32_t *parent_slot, const 
 	join_post(c);
 	if (fold_enable_state(c)) // the tiles are about to be rebuilt
 		return 1;
+	++c->rebuilds;
 	c->en_resolved = false;
 	if (n >= 0x00ffffffu)
 		return fail("hgb_set_topology: %u slots exceeds the reference's vector_list capacity (2^24-1, foundation/vector_list.h:40)", n);
@@ -534,8 +537,8 @@ int hgb_upload_trs(hgb_ctx *c, uint32_t first, uint32_t count, const float *trs9
 	if (!c)
 		return fail("null context");
 	join_post(c);
-	if (uint64_t(first) + count > c->n_slots)
-		return fail("hgb_upload_trs: range [%u,%u) outside the %u slots of the topology", first, first + count, c->n_slots);
+	if (uint64_t(first) + count > slot_limit(c))
+		return fail("hgb_upload_trs: range [%u,%u) outside the %u slots of the topology", first, first + count, slot_limit(c));
 	if (!count)
 		return 0;
 	CK(cudaSetDevice(c->device));
@@ -583,7 +586,7 @@ int hgb_set_matrices(hgb_ctx *c, uint32_t n, const uint32_t *slot, const float *
 		return 1;
 	std::vector<uint32_t> pos(n);
 	for (uint32_t i = 0; i < n; ++i) {
-		if (slot[i] >= c->n_slots || c->pos_of_slot[slot[i]] >= c->n_pos)
+		if (slot[i] >= c->n_slots || !pos_is_live(c, c->pos_of_slot[slot[i]]))
 			return fail("hgb_set_matrices: slot %u is not a live transform", slot[i]);
 		pos[i] = c->pos_of_slot[slot[i]];
 	}
@@ -1065,6 +1068,7 @@ static int prepare_tables(hgb_ctx *c) {
 	if (!c->entries_dirty)
 		return 0;
 	CK(cudaSetDevice(c->device));
+	++c->rebuilds;
 	join_post(c); // the tables are about to be rebuilt
 	if (fold_enable_state(c))
 		return 1;

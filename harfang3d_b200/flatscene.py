@@ -109,6 +109,9 @@ def load():
     _sig(L, "hgfacade_read_visible", c_i, [c_p, c_p, c_i])
     _sig(L, "hgfacade_set_default_device", None, [c_i])
     _sig(L, "hgfacade_visible_breakdown", None, [c_p])
+    _sig(L, "hgfacade_set_default_append_slack", None, [c_i])
+    _sig(L, "hgfacade_launch_count", C.c_uint64, [c_p])
+    _sig(L, "hgfacade_rebuild_count", C.c_uint64, [c_p])
     return L
 
 

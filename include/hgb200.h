@@ -110,6 +110,7 @@ int hgb_append_nodes(hgb_ctx *, uint32_t n, const uint32_t *slot, const uint32_t
 int hgb_remove_nodes(hgb_ctx *, uint32_t n, const uint32_t *slot, int *out_rebuilt /* nullable */);
 int hgb_append_display_entries(hgb_ctx *, int kind, uint32_t n, const uint32_t *mtx_slot, const uint32_t *bounds_idx, const uint8_t *flags /* nullable */,
 	const uint16_t *view /* nullable */, int *out_rebuilt /* nullable */);
+int hgb_slot_capacity(hgb_ctx *, uint32_t *out_capacity); /* slots the device arrays hold (topology + append slack) */
 /* TRS of slots [first, first+count) — dirty-range upload. */
 int hgb_upload_trs(hgb_ctx *, uint32_t first, uint32_t count, const float *trs9);
 /* SetNodeWorldMatrix overrides (scene.cpp:768-786) for the NEXT hgb_update only. */
@@ -206,6 +207,11 @@ int hgb_get_visible_ptr(hgb_ctx *, int kind, uint32_t view, const uint32_t **out
  * gathered on the device, one round trip, pinned buffer owned by the context (valid until the next call for this kind). */
 int hgb_set_entry_records(hgb_ctx *, int kind, uint32_t first, uint32_t count, const void *rec16); /* contiguous from 0: the whole table, or the tail behind the records already set */
 int hgb_get_visible_records_ptr(hgb_ctx *, int kind, uint32_t view, const void **out_rec16, uint32_t *out_count);
+/* ... pipelined: returns as soon as the count is known; the records arrive in chunks of `chunk_records` (>= 1024), chunk i has landed in the
+ * pinned buffer when hgb_visible_records_wait(ctx, kind, i) returns 0 (callable from any thread), so a caller copies chunk i into its own
+ * container while chunk i + 1 is still on the link (the facade's GetVisibleModelDisplayLists does). */
+int hgb_get_visible_records_begin(hgb_ctx *, int kind, uint32_t view, uint32_t chunk_records, const void **out_rec16, uint32_t *out_count);
+int hgb_visible_records_wait(hgb_ctx *, int kind, uint32_t chunk);
 /* instance mode: exclusive offsets of every instance's survivors inside the kind-0 list, n_instances+1 values */
 int hgb_get_instance_offsets(hgb_ctx *, uint32_t *out_offsets);
 int hgb_get_bone_matrices(hgb_ctx *, float *out16, int previous);
@@ -241,6 +247,7 @@ int hgb_peer_result(hgb_ctx *, uint32_t *out_rank_off, uint32_t *out_idx /* null
 /* device pointers: 0 worlds, 1 previous worlds, 2 visible list (kind 0, view 0), 3 visible count (kind 0, view 0), 4 bone matrices,
  * 5 instance offsets, 6 TRS SoA, 7 gathered visible list (peer gather destination), 8 its rank offsets */
 void *hgb_device_ptr(hgb_ctx *, int which);
+uint64_t hgb_rebuild_count(hgb_ctx *);  /* depth sorts + entry / track table rebuilds + graph captures so far: an in-place edit leaves it unchanged */
 uint64_t hgb_launch_count(hgb_ctx *);   /* kernels launched by this context so far (graph launches count their kernel nodes) */
 uint32_t hgb_level_count(hgb_ctx *);
 int hgb_is_identity_order(hgb_ctx *);   /* 1 when slot order already is the depth-sorted order (no shuffle kernels needed) */

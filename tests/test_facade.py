@@ -617,3 +617,59 @@ def test_facade_scene_instances_match_reference(fac, ref, tmp_path):
         counts.append(same(frame))
     assert counts[15] < counts[5] and counts[25] == counts[5]  # the instantiated objects left and came back
     a.close(); b.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.ref
+def test_facade_fused_lists_and_in_place_edits(fac, ref):
+    """The fused path a HARFANG user calls — SetCullingFrustums, Scene::Update(dt), GetVisibleModelDisplayLists — returns the list
+    GetModelDisplayLists + CullModelDisplayLists leave behind in the reference, frame after frame; with append slack, nodes spawned at the
+    end of the live scene (CreateNode + CreateTransform + SetParent + CreateObject) and Enable / DisableNode reach the device in place:
+    no depth sort, no table rebuild, no graph capture (launch count), same worlds and lists as the reference."""
+    rng = np.random.default_rng(131)
+    fs = scenegen.static_scene(6_000, 5, 6, n_models=2, seed=131)
+    nodes = np.sort(rng.choice(fs.n, 1_500, replace=False)).astype(np.int32)
+    scenegen.add_position_tracks(fs, nodes, rng, n_keys=10)
+    fac.hgfacade_set_default_append_slack(1024)
+    try:
+        a, b = RefScene(ref, fs), RefScene(fac, fs)
+    finally:
+        fac.hgfacade_set_default_append_slack(0)
+    fr = np.ascontiguousarray(hostmirror.scene_frusta(fs)[0])
+    out3, n_all = np.zeros(3), [fs.n]
+
+    def frame_and_compare():
+        a.update(scenegen.FRAME_DT)
+        nv = fac.hgfacade_time_fused_frames(b.h, 1, scenegen.FRAME_DT, P(fr), P(out3))
+        got = np.zeros(max(nv, 1), np.uint32)
+        assert fac.hgfacade_read_visible(b.h, P(got), len(got)) == nv
+        _, mtx_ref = a.cull(0, fr)
+        assert nv == len(mtx_ref) and (got[:nv] == mtx_ref).all()
+        assert (bits(a.worlds()[: n_all[0]]) == bits(b.worlds()[: n_all[0]])).all()
+        return nv
+
+    for _ in range(3):
+        assert frame_and_compare() > 0
+    # spawn 200 objects under random nodes, 40 of them under nodes of the same batch
+    k = 200
+    parent = rng.integers(0, fs.n, k).astype(np.int32)
+    parent[160:] = fs.n + rng.integers(0, 160, 40)
+    trs = scenegen.random_trs(rng, k, parent)
+    trs[:, 6:9] = rng.uniform(0.8, 1.25, (k, 3))
+    model = rng.integers(0, 2, k).astype(np.int32)
+    for L_, s in ((ref, a), (fac, b)):
+        L_.hgref_add_nodes(s.h, k, P(np.ascontiguousarray(trs)), P(parent), None, P(model), P(np.ones(k, np.uint8)), P(np.zeros(k, np.uint32)), None)
+    n_all[0] = fs.n + k
+    before = fac.hgfacade_rebuild_count(b.h)
+    for _ in range(2):
+        frame_and_compare()
+    for nd in list(rng.choice(fs.n + k, 30, replace=False)):  # flag flips on live tables
+        for L_, s in ((ref, a), (fac, b)):
+            L_.hgref_enable_node(s.h, int(nd), 0)
+    frame_and_compare()
+    for nd in range(0, fs.n, 400):
+        for L_, s in ((ref, a), (fac, b)):
+            L_.hgref_enable_node(s.h, int(nd), 1)
+    frame_and_compare()
+    assert fac.hgfacade_rebuild_count(b.h) == before, "in-place edits must not re-sort, rebuild tables or capture graphs"
+    a.close(); b.close()

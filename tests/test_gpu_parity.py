@@ -870,7 +870,7 @@ def test_append_and_remove_nodes_in_place(hgb, oracles):
                         oracle_lib.P(np.ones(k, np.uint8)), oracle_lib.P(np.zeros(k, np.uint32)), None)
     slots = np.arange(n0, n0 + k, dtype=np.uint32)
     par_slot = np.where(parent >= 0, parent, 0xFFFFFFFF).astype(np.uint32)
-    before = ctx.launch_count
+    before, rebuilds = ctx.launch_count, ctx.rebuild_count
     assert ctx.append_nodes(slots, par_slot, trs) is False
     assert ctx.append_display_entries(0, t2["ent0_mtx_slot"][n_old_ent:], t2["ent0_bounds_idx"][n_old_ent:], t2["ent0_flags"][n_old_ent:]) is False
     assert plain.append_nodes(slots, par_slot, trs) is True
@@ -899,6 +899,7 @@ def test_append_and_remove_nodes_in_place(hgb, oracles):
     check_visible(ctx, t2, orc, fr)
     check_visible(plain, t2, orc, fr)
     assert ctx.launch_count - before < 16 + 40 + 8
+    assert ctx.rebuild_count == rebuilds
 
     # ---- despawn: childless nodes of the append region and of the sorted part
     has_child = np.zeros(n0 + k, bool)
@@ -921,7 +922,7 @@ def test_append_and_remove_nodes_in_place(hgb, oracles):
         assert (bits(plain.get_worlds())[live] == bits(w_ref)[live]).all()
         check_visible(ctx, t2, orc, fr)
         check_visible(plain, t2, orc, fr)
-    assert ctx.launch_count - before < 12
+    assert ctx.launch_count - before < 12 and ctx.rebuild_count == rebuilds
     # the stand-alone cull reads the entry tables: the removed nodes' entries are disabled there as well
     ctx.update(None, fused_cull=False); ctx.cull(); orc.update(0)
     check_visible(ctx, t2, orc, fr)
