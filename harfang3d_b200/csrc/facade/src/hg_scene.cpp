@@ -196,7 +196,7 @@ Node Scene::CreateNode(std::string name) {
 	Node_ n;
 	n.name = std::move(name);
 	const NodeRef ref = nodes.add_ref(std::move(n));
-	impl->fresh_nodes.insert(ref.idx);
+	Impl::stamp(impl->node_epoch, ref.idx, impl->epoch);
 	impl->touch_entries(ref.idx); // a node behind the last one of the entry tables only appends to them
 	return {this, ref};
 }
@@ -265,7 +265,7 @@ bool Scene::IsChildOf(NodeRef node, NodeRef parent) const { // walk up from `nod
 // a transform created since the last sync: the first hierarchy edit of a batch that may be appended in place (SyncEdits)
 void Scene::NoteFreshTransform(uint32_t idx) {
 	impl->fresh_slots.push_back(idx);
-	impl->fresh_set.insert(idx);
+	Impl::stamp(impl->slot_epoch, idx, impl->epoch);
 	if (!impl->topology_dirty)
 		impl->topology_append_only = true;
 	impl->topology_reparent_only = false;
@@ -405,7 +405,7 @@ void Scene::SetTransformParent(ComponentRef ref, const NodeRef &v) {
 		walk = transforms[t.idx].parent;
 	}
 	transforms[ref.idx].parent = v;
-	if (impl->topology_dirty && impl->topology_append_only && impl->fresh_set.count(ref.idx))
+	if (impl->topology_dirty && impl->topology_append_only && impl->fresh_slot(ref.idx))
 		return; // a fresh transform finds its place: still an append (its parent is read at the sync)
 	impl->topology_append_only = false;
 	if (!impl->topology_dirty) // first hierarchy edit since the last sync: a candidate for the incremental path (hgb_set_parents)
@@ -429,7 +429,7 @@ void Scene::SetNodeTransform(NodeRef ref, ComponentRef cref) {
 		return;
 	}
 	nodes[ref.idx].transform = cref;
-	if (impl->fresh_nodes.count(ref.idx) && impl->fresh_set.count(cref.idx) && impl->topology_dirty && impl->topology_append_only) {
+	if (impl->fresh_node(ref.idx) && impl->fresh_slot(cref.idx) && impl->topology_dirty && impl->topology_append_only) {
 		impl->touch_entries(ref.idx); // a node created a moment ago takes a transform created a moment ago: nothing refers to either yet
 		return;
 	}
@@ -1099,7 +1099,6 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 		}
 	}
 	impl->topology_append_only = false;
-	impl->fresh_set.clear();
 	if (impl->topology_dirty) {
 		RefreshTRSFromDevice(); // sampled values must survive the re-layout: they are re-uploaded below
 		std::vector<uint32_t> parent(n, HGB_ROOT);
@@ -1397,7 +1396,7 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 		impl->entries_dirty = false;
 	}
 	impl->entries_append_only = false;
-	impl->fresh_nodes.clear();
+	++impl->epoch; // nothing created before this sync counts as fresh any more
 	if (impl->enable_state_push && !impl->enable_nodes.empty()) { // the host's flags are the truth right now: tracked nodes take them
 		std::vector<uint32_t> slots;
 		std::vector<uint8_t> dis;

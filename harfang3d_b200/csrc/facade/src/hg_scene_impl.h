@@ -3,7 +3,6 @@
 #include "engine/scene.h"
 #include <map>
 #include <string>
-#include <unordered_set>
 #include <vector>
 
 namespace hg {
@@ -23,8 +22,16 @@ struct Scene::Impl {
 	size_t ent_bounds_count{0};              // bounds rows the device holds
 	std::vector<uint32_t> ent_node[2];       // node index of every entry (ascending): a node's entries are found by binary search
 	std::vector<uint32_t> flag_nodes;        // nodes whose enabled state may have flipped since the last sync
-	std::unordered_set<uint32_t> fresh_set;  // = fresh_slots
-	std::unordered_set<uint32_t> fresh_nodes;
+	// "created since the last sync": an epoch stamp per transform slot / node slot (no per-sync clearing, O(1) lookup)
+	uint32_t epoch{1};
+	std::vector<uint32_t> slot_epoch, node_epoch;
+	static void stamp(std::vector<uint32_t> &v, uint32_t idx, uint32_t e) {
+		if (idx >= v.size())
+			v.resize(size_t(idx) + 1 + v.size() / 2, 0u);
+		v[idx] = e;
+	}
+	bool fresh_slot(uint32_t idx) const { return idx < slot_epoch.size() && slot_epoch[idx] == epoch; }
+	bool fresh_node(uint32_t idx) const { return idx < node_epoch.size() && node_epoch[idx] == epoch; }
 	void touch_entries(uint32_t node_idx) {  // an edit that changes the display entries of ONE node
 		if (!entries_dirty)
 			entries_append_only = true;
