@@ -135,6 +135,7 @@ static void check(int rc) {
 
 Scene::Scene() : impl(new Impl) {
 	device = g_default_device;
+	impl->append_slack = g_default_append_slack;
 	std::lock_guard<std::mutex> lock(g_registry_mutex);
 	g_registry[&transform_worlds] = this;
 	g_registry[&previous_transform_worlds] = this;
@@ -157,7 +158,7 @@ bool Scene::EnsureContext() const {
 	Scene *self = const_cast<Scene *>(this);
 	hgb_options opt{};
 	opt.use_graph = 1;
-	opt.append_slack = g_default_append_slack;
+	opt.append_slack = impl->append_slack; // the default in force when the scene was created
 	self->ctx = hgb_create(device, &opt);
 	if (!ctx) {
 		if (!impl->warned_no_device)
@@ -1386,9 +1387,9 @@ bool Scene::SyncEdits(const PipelineResources *resources) {
 			if (!impl->ent[k].empty()) // the display lists themselves: survivors come back as these records (GetVisibleModelDisplayLists)
 				check(hgb_set_entry_records(ctx, k, 0, uint32_t(impl->ent[k].size()), impl->ent[k].data()));
 		}
-		if (!append && g_default_append_slack) // later appends must not re-allocate (and copy) the whole table
+		if (!append && impl->append_slack) // later appends must not re-allocate (and copy) the whole table
 			for (int k = 0; k < 2; ++k) {
-				const size_t want = impl->ent[k].size() + size_t(g_default_append_slack);
+				const size_t want = impl->ent[k].size() + size_t(impl->append_slack);
 				impl->ent[k].reserve(want), impl->ent_flags[k].reserve(want), impl->ent_node[k].reserve(want);
 			}
 		impl->ent_nodes_end = last_node + 1;

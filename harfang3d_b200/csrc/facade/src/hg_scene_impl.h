@@ -15,6 +15,7 @@ struct Scene::Impl {
 	// CreateTransform calls and SetTransformParent / SetNodeTransform on those fresh transforms, the sync appends them (hgb_append_nodes)
 	// instead of re-sorting the hierarchy; while the only display-list edits touch nodes behind the last node of the entry tables, it
 	// appends their entries; Enable / DisableNode flips entry flags in place.
+	int append_slack{0};                     // Scene::SetDefaultAppendSlack at construction
 	bool topology_append_only{false};
 	bool entries_append_only{false};
 	uint32_t ent_nodes_end{0};               // node slots [0, ent_nodes_end) were walked by the last entry-table build

@@ -661,15 +661,19 @@ def test_facade_fused_lists_and_in_place_edits(fac, ref):
         L_.hgref_add_nodes(s.h, k, P(np.ascontiguousarray(trs)), P(parent), None, P(model), P(np.ones(k, np.uint8)), P(np.zeros(k, np.uint32)), None)
     n_all[0] = fs.n + k
     before = fac.hgfacade_rebuild_count(b.h)
+    counts = []
     for _ in range(2):
         frame_and_compare()
+        counts.append(fac.hgfacade_rebuild_count(b.h))
     for nd in list(rng.choice(fs.n + k, 30, replace=False)):  # flag flips on live tables
         for L_, s in ((ref, a), (fac, b)):
             L_.hgref_enable_node(s.h, int(nd), 0)
     frame_and_compare()
+    counts.append(fac.hgfacade_rebuild_count(b.h))
     for nd in range(0, fs.n, 400):
         for L_, s in ((ref, a), (fac, b)):
             L_.hgref_enable_node(s.h, int(nd), 1)
     frame_and_compare()
-    assert fac.hgfacade_rebuild_count(b.h) == before, "in-place edits must not re-sort, rebuild tables or capture graphs"
+    counts.append(fac.hgfacade_rebuild_count(b.h))
+    assert counts == [before] * 4, "in-place edits must not re-sort, rebuild tables or capture graphs: %d -> %s" % (before, counts)
     a.close(); b.close()
