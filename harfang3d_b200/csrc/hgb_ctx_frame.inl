@@ -890,7 +890,7 @@ static int fetch_visible(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_idx,
 	CK(cudaSetDevice(c->device));
 	CK(c->count_h.reserve(64));
 	uint32_t *cnt = c->count_h.as<uint32_t>();
-	const uint64_t want = uint64_t(t.last_count[view]) + t.last_count[view] / 4 + 4096;
+	const uint64_t want = uint64_t(t.last_count[view]) + t.last_count[view] / 16 + 4096; // a frame rarely moves the count by more than a few per cent
 	const uint32_t guess = uint32_t(std::min<uint64_t>(std::min<uint64_t>(want, capacity), t.n));
 	CK(cudaMemcpyAsync(cnt, t.counts.as<uint32_t>() + view, 4, cudaMemcpyDeviceToHost, c->stream));
 	if (guess)
