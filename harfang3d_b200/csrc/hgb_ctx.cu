@@ -14,6 +14,8 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <unordered_map>
+#include <array>
 
 using namespace hgb;
 
@@ -147,6 +149,8 @@ struct hgb_ctx {
 	cudaStream_t own_stream = nullptr, stream = nullptr;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	uint64_t launches = 0;
+	bool in_post_phase = false;   // enqueue_frame_kernels is recording the frame's asynchronous tail
+	uint32_t compact_ctas = 148;  // persistent CTAs of the tail's compaction (HGB_COMPACT_CTAS; 0 = one CTA per tile)
 	uint64_t rebuilds = 0; // depth sorts + table rebuilds + graph captures so far (hgb_rebuild_count)
 	Prof prof;
 
@@ -179,6 +183,9 @@ struct hgb_ctx {
 	std::vector<uint32_t> child_cnt_h; // per position: live children
 	std::vector<uint8_t> has_entry_h;  // per position: rows 10 / 11 hold an entry
 	DBuf edit_d;                       // scratch of the in-place edit kernels
+	// removed transforms: entries [0, tomb[slot][kind]) of that slot's display entries belonged to the node that was removed and stay
+	// disabled for good, also when the slot is handed out again and the tables are rebuilt from the host arrays
+	std::unordered_map<uint32_t, std::array<uint32_t, 2>> tomb;
 	uint32_t slice_nodes = 0;          // >0: with the overlapped sampler, big levels are cut into slices of this many positions (multiple of 256)
 	uint32_t persistent_ctas = 148 * 6; // resident CTAs of the device for the persistent level kernel
 	uint32_t lookahead = 0; // positions (see SceneDev::lookahead)
@@ -385,6 +392,13 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 		c->slice_nodes = (uint32_t(opt->slice_nodes) + 255u) & ~255u;
 	if (opt && opt->append_slack > 0)
 		c->append_slack = uint32_t(opt->append_slack);
+	if (const char *e = getenv("HGB_COMPACT_CTAS"))
+		c->compact_ctas = uint32_t(atoi(e));
+	else {
+		cudaDeviceProp prop{};
+		if (cudaGetDeviceProperties(&prop, device) == cudaSuccess)
+			c->compact_ctas = uint32_t(prop.multiProcessorCount);
+	}
 	if (opt && opt->async_post != 0)
 		c->async_post = opt->async_post > 0; // 0 = default (on), 1 = on, -1 = off
 	if (const char *e_ap = getenv("HGB_ASYNC_POST"))

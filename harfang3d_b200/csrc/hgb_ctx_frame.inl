@@ -102,7 +102,9 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 				d.out2_step = static_cast<const uint32_t *>(c->peer.mailbox) + 1;
 			}
 			prof_begin(c, HGB_K_COMPACT);
-			launch_after(c, chained, k_compact, dim3(t.n_tiles), dim3(kCompactThreads), d);
+			// hidden behind the next frame (asynchronous tail): a few persistent CTAs, so that the level kernels keep the SMs
+			const uint32_t grid = (c->in_post_phase && c->compact_ctas) ? std::min(t.n_tiles, c->compact_ctas) : t.n_tiles;
+			launch_after(c, chained, k_compact, dim3(grid), dim3(kCompactThreads), d);
 			prof_end(c);
 			++*n_k;
 		}
@@ -192,8 +194,12 @@ static int enqueue_frame_kernels(hgb_ctx *c, bool fused, bool with_preset, uint6
 	// in ONE stream-ordered sequence (the whole frame, or the tail on stream2), and none of them can see another frame's step.
 	if (c->peer.on && fused && (phases & kPhasePost))
 		peer_enqueue_begin(c, n_k);
-	if (phases == kPhasePost)
-		return do_post ? enqueue_compaction(c, n_k, true) : 0;
+	if (phases == kPhasePost) {
+		c->in_post_phase = true;
+		const int rc = do_post ? enqueue_compaction(c, n_k, true) : 0;
+		c->in_post_phase = false;
+		return rc;
+	}
 	const bool has_anim = c->n_tracks && c->n_play;
 	AnimDev a{};
 	if (has_anim) {

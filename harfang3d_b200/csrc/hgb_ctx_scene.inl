@@ -382,6 +382,7 @@ int hgb_append_nodes(hgb_ctx *c, uint32_t n, const uint32_t *slot, const uint32_
 	CK(cudaSetDevice(c->device));
 	std::vector<NodeWrite> w;
 	w.reserve(n);
+	auto level_of = [&](uint32_t pos) { return uint32_t(std::upper_bound(c->level_off.begin(), c->level_off.end(), pos) - c->level_off.begin()) - 1u; };
 	bool fast = c->append_slack && c->tiles.p;
 	uint32_t n_slots = c->n_slots;
 	for (uint32_t i = 0; i < n && fast; ++i) {
@@ -399,7 +400,14 @@ int hgb_append_nodes(hgb_ctx *c, uint32_t n, const uint32_t *slot, const uint32_
 		const bool root = ps == HGB_ROOT || ps >= c->cap_slots || !c->live_h[c->pos_of_slot[ps]] || ps == slot[i];
 		const uint32_t par = root ? kRoot : c->pos_of_slot[ps];
 		uint8_t depth = 0;
-		if (!root && par >= c->n_pos) {
+		if (p < c->n_pos) {
+			// the slot of a node removed from the SORTED part: its position belongs to a level, so the new node may only hang below a
+			// node of an earlier level (whose row is final when this level runs) or be a root
+			if (!root && (par >= c->n_pos || level_of(par) >= level_of(p))) {
+				fast = false;
+				break;
+			}
+		} else if (!root && par >= c->n_pos) {
 			if (c->late_depth_h[par] + 1 >= kMaxWalk) {
 				fast = false;
 				break;
@@ -473,6 +481,8 @@ int hgb_remove_nodes(hgb_ctx *c, uint32_t n, const uint32_t *slot, int *out_rebu
 	for (uint32_t i = 0; i < n; ++i)
 		if (slot[i] >= c->n_slots || !pos_is_live(c, c->pos_of_slot[slot[i]]))
 			return fail("hgb_remove_nodes: slot %u is not a live transform", slot[i]);
+	for (uint32_t i = 0; i < n; ++i) // the display entries these nodes own today are dead from here on (prepare_tables)
+		c->tomb[slot[i]] = {c->ent[0].n, c->ent[1].n};
 	bool fast = c->append_slack != 0;
 	std::vector<uint32_t> pos;
 	if (fast) { // children removed earlier in the batch no longer count
@@ -508,8 +518,7 @@ int hgb_remove_nodes(hgb_ctx *c, uint32_t n, const uint32_t *slot, int *out_rebu
 	for (uint32_t p : pos) {
 		c->parent_pos_h[p] = p >= c->n_pos ? kDead : kRoot;
 		c->late_depth_h[p] = 0;
-		if (p >= c->n_pos)
-			c->has_entry_h[p] = 0;
+		c->has_entry_h[p] = 0; // (a retired position of the sorted part keeps a disabled entry in its row until a new node overwrites it)
 	}
 	if (edit_upload(c, c->edit_d, pos.data(), pos.size() * 4))
 		return 1;
@@ -684,6 +693,10 @@ int hgb_set_display_entries(hgb_ctx *c, int kind, uint32_t n, const uint32_t *mt
 	t.n = n;
 	t.n_dev = n + c->append_slack; // free entries behind the table for hgb_append_display_entries
 	t.n_records = 0;
+	for (auto it = c->tomb.begin(); it != c->tomb.end();) { // a new table: nothing in it belongs to a removed node
+		it->second[kind] = 0;
+		it = (it->second[0] | it->second[1]) ? std::next(it) : c->tomb.erase(it);
+	}
 	if (c->append_slack) { // appended entries must not re-allocate 16M-element host arrays
 		t.mtx_slot.reserve(t.n_dev), t.bounds_idx.reserve(t.n_dev), t.flags.reserve(t.n_dev);
 		if (view)
@@ -1096,6 +1109,11 @@ static int prepare_tables(hgb_ctx *c) {
 			mtx_pos[e] = c->pos_of_slot[t.mtx_slot[e]];
 			if (!pos_is_live(c, mtx_pos[e])) // its node was removed (hgb_remove_nodes) or never existed: the entry stays, disabled
 				t.flags[e] |= HGB_ENTRY_DISABLED;
+			else if (!c->tomb.empty()) { // ... also when the slot has been handed out again since
+				const auto it = c->tomb.find(t.mtx_slot[e]);
+				if (it != c->tomb.end() && e < it->second[k])
+					t.flags[e] |= HGB_ENTRY_DISABLED;
+			}
 			meta[e] = t.bounds_idx[e] | (uint32_t(t.flags[e] & HGB_ENTRY_DISABLED ? 1 : 0) << 24);
 			++ent_off[mtx_pos[e] + 1];
 		}

@@ -427,10 +427,19 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact(CompactDev c) {
 	// visibility bytes are complete (both are no-ops in a plain launch)
 	asm volatile("griddepcontrol.launch_dependents;");
 	asm volatile("griddepcontrol.wait;" ::: "memory");
+	// A CTA takes tiles by ticket until none is left. One tile per CTA (grid = tiles) is the fastest form when the compaction is on the
+	// frame's critical path; as the asynchronous tail of the frame it is launched with a FEW persistent CTAs instead (hgb_ctx:
+	// compact_ctas), because a full grid of 32 KB CTAs on the high-priority stream takes the shared memory of every SM away from the
+	// level kernels of the next frame for as long as its stores to the gather destination are held up by the fabric.
+	const uint32_t n_tiles = (c.n + kCompactTile - 1) / kCompactTile;
+	for (;;) {
+	__syncthreads(); // s_tile / s_list of the previous tile are no longer read
 	if (threadIdx.x == 0)
 		s_tile = atomicAdd(c.ticket, 1u);
 	__syncthreads();
 	const uint32_t tile = s_tile;
+	if (tile >= n_tiles)
+		break;
 	const uint32_t base = tile * kCompactTile + threadIdx.x * kCompactItems;
 
 	// 32 flags per thread, two 128-bit loads (vis buffers are padded to a tile multiple and zero-filled); bit `c.bit` of every byte is
@@ -530,6 +539,7 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact(CompactDev c) {
 		for (uint32_t i = threadIdx.x; i < tile_total; i += kCompactThreads)
 			c.out[prefix + i] = s_list[i];
 	}
+	} // next tile
 }
 
 // ---- all views of an entry table in ONE pass -----------------------------------------------------------------------------------------

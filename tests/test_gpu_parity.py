@@ -933,6 +933,17 @@ def test_append_and_remove_nodes_in_place(hgb, oracles):
     ppar = rng.integers(0, n0, 40).astype(np.uint32)
     ppar[np.isin(ppar, gone)] = 0
     assert ctx.append_nodes(back, ppar, ptrs) is False
+    # a slot freed in the SORTED part is taken again in place when the new parent sits in an earlier level (here: a root) ...
+    depth0 = np.zeros(n0, np.int32)
+    for i in range(n0):
+        depth0[i] = depth0[fs.parent[i]] + 1 if fs.parent[i] >= 0 else 0
+    srt = gone[80:100]  # despawned slots of the sorted part (childless nodes: deeper than level 0)
+    assert (depth0[srt] > 0).all()
+    strs = scenegen.random_trs(rng, 20, np.zeros(20, np.int32))
+    roots0 = np.nonzero(fs.parent < 0)[0]
+    spar = rng.choice(roots0, 20).astype(np.uint32)
+    assert ctx.append_nodes(srt, spar, strs) is False
+    back = np.concatenate([back, srt]); ptrs = np.concatenate([ptrs, strs]); ppar = np.concatenate([ppar, spar])
     chain = np.arange(n0 + k, n0 + k + 14, dtype=np.uint32)
     cpar = np.concatenate([[5], chain[:-1]]).astype(np.uint32)
     ctrs = scenegen.random_trs(rng, 14, np.zeros(14, np.int32))
@@ -945,7 +956,8 @@ def test_append_and_remove_nodes_in_place(hgb, oracles):
     scratch = hgb.Context(0)
     par3 = np.where(fs3.parent >= 0, fs3.parent, 0xFFFFFFFF).astype(np.uint32)
     used3 = np.ones(fs3.n, np.uint8)
-    used3[gone[40:]] = 0
+    used3[gone[40:80]] = 0
+    used3[gone[100:]] = 0
     scratch.set_topology(par3, used3)
     scratch.upload_trs(np.ascontiguousarray(fs3.trs, np.float32))
     for _ in range(2):
