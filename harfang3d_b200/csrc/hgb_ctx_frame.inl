@@ -102,8 +102,10 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 				d.out2_step = static_cast<const uint32_t *>(c->peer.mailbox) + 1;
 			}
 			prof_begin(c, HGB_K_COMPACT);
-			// hidden behind the next frame (asynchronous tail): a few persistent CTAs, so that the level kernels keep the SMs
-			const uint32_t grid = (c->in_post_phase && c->compact_ctas) ? std::min(t.n_tiles, c->compact_ctas) : t.n_tiles;
+			// hidden behind the next frame (asynchronous tail): one persistent CTA per SM, so that the level kernels keep the SMs
+			// (only with the peer gather, whose stores the fabric can hold up: measured at N = 4 0.488 -> 0.480 ms; alone on a GPU the
+			// full grid is faster, 0.461 vs 0.469 ms — profiles/README.md r02)
+			const uint32_t grid = (c->in_post_phase && c->peer.on && c->compact_ctas) ? std::min(t.n_tiles, c->compact_ctas) : t.n_tiles;
 			launch_after(c, chained, k_compact, dim3(grid), dim3(kCompactThreads), d);
 			prof_end(c);
 			++*n_k;
