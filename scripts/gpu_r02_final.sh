@@ -10,7 +10,7 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smok
 timeout 700 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
 timeout 600 python bench.py --impl reference --steps 6 --warmup 2 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; cat gpurun_out/bench_ref.json
 for w in c1 c2 c3 c5; do
-  timeout 600 python bench.py --workload $w --no-cpu-baseline > gpurun_out/bench_${w}_n1.json 2> gpurun_out/bench_${w}_n1.err; echo "$w exit $?"
+  timeout 600 python bench.py --workload $w > gpurun_out/bench_${w}_n1.json 2> gpurun_out/bench_${w}_n1.err; echo "$w exit $?"
 done
 timeout 600 python scripts/edit_cost.py > gpurun_out/edit_cost.json 2> gpurun_out/edit_cost.err
 B="python bench.py --steps 3 --warmup 3 --no-cpu-baseline"

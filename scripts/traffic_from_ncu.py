@@ -8,6 +8,7 @@ k_update_top; its DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum, summ
 roofline.traffic beside the algorithmic bytes of the same frame."""
 import csv
 import json
+import re
 import subprocess
 import sys
 
@@ -23,7 +24,8 @@ def rows(rep):
     out = []
     for x in r[2:]:
         f = lambda k: float(x[col[k]].replace(",", ""))
-        out.append({"kernel": x[col["Kernel Name"]].split("(")[0].split("<")[0].replace("void hgb::", "").replace("hgb::", ""), "time_s": f("gpu__time_duration.sum") * 1e-9,
+        m = re.search(r"(k_[a-z0-9_]+)", x[col["Kernel Name"]])
+        out.append({"kernel": m.group(1) if m else x[col["Kernel Name"]], "time_s": f("gpu__time_duration.sum") * 1e-9,
                     "dram_read": f("dram__bytes_read.sum"), "dram_write": f("dram__bytes_write.sum"), "grid": x[col["Grid Size"]], "block": x[col["Block Size"]]})
     return out
 
@@ -38,7 +40,8 @@ def main():
     doc = {
         "capture": label,
         "source": "ncu --set full --clock-control none of `python bench.py --steps 3 --warmup 3 --no-cpu-baseline` (c4 workload); one frame = 1 k_update_top + %d k_update_level launches" % len(levels),
-        "k_update_level_bytes_per_launch_sum_per_step": sum(r["dram_read"] + r["dram_write"] for r in levels),
+        # what bench.py quotes as roofline.traffic: every launch of the level path of one frame (k_update_top + k_update_level)
+        "k_update_level_bytes_per_launch_sum_per_step": sum(r["dram_read"] + r["dram_write"] for r in frame),
         "k_update_top_bytes_per_step": sum(r["dram_read"] + r["dram_write"] for r in frame if r["kernel"] == "k_update_top"),
         "frame_launches": [{k: r[k] for k in ("kernel", "grid", "block", "time_s", "dram_read", "dram_write")} for r in frame],
         "k_update_level_last_level": {k: last[k] for k in ("dram_read", "dram_write", "time_s")},
