@@ -130,7 +130,7 @@ class Context:
 
     def __init__(self, device=0, use_graph=True, row_store=False, lookahead=0, tma_level=False, top_walk=0, overlap_sampler=False, slice_nodes=0, async_post=None, append_slack=0):
         """row_store=True: world rows are stored per thread (3 x 16 B at a 48-byte stride) instead of through the shared-memory
-        transpose — an A/B switch for profiling (hgb_options.reserved[0])"""
+        transpose — an A/B switch for profiling (hgb_options.row_store)"""
         self._L = lib()
         # async_post: None = the library default (on; HGB_ASYNC_POST=0/1 in the environment overrides), True / False = forced
         opt = (C.c_int * 9)(1 if use_graph else 0, 1 if row_store else 0, lookahead, 1 if tma_level else 0, (0 if async_post is None else (1 if async_post else -1)), top_walk, 1 if overlap_sampler else 0, slice_nodes, append_slack)  # lookahead: 0 default, -1 off, n positions

@@ -1,6 +1,6 @@
 """Seeded synthetic scenes for the BASELINE.json configs, as flat numpy arrays ("FlatScene").
 
-A FlatScene is a neutral description: tests feed the SAME arrays to the reference (through oracle/ref_driver.cpp, using the
+A FlatScene is a neutral description: tests feed the SAME arrays to the reference (through the flat binding csrc/facade/flat/hg_flat.cpp, using the
 reference's public Scene API) and to the product (through hostmirror.upload -> C ABI). Node i owns transform slot i, which is how
 the reference numbers them when nodes are created in order (vector_list LIFO free list, foundation/vector_list.h:182-218).
 Workload definitions follow SURVEY.md §8(d).

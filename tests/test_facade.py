@@ -1,5 +1,6 @@
 """The hg::Scene facade (harfang3d_b200/csrc/facade) driven through the SAME flat driver that drives the reference
-(oracle/ref_driver.cpp compiled twice: against /root/reference -> oracle/_ref, against the facade headers -> oracle/_facade).
+(harfang3d_b200/csrc/facade/flat/hg_flat.cpp compiled twice: against /root/reference -> oracle/_ref/libhg_ref.so, against the facade
+headers -> harfang3d_b200/libhg_facade_flat.so).
 
 CPU tests: the host-side half of the facade — slot containers, refs, GetModelDisplayLists — needs no GPU and must match the
 reference's behaviour (harfang/tests/engine/scene.cpp:115-154, foundation/vector_list.h).
@@ -24,7 +25,7 @@ G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 def fac():
     L = oracle_lib.load_facade_driver()
     if L is None:
-        pytest.skip("oracle/_facade/libhg_facade_driver.so not built (make -C harfang3d_b200 facade && make -C oracle facade_driver)")
+        pytest.skip("harfang3d_b200/libhg_facade_flat.so not built (make -C harfang3d_b200 facade)")
     return L
 
 
