@@ -43,6 +43,7 @@ SIGNATURES = {
     "hgb_set_topology": (_i, [_p, _u32, _p, _p]),
     "hgb_upload_trs": (_i, [_p, _u32, _u32, _p]),
     "hgb_set_parents": (_i, [_p, _u32, _p, _p, _p]),
+    "hgb_compact_visible_noalloc": (_i, [_i, _p, _u32, _u32, _p, _u32, _p, _p]),
     "hgb_append_nodes": (_i, [_p, _u32, _p, _p, _p, _p]),
     "hgb_slot_capacity": (_i, [_p, _p]),
     "hgb_remove_nodes": (_i, [_p, _u32, _p, _p]),
@@ -123,6 +124,17 @@ def _ptr(a, dtype, what):
     if not isinstance(a, np.ndarray) or a.dtype != np.dtype(dtype) or not a.flags["C_CONTIGUOUS"]:
         raise TypeError("%s must be a C-contiguous numpy array of dtype %s" % (what, np.dtype(dtype)))
     return a.ctypes.data_as(C.c_void_p)
+
+
+NOALLOC_MAX_ENTRIES = 1 << 24
+
+
+def compact_visible_noalloc(device, d_vis, n, view_bit, d_out, out_capacity, d_count, stream=None):
+    """hgb_compact_visible_noalloc: device POINTERS (ints) of the caller's buffers; enqueues on `stream` (cudaStream_t as int, None =
+    default stream) and returns — synchronise before reading. Allocates nothing; n <= NOALLOC_MAX_ENTRIES."""
+    L = lib()
+    if L.hgb_compact_visible_noalloc(device, C.c_void_p(d_vis), n, view_bit, C.c_void_p(d_out), out_capacity, C.c_void_p(d_count), C.c_void_p(stream or 0)):
+        raise HgbError(L.hgb_last_error().decode())
 
 
 class Context:

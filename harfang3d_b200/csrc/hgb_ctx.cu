@@ -31,6 +31,9 @@ static int fail(const char *fmt, ...) {
 	return 1;
 }
 
+// error text of entry points that live in other translation units of the library (hgb_noalloc.cu); not exported
+extern "C" __attribute__((visibility("hidden"))) void hgbi_set_error(const char *msg) { g_err = msg ? msg : ""; }
+
 #define CK(call)                                                                                                                                               \
 	do {                                                                                                                                                       \
 		cudaError_t e_ = (call);                                                                                                                               \

@@ -247,6 +247,21 @@ int hgb_peer_result(hgb_ctx *, uint32_t *out_rank_off, uint32_t *out_idx /* null
 /* device pointers: 0 worlds, 1 previous worlds, 2 visible list (kind 0, view 0), 3 visible count (kind 0, view 0), 4 bone matrices,
  * 5 instance offsets, 6 TRS SoA, 7 gathered visible list (peer gather destination), 8 its rank offsets */
 void *hgb_device_ptr(hgb_ctx *, int which);
+/* ---- allocation-free entry point ----
+ * No counterpart in the reference; added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it). Order-preserving compaction of one view's bit of a
+ * visibility-byte array — what k_compact does behind hgb_update / hgb_cull — on the CALLER's device buffers: d_vis[n] (one byte per
+ * entry, bit v set = survives view v; 16-byte aligned, no padding needed), d_out[out_capacity] receives the surviving entry indices in
+ * ascending order (writes stop at out_capacity), *d_count the total number of survivors (may exceed out_capacity). Enqueued on
+ * `cuda_stream` (cudaStream_t, NULL = default stream) of `device`, which it makes current; returns once enqueued — synchronise the
+ * stream before reading. Calls no cudaMalloc / cudaFree / allocating routine: the kernel's scratch (tile ticket + look-back status words)
+ * is a static __device__ array of 8.25 KB that every GPU loading the library holds until exit, which bounds n at
+ * HGB_NOALLOC_MAX_ENTRIES (larger n is refused with an error). All calls on a device SHARE that array: each call clears what it uses on
+ * its stream, so back-to-back calls on one stream are fine, but calls whose GPU work overlaps (different streams or threads) race. */
+#define HGB_NOALLOC_MAX_ENTRIES (1u << 24)
+int hgb_compact_visible_noalloc(int device, const uint8_t *d_vis, uint32_t n, uint32_t view_bit, uint32_t *d_out, uint32_t out_capacity, uint32_t *d_count,
+	void *cuda_stream);
+
 uint64_t hgb_rebuild_count(hgb_ctx *);  /* depth sorts + entry / track table rebuilds + graph captures so far: an in-place edit leaves it unchanged */
 uint64_t hgb_launch_count(hgb_ctx *);   /* kernels launched by this context so far (graph launches count their kernel nodes) */
 uint32_t hgb_level_count(hgb_ctx *);
