@@ -90,6 +90,7 @@ SIGNATURES = {
     "hgb_device_ptr": (_p, [_p, _i]),
     "hgb_launch_count": (C.c_uint64, [_p]),
     "hgb_rebuild_count": (C.c_uint64, [_p]),
+    "hgb_frame_was_async": (_i, [_p]),
     "hgb_level_count": (_u32, [_p]),
     "hgb_is_identity_order": (_i, [_p]),
     "hgb_time_begin": (_i, [_p]),
@@ -144,7 +145,7 @@ class Context:
         """row_store=True: world rows are stored per thread (3 x 16 B at a 48-byte stride) instead of through the shared-memory
         transpose — an A/B switch for profiling (hgb_options.row_store)"""
         self._L = lib()
-        # async_post: None = the library default (on; HGB_ASYNC_POST=0/1 in the environment overrides), True / False = forced
+        # async_post: None = the library default (chosen per frame; HGB_ASYNC_POST=0/1/2 in the environment overrides), True / False = forced
         opt = (C.c_int * 9)(1 if use_graph else 0, 1 if row_store else 0, lookahead, 1 if tma_level else 0, (0 if async_post is None else (1 if async_post else -1)), top_walk, 1 if overlap_sampler else 0, slice_nodes, append_slack)  # lookahead: 0 default, -1 off, n positions
         self._h = self._L.hgb_create(device, C.cast(opt, C.c_void_p))
         if not self._h:
@@ -441,6 +442,10 @@ class Context:
     @property
     def launch_count(self):
         return self._L.hgb_launch_count(self._h)
+
+    @property
+    def frame_was_async(self):
+        return bool(self._L.hgb_frame_was_async(self._h))
 
     @property
     def rebuild_count(self):

@@ -266,6 +266,14 @@ struct hgb_ctx {
 	bool pdl_first = true; // the first level is chained to the track sampler (HGB_PDL_FIRST=0: plain launch; A/B)
 	bool pdl_late_wait = true; // see SceneDev::late_wait (HGB_PDL_LATE=0: wait ahead of the sampled values, sampler -> first level chained instead; A/B)
 	bool async_post = true;
+	// ... chosen per frame when nobody forced it: a caller that reads the frame's result on the host after EVERY update (a synchronising
+	// getter between two updates) leaves the tail nothing to overlap with, and the one-graph frame — tail chained to the last level by a
+	// programmatic dependency, no cross-stream event — ends sooner. Two such frames in a row switch to it, the first update that finds the
+	// previous result unread switches back.
+	bool async_auto = true;
+	bool result_read = false;     // a result getter synchronised since the last hgb_update
+	uint32_t sync_streak = 0;
+	bool last_frame_async = false;
 	cudaGraphExec_t phase_exec[3][2] = {}; // [phase][world-buffer parity]
 	bool phase_valid[3][2] = {};
 	uint64_t phase_kernels[3][2] = {};
@@ -403,9 +411,9 @@ hgb_ctx *hgb_create(int device, const hgb_options *opt) {
 			c->compact_ctas = uint32_t(prop.multiProcessorCount);
 	}
 	if (opt && opt->async_post != 0)
-		c->async_post = opt->async_post > 0; // 0 = default (on), 1 = on, -1 = off
-	if (const char *e_ap = getenv("HGB_ASYNC_POST"))
-		c->async_post = e_ap[0] != '0';
+		c->async_post = opt->async_post > 0, c->async_auto = false; // 0 = default (chosen per frame), 1 = always, -1 = never
+	if (const char *e_ap = getenv("HGB_ASYNC_POST")) // A/B: 0 never, 1 always, 2 chosen per frame
+		c->async_post = e_ap[0] != '0', c->async_auto = e_ap[0] == '2';
 	if (const char *e_pdl = getenv("HGB_PDL"))
 		c->pdl_levels = e_pdl[0] != '0';
 	if (const char *e_first = getenv("HGB_PDL_FIRST"))
@@ -527,6 +535,7 @@ int hgb_sync(hgb_ctx *c) {
 
 uint64_t hgb_launch_count(hgb_ctx *c) { return c ? c->launches : 0; }
 uint64_t hgb_rebuild_count(hgb_ctx *c) { return c ? c->rebuilds : 0; }
+int hgb_frame_was_async(hgb_ctx *c) { return c && c->last_frame_async ? 1 : 0; }
 uint32_t hgb_level_count(hgb_ctx *c) { return c && !c->level_off.empty() ? uint32_t(c->level_off.size() - 1) : 0; }
 int hgb_is_identity_order(hgb_ctx *c) { return c && c->identity ? 1 : 0; }
 

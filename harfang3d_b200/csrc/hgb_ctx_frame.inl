@@ -74,12 +74,15 @@ static int enqueue_compaction(hgb_ctx *c, uint64_t *n_k, bool with_peer = false,
 			d.status = t.status.as<uint32_t>();
 			d.n_tiles = t.n_tiles;
 			prof_begin(c, HGB_K_COMPACT);
-			if (n_views <= 2)
-				launch_after(c, chained, k_compact_multi<2>, dim3(t.n_tiles), dim3(kCompactThreads), d);
-			else if (n_views <= 4)
-				launch_after(c, chained, k_compact_multi<4>, dim3(t.n_tiles), dim3(kCompactThreads), d);
-			else
-				launch_after(c, chained, k_compact_multi<8>, dim3(t.n_tiles), dim3(kCompactThreads), d);
+			switch (n_views) { // exactly the views there are: an empty view still costs its scans and barriers
+			case 2: launch_after(c, chained, k_compact_multi<2>, dim3(t.n_tiles), dim3(kCompactThreads), d); break;
+			case 3: launch_after(c, chained, k_compact_multi<3>, dim3(t.n_tiles), dim3(kCompactThreads), d); break;
+			case 4: launch_after(c, chained, k_compact_multi<4>, dim3(t.n_tiles), dim3(kCompactThreads), d); break;
+			case 5: launch_after(c, chained, k_compact_multi<5>, dim3(t.n_tiles), dim3(kCompactThreads), d); break;
+			case 6: launch_after(c, chained, k_compact_multi<6>, dim3(t.n_tiles), dim3(kCompactThreads), d); break;
+			case 7: launch_after(c, chained, k_compact_multi<7>, dim3(t.n_tiles), dim3(kCompactThreads), d); break;
+			default: launch_after(c, chained, k_compact_multi<8>, dim3(t.n_tiles), dim3(kCompactThreads), d); break;
+			}
 			prof_end(c);
 			++*n_k;
 			continue;
@@ -464,7 +467,12 @@ int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cul
 	if (!c->en_target_slot_h.empty() && c->n_play)
 		c->en_state_dirty = true;
 	const bool fused = fused_cull != 0;
-	if (c->async_post && c->use_graph && fused && !with_preset && !c->prof.on && (c->ent[0].n_dev || c->ent[1].n_dev || c->peer.on))
+	if (c->async_auto)
+		c->sync_streak = c->result_read ? std::min(c->sync_streak + 1u, 1000u) : 0u;
+	c->result_read = false;
+	c->last_frame_async = c->async_post && !(c->async_auto && c->sync_streak >= 2) && c->use_graph && fused && !with_preset && !c->prof.on &&
+						  (c->ent[0].n_dev || c->ent[1].n_dev || c->peer.on);
+	if (c->last_frame_async)
 		return launch_frame_async(c);
 	join_post(c);
 	if (!c->use_graph || with_preset || c->prof.on) {
@@ -872,6 +880,7 @@ int hgb_get_trs(hgb_ctx *c, uint32_t first, uint32_t count, float *out9) {
 int hgb_get_visible_count(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_count) {
 	if (!c)
 		return fail("null context");
+	c->result_read = true;
 	join_post(c);
 	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews))
 		return fail("hgb_get_visible_count: bad kind/view");
@@ -920,6 +929,7 @@ static int fetch_visible(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_idx,
 int hgb_get_visible(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_idx, uint32_t capacity, uint32_t *out_count) {
 	if (!c)
 		return fail("null context");
+	c->result_read = true;
 	join_post(c);
 	return fetch_visible(c, kind, view, out_idx, capacity, out_count);
 }
@@ -927,6 +937,7 @@ int hgb_get_visible(hgb_ctx *c, int kind, uint32_t view, uint32_t *out_idx, uint
 int hgb_get_visible_ptr(hgb_ctx *c, int kind, uint32_t view, const uint32_t **out_idx, uint32_t *out_count) {
 	if (!c)
 		return fail("null context");
+	c->result_read = true;
 	join_post(c);
 	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews))
 		return fail("hgb_get_visible_ptr: bad kind/view");
@@ -973,6 +984,7 @@ int hgb_set_entry_records(hgb_ctx *c, int kind, uint32_t first, uint32_t count, 
 int hgb_get_visible_records_begin(hgb_ctx *c, int kind, uint32_t view, uint32_t chunk_records, const void **out_rec16, uint32_t *out_count) {
 	if (!c)
 		return fail("null context");
+	c->result_read = true;
 	join_post(c);
 	if ((kind != 0 && kind != 1) || view >= uint32_t(kMaxViews))
 		return fail("hgb_get_visible_records: bad kind/view");
@@ -1047,6 +1059,7 @@ int hgb_get_visible_records_ptr(hgb_ctx *c, int kind, uint32_t view, const void 
 int hgb_get_instance_offsets(hgb_ctx *c, uint32_t *out) {
 	if (!c)
 		return fail("null context");
+	c->result_read = true;
 	join_post(c);
 	if (!c->instance_mode)
 		return fail("hgb_get_instance_offsets: not in instance mode");

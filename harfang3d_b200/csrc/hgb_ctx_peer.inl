@@ -122,6 +122,7 @@ int hgb_peer_status(hgb_ctx *c, uint32_t *out_step, uint32_t *out_error) {
 int hgb_peer_result(hgb_ctx *c, uint32_t *out_rank_off, uint32_t *out_idx, uint32_t idx_capacity, uint32_t *out_aux, uint32_t aux_capacity) {
 	if (!c)
 		return fail("null context");
+	c->result_read = true;
 	join_post(c);
 	Peer &p = c->peer;
 	if (!p.on || p.rank != p.dst)

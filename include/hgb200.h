@@ -52,7 +52,10 @@ typedef struct hgb_options {
 	int async_post;    /* the tail of the frame — compaction of the visible lists and the peer gather — runs as its own graph on a second stream
 	                      and overlaps the NEXT frame's track sampling and level kernels (visibility bytes are double-buffered by world-buffer
 	                      parity; frame N + 2 waits for the tail of frame N, every other entry point joins the pending tails first), so
-	                      results and API semantics are unchanged. 0 = default (on), 1 = on, -1 = off (one graph per frame) */
+	                      results and API semantics are unchanged. 0 = default: chosen per frame — on, unless the caller reads the frame's
+	                      result on the host (hgb_get_visible*, hgb_peer_result, ...) between every two updates, which leaves the tail
+	                      nothing to overlap with: after two such frames the one-graph frame is used (it ends sooner), until an update
+	                      finds the previous result unread. 1 = always on, -1 = off (one graph per frame) */
 	int top_walk;      /* the leading levels of the hierarchy go out as ONE launch (k_update_top: every node recomputes its ancestor chain, no
 	                      dependency between threads). 0 = default budget (levels are added while sum(nodes x depth) <= 250 K: measured best on the 16M-node batch, profiles/README.md r02), -1 = off (one
 	                      launch per level), n = budget in node evaluations */
@@ -262,6 +265,7 @@ void *hgb_device_ptr(hgb_ctx *, int which);
 int hgb_compact_visible_noalloc(int device, const uint8_t *d_vis, uint32_t n, uint32_t view_bit, uint32_t *d_out, uint32_t out_capacity, uint32_t *d_count,
 	void *cuda_stream);
 
+int hgb_frame_was_async(hgb_ctx *);       /* 1: the last hgb_update ran with the asynchronous tail (hgb_options.async_post), 0: as one graph */
 uint64_t hgb_rebuild_count(hgb_ctx *);  /* depth sorts + entry / track table rebuilds + graph captures so far: an in-place edit leaves it unchanged */
 uint64_t hgb_launch_count(hgb_ctx *);   /* kernels launched by this context so far (graph launches count their kernel nodes) */
 uint32_t hgb_level_count(hgb_ctx *);

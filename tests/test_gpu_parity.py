@@ -713,6 +713,42 @@ def test_async_tail_and_one_round_trip_fetch(hgb):
     a.close(); b.close()
 
 
+def test_async_tail_chosen_per_frame(hgb):
+    """hgb_options.async_post = 0 (default): back-to-back updates run with the asynchronous tail; a caller that reads the result after every
+    update gets the one-graph frame from the third such frame on, and the tail comes back with the first update that finds the previous
+    result unread. The lists are the same in every mode."""
+    rng = np.random.default_rng(94)
+    fs = scenegen.static_scene(40_000, 6, 7, n_models=3, seed=94)
+    nodes = np.sort(rng.choice(fs.n, 10_000, replace=False)).astype(np.int32)
+    scenegen.add_position_tracks(fs, nodes, rng, n_keys=12)
+    a, b = hgb.Context(0), hgb.Context(0, async_post=False)
+    ta = hostmirror.upload(a, fs)
+    hostmirror.upload(b, fs, tables=ta)
+    ca, cb = hostmirror.PlayClocks(fs), hostmirror.PlayClocks(fs)
+
+    def frame():
+        a.update(ca.step(scenegen.FRAME_DT), fused_cull=True)
+        b.update(cb.step(scenegen.FRAME_DT), fused_cull=True)
+        return a.frame_was_async
+
+    def same():
+        ia, ib = a.get_visible(0, 0), b.get_visible(0, 0)
+        assert len(ia) == len(ib) and len(ia) > 0 and (ia == ib).all()
+
+    modes = [frame() for _ in range(4)]  # nobody reads: the tail overlaps the next frame
+    assert modes == [True] * 4 and not b.frame_was_async
+    same()
+    modes = []
+    for _ in range(5):  # read after every update
+        modes.append(frame())
+        same()
+    assert modes == [True, False, False, False, False], modes  # (the read before this loop was the first of the streak)
+    modes = [frame() for _ in range(3)]  # the first of these still follows a read
+    assert modes == [False, True, True], modes
+    same()
+    a.close(); b.close()
+
+
 def test_cull_list_rejects_oversized_bounds_table(hgb):
     ctx = hgb.Context(0)
     ctx.set_topology(np.full(4, 0xFFFFFFFF, np.uint32))
@@ -841,7 +877,7 @@ def test_append_and_remove_nodes_in_place(hgb, oracles):
     rng = np.random.default_rng(97)
     fs = scenegen.static_scene(20_000, 6, 7, n_models=2, seed=97)
     n0 = fs.n
-    ctx = hgb.Context(0, append_slack=2048)
+    ctx = hgb.Context(0, append_slack=2048, async_post=True)  # (forced: the launch / rebuild counts below must not see a change of frame mode)
     plain = hgb.Context(0)  # no slack: every edit rebuilds
     t = hostmirror.upload(ctx, fs)
     hostmirror.upload(plain, fs, tables=t)
