@@ -1455,6 +1455,8 @@ bool Scene::GetVisibleModelDisplayLists(uint32_t view, bool transparent, std::ve
 	// moment it has landed — the copy into the caller's vector hides behind the link
 	static_assert(std::is_trivially_copyable<ModelDisplayList>::value, "copied with memcpy");
 	const double t1 = now_sec();
+	if (out.capacity() < n) // a list that grows by a few entries per frame must not re-allocate (and page in) 26 MB every time it does
+		out.reserve(size_t(n) + n / 8 + 1024);
 	out.resize(n);
 	const double t2 = now_sec();
 	const uint8_t *src = static_cast<const uint8_t *>(rec);

@@ -108,6 +108,9 @@ int hgb_set_parents(hgb_ctx *, uint32_t n, const uint32_t *slot, const uint32_t 
  *     component.cpp:184-193): slot, parent slot (or HGB_ROOT) and TRS (9 floats) per node; a slot may be one past the current end.
  *   hgb_remove_nodes: DestroyNode / DestroyTransform + GarbageCollect (scene.cpp:139-237). Display entries of the node are disabled
  *     for good; children of a removed node become roots (scene.cpp:268-272), which is a rebuild.
+ *     Bound tracks are the caller's: a track that targets a removed slot keeps sampling into nothing, but it must be dropped
+ *     (hgb_set_tracks) before that slot is handed out again, or it will drive the new node at the next re-bind — the reference's
+ *     BoundToNodeAnim holds a generational NodeRef that dies with the node (the facade re-binds on DestroyNode).
  *   hgb_append_display_entries: entries behind the last one of a table, same arguments as hgb_set_display_entries. */
 int hgb_append_nodes(hgb_ctx *, uint32_t n, const uint32_t *slot, const uint32_t *parent_slot /* nullable: roots */, const float *trs9, int *out_rebuilt /* nullable */);
 int hgb_remove_nodes(hgb_ctx *, uint32_t n, const uint32_t *slot, int *out_rebuilt /* nullable */);
