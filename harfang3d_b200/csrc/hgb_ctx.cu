@@ -170,7 +170,7 @@ struct hgb_ctx {
 	uint32_t n_tiles = 0;
 	bool transpose_store = true;
 	bool tma_level = false;   // A/B switch: persistent TMA-staged level kernel instead of one thread per node with LDG rows (measured slower: r01c)
-	uint64_t top_budget = 250000;  // k_update_top covers the leading levels whose recomputed work (sum of nodes x depth) stays below this; 0 = one launch per level
+	uint64_t top_budget = 500000;  // k_update_top covers the leading levels whose recomputed work (sum of nodes x depth) stays below this; 0 = one launch per level
 	uint32_t level_block = 128;    // threads per CTA of the level kernel: small CTAs recycle their slots sooner (HGB_LEVEL_BLOCK=256: A/B, +2.5 % frame time)
 	bool multi_compact = true;     // all views of an entry table compacted in one pass (HGB_MULTI_COMPACT=0: one k_compact launch per view; A/B)
 	int level_minb = 6;            // resident CTAs per SM the level kernel's registers are held to (HGB_LEVEL_MINB=5: 48 registers; A/B)

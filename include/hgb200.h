@@ -57,7 +57,7 @@ typedef struct hgb_options {
 	                      nothing to overlap with: after two such frames the one-graph frame is used (it ends sooner), until an update
 	                      finds the previous result unread. 1 = always on, -1 = off (one graph per frame) */
 	int top_walk;      /* the leading levels of the hierarchy go out as ONE launch (k_update_top: every node recomputes its ancestor chain, no
-	                      dependency between threads). 0 = default budget (levels are added while sum(nodes x depth) <= 250 K: measured best on the 16M-node batch, profiles/README.md r02), -1 = off (one
+	                      dependency between threads). 0 = default budget (levels are added while sum(nodes x depth) <= 500 K: on the 16M-node batch the same cut as the 250 K measured best there, one launch fewer on c5 / c3, profiles/README.md r02), -1 = off (one
 	                      launch per level), n = budget in node evaluations */
 	int overlap_sampler; /* 1: tracks are sampled in chunks by target level on a second stream, overlapped with the level kernels. Default 0:
 	                        both kernels lean on HBM, running them together measured 1-8 % slower than back to back (profiles r01c) */
