@@ -470,7 +470,11 @@ int hgb_update(hgb_ctx *c, uint32_t n_play, const int64_t *play_t, int fused_cul
 	if (c->async_auto)
 		c->sync_streak = c->result_read ? std::min(c->sync_streak + 1u, 1000u) : 0u;
 	c->result_read = false;
-	c->last_frame_async = c->async_post && !(c->async_auto && c->sync_streak >= 2) && c->use_graph && fused && !with_preset && !c->prof.on &&
+	// (with the peer gather only for batches of at least 4 M nodes: on a short frame the gather's fixed latencies are longer than the
+	// frame and the tail is better off the frame's stream — measured: c4, 16 M nodes per GPU, e2e + 7 / + 9 / + 25 % at N = 2 / 4 / 8 with
+	// the one-graph frame; c5 strong + 7 % at 8.4 M nodes per GPU, equal at 4.2 M, - 25 % at 2.1 M; profiles/README.md r02)
+	const bool sync_pays = !c->peer.on || c->n_pos >= (4u << 20);
+	c->last_frame_async = c->async_post && !(c->async_auto && c->sync_streak >= 2 && sync_pays) && c->use_graph && fused && !with_preset && !c->prof.on &&
 						  (c->ent[0].n_dev || c->ent[1].n_dev || c->peer.on);
 	if (c->last_frame_async)
 		return launch_frame_async(c);
