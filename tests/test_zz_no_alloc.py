@@ -89,3 +89,23 @@ def test_compact_visible_noalloc_matches_the_context_path():
     # ... and the call after the refusals still works
     out, cnt = run(n, 7, n)
     assert cnt == int(((vis2 >> 7) & 1).sum())
+
+
+def test_compact_visible_noalloc_refusals_need_no_device():
+    """the size / argument checks come before any CUDA call, and without a device the entry point fails loudly (no CPU path)"""
+    buf = np.zeros(64, np.uint8)
+    out = np.zeros(64, np.uint32)
+    cnt = np.zeros(1, np.uint32)
+    aligned = (buf.ctypes.data + 15) & ~15
+    with pytest.raises(capi.HgbError, match="exceed the maximum"):
+        capi.compact_visible_noalloc(0, aligned, capi.NOALLOC_MAX_ENTRIES + 1, 0, out.ctypes.data, 64, cnt.ctypes.data)
+    with pytest.raises(capi.HgbError, match="view bit"):
+        capi.compact_visible_noalloc(0, aligned, 16, 9, out.ctypes.data, 64, cnt.ctypes.data)
+    with pytest.raises(capi.HgbError, match="null buffer"):
+        capi.compact_visible_noalloc(0, aligned, 16, 0, out.ctypes.data, 64, 0)
+    with pytest.raises(capi.HgbError, match="aligned"):
+        capi.compact_visible_noalloc(0, aligned + 1, 16, 0, out.ctypes.data, 64, cnt.ctypes.data)
+    if capi.lib().hgb_device_count() == 0:  # this container: nothing may be computed on the host
+        with pytest.raises(capi.HgbError, match="no CPU path"):
+            capi.compact_visible_noalloc(0, aligned, 16, 0, out.ctypes.data, 64, cnt.ctypes.data)
+        assert (out == 0).all() and cnt[0] == 0
