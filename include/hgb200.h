@@ -55,7 +55,8 @@ typedef struct hgb_options {
 	                      results and API semantics are unchanged. 0 = default: chosen per frame — on, unless the caller reads the frame's
 	                      result on the host (hgb_get_visible*, hgb_peer_result, ...) between every two updates, which leaves the tail
 	                      nothing to overlap with: after two such frames the one-graph frame is used (it ends sooner), until an update
-	                      finds the previous result unread. 1 = always on, -1 = off (one graph per frame) */
+	                      finds the previous result unread (with the peer gather only for batches of >= 4 M nodes: on short frames
+	                      the tail stays on its own stream). 1 = always on, -1 = off (one graph per frame) */
 	int top_walk;      /* the leading levels of the hierarchy go out as ONE launch (k_update_top: every node recomputes its ancestor chain, no
 	                      dependency between threads). 0 = default budget (levels are added while sum(nodes x depth) <= 500 K: on the 16M-node batch the same cut as the 250 K measured best there, one launch fewer on c5 / c3, profiles/README.md r02), -1 = off (one
 	                      launch per level), n = budget in node evaluations */
